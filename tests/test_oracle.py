@@ -1,0 +1,225 @@
+"""CPU tests of the oracle itself: RNG pinned against libstdc++, known-answer tests
+(SURVEY.md section 4), C restatement vs the independent NumPy twin, resampler equivalence."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle import orc, pf_oracle_np as twin
+from pf_monocular_pose_estimator_b200 import scenes as S
+from tests.util import frame_inputs
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ORACLE_DIR = os.path.join(os.path.dirname(HERE), "oracle")
+
+
+def test_rng_pinned_against_libstdcxx():
+    subprocess.check_call(["make", "-C", ORACLE_DIR, "check_rng"], stdout=subprocess.DEVNULL)
+    r = subprocess.run([os.path.join(ORACLE_DIR, "check_rng")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout
+    assert " 0 mismatches" in r.stdout
+
+
+def test_rng_known_answers():
+    # minstd_rand0: the 10000th output from seed 1 is 1043618065 (C++ standard, [rand.predef])
+    assert orc.lib().orc_rng_skip(1, 10000) == 1043618065
+    g = twin.MinStd(1)
+    for _ in range(10000):
+        v = g.next()
+    assert v == 1043618065
+    assert orc.seed_state(0) == 1 and orc.seed_state(2147483647) == 1 and orc.seed_state(2147483648) == 1
+
+
+def test_score_perfect_particle():
+    # KAT (i): particle == true pose, noise-free blobs -> L*(L+1)
+    T = S.true_pose(0.3)
+    uv = S.project(S.K_README, T, S.MARKERS_5)
+    v, pairs = orc.score(S.DEFAULT_PARAMS, uv[::-1].copy(), uv)
+    assert abs(v - 30.0) < 1e-12
+    assert sorted(map(tuple, pairs)) == [(j + 1, 5 - j) for j in range(5)]
+    v2, _ = twin.score(S.DEFAULT_PARAMS, 5, uv[::-1].copy(), uv)
+    assert abs(v2 - 30.0) < 1e-12
+
+
+def test_score_all_leds_on_one_blob():
+    # KAT (ii): L LEDs collapse on one blob: L*L + sum(..)^2 - 3*(1+..+(L-1))
+    proj = np.array([[100.0, 100.0], [100.5, 100.0], [101.0, 100.0], [100.0, 101.5], [102.0, 100.0]])
+    img = np.array([[100.0, 100.0], [300.0, 300.0], [10.0, 20.0], [500.0, 400.0], [600.0, 50.0]])
+    d = np.sqrt(((proj - img[0]) ** 2).sum(1))
+    expect = 25 + (((5 - d) / 5) ** 2).sum() - 3 * (1 + 2 + 3 + 4)
+    v, pairs = orc.score(S.DEFAULT_PARAMS, img, proj)
+    assert abs(v - expect) < 1e-12 and v < 0
+    assert (pairs[:, 1] == 1).all()
+    v2, p2 = twin.score(S.DEFAULT_PARAMS, 5, img, proj)
+    assert abs(v2 - expect) < 1e-12 and (p2 == pairs).all()
+
+
+def test_score_tie_rules_and_downgrade():
+    # duplicated blobs: ties go to the smallest LED, then the smallest blob (Eigen column-major visitor)
+    proj = np.array([[10.0, 10.0], [10.0, 10.0], [50.0, 50.0]])
+    img = np.array([[10.0, 10.0], [10.0, 10.0], [50.0, 53.0], [50.0, 47.0]])
+    p = dict(S.DEFAULT_PARAMS, bMarkerDowngrade=[0, 1, 0, 0, 0])
+    v, pairs = orc.score(p, img, proj)
+    assert pairs.tolist() == [[1, 1], [2, 1], [3, 3]]
+    expect = (3 + 1) + (3 + 1 - 3 - 2) + (3 + ((5 - 3) / 5) ** 2)
+    assert abs(v - expect) < 1e-12
+    v2, p2 = twin.score(p, 3, img, proj)
+    assert abs(v2 - v) < 1e-12 and p2.tolist() == pairs.tolist()
+
+
+def test_score_gate_uses_tol_pf_gain_uses_tol():
+    proj = np.array([[0.0, 0.0]])
+    for d, ok in [(3.999, True), (4.0, True), (4.001, False)]:
+        v, pairs = orc.score(S.DEFAULT_PARAMS, np.array([[d, 0.0]]), proj)
+        assert (len(pairs) == 1) == ok
+        if ok:
+            assert abs(v - (1 + ((5 - d) / 5) ** 2)) < 1e-12
+
+
+def test_score_fewer_blobs_than_leds():
+    T = S.true_pose(0.1)
+    uv = S.project(S.K_README, T, S.MARKERS_5)
+    v, pairs = orc.score(S.DEFAULT_PARAMS, uv[:3].copy(), uv)
+    assert len(pairs) == 3 and abs(v - 18.0) < 1e-12
+    v0, p0 = orc.score(S.DEFAULT_PARAMS, np.zeros((0, 2)), uv)
+    assert v0 == 0 and len(p0) == 0
+
+
+def test_resample_identity_for_uniform_weights():
+    # KAT (iii): uniform weights with r_k = 0.5 -> identity permutation
+    N = 64
+    idx, cnt = orc.resample(np.full(N, 1.0 / N), np.full(N, 0.5), literal=True)
+    assert (idx == np.arange(N)).all() and (cnt == 1).all()
+
+
+@pytest.mark.parametrize("N", [1, 2, 17, 100, 1000, 5000])
+def test_resample_linear_equals_literal(N):
+    rng = np.random.default_rng(N)
+    for trial in range(4):
+        w = rng.uniform(0, 30, N)
+        if trial >= 1:
+            w[rng.uniform(size=N) < 0.5] = 0.0
+        if trial >= 2:
+            w[rng.uniform(size=N) < 0.2] *= -0.3      # negative weights: non-monotone prefix (D4)
+        if trial == 3:
+            w = -w                                    # negative sum flips every sign (Q6)
+        s = w.sum()
+        if s != 0:
+            w = w / s
+        r = rng.uniform(size=N)
+        a = orc.resample(w, r, literal=True)
+        b = orc.resample(w, r, literal=False)
+        assert (a[0] == b[0]).all() and (a[1] == b[1]).all()
+
+
+def test_resample_not_found_keeps_previous_index():
+    # Q7: prefix never reaches u_k -> Particle_index keeps its value, no count
+    w = np.array([0.3, 0.3, 0.0, 0.0])
+    r = np.array([0.0, 0.5, 0.9, 0.9])
+    idx, cnt = orc.resample(w, r, literal=True)
+    assert idx.tolist() == [0, 1, 1, 1] and cnt.tolist() == [1, 1, 0, 0]
+    idx2, cnt2 = orc.resample(w, r, literal=False)
+    assert idx2.tolist() == idx.tolist() and cnt2.tolist() == cnt.tolist()
+
+
+def _compare_with_twin(fi, N):
+    a = orc.pf_update(resampler=0, **{k: v for k, v in fi.items() if k != "truth"})
+    b = twin.pf_update(fi["params"], fi["markers"], fi["K"], fi["img"], fi["E"], fi["T_cur"], fi["T_pred"],
+                       fi["P"], fi["Cm"], fi["isi"], fi["dt"], fi["seed"])
+    assert a["iterations"] == b["iterations"] and a["best_iteration"] == b["best_iteration"]
+    assert a["rng_steps"] == b["rng_steps"]
+    np.testing.assert_allclose(a["T"], b["T"], rtol=0, atol=1e-12)
+    np.testing.assert_allclose(a["w_raw"], b["w_raw"], rtol=0, atol=1e-9)
+    assert a["accepted"] == b["accepted"] and a["resampled"] == b["resampled"]
+    assert a["most_likely_particle_idx"] == b["most_likely_particle_idx"]
+    for n in range(N):
+        assert a["pairs"][n][: 2 * a["npairs"][n]].reshape(-1, 2).tolist() == b["corr"][n].tolist()
+    if a["resampled"]:
+        assert (a["idx"] == b["idx"]).all() and (a["count"] == b["count"]).all()
+        assert a["most_likely_pose_idx"] == b["most_likely_pose_idx"]
+    return a
+
+
+@pytest.mark.parametrize("isi", [1, 2])
+def test_pf_update_c_vs_numpy_twin(isi):
+    N = 60
+    fi = frame_inputs(N, frame=9, isi=isi)
+    a = _compare_with_twin(fi, N)
+    assert a["iterations"] == 1 and a["accepted"] == 1 and a["resampled"] == 1
+    assert a["rng_steps"] == 12 * (N - 2) + 2 * N
+
+
+def test_pf_update_multi_iteration_c_vs_numpy_twin():
+    # one LED occluded + outliers -> max score stays below L*min(5,D) -> all 80 iterations run (D7)
+    N = 12
+    fi = frame_inputs(N, frame=11, occlude=(2,))
+    a = _compare_with_twin(fi, N)
+    assert a["iterations"] == 80 and 0 <= a["best_iteration"] < 80
+    assert a["rng_steps"] == 12 * (N - 2) * 80 + 2 * N
+
+
+def test_pf_update_reject_path():
+    N = 20
+    fi = frame_inputs(N, frame=7)
+    fi["img"] = fi["img"] + 300.0          # no blob anywhere near -> all scores 0
+    a = _compare_with_twin(fi, N)
+    assert a["accepted"] == 0 and a["flag_fail"] == 4.0 and a["resampled"] == 0 and a["iterations"] == 80
+
+
+def test_lie_maps_roundtrip_and_predict():
+    rng = np.random.default_rng(3)
+    for _ in range(20):
+        tw = rng.uniform(-0.5, 0.5, 6)
+        T = orc.exponential_map(tw)
+        np.testing.assert_allclose(T[:3, :3] @ T[:3, :3].T, np.eye(3), atol=1e-12)
+        np.testing.assert_allclose(orc.logarithm_map(T), tw, atol=1e-10)
+    np.testing.assert_allclose(orc.exponential_map(np.zeros(6)), np.eye(4), atol=0)
+    # constant twist motion is extrapolated exactly
+    tw = np.array([0.01, -0.02, 0.03, 0.02, 0.01, -0.015])
+    A = S.true_pose(0.2)
+    Bm = A @ orc.exponential_map(tw)
+    P, pred = orc.predict_pose(A, Bm, 0.0, 0.02, 0.04)
+    np.testing.assert_allclose(P, orc.exponential_map(tw), atol=1e-12)
+    np.testing.assert_allclose(pred, Bm @ orc.exponential_map(tw), atol=1e-12)
+
+
+def test_gauss_newton_recovers_true_pose():
+    T = S.true_pose(0.5)
+    uv = S.project(S.K_README, T, S.MARKERS_5)
+    rng = np.random.default_rng(0)
+    from tests.util import perturb
+    start = perturb(T, rng, 0.01, 0.01)
+    pairs = np.array([[j + 1, j + 1] for j in range(5)], dtype=np.uint32)
+    pose, cov, it = orc.optimise_pose(S.K_README, S.MARKERS_5, uv, pairs, start)
+    np.testing.assert_allclose(pose, T, atol=1e-8)
+    assert 0 <= it < 50
+    assert np.allclose(cov, cov.T, rtol=1e-6, atol=1e-12) and (np.linalg.eigvalsh((cov + cov.T) / 2) > 0).all()
+
+
+def test_tracker_follows_trajectory():
+    sc = S.Scene()
+    trk = orc.OracleTracker(100, sc.markers, sc.K, sc.params, sc.pose(0), sc.time(0), sc.pose(1), sc.time(1),
+                            resampler=0)
+    for f in range(2, 60):
+        flag = trk.frame(sc.time(f), sc.blobs(f), sc.seed(f))
+        assert flag in (1.0, 1.5)
+        uv = S.project(sc.K, trk.current_pose, sc.markers)
+        uv_true = S.project(sc.K, sc.pose(f), sc.markers)
+        assert np.abs(uv - uv_true).max() < 2.0
+    trk.close()
+
+
+def test_weighted_mean_cov_definition():
+    rng = np.random.default_rng(5)
+    from tests.util import perturb
+    base = S.true_pose(0.7)
+    T = np.stack([perturb(base, rng, 0.01, 0.01) for _ in range(200)])
+    w = rng.uniform(0, 1, 200)
+    w /= w.sum()
+    mp, cov = orc.weighted_mean_cov(T, w)
+    np.testing.assert_allclose(mp[:3, :3] @ mp[:3, :3].T, np.eye(3), atol=1e-10)
+    assert abs(np.linalg.det(mp[:3, :3]) - 1) < 1e-10
+    np.testing.assert_allclose(mp[:3, 3], (w[:, None] * T[:, :3, 3]).sum(0), atol=1e-12)
+    assert np.abs(mp[:3, :3] - base[:3, :3]).max() < 0.01
+    assert np.allclose(cov, cov.T) and (np.linalg.eigvalsh(cov) > -1e-15).all()
