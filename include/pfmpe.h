@@ -1,0 +1,193 @@
+/*
+ * pfmpe.h -- C ABI of the B200-native particle-filter tracking core (libpfmpe.so).
+ *
+ * Drop-in boundary for the PF block that pf_mpe_lib inlines in
+ * PoseEstimator::estimateBodyPose (/root/reference/pf_mpe_lib/src/pose_estimator.cpp:471-735):
+ * everything between setImagePoints() (:469) and optimiseAndUpdatePose() (:690) is replaced by
+ * pfmpe_update(); the reference has no FFI for this path, so each entry point cites the
+ * PoseEstimator member / source lines it stands in for (header: pf_mpe_lib/include/pf_mpe_lib/
+ * pose_estimator.h).  INTEGRATION.md shows the shim a maintainer adds on the reference side.
+ *
+ * Conventions: C linkage, POD structs, caller owns every host buffer, the handle owns device
+ * memory and its stream.  Every function returns 0 on success or a negative pfmpe_status; it
+ * never throws and never falls back to a CPU path (a missing/failed CUDA device is an error).
+ * One handle is single-threaded like the reference (callers serialise); handles are independent.
+ * Matrices: 4x4 poses are column-major double[16] (Eigen::Matrix4d memory layout); K is row-major
+ * double[9] (cv::Mat / sensor_msgs::CameraInfo.K order); 6x6 covariances are column-major.
+ */
+#ifndef PFMPE_H_
+#define PFMPE_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PFMPE_MAX_LED 8
+#define PFMPE_VERSION 1
+
+typedef enum {
+  PFMPE_OK = 0,
+  PFMPE_ERR_INVALID = -1,     /* bad argument                                       */
+  PFMPE_ERR_CUDA = -2,        /* a CUDA call failed; see pfmpe_last_error()          */
+  PFMPE_ERR_NO_DEVICE = -3,   /* no usable CUDA device (there is no CPU fallback)    */
+  PFMPE_ERR_STATE = -4,       /* call sequence error (e.g. update before set_particles) */
+  PFMPE_ERR_UNSUPPORTED = -5, /* configuration outside the supported range           */
+  PFMPE_ERR_COMM = -6         /* multi-GPU communicator error                        */
+} pfmpe_status;
+
+typedef struct pfmpe_handle pfmpe_handle;
+
+/* flags */
+#define PFMPE_FLAG_MEAN_COV 1u /* also reduce to a weighted mean pose + covariance (north_star extra) */
+
+typedef struct {
+  int32_t n_particles;  /* N_Particle (pose_estimator.h:139)                                  */
+  int32_t n_trackers;   /* tracked objects sharing the handle (object_points_Vec.size())      */
+  int32_t n_leds;       /* LEDs per object, 1..PFMPE_MAX_LED (object_points_.size())          */
+  int32_t max_blobs;    /* capacity for detections per frame (image_points_.size())           */
+  int32_t device;       /* CUDA ordinal                                                       */
+  uint32_t flags;
+  int32_t reserved[4];
+} pfmpe_config;
+
+/* PF parameters: public fields of PoseEstimator (pose_estimator.h:139-155), set by
+ * MPENode::dynamicParametersCallback (pf_mpe/src/monocular_pose_estimator.cpp:480-527). */
+typedef struct {
+  double min_angular_noise, max_angular_noise;           /* minAngularNoise / maxAngularNoise        */
+  double min_transition_noise, max_transition_noise;     /* minTransitionNoise / maxTransitionNoise  */
+  double back_projection_pixel_tolerance;                /* setBackProjectionPixelTolerance(), :2416 */
+  double back_projection_pixel_tolerance_PF;             /* back_projection_pixel_tolerance_PF, :2414 */
+  int32_t marker_downgrade[5];                           /* bMarkerDowngrade (bMarkerNr1..5), :2431  */
+  int32_t reserved;
+} pfmpe_pf_params;
+
+/* Inputs of one PF update = the members the PF block reads at :475-616. */
+typedef struct {
+  const double* image_points;    /* image_points_ (setImagePoints, :469): n x 2 undistorted pixels */
+  int32_t n_image_points;        /* numLED = detected_led_positions.size() (:449)                  */
+  uint32_t it_since_initialized; /* it_since_initialized_ (:488,:555)                              */
+  double current_pose[16];       /* current_pose_ (:547)                                           */
+  double predicted_pose[16];     /* predicted_pose_ = camMoveInv * predicted_pose_ (:395,:551)     */
+  double prediction_matrix[16];  /* predictionMatrix = predictPose() (:234)                        */
+  double cam_move_inv[16];       /* camMoveInv (:393)                                              */
+  double dt;                     /* predicted_time_ - current_time_ (:499)                         */
+  uint32_t seed;                 /* value of rd() at :476-477 (the reference draws it per frame)   */
+  uint32_t reserved;
+} pfmpe_frame_in;
+
+/* Outputs of one PF update = what the PF block leaves behind at :619-719. */
+typedef struct {
+  int32_t status;                   /* Flag_Fail written by the PF block: 1 (:635) or 4 (:711)     */
+  int32_t iterations;               /* do/while iterations executed (:535-616)                    */
+  int32_t best_iteration;           /* iteration kept by the snapshot logic (:608-624), -1 none   */
+  int32_t resampled;                /* 1 if :666-682 ran                                          */
+  double highest_prob;              /* highestProb (:519,:610)                                    */
+  double weight_sum;                /* probPartSum before normalisation (:627)                    */
+  int32_t most_likely_particle_idx; /* mostLikelyParticleIdx (:610 / :714)                        */
+  int32_t most_likely_pose_idx;     /* mostLikelyPoseIdx (:686), -1 if not resampled              */
+  uint32_t max_count;               /* counterMeas.maxCoeff() (:686)                              */
+  int32_t n_correspondences;        /* correspondences_.rows() (:688)                             */
+  uint32_t correspondences[2 * PFMPE_MAX_LED]; /* rows (LED, detection), 1-based (:2417-2418)     */
+  double winner_pose[16];           /* predicted_pose_ leaving the block (:687 / :716)            */
+  double mean_pose[16];             /* PFMPE_FLAG_MEAN_COV only                                    */
+  double mean_cov[36];              /* PFMPE_FLAG_MEAN_COV only                                    */
+} pfmpe_frame_out;
+
+/* ---- lifetime ---------------------------------------------------------------------------- */
+int pfmpe_create(const pfmpe_config* cfg, pfmpe_handle** out);
+int pfmpe_destroy(pfmpe_handle* h);
+const char* pfmpe_strerror(int status);
+const char* pfmpe_last_error(const pfmpe_handle* h); /* detail of the last failure on this handle */
+int pfmpe_version(void);
+
+/* ---- configuration ----------------------------------------------------------------------- */
+/* setMarkerPositions (pose_estimator.h:445, pose_estimator.cpp:56-62): xyz = n_leds x 3 metres;
+ * tracker = -1 sets every tracker. */
+int pfmpe_set_markers(pfmpe_handle* h, int tracker, const double* xyz, int n_leds);
+/* camera_matrix_K_ / camera_distortion_coeffs_ (pose_estimator.h:121-122).  D may be NULL; the PF
+ * projects with K only (project2d, :1017-1034) -- detections arrive already undistorted. */
+int pfmpe_set_camera(pfmpe_handle* h, const double K[9], const double* D5);
+int pfmpe_set_params(pfmpe_handle* h, const pfmpe_pf_params* prm);
+/* PoseParticle_Vec[t] = newPoseEstimation_Vec[t] = poses (:190-191 after initialise()):
+ * n_particles x 16 column-major doubles. */
+int pfmpe_set_particles(pfmpe_handle* h, int tracker, const double* poses, int n);
+
+/* ---- the hot path ------------------------------------------------------------------------- */
+/* One PF update of one tracker (:475-719).  Synchronous: outputs are valid on return. */
+int pfmpe_update(pfmpe_handle* h, int tracker, const pfmpe_frame_in* in, pfmpe_frame_out* out);
+/* One PF update of every tracker of the handle (the `for objectNumber` loop at :89, batched). */
+int pfmpe_update_batch(pfmpe_handle* h, const pfmpe_frame_in* in, pfmpe_frame_out* out);
+
+/* ---- state getters (getPoseParticles :917, getResampledParticles :923, probPart_Vec :733) -- */
+/* which = 0: PoseParticle (propagated, kept iteration); 1: newPoseEstimation (resampled). */
+int pfmpe_get_particles(pfmpe_handle* h, int tracker, int which, double* poses /* n x 16 */);
+/* normalised != 0: probPart after :627-629; else the raw scores. */
+int pfmpe_get_weights(pfmpe_handle* h, int tracker, int normalised, double* w /* n */);
+/* Particle_index per resample slot (:678-681) and counterMeas (:524,:678); valid after a resampled frame. */
+int pfmpe_get_resample_indices(pfmpe_handle* h, int tracker, int32_t* idx /* n */);
+int pfmpe_get_resample_counts(pfmpe_handle* h, int tracker, uint32_t* count /* n */);
+
+/* ---- host tail (FP64), used by the reference-side shim between two updates ----------------- */
+/* optimisePose (:1805-2009): pose in/out, cov 6x6; *iters = PubData.numIter or -1. */
+int pfmpe_optimise_pose(const double K[9], const double* markers_xyz, int n_leds, const double* image_points,
+                        int n_image_points, const uint32_t* correspondences, int n_correspondences,
+                        double pose[16], double cov[36], int* iters);
+/* predictPose (:995-1010) */
+int pfmpe_predict_pose(const double previous_pose[16], const double current_pose[16], double previous_time,
+                       double current_time, double time_to_predict, double prediction_matrix[16],
+                       double predicted_pose[16]);
+int pfmpe_exponential_map(const double twist[6], double pose[16]);  /* :2194-2226 */
+int pfmpe_logarithm_map(const double pose[16], double twist[6]);    /* :2228-2296 */
+
+/* ---- device-resident tracking (whole sequences without a host round trip) ------------------ */
+/* Mirrors the PF branch of estimateBodyPose (:223-733) minus detection/ROI: predictPose, PF update,
+ * optimiseAndUpdatePose and the jump check all run on the device.
+ * State after "initialise": previous_pose_/current_pose_ and their times, it_since_initialized_ = 2,
+ * every particle = pose1 (:106-109,:190-191). */
+int pfmpe_track_init(pfmpe_handle* h, int tracker, const double pose0[16], double t0, const double pose1[16],
+                     double t1);
+/* Upload a sequence: image_points [n_trackers][n_frames][max_blobs][2], counts [n_trackers][n_frames],
+ * times [n_frames] (time_to_predict per frame), seeds [n_trackers][n_frames]. */
+int pfmpe_track_upload(pfmpe_handle* h, int n_frames, const double* image_points, const int32_t* counts,
+                       const double* times, const uint32_t* seeds);
+/* Same, from device pointers already resident in HBM (no copy is made; buffers must outlive the runs). */
+int pfmpe_track_attach(pfmpe_handle* h, int n_frames, const void* d_image_points, const void* d_counts,
+                       const void* d_times, const void* d_seeds);
+/* Run frames [first, first + n) of the uploaded sequence for all trackers. Asynchronous on the handle's
+ * stream; pfmpe_sync() or a getter completes it. */
+int pfmpe_track_run(pfmpe_handle* h, int first_frame, int n_frames);
+
+typedef struct {
+  int32_t status;       /* 0 not run (track lost earlier), 1 accepted, 4 rejected                   */
+  float flag_fail;      /* PubData.Flag_Fail: 1, 1.5 (:699) or 4                                    */
+  int32_t iterations;
+  int32_t gn_iterations; /* PubData.numIter (:1883)                                                  */
+  int32_t most_likely_pose_idx;
+  uint32_t max_count;
+  double highest_prob, weight_sum;
+  double pose[16];      /* current_pose_ after updatePose (getPredictedPose, :905)                  */
+  double cov[36];       /* pose_covariance_ (getPoseCovariance, :911)                               */
+  double winner_pose[16];
+  int32_t n_correspondences;
+  uint32_t correspondences[2 * PFMPE_MAX_LED];
+  int32_t reserved;
+} pfmpe_track_result;
+/* results of frames [first, first+n) of one tracker */
+int pfmpe_track_results(pfmpe_handle* h, int tracker, int first_frame, int n_frames, pfmpe_track_result* out);
+
+/* ---- streams / timing ---------------------------------------------------------------------- */
+int pfmpe_set_stream(pfmpe_handle* h, void* cuda_stream); /* use an external cudaStream_t (e.g. torch's) */
+int pfmpe_sync(pfmpe_handle* h);
+/* device time of the most recent pfmpe_update* / pfmpe_track_run launch (CUDA events on the handle's stream) */
+int pfmpe_last_launch_ms(pfmpe_handle* h, float* ms);
+/* number of kernels this handle has launched so far */
+int pfmpe_launch_count(const pfmpe_handle* h, uint64_t* n);
+/* launch geometry chosen for the hot-path kernel: grid.x, grid.y, block, cooperative? */
+int pfmpe_launch_info(const pfmpe_handle* h, int32_t info[4]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PFMPE_H_ */

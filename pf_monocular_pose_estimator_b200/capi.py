@@ -1,0 +1,372 @@
+"""ctypes binding of libpfmpe.so (the C ABI in include/pfmpe.h).
+
+Thin, mechanical mirror of the header: tests and bench.py call the CUDA path through these
+functions only.  Loading fails loudly when the library has not been built; creating a handle
+fails loudly (PfmpeError) when no CUDA device is usable -- there is no CPU fallback.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpfmpe.so")
+MAX_LED = 8
+
+OK, ERR_INVALID, ERR_CUDA, ERR_NO_DEVICE, ERR_STATE, ERR_UNSUPPORTED, ERR_COMM = 0, -1, -2, -3, -4, -5, -6
+FLAG_MEAN_COV = 1
+
+EXPORTS = [
+    "pfmpe_create", "pfmpe_destroy", "pfmpe_strerror", "pfmpe_last_error", "pfmpe_version",
+    "pfmpe_set_markers", "pfmpe_set_camera", "pfmpe_set_params", "pfmpe_set_particles",
+    "pfmpe_update", "pfmpe_update_batch",
+    "pfmpe_get_particles", "pfmpe_get_weights", "pfmpe_get_resample_indices", "pfmpe_get_resample_counts",
+    "pfmpe_optimise_pose", "pfmpe_predict_pose", "pfmpe_exponential_map", "pfmpe_logarithm_map",
+    "pfmpe_track_init", "pfmpe_track_upload", "pfmpe_track_attach", "pfmpe_track_run", "pfmpe_track_results",
+    "pfmpe_set_stream", "pfmpe_sync", "pfmpe_last_launch_ms", "pfmpe_launch_count", "pfmpe_launch_info",
+]
+
+
+class PfmpeError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("pfmpe error %d: %s" % (code, msg))
+        self.code = code
+
+
+class Config(C.Structure):
+    _fields_ = [("n_particles", C.c_int32), ("n_trackers", C.c_int32), ("n_leds", C.c_int32),
+                ("max_blobs", C.c_int32), ("device", C.c_int32), ("flags", C.c_uint32),
+                ("reserved", C.c_int32 * 4)]
+
+
+class PfParams(C.Structure):
+    _fields_ = [("min_angular_noise", C.c_double), ("max_angular_noise", C.c_double),
+                ("min_transition_noise", C.c_double), ("max_transition_noise", C.c_double),
+                ("back_projection_pixel_tolerance", C.c_double),
+                ("back_projection_pixel_tolerance_PF", C.c_double),
+                ("marker_downgrade", C.c_int32 * 5), ("reserved", C.c_int32)]
+
+
+class FrameIn(C.Structure):
+    _fields_ = [("image_points", C.POINTER(C.c_double)), ("n_image_points", C.c_int32),
+                ("it_since_initialized", C.c_uint32),
+                ("current_pose", C.c_double * 16), ("predicted_pose", C.c_double * 16),
+                ("prediction_matrix", C.c_double * 16), ("cam_move_inv", C.c_double * 16),
+                ("dt", C.c_double), ("seed", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+class FrameOut(C.Structure):
+    _fields_ = [("status", C.c_int32), ("iterations", C.c_int32), ("best_iteration", C.c_int32),
+                ("resampled", C.c_int32), ("highest_prob", C.c_double), ("weight_sum", C.c_double),
+                ("most_likely_particle_idx", C.c_int32), ("most_likely_pose_idx", C.c_int32),
+                ("max_count", C.c_uint32), ("n_correspondences", C.c_int32),
+                ("correspondences", C.c_uint32 * (2 * MAX_LED)),
+                ("winner_pose", C.c_double * 16), ("mean_pose", C.c_double * 16), ("mean_cov", C.c_double * 36)]
+
+
+class TrackResult(C.Structure):
+    _fields_ = [("status", C.c_int32), ("flag_fail", C.c_float), ("iterations", C.c_int32),
+                ("gn_iterations", C.c_int32), ("most_likely_pose_idx", C.c_int32), ("max_count", C.c_uint32),
+                ("highest_prob", C.c_double), ("weight_sum", C.c_double),
+                ("pose", C.c_double * 16), ("cov", C.c_double * 36), ("winner_pose", C.c_double * 16),
+                ("n_correspondences", C.c_int32), ("correspondences", C.c_uint32 * (2 * MAX_LED)),
+                ("reserved", C.c_int32)]
+
+
+_lib = None
+_dp = C.POINTER(C.c_double)
+
+
+def lib():
+    """Load libpfmpe.so; raises if it has not been built (python __graft_entry__.py build)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError("libpfmpe.so is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                              "(make -C pf_monocular_pose_estimator_b200/csrc). There is no CPU fallback.")
+        L = C.CDLL(LIB_PATH)
+        L.pfmpe_strerror.restype = C.c_char_p
+        L.pfmpe_last_error.restype = C.c_char_p
+        L.pfmpe_last_error.argtypes = [C.c_void_p]
+        L.pfmpe_create.argtypes = [C.POINTER(Config), C.POINTER(C.c_void_p)]
+        L.pfmpe_destroy.argtypes = [C.c_void_p]
+        L.pfmpe_set_markers.argtypes = [C.c_void_p, C.c_int, _dp, C.c_int]
+        L.pfmpe_set_camera.argtypes = [C.c_void_p, _dp, _dp]
+        L.pfmpe_set_params.argtypes = [C.c_void_p, C.POINTER(PfParams)]
+        L.pfmpe_set_particles.argtypes = [C.c_void_p, C.c_int, _dp, C.c_int]
+        L.pfmpe_update.argtypes = [C.c_void_p, C.c_int, C.POINTER(FrameIn), C.POINTER(FrameOut)]
+        L.pfmpe_update_batch.argtypes = [C.c_void_p, C.POINTER(FrameIn), C.POINTER(FrameOut)]
+        L.pfmpe_get_particles.argtypes = [C.c_void_p, C.c_int, C.c_int, _dp]
+        L.pfmpe_get_weights.argtypes = [C.c_void_p, C.c_int, C.c_int, _dp]
+        L.pfmpe_get_resample_indices.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int32)]
+        L.pfmpe_get_resample_counts.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint32)]
+        L.pfmpe_optimise_pose.argtypes = [_dp, _dp, C.c_int, _dp, C.c_int, C.POINTER(C.c_uint32), C.c_int, _dp, _dp,
+                                          C.POINTER(C.c_int)]
+        L.pfmpe_predict_pose.argtypes = [_dp, _dp, C.c_double, C.c_double, C.c_double, _dp, _dp]
+        L.pfmpe_exponential_map.argtypes = [_dp, _dp]
+        L.pfmpe_logarithm_map.argtypes = [_dp, _dp]
+        L.pfmpe_track_init.argtypes = [C.c_void_p, C.c_int, _dp, C.c_double, _dp, C.c_double]
+        L.pfmpe_track_upload.argtypes = [C.c_void_p, C.c_int, _dp, C.POINTER(C.c_int32), _dp, C.POINTER(C.c_uint32)]
+        L.pfmpe_track_attach.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.pfmpe_track_run.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.pfmpe_track_results.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(TrackResult)]
+        L.pfmpe_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+        L.pfmpe_sync.argtypes = [C.c_void_p]
+        L.pfmpe_last_launch_ms.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
+        L.pfmpe_launch_count.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
+        L.pfmpe_launch_info.argtypes = [C.c_void_p, C.POINTER(C.c_int32)]
+        _lib = L
+    return _lib
+
+
+def _d(a):
+    return a.ctypes.data_as(_dp)
+
+
+def _c64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def colmajor(T):
+    """(..., 4, 4) numpy matrices -> (..., 16) column-major doubles (Eigen::Matrix4d layout)."""
+    T = np.asarray(T, dtype=np.float64)
+    return np.ascontiguousarray(np.swapaxes(T, -1, -2).reshape(T.shape[:-2] + (16,)))
+
+
+def from_colmajor(a):
+    a = np.asarray(a, dtype=np.float64)
+    return np.swapaxes(a.reshape(a.shape[:-1] + (4, 4)), -1, -2).copy()
+
+
+def make_params(p):
+    q = PfParams()
+    q.min_angular_noise = p["minAngularNoise"]
+    q.max_angular_noise = p["maxAngularNoise"]
+    q.min_transition_noise = p["minTransitionNoise"]
+    q.max_transition_noise = p["maxTransitionNoise"]
+    q.back_projection_pixel_tolerance = p["back_projection_pixel_tolerance"]
+    q.back_projection_pixel_tolerance_PF = p["back_projection_pixel_tolerance_PF"]
+    dg = p.get("bMarkerDowngrade", [0] * 5)
+    for i in range(5):
+        q.marker_downgrade[i] = int(dg[i])
+    return q
+
+
+def make_frame_in(img, T_cur, T_pred, P, Cm, isi, dt, seed, keep):
+    """Build a pfmpe_frame_in; `keep` collects the numpy buffers that must outlive the call."""
+    img = _c64(img).reshape(-1, 2)
+    keep.append(img)
+    fi = FrameIn()
+    fi.image_points = _d(img)
+    fi.n_image_points = img.shape[0]
+    fi.it_since_initialized = isi
+    for name, M in (("current_pose", T_cur), ("predicted_pose", T_pred), ("prediction_matrix", P), ("cam_move_inv", Cm)):
+        arr = colmajor(M)
+        for i in range(16):
+            getattr(fi, name)[i] = arr[i]
+    fi.dt = dt
+    fi.seed = seed & 0xFFFFFFFF
+    return fi
+
+
+def unpack_frame_out(o):
+    nc = o.n_correspondences
+    return dict(status=o.status, iterations=o.iterations, best_iteration=o.best_iteration, resampled=o.resampled,
+                highest_prob=o.highest_prob, weight_sum=o.weight_sum,
+                most_likely_particle_idx=o.most_likely_particle_idx, most_likely_pose_idx=o.most_likely_pose_idx,
+                max_count=o.max_count,
+                correspondences=np.array(o.correspondences[: 2 * nc], dtype=np.uint32).reshape(-1, 2),
+                winner_pose=from_colmajor(np.array(o.winner_pose[:])),
+                mean_pose=from_colmajor(np.array(o.mean_pose[:])),
+                mean_cov=np.array(o.mean_cov[:]).reshape(6, 6).T.copy())
+
+
+class Handle:
+    """RAII wrapper of a pfmpe_handle."""
+
+    def __init__(self, n_particles, n_trackers=1, n_leds=5, max_blobs=32, device=0, flags=0, force_mode=0, grid_cap=0):
+        self._h = C.c_void_p()
+        cfg = Config()
+        cfg.n_particles, cfg.n_trackers, cfg.n_leds, cfg.max_blobs = n_particles, n_trackers, n_leds, max_blobs
+        cfg.device, cfg.flags = device, flags
+        cfg.reserved[0], cfg.reserved[1] = force_mode, grid_cap
+        rc = lib().pfmpe_create(C.byref(cfg), C.byref(self._h))
+        if rc != OK:
+            msg = lib().pfmpe_last_error(None).decode() or lib().pfmpe_strerror(rc).decode()
+            self._h = C.c_void_p()
+            raise PfmpeError(rc, msg)
+        self.N, self.T, self.L, self.max_blobs = n_particles, n_trackers, n_leds, max_blobs
+
+    def _chk(self, rc):
+        if rc != OK:
+            raise PfmpeError(rc, (lib().pfmpe_last_error(self._h) or b"").decode() + " (" + lib().pfmpe_strerror(rc).decode() + ")")
+
+    def close(self):
+        if self._h:
+            lib().pfmpe_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # configuration
+    def set_markers(self, xyz, tracker=-1):
+        a = _c64(xyz).reshape(-1, 3)
+        self._chk(lib().pfmpe_set_markers(self._h, tracker, _d(a), a.shape[0]))
+
+    def set_camera(self, K, D=None):
+        k = _c64(K).reshape(9)
+        d = _c64(D).reshape(-1) if D is not None else None
+        self._chk(lib().pfmpe_set_camera(self._h, _d(k), _d(d) if d is not None else None))
+
+    def set_params(self, params):
+        q = make_params(params)
+        self._chk(lib().pfmpe_set_params(self._h, C.byref(q)))
+
+    def set_particles(self, poses, tracker=0):
+        a = colmajor(poses)
+        self._chk(lib().pfmpe_set_particles(self._h, tracker, _d(a), a.shape[0]))
+
+    def configure(self, markers, K, params):
+        self.set_markers(markers)
+        self.set_camera(K)
+        self.set_params(params)
+
+    # hot path
+    def update(self, img, T_cur, T_pred, P, Cm, isi, dt, seed, tracker=0):
+        keep = []
+        fi = make_frame_in(img, T_cur, T_pred, P, Cm, isi, dt, seed, keep)
+        fo = FrameOut()
+        self._chk(lib().pfmpe_update(self._h, tracker, C.byref(fi), C.byref(fo)))
+        return unpack_frame_out(fo)
+
+    def update_batch(self, frames):
+        """frames: list (len n_trackers) of dicts with keys img,T_cur,T_pred,P,Cm,isi,dt,seed."""
+        keep = []
+        arr_in = (FrameIn * self.T)()
+        for t, f in enumerate(frames):
+            arr_in[t] = make_frame_in(f["img"], f["T_cur"], f["T_pred"], f["P"], f["Cm"], f["isi"], f["dt"], f["seed"], keep)
+        arr_out = (FrameOut * self.T)()
+        self._chk(lib().pfmpe_update_batch(self._h, arr_in, arr_out))
+        return [unpack_frame_out(arr_out[t]) for t in range(self.T)]
+
+    # getters
+    def particles(self, which=0, tracker=0):
+        out = np.zeros((self.N, 16))
+        self._chk(lib().pfmpe_get_particles(self._h, tracker, which, _d(out)))
+        return from_colmajor(out)
+
+    def weights(self, normalised=False, tracker=0):
+        out = np.zeros(self.N)
+        self._chk(lib().pfmpe_get_weights(self._h, tracker, int(normalised), _d(out)))
+        return out
+
+    def resample_indices(self, tracker=0):
+        out = np.zeros(self.N, dtype=np.int32)
+        self._chk(lib().pfmpe_get_resample_indices(self._h, tracker, out.ctypes.data_as(C.POINTER(C.c_int32))))
+        return out
+
+    def resample_counts(self, tracker=0):
+        out = np.zeros(self.N, dtype=np.uint32)
+        self._chk(lib().pfmpe_get_resample_counts(self._h, tracker, out.ctypes.data_as(C.POINTER(C.c_uint32))))
+        return out
+
+    # device-resident tracking
+    def track_init(self, pose0, t0, pose1, t1, tracker=0):
+        a, b = colmajor(pose0), colmajor(pose1)
+        self._chk(lib().pfmpe_track_init(self._h, tracker, _d(a), t0, _d(b), t1))
+
+    def track_upload(self, image_points, counts, times, seeds):
+        ip = _c64(image_points)
+        cn = np.ascontiguousarray(counts, dtype=np.int32)
+        tm = _c64(times)
+        sd = np.ascontiguousarray(seeds, dtype=np.uint32)
+        n_frames = tm.shape[0]
+        assert ip.shape == (self.T, n_frames, self.max_blobs, 2), ip.shape
+        assert cn.shape == (self.T, n_frames) and sd.shape == (self.T, n_frames)
+        self._chk(lib().pfmpe_track_upload(self._h, n_frames, _d(ip), cn.ctypes.data_as(C.POINTER(C.c_int32)), _d(tm),
+                                          sd.ctypes.data_as(C.POINTER(C.c_uint32))))
+
+    def track_attach(self, n_frames, d_image_points, d_counts, d_times, d_seeds):
+        self._chk(lib().pfmpe_track_attach(self._h, n_frames, d_image_points, d_counts, d_times, d_seeds))
+
+    def track_run(self, first_frame, n_frames):
+        self._chk(lib().pfmpe_track_run(self._h, first_frame, n_frames))
+
+    def track_results(self, first_frame, n_frames, tracker=0):
+        arr = (TrackResult * n_frames)()
+        self._chk(lib().pfmpe_track_results(self._h, tracker, first_frame, n_frames, arr))
+        out = []
+        for r in arr:
+            nc = r.n_correspondences
+            out.append(dict(status=r.status, flag_fail=r.flag_fail, iterations=r.iterations,
+                            gn_iterations=r.gn_iterations, most_likely_pose_idx=r.most_likely_pose_idx,
+                            max_count=r.max_count, highest_prob=r.highest_prob, weight_sum=r.weight_sum,
+                            pose=from_colmajor(np.array(r.pose[:])), cov=np.array(r.cov[:]).reshape(6, 6).T.copy(),
+                            winner_pose=from_colmajor(np.array(r.winner_pose[:])),
+                            correspondences=np.array(r.correspondences[: 2 * nc], dtype=np.uint32).reshape(-1, 2)))
+        return out
+
+    # streams / timing
+    def set_stream(self, cuda_stream_ptr):
+        self._chk(lib().pfmpe_set_stream(self._h, C.c_void_p(cuda_stream_ptr)))
+
+    def sync(self):
+        self._chk(lib().pfmpe_sync(self._h))
+
+    def last_launch_ms(self):
+        ms = C.c_float()
+        self._chk(lib().pfmpe_last_launch_ms(self._h, C.byref(ms)))
+        return ms.value
+
+    def launch_count(self):
+        n = C.c_uint64()
+        self._chk(lib().pfmpe_launch_count(self._h, C.byref(n)))
+        return n.value
+
+    def launch_info(self):
+        a = (C.c_int32 * 4)()
+        self._chk(lib().pfmpe_launch_info(self._h, a))
+        return list(a)
+
+
+# ---- host tail (FP64, no device needed) --------------------------------------------------
+def optimise_pose(K, markers, img, pairs, pose):
+    k = _c64(K).reshape(9)
+    m = _c64(markers).reshape(-1, 3)
+    im = _c64(img).reshape(-1, 2)
+    pr = np.ascontiguousarray(pairs, dtype=np.uint32).reshape(-1, 2)
+    p = colmajor(pose).copy()
+    cov = np.zeros(36)
+    it = C.c_int()
+    rc = lib().pfmpe_optimise_pose(_d(k), _d(m), m.shape[0], _d(im), im.shape[0],
+                                   pr.ctypes.data_as(C.POINTER(C.c_uint32)), pr.shape[0], _d(p), _d(cov), C.byref(it))
+    if rc != OK:
+        raise PfmpeError(rc, lib().pfmpe_strerror(rc).decode())
+    return from_colmajor(p), cov.reshape(6, 6).T.copy(), it.value
+
+
+def predict_pose(prev, cur, t_prev, t_cur, t_pred):
+    a, b = colmajor(prev), colmajor(cur)
+    P, pred = np.zeros(16), np.zeros(16)
+    rc = lib().pfmpe_predict_pose(_d(a), _d(b), t_prev, t_cur, t_pred, _d(P), _d(pred))
+    if rc != OK:
+        raise PfmpeError(rc, lib().pfmpe_strerror(rc).decode())
+    return from_colmajor(P), from_colmajor(pred)
+
+
+def exponential_map(tw):
+    t = _c64(tw)
+    out = np.zeros(16)
+    lib().pfmpe_exponential_map(_d(t), _d(out))
+    return from_colmajor(out)
+
+
+def logarithm_map(T):
+    t = colmajor(T)
+    out = np.zeros(6)
+    lib().pfmpe_logarithm_map(_d(t), _d(out))
+    return out

@@ -1,0 +1,313 @@
+// pf_math.cuh -- per-particle math of the PF hot path (FP32 state, exact integer RNG).
+//
+// Everything here is `PF_HD` (host+device): the CUDA kernels in pf_kernels.cuh inline these
+// functions; tests/ additionally compile this header with g++ (tests/hostmath.cpp) to check
+// the device arithmetic against the oracle without a GPU.  That host build is a test
+// artefact only -- the shipped library has no CPU execution path.
+//
+// Reference semantics restated (file:line are /root/reference/pf_mpe_lib/src/pose_estimator.cpp):
+//   motion model            :543-588      pf_propagate
+//   project2d               :1017-1034    pf_project
+//   calculateEstimationProbability :2385-2445   pf_score
+//   RNG stream              :476-477,:510-523 (libstdc++ minstd_rand0 + generate_canonical)
+//   stratified resampling   :668-682      pf_threshold / pf_count_leq (source-centric form)
+#pragma once
+
+#include <stdint.h>
+#include <math.h>
+
+#if defined(__CUDACC__)
+#define PF_HD __host__ __device__ __forceinline__
+#else
+#define PF_HD inline
+#endif
+
+#define PF_MAX_LED 8
+#define PF_RNG_M 2147483647u     /* 2^31 - 1 */
+#define PF_RNG_A 16807u
+#define PF_RNG_ORDER 2147483646u /* multiplicative order divides m-1 */
+#define PF_FX_BITS 30            /* weights are accumulated as Q33.30 fixed point (int64) */
+
+struct pf_f2 { float x, y; };
+
+// ----------------------------------------------------------------------------------------
+// RNG: x <- 16807 x mod (2^31-1); exact skip-ahead with radix-256 power tables.
+// ----------------------------------------------------------------------------------------
+PF_HD uint32_t pf_modmul(uint32_t a, uint32_t b)
+{
+  uint64_t p = (uint64_t)a * (uint64_t)b;                 // < 2^62
+  uint32_t s = (uint32_t)(p & PF_RNG_M) + (uint32_t)(p >> 31);
+  s = (s & PF_RNG_M) + (s >> 31);
+  return s >= PF_RNG_M ? s - PF_RNG_M : s;
+}
+
+PF_HD uint32_t pf_rng_next(uint32_t x) { return pf_modmul(x, PF_RNG_A); }
+
+// tab[d*256 + v] = 16807^(v * 256^d) mod m, d = 0..3 (built on the host, pfmpe_api.cu)
+PF_HD uint32_t pf_rng_skip(uint32_t x, uint64_t steps, const uint32_t* __restrict__ tab)
+{
+  uint32_t e = (uint32_t)(steps % PF_RNG_ORDER);
+  x = pf_modmul(x, tab[e & 255u]);
+  x = pf_modmul(x, tab[256 + ((e >> 8) & 255u)]);
+  x = pf_modmul(x, tab[512 + ((e >> 16) & 255u)]);
+  x = pf_modmul(x, tab[768 + (e >> 24)]);
+  return x;
+}
+
+// generate_canonical<double,53> from two consecutive engine outputs, bit-exact with libstdc++
+// (sum = (g1-1) + (g2-1)*R; ret = sum / (R*R)), no FMA contraction.
+PF_HD double pf_canonical_f64(uint32_t g1, uint32_t g2)
+{
+  const double R = 2147483646.0;
+  const double RR = 2147483646.0 * 2147483646.0;  // constant-folded with one IEEE rounding
+#if defined(__CUDA_ARCH__)
+  double sum = __dadd_rn((double)(g1 - 1u), __dmul_rn((double)(g2 - 1u), R));
+  double c = __ddiv_rn(sum, RR);
+#else
+  volatile double prod = (double)(g2 - 1u) * R;   // volatile: forbid host FMA contraction
+  double sum = (double)(g1 - 1u) + prod;
+  double c = sum / RR;
+#endif
+  if (c >= 1.0) c = 0.99999999999999988897769753748;  // nextafter(1,0)
+  return c;
+}
+
+// FP32 rendering of the same canonical value (within 1 ulp_f32 of the double one): used for
+// the motion noise, whose consumer is FP32 anyway.
+PF_HD float pf_canonical_f32(uint32_t g1, uint32_t g2)
+{
+  const float invR = 1.0f / 2147483646.0f;
+  float hi = (float)(g2 - 1u), lo = (float)(g1 - 1u);
+  return fminf(fmaf(lo, invR, hi) * invR, 0.99999994f);
+}
+
+// ----------------------------------------------------------------------------------------
+// Poses: 3x4 row-major float, implicit bottom row (0,0,0,1).  p[4*i+j]; p[4*i+3] = t_i.
+// ----------------------------------------------------------------------------------------
+struct pf_pose { float p[12]; };
+
+PF_HD pf_pose pf_affine_mul(const pf_pose& A, const pf_pose& B)
+{
+  pf_pose C;
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float s = A.p[4 * i] * B.p[j];
+      s = fmaf(A.p[4 * i + 1], B.p[4 + j], s);
+      s = fmaf(A.p[4 * i + 2], B.p[8 + j], s);
+      if (j == 3) s += A.p[4 * i + 3];
+      C.p[4 * i + j] = s;
+    }
+  }
+  return C;
+}
+
+struct pf_noise_cfg {
+  float ang_lo, ang_span;  // U(a, b) = c*(b-a)+a  with a = minAngularNoise*facRot   (:514-516)
+  float tr_lo, tr_span;    // same for the translation ranges                          (:510-512)
+};
+
+// Motion model for particle n >= 2 (:555-587).  `base` = camMoveInv*E_n[*predictionMatrix];
+// x = engine state right before this particle's first draw; 12 engine steps are consumed in
+// the order aX,aY,aZ,tX,tY,tZ.  scale = 1 + 0.025*floor(iter/10).
+PF_HD pf_pose pf_propagate(const pf_pose& base, uint32_t x, const pf_noise_cfg& nc, float scale)
+{
+  float c6[6];
+#pragma unroll
+  for (int d = 0; d < 6; ++d) {
+    uint32_t g1 = pf_rng_next(x);
+    uint32_t g2 = pf_rng_next(g1);
+    x = g2;
+    c6[d] = pf_canonical_f32(g1, g2);
+  }
+  const float a = fmaf(c6[0], nc.ang_span, nc.ang_lo) * scale;
+  const float b = fmaf(c6[1], nc.ang_span, nc.ang_lo) * scale;
+  const float c = fmaf(c6[2], nc.ang_span, nc.ang_lo) * scale;
+  float sa, ca, sb, cb, sc, cc;
+#if defined(__CUDA_ARCH__)
+  sincosf(a, &sa, &ca); sincosf(b, &sb, &cb); sincosf(c, &sc, &cc);
+#else
+  sa = sinf(a); ca = cosf(a); sb = sinf(b); cb = cosf(b); sc = sinf(c); cc = cosf(c);
+#endif
+  // Rn = Rz(c) * Ry(b) * Rx(a)   (:567-582)
+  float r[9];
+  r[0] = cc * cb; r[1] = cc * sb * sa - sc * ca; r[2] = cc * sb * ca + sc * sa;
+  r[3] = sc * cb; r[4] = sc * sb * sa + cc * ca; r[5] = sc * sb * ca - cc * sa;
+  r[6] = -sb;     r[7] = cb * sa;                r[8] = cb * ca;
+  pf_pose T;
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      float s = base.p[4 * i] * r[j];
+      s = fmaf(base.p[4 * i + 1], r[3 + j], s);
+      s = fmaf(base.p[4 * i + 2], r[6 + j], s);
+      T.p[4 * i + j] = s;
+    }
+  }
+  // translation added separately (:585-587)
+  T.p[3]  = base.p[3]  + fmaf(c6[3], nc.tr_span, nc.tr_lo) * scale;
+  T.p[7]  = base.p[7]  + fmaf(c6[4], nc.tr_span, nc.tr_lo) * scale;
+  T.p[11] = base.p[11] + fmaf(c6[5], nc.tr_span, nc.tr_lo) * scale;
+  return T;
+}
+
+// project2d (:1017-1034): p = K (R X + t), (u,v) = (p0/p2, p1/p2); full 3x3 K, no cheirality test.
+PF_HD void pf_project(const float* __restrict__ K9, const pf_pose& T, float X, float Y, float Z, float& u, float& v)
+{
+  float xc = fmaf(T.p[0], X, fmaf(T.p[1], Y, fmaf(T.p[2], Z, T.p[3])));
+  float yc = fmaf(T.p[4], X, fmaf(T.p[5], Y, fmaf(T.p[6], Z, T.p[7])));
+  float zc = fmaf(T.p[8], X, fmaf(T.p[9], Y, fmaf(T.p[10], Z, T.p[11])));
+  float p0 = fmaf(K9[0], xc, fmaf(K9[1], yc, K9[2] * zc));
+  float p1 = fmaf(K9[3], xc, fmaf(K9[4], yc, K9[5] * zc));
+  float p2 = fmaf(K9[6], xc, fmaf(K9[7], yc, K9[8] * zc));
+  u = p0 / p2;
+  v = p1 / p2;
+}
+
+// ----------------------------------------------------------------------------------------
+// Scoring (:2385-2445) in the per-LED-minimum form: for every LED the nearest
+// blob (ties -> smallest blob index), then LEDs in ascending (min, j) order, at most
+// min(D,L), stop at the first beyond tol_PF.
+// ----------------------------------------------------------------------------------------
+struct pf_score_cfg {
+  float tol, inv_tol;   // back_projection_pixel_tolerance_ (gain)        :2416
+  float tol_pf;         // back_projection_pixel_tolerance_PF (gate)      :2414
+  unsigned dg_mask;     // bMarkerDowngrade bits (first five LEDs only)   :2431
+};
+
+template <int L, bool WANT_PAIRS>
+PF_HD float pf_score(const pf_f2* __restrict__ blobs, int D, const float* u, const float* v,
+                     const pf_score_cfg& sc, unsigned* pairs, int* npairs)
+{
+  float m[L];
+  int am[L];
+#pragma unroll
+  for (int j = 0; j < L; ++j) { m[j] = INFINITY; am[j] = 0; }
+  for (int i = 0; i < D; ++i) {
+    const pf_f2 z = blobs[i];
+#pragma unroll
+    for (int j = 0; j < L; ++j) {
+      float dx = z.x - u[j], dy = z.y - v[j];
+      float d2 = fmaf(dy, dy, dx * dx);
+      if (d2 < m[j]) { m[j] = d2; am[j] = i; }
+    }
+  }
+  const int steps = D < L ? D : L;   // :2409
+  unsigned used = 0;                 // LEDs already consumed (column set to +inf, :2435)
+  float P = 0.0f;
+  int occ = 1, nacc = 0;
+#pragma unroll
+  for (int k = 0; k < L; ++k) {
+    if (k >= steps) break;
+    int best = -1, bam = 0;
+    float bm = INFINITY;
+#pragma unroll
+    for (int j = 0; j < L; ++j) {
+      bool free_j = !((used >> j) & 1u);
+      if (free_j && (best < 0 || m[j] < bm)) { best = j; bm = m[j]; bam = am[j]; }
+    }
+    const float d = sqrtf(bm);       // :2412
+    if (!(d <= sc.tol_pf)) break;    // :2414 / :2438
+    const float g = (sc.tol - d) * sc.inv_tol;
+    P += (float)L + g * g;           // :2416
+    bool reused = false;             // :2421
+#pragma unroll
+    for (int j = 0; j < L; ++j)
+      if (((used >> j) & 1u) && am[j] == bam) reused = true;
+    if (reused) { P -= (float)(3 * occ); ++occ; }   // :2423-2424
+    if ((sc.dg_mask >> best) & 1u) P -= 2.0f;       // :2431-2432
+    if (WANT_PAIRS) { pairs[2 * nacc] = (unsigned)best + 1u; pairs[2 * nacc + 1] = (unsigned)bam + 1u; }
+    ++nacc;
+    used |= 1u << best;
+  }
+  if (WANT_PAIRS) *npairs = nacc;
+  return P;
+}
+
+// ----------------------------------------------------------------------------------------
+// Fixed-point weights and stratified-resampling thresholds.
+//
+// Raw FP32 scores are accumulated exactly as int64 Q.30, so sums / prefix sums are associative:
+// any tiling, any number of CTAs or GPUs gives bit-identical totals and prefixes.  With
+// S = sum_i w_i (raw), sg = sign(S), the reference test  (sum_{j<=i} w_j / S) >= u_k  (:676-677)
+// becomes  sg * prefix_fx(i) >= t_k,  t_k = ceil(u_k * |S_fx|).
+// ----------------------------------------------------------------------------------------
+PF_HD long long pf_w_to_fx(float w)
+{
+#if defined(__CUDA_ARCH__)
+  return __double2ll_rn((double)w * 1073741824.0);
+#else
+  return (long long)llrint((double)w * 1073741824.0);
+#endif
+}
+
+struct pf_resample_cfg {
+  uint32_t x_base;   // engine state right before resample draw 0 (after 12*(N-2)*I steps)
+  int N;             // number of strata (global N when sharded)
+  double Nd;         // (double)N
+  double Sabs;       // (double)|S_fx|
+  double margin;     // fast-path guard, see pf_count_leq
+};
+
+PF_HD pf_resample_cfg pf_make_resample_cfg(uint32_t x_base, int N, long long S_fx)
+{
+  pf_resample_cfg c;
+  c.x_base = x_base;
+  c.N = N;
+  c.Nd = (double)N;
+  long long a = S_fx < 0 ? -S_fx : S_fx;
+  c.Sabs = (double)a;
+  c.margin = 8.0 * 2.220446049250313e-16 * c.Nd + 2.0 * c.Nd / (c.Sabs > 0 ? c.Sabs : 1.0) + 1e-12;
+  return c;
+}
+
+// t_k = ceil( ((k + r_k)/N) * |S_fx| ), r_k = draw k of randResample (:671), double ops as in
+// the reference ((k + r)/N is an IEEE add and an IEEE divide).  Non-decreasing in k.
+PF_HD long long pf_threshold(int k, const pf_resample_cfg& rc, const uint32_t* __restrict__ tab)
+{
+  uint32_t x = pf_rng_skip(rc.x_base, 2ull * (uint64_t)k, tab);
+  uint32_t g1 = pf_rng_next(x), g2 = pf_rng_next(g1);
+  double r = pf_canonical_f64(g1, g2);
+#if defined(__CUDA_ARCH__)
+  double u = __ddiv_rn(__dadd_rn((double)k, r), rc.Nd);
+  double td = __dmul_rn(u, rc.Sabs);
+#else
+  volatile double s = (double)k + r;
+  volatile double u = s / rc.Nd;
+  double td = u * rc.Sabs;
+#endif
+  return (long long)ceil(td);
+}
+
+// K(m) = #{k in [0,N): t_k <= m}.  Offspring of source i are the strata [K(M_{i-1}), K(M_i))
+// where M is the running maximum of sg*prefix_fx (first-crossing semantics for non-monotone
+// prefixes).  One RNG evaluation in the common case.
+PF_HD int pf_count_leq(long long m, const pf_resample_cfg& rc, const uint32_t* __restrict__ tab)
+{
+  if (m < 0) return 0;
+  double x = (double)m * rc.Nd / rc.Sabs;
+  int kf;
+  if (!(x < rc.Nd)) kf = rc.N; else kf = (int)x;   // floor, x >= 0
+  double frac = x - (double)kf;
+  if (kf < rc.N && frac > rc.margin && frac < 1.0 - rc.margin)
+    return kf + (pf_threshold(kf, rc, tab) <= m ? 1 : 0);
+  int K = kf;
+  while (K < rc.N && pf_threshold(K, rc, tab) <= m) ++K;
+  while (K > 0 && pf_threshold(K - 1, rc, tab) > m) --K;
+  return K;
+}
+
+// (sum, running-max-of-prefix) scan operator:  (s1,m1) (+) (s2,m2) = (s1+s2, max(m1, s1+m2)).
+struct pf_sm { long long s, m; };
+#define PF_SM_NEG (-(1ll << 62))
+PF_HD pf_sm pf_sm_identity() { pf_sm r; r.s = 0; r.m = PF_SM_NEG; return r; }
+PF_HD pf_sm pf_sm_combine(const pf_sm& a, const pf_sm& b)
+{
+  pf_sm r;
+  r.s = a.s + b.s;
+  long long t = b.m <= PF_SM_NEG ? PF_SM_NEG : a.s + b.m;
+  r.m = a.m > t ? a.m : t;
+  return r;
+}

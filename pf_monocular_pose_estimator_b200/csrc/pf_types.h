@@ -1,0 +1,104 @@
+// pf_types.h -- device-resident records shared by the kernels (pf_kernels.cuh) and the
+// host side of the C ABI (pfmpe_api.cu).  Plain structs (float4 is the only CUDA type).
+#pragma once
+#include <stdint.h>
+#include "pf_tail.cuh"
+
+#define PF_BLOCK 256          /* threads per CTA                                     */
+#define PF_SCAN_ITEMS 4       /* consecutive particles per thread in the scan stage  */
+#define PF_SCAN_TILE (PF_BLOCK * PF_SCAN_ITEMS)
+#define PF_MAX_ITER 80        /* do/while bound, pose_estimator.cpp:616              */
+
+// Per-tracker persistent state (device memory).
+struct pf_tracker_state {
+  // FP64 tracker state, used by the device tail (track mode)
+  double cur[12], prev[12], pred[12];        // current_pose_, previous_pose_, predicted_pose_ (affine row-major)
+  double t_cur, t_prev, t_pred;
+  double cov[36];
+  uint32_t isi;
+  int32_t failed;                            // track mode: set when a frame ends with Flag_Fail 4
+  // particle-set bookkeeping
+  int32_t src_buf;                           // pose buffer that holds the source set of the next frame
+  int32_t src_mode;                          // 0: E[n] = pose[src_buf][n];  1: E[n] = pose[src_buf][idx(n)] via kend (resampled)
+  uint32_t scan_epoch;                       // look-back flag stamp, monotonically increasing
+  int32_t frames_done;
+  int32_t t_buf;                             // pose buffer that holds the last propagated set (PoseParticle)
+  int32_t pad;
+};
+
+// Result record of one frame (device -> host).
+struct pf_frame_result {
+  int32_t status;                 // 0 not run, 1 accepted (Flag_Fail 1), 4 rejected (Flag_Fail 4)
+  int32_t iterations;             // do/while iterations executed
+  int32_t best_iteration;         // iteration whose particles were kept (-1: none scored > 0)
+  int32_t resampled;
+  float   highest_prob;
+  int32_t most_likely_particle_idx;   // first argmax weight (kept iteration)
+  int32_t most_likely_pose_idx;       // first argmax resample count
+  uint32_t max_count;
+  long long sum_fx;               // weight sum, Q.30
+  float   winner_pose[12];        // predicted_pose_ leaving the PF block (affine row-major, FP32 particle)
+  uint32_t pairs[2 * PF_MAX_LED]; // winner correspondences (LED+1, blob+1), greedy order
+  int32_t npairs;
+  int32_t gn_iters;               // track mode: PubData.numIter
+  float   flag_fail;              // track mode: 1, 1.5 or 4
+  int32_t pad;
+  double  pose[12];               // track mode: refined pose (current_pose_ after updatePose)
+  double  cov[36];                // track mode: pose_covariance_
+  double  mean_pose[12];          // optional weighted mean (north_star extra)
+  double  mean_cov[36];
+};
+
+// Cross-CTA accumulators for one reduction round (grid mode); zero-initialised.
+struct pf_accum {
+  unsigned long long maxkey;      // (ord(w) << 32) | ~idx          -> atomicMax: max w, first index
+  unsigned long long minkey_inv;  // ~((ord(w) << 32) | idx)        -> atomicMax: min w, first index
+  long long sum;                  // sum of Q.30 weights
+  unsigned long long cntkey;      // (count << 32) | ~idx           -> atomicMax: max count, first index
+};
+
+// Decoupled look-back descriptor (grid mode scan), one per scan tile.
+struct pf_tile_desc {
+  long long agg_s, agg_m;         // tile aggregate (sum, running max of prefix)
+  long long inc_s, inc_m;         // inclusive prefix up to and including this tile
+  uint32_t flag;                  // epoch*4 + {1: aggregate ready, 2: inclusive ready}
+  uint32_t pad[7];
+};
+
+struct pf_kparams {
+  int N;                          // particles per tracker
+  int n_trackers;
+  int tracker_base;               // first tracker handled by blockIdx.y == 0
+  int D_max;                      // capacity of the per-frame blob arrays
+  int mode;                       // 0: per-frame (host tail), 1: device-resident tracking (device tail)
+  int n_frames;                   // frames processed by this launch
+  int frame0;                     // index of the first frame in the uploaded sequence (track mode)
+  int total_frames;               // frames uploaded (track mode)
+  int coop;                       // 1: grid-wide cooperation (gridDim.x > 1)
+  int want_mean;                  // compute weighted mean / covariance
+  // particle state
+  float4* pose0; float4* pose1;   // [tracker][3 planes][N]
+  float*  w;                      // [tracker][N] raw scores of the kept iteration
+  int*    kend;                   // [tracker][N] cumulative offspring count K(M_i)
+  int*    idx;                    // [tracker][N] source index of slot n for the current frame
+  int*    tile_kend;              // [tracker][ntiles_scan]
+  pf_tile_desc* desc;             // [ntiles_scan] (grid mode)
+  pf_accum* accum;                // [3] rotating slots (grid mode)
+  // per-tracker records
+  pf_frame_const* fconst;         // [tracker]
+  pf_tracker_state* state;        // [tracker]
+  pf_frame_result* result;        // per-frame mode: [tracker]; track mode: [tracker][total_frames]
+  // inputs
+  const double* blobs;            // per-frame mode: [tracker][D_max][2]; track mode: [tracker][total_frames][D_max][2]
+  const int* blob_count;          // track mode: [tracker][total_frames]
+  const double* times;            // track mode: [total_frames] time_to_predict
+  const uint32_t* seeds;          // track mode: [tracker][total_frames]
+  // constants
+  const float* obj_f;             // [tracker][PF_MAX_LED*3]
+  const double* obj_d;            // [tracker][PF_MAX_LED*3]
+  float K9f[9];
+  double K9d[9];
+  pf_score_cfg score;
+  double min_ang, max_ang, min_tr, max_tr;   // minAngularNoise.. (track mode recomputes the ranges per frame)
+  const uint32_t* rng_tab;        // [4*256]
+};

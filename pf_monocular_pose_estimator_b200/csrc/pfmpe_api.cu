@@ -1,0 +1,877 @@
+// pfmpe_api.cu -- host side of the C ABI declared in include/pfmpe.h.
+// Owns device memory, the stream and the launch geometry; all arithmetic of the hot path is in
+// the sm_100a kernels of pf_kernels.cuh.  There is no CPU execution path: every entry point that
+// needs the device fails with PFMPE_ERR_NO_DEVICE / PFMPE_ERR_CUDA if it is not usable.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/pfmpe.h"
+#include "pf_kernels.cuh"
+
+namespace {
+
+struct TrackSeq {
+  double* blobs = nullptr;
+  int* counts = nullptr;
+  double* times = nullptr;
+  uint32_t* seeds = nullptr;
+  pf_frame_result* result = nullptr;
+  int n_frames = 0;
+  bool owned = false;
+  int next_frame = -1;     // frame whose constants are currently staged in fconst (track mode)
+  int last_frame = -1;     // last frame processed by track_run
+};
+
+}  // namespace
+
+struct pfmpe_handle {
+  pfmpe_config cfg{};
+  pfmpe_pf_params prm{};
+  bool have_markers = false, have_camera = false, have_params = false;
+  std::vector<char> particles_set;
+  std::vector<double> markers;   // [tracker][PF_MAX_LED*3]
+  double K[9]{};
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  bool timing_valid = false;
+  uint64_t launches = 0;
+  int num_sms = 0;
+  int force_mode = 0;            // 0 auto, 1 batch, 2 grid (cfg.reserved[0])
+  int grid_cap = 0;              // cfg.reserved[1]
+  int info[4] = {0, 0, PF_BLOCK, 0};
+  int ntiles_scan = 0;
+  // device
+  float4 *pose0 = nullptr, *pose1 = nullptr, *gather_tmp = nullptr;
+  float* w = nullptr;
+  int *kend = nullptr, *idx = nullptr, *tile_kend = nullptr, *gather_idx = nullptr;
+  pf_tile_desc* desc = nullptr;
+  pf_accum* accum = nullptr;
+  unsigned char* inbox = nullptr;       // [fconst x n_trackers | blobs x n_trackers x max_blobs x 2]
+  pf_frame_const* fconst = nullptr;     // = inbox
+  double* blobs = nullptr;              // = inbox + ...
+  size_t inbox_bytes = 0, blobs_off = 0;
+  pf_tracker_state* state = nullptr;
+  pf_frame_result* result = nullptr;
+  float* obj_f = nullptr;
+  double* obj_d = nullptr;
+  uint32_t* rng_tab = nullptr;
+  // pinned host mirrors
+  unsigned char* h_inbox = nullptr;
+  pf_frame_result* h_result = nullptr;
+  pf_tracker_state* h_state = nullptr;
+  std::vector<long long> last_sum_fx;
+  bool last_was_track = false;
+  TrackSeq seq;
+  std::string err;
+};
+
+namespace {
+
+thread_local std::string g_create_err;
+
+#define PF_CUDA(h, call)                                                                         \
+  do {                                                                                           \
+    cudaError_t e_ = (call);                                                                     \
+    if (e_ != cudaSuccess) {                                                                     \
+      (h)->err = std::string(#call) + ": " + cudaGetErrorString(e_);                             \
+      return PFMPE_ERR_CUDA;                                                                     \
+    }                                                                                            \
+  } while (0)
+
+int fail(pfmpe_handle* h, int code, const char* msg)
+{
+  if (h) h->err = msg;
+  return code;
+}
+
+void build_rng_table(uint32_t* tab)
+{
+  uint32_t base = PF_RNG_A;
+  for (int d = 0; d < 4; ++d) {
+    tab[d * 256] = 1u;
+    for (int v = 1; v < 256; ++v) tab[d * 256 + v] = pf_modmul(tab[d * 256 + v - 1], base);
+    uint32_t nb = pf_modmul(tab[d * 256 + 255], base);   // base^256
+    base = nb;
+  }
+}
+
+template <typename T>
+cudaError_t dev_alloc(T** p, size_t n)
+{
+  return cudaMalloc((void**)p, n * sizeof(T));
+}
+
+void free_all(pfmpe_handle* h)
+{
+  cudaFree(h->pose0); cudaFree(h->pose1); cudaFree(h->gather_tmp); cudaFree(h->w); cudaFree(h->kend);
+  cudaFree(h->idx); cudaFree(h->tile_kend); cudaFree(h->gather_idx); cudaFree(h->desc); cudaFree(h->accum);
+  cudaFree(h->inbox); cudaFree(h->state); cudaFree(h->result); cudaFree(h->obj_f); cudaFree(h->obj_d);
+  cudaFree(h->rng_tab);
+  if (h->seq.owned) { cudaFree(h->seq.blobs); cudaFree(h->seq.counts); cudaFree(h->seq.times); cudaFree(h->seq.seeds); }
+  cudaFree(h->seq.result);
+  if (h->h_inbox) cudaFreeHost(h->h_inbox);
+  if (h->h_result) cudaFreeHost(h->h_result);
+  if (h->h_state) cudaFreeHost(h->h_state);
+  if (h->ev0) cudaEventDestroy(h->ev0);
+  if (h->ev1) cudaEventDestroy(h->ev1);
+  if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
+}
+
+void fill_kparams(const pfmpe_handle* h, pf_kparams& p)
+{
+  std::memset(&p, 0, sizeof p);
+  p.N = h->cfg.n_particles;
+  p.n_trackers = h->cfg.n_trackers;
+  p.D_max = h->cfg.max_blobs;
+  p.want_mean = (h->cfg.flags & PFMPE_FLAG_MEAN_COV) ? 1 : 0;
+  p.pose0 = h->pose0; p.pose1 = h->pose1; p.w = h->w; p.kend = h->kend; p.idx = h->idx;
+  p.tile_kend = h->tile_kend; p.desc = h->desc; p.accum = h->accum;
+  p.fconst = h->fconst; p.state = h->state;
+  p.obj_f = h->obj_f; p.obj_d = h->obj_d;
+  for (int i = 0; i < 9; ++i) { p.K9d[i] = h->K[i]; p.K9f[i] = (float)h->K[i]; }
+  p.score.tol = (float)h->prm.back_projection_pixel_tolerance;
+  p.score.inv_tol = (float)(1.0 / h->prm.back_projection_pixel_tolerance);
+  p.score.tol_pf = (float)h->prm.back_projection_pixel_tolerance_PF;
+  unsigned m = 0;
+  for (int i = 0; i < 5; ++i) if (h->prm.marker_downgrade[i]) m |= 1u << i;
+  p.score.dg_mask = m;
+  p.min_ang = h->prm.min_angular_noise; p.max_ang = h->prm.max_angular_noise;
+  p.min_tr = h->prm.min_transition_noise; p.max_tr = h->prm.max_transition_noise;
+  p.rng_tab = h->rng_tab;
+}
+
+typedef void (*frames_kernel_t)(const pf_kparams);
+
+frames_kernel_t kernel_for(int L)
+{
+  switch (L) {
+    case 1: return pf_frames_kernel<1>;
+    case 2: return pf_frames_kernel<2>;
+    case 3: return pf_frames_kernel<3>;
+    case 4: return pf_frames_kernel<4>;
+    case 5: return pf_frames_kernel<5>;
+    case 6: return pf_frames_kernel<6>;
+    case 7: return pf_frames_kernel<7>;
+    case 8: return pf_frames_kernel<8>;
+    default: return nullptr;
+  }
+}
+
+// Launch the frame kernel for trackers [t0, t0+nt).  mode 0: per-frame, 1: track.
+int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_frames)
+{
+  const int N = h->cfg.n_particles;
+  frames_kernel_t k = kernel_for(h->cfg.n_leds);
+  if (!k) return fail(h, PFMPE_ERR_UNSUPPORTED, "n_leds must be 1..8");
+  const size_t smem = (size_t)h->cfg.max_blobs * sizeof(pf_f2);
+  bool grid_mode;
+  if (h->force_mode == 1) grid_mode = false;
+  else if (h->force_mode == 2) grid_mode = true;
+  else grid_mode = (nt == 1) ? (N > 1024) : (N > 16384);
+
+  pf_kparams p;
+  fill_kparams(h, p);
+  p.mode = mode;
+  p.frame0 = frame0;
+  p.n_frames = n_frames;
+  if (mode == 1) {
+    p.blobs = h->seq.blobs; p.blob_count = h->seq.counts; p.times = h->seq.times; p.seeds = h->seq.seeds;
+    p.result = h->seq.result; p.total_frames = h->seq.n_frames;
+  } else {
+    p.blobs = h->blobs; p.result = h->result; p.total_frames = 1;
+  }
+  PF_CUDA(h, cudaEventRecord(h->ev0, h->stream));
+  if (!grid_mode) {
+    p.coop = 0;
+    p.tracker_base = t0;
+    dim3 grid(1, (unsigned)nt, 1);
+    h->info[0] = 1; h->info[1] = nt; h->info[3] = 0;
+    k<<<grid, PF_BLOCK, smem, h->stream>>>(p);
+    PF_CUDA(h, cudaGetLastError());
+    h->launches += 1;
+  } else {
+    int per_sm = 0;
+    PF_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, PF_BLOCK, smem));
+    int cap = per_sm * h->num_sms;
+    if (cap < 1) return fail(h, PFMPE_ERR_CUDA, "kernel cannot be made resident");
+    if (h->grid_cap > 0 && h->grid_cap < cap) cap = h->grid_cap;
+    int tiles = (N + PF_BLOCK - 1) / PF_BLOCK;
+    int G = tiles < cap ? tiles : cap;
+    if (G < 2) G = 2 <= cap ? 2 : 1;
+    p.coop = G > 1 ? 1 : 0;
+    h->info[0] = G; h->info[1] = 1; h->info[3] = p.coop;
+    for (int t = t0; t < t0 + nt; ++t) {
+      p.tracker_base = t;
+      PF_CUDA(h, cudaMemsetAsync(h->accum, 0, 3 * sizeof(pf_accum), h->stream));
+      void* args[] = {(void*)&p};
+      dim3 grid((unsigned)G, 1, 1);
+      if (p.coop) PF_CUDA(h, cudaLaunchCooperativeKernel((const void*)k, grid, dim3(PF_BLOCK), args, smem, h->stream));
+      else { k<<<grid, PF_BLOCK, smem, h->stream>>>(p); PF_CUDA(h, cudaGetLastError()); }
+      h->launches += 1;
+    }
+  }
+  PF_CUDA(h, cudaEventRecord(h->ev1, h->stream));
+  h->timing_valid = true;
+  return PFMPE_OK;
+}
+
+void cm16_to_planes(const double* poses, int N, float* planes /* 3*N*4 */)
+{
+  for (int n = 0; n < N; ++n) {
+    const double* m = poses + 16 * (size_t)n;
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 4; ++j) planes[((size_t)i * N + n) * 4 + j] = (float)m[i + 4 * j];
+  }
+}
+
+void planes_to_cm16(const float* planes, int N, double* poses)
+{
+  for (int n = 0; n < N; ++n) {
+    double* m = poses + 16 * (size_t)n;
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 4; ++j) m[i + 4 * j] = (double)planes[((size_t)i * N + n) * 4 + j];
+    m[3] = 0; m[7] = 0; m[11] = 0; m[15] = 1;
+  }
+}
+
+__global__ void pf_fill_kernel(float4* base, int N, float4 r0, float4 r1, float4 r2)
+{
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  base[n] = r0;
+  base[(size_t)N + n] = r1;
+  base[2 * (size_t)N + n] = r2;
+}
+
+// track mode: stage the constants of `frame` from the device-resident tracker state
+__global__ void pf_track_prepare_kernel(pf_kparams p, int frame)
+{
+  const int trk = blockIdx.x * blockDim.x + threadIdx.x;
+  if (trk >= p.n_trackers) return;
+  pf_tracker_state* st = p.state + trk;
+  if (st->failed) return;
+  pf_aff cur, prev, P, pred;
+  for (int i = 0; i < 12; ++i) { cur.a[i] = st->cur[i]; prev.a[i] = st->prev[i]; }
+  const double t_next = p.times[frame];
+  pf_predict_pose(prev, cur, st->t_prev, st->t_cur, t_next, P, pred);
+  st->t_pred = t_next;
+  for (int i = 0; i < 12; ++i) st->pred[i] = pred.a[i];
+  const size_t fi = (size_t)trk * p.total_frames + frame;
+  pf_make_frame_const(p.fconst[trk], cur, pred, P, pf_aff_identity(), st->isi, t_next - st->t_cur, p.seeds[fi],
+                      p.blob_count[fi], p.min_ang, p.max_ang, p.min_tr, p.max_tr);
+}
+
+}  // namespace
+
+// =========================================================================================
+// C ABI
+// =========================================================================================
+extern "C" {
+
+int pfmpe_version(void) { return PFMPE_VERSION; }
+
+const char* pfmpe_strerror(int s)
+{
+  switch (s) {
+    case PFMPE_OK: return "ok";
+    case PFMPE_ERR_INVALID: return "invalid argument";
+    case PFMPE_ERR_CUDA: return "CUDA error";
+    case PFMPE_ERR_NO_DEVICE: return "no usable CUDA device (no CPU fallback exists)";
+    case PFMPE_ERR_STATE: return "call sequence error";
+    case PFMPE_ERR_UNSUPPORTED: return "unsupported configuration";
+    case PFMPE_ERR_COMM: return "communicator error";
+    default: return "unknown status";
+  }
+}
+
+const char* pfmpe_last_error(const pfmpe_handle* h) { return h ? h->err.c_str() : g_create_err.c_str(); }
+
+int pfmpe_create(const pfmpe_config* cfg, pfmpe_handle** out)
+{
+  if (!cfg || !out) return PFMPE_ERR_INVALID;
+  *out = nullptr;
+  if (cfg->n_particles < 2 || cfg->n_trackers < 1 || cfg->n_leds < 1 || cfg->n_leds > PFMPE_MAX_LED ||
+      cfg->max_blobs < 1 || cfg->max_blobs > 4096) {
+    g_create_err = "pfmpe_create: n_particles >= 2, n_trackers >= 1, 1 <= n_leds <= 8, 1 <= max_blobs <= 4096";
+    return PFMPE_ERR_INVALID;
+  }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || cfg->device < 0 || cfg->device >= ndev) {
+    g_create_err = "pfmpe_create: no usable CUDA device";
+    (void)cudaGetLastError();
+    return PFMPE_ERR_NO_DEVICE;
+  }
+  pfmpe_handle* h = new (std::nothrow) pfmpe_handle();
+  if (!h) return PFMPE_ERR_INVALID;
+  h->cfg = *cfg;
+  h->force_mode = cfg->reserved[0];
+  h->grid_cap = cfg->reserved[1];
+  const size_t N = (size_t)cfg->n_particles, T = (size_t)cfg->n_trackers;
+  h->ntiles_scan = (int)((N + PF_SCAN_TILE - 1) / PF_SCAN_TILE);
+  h->particles_set.assign(T, 0);
+  h->markers.assign(T * PF_MAX_LED * 3, 0.0);
+  h->last_sum_fx.assign(T, 0);
+#define PF_TRY(call)                                                              \
+  do {                                                                            \
+    cudaError_t e_ = (call);                                                      \
+    if (e_ != cudaSuccess) {                                                      \
+      g_create_err = std::string(#call) + ": " + cudaGetErrorString(e_);          \
+      free_all(h); delete h;                                                      \
+      return PFMPE_ERR_CUDA;                                                      \
+    }                                                                             \
+  } while (0)
+  PF_TRY(cudaSetDevice(cfg->device));
+  cudaDeviceProp prop;
+  PF_TRY(cudaGetDeviceProperties(&prop, cfg->device));
+  h->num_sms = prop.multiProcessorCount;
+  PF_TRY(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+  h->own_stream = true;
+  PF_TRY(cudaEventCreate(&h->ev0));
+  PF_TRY(cudaEventCreate(&h->ev1));
+  PF_TRY(dev_alloc(&h->pose0, T * 3 * N));
+  PF_TRY(dev_alloc(&h->pose1, T * 3 * N));
+  PF_TRY(dev_alloc(&h->gather_tmp, 3 * N));
+  PF_TRY(dev_alloc(&h->w, T * N));
+  PF_TRY(dev_alloc(&h->kend, T * N));
+  PF_TRY(dev_alloc(&h->idx, T * N));
+  PF_TRY(dev_alloc(&h->gather_idx, N));
+  PF_TRY(dev_alloc(&h->tile_kend, T * (size_t)h->ntiles_scan));
+  PF_TRY(dev_alloc(&h->desc, (size_t)h->ntiles_scan));
+  PF_TRY(dev_alloc(&h->accum, 3));
+  h->blobs_off = (T * sizeof(pf_frame_const) + 255) / 256 * 256;
+  h->inbox_bytes = h->blobs_off + T * (size_t)cfg->max_blobs * 2 * sizeof(double);
+  PF_TRY(cudaMalloc((void**)&h->inbox, h->inbox_bytes));
+  h->fconst = reinterpret_cast<pf_frame_const*>(h->inbox);
+  h->blobs = reinterpret_cast<double*>(h->inbox + h->blobs_off);
+  PF_TRY(dev_alloc(&h->state, T));
+  PF_TRY(dev_alloc(&h->result, T));
+  PF_TRY(dev_alloc(&h->obj_f, T * PF_MAX_LED * 3));
+  PF_TRY(dev_alloc(&h->obj_d, T * PF_MAX_LED * 3));
+  PF_TRY(dev_alloc(&h->rng_tab, 1024));
+  PF_TRY(cudaMallocHost((void**)&h->h_inbox, h->inbox_bytes));
+  PF_TRY(cudaMallocHost((void**)&h->h_result, T * sizeof(pf_frame_result)));
+  PF_TRY(cudaMallocHost((void**)&h->h_state, T * sizeof(pf_tracker_state)));
+  std::memset(h->h_inbox, 0, h->inbox_bytes);
+  PF_TRY(cudaMemset(h->desc, 0, (size_t)h->ntiles_scan * sizeof(pf_tile_desc)));
+  PF_TRY(cudaMemset(h->accum, 0, 3 * sizeof(pf_accum)));
+  PF_TRY(cudaMemset(h->w, 0, T * N * sizeof(float)));
+  PF_TRY(cudaMemset(h->kend, 0, T * N * sizeof(int)));
+  PF_TRY(cudaMemset(h->idx, 0, T * N * sizeof(int)));
+  PF_TRY(cudaMemset(h->tile_kend, 0, T * (size_t)h->ntiles_scan * sizeof(int)));
+  PF_TRY(cudaMemset(h->result, 0, T * sizeof(pf_frame_result)));
+  std::memset(h->h_state, 0, T * sizeof(pf_tracker_state));
+  for (size_t t = 0; t < T; ++t) h->h_state[t].scan_epoch = 1u;
+  PF_TRY(cudaMemcpy(h->state, h->h_state, T * sizeof(pf_tracker_state), cudaMemcpyHostToDevice));
+  {
+    std::vector<uint32_t> tab(1024);
+    build_rng_table(tab.data());
+    PF_TRY(cudaMemcpy(h->rng_tab, tab.data(), 1024 * sizeof(uint32_t), cudaMemcpyHostToDevice));
+  }
+#undef PF_TRY
+  *out = h;
+  return PFMPE_OK;
+}
+
+int pfmpe_destroy(pfmpe_handle* h)
+{
+  if (!h) return PFMPE_ERR_INVALID;
+  cudaSetDevice(h->cfg.device);
+  if (h->stream) cudaStreamSynchronize(h->stream);
+  free_all(h);
+  delete h;
+  return PFMPE_OK;
+}
+
+int pfmpe_set_markers(pfmpe_handle* h, int tracker, const double* xyz, int n_leds)
+{
+  if (!h || !xyz) return PFMPE_ERR_INVALID;
+  if (n_leds != h->cfg.n_leds) return fail(h, PFMPE_ERR_INVALID, "n_leds differs from pfmpe_config.n_leds");
+  if (tracker < -1 || tracker >= h->cfg.n_trackers) return fail(h, PFMPE_ERR_INVALID, "tracker out of range");
+  const int T = h->cfg.n_trackers;
+  for (int t = 0; t < T; ++t)
+    if (tracker < 0 || tracker == t) std::memcpy(&h->markers[(size_t)t * PF_MAX_LED * 3], xyz, sizeof(double) * 3 * n_leds);
+  std::vector<float> f(h->markers.size());
+  for (size_t i = 0; i < f.size(); ++i) f[i] = (float)h->markers[i];
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  PF_CUDA(h, cudaMemcpy(h->obj_d, h->markers.data(), h->markers.size() * sizeof(double), cudaMemcpyHostToDevice));
+  PF_CUDA(h, cudaMemcpy(h->obj_f, f.data(), f.size() * sizeof(float), cudaMemcpyHostToDevice));
+  h->have_markers = true;
+  return PFMPE_OK;
+}
+
+int pfmpe_set_camera(pfmpe_handle* h, const double K[9], const double* D5)
+{
+  (void)D5;   // the PF projects with K only (project2d); D is accepted for interface parity
+  if (!h || !K) return PFMPE_ERR_INVALID;
+  std::memcpy(h->K, K, sizeof h->K);
+  h->have_camera = true;
+  return PFMPE_OK;
+}
+
+int pfmpe_set_params(pfmpe_handle* h, const pfmpe_pf_params* prm)
+{
+  if (!h || !prm) return PFMPE_ERR_INVALID;
+  if (!(prm->back_projection_pixel_tolerance > 0)) return fail(h, PFMPE_ERR_INVALID, "back_projection_pixel_tolerance must be > 0");
+  h->prm = *prm;
+  h->have_params = true;
+  return PFMPE_OK;
+}
+
+int pfmpe_set_particles(pfmpe_handle* h, int tracker, const double* poses, int n)
+{
+  if (!h || !poses) return PFMPE_ERR_INVALID;
+  if (n != h->cfg.n_particles) return fail(h, PFMPE_ERR_INVALID, "n differs from pfmpe_config.n_particles");
+  if (tracker < 0 || tracker >= h->cfg.n_trackers) return fail(h, PFMPE_ERR_INVALID, "tracker out of range");
+  const size_t N = (size_t)n;
+  std::vector<float> planes(3 * N * 4);
+  cm16_to_planes(poses, n, planes.data());
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  PF_CUDA(h, cudaMemcpy(h->pose0 + (size_t)tracker * 3 * N, planes.data(), planes.size() * sizeof(float), cudaMemcpyHostToDevice));
+  PF_CUDA(h, cudaMemcpy(h->pose1 + (size_t)tracker * 3 * N, planes.data(), planes.size() * sizeof(float), cudaMemcpyHostToDevice));
+  PF_CUDA(h, cudaMemcpy(h->h_state + tracker, h->state + tracker, sizeof(pf_tracker_state), cudaMemcpyDeviceToHost));
+  pf_tracker_state& s = h->h_state[tracker];
+  s.src_buf = 0; s.src_mode = 0; s.t_buf = 1; s.failed = 0;
+  PF_CUDA(h, cudaMemcpy(h->state + tracker, &s, sizeof s, cudaMemcpyHostToDevice));
+  h->particles_set[tracker] = 1;
+  return PFMPE_OK;
+}
+
+static int check_ready(pfmpe_handle* h)
+{
+  if (!h->have_markers || !h->have_camera || !h->have_params)
+    return fail(h, PFMPE_ERR_STATE, "set_markers, set_camera and set_params must be called first");
+  return PFMPE_OK;
+}
+
+static int stage_frame(pfmpe_handle* h, int t, const pfmpe_frame_in* in)
+{
+  if (in->n_image_points < 0 || in->n_image_points > h->cfg.max_blobs) return fail(h, PFMPE_ERR_INVALID, "n_image_points exceeds max_blobs");
+  if (in->n_image_points > 0 && !in->image_points) return fail(h, PFMPE_ERR_INVALID, "image_points is NULL");
+  if (!h->particles_set[t]) return fail(h, PFMPE_ERR_STATE, "set_particles / track_init must precede update");
+  pf_frame_const* fc = reinterpret_cast<pf_frame_const*>(h->h_inbox) + t;
+  pf_make_frame_const(*fc, pf_aff_from_cm16(in->current_pose), pf_aff_from_cm16(in->predicted_pose),
+                      pf_aff_from_cm16(in->prediction_matrix), pf_aff_from_cm16(in->cam_move_inv),
+                      in->it_since_initialized, in->dt, in->seed, in->n_image_points, h->prm.min_angular_noise,
+                      h->prm.max_angular_noise, h->prm.min_transition_noise, h->prm.max_transition_noise);
+  double* b = reinterpret_cast<double*>(h->h_inbox + h->blobs_off) + (size_t)t * h->cfg.max_blobs * 2;
+  if (in->n_image_points) std::memcpy(b, in->image_points, sizeof(double) * 2 * (size_t)in->n_image_points);
+  return PFMPE_OK;
+}
+
+static void unpack_result(const pf_frame_result& r, pfmpe_frame_out* o)
+{
+  std::memset(o, 0, sizeof *o);
+  o->status = r.status;
+  o->iterations = r.iterations;
+  o->best_iteration = r.best_iteration;
+  o->resampled = r.resampled;
+  o->highest_prob = (double)r.highest_prob;
+  o->weight_sum = (double)r.sum_fx / 1073741824.0;
+  o->most_likely_particle_idx = r.most_likely_particle_idx;
+  o->most_likely_pose_idx = r.most_likely_pose_idx;
+  o->max_count = r.max_count;
+  o->n_correspondences = r.npairs;
+  for (int i = 0; i < 2 * PFMPE_MAX_LED; ++i) o->correspondences[i] = r.pairs[i];
+  pf_aff T;
+  for (int i = 0; i < 12; ++i) T.a[i] = (double)r.winner_pose[i];
+  pf_aff_to_cm16(T, o->winner_pose);
+  for (int i = 0; i < 12; ++i) T.a[i] = r.mean_pose[i];
+  pf_aff_to_cm16(T, o->mean_pose);
+  for (int i = 0; i < 36; ++i) o->mean_cov[i] = r.mean_cov[i];
+}
+
+static int run_update(pfmpe_handle* h, int t0, int nt, const pfmpe_frame_in* in, pfmpe_frame_out* out)
+{
+  int rc = check_ready(h);
+  if (rc) return rc;
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  for (int i = 0; i < nt; ++i) {
+    rc = stage_frame(h, t0 + i, in + i);
+    if (rc) return rc;
+  }
+  const int T = h->cfg.n_trackers;
+  if (nt == T) {
+    PF_CUDA(h, cudaMemcpyAsync(h->inbox, h->h_inbox, h->inbox_bytes, cudaMemcpyHostToDevice, h->stream));
+  } else {
+    PF_CUDA(h, cudaMemcpyAsync(h->fconst + t0, reinterpret_cast<pf_frame_const*>(h->h_inbox) + t0,
+                               sizeof(pf_frame_const) * nt, cudaMemcpyHostToDevice, h->stream));
+    const size_t off = (size_t)t0 * h->cfg.max_blobs * 2;
+    PF_CUDA(h, cudaMemcpyAsync(h->blobs + off, reinterpret_cast<double*>(h->h_inbox + h->blobs_off) + off,
+                               sizeof(double) * 2 * (size_t)h->cfg.max_blobs * nt, cudaMemcpyHostToDevice, h->stream));
+  }
+  rc = launch_frames(h, 0, t0, nt, 0, 1);
+  if (rc) return rc;
+  PF_CUDA(h, cudaMemcpyAsync(h->h_result + t0, h->result + t0, sizeof(pf_frame_result) * nt, cudaMemcpyDeviceToHost, h->stream));
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  for (int i = 0; i < nt; ++i) {
+    unpack_result(h->h_result[t0 + i], out + i);
+    h->last_sum_fx[t0 + i] = h->h_result[t0 + i].sum_fx;
+  }
+  h->last_was_track = false;
+  return PFMPE_OK;
+}
+
+int pfmpe_update(pfmpe_handle* h, int tracker, const pfmpe_frame_in* in, pfmpe_frame_out* out)
+{
+  if (!h || !in || !out) return PFMPE_ERR_INVALID;
+  if (tracker < 0 || tracker >= h->cfg.n_trackers) return fail(h, PFMPE_ERR_INVALID, "tracker out of range");
+  return run_update(h, tracker, 1, in, out);
+}
+
+int pfmpe_update_batch(pfmpe_handle* h, const pfmpe_frame_in* in, pfmpe_frame_out* out)
+{
+  if (!h || !in || !out) return PFMPE_ERR_INVALID;
+  return run_update(h, 0, h->cfg.n_trackers, in, out);
+}
+
+// ---- getters ------------------------------------------------------------------------------
+static int fetch_state(pfmpe_handle* h, int tracker)
+{
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  PF_CUDA(h, cudaMemcpy(h->h_state + tracker, h->state + tracker, sizeof(pf_tracker_state), cudaMemcpyDeviceToHost));
+  return PFMPE_OK;
+}
+
+// run the gather kernel: gather_tmp = newPoseEstimation, gather_idx = Particle_index per slot
+static int run_gather(pfmpe_handle* h, int tracker)
+{
+  const pf_tracker_state& s = h->h_state[tracker];
+  const size_t N = (size_t)h->cfg.n_particles;
+  const float4* T = (s.src_buf == 0 ? h->pose0 : h->pose1) + (size_t)tracker * 3 * N;
+  const int blocks = (int)((N + PF_BLOCK - 1) / PF_BLOCK);
+  pf_gather_kernel<<<blocks, PF_BLOCK, 0, h->stream>>>(T, h->kend + (size_t)tracker * N,
+                                                      h->tile_kend + (size_t)tracker * h->ntiles_scan, h->ntiles_scan,
+                                                      (int)N, s.src_mode, h->gather_tmp, h->gather_idx);
+  PF_CUDA(h, cudaGetLastError());
+  h->launches += 1;
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  return PFMPE_OK;
+}
+
+int pfmpe_get_particles(pfmpe_handle* h, int tracker, int which, double* poses)
+{
+  if (!h || !poses) return PFMPE_ERR_INVALID;
+  if (tracker < 0 || tracker >= h->cfg.n_trackers) return fail(h, PFMPE_ERR_INVALID, "tracker out of range");
+  int rc = fetch_state(h, tracker);
+  if (rc) return rc;
+  const size_t N = (size_t)h->cfg.n_particles;
+  std::vector<float> planes(3 * N * 4);
+  const float4* src;
+  if (which == 0) {
+    src = (h->h_state[tracker].t_buf == 0 ? h->pose0 : h->pose1) + (size_t)tracker * 3 * N;
+  } else {
+    rc = run_gather(h, tracker);
+    if (rc) return rc;
+    src = h->gather_tmp;
+  }
+  PF_CUDA(h, cudaMemcpy(planes.data(), src, planes.size() * sizeof(float), cudaMemcpyDeviceToHost));
+  planes_to_cm16(planes.data(), (int)N, poses);
+  return PFMPE_OK;
+}
+
+static int current_sum_fx(pfmpe_handle* h, int tracker, long long* s)
+{
+  if (h->last_was_track && h->seq.last_frame >= 0) {
+    pf_frame_result r;
+    PF_CUDA(h, cudaMemcpy(&r, h->seq.result + (size_t)tracker * h->seq.n_frames + h->seq.last_frame, sizeof r,
+                          cudaMemcpyDeviceToHost));
+    *s = r.sum_fx;
+  } else *s = h->last_sum_fx[tracker];
+  return PFMPE_OK;
+}
+
+int pfmpe_get_weights(pfmpe_handle* h, int tracker, int normalised, double* w)
+{
+  if (!h || !w) return PFMPE_ERR_INVALID;
+  if (tracker < 0 || tracker >= h->cfg.n_trackers) return fail(h, PFMPE_ERR_INVALID, "tracker out of range");
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  const size_t N = (size_t)h->cfg.n_particles;
+  std::vector<float> f(N);
+  PF_CUDA(h, cudaMemcpy(f.data(), h->w + (size_t)tracker * N, N * sizeof(float), cudaMemcpyDeviceToHost));
+  double S = 1.0;
+  if (normalised) {
+    long long sfx = 0;
+    int rc = current_sum_fx(h, tracker, &sfx);
+    if (rc) return rc;
+    S = sfx != 0 ? (double)sfx / 1073741824.0 : 1.0;   // probPart / probPartSum only if the sum is non-zero (:628)
+  }
+  for (size_t i = 0; i < N; ++i) w[i] = (double)f[i] / S;
+  return PFMPE_OK;
+}
+
+int pfmpe_get_resample_indices(pfmpe_handle* h, int tracker, int32_t* idx)
+{
+  if (!h || !idx) return PFMPE_ERR_INVALID;
+  if (tracker < 0 || tracker >= h->cfg.n_trackers) return fail(h, PFMPE_ERR_INVALID, "tracker out of range");
+  int rc = fetch_state(h, tracker);
+  if (rc) return rc;
+  if (h->h_state[tracker].src_mode != 1) return fail(h, PFMPE_ERR_STATE, "the last frame of this tracker was not resampled");
+  rc = run_gather(h, tracker);
+  if (rc) return rc;
+  PF_CUDA(h, cudaMemcpy(idx, h->gather_idx, (size_t)h->cfg.n_particles * sizeof(int), cudaMemcpyDeviceToHost));
+  return PFMPE_OK;
+}
+
+int pfmpe_get_resample_counts(pfmpe_handle* h, int tracker, uint32_t* count)
+{
+  if (!h || !count) return PFMPE_ERR_INVALID;
+  if (tracker < 0 || tracker >= h->cfg.n_trackers) return fail(h, PFMPE_ERR_INVALID, "tracker out of range");
+  int rc = fetch_state(h, tracker);
+  if (rc) return rc;
+  if (h->h_state[tracker].src_mode != 1) return fail(h, PFMPE_ERR_STATE, "the last frame of this tracker was not resampled");
+  const size_t N = (size_t)h->cfg.n_particles;
+  std::vector<int> ke(N);
+  PF_CUDA(h, cudaMemcpy(ke.data(), h->kend + (size_t)tracker * N, N * sizeof(int), cudaMemcpyDeviceToHost));
+  int prev = 0;
+  for (size_t i = 0; i < N; ++i) { count[i] = (uint32_t)(ke[i] - prev); prev = ke[i]; }
+  return PFMPE_OK;
+}
+
+// ---- host tail ----------------------------------------------------------------------------
+int pfmpe_optimise_pose(const double K[9], const double* markers_xyz, int n_leds, const double* image_points,
+                        int n_image_points, const uint32_t* correspondences, int n_correspondences,
+                        double pose[16], double cov[36], int* iters)
+{
+  if (!K || !markers_xyz || !pose || !cov || n_correspondences < 0 || (n_correspondences > 0 && (!correspondences || !image_points)))
+    return PFMPE_ERR_INVALID;
+  for (int i = 0; i < n_correspondences; ++i) {
+    if (correspondences[2 * i] < 1 || (int)correspondences[2 * i] > n_leds) return PFMPE_ERR_INVALID;
+    if ((int)correspondences[2 * i + 1] > n_image_points) return PFMPE_ERR_INVALID;
+  }
+  pf_aff T = pf_aff_from_cm16(pose);
+  double c[36];
+  const int it = pf_optimise_pose(K, markers_xyz, image_points, correspondences, n_correspondences, T, c);
+  pf_aff_to_cm16(T, pose);
+  for (int i = 0; i < 6; ++i)
+    for (int j = 0; j < 6; ++j) cov[i + 6 * j] = c[6 * i + j];
+  if (iters) *iters = it;
+  return PFMPE_OK;
+}
+
+int pfmpe_predict_pose(const double previous_pose[16], const double current_pose[16], double previous_time,
+                       double current_time, double time_to_predict, double prediction_matrix[16],
+                       double predicted_pose[16])
+{
+  if (!previous_pose || !current_pose || !prediction_matrix || !predicted_pose) return PFMPE_ERR_INVALID;
+  pf_aff P, pred;
+  pf_predict_pose(pf_aff_from_cm16(previous_pose), pf_aff_from_cm16(current_pose), previous_time, current_time,
+                  time_to_predict, P, pred);
+  pf_aff_to_cm16(P, prediction_matrix);
+  pf_aff_to_cm16(pred, predicted_pose);
+  return PFMPE_OK;
+}
+
+int pfmpe_exponential_map(const double twist[6], double pose[16])
+{
+  if (!twist || !pose) return PFMPE_ERR_INVALID;
+  pf_aff_to_cm16(pf_exp_map(twist), pose);
+  return PFMPE_OK;
+}
+
+int pfmpe_logarithm_map(const double pose[16], double twist[6])
+{
+  if (!pose || !twist) return PFMPE_ERR_INVALID;
+  pf_log_map(pf_aff_from_cm16(pose), twist);
+  return PFMPE_OK;
+}
+
+// ---- device-resident tracking ----------------------------------------------------------------
+int pfmpe_track_init(pfmpe_handle* h, int tracker, const double pose0[16], double t0, const double pose1[16], double t1)
+{
+  if (!h || !pose0 || !pose1) return PFMPE_ERR_INVALID;
+  if (tracker < 0 || tracker >= h->cfg.n_trackers) return fail(h, PFMPE_ERR_INVALID, "tracker out of range");
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  pf_tracker_state s;
+  PF_CUDA(h, cudaMemcpyAsync(&h->h_state[tracker], h->state + tracker, sizeof s, cudaMemcpyDeviceToHost, h->stream));
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  s = h->h_state[tracker];
+  const pf_aff a0 = pf_aff_from_cm16(pose0), a1 = pf_aff_from_cm16(pose1);
+  for (int i = 0; i < 12; ++i) { s.prev[i] = a0.a[i]; s.cur[i] = a1.a[i]; s.pred[i] = a1.a[i]; }
+  s.t_prev = t0; s.t_cur = t1; s.t_pred = t1;
+  for (int i = 0; i < 36; ++i) s.cov[i] = 0.0;
+  s.isi = 2; s.failed = 0; s.src_buf = 0; s.src_mode = 0; s.t_buf = 1; s.frames_done = 0;
+  h->h_state[tracker] = s;
+  PF_CUDA(h, cudaMemcpyAsync(h->state + tracker, &h->h_state[tracker], sizeof s, cudaMemcpyHostToDevice, h->stream));
+  const pf_pose f = pf_aff_to_f32(a1);
+  const int N = h->cfg.n_particles;
+  const float4 r0 = make_float4(f.p[0], f.p[1], f.p[2], f.p[3]), r1 = make_float4(f.p[4], f.p[5], f.p[6], f.p[7]),
+               r2 = make_float4(f.p[8], f.p[9], f.p[10], f.p[11]);
+  const int blocks = (N + 255) / 256;
+  pf_fill_kernel<<<blocks, 256, 0, h->stream>>>(h->pose0 + (size_t)tracker * 3 * N, N, r0, r1, r2);
+  pf_fill_kernel<<<blocks, 256, 0, h->stream>>>(h->pose1 + (size_t)tracker * 3 * N, N, r0, r1, r2);
+  PF_CUDA(h, cudaGetLastError());
+  h->launches += 2;
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));   // h_state is reused by the next call
+  h->particles_set[tracker] = 1;
+  h->seq.next_frame = -1;
+  return PFMPE_OK;
+}
+
+static int seq_release(pfmpe_handle* h)
+{
+  if (h->seq.owned) { cudaFree(h->seq.blobs); cudaFree(h->seq.counts); cudaFree(h->seq.times); cudaFree(h->seq.seeds); }
+  cudaFree(h->seq.result);
+  h->seq = TrackSeq();
+  return PFMPE_OK;
+}
+
+static int seq_alloc_results(pfmpe_handle* h, int n_frames)
+{
+  const size_t n = (size_t)h->cfg.n_trackers * n_frames;
+  PF_CUDA(h, dev_alloc(&h->seq.result, n));
+  PF_CUDA(h, cudaMemset(h->seq.result, 0, n * sizeof(pf_frame_result)));
+  return PFMPE_OK;
+}
+
+int pfmpe_track_upload(pfmpe_handle* h, int n_frames, const double* image_points, const int32_t* counts,
+                       const double* times, const uint32_t* seeds)
+{
+  if (!h || n_frames < 1 || !image_points || !counts || !times || !seeds) return PFMPE_ERR_INVALID;
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  const size_t T = (size_t)h->cfg.n_trackers, F = (size_t)n_frames, D = (size_t)h->cfg.max_blobs;
+  for (size_t i = 0; i < T * F; ++i)
+    if (counts[i] < 0 || counts[i] > h->cfg.max_blobs) return fail(h, PFMPE_ERR_INVALID, "blob count exceeds max_blobs");
+  seq_release(h);
+  h->seq.owned = true;
+  h->seq.n_frames = n_frames;
+  PF_CUDA(h, dev_alloc(&h->seq.blobs, T * F * D * 2));
+  PF_CUDA(h, dev_alloc(&h->seq.counts, T * F));
+  PF_CUDA(h, dev_alloc(&h->seq.times, F));
+  PF_CUDA(h, dev_alloc(&h->seq.seeds, T * F));
+  PF_CUDA(h, cudaMemcpy(h->seq.blobs, image_points, T * F * D * 2 * sizeof(double), cudaMemcpyHostToDevice));
+  PF_CUDA(h, cudaMemcpy(h->seq.counts, counts, T * F * sizeof(int), cudaMemcpyHostToDevice));
+  PF_CUDA(h, cudaMemcpy(h->seq.times, times, F * sizeof(double), cudaMemcpyHostToDevice));
+  PF_CUDA(h, cudaMemcpy(h->seq.seeds, seeds, T * F * sizeof(uint32_t), cudaMemcpyHostToDevice));
+  return seq_alloc_results(h, n_frames);
+}
+
+int pfmpe_track_attach(pfmpe_handle* h, int n_frames, const void* d_image_points, const void* d_counts,
+                       const void* d_times, const void* d_seeds)
+{
+  if (!h || n_frames < 1 || !d_image_points || !d_counts || !d_times || !d_seeds) return PFMPE_ERR_INVALID;
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  seq_release(h);
+  h->seq.owned = false;
+  h->seq.n_frames = n_frames;
+  h->seq.blobs = (double*)d_image_points;
+  h->seq.counts = (int*)d_counts;
+  h->seq.times = (double*)d_times;
+  h->seq.seeds = (uint32_t*)d_seeds;
+  return seq_alloc_results(h, n_frames);
+}
+
+int pfmpe_track_run(pfmpe_handle* h, int first_frame, int n_frames)
+{
+  if (!h) return PFMPE_ERR_INVALID;
+  int rc = check_ready(h);
+  if (rc) return rc;
+  if (!h->seq.blobs) return fail(h, PFMPE_ERR_STATE, "track_upload / track_attach must precede track_run");
+  if (first_frame < 0 || n_frames < 1 || first_frame + n_frames > h->seq.n_frames) return fail(h, PFMPE_ERR_INVALID, "frame range outside the uploaded sequence");
+  for (int t = 0; t < h->cfg.n_trackers; ++t)
+    if (!h->particles_set[t]) return fail(h, PFMPE_ERR_STATE, "track_init must be called for every tracker");
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  if (h->seq.next_frame != first_frame) {
+    pf_kparams p;
+    fill_kparams(h, p);
+    p.blob_count = h->seq.counts; p.times = h->seq.times; p.seeds = h->seq.seeds; p.total_frames = h->seq.n_frames;
+    const int T = h->cfg.n_trackers;
+    pf_track_prepare_kernel<<<(T + 127) / 128, 128, 0, h->stream>>>(p, first_frame);
+    PF_CUDA(h, cudaGetLastError());
+    h->launches += 1;
+  }
+  rc = launch_frames(h, 1, 0, h->cfg.n_trackers, first_frame, n_frames);
+  if (rc) return rc;
+  h->seq.next_frame = first_frame + n_frames;   // the tail staged the constants of the following frame
+  h->seq.last_frame = first_frame + n_frames - 1;
+  h->last_was_track = true;
+  return PFMPE_OK;
+}
+
+int pfmpe_track_results(pfmpe_handle* h, int tracker, int first_frame, int n_frames, pfmpe_track_result* out)
+{
+  if (!h || !out) return PFMPE_ERR_INVALID;
+  if (tracker < 0 || tracker >= h->cfg.n_trackers) return fail(h, PFMPE_ERR_INVALID, "tracker out of range");
+  if (!h->seq.result || first_frame < 0 || n_frames < 1 || first_frame + n_frames > h->seq.n_frames)
+    return fail(h, PFMPE_ERR_INVALID, "frame range outside the uploaded sequence");
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  std::vector<pf_frame_result> r((size_t)n_frames);
+  PF_CUDA(h, cudaMemcpy(r.data(), h->seq.result + (size_t)tracker * h->seq.n_frames + first_frame,
+                        r.size() * sizeof(pf_frame_result), cudaMemcpyDeviceToHost));
+  for (int f = 0; f < n_frames; ++f) {
+    const pf_frame_result& s = r[f];
+    pfmpe_track_result* o = out + f;
+    std::memset(o, 0, sizeof *o);
+    o->status = s.status; o->flag_fail = s.flag_fail; o->iterations = s.iterations; o->gn_iterations = s.gn_iters;
+    o->most_likely_pose_idx = s.most_likely_pose_idx; o->max_count = s.max_count;
+    o->highest_prob = s.highest_prob; o->weight_sum = (double)s.sum_fx / 1073741824.0;
+    pf_aff T;
+    for (int i = 0; i < 12; ++i) T.a[i] = s.pose[i];
+    pf_aff_to_cm16(T, o->pose);
+    for (int i = 0; i < 6; ++i) for (int j = 0; j < 6; ++j) o->cov[i + 6 * j] = s.cov[6 * i + j];
+    for (int i = 0; i < 12; ++i) T.a[i] = (double)s.winner_pose[i];
+    pf_aff_to_cm16(T, o->winner_pose);
+    o->n_correspondences = s.npairs;
+    for (int i = 0; i < 2 * PFMPE_MAX_LED; ++i) o->correspondences[i] = s.pairs[i];
+  }
+  return PFMPE_OK;
+}
+
+// ---- streams / timing ---------------------------------------------------------------------
+int pfmpe_set_stream(pfmpe_handle* h, void* cuda_stream)
+{
+  if (!h) return PFMPE_ERR_INVALID;
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  if (h->stream) PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
+  h->stream = (cudaStream_t)cuda_stream;
+  h->own_stream = false;
+  return PFMPE_OK;
+}
+
+int pfmpe_sync(pfmpe_handle* h)
+{
+  if (!h) return PFMPE_ERR_INVALID;
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  return PFMPE_OK;
+}
+
+int pfmpe_last_launch_ms(pfmpe_handle* h, float* ms)
+{
+  if (!h || !ms) return PFMPE_ERR_INVALID;
+  if (!h->timing_valid) return fail(h, PFMPE_ERR_STATE, "nothing has been launched yet");
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  PF_CUDA(h, cudaEventSynchronize(h->ev1));
+  PF_CUDA(h, cudaEventElapsedTime(ms, h->ev0, h->ev1));
+  return PFMPE_OK;
+}
+
+int pfmpe_launch_count(const pfmpe_handle* h, uint64_t* n)
+{
+  if (!h || !n) return PFMPE_ERR_INVALID;
+  *n = h->launches;
+  return PFMPE_OK;
+}
+
+int pfmpe_launch_info(const pfmpe_handle* h, int32_t info[4])
+{
+  if (!h || !info) return PFMPE_ERR_INVALID;
+  for (int i = 0; i < 4; ++i) info[i] = h->info[i];
+  return PFMPE_OK;
+}
+
+}  // extern "C"
