@@ -454,9 +454,9 @@ static int check_ready(pfmpe_handle* h)
 
 static int stage_frame(pfmpe_handle* h, int t, const pfmpe_frame_in* in)
 {
+  if (!h->particles_set[t]) return fail(h, PFMPE_ERR_STATE, "set_particles / track_init must precede update");
   if (in->n_image_points < 0 || in->n_image_points > h->cfg.max_blobs) return fail(h, PFMPE_ERR_INVALID, "n_image_points exceeds max_blobs");
   if (in->n_image_points > 0 && !in->image_points) return fail(h, PFMPE_ERR_INVALID, "image_points is NULL");
-  if (!h->particles_set[t]) return fail(h, PFMPE_ERR_STATE, "set_particles / track_init must precede update");
   pf_frame_const* fc = reinterpret_cast<pf_frame_const*>(h->h_inbox) + t;
   pf_make_frame_const(*fc, pf_aff_from_cm16(in->current_pose), pf_aff_from_cm16(in->predicted_pose),
                       pf_aff_from_cm16(in->prediction_matrix), pf_aff_from_cm16(in->cam_move_inv),

@@ -143,3 +143,56 @@ def blob_tensor(scenes, frames, d_max=None):
             out[i, j, : b.shape[0]] = b
             cnt[i, j] = b.shape[0]
     return out, cnt
+
+
+def true_pose_batch(t, phase):
+    """Vectorised true_pose: t scalar, phase (T,) -> (T,4,4)."""
+    tt = t + np.asarray(phase, dtype=np.float64)
+    n = tt.shape[0]
+
+    def rz(a):
+        c, s = np.cos(a), np.sin(a)
+        R = np.zeros((n, 3, 3)); R[:, 0, 0] = c; R[:, 0, 1] = -s; R[:, 1, 0] = s; R[:, 1, 1] = c; R[:, 2, 2] = 1
+        return R
+
+    def ry(a):
+        c, s = np.cos(a), np.sin(a)
+        R = np.zeros((n, 3, 3)); R[:, 0, 0] = c; R[:, 0, 2] = s; R[:, 1, 1] = 1; R[:, 2, 0] = -s; R[:, 2, 2] = c
+        return R
+
+    def rx(a):
+        c, s = np.cos(a), np.sin(a)
+        R = np.zeros((n, 3, 3)); R[:, 0, 0] = 1; R[:, 1, 1] = c; R[:, 1, 2] = -s; R[:, 2, 1] = s; R[:, 2, 2] = c
+        return R
+
+    T = np.zeros((n, 4, 4))
+    T[:, :3, :3] = rz(0.4 * np.sin(0.5 * tt)) @ ry(0.3 * np.sin(0.8 * tt + 1.0)) @ rx(0.3 * np.sin(0.6 * tt + 2.0))
+    T[:, 0, 3] = 0.3 * np.sin(0.7 * tt)
+    T[:, 1, 3] = 0.2 * np.sin(1.1 * tt + 0.5)
+    T[:, 2, 3] = 2.0 + 0.5 * np.sin(0.4 * tt)
+    T[:, 3, 3] = 1.0
+    return T
+
+
+def blob_tensor_fast(trackers, frames, n_outliers=10, markers=MARKERS_5, K=K_README, noise_px=0.3, seed=20240001):
+    """Vectorised synthetic detections for many trackers (bench workloads): same distribution as
+    blobs_for_frame (true projections + N(0, noise^2) + uniform outliers, shuffled), one seeded
+    generator for the whole tensor.  Returns (T, F, D, 2) float64 and (T, F) int32 counts."""
+    trackers = np.asarray(trackers)
+    phase = tracker_phase(trackers.astype(np.float64))
+    rng = np.random.default_rng(seed)
+    L = markers.shape[0]
+    D = L + n_outliers
+    out = np.zeros((len(trackers), len(frames), D, 2))
+    for j, f in enumerate(frames):
+        T = true_pose_batch(f * DT, phase)
+        pc = np.einsum("tij,lj->tli", T[:, :3, :3], markers) + T[:, None, :3, 3]
+        p = pc @ np.asarray(K).T
+        uv = p[:, :, :2] / p[:, :, 2:3] + rng.normal(0.0, noise_px, size=(len(trackers), L, 2))
+        o = np.stack([rng.uniform(0, IMAGE_W, size=(len(trackers), n_outliers)),
+                      rng.uniform(0, IMAGE_H, size=(len(trackers), n_outliers))], axis=-1)
+        pts = np.concatenate([uv, o], axis=1)
+        perm = np.argsort(rng.uniform(size=(len(trackers), D)), axis=1)
+        out[:, j] = np.take_along_axis(pts, perm[:, :, None], axis=1)
+    cnt = np.full((len(trackers), len(frames)), D, dtype=np.int32)
+    return out, cnt

@@ -1,0 +1,92 @@
+"""-m gpu: device-resident tracking (whole sequences on the GPU, FP64 tail on the device) against
+(a) the per-frame C-ABI path with the host FP64 tail and (b) the oracle tracker."""
+import numpy as np
+import pytest
+
+from oracle import orc
+from pf_monocular_pose_estimator_b200 import capi, scenes as S
+from tests.host_loop import HostTracker
+
+pytestmark = pytest.mark.gpu
+
+
+def _upload(h, scenes, first, n_frames, d_max):
+    frames = list(range(first, first + n_frames))
+    blobs, counts = S.blob_tensor(scenes, frames, d_max=d_max)
+    times = np.array([scenes[0].time(f) for f in frames])
+    seeds = np.array([[s.seed(f) for f in frames] for s in scenes], dtype=np.uint32)
+    h.track_upload(blobs, counts, times, seeds)
+
+
+@pytest.mark.parametrize("N,mode", [(100, 0), (2000, 2)])
+def test_track_mode_matches_host_loop(N, mode):
+    sc = S.Scene()
+    F = 12
+    # (a) per-frame path + host tail
+    ha = capi.Handle(N, max_blobs=16, force_mode=mode)
+    ha.configure(sc.markers, sc.K, sc.params)
+    trk = HostTracker(ha, sc)
+    host = [trk.frame(f) for f in range(2, 2 + F)]
+    # (b) device-resident
+    hb = capi.Handle(N, max_blobs=16, force_mode=mode)
+    hb.configure(sc.markers, sc.K, sc.params)
+    hb.track_init(sc.pose(0), sc.time(0), sc.pose(1), sc.time(1))
+    _upload(hb, [sc], 2, F, 16)
+    hb.track_run(0, 5)          # split in two launches: constants are handed over on the device
+    hb.track_run(5, F - 5)
+    dev = hb.track_results(0, F)
+    for f in range(F):
+        a, b = host[f], dev[f]
+        assert b["status"] == a["status"] == 1 and b["iterations"] == a["iterations"]
+        assert b["most_likely_pose_idx"] == a["most_likely_pose_idx"] and b["max_count"] == a["max_count"]
+        assert b["correspondences"].tolist() == a["correspondences"].tolist()
+        np.testing.assert_allclose(b["winner_pose"], a["winner_pose"], atol=0)
+        np.testing.assert_allclose(b["pose"], a["pose"], atol=1e-9)
+        np.testing.assert_allclose(b["cov"], a["cov"], rtol=1e-6, atol=1e-12)
+        assert b["flag_fail"] == a["flag_fail"]
+    np.testing.assert_array_equal(hb.particles(0), ha.particles(0))
+    np.testing.assert_array_equal(hb.particles(1), ha.particles(1))
+    ha.close(); hb.close()
+
+
+def test_track_mode_batch_of_trackers_follows_truth_and_oracle():
+    N, T, F = 256, 6, 30
+    scenes = [S.Scene(tracker=t) for t in range(T)]
+    h = capi.Handle(N, n_trackers=T, max_blobs=16)
+    h.configure(scenes[0].markers, scenes[0].K, scenes[0].params)
+    for t, sc in enumerate(scenes):
+        h.track_init(sc.pose(0), sc.time(0), sc.pose(1), sc.time(1), tracker=t)
+    _upload(h, scenes, 2, F, 16)
+    h.track_run(0, F)
+    for t, sc in enumerate(scenes):
+        res = h.track_results(0, F, tracker=t)
+        otrk = orc.OracleTracker(N, sc.markers, sc.K, sc.params, sc.pose(0), sc.time(0), sc.pose(1), sc.time(1), resampler=0)
+        for f in range(F):
+            r = res[f]
+            assert r["status"] == 1 and r["flag_fail"] in (1.0, 1.5)
+            uv = S.project(sc.K, r["pose"], sc.markers)
+            uv_true = S.project(sc.K, sc.pose(2 + f), sc.markers)
+            assert np.abs(uv - uv_true).max() < 4.0      # a spurious blob inside tol_PF may be matched
+            # oracle tracker on the same sequence: same blobs + same correspondences -> same GN optimum
+            otrk.frame(sc.time(2 + f), sc.blobs(2 + f), sc.seed(2 + f))
+            uvo = S.project(sc.K, otrk.current_pose, sc.markers)
+            assert np.abs(uv - uvo).max() < 0.05
+        otrk.close()
+    h.close()
+
+
+def test_track_run_errors():
+    sc = S.Scene()
+    h = capi.Handle(64, max_blobs=16)
+    h.configure(sc.markers, sc.K, sc.params)
+    with pytest.raises(capi.PfmpeError):
+        h.track_run(0, 1)                      # nothing uploaded
+    _upload(h, [sc], 2, 4, 16)
+    with pytest.raises(capi.PfmpeError):
+        h.track_run(0, 1)                      # track_init missing
+    h.track_init(sc.pose(0), sc.time(0), sc.pose(1), sc.time(1))
+    with pytest.raises(capi.PfmpeError):
+        h.track_run(2, 5)                      # outside the uploaded sequence
+    h.track_run(0, 4)
+    assert all(r["status"] == 1 for r in h.track_results(0, 4))
+    h.close()
