@@ -187,6 +187,12 @@ int pfmpe_launch_count(const pfmpe_handle* h, uint64_t* n);
 /* launch geometry chosen for the hot-path kernel: grid.x, grid.y, block, cooperative? */
 int pfmpe_launch_info(const pfmpe_handle* h, int32_t info[4]);
 
+/* Profiling aid: enable/disable in-kernel %globaltimer stamps (CTA 0, thread 0) and read the stamps of the
+ * most recent frame: [0] frame start, [1] blobs staged, [2] first score pass done (this CTA), [3] after the
+ * grid reduction, [4] scan start, [5] scan done (this CTA), [6] after the count reduction, [7] result record
+ * written, [8] tail done (incl. device Gauss-Newton in track mode), [9] after the end-of-frame barrier. */
+int pfmpe_debug_timeline(pfmpe_handle* h, int enable, uint64_t stamps_ns[16]);
+
 #ifdef __cplusplus
 }
 #endif

@@ -23,7 +23,7 @@ EXPORTS = [
     "pfmpe_get_particles", "pfmpe_get_weights", "pfmpe_get_resample_indices", "pfmpe_get_resample_counts",
     "pfmpe_optimise_pose", "pfmpe_predict_pose", "pfmpe_exponential_map", "pfmpe_logarithm_map",
     "pfmpe_track_init", "pfmpe_track_upload", "pfmpe_track_attach", "pfmpe_track_run", "pfmpe_track_results",
-    "pfmpe_set_stream", "pfmpe_sync", "pfmpe_last_launch_ms", "pfmpe_launch_count", "pfmpe_launch_info",
+    "pfmpe_set_stream", "pfmpe_sync", "pfmpe_last_launch_ms", "pfmpe_launch_count", "pfmpe_launch_info", "pfmpe_debug_timeline",
 ]
 
 
@@ -115,6 +115,7 @@ def lib():
         L.pfmpe_last_launch_ms.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
         L.pfmpe_launch_count.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
         L.pfmpe_launch_info.argtypes = [C.c_void_p, C.POINTER(C.c_int32)]
+        L.pfmpe_debug_timeline.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint64)]
         _lib = L
     return _lib
 
@@ -326,6 +327,11 @@ class Handle:
         n = C.c_uint64()
         self._chk(lib().pfmpe_launch_count(self._h, C.byref(n)))
         return n.value
+
+    def debug_timeline(self, enable=True):
+        a = (C.c_uint64 * 16)()
+        self._chk(lib().pfmpe_debug_timeline(self._h, int(enable), a))
+        return np.array(list(a), dtype=np.uint64)
 
     def launch_info(self):
         a = (C.c_int32 * 4)()

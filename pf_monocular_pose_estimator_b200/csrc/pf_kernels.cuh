@@ -107,6 +107,15 @@ __device__ __forceinline__ pf_red pf_grid_reduce(pf_red v, pf_red* red_smem, con
   return r;
 }
 
+__device__ __forceinline__ void pf_stamp(const pf_kparams& p, int slot)
+{
+  if (p.timeline && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    p.timeline[slot] = t;
+  }
+}
+
 __device__ __forceinline__ void pf_sync_all(const pf_kparams& p)
 {
   if (p.coop) cg::this_grid().sync(); else __syncthreads();
@@ -432,6 +441,7 @@ __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, const pf_ctx& cx
     st->scan_epoch = cx.scan_epoch + 1u;
   }
   st->frames_done += 1;
+  pf_stamp(p, 7);
 
   if (p.mode != 1) return;
 
@@ -508,6 +518,7 @@ __global__ void __launch_bounds__(PF_BLOCK, 3) pf_frames_kernel(const __grid_con
     }
     if (threadIdx.x < 3 * L) cx.obj[threadIdx.x] = p.obj_f[(size_t)trk * PF_MAX_LED * 3 + threadIdx.x];
     const int failed = (p.mode == 1) ? st->failed : 0;
+    pf_stamp(p, 0);
     __syncthreads();
     if (failed) {   // track lost earlier in this sequence: the host must re-initialise (:707-719)
       if (blockIdx.x == 0 && threadIdx.x == 0) p.result[(size_t)trk * p.total_frames + frame].status = 0;
@@ -523,6 +534,7 @@ __global__ void __launch_bounds__(PF_BLOCK, 3) pf_frames_kernel(const __grid_con
       }
     }
     __syncthreads();
+    pf_stamp(p, 1);
 
     // ---- do { propagate, project, score } while (iter < 80 && max < L*min(5,numLED))  (:535-616)
     const float thr_exit = (float)(L * (D < 5 ? D : 5));
@@ -531,7 +543,9 @@ __global__ void __launch_bounds__(PF_BLOCK, 3) pf_frames_kernel(const __grid_con
     pf_red kept = pf_red_identity(), last = pf_red_identity();
     for (;;) {
       pf_red r = pf_stage_score<L>(p, cx, blobs, trk, it, it == 0);
+      if (it == 0) pf_stamp(p, 2);
       r = pf_grid_reduce(r, red_smem, p, round);
+      if (it == 0) pf_stamp(p, 3);
       const float m = pf_unord((unsigned)(r.maxkey >> 32));
       last = r;
       ++it;
@@ -552,13 +566,18 @@ __global__ void __launch_bounds__(PF_BLOCK, 3) pf_frames_kernel(const __grid_con
     const bool resampled = accept && cx.fc.isi > 0;
     pf_red cnt = pf_red_identity();
     if (resampled) {
+      pf_stamp(p, 4);
       cnt = pf_stage_scan(p, cx, trk, kept.sum, iters, sm_warp, &sm_bcast);
+      pf_stamp(p, 5);
       cnt = pf_grid_reduce(cnt, red_smem, p, round);
+      pf_stamp(p, 6);
     }
 
     if (blockIdx.x == 0 && threadIdx.x == 0)
       pf_frame_tail<L>(p, cx, blobs, trk, frame, iters, best_it, highest, kept, accept, resampled, cnt);
+    pf_stamp(p, 8);
     if (f + 1 < p.n_frames) { __threadfence(); pf_sync_all(p); }
+    pf_stamp(p, 9);
   }
 }
 

@@ -101,4 +101,5 @@ struct pf_kparams {
   pf_score_cfg score;
   double min_ang, max_ang, min_tr, max_tr;   // minAngularNoise.. (track mode recomputes the ranges per frame)
   const uint32_t* rng_tab;        // [4*256]
+  unsigned long long* timeline;   // optional [16] globaltimer stamps of the last frame (CTA 0, thread 0)
 };

@@ -62,6 +62,8 @@ struct pfmpe_handle {
   float* obj_f = nullptr;
   double* obj_d = nullptr;
   uint32_t* rng_tab = nullptr;
+  unsigned long long* timeline = nullptr;
+  bool timeline_on = false;
   // pinned host mirrors
   unsigned char* h_inbox = nullptr;
   pf_frame_result* h_result = nullptr;
@@ -113,7 +115,7 @@ void free_all(pfmpe_handle* h)
   cudaFree(h->pose0); cudaFree(h->pose1); cudaFree(h->gather_tmp); cudaFree(h->w); cudaFree(h->kend);
   cudaFree(h->idx); cudaFree(h->tile_kend); cudaFree(h->gather_idx); cudaFree(h->desc); cudaFree(h->accum);
   cudaFree(h->inbox); cudaFree(h->state); cudaFree(h->result); cudaFree(h->obj_f); cudaFree(h->obj_d);
-  cudaFree(h->rng_tab);
+  cudaFree(h->rng_tab); cudaFree(h->timeline);
   if (h->seq.owned) { cudaFree(h->seq.blobs); cudaFree(h->seq.counts); cudaFree(h->seq.times); cudaFree(h->seq.seeds); }
   cudaFree(h->seq.result);
   if (h->h_inbox) cudaFreeHost(h->h_inbox);
@@ -145,6 +147,7 @@ void fill_kparams(const pfmpe_handle* h, pf_kparams& p)
   p.min_ang = h->prm.min_angular_noise; p.max_ang = h->prm.max_angular_noise;
   p.min_tr = h->prm.min_transition_noise; p.max_tr = h->prm.max_transition_noise;
   p.rng_tab = h->rng_tab;
+  p.timeline = h->timeline_on ? h->timeline : nullptr;
 }
 
 typedef void (*frames_kernel_t)(const pf_kparams);
@@ -355,6 +358,8 @@ int pfmpe_create(const pfmpe_config* cfg, pfmpe_handle** out)
   PF_TRY(dev_alloc(&h->obj_f, T * PF_MAX_LED * 3));
   PF_TRY(dev_alloc(&h->obj_d, T * PF_MAX_LED * 3));
   PF_TRY(dev_alloc(&h->rng_tab, 1024));
+  PF_TRY(dev_alloc(&h->timeline, 16));
+  PF_TRY(cudaMemset(h->timeline, 0, 16 * sizeof(unsigned long long)));
   PF_TRY(cudaMallocHost((void**)&h->h_inbox, h->inbox_bytes));
   PF_TRY(cudaMallocHost((void**)&h->h_result, T * sizeof(pf_frame_result)));
   PF_TRY(cudaMallocHost((void**)&h->h_state, T * sizeof(pf_tracker_state)));
@@ -864,6 +869,16 @@ int pfmpe_launch_count(const pfmpe_handle* h, uint64_t* n)
 {
   if (!h || !n) return PFMPE_ERR_INVALID;
   *n = h->launches;
+  return PFMPE_OK;
+}
+
+int pfmpe_debug_timeline(pfmpe_handle* h, int enable, uint64_t stamps_ns[16])
+{
+  if (!h) return PFMPE_ERR_INVALID;
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  if (stamps_ns) PF_CUDA(h, cudaMemcpy(stamps_ns, h->timeline, 16 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+  h->timeline_on = enable != 0;
   return PFMPE_OK;
 }
 
