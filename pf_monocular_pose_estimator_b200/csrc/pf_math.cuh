@@ -21,6 +21,11 @@
 #else
 #define PF_HD inline
 #endif
+#if defined(__CUDACC__)
+#define PF_UNROLL _Pragma("unroll")
+#else
+#define PF_UNROLL
+#endif
 
 #define PF_MAX_LED 8
 #define PF_RNG_M 2147483647u     /* 2^31 - 1 */
@@ -302,6 +307,30 @@ PF_HD int pf_count_leq(long long m, const pf_resample_cfg& rc, const uint32_t* _
 // (sum, running-max-of-prefix) scan operator:  (s1,m1) (+) (s2,m2) = (s1+s2, max(m1, s1+m2)).
 struct pf_sm { long long s, m; };
 #define PF_SM_NEG (-(1ll << 62))
+#define PF_SM_POS (1ll << 62)
+
+// Sign-agnostic aggregate of a run of particles, built while scoring (before the sign of the
+// weight sum is known): sum, running max and running min of the prefix.  After the
+// grid-wide sum S is known, sg = sign(S) selects  M = sg > 0 ? mx : -mn.
+struct pf_sm3 { long long s, mx, mn; };
+PF_HD pf_sm3 pf_sm3_identity() { pf_sm3 r; r.s = 0; r.mx = PF_SM_NEG; r.mn = PF_SM_POS; return r; }
+PF_HD pf_sm3 pf_sm3_combine(const pf_sm3& a, const pf_sm3& b)
+{
+  pf_sm3 r;
+  r.s = a.s + b.s;
+  const long long tx = b.mx <= PF_SM_NEG ? PF_SM_NEG : a.s + b.mx;
+  const long long tn = b.mn >= PF_SM_POS ? PF_SM_POS : a.s + b.mn;
+  r.mx = a.mx > tx ? a.mx : tx;
+  r.mn = a.mn < tn ? a.mn : tn;
+  return r;
+}
+// (sum, running max) of sg * prefix from the sign-agnostic aggregate
+PF_HD void pf_sm3_select(const pf_sm3& a, long long sg, long long& s, long long& m)
+{
+  s = sg * a.s;
+  if (sg > 0) m = a.mx <= PF_SM_NEG ? PF_SM_NEG : a.mx;
+  else m = a.mn >= PF_SM_POS ? PF_SM_NEG : -a.mn;
+}
 PF_HD pf_sm pf_sm_identity() { pf_sm r; r.s = 0; r.m = PF_SM_NEG; return r; }
 PF_HD pf_sm pf_sm_combine(const pf_sm& a, const pf_sm& b)
 {

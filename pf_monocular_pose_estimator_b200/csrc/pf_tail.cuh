@@ -15,6 +15,7 @@ struct pf_aff { double a[12]; };
 PF_HD pf_aff pf_aff_identity()
 {
   pf_aff T;
+  PF_UNROLL
   for (int i = 0; i < 12; ++i) T.a[i] = 0.0;
   T.a[0] = T.a[5] = T.a[10] = 1.0;
   return T;
@@ -23,7 +24,9 @@ PF_HD pf_aff pf_aff_identity()
 PF_HD pf_aff pf_aff_mul(const pf_aff& A, const pf_aff& B)
 {
   pf_aff C;
+  PF_UNROLL
   for (int i = 0; i < 3; ++i)
+    PF_UNROLL
     for (int j = 0; j < 4; ++j) {
       double s = A.a[4 * i] * B.a[j] + A.a[4 * i + 1] * B.a[4 + j] + A.a[4 * i + 2] * B.a[8 + j];
       if (j == 3) s += A.a[4 * i + 3];
@@ -43,6 +46,7 @@ PF_HD pf_aff pf_aff_inverse(const pf_aff& T)
   R.a[0] = c00 * id; R.a[1] = (a[2] * a[9] - a[1] * a[10]) * id; R.a[2] = (a[1] * a[6] - a[2] * a[5]) * id;
   R.a[4] = c01 * id; R.a[5] = (a[0] * a[10] - a[2] * a[8]) * id; R.a[6] = (a[2] * a[4] - a[0] * a[6]) * id;
   R.a[8] = c02 * id; R.a[9] = (a[1] * a[8] - a[0] * a[9]) * id;  R.a[10] = (a[0] * a[5] - a[1] * a[4]) * id;
+  PF_UNROLL
   for (int i = 0; i < 3; ++i)
     R.a[4 * i + 3] = -(R.a[4 * i] * a[3] + R.a[4 * i + 1] * a[7] + R.a[4 * i + 2] * a[11]);
   return R;
@@ -52,25 +56,31 @@ PF_HD pf_aff pf_aff_inverse(const pf_aff& T)
 PF_HD pf_aff pf_aff_from_cm16(const double* m)
 {
   pf_aff T;
+  PF_UNROLL
   for (int i = 0; i < 3; ++i)
+    PF_UNROLL
     for (int j = 0; j < 4; ++j) T.a[4 * i + j] = m[i + 4 * j];
   return T;
 }
 PF_HD void pf_aff_to_cm16(const pf_aff& T, double* m)
 {
+  PF_UNROLL
   for (int i = 0; i < 3; ++i)
+    PF_UNROLL
     for (int j = 0; j < 4; ++j) m[i + 4 * j] = T.a[4 * i + j];
   m[3] = 0.0; m[7] = 0.0; m[11] = 0.0; m[15] = 1.0;
 }
 PF_HD pf_pose pf_aff_to_f32(const pf_aff& T)
 {
   pf_pose p;
+  PF_UNROLL
   for (int i = 0; i < 12; ++i) p.p[i] = (float)T.a[i];
   return p;
 }
 PF_HD pf_aff pf_aff_from_f32(const pf_pose& p)
 {
   pf_aff T;
+  PF_UNROLL
   for (int i = 0; i < 12; ++i) T.a[i] = (double)p.p[i];
   return T;
 }
@@ -84,18 +94,23 @@ PF_HD pf_aff pf_exp_map(const double* tw)
   // Omega and Omega^2 (row-major 3x3)
   const double O[9] = {0, -wz, wy, wz, 0, -wx, -wy, wx, 0};
   double O2[9];
+  PF_UNROLL
   for (int i = 0; i < 3; ++i)
+    PF_UNROLL
     for (int j = 0; j < 3; ++j) O2[3 * i + j] = O[3 * i] * O[j] + O[3 * i + 1] * O[3 + j] + O[3 * i + 2] * O[6 + j];
   double R[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, V[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
   if (theta != 0) {
     const double st = sin(theta), ct = cos(theta);
+    PF_UNROLL
     for (int i = 0; i < 9; ++i) {
       R[i] += O[i] / theta * st + O2[i] / th2 * (1 - ct);
       V[i] += (1 - ct) / th2 * O[i] + (theta - st) / (th2 * theta) * O2[i];
     }
   }
   pf_aff T;
+  PF_UNROLL
   for (int i = 0; i < 3; ++i) {
+    PF_UNROLL
     for (int j = 0; j < 3; ++j) T.a[4 * i + j] = R[3 * i + j];
     T.a[4 * i + 3] = V[3 * i] * tw[0] + V[3 * i + 1] * tw[1] + V[3 * i + 2] * tw[2];
   }
@@ -107,7 +122,9 @@ PF_HD void pf_log_map(const pf_aff& T, double* xi)
 {
   const double* a = T.a;
   double dev = 0, nrm = 0;
+  PF_UNROLL
   for (int i = 0; i < 3; ++i)
+    PF_UNROLL
     for (int j = 0; j < 3; ++j) {
       double e = a[4 * i + j] - (i == j ? 1.0 : 0.0);
       dev += e * e;
@@ -121,7 +138,9 @@ PF_HD void pf_log_map(const pf_aff& T, double* xi)
     const double phi = acos(c);
     if (phi != 0) {
       const double f = 2 * sin(phi);
+      PF_UNROLL
       for (int i = 0; i < 3; ++i)
+        PF_UNROLL
         for (int j = 0; j < 3; ++j) wh[3 * i + j] = (a[4 * i + j] - a[4 * j + i]) / f * phi;
     }
   }
@@ -134,13 +153,16 @@ PF_HD void pf_log_map(const pf_aff& T, double* xi)
     Ai[0] = Ai[4] = Ai[8] = 1.0;
     if (!(wn == 0 || sin(wn) == 0)) {
       const double f = (2 * sin(wn) - wn * (1 + cos(wn))) / (2 * wn * wn * sin(wn));
+      PF_UNROLL
       for (int i = 0; i < 3; ++i)
+        PF_UNROLL
         for (int j = 0; j < 3; ++j) {
           double w2 = wh[3 * i] * wh[j] + wh[3 * i + 1] * wh[3 + j] + wh[3 * i + 2] * wh[6 + j];
           Ai[3 * i + j] += -wh[3 * i + j] / 2 + f * w2;
         }
     }
   }
+  PF_UNROLL
   for (int i = 0; i < 3; ++i) xi[i] = Ai[3 * i] * t[0] + Ai[3 * i + 1] * t[1] + Ai[3 * i + 2] * t[2];
   xi[3] = w[0]; xi[4] = w[1]; xi[5] = w[2];
 }
@@ -151,6 +173,7 @@ PF_HD void pf_predict_pose(const pf_aff& prev, const pf_aff& cur, double t_prev,
 {
   double d[6];
   pf_log_map(pf_aff_mul(pf_aff_inverse(prev), cur), d);
+  PF_UNROLL
   for (int i = 0; i < 6; ++i) d[i] = d[i] / (t_cur - t_prev) * (t_pred - t_cur);
   P = pf_exp_map(d);
   pred = pf_aff_mul(cur, P);
@@ -162,39 +185,54 @@ PF_HD void pf_ldlt6_solve(const double* A, const double* b, double* x)
 {
   double M[36];
   int p[6];
+  PF_UNROLL
   for (int i = 0; i < 36; ++i) M[i] = A[i];
+  PF_UNROLL
   for (int i = 0; i < 6; ++i) p[i] = i;
+  PF_UNROLL
   for (int k = 0; k < 6; ++k) {
     int piv = k;
     double big = fabs(M[7 * k]);
+    PF_UNROLL
     for (int i = k + 1; i < 6; ++i)
       if (fabs(M[7 * i]) > big) { big = fabs(M[7 * i]); piv = i; }
     if (piv != k) {
+      PF_UNROLL
       for (int j = 0; j < 6; ++j) { double t = M[6 * k + j]; M[6 * k + j] = M[6 * piv + j]; M[6 * piv + j] = t; }
+      PF_UNROLL
       for (int j = 0; j < 6; ++j) { double t = M[6 * j + k]; M[6 * j + k] = M[6 * j + piv]; M[6 * j + piv] = t; }
       int t = p[k]; p[k] = p[piv]; p[piv] = t;
     }
     const double d = M[7 * k];
     if (d == 0.0) continue;
+    PF_UNROLL
     for (int i = k + 1; i < 6; ++i) M[6 * i + k] /= d;       // L(i,k)
+    PF_UNROLL
     for (int i = k + 1; i < 6; ++i)
+      PF_UNROLL
       for (int j = k + 1; j <= i; ++j) {
         M[6 * i + j] -= M[6 * i + k] * d * M[6 * j + k];
         M[6 * j + i] = M[6 * i + j];
       }
   }
   double y[6];
+  PF_UNROLL
   for (int i = 0; i < 6; ++i) {
     double s = b[p[i]];
+    PF_UNROLL
     for (int k = 0; k < i; ++k) s -= M[6 * i + k] * y[k];
     y[i] = s;
   }
+  PF_UNROLL
   for (int i = 0; i < 6; ++i) y[i] = M[7 * i] != 0.0 ? y[i] / M[7 * i] : 0.0;
+  PF_UNROLL
   for (int i = 5; i >= 0; --i) {
     double s = y[i];
+    PF_UNROLL
     for (int k = i + 1; k < 6; ++k) s -= M[6 * k + i] * y[k];
     y[i] = s;
   }
+  PF_UNROLL
   for (int i = 0; i < 6; ++i) x[p[i]] = y[i];
 }
 
@@ -202,24 +240,33 @@ PF_HD void pf_ldlt6_solve(const double* A, const double* b, double* x)
 PF_HD void pf_inv6(const double* A, double* Ai)
 {
   double M[36];
+  PF_UNROLL
   for (int i = 0; i < 36; ++i) { M[i] = A[i]; Ai[i] = 0.0; }
+  PF_UNROLL
   for (int i = 0; i < 6; ++i) Ai[7 * i] = 1.0;
+  PF_UNROLL
   for (int c = 0; c < 6; ++c) {
     int piv = c;
     double big = fabs(M[6 * c + c]);
+    PF_UNROLL
     for (int r = c + 1; r < 6; ++r)
       if (fabs(M[6 * r + c]) > big) { big = fabs(M[6 * r + c]); piv = r; }
-    if (piv != c)
+    if (piv != c) {
+      PF_UNROLL
       for (int j = 0; j < 6; ++j) {
         double t = M[6 * c + j]; M[6 * c + j] = M[6 * piv + j]; M[6 * piv + j] = t;
         t = Ai[6 * c + j]; Ai[6 * c + j] = Ai[6 * piv + j]; Ai[6 * piv + j] = t;
       }
+    }
     const double s = 1.0 / M[6 * c + c];
+    PF_UNROLL
     for (int j = 0; j < 6; ++j) { M[6 * c + j] *= s; Ai[6 * c + j] *= s; }
+    PF_UNROLL
     for (int r = 0; r < 6; ++r) {
       if (r == c) continue;
       const double f = M[6 * r + c];
       if (f == 0.0) continue;
+      PF_UNROLL
       for (int j = 0; j < 6; ++j) { M[6 * r + j] -= f * M[6 * c + j]; Ai[6 * r + j] -= f * Ai[6 * c + j]; }
     }
   }
@@ -237,10 +284,13 @@ PF_HD int pf_optimise_pose(const double* K9, const double* obj, const double* im
   const double fx = K9[0], fy = K9[4];
   double e_first = 0, e_last = 0;
   double A[36], b[6], dT[6];
+  PF_UNROLL
   for (int i = 0; i < 36; ++i) A[i] = 0.0;
   int reported = -1;
   for (int it = 0; it < max_itr; ++it) {
+    PF_UNROLL
     for (int i = 0; i < 36; ++i) A[i] = 0.0;
+    PF_UNROLL
     for (int i = 0; i < 6; ++i) b[i] = 0.0;
     for (int q = 0; q < npairs; ++q) {
       const unsigned led = pairs[2 * q], det = pairs[2 * q + 1];
@@ -261,7 +311,9 @@ PF_HD int pf_optimise_pose(const double* K9, const double* obj, const double* im
       const double z2 = z * z;
       const double J0[6] = {1 / z * fx, 0, -x / z2 * fx, -x * y / z2 * fx, (1 + (x * x / z2)) * fx, -y / z * fx};
       const double J1[6] = {0, 1 / z * fy, -y / z2 * fy, -(1 + y * y / z2) * fy, x * y / z2 * fy, x / z * fy};
+      PF_UNROLL
       for (int r = 0; r < 6; ++r) {
+        PF_UNROLL
         for (int c = 0; c < 6; ++c) A[6 * r + c] += J0[r] * J0[c] + J1[r] * J1[c];
         b[r] += J0[r] * ex + J1[r] * ey;
       }
@@ -269,6 +321,7 @@ PF_HD int pf_optimise_pose(const double* K9, const double* obj, const double* im
     pf_ldlt6_solve(A, b, dT);
     pose = pf_aff_mul(pf_exp_map(dT), pose);   // :1876
     double nm = -1;
+    PF_UNROLL
     for (int i = 0; i < 6; ++i) { double v = fabs(dT[i]); if (v > nm) nm = v; }
     if (nm <= conv) { reported = it; break; }
     if (it + 1 == max_itr && e_first < e_last) pose = pose0;   // :1886-1892
@@ -296,6 +349,7 @@ PF_HD void pf_make_frame_const(pf_frame_const& fc, const pf_aff& cur, const pf_a
                                const pf_aff& C, uint32_t isi, double dt, uint32_t seed, int D,
                                double min_ang, double max_ang, double min_tr, double max_tr)
 {
+  PF_UNROLL
   for (int i = 0; i < 12; ++i) {
     fc.Tcur[i] = (float)cur.a[i];
     fc.Tpred[i] = (float)pred.a[i];

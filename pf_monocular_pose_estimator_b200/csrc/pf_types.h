@@ -5,8 +5,9 @@
 #include "pf_tail.cuh"
 
 #define PF_BLOCK 256          /* threads per CTA                                     */
-#define PF_SCAN_ITEMS 4       /* consecutive particles per thread in the scan stage  */
-#define PF_SCAN_TILE (PF_BLOCK * PF_SCAN_ITEMS)
+#define PF_WARPS (PF_BLOCK / 32)
+#define PF_SEARCH_BLOCK 256   /* particles per entry of the coarse offspring index (tile_kend) */
+#define PF_MAX_GRID 2048      /* capacity of the per-CTA aggregate array (grid mode)  */
 #define PF_MAX_ITER 80        /* do/while bound, pose_estimator.cpp:616              */
 
 // Per-tracker persistent state (device memory).
@@ -20,7 +21,7 @@ struct pf_tracker_state {
   // particle-set bookkeeping
   int32_t src_buf;                           // pose buffer that holds the source set of the next frame
   int32_t src_mode;                          // 0: E[n] = pose[src_buf][n];  1: E[n] = pose[src_buf][idx(n)] via kend (resampled)
-  uint32_t scan_epoch;                       // look-back flag stamp, monotonically increasing
+  uint32_t reserved0;
   int32_t frames_done;
   int32_t t_buf;                             // pose buffer that holds the last propagated set (PoseParticle)
   int32_t pad;
@@ -57,12 +58,10 @@ struct pf_accum {
   unsigned long long cntkey;      // (count << 32) | ~idx           -> atomicMax: max count, first index
 };
 
-// Decoupled look-back descriptor (grid mode scan), one per scan tile.
-struct pf_tile_desc {
-  long long agg_s, agg_m;         // tile aggregate (sum, running max of prefix)
-  long long inc_s, inc_m;         // inclusive prefix up to and including this tile
-  uint32_t flag;                  // epoch*4 + {1: aggregate ready, 2: inclusive ready}
-  uint32_t pad[7];
+// Per-CTA aggregate of the sign-agnostic prefix statistics (grid mode), written before the
+// grid-wide barrier that follows every score pass; 32-byte records.
+struct pf_cta_agg {
+  long long s, mx, mn, pad;
 };
 
 struct pf_kparams {
@@ -76,14 +75,15 @@ struct pf_kparams {
   int total_frames;               // frames uploaded (track mode)
   int coop;                       // 1: grid-wide cooperation (gridDim.x > 1)
   int want_mean;                  // compute weighted mean / covariance
+  int cta_chunk;                  // particles owned by one CTA (multiple of PF_BLOCK); warp w owns the w-th eighth
   // particle state
   float4* pose0; float4* pose1;   // [tracker][3 planes][N]
   float*  w;                      // [tracker][N] raw scores of the kept iteration
   int*    kend;                   // [tracker][N] cumulative offspring count K(M_i)
   int*    idx;                    // [tracker][N] source index of slot n for the current frame
-  int*    tile_kend;              // [tracker][ntiles_scan]
-  pf_tile_desc* desc;             // [ntiles_scan] (grid mode)
-  pf_accum* accum;                // [3] rotating slots (grid mode)
+  int*    tile_kend;              // [tracker][ceil(N / PF_SEARCH_BLOCK)] kend of the last particle of each block
+  pf_cta_agg* cta_agg;            // [PF_MAX_GRID] (grid mode)
+  pf_accum* accum;                // [3] rotating slots (grid mode) + [3].maxkey = next round mod 3
   // per-tracker records
   pf_frame_const* fconst;         // [tracker]
   pf_tracker_state* state;        // [tracker]

@@ -46,12 +46,12 @@ struct pfmpe_handle {
   int force_mode = 0;            // 0 auto, 1 batch, 2 grid (cfg.reserved[0])
   int grid_cap = 0;              // cfg.reserved[1]
   int info[4] = {0, 0, PF_BLOCK, 0};
-  int ntiles_scan = 0;
+  int nblk = 0;                  // entries of the coarse offspring index per tracker
   // device
   float4 *pose0 = nullptr, *pose1 = nullptr, *gather_tmp = nullptr;
   float* w = nullptr;
   int *kend = nullptr, *idx = nullptr, *tile_kend = nullptr, *gather_idx = nullptr;
-  pf_tile_desc* desc = nullptr;
+  pf_cta_agg* cta_agg = nullptr;
   pf_accum* accum = nullptr;
   unsigned char* inbox = nullptr;       // [fconst x n_trackers | blobs x n_trackers x max_blobs x 2]
   pf_frame_const* fconst = nullptr;     // = inbox
@@ -113,7 +113,7 @@ cudaError_t dev_alloc(T** p, size_t n)
 void free_all(pfmpe_handle* h)
 {
   cudaFree(h->pose0); cudaFree(h->pose1); cudaFree(h->gather_tmp); cudaFree(h->w); cudaFree(h->kend);
-  cudaFree(h->idx); cudaFree(h->tile_kend); cudaFree(h->gather_idx); cudaFree(h->desc); cudaFree(h->accum);
+  cudaFree(h->idx); cudaFree(h->tile_kend); cudaFree(h->gather_idx); cudaFree(h->cta_agg); cudaFree(h->accum);
   cudaFree(h->inbox); cudaFree(h->state); cudaFree(h->result); cudaFree(h->obj_f); cudaFree(h->obj_d);
   cudaFree(h->rng_tab); cudaFree(h->timeline);
   if (h->seq.owned) { cudaFree(h->seq.blobs); cudaFree(h->seq.counts); cudaFree(h->seq.times); cudaFree(h->seq.seeds); }
@@ -134,7 +134,7 @@ void fill_kparams(const pfmpe_handle* h, pf_kparams& p)
   p.D_max = h->cfg.max_blobs;
   p.want_mean = (h->cfg.flags & PFMPE_FLAG_MEAN_COV) ? 1 : 0;
   p.pose0 = h->pose0; p.pose1 = h->pose1; p.w = h->w; p.kend = h->kend; p.idx = h->idx;
-  p.tile_kend = h->tile_kend; p.desc = h->desc; p.accum = h->accum;
+  p.tile_kend = h->tile_kend; p.cta_agg = h->cta_agg; p.accum = h->accum;
   p.fconst = h->fconst; p.state = h->state;
   p.obj_f = h->obj_f; p.obj_d = h->obj_d;
   for (int i = 0; i < 9; ++i) { p.K9d[i] = h->K[i]; p.K9f[i] = (float)h->K[i]; }
@@ -194,6 +194,7 @@ int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_f
   if (!grid_mode) {
     p.coop = 0;
     p.tracker_base = t0;
+    p.cta_chunk = (N + PF_BLOCK - 1) / PF_BLOCK * PF_BLOCK;
     dim3 grid(1, (unsigned)nt, 1);
     h->info[0] = 1; h->info[1] = nt; h->info[3] = 0;
     k<<<grid, PF_BLOCK, smem, h->stream>>>(p);
@@ -204,15 +205,19 @@ int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_f
     PF_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, PF_BLOCK, smem));
     int cap = per_sm * h->num_sms;
     if (cap < 1) return fail(h, PFMPE_ERR_CUDA, "kernel cannot be made resident");
+    if (cap > PF_MAX_GRID) cap = PF_MAX_GRID;
     if (h->grid_cap > 0 && h->grid_cap < cap) cap = h->grid_cap;
-    int tiles = (N + PF_BLOCK - 1) / PF_BLOCK;
-    int G = tiles < cap ? tiles : cap;
-    if (G < 2) G = 2 <= cap ? 2 : 1;
+    // contiguous chunk per CTA: a multiple of PF_BLOCK when the filter is large enough to give every
+    // warp full 32-particle steps, else (forced grid mode on a small filter) a multiple of PF_WARPS
+    int chunk = (N + cap - 1) / cap;
+    if (chunk >= PF_BLOCK || h->force_mode != 2) chunk = (chunk + PF_BLOCK - 1) / PF_BLOCK * PF_BLOCK;
+    else chunk = (chunk + PF_WARPS - 1) / PF_WARPS * PF_WARPS;
+    const int G = (N + chunk - 1) / chunk;
+    p.cta_chunk = chunk;
     p.coop = G > 1 ? 1 : 0;
     h->info[0] = G; h->info[1] = 1; h->info[3] = p.coop;
     for (int t = t0; t < t0 + nt; ++t) {
       p.tracker_base = t;
-      PF_CUDA(h, cudaMemsetAsync(h->accum, 0, 3 * sizeof(pf_accum), h->stream));
       void* args[] = {(void*)&p};
       dim3 grid((unsigned)G, 1, 1);
       if (p.coop) PF_CUDA(h, cudaLaunchCooperativeKernel((const void*)k, grid, dim3(PF_BLOCK), args, smem, h->stream));
@@ -317,7 +322,7 @@ int pfmpe_create(const pfmpe_config* cfg, pfmpe_handle** out)
   h->force_mode = cfg->reserved[0];
   h->grid_cap = cfg->reserved[1];
   const size_t N = (size_t)cfg->n_particles, T = (size_t)cfg->n_trackers;
-  h->ntiles_scan = (int)((N + PF_SCAN_TILE - 1) / PF_SCAN_TILE);
+  h->nblk = (int)((N + PF_SEARCH_BLOCK - 1) / PF_SEARCH_BLOCK);
   h->particles_set.assign(T, 0);
   h->markers.assign(T * PF_MAX_LED * 3, 0.0);
   h->last_sum_fx.assign(T, 0);
@@ -345,9 +350,9 @@ int pfmpe_create(const pfmpe_config* cfg, pfmpe_handle** out)
   PF_TRY(dev_alloc(&h->kend, T * N));
   PF_TRY(dev_alloc(&h->idx, T * N));
   PF_TRY(dev_alloc(&h->gather_idx, N));
-  PF_TRY(dev_alloc(&h->tile_kend, T * (size_t)h->ntiles_scan));
-  PF_TRY(dev_alloc(&h->desc, (size_t)h->ntiles_scan));
-  PF_TRY(dev_alloc(&h->accum, 3));
+  PF_TRY(dev_alloc(&h->tile_kend, T * (size_t)h->nblk));
+  PF_TRY(dev_alloc(&h->cta_agg, (size_t)PF_MAX_GRID));
+  PF_TRY(dev_alloc(&h->accum, 4));
   h->blobs_off = (T * sizeof(pf_frame_const) + 255) / 256 * 256;
   h->inbox_bytes = h->blobs_off + T * (size_t)cfg->max_blobs * 2 * sizeof(double);
   PF_TRY(cudaMalloc((void**)&h->inbox, h->inbox_bytes));
@@ -364,15 +369,14 @@ int pfmpe_create(const pfmpe_config* cfg, pfmpe_handle** out)
   PF_TRY(cudaMallocHost((void**)&h->h_result, T * sizeof(pf_frame_result)));
   PF_TRY(cudaMallocHost((void**)&h->h_state, T * sizeof(pf_tracker_state)));
   std::memset(h->h_inbox, 0, h->inbox_bytes);
-  PF_TRY(cudaMemset(h->desc, 0, (size_t)h->ntiles_scan * sizeof(pf_tile_desc)));
-  PF_TRY(cudaMemset(h->accum, 0, 3 * sizeof(pf_accum)));
+  PF_TRY(cudaMemset(h->cta_agg, 0, (size_t)PF_MAX_GRID * sizeof(pf_cta_agg)));
+  PF_TRY(cudaMemset(h->accum, 0, 4 * sizeof(pf_accum)));
   PF_TRY(cudaMemset(h->w, 0, T * N * sizeof(float)));
   PF_TRY(cudaMemset(h->kend, 0, T * N * sizeof(int)));
   PF_TRY(cudaMemset(h->idx, 0, T * N * sizeof(int)));
-  PF_TRY(cudaMemset(h->tile_kend, 0, T * (size_t)h->ntiles_scan * sizeof(int)));
+  PF_TRY(cudaMemset(h->tile_kend, 0, T * (size_t)h->nblk * sizeof(int)));
   PF_TRY(cudaMemset(h->result, 0, T * sizeof(pf_frame_result)));
   std::memset(h->h_state, 0, T * sizeof(pf_tracker_state));
-  for (size_t t = 0; t < T; ++t) h->h_state[t].scan_epoch = 1u;
   PF_TRY(cudaMemcpy(h->state, h->h_state, T * sizeof(pf_tracker_state), cudaMemcpyHostToDevice));
   {
     std::vector<uint32_t> tab(1024);
@@ -555,7 +559,7 @@ static int run_gather(pfmpe_handle* h, int tracker)
   const float4* T = (s.src_buf == 0 ? h->pose0 : h->pose1) + (size_t)tracker * 3 * N;
   const int blocks = (int)((N + PF_BLOCK - 1) / PF_BLOCK);
   pf_gather_kernel<<<blocks, PF_BLOCK, 0, h->stream>>>(T, h->kend + (size_t)tracker * N,
-                                                      h->tile_kend + (size_t)tracker * h->ntiles_scan, h->ntiles_scan,
+                                                      h->tile_kend + (size_t)tracker * h->nblk, h->nblk,
                                                       (int)N, s.src_mode, h->gather_tmp, h->gather_idx);
   PF_CUDA(h, cudaGetLastError());
   h->launches += 1;
