@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpfmpe.so")
+LIB_PATH = os.environ.get("PFMPE_LIB", os.path.join(_HERE, "libpfmpe.so"))   # override: A/B experiments only
 MAX_LED = 8
 
 OK, ERR_INVALID, ERR_CUDA, ERR_NO_DEVICE, ERR_STATE, ERR_UNSUPPORTED, ERR_COMM = 0, -1, -2, -3, -4, -5, -6

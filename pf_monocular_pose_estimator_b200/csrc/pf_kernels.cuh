@@ -59,7 +59,7 @@ __device__ __forceinline__ pf_red pf_red_identity()
   pf_red r; r.maxkey = 0ull; r.minkey_inv = 0ull; r.cntkey = 0ull; r.sum = 0ll; return r;
 }
 
-// block-wide reduction of pf_red; result valid in every thread.  red_smem: PF_WARPS entries.
+// block-wide reduction of pf_red; result valid in every thread.  red_smem: PF_MAX_WARPS entries.
 __device__ __forceinline__ pf_red pf_block_reduce(pf_red v, pf_red* red_smem)
 {
 #pragma unroll
@@ -78,8 +78,8 @@ __device__ __forceinline__ pf_red pf_block_reduce(pf_red v, pf_red* red_smem)
   if (lane == 0) red_smem[warp] = v;
   __syncthreads();
   pf_red r = red_smem[0];
-#pragma unroll
-  for (int i = 1; i < PF_WARPS; ++i) {
+  const int nwarps = blockDim.x >> 5;
+  for (int i = 1; i < nwarps; ++i) {
     pf_red t = red_smem[i];
     r.maxkey = t.maxkey > r.maxkey ? t.maxkey : r.maxkey;
     r.minkey_inv = t.minkey_inv > r.minkey_inv ? t.minkey_inv : r.minkey_inv;
@@ -95,40 +95,63 @@ __device__ __forceinline__ void pf_publish_cta_agg(const pf_kparams& p, const pf
 {
   if (p.coop && threadIdx.x == 0) {
     pf_sm3 a = warp_agg[0];
-#pragma unroll
-    for (int i = 1; i < PF_WARPS; ++i) a = pf_sm3_combine(a, warp_agg[i]);
+    const int nwarps = blockDim.x >> 5;
+    for (int i = 1; i < nwarps; ++i) a = pf_sm3_combine(a, warp_agg[i]);
     pf_cta_agg* g = p.cta_agg + blockIdx.x;
     g->s = a.s; g->mx = a.mx; g->mn = a.mn;
   }
 }
 
+// Grid-wide barrier (grid mode; all CTAs are co-resident: cooperative launch).  One monotonically
+// increasing 64-bit arrival counter that is never reset: barrier number b (counted across
+// launches, kept in pf_bar) completes when the counter reaches (b + 1) * gridDim.x.  Arrival is a
+// release reduction (no return value to wait for), the wait is an acquire poll by thread 0.
+struct pf_bar { unsigned long long done; unsigned round; };
+
+__device__ __forceinline__ void pf_grid_barrier(const pf_kparams& p, pf_bar& bar)
+{
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned long long* c = &p.accum[3].cntkey;
+    const unsigned long long target = (bar.done + 1ull) * gridDim.x;
+    asm volatile("red.release.gpu.global.add.u64 [%0], %1;" ::"l"(c), "l"(1ull) : "memory");
+    unsigned long long v;
+    do {
+      asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(c) : "memory");
+    } while (v < target);
+    __threadfence();
+  }
+  __syncthreads();
+  bar.done += 1ull;
+}
+
 // Combine the CTA results of one reduction round across the grid (grid mode) and return the
 // global result to every thread of every CTA.  Slot rotation: round e uses slot e%3; slot
 // (e+2)%3 (last read before the barrier of round e) is re-zeroed by CTA 0 after the barrier.
-__device__ __forceinline__ pf_red pf_grid_reduce(pf_red v, pf_red* red_smem, const pf_kparams& p, unsigned& round,
+__device__ __forceinline__ pf_red pf_grid_reduce(pf_red v, pf_red* red_smem, const pf_kparams& p, pf_bar& bar,
                                                  const pf_sm3* warp_agg)
 {
   pf_red r = pf_block_reduce(v, red_smem);
   if (p.coop) {
     if (warp_agg) pf_publish_cta_agg(p, warp_agg);
-    pf_accum* slot = p.accum + (round % 3u);
+    pf_accum* slot = p.accum + (bar.round % 3u);
     if (threadIdx.x == 0) {
       atomicMax(&slot->maxkey, r.maxkey);
       atomicMax(&slot->minkey_inv, r.minkey_inv);
       atomicMax(&slot->cntkey, r.cntkey);
       atomicAdd((unsigned long long*)&slot->sum, (unsigned long long)r.sum);
     }
-    cg::this_grid().sync();
+    pf_grid_barrier(p, bar);
     r.maxkey = *(volatile unsigned long long*)&slot->maxkey;
     r.minkey_inv = *(volatile unsigned long long*)&slot->minkey_inv;
     r.cntkey = *(volatile unsigned long long*)&slot->cntkey;
     r.sum = *(volatile long long*)&slot->sum;
     if (blockIdx.x == 0 && threadIdx.x == 0) {
-      pf_accum* z = p.accum + ((round + 2u) % 3u);
+      pf_accum* z = p.accum + ((bar.round + 2u) % 3u);
       z->maxkey = 0ull; z->minkey_inv = 0ull; z->cntkey = 0ull; z->sum = 0ll;
     }
   }
-  ++round;
+  bar.round += 1u;
   return r;
 }
 
@@ -141,9 +164,9 @@ __device__ __forceinline__ void pf_stamp(const pf_kparams& p, int slot)
   }
 }
 
-__device__ __forceinline__ void pf_sync_all(const pf_kparams& p)
+__device__ __forceinline__ void pf_sync_all(const pf_kparams& p, pf_bar& bar)
 {
-  if (p.coop) cg::this_grid().sync(); else __syncthreads();
+  if (p.coop) pf_grid_barrier(p, bar); else __syncthreads();
 }
 
 __device__ __forceinline__ pf_pose pf_load_pose(const float4* base, int N, int n)
@@ -162,30 +185,6 @@ __device__ __forceinline__ void pf_store_pose(float4* base, int N, int n, const 
   base[2 * (size_t)N + n] = make_float4(T.p[8], T.p[9], T.p[10], T.p[11]);
 }
 
-// Source index of output slot n after a resampled frame: first i with kend[i] > min(n, Ktot-1)
-// (two-level search: coarse block ends, then inside the PF_SEARCH_BLOCK-source block).
-// Reproduces :681 incl. the "not found keeps the previous index" tail (Q7).
-// kend / tile_kend are rewritten by the resampling stage of the same launch in multi-frame runs,
-// so they are read with plain (coherent) loads, never through the non-coherent path.
-__device__ __forceinline__ int pf_source_index(const int* kend, const int* tile_kend, int nblk, int N, int n)
-{
-  const int ktot = tile_kend[nblk - 1];
-  int k = n < ktot ? n : ktot - 1;
-  if (k < 0) return n;                 // nothing was ever found: the slot keeps its own particle
-  int lo = 0, hi = nblk - 1;           // smallest block with tile_kend > k
-  while (lo < hi) {
-    int mid = (lo + hi) >> 1;
-    if (tile_kend[mid] > k) hi = mid; else lo = mid + 1;
-  }
-  int a = lo * PF_SEARCH_BLOCK, b = a + PF_SEARCH_BLOCK - 1;
-  if (b > N - 1) b = N - 1;
-  while (a < b) {
-    int mid = (a + b) >> 1;
-    if (kend[mid] > k) b = mid; else a = mid + 1;
-  }
-  return a;
-}
-
 // ---------------------------------------------------------------------------------------
 // warp-level primitives on fixed-point weights
 // ---------------------------------------------------------------------------------------
@@ -200,23 +199,125 @@ __device__ __forceinline__ long long pf_warp_sum_nonneg(long long e)
 __device__ __forceinline__ long long pf_shfl_ll(long long v, int src) { return __shfl_sync(PF_FULL, v, src); }
 
 // ---------------------------------------------------------------------------------------
+// Detections of the frame in shared memory, bucketed by image column.
+//
+// The score (:2385-2445) depends, per LED, only on the nearest blob if it lies within the gate
+// tol_PF (the greedy loop stops at the first LED whose nearest blob is farther, :2414/:2438).  A
+// blob within the gate has |dx| <= tol_PF, so the search is restricted to the column buckets that
+// intersect [u - r, u + r], r slightly above tol_PF: same minimum, same index, same ties as the
+// reference's full scan whenever the result matters, at a fraction of the distance evaluations.
+// col() is a monotone function of x (subtract, scale by a positive constant, clamp, floor), which
+// is all the argument needs; NaN coordinates fall into bucket 0 and never win a comparison.
+// ---------------------------------------------------------------------------------------
+#define PF_NCOL 128
+struct pf_blob { float x, y; int idx; int pad; };          // 16 B: one LDS.128
+struct pf_blobtab {
+  float x0, inv_cw, r;
+  int D;
+  unsigned short colstart[PF_NCOL + 2];
+  int work[PF_NCOL];                                      // histogram, then insertion cursors
+};
+
+__device__ __forceinline__ int pf_col(const pf_blobtab& bt, float x)
+{
+  const float t = fminf(fmaxf((x - bt.x0) * bt.inv_cw, 0.0f), (float)(PF_NCOL - 1));
+  return (int)t;                                          // t >= 0: truncation == floor
+}
+
+// executed by warp 0; bsrc: D x 2 doubles in global memory
+__device__ __forceinline__ void pf_stage_blobs(const double* bsrc, int D, float tol_pf, pf_blobtab& bt, pf_blob* blobs, int lane)
+{
+  float lo = INFINITY, hi = -INFINITY;
+  for (int i = lane; i < D; i += 32) {
+    const float x = (float)bsrc[2 * i];
+    lo = fminf(lo, x); hi = fmaxf(hi, x);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    lo = fminf(lo, __shfl_xor_sync(PF_FULL, lo, o));
+    hi = fmaxf(hi, __shfl_xor_sync(PF_FULL, hi, o));
+  }
+  const float span = hi - lo;
+  if (lane == 0) {
+    bt.x0 = D > 0 ? lo : 0.0f;
+    bt.inv_cw = (D > 0 && span > 0.0f && span < 3.0e38f) ? (float)PF_NCOL / span : 0.0f;
+    bt.r = tol_pf * 1.0001f + 1.0e-3f;
+    bt.D = D;
+  }
+#pragma unroll
+  for (int c = lane; c < PF_NCOL; c += 32) bt.work[c] = 0;
+  __syncwarp();
+  for (int i = lane; i < D; i += 32) atomicAdd(&bt.work[pf_col(bt, (float)bsrc[2 * i])], 1);
+  __syncwarp();
+  {
+    int h[PF_NCOL / 32], sum = 0;
+#pragma unroll
+    for (int q = 0; q < PF_NCOL / 32; ++q) { h[q] = bt.work[lane * (PF_NCOL / 32) + q]; sum += h[q]; }
+    int inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(PF_FULL, inc, o);
+      if (lane >= o) inc += t;
+    }
+    int run = inc - sum;
+#pragma unroll
+    for (int q = 0; q < PF_NCOL / 32; ++q) {
+      bt.colstart[lane * (PF_NCOL / 32) + q] = (unsigned short)run;
+      bt.work[lane * (PF_NCOL / 32) + q] = run;
+      run += h[q];
+    }
+    if (lane == 31) { bt.colstart[PF_NCOL] = (unsigned short)run; bt.colstart[PF_NCOL + 1] = (unsigned short)run; }
+  }
+  __syncwarp();
+  for (int i = lane; i < D; i += 32) {
+    pf_blob b;
+    b.x = (float)bsrc[2 * i]; b.y = (float)bsrc[2 * i + 1]; b.idx = i; b.pad = 0;
+    const int pos = atomicAdd(&bt.work[pf_col(bt, b.x)], 1);
+    blobs[pos] = b;
+  }
+}
+
+// nearest blob of every projected LED among the buckets within the gate radius; m[j] = +inf,
+// am[j] = 0 if there is none.  Ties go to the smaller blob index (packed-key minimum).
+template <int L>
+__device__ __forceinline__ void pf_nearest_pruned(const pf_blobtab& bt, const pf_blob* blobs, const float* u, const float* v,
+                                                  float* m, int* am)
+{
+#pragma unroll
+  for (int j = 0; j < L; ++j) {
+    const int c0 = pf_col(bt, u[j] - bt.r), c1 = pf_col(bt, u[j] + bt.r);
+    const int a = bt.colstart[c0], b = bt.colstart[c1 + 1];
+    unsigned long long key = ((unsigned long long)0x7F800000u << 32);
+    for (int k = a; k < b; ++k) {
+      const float4 z = *reinterpret_cast<const float4*>(&blobs[k]);
+      const float dx = z.x - u[j], dy = z.y - v[j];
+      const float d2 = fmaf(dy, dy, dx * dx);
+      const unsigned long long kk = ((unsigned long long)__float_as_uint(d2) << 32) | (unsigned)__float_as_int(z.z);
+      key = kk < key ? kk : key;
+    }
+    m[j] = __uint_as_float((unsigned)(key >> 32));
+    am[j] = (int)(unsigned)(key & 0xFFFFFFFFull);
+  }
+}
+
+// ---------------------------------------------------------------------------------------
 // shared-memory frame context (uniform per CTA)
 // ---------------------------------------------------------------------------------------
 struct pf_ctx {
   pf_frame_const fc;
   float obj[PF_MAX_LED * 3];
   double objd[PF_MAX_LED * 3];
-  int src_buf, src_mode, nblk, pad;
+  int src_buf, src_mode, pad[2];
+  pf_blobtab bt;
 };
 
 // ---------------------------------------------------------------------------------------
 // Stage A: fused propagate -> project -> score over this warp's contiguous particles for
-// iteration `it` (:543-605).  first_pass: resolve and cache the resampling source index of every
-// slot.  Leaves the warp's sign-agnostic prefix aggregate in warp_agg[warp].
+// iteration `it` (:543-605).  Leaves the warp's sign-agnostic prefix aggregate in warp_agg[warp].
 // ---------------------------------------------------------------------------------------
 template <int L>
-__device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_ctx& cx, const pf_f2* blobs,
-                                                 int trk, int it, bool first_pass, pf_sm3* warp_agg)
+__device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_ctx& cx, const pf_blob* blobs,
+                                                 const uint32_t* tab, int trk, int it, pf_sm3* warp_agg)
 {
   const int N = p.N;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -225,22 +326,32 @@ __device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_c
   const float4* src = (cx.src_buf == 0 ? p.pose0 : p.pose1) + tb;
   float4* dst = (cx.src_buf == 0 ? p.pose1 : p.pose0) + tb;
   float* w = p.w + (size_t)trk * N;
-  int* idx = p.idx + (size_t)trk * N;
-  const int* kend = p.kend + (size_t)trk * N;
-  const int* tile_kend = p.tile_kend + (size_t)trk * cx.nblk;
+  const int* idx = p.idx + (size_t)trk * N;
 
   pf_pose Pm, Cm;
 #pragma unroll
   for (int i = 0; i < 12; ++i) { Pm.p[i] = cx.fc.P[i]; Cm.p[i] = cx.fc.C[i]; }
   const bool use_cam = cx.fc.isi > 1;                       // :555-560
   const bool use_pred = use_cam && (it % 10) != 0;
+  const bool cam_mul = use_cam && !(cx.fc.flags & PF_FC_CAM_IDENTITY);
+  const bool small_ang = (cx.fc.flags & PF_FC_SMALL_ANG) != 0;
+  const bool kstd = p.kstd != 0;
   const float scale = 1.0f + 0.025f * (float)(it / 10);    // :563 (integer division)
-  const uint64_t step0 = 12ull * (uint64_t)(N - 2) * (uint64_t)it;
 
-  const int wchunk = p.cta_chunk / PF_WARPS;               // multiple of 32
+  const int wchunk = p.cta_chunk / (int)(blockDim.x >> 5); // multiple of 32
   const long long w0l = (long long)blockIdx.x * p.cta_chunk + (long long)warp * wchunk;
   const int w0 = w0l < (long long)N ? (int)w0l : N;
   const int w1 = (w0l + wchunk) < (long long)N ? (int)(w0l + wchunk) : N;
+
+  // RNG: particle n >= 2 starts at engine step 12*((N-2)*it + n-2).  Each lane keeps the
+  // state of "its" particle of the current step and advances it by 32 particles = 384 engine steps
+  // with one modular multiplication (exponents mod the group order, so n < 2 is harmless).
+  uint32_t xs;
+  {
+    const uint64_t e0 = (12ull * (uint64_t)(N - 2) * (uint64_t)it) % PF_RNG_ORDER;
+    const uint64_t ee = (e0 + (uint64_t)PF_RNG_ORDER - 24ull + 12ull * (uint64_t)(w0 + lane)) % PF_RNG_ORDER;
+    xs = pf_rng_skip_e(cx.fc.seed_state, (uint32_t)ee, tab);
+  }
 
   pf_red acc = pf_red_identity();
   pf_sm3 carry = pf_sm3_identity();
@@ -248,12 +359,10 @@ __device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_c
     const int n = base + lane;
     const bool valid = n < w1;
     long long e = 0;
+    const uint32_t x = xs;
+    xs = pf_modmul(xs, PF_RNG_A384);
     if (valid) {
-      int s = n;
-      if (cx.src_mode == 1) {
-        if (first_pass) { s = pf_source_index(kend, tile_kend, cx.nblk, N, n); idx[n] = s; }
-        else s = idx[n];
-      }
+      const int s = cx.src_mode == 1 ? idx[n] : n;      // Particle_index of slot n (:678-681), written by stage B
       pf_pose T;
       if (n == 0) {
 #pragma unroll
@@ -263,16 +372,18 @@ __device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_c
         for (int i = 0; i < 12; ++i) T.p[i] = cx.fc.Tpred[i];     // :551
       } else {
         pf_pose B = pf_load_pose(src, N, s);
-        if (use_cam) B = pf_affine_mul(Cm, B);
+        if (cam_mul) B = pf_affine_mul(Cm, B);
         if (use_pred) B = pf_affine_mul(B, Pm);
-        uint32_t x = pf_rng_skip(cx.fc.seed_state, step0 + 12ull * (uint64_t)(n - 2), p.rng_tab);
-        T = pf_propagate(B, x, cx.fc.noise, scale);
+        T = pf_propagate(B, x, cx.fc.noise, scale, small_ang);
       }
       pf_store_pose(dst, N, n, T);
       float u[L], v[L];
 #pragma unroll
-      for (int j = 0; j < L; ++j) pf_project(p.K9f, T, cx.obj[3 * j], cx.obj[3 * j + 1], cx.obj[3 * j + 2], u[j], v[j]);
-      const float wn = pf_score<L, false>(blobs, cx.fc.D, u, v, p.score, nullptr, nullptr);
+      for (int j = 0; j < L; ++j) pf_project(p.K9f, kstd, T, cx.obj[3 * j], cx.obj[3 * j + 1], cx.obj[3 * j + 2], u[j], v[j]);
+      float m[L];
+      int am[L];
+      pf_nearest_pruned<L>(cx.bt, blobs, u, v, m, am);
+      const float wn = pf_greedy<L, false>(m, am, cx.fc.D, p.score, nullptr, nullptr);
       w[n] = wn;
       const unsigned o = pf_ord(wn);
       const unsigned long long kmax = ((unsigned long long)o << 32) | (unsigned)(~(unsigned)n);
@@ -310,111 +421,191 @@ __device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_c
   return acc;
 }
 
-// Exclusive combination of the aggregates of CTAs 0..b-1 (grid mode, after barrier 1).
-// scr: PF_WARPS entries of shared scratch.  Result valid in every thread.
-__device__ __forceinline__ pf_sm3 pf_cta_exclusive(const pf_kparams& p, pf_sm3* scr)
+// Exclusive combination of the aggregates of CTAs 0..b-1 and the combination of all of them
+// (after barrier 1; batch mode: one CTA, the total is the combination of its warps).
+// scr: 2 * PF_MAX_WARPS entries of shared scratch.  Results valid in every thread.
+__device__ __forceinline__ void pf_cta_prefix(const pf_kparams& p, const pf_sm3* warp_agg, pf_sm3* scr, pf_sm3& excl,
+                                              pf_sm3& total)
 {
-  const int b = blockIdx.x;
+  const int nwarps = blockDim.x >> 5;
+  if (!p.coop) {
+    excl = pf_sm3_identity();
+    total = warp_agg[0];
+    for (int i = 1; i < nwarps; ++i) total = pf_sm3_combine(total, warp_agg[i]);
+    return;
+  }
+  const int b = blockIdx.x, G = gridDim.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const volatile pf_cta_agg* g = p.cta_agg;
-  const int seg = (b + PF_BLOCK - 1) / PF_BLOCK;
-  pf_sm3 v = pf_sm3_identity();
-  for (int i = threadIdx.x * seg; i < (threadIdx.x + 1) * seg && i < b; ++i) {
+  const int seg = (G + (int)blockDim.x - 1) / (int)blockDim.x;
+  pf_sm3 v = pf_sm3_identity(), a = pf_sm3_identity();
+  for (int i = threadIdx.x * seg; i < (threadIdx.x + 1) * seg && i < G; ++i) {
     pf_sm3 t; t.s = g[i].s; t.mx = g[i].mx; t.mn = g[i].mn;
-    v = pf_sm3_combine(v, t);
+    if (i < b) v = pf_sm3_combine(v, t);
+    a = pf_sm3_combine(a, t);
   }
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
-    pf_sm3 t;
+    pf_sm3 t, u;
     t.s = __shfl_down_sync(PF_FULL, v.s, o);
     t.mx = __shfl_down_sync(PF_FULL, v.mx, o);
     t.mn = __shfl_down_sync(PF_FULL, v.mn, o);
-    if (lane + o < 32) v = pf_sm3_combine(v, t);
+    u.s = __shfl_down_sync(PF_FULL, a.s, o);
+    u.mx = __shfl_down_sync(PF_FULL, a.mx, o);
+    u.mn = __shfl_down_sync(PF_FULL, a.mn, o);
+    if (lane + o < 32) { v = pf_sm3_combine(v, t); a = pf_sm3_combine(a, u); }
   }
   __syncthreads();
-  if (lane == 0) scr[warp] = v;
+  if (lane == 0) { scr[warp] = v; scr[PF_MAX_WARPS + warp] = a; }
   __syncthreads();
-  pf_sm3 r = scr[0];
-#pragma unroll
-  for (int i = 1; i < PF_WARPS; ++i) r = pf_sm3_combine(r, scr[i]);
-  return r;
+  excl = scr[0];
+  total = scr[PF_MAX_WARPS];
+  for (int i = 1; i < nwarps; ++i) {
+    excl = pf_sm3_combine(excl, scr[i]);
+    total = pf_sm3_combine(total, scr[PF_MAX_WARPS + i]);
+  }
 }
 
 // ---------------------------------------------------------------------------------------
 // Stage B: normalise + prefix + stratified resampling in source-centric form (:627-629, :668-682).
 // The prefix runs on sg*Q.30 weights with the (sum, running max) operator; for every source i the
-// cumulative offspring count kend[i] = K(M_i) is stored (4 B) instead of the FP64 prefix,
-// count_i = kend[i] - kend[i-1], and the most-resampled particle (:685-686) falls out of the same
-// pass.  Each warp walks its contiguous particles with a register carry whose start value is
-// (exclusive CTA prefix) (+) (aggregates of the lower warps of this CTA), both from stage A.
+// cumulative offspring count kend[i] = K(M_i) is computed, count_i = kend[i] - kend[i-1], and the
+// most-resampled particle (:685-686) falls out of the same pass.  Each warp walks its contiguous
+// particles with a register carry whose start value is (exclusive CTA prefix) (+) (aggregates of
+// the lower warps of this CTA), both from stage A.
+// Every source then writes its own index into the output slots it owns, idx[kend[i-1] .. kend[i])
+// (= Particle_index of :678-681), so that the next score pass reads its source with one coalesced
+// load instead of searching.  The last source with offspring also owns the slots >= K_total
+// ("not found keeps the previous index", Q7).  The 32 sources of a warp step own one contiguous
+// slot range: the warp fills it with coalesced stores, each slot finding its source lane by a
+// 5-step shuffle search over the lanes' cumulative counts; a source with more than PF_FILL_WARP
+// slots is handed to the whole CTA after the walk.
 // ---------------------------------------------------------------------------------------
-__device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const pf_ctx& cx, int trk, long long S_fx,
-                                                    int iters_total, const pf_sm3& cta_excl, const pf_sm3* warp_agg)
+#define PF_FILL_WARP 4096
+#define PF_FILL_LIST 32
+
+struct pf_fill_list {
+  int n;
+  int start[PF_FILL_LIST], end[PF_FILL_LIST], src[PF_FILL_LIST];
+};
+
+__device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const pf_ctx& cx, const uint32_t* tab, int trk,
+                                                    long long S_fx, int iters_total, const pf_sm3& cta_excl,
+                                                    const pf_sm3& total3, const pf_sm3* warp_agg, pf_fill_list* fl)
 {
   const int N = p.N;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const float* w = p.w + (size_t)trk * N;
   int* kend = p.kend + (size_t)trk * N;
-  int* tile_kend = p.tile_kend + (size_t)trk * cx.nblk;
+  int* idx = p.idx + (size_t)trk * N;
   const long long sg = S_fx < 0 ? -1ll : 1ll;
-  const uint32_t x_base = pf_rng_skip(cx.fc.seed_state, 12ull * (uint64_t)(N - 2) * (uint64_t)iters_total, p.rng_tab);
+  const uint32_t x_base = pf_rng_skip(cx.fc.seed_state, 12ull * (uint64_t)(N - 2) * (uint64_t)iters_total, tab);
   const pf_resample_cfg rc = pf_make_resample_cfg(x_base, N, S_fx);
+  int ktot;                                               // K(M) of the whole filter
+  {
+    long long ts_, tm_;
+    pf_sm3_select(total3, sg, ts_, tm_);
+    ktot = pf_count_leq(tm_, rc, tab);
+  }
 
-  const int wchunk = p.cta_chunk / PF_WARPS;
+  const int wchunk = p.cta_chunk / (int)(blockDim.x >> 5);
   const long long w0l = (long long)blockIdx.x * p.cta_chunk + (long long)warp * wchunk;
   const int w0 = w0l < (long long)N ? (int)w0l : N;
   const int w1 = (w0l + wchunk) < (long long)N ? (int)(w0l + wchunk) : N;
 
   pf_red acc = pf_red_identity();
-  if (w0 >= w1) return acc;
-  pf_sm3 pre3 = cta_excl;
-  for (int i = 0; i < warp; ++i) pre3 = pf_sm3_combine(pre3, warp_agg[i]);
-  pf_sm carry;
-  pf_sm3_select(pre3, sg, carry.s, carry.m);
-  int k_carry = pf_count_leq(carry.m, rc, p.rng_tab);     // K(M) of everything before this warp
+  if (w0 < w1) {
+    pf_sm3 pre3 = cta_excl;
+    for (int i = 0; i < warp; ++i) pre3 = pf_sm3_combine(pre3, warp_agg[i]);
+    pf_sm carry;
+    pf_sm3_select(pre3, sg, carry.s, carry.m);
+    int k_carry = pf_count_leq(carry.m, rc, tab);         // K(M) of everything before this warp
 
-  for (int base = w0; base < w1; base += 32) {
-    const int n = base + lane;
-    const bool valid = n < w1;
-    const long long e = valid ? sg * pf_w_to_fx(w[n]) : 0ll;
-    long long M, total;
-    if (!__any_sync(PF_FULL, e < 0)) {
-      long long ps = e;                                   // inclusive prefix sum inside the step
+    for (int base = w0; base < w1; base += 32) {
+      const int n = base + lane;
+      const bool valid = n < w1;
+      const long long e = valid ? sg * pf_w_to_fx(w[n]) : 0ll;
+      long long M, total;
+      if (!__any_sync(PF_FULL, e < 0)) {
+        long long ps = e;                                 // inclusive prefix sum inside the step
 #pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const long long t = __shfl_up_sync(PF_FULL, ps, o);
-        if (lane >= o) ps += t;
-      }
-      const long long pfx = carry.s + ps;
-      M = carry.m > pfx ? carry.m : pfx;
-      total = pf_shfl_ll(ps, 31);
-    } else {
-      pf_sm a;
-      if (valid) { a.s = e; a.m = e; } else a = pf_sm_identity();
+        for (int o = 1; o < 32; o <<= 1) {
+          const long long t = __shfl_up_sync(PF_FULL, ps, o);
+          if (lane >= o) ps += t;
+        }
+        const long long pfx = carry.s + ps;
+        M = carry.m > pfx ? carry.m : pfx;
+        total = pf_shfl_ll(ps, 31);
+      } else {
+        pf_sm a;
+        if (valid) { a.s = e; a.m = e; } else a = pf_sm_identity();
 #pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        pf_sm t;
-        t.s = __shfl_up_sync(PF_FULL, a.s, o);
-        t.m = __shfl_up_sync(PF_FULL, a.m, o);
-        if (lane >= o) a = pf_sm_combine(t, a);
+        for (int o = 1; o < 32; o <<= 1) {
+          pf_sm t;
+          t.s = __shfl_up_sync(PF_FULL, a.s, o);
+          t.m = __shfl_up_sync(PF_FULL, a.m, o);
+          if (lane >= o) a = pf_sm_combine(t, a);
+        }
+        const pf_sm pre = pf_sm_combine(carry, a);
+        M = pre.m;
+        total = pf_shfl_ll(a.s, 31);
       }
-      const pf_sm pre = pf_sm_combine(carry, a);
-      M = pre.m;
-      total = pf_shfl_ll(a.s, 31);
+      const int ke = pf_count_leq(M, rc, tab);
+      int k_prev = __shfl_up_sync(PF_FULL, ke, 1);
+      if (lane == 0) k_prev = k_carry;
+      if (valid) {
+        kend[n] = ke;
+        const unsigned cnt = (unsigned)(ke - k_prev);
+        const unsigned long long key = ((unsigned long long)cnt << 32) | (unsigned)(~(unsigned)n);
+        acc.cntkey = key > acc.cntkey ? key : acc.cntkey;
+      }
+      // ---- slot fill: the sources of this step own the contiguous slots [E(k_carry), E(ke of lane 31)),
+      // E(k) = N if k == K_total (the last source with offspring also owns the not-found tail, Q7)
+      if (ktot == 0) {
+        if (valid) idx[n] = n;                            // nothing was ever found: every slot keeps its own particle
+      } else {
+        const int Ecur = ke == ktot ? N : ke;
+        const int Eprev = k_prev == ktot ? N : k_prev;
+        const int own = Ecur - Eprev;                     // invalid lanes repeat the last prefix: 0
+        const unsigned bigm = __ballot_sync(PF_FULL, own > PF_FILL_WARP);
+        if (bigm == 0u) {
+          const int E0 = __shfl_sync(PF_FULL, Eprev, 0), R = __shfl_sync(PF_FULL, Ecur, 31) - E0;
+          for (int q0 = 0; q0 < R; q0 += 32) {            // warp-uniform trip count: every lane serves the shuffles
+            const int k = E0 + q0 + lane;
+            int lo = 0, hi = 31;                          // smallest lane whose Ecur > k
+#pragma unroll
+            for (int t = 0; t < 5; ++t) {
+              const int mid = (lo + hi) >> 1;
+              const int v = __shfl_sync(PF_FULL, Ecur, mid);
+              if (v > k) hi = mid; else lo = mid + 1;
+            }
+            if (q0 + lane < R) idx[k] = base + lo;
+          }
+        } else {
+          // rare: a source owns more than PF_FILL_WARP slots; hand those to the whole CTA (list) and
+          // fill the rest lane by lane
+          const bool isbig = (bigm >> lane) & 1u;
+          int slot = -1;
+          if (isbig) {
+            slot = atomicAdd(&fl->n, 1);
+            if (slot < PF_FILL_LIST) { fl->start[slot] = Eprev; fl->end[slot] = Ecur; fl->src[slot] = n; }
+          }
+          if (!isbig || slot >= PF_FILL_LIST)
+            for (int k = Eprev; k < Ecur; ++k) idx[k] = n;
+        }
+      }
+      carry.s += total;
+      carry.m = pf_shfl_ll(M, 31);          // invalid lanes repeat the last valid prefix
+      k_carry = __shfl_sync(PF_FULL, ke, 31);
     }
-    const int ke = pf_count_leq(M, rc, p.rng_tab);
-    int k_prev = __shfl_up_sync(PF_FULL, ke, 1);
-    if (lane == 0) k_prev = k_carry;
-    if (valid) {
-      kend[n] = ke;
-      const unsigned cnt = (unsigned)(ke - k_prev);
-      const unsigned long long key = ((unsigned long long)cnt << 32) | (unsigned)(~(unsigned)n);
-      acc.cntkey = key > acc.cntkey ? key : acc.cntkey;
-      if ((n % PF_SEARCH_BLOCK) == PF_SEARCH_BLOCK - 1 || n == N - 1) tile_kend[n / PF_SEARCH_BLOCK] = ke;
+  }
+  __syncthreads();
+  {
+    const int nl = fl->n < PF_FILL_LIST ? fl->n : PF_FILL_LIST;
+    for (int q = 0; q < nl; ++q) {
+      const int s0 = fl->start[q], s1 = fl->end[q], src = fl->src[q];
+      for (int k = s0 + (int)threadIdx.x; k < s1; k += (int)blockDim.x) idx[k] = src;
     }
-    carry.s += total;
-    carry.m = pf_shfl_ll(M, 31);          // invalid lanes repeat the last valid prefix
-    k_carry = __shfl_sync(PF_FULL, ke, 31);
   }
   return acc;
 }
@@ -428,7 +619,7 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
 // ---------------------------------------------------------------------------------------
 template <int L>
 __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, pf_ctx& cx, pf_tracker_state& st, pf_tail_smem& ts,
-                                           const pf_f2* blobs, int trk, int frame, int iters, int best_it,
+                                           const pf_blob* blobs, int trk, int frame, int iters, int best_it,
                                            float highest, const pf_red& kept, bool accept, bool resampled,
                                            const pf_red& cnt)
 {
@@ -451,10 +642,10 @@ __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, pf_ctx& cx, pf_t
   {
     float u[L], v[L];
 #pragma unroll
-    for (int j = 0; j < L; ++j) pf_project(p.K9f, Tw, cx.obj[3 * j], cx.obj[3 * j + 1], cx.obj[3 * j + 2], u[j], v[j]);
+    for (int j = 0; j < L; ++j) pf_project(p.K9f, p.kstd != 0, Tw, cx.obj[3 * j], cx.obj[3 * j + 1], cx.obj[3 * j + 2], u[j], v[j]);
 #pragma unroll
     for (int j = 0; j < 2 * L; ++j) pairs[j] = 0u;
-    (void)pf_score<L, true>(blobs, cx.fc.D, u, v, p.score, pairs, &npairs);
+    (void)pf_score_warp<L>(blobs, cx.fc.D, u, v, p.score, pairs, &npairs, lane);
   }
   if (writer) {
     res->status = accept ? 1 : 4;
@@ -499,6 +690,7 @@ __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, pf_ctx& cx, pf_t
       const pf_aff before = pose;
       const double* img = p.blobs + ((size_t)trk * p.total_frames + frame) * (size_t)p.D_max * 2;
       const int gn = pf_gn_warp<L>(p.K9d, cx.objd, img, pairs, npairs, pose, ts, lane);   // cov -> ts.M
+      pf_stamp(p, 10);
       if (isi < 2) ++isi;                                // :2027-2030
       prev = cur;                                        // updatePose :2013-2014
       cur = pose;
@@ -539,7 +731,8 @@ __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, pf_ctx& cx, pf_t
     if (resampled && frame + 1 < p.total_frames) {
       const double t_next = p.times[frame + 1];
       pf_aff P, predn;
-      pf_predict_pose(prev, cur, t_prev, t_cur, t_next, P, predn);   // :234 -> :995-1010
+      pf_predict_pose_dev(prev, cur, t_prev, t_cur, t_next, P, predn);   // :234 -> :995-1010
+      pf_stamp(p, 11);
       const size_t fi = (size_t)trk * p.total_frames + frame + 1;
       if (lane == 0) {
         st.t_pred = t_next;
@@ -569,35 +762,40 @@ __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, pf_ctx& cx, pf_t
 // The persistent frame kernel.
 // ---------------------------------------------------------------------------------------
 template <int L>
-__global__ void __launch_bounds__(PF_BLOCK, 3) pf_frames_kernel(const __grid_constant__ pf_kparams p)
+__global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid_constant__ pf_kparams p)
 {
   extern __shared__ __align__(16) unsigned char pf_dyn_smem[];
-  pf_f2* blobs = reinterpret_cast<pf_f2*>(pf_dyn_smem);
+  pf_blob* blobs = reinterpret_cast<pf_blob*>(pf_dyn_smem);
   __shared__ pf_ctx cx;
   __shared__ pf_tracker_state st;
   __shared__ pf_tail_smem ts;
-  __shared__ pf_red red_smem[PF_WARPS];
-  __shared__ pf_sm3 warp_agg[PF_WARPS];
-  __shared__ pf_sm3 scr[PF_WARPS];
+  __shared__ pf_red red_smem[PF_MAX_WARPS];
+  __shared__ pf_sm3 warp_agg[PF_MAX_WARPS];
+  __shared__ pf_sm3 scr[2 * PF_MAX_WARPS];
+  __shared__ pf_fill_list fill;
+  __shared__ uint32_t tab[1024];         // radix-256 power table of the RNG skip-ahead
 
   const int trk = p.tracker_base + blockIdx.y;
   const int N = p.N;
-  // reduction-slot rotation continues across launches (accum[3] holds the next round, mod 3)
-  unsigned round = p.coop ? (unsigned)(*(volatile unsigned long long*)&p.accum[3].maxkey) : 0u;
+  // reduction-slot rotation and the barrier count continue across launches (accum[3]); every CTA
+  // reads them before its first barrier, CTA 0 writes them back after its last one
+  pf_bar bar;
+  bar.round = p.coop ? (unsigned)(*(volatile unsigned long long*)&p.accum[3].maxkey) : 0u;
+  bar.done = p.coop ? *(volatile unsigned long long*)&p.accum[3].minkey_inv : 0ull;
 
   // tracker state and the staged constants of the first frame: global -> shared (every CTA)
   {
     const uint32_t* g32 = reinterpret_cast<const uint32_t*>(p.state + trk);
     uint32_t* s32 = reinterpret_cast<uint32_t*>(&st);
-    for (int i = threadIdx.x; i < (int)(sizeof(pf_tracker_state) / 4); i += PF_BLOCK) s32[i] = g32[i];
+    for (int i = threadIdx.x; i < (int)(sizeof(pf_tracker_state) / 4); i += blockDim.x) s32[i] = g32[i];
     const uint32_t* h32 = reinterpret_cast<const uint32_t*>(p.fconst + trk);
     uint32_t* f32 = reinterpret_cast<uint32_t*>(&cx.fc);
-    for (int i = threadIdx.x; i < (int)(sizeof(pf_frame_const) / 4); i += PF_BLOCK) f32[i] = h32[i];
+    for (int i = threadIdx.x; i < (int)(sizeof(pf_frame_const) / 4); i += blockDim.x) f32[i] = h32[i];
     if (threadIdx.x < 3 * L) {
       cx.obj[threadIdx.x] = p.obj_f[(size_t)trk * PF_MAX_LED * 3 + threadIdx.x];
       cx.objd[threadIdx.x] = p.obj_d[(size_t)trk * PF_MAX_LED * 3 + threadIdx.x];
     }
-    if (threadIdx.x == 0) cx.nblk = (N + PF_SEARCH_BLOCK - 1) / PF_SEARCH_BLOCK;
+    for (int i = threadIdx.x; i < 1024; i += blockDim.x) tab[i] = p.rng_tab[i];
   }
 
   for (int f = 0; f < p.n_frames; ++f) {
@@ -610,13 +808,10 @@ __global__ void __launch_bounds__(PF_BLOCK, 3) pf_frames_kernel(const __grid_con
     }
     if (threadIdx.x == 0) { cx.src_buf = st.src_buf; cx.src_mode = st.src_mode; }
     const int D = cx.fc.D;
-    {
+    if (threadIdx.x < 32) {
       const double* bsrc = p.blobs + ((size_t)trk * (p.mode == 1 ? p.total_frames : 1) + (p.mode == 1 ? frame : 0)) *
                                          (size_t)p.D_max * 2;
-      for (int i = threadIdx.x; i < D; i += PF_BLOCK) {
-        pf_f2 z; z.x = (float)bsrc[2 * i]; z.y = (float)bsrc[2 * i + 1];
-        blobs[i] = z;
-      }
+      pf_stage_blobs(bsrc, D, p.score.tol_pf, cx.bt, blobs, threadIdx.x);
     }
     __syncthreads();
     pf_stamp(p, 1);
@@ -627,9 +822,9 @@ __global__ void __launch_bounds__(PF_BLOCK, 3) pf_frames_kernel(const __grid_con
     int best_it = -1, it = 0;
     pf_red kept = pf_red_identity(), last = pf_red_identity();
     for (;;) {
-      pf_red r = pf_stage_score<L>(p, cx, blobs, trk, it, it == 0, warp_agg);
+      pf_red r = pf_stage_score<L>(p, cx, blobs, tab, trk, it, warp_agg);
       if (it == 0) pf_stamp(p, 2);
-      r = pf_grid_reduce(r, red_smem, p, round, warp_agg);
+      r = pf_grid_reduce(r, red_smem, p, bar, warp_agg);
       if (it == 0) pf_stamp(p, 3);
       const float m = pf_unord((unsigned)(r.maxkey >> 32));
       last = r;
@@ -642,10 +837,10 @@ __global__ void __launch_bounds__(PF_BLOCK, 3) pf_frames_kernel(const __grid_con
     else if (best_it != iters - 1) {
       // the kept iteration is not the last one: regenerate its particles, weights and prefix
       // aggregates (exact: the RNG is addressed by (iteration, particle))
-      (void)pf_stage_score<L>(p, cx, blobs, trk, best_it, false, warp_agg);
+      (void)pf_stage_score<L>(p, cx, blobs, tab, trk, best_it, warp_agg);
       __syncthreads();
       pf_publish_cta_agg(p, warp_agg);
-      pf_sync_all(p);
+      pf_sync_all(p, bar);
     }
 
     // ---- accept test (:633) and resampling (:666-682)
@@ -654,10 +849,13 @@ __global__ void __launch_bounds__(PF_BLOCK, 3) pf_frames_kernel(const __grid_con
     pf_red cnt = pf_red_identity();
     if (resampled) {
       pf_stamp(p, 4);
-      const pf_sm3 cta_excl = p.coop ? pf_cta_exclusive(p, scr) : pf_sm3_identity();
-      cnt = pf_stage_resample(p, cx, trk, kept.sum, iters, cta_excl, warp_agg);
+      pf_sm3 cta_excl, total3;
+      if (threadIdx.x == 0) fill.n = 0;                  // ordered before its use by the barriers in pf_cta_prefix / below
+      pf_cta_prefix(p, warp_agg, scr, cta_excl, total3);
+      __syncthreads();
+      cnt = pf_stage_resample(p, cx, tab, trk, kept.sum, iters, cta_excl, total3, warp_agg, &fill);
       pf_stamp(p, 5);
-      cnt = pf_grid_reduce(cnt, red_smem, p, round, nullptr);
+      cnt = pf_grid_reduce(cnt, red_smem, p, bar, nullptr);
       pf_stamp(p, 6);
     }
 
@@ -666,17 +864,19 @@ __global__ void __launch_bounds__(PF_BLOCK, 3) pf_frames_kernel(const __grid_con
     pf_stamp(p, 8);
     pf_stamp(p, 9);
   }
-  // every CTA read accum[3] before its first barrier; CTA 0 gets here after the last one
-  if (p.coop && blockIdx.x == 0 && threadIdx.x == 0) p.accum[3].maxkey = (unsigned long long)(round % 3u);
+  if (p.coop && blockIdx.x == 0 && threadIdx.x == 0) {
+    p.accum[3].maxkey = (unsigned long long)(bar.round % 3u);
+    p.accum[3].minkey_inv = bar.done;
+  }
 }
 
-// Materialise newPoseEstimation (the resampled set) for the getters / ROI: out[n] = T[idx(n)].
-__global__ void __launch_bounds__(PF_BLOCK) pf_gather_kernel(const float4* T, const int* kend, const int* tile_kend,
-                                                             int nblk, int N, int src_mode, float4* out, int* idx_out)
+// Materialise newPoseEstimation (the resampled set) for the getters / ROI: out[n] = T[idx[n]].
+__global__ void __launch_bounds__(PF_BLOCK) pf_gather_kernel(const float4* T, const int* idx, int N, int src_mode,
+                                                             float4* out, int* idx_out)
 {
   const int n = blockIdx.x * PF_BLOCK + threadIdx.x;
   if (n >= N) return;
-  const int s = src_mode == 1 ? pf_source_index(kend, tile_kend, nblk, N, n) : n;
+  const int s = src_mode == 1 ? idx[n] : n;
   out[n] = T[s];
   out[(size_t)N + n] = T[(size_t)N + s];
   out[2 * (size_t)N + n] = T[2 * (size_t)N + s];

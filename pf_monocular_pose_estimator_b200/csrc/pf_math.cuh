@@ -15,6 +15,7 @@
 
 #include <stdint.h>
 #include <math.h>
+#include <string.h>
 
 #if defined(__CUDACC__)
 #define PF_HD __host__ __device__ __forceinline__
@@ -46,9 +47,28 @@ PF_HD uint32_t pf_modmul(uint32_t a, uint32_t b)
   return s >= PF_RNG_M ? s - PF_RNG_M : s;
 }
 
-PF_HD uint32_t pf_rng_next(uint32_t x) { return pf_modmul(x, PF_RNG_A); }
+// one engine step: x * 16807 < 2^46, so a single fold leaves s < 2^31 + 2^15 and one conditional
+// subtraction (as an unsigned min) finishes the reduction
+PF_HD uint32_t pf_rng_next(uint32_t x)
+{
+  const uint64_t p = (uint64_t)x * (uint64_t)PF_RNG_A;
+  const uint32_t s = (uint32_t)(p & PF_RNG_M) + (uint32_t)(p >> 31);
+  const uint32_t t = s - PF_RNG_M;          // wraps to a huge value when s < m
+  return s < t ? s : t;
+}
 
 // tab[d*256 + v] = 16807^(v * 256^d) mod m, d = 0..3 (built on the host, pfmpe_api.cu)
+// pf_rng_skip_e: exponent already reduced mod PF_RNG_ORDER (16807 is a primitive root of 2^31-1).
+PF_HD uint32_t pf_rng_skip_e(uint32_t x, uint32_t e, const uint32_t* tab)
+{
+  x = pf_modmul(x, tab[e & 255u]);
+  x = pf_modmul(x, tab[256 + ((e >> 8) & 255u)]);
+  x = pf_modmul(x, tab[512 + ((e >> 16) & 255u)]);
+  x = pf_modmul(x, tab[768 + (e >> 24)]);
+  return x;
+}
+#define PF_RNG_A384 1618907920u /* 16807^384 mod (2^31-1): 32 particles x 12 engine steps (checked in pfmpe_api.cu) */
+
 PF_HD uint32_t pf_rng_skip(uint32_t x, uint64_t steps, const uint32_t* __restrict__ tab)
 {
   uint32_t e = (uint32_t)(steps % PF_RNG_ORDER);
@@ -116,7 +136,21 @@ struct pf_noise_cfg {
 // Motion model for particle n >= 2 (:555-587).  `base` = camMoveInv*E_n[*predictionMatrix];
 // x = engine state right before this particle's first draw; 12 engine steps are consumed in
 // the order aX,aY,aZ,tX,tY,tZ.  scale = 1 + 0.025*floor(iter/10).
-PF_HD pf_pose pf_propagate(const pf_pose& base, uint32_t x, const pf_noise_cfg& nc, float scale)
+// sin/cos for |x| <= 0.3 (truncation error < 1e-12 relative: below FP32 rounding)
+PF_HD void pf_sincos_small(float x, float& s, float& c)
+{
+  const float x2 = x * x;
+  float p = fmaf(x2, 2.7557319e-6f, -1.9841270e-4f);
+  p = fmaf(p, x2, 8.3333333e-3f);
+  p = fmaf(p, x2, -1.6666667e-1f);
+  s = fmaf(x * x2, p, x);
+  float q = fmaf(x2, 2.4801587e-5f, -1.3888889e-3f);
+  q = fmaf(q, x2, 4.1666667e-2f);
+  q = fmaf(q, x2, -0.5f);
+  c = fmaf(q, x2, 1.0f);
+}
+
+PF_HD pf_pose pf_propagate(const pf_pose& base, uint32_t x, const pf_noise_cfg& nc, float scale, bool small_ang)
 {
   float c6[6];
 #pragma unroll
@@ -130,11 +164,15 @@ PF_HD pf_pose pf_propagate(const pf_pose& base, uint32_t x, const pf_noise_cfg& 
   const float b = fmaf(c6[1], nc.ang_span, nc.ang_lo) * scale;
   const float c = fmaf(c6[2], nc.ang_span, nc.ang_lo) * scale;
   float sa, ca, sb, cb, sc, cc;
+  if (small_ang) {   // uniform per frame (PF_FC_SMALL_ANG): every possible draw is within +-0.3 rad
+    pf_sincos_small(a, sa, ca); pf_sincos_small(b, sb, cb); pf_sincos_small(c, sc, cc);
+  } else {
 #if defined(__CUDA_ARCH__)
-  sincosf(a, &sa, &ca); sincosf(b, &sb, &cb); sincosf(c, &sc, &cc);
+    sincosf(a, &sa, &ca); sincosf(b, &sb, &cb); sincosf(c, &sc, &cc);
 #else
-  sa = sinf(a); ca = cosf(a); sb = sinf(b); cb = cosf(b); sc = sinf(c); cc = cosf(c);
+    sa = sinf(a); ca = cosf(a); sb = sinf(b); cb = cosf(b); sc = sinf(c); cc = cosf(c);
 #endif
+  }
   // Rn = Rz(c) * Ry(b) * Rx(a)   (:567-582)
   float r[9];
   r[0] = cc * cb; r[1] = cc * sb * sa - sc * ca; r[2] = cc * sb * ca + sc * sa;
@@ -159,16 +197,29 @@ PF_HD pf_pose pf_propagate(const pf_pose& base, uint32_t x, const pf_noise_cfg& 
 }
 
 // project2d (:1017-1034): p = K (R X + t), (u,v) = (p0/p2, p1/p2); full 3x3 K, no cheirality test.
-PF_HD void pf_project(const float* __restrict__ K9, const pf_pose& T, float X, float Y, float Z, float& u, float& v)
+// kstd (uniform): K has the usual zero pattern (K01 = K10 = K20 = K21 = 0, K22 = 1); the skipped
+// terms are exact zeros, so both branches give the same bits for finite inputs.  The two
+// divisions share one correctly rounded reciprocal (<= 1 ulp from the quotient).
+PF_HD bool pf_k_is_std(const float* K9) { return K9[1] == 0.0f && K9[3] == 0.0f && K9[6] == 0.0f && K9[7] == 0.0f && K9[8] == 1.0f; }
+
+PF_HD void pf_project(const float* __restrict__ K9, bool kstd, const pf_pose& T, float X, float Y, float Z, float& u, float& v)
 {
   float xc = fmaf(T.p[0], X, fmaf(T.p[1], Y, fmaf(T.p[2], Z, T.p[3])));
   float yc = fmaf(T.p[4], X, fmaf(T.p[5], Y, fmaf(T.p[6], Z, T.p[7])));
   float zc = fmaf(T.p[8], X, fmaf(T.p[9], Y, fmaf(T.p[10], Z, T.p[11])));
-  float p0 = fmaf(K9[0], xc, fmaf(K9[1], yc, K9[2] * zc));
-  float p1 = fmaf(K9[3], xc, fmaf(K9[4], yc, K9[5] * zc));
-  float p2 = fmaf(K9[6], xc, fmaf(K9[7], yc, K9[8] * zc));
-  u = p0 / p2;
-  v = p1 / p2;
+  float p0, p1, p2;
+  if (kstd) {
+    p0 = fmaf(K9[0], xc, K9[2] * zc);
+    p1 = fmaf(K9[4], yc, K9[5] * zc);
+    p2 = zc;
+  } else {
+    p0 = fmaf(K9[0], xc, fmaf(K9[1], yc, K9[2] * zc));
+    p1 = fmaf(K9[3], xc, fmaf(K9[4], yc, K9[5] * zc));
+    p2 = fmaf(K9[6], xc, fmaf(K9[7], yc, K9[8] * zc));
+  }
+  const float r = 1.0f / p2;
+  u = p0 * r;
+  v = p1 * r;
 }
 
 // ----------------------------------------------------------------------------------------
@@ -181,6 +232,67 @@ struct pf_score_cfg {
   float tol_pf;         // back_projection_pixel_tolerance_PF (gate)      :2414
   unsigned dg_mask;     // bMarkerDowngrade bits (first five LEDs only)   :2431
 };
+
+// Greedy part (:2409-2438) on the per-LED nearest-blob results (m[j] = squared distance >= 0 or
+// +inf, am[j] = blob index < 65536).  The reference takes the LEDs in ascending (distance, LED)
+// order: the keys (bits(m) << 32 | j << 16 | am) are sorted with a fixed compare-exchange network
+// (squared distances are non-negative, so their bit patterns order like the values) and walked
+// until the first one beyond the gate.
+template <int L, bool WANT_PAIRS>
+PF_HD float pf_greedy(const float* m, const int* am, int D, const pf_score_cfg& sc, unsigned* pairs, int* npairs)
+{
+  uint64_t key[L];
+#pragma unroll
+  for (int j = 0; j < L; ++j) {
+    uint32_t mb;
+#if defined(__CUDA_ARCH__)
+    mb = __float_as_uint(m[j]);
+#else
+    { float t = m[j]; memcpy(&mb, &t, 4); }
+#endif
+    key[j] = ((uint64_t)mb << 32) | ((uint64_t)j << 16) | (uint64_t)(unsigned)am[j];
+  }
+  // odd-even transposition sort, L rounds (all indices compile-time)
+#pragma unroll
+  for (int r = 0; r < L; ++r) {
+#pragma unroll
+    for (int i = (r & 1); i + 1 < L; i += 2) {
+      const uint64_t a = key[i], b = key[i + 1];
+      key[i] = a < b ? a : b;
+      key[i + 1] = a < b ? b : a;
+    }
+  }
+  const int steps = D < L ? D : L;   // :2409
+  float P = 0.0f;
+  int occ = 1, nacc = 0;
+  unsigned prev_am[L];
+#pragma unroll
+  for (int k = 0; k < L; ++k) {
+    if (k >= steps) break;
+    const uint32_t mb = (uint32_t)(key[k] >> 32);
+    const unsigned best = (unsigned)(key[k] >> 16) & 0xFFFFu, bam = (unsigned)key[k] & 0xFFFFu;
+    float bm;
+#if defined(__CUDA_ARCH__)
+    bm = __uint_as_float(mb);
+#else
+    memcpy(&bm, &mb, 4);
+#endif
+    const float d = sqrtf(bm);       // :2412
+    if (!(d <= sc.tol_pf)) break;    // :2414 / :2438
+    const float g = (sc.tol - d) * sc.inv_tol;
+    P += (float)L + g * g;           // :2416
+    bool reused = false;             // :2421
+#pragma unroll
+    for (int q = 0; q < k; ++q) reused = reused || (prev_am[q] == bam);
+    prev_am[k] = bam;
+    if (reused) { P -= (float)(3 * occ); ++occ; }   // :2423-2424
+    if ((sc.dg_mask >> best) & 1u) P -= 2.0f;       // :2431-2432
+    if (WANT_PAIRS) { pairs[2 * nacc] = best + 1u; pairs[2 * nacc + 1] = bam + 1u; }
+    ++nacc;
+  }
+  if (WANT_PAIRS) *npairs = nacc;
+  return P;
+}
 
 template <int L, bool WANT_PAIRS>
 PF_HD float pf_score(const pf_f2* __restrict__ blobs, int D, const float* u, const float* v,
@@ -199,36 +311,7 @@ PF_HD float pf_score(const pf_f2* __restrict__ blobs, int D, const float* u, con
       if (d2 < m[j]) { m[j] = d2; am[j] = i; }
     }
   }
-  const int steps = D < L ? D : L;   // :2409
-  unsigned used = 0;                 // LEDs already consumed (column set to +inf, :2435)
-  float P = 0.0f;
-  int occ = 1, nacc = 0;
-#pragma unroll
-  for (int k = 0; k < L; ++k) {
-    if (k >= steps) break;
-    int best = -1, bam = 0;
-    float bm = INFINITY;
-#pragma unroll
-    for (int j = 0; j < L; ++j) {
-      bool free_j = !((used >> j) & 1u);
-      if (free_j && (best < 0 || m[j] < bm)) { best = j; bm = m[j]; bam = am[j]; }
-    }
-    const float d = sqrtf(bm);       // :2412
-    if (!(d <= sc.tol_pf)) break;    // :2414 / :2438
-    const float g = (sc.tol - d) * sc.inv_tol;
-    P += (float)L + g * g;           // :2416
-    bool reused = false;             // :2421
-#pragma unroll
-    for (int j = 0; j < L; ++j)
-      if (((used >> j) & 1u) && am[j] == bam) reused = true;
-    if (reused) { P -= (float)(3 * occ); ++occ; }   // :2423-2424
-    if ((sc.dg_mask >> best) & 1u) P -= 2.0f;       // :2431-2432
-    if (WANT_PAIRS) { pairs[2 * nacc] = (unsigned)best + 1u; pairs[2 * nacc + 1] = (unsigned)bam + 1u; }
-    ++nacc;
-    used |= 1u << best;
-  }
-  if (WANT_PAIRS) *npairs = nacc;
-  return P;
+  return pf_greedy<L, WANT_PAIRS>(m, am, D, sc, pairs, npairs);
 }
 
 // ----------------------------------------------------------------------------------------
@@ -253,6 +336,7 @@ struct pf_resample_cfg {
   int N;             // number of strata (global N when sharded)
   double Nd;         // (double)N
   double Sabs;       // (double)|S_fx|
+  double NdS;        // Nd / Sabs (estimate only; the threshold test itself is exact)
   double margin;     // fast-path guard, see pf_count_leq
 };
 
@@ -264,7 +348,8 @@ PF_HD pf_resample_cfg pf_make_resample_cfg(uint32_t x_base, int N, long long S_f
   c.Nd = (double)N;
   long long a = S_fx < 0 ? -S_fx : S_fx;
   c.Sabs = (double)a;
-  c.margin = 8.0 * 2.220446049250313e-16 * c.Nd + 2.0 * c.Nd / (c.Sabs > 0 ? c.Sabs : 1.0) + 1e-12;
+  c.NdS = c.Nd / (c.Sabs > 0 ? c.Sabs : 1.0);
+  c.margin = 8.0 * 2.220446049250313e-16 * c.Nd + 2.0 * c.NdS + 1e-12;
   return c;
 }
 
@@ -292,7 +377,7 @@ PF_HD long long pf_threshold(int k, const pf_resample_cfg& rc, const uint32_t* _
 PF_HD int pf_count_leq(long long m, const pf_resample_cfg& rc, const uint32_t* __restrict__ tab)
 {
   if (m < 0) return 0;
-  double x = (double)m * rc.Nd / rc.Sabs;
+  double x = (double)m * rc.NdS;
   int kf;
   if (!(x < rc.Nd)) kf = rc.N; else kf = (int)x;   // floor, x >= 0
   double frac = x - (double)kf;

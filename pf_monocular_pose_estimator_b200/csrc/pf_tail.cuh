@@ -338,8 +338,10 @@ struct pf_frame_const {
   uint32_t seed_state;                       // minstd_rand0 state after seeding (:476-477, injected seed)
   uint32_t isi;                              // it_since_initialized_
   int32_t D;                                 // numLED = image_points_.size()
-  int32_t pad;
+  uint32_t flags;                            // PF_FC_*
 };
+#define PF_FC_CAM_IDENTITY 1u                /* camMoveInv is exactly I: C*E == E bit for bit, product skipped */
+#define PF_FC_SMALL_ANG 2u                   /* every angle draw of the frame is within +-0.3 rad              */
 
 // ---------------------------------------------------------------------------------------
 // frame constants from tracker inputs (host: pfmpe_update; device: track-mode tail)
@@ -372,6 +374,9 @@ PF_HD void pf_make_frame_const(pf_frame_const& fc, const pf_aff& cur, const pf_a
   fc.seed_state = x ? x : 1u;
   fc.isi = isi;
   fc.D = D;
-  fc.pad = 0;
+  bool ident = true;
+  for (int i = 0; i < 12; ++i) ident = ident && (C.a[i] == ((i == 0 || i == 5 || i == 10) ? 1.0 : 0.0));
+  const double amax = (fabs(alo) > fabs(ahi) ? fabs(alo) : fabs(ahi)) * (1.0 + 0.025 * 7);   // scale <= 1.175 (:563)
+  fc.flags = (ident ? PF_FC_CAM_IDENTITY : 0u) | (amax <= 0.3 ? PF_FC_SMALL_ANG : 0u);
 }
 

@@ -4,10 +4,9 @@
 // pfmpe_optimise_pose / pfmpe_predict_pose use), restructured for one warp:
 //   optimisePose :1805-2009  -> pf_gn_warp: lane q owns correspondence q (projection, residual,
 //                               Jacobian rows); 27 lanes own the unique entries of A = sum J^T J and
-//                               b = sum J^T e; the pivoted LDL^T (Eigen's A.ldlt().solve(b), :1872)
-//                               runs on a 6x6 tile in shared memory with 21 lanes on the lower
-//                               triangle; the triangular solves travel by warp shuffle.
-//   A.inverse() :2004        -> pf_inv6_warp: Gauss-Jordan, lane c holds column c of [A | I].
+//                               b = sum J^T e; the 6x6 SPD solve (Eigen's A.ldlt().solve(b), :1872)
+//                               is done in 3x3 blocks (Schur complement, cofactor inverses).
+//   A.inverse() :2004        -> block inverse from the same factors.
 // (file:line are /root/reference/pf_mpe_lib/src/pose_estimator.cpp)
 // Everything that is O(1) and scalar (exp/log map, pose products) is evaluated redundantly by
 // every lane, so the refined pose is available in registers of all lanes without broadcasts.
@@ -18,17 +17,214 @@
 
 struct pf_tail_smem {
   double J[PF_MAX_LED][14];   // per correspondence: J row 0 (6), J row 1 (6), ex, ey
-  double M[36];               // LDL^T work tile; afterwards the covariance (row-major)
-  double A[36];               // sum J^T J of the last iteration
+  double M[36];               // covariance (row-major) after the solve
+  double A[36];               // sum J^T J of the last iteration (full symmetric)
   double b[6];
-  double dT[6];
-  int perm[6];
-  int pad[2];
+  double pose0[12];           // starting pose (restored if max_itr is hit with a larger error, :1886)
 };
 
 #define PF_FULL 0xFFFFFFFFu
 
 __device__ __forceinline__ double pf_shfl_d(double v, int src) { return __shfl_sync(PF_FULL, v, src); }
+
+// ---- O(1) scalar pieces, evaluated redundantly by every lane ---------------------------------
+// Same functions as pf_exp_map / pf_log_map / pf_predict_pose (pf_tail.cuh), with the divisions
+// of the reference expressions (O/theta*sin, (R-R^T)/f*phi, ...) hoisted into one reciprocal each:
+// results agree to a few ulp; the dependent-latency chain is several times shorter.
+__device__ __forceinline__ pf_aff pf_exp_map_dev(const double* tw)
+{
+  const double wx = tw[3], wy = tw[4], wz = tw[5];
+  const double th2 = wx * wx + wy * wy + wz * wz;
+  double a = 1.0, b = 0.5, c = 1.0 / 6.0;      // R = I + a O + b O^2 ; V = I + b O + c O^2
+  if (th2 < 1e-4) {
+    // Gauss-Newton steps are tiny: Taylor series in theta^2 (next omitted term < 1e-21 relative);
+    // also free of the cancellation in (1 - cos theta) / theta^2 of the closed forms
+    a = 1.0 + th2 * (-1.0 / 6.0 + th2 * (1.0 / 120.0 + th2 * (-1.0 / 5040.0 + th2 * (1.0 / 362880.0))));
+    b = 0.5 + th2 * (-1.0 / 24.0 + th2 * (1.0 / 720.0 + th2 * (-1.0 / 40320.0 + th2 * (1.0 / 3628800.0))));
+    c = 1.0 / 6.0 + th2 * (-1.0 / 120.0 + th2 * (1.0 / 5040.0 + th2 * (-1.0 / 362880.0 + th2 * (1.0 / 39916800.0))));
+  } else {
+    const double theta = sqrt(th2);
+    double st, ct;
+    sincos(theta, &st, &ct);
+    const double it = 1.0 / theta, it2 = it * it;
+    a = st * it; b = (1.0 - ct) * it2; c = (theta - st) * it2 * it;
+  }
+  const double O[9] = {0, -wz, wy, wz, 0, -wx, -wy, wx, 0};
+  double O2[9];
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) O2[3 * i + j] = O[3 * i] * O[j] + O[3 * i + 1] * O[3 + j] + O[3 * i + 2] * O[6 + j];
+  pf_aff T;
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    double V[3];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const double id = i == j ? 1.0 : 0.0;
+      T.a[4 * i + j] = id + a * O[3 * i + j] + b * O2[3 * i + j];
+      V[j] = id + b * O[3 * i + j] + c * O2[3 * i + j];
+    }
+    T.a[4 * i + 3] = V[0] * tw[0] + V[1] * tw[1] + V[2] * tw[2];
+  }
+  return T;
+}
+
+__device__ __forceinline__ void pf_log_map_dev(const pf_aff& T, double* xi)
+{
+  const double* a = T.a;
+  double dev = 0, nrm = 0;
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const double e = a[4 * i + j] - (i == j ? 1.0 : 0.0);
+      dev += e * e;
+      nrm += a[4 * i + j] * a[4 * i + j];
+    }
+  double k = 0.0;                                  // w_hat = (R - R^T) * k,  k = phi / (2 sin phi)
+  if (!(dev <= 1e-20 * (nrm < 3.0 ? nrm : 3.0))) {
+    double c = (a[0] + a[5] + a[10] - 1) / 2;
+    c = c > 1 ? 1 : (c < -1 ? -1 : c);
+    const double phi = acos(c);
+    if (phi != 0) k = phi / (2 * sin(phi));
+  }
+  const double w0 = (a[9] - a[6]) * k, w1 = (a[2] - a[8]) * k, w2 = (a[4] - a[1]) * k;
+  const double wh[9] = {0, -w2, w1, w2, 0, -w0, -w1, w0, 0};
+  const double wn = sqrt(w0 * w0 + w1 * w1 + w2 * w2);
+  const double t[3] = {a[3], a[7], a[11]};
+  const bool t_zero = (t[0] * t[0] + t[1] * t[1] + t[2] * t[2]) <= 0.0;
+  double f = 0.0, h = 0.0, d = 0.0;                // A_inv = d I - h w_hat + f w_hat^2
+  if (!t_zero) {
+    d = 1.0;
+    double sw, cw;
+    sincos(wn, &sw, &cw);
+    if (!(wn == 0 || sw == 0)) { h = 0.5; f = (2 * sw - wn * (1 + cw)) / (2 * wn * wn * sw); }
+  }
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    double r = 0.0;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const double w2ij = wh[3 * i] * wh[j] + wh[3 * i + 1] * wh[3 + j] + wh[3 * i + 2] * wh[6 + j];
+      const double Aij = (i == j ? d : 0.0) - h * wh[3 * i + j] + f * w2ij;
+      r += Aij * t[j];
+    }
+    xi[i] = r;
+  }
+  xi[3] = w0; xi[4] = w1; xi[5] = w2;
+}
+
+__device__ __forceinline__ void pf_predict_pose_dev(const pf_aff& prev, const pf_aff& cur, double t_prev, double t_cur,
+                                                    double t_pred, pf_aff& P, pf_aff& pred)
+{
+  double d[6];
+  pf_log_map_dev(pf_aff_mul(pf_aff_inverse(prev), cur), d);
+#pragma unroll
+  for (int i = 0; i < 6; ++i) d[i] = d[i] / (t_cur - t_prev) * (t_pred - t_cur);
+  P = pf_exp_map_dev(d);
+  pred = pf_aff_mul(cur, P);
+}
+
+// ---- 6x6 SPD system in 3x3 blocks ------------------------------------------------------------
+// A = [P Q; Q^T R] (symmetric positive definite normal matrix of the Gauss-Newton step).
+// inv(P) and inv(S), S = R - Q^T inv(P) Q, by cofactors: two reciprocals on the critical path
+// instead of six pivots (the reference solves with Eigen's pivoted LDL^T, :1872; same solution up
+// to rounding).  Evaluated redundantly by every lane from the shared-memory copy of A.
+struct pf_blk6 { double Pi[6], W[9], Si[6]; };     // symmetric 3x3 stored as 00 01 02 11 12 22
+
+__device__ __forceinline__ void pf_sym3_inv(const double* m, double* o)
+{
+  const double c00 = m[3] * m[5] - m[4] * m[4], c01 = m[2] * m[4] - m[1] * m[5], c02 = m[1] * m[4] - m[2] * m[3];
+  const double id = 1.0 / (m[0] * c00 + m[1] * c01 + m[2] * c02);
+  o[0] = c00 * id; o[1] = c01 * id; o[2] = c02 * id;
+  o[3] = (m[0] * m[5] - m[2] * m[2]) * id; o[4] = (m[1] * m[2] - m[0] * m[4]) * id;
+  o[5] = (m[0] * m[3] - m[1] * m[1]) * id;
+}
+#define PF_S3(m, i, j) ((m)[(i) <= (j) ? ((i) == 0 ? (j) : ((i) == 1 ? 2 + (j) : 5)) : ((j) == 0 ? (i) : ((j) == 1 ? 2 + (i) : 5))])
+
+__device__ __forceinline__ void pf_blk6_factor(const double* A, pf_blk6& f)
+{
+  const double P[6] = {A[0], A[1], A[2], A[7], A[8], A[14]};
+  pf_sym3_inv(P, f.Pi);
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j)   // W = inv(P) Q,  Q(k,j) = A[6k + 3 + j]
+      f.W[3 * i + j] = PF_S3(f.Pi, i, 0) * A[3 + j] + PF_S3(f.Pi, i, 1) * A[9 + j] + PF_S3(f.Pi, i, 2) * A[15 + j];
+  double S[6];
+  int t = 0;
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = i; j < 3; ++j, ++t)   // S = R - Q^T W
+      S[t] = A[6 * (3 + i) + 3 + j] - (A[3 + i] * f.W[j] + A[9 + i] * f.W[3 + j] + A[15 + i] * f.W[6 + j]);
+  pf_sym3_inv(S, f.Si);
+}
+
+__device__ __forceinline__ void pf_blk6_solve(const pf_blk6& f, const double* A, const double* b, double* x)
+{
+  double y1[3], r2[3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) y1[i] = PF_S3(f.Pi, i, 0) * b[0] + PF_S3(f.Pi, i, 1) * b[1] + PF_S3(f.Pi, i, 2) * b[2];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) r2[i] = b[3 + i] - (A[3 + i] * y1[0] + A[9 + i] * y1[1] + A[15 + i] * y1[2]);
+#pragma unroll
+  for (int i = 0; i < 3; ++i) x[3 + i] = PF_S3(f.Si, i, 0) * r2[0] + PF_S3(f.Si, i, 1) * r2[1] + PF_S3(f.Si, i, 2) * r2[2];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) x[i] = y1[i] - (f.W[3 * i] * x[3] + f.W[3 * i + 1] * x[4] + f.W[3 * i + 2] * x[5]);
+}
+
+// inv(A) = [inv(P) + W Si W^T, -W Si; -Si W^T, Si]  -> cov (row-major 6x6)
+__device__ __forceinline__ void pf_blk6_inverse(const pf_blk6& f, double* cov)
+{
+  double WS[9];
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+      WS[3 * i + j] = f.W[3 * i] * PF_S3(f.Si, 0, j) + f.W[3 * i + 1] * PF_S3(f.Si, 1, j) + f.W[3 * i + 2] * PF_S3(f.Si, 2, j);
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      cov[6 * i + j] = PF_S3(f.Pi, i, j) + (WS[3 * i] * f.W[3 * j] + WS[3 * i + 1] * f.W[3 * j + 1] + WS[3 * i + 2] * f.W[3 * j + 2]);
+      cov[6 * i + 3 + j] = -WS[3 * i + j];
+      cov[6 * (3 + j) + i] = -WS[3 * i + j];
+      cov[6 * (3 + i) + 3 + j] = PF_S3(f.Si, i, j);
+    }
+}
+
+// Correspondences of one pose by the whole warp (calculateEstimationProbability :2385-2445 for the
+// winner): lane i scans blobs i, i+32, ...; per LED the (distance, blob index) minimum is combined
+// across lanes on a packed key (squared distances are >= 0, so their bit patterns order like the
+// values; ties go to the smaller blob index as in the per-particle loop).
+template <int L, typename Blob>
+__device__ __forceinline__ float pf_score_warp(const Blob* blobs, int D, const float* u, const float* v,
+                                               const pf_score_cfg& sc, unsigned* pairs, int* npairs, int lane)
+{
+  float m[L];
+  int am[L];
+#pragma unroll
+  for (int j = 0; j < L; ++j) {
+    unsigned long long key = ((unsigned long long)__float_as_uint(INFINITY) << 32);
+    for (int i = lane; i < D; i += 32) {
+      const Blob z = blobs[i];                            // any order: the key carries the blob index
+      const float dx = z.x - u[j], dy = z.y - v[j];
+      const float d2 = fmaf(dy, dy, dx * dx);
+      const unsigned long long k = ((unsigned long long)__float_as_uint(d2) << 32) | (unsigned)z.idx;
+      key = k < key ? k : key;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const unsigned long long t = __shfl_xor_sync(PF_FULL, key, o);
+      key = t < key ? t : key;
+    }
+    m[j] = __uint_as_float((unsigned)(key >> 32));
+    am[j] = (int)(unsigned)(key & 0xFFFFFFFFull);
+  }
+  return pf_greedy<L, true>(m, am, D, sc, pairs, npairs);
+}
 
 // lower-triangle lane map: lane l < 21 -> (i, j), j <= i
 __device__ __forceinline__ void pf_tri_ij(int l, int& i, int& j)
@@ -39,109 +235,20 @@ __device__ __forceinline__ void pf_tri_ij(int l, int& i, int& j)
   j = l - i * (i + 1) / 2;
 }
 
-// Solve A x = b by LDL^T with diagonal pivoting; A (symmetric) in ts.M (full 6x6, overwritten),
-// b in ts.b, x -> ts.dT.  All 32 lanes must call.
-__device__ __forceinline__ void pf_ldlt6_warp(pf_tail_smem& ts, int lane)
-{
-  int ti, tj;
-  pf_tri_ij(lane < 21 ? lane : 0, ti, tj);
-  const bool tri = lane < 21;
-  if (lane < 6) ts.perm[lane] = lane;
-  __syncwarp();
-#pragma unroll
-  for (int k = 0; k < 6; ++k) {
-    int piv = k;
-    double big = fabs(ts.M[7 * k]);
-#pragma unroll
-    for (int t = k + 1; t < 6; ++t) {
-      const double v = fabs(ts.M[7 * t]);
-      if (v > big) { big = v; piv = t; }
-    }
-    if (piv != k) {   // symmetric row/column swap k <-> piv (warp-uniform branch)
-      const int pi = ti == k ? piv : (ti == piv ? k : ti);
-      const int pj = tj == k ? piv : (tj == piv ? k : tj);
-      const double v = tri ? ts.M[6 * pi + pj] : 0.0;
-      __syncwarp();
-      if (tri) { ts.M[6 * ti + tj] = v; ts.M[6 * tj + ti] = v; }
-      if (lane == 0) { const int t = ts.perm[k]; ts.perm[k] = ts.perm[piv]; ts.perm[piv] = t; }
-      __syncwarp();
-    }
-    const double d = ts.M[7 * k];
-    if (d == 0.0) continue;
-    if (tri && tj == k && ti > k) ts.M[6 * ti + k] = ts.M[6 * ti + k] / d;   // L(i,k)
-    __syncwarp();
-    if (tri && tj > k) {   // ti >= tj > k
-      const double v = ts.M[6 * ti + tj] - ts.M[6 * ti + k] * d * ts.M[6 * tj + k];
-      ts.M[6 * ti + tj] = v;
-      ts.M[6 * tj + ti] = v;
-    }
-    __syncwarp();
-  }
-  // L y = P b ; D z = y ; L^T x' = z ; x = P^T x'
-  const int li = lane < 6 ? lane : 0;
-  double y = lane < 6 ? ts.b[ts.perm[li]] : 0.0;
-#pragma unroll
-  for (int k = 0; k < 5; ++k) {
-    const double yk = pf_shfl_d(y, k);
-    if (lane > k && lane < 6) y -= ts.M[6 * li + k] * yk;
-  }
-  if (lane < 6) { const double dd = ts.M[7 * li]; y = dd != 0.0 ? y / dd : 0.0; }
-#pragma unroll
-  for (int k = 5; k >= 1; --k) {
-    const double yk = pf_shfl_d(y, k);
-    if (lane < k) y -= ts.M[6 * k + li] * yk;
-  }
-  if (lane < 6) ts.dT[ts.perm[li]] = y;
-  __syncwarp();
-}
-
-// cov = A^-1 (Gauss-Jordan with partial pivoting on [A | I]); A in ts.A, result -> ts.M row-major.
-__device__ __forceinline__ void pf_inv6_warp(pf_tail_smem& ts, int lane)
-{
-  double col[6];
-#pragma unroll
-  for (int r = 0; r < 6; ++r) col[r] = lane < 6 ? ts.A[6 * r + lane] : ((lane - 6) == r ? 1.0 : 0.0);
-#pragma unroll
-  for (int c = 0; c < 6; ++c) {
-    int piv = c;
-    double big = fabs(col[c]);
-#pragma unroll
-    for (int r = c + 1; r < 6; ++r) {
-      const double v = fabs(col[r]);
-      if (v > big) { big = v; piv = r; }
-    }
-    piv = __shfl_sync(PF_FULL, piv, c);
-#pragma unroll
-    for (int r = c + 1; r < 6; ++r)
-      if (piv == r) { const double t = col[c]; col[c] = col[r]; col[r] = t; }
-    const double s = pf_shfl_d(1.0 / col[c], c);
-    col[c] *= s;
-#pragma unroll
-    for (int r = 0; r < 6; ++r) {
-      if (r == c) continue;
-      const double f = pf_shfl_d(col[r], c);
-      if (f != 0.0) col[r] -= f * col[c];
-    }
-  }
-  __syncwarp();
-  if (lane >= 6 && lane < 12) {
-#pragma unroll
-    for (int r = 0; r < 6; ++r) ts.M[6 * r + (lane - 6)] = col[r];
-  }
-  __syncwarp();
-}
-
 // optimisePose (:1805-2009) by one warp.  K9: row-major K (kernel parameter space); obj: L x 3
 // marker coordinates (shared memory); img: detections of the frame (D x 2 doubles, global);
 // pairs: (LED+1, blob+1) rows in registers.  pose in/out (replicated in every lane).  The
-// covariance is left in ts.M (row-major).  Returns PubData.numIter (-1 when max_itr is hit).
+// covariance (:2004) is left in ts.M (row-major).  Returns PubData.numIter (-1 when max_itr is hit).
 template <int L>
 __device__ __forceinline__ int pf_gn_warp(const double* K9, const double* obj, const double* img, const unsigned* pairs,
                                           int npairs, pf_aff& pose, pf_tail_smem& ts, int lane)
 {
   const double conv = 1e-13;
   const int max_itr = 500;
-  const pf_aff pose0 = pose;
+  if (lane == 0) {
+#pragma unroll
+    for (int i = 0; i < 12; ++i) ts.pose0[i] = pose.a[i];
+  }
   const double fx = K9[0], fy = K9[4];
   // my correspondence
   unsigned led = 0, det = 0;
@@ -178,13 +285,12 @@ __device__ __forceinline__ int pf_gn_warp(const double* K9, const double* obj, c
       const double p0 = K9[0] * x + K9[1] * y + K9[2] * z;     // project2d with the full K (:1017-1034)
       const double p1 = K9[3] * x + K9[4] * y + K9[5] * z;
       const double p2 = K9[6] * x + K9[7] * y + K9[8] * z;
-      const double ex = zx - p0 / p2, ey = zy - p1 / p2;
-      en = sqrt(ex * ex + ey * ey);
-      const double z2 = z * z;
-      Jr[0] = 1 / z * fx;  Jr[1] = 0;           Jr[2] = -x / z2 * fx;
-      Jr[3] = -x * y / z2 * fx;  Jr[4] = (1 + (x * x / z2)) * fx;  Jr[5] = -y / z * fx;
-      Jr[6] = 0;           Jr[7] = 1 / z * fy;  Jr[8] = -y / z2 * fy;
-      Jr[9] = -(1 + y * y / z2) * fy;  Jr[10] = x * y / z2 * fy;   Jr[11] = x / z * fy;
+      const double ip2 = 1.0 / p2, iz = 1.0 / z;
+      const double ex = zx - p0 * ip2, ey = zy - p1 * ip2;
+      if (it == 0 || it + 1 == max_itr) en = sqrt(ex * ex + ey * ey);
+      const double xz = x * iz, yz = y * iz;                    // computeJacobian (:2163-2192)
+      Jr[0] = fx * iz;  Jr[2] = -fx * xz * iz;  Jr[3] = -fx * xz * yz;  Jr[4] = fx * (1.0 + xz * xz);  Jr[5] = -fx * yz;
+      Jr[7] = fy * iz;  Jr[8] = -fy * yz * iz;  Jr[9] = -fy * (1.0 + yz * yz);  Jr[10] = fy * xz * yz;  Jr[11] = fy * xz;
       Jr[12] = ex; Jr[13] = ey;
     }
     if (it == 0) e_first = pf_shfl_d(en, last_active);                 // `=+`: last pair wins (:1859)
@@ -198,22 +304,38 @@ __device__ __forceinline__ int pf_gn_warp(const double* K9, const double* obj, c
       double acc = 0.0;
 #pragma unroll
       for (int q = 0; q < L; ++q) acc += ts.J[q][i0] * ts.J[q][i1] + ts.J[q][i2] * ts.J[q][i3];
-      if (own_A) { ts.A[6 * ti + tj] = acc; ts.A[6 * tj + ti] = acc; ts.M[6 * ti + tj] = acc; ts.M[6 * tj + ti] = acc; }
+      if (own_A) { ts.A[6 * ti + tj] = acc; ts.A[6 * tj + ti] = acc; }
       else ts.b[rb] = acc;
     }
     __syncwarp();
-    pf_ldlt6_warp(ts, lane);
     double dT[6];
-#pragma unroll
-    for (int i = 0; i < 6; ++i) dT[i] = ts.dT[i];
-    pose = pf_aff_mul(pf_exp_map(dT), pose);   // :1876
+    {
+      pf_blk6 f;
+      pf_blk6_factor(ts.A, f);
+      pf_blk6_solve(f, ts.A, ts.b, dT);
+    }
+    pose = pf_aff_mul(pf_exp_map_dev(dT), pose);   // :1876
     double nm = -1;
 #pragma unroll
     for (int i = 0; i < 6; ++i) { const double v = fabs(dT[i]); if (v > nm) nm = v; }
     if (nm <= conv) { reported = it; break; }
-    if (it + 1 == max_itr && e_first < e_last) pose = pose0;   // :1886-1892
+    if (it + 1 == max_itr && e_first < e_last) {   // :1886-1892
+#pragma unroll
+      for (int i = 0; i < 12; ++i) pose.a[i] = ts.pose0[i];
+    }
   }
-  pf_inv6_warp(ts, lane);
+  {
+    pf_blk6 f;
+    pf_blk6_factor(ts.A, f);
+    double cov[36];
+    pf_blk6_inverse(f, cov);
+    __syncwarp();
+    if (lane == 0) {
+#pragma unroll
+      for (int i = 0; i < 36; ++i) ts.M[i] = cov[i];
+    }
+    __syncwarp();
+  }
   return reported;
 }
 

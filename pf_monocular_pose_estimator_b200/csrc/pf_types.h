@@ -4,9 +4,10 @@
 #include <stdint.h>
 #include "pf_tail.cuh"
 
-#define PF_BLOCK 256          /* threads per CTA                                     */
-#define PF_WARPS (PF_BLOCK / 32)
-#define PF_SEARCH_BLOCK 256   /* particles per entry of the coarse offspring index (tile_kend) */
+#define PF_BLOCK 256          /* threads per CTA, batch mode (one CTA per tracker, 3 CTAs / SM)     */
+#define PF_GRID_BLOCK 768     /* threads per CTA, grid mode (one CTA per SM: fewest barrier parties) */
+#define PF_MAX_BLOCK 768
+#define PF_MAX_WARPS (PF_MAX_BLOCK / 32)
 #define PF_MAX_GRID 2048      /* capacity of the per-CTA aggregate array (grid mode)  */
 #define PF_MAX_ITER 80        /* do/while bound, pose_estimator.cpp:616              */
 
@@ -75,15 +76,14 @@ struct pf_kparams {
   int total_frames;               // frames uploaded (track mode)
   int coop;                       // 1: grid-wide cooperation (gridDim.x > 1)
   int want_mean;                  // compute weighted mean / covariance
-  int cta_chunk;                  // particles owned by one CTA (multiple of PF_BLOCK); warp w owns the w-th eighth
+  int cta_chunk;                  // particles owned by one CTA (multiple of 32 * warps per CTA); warp w owns the w-th part
   // particle state
   float4* pose0; float4* pose1;   // [tracker][3 planes][N]
   float*  w;                      // [tracker][N] raw scores of the kept iteration
   int*    kend;                   // [tracker][N] cumulative offspring count K(M_i)
-  int*    idx;                    // [tracker][N] source index of slot n for the current frame
-  int*    tile_kend;              // [tracker][ceil(N / PF_SEARCH_BLOCK)] kend of the last particle of each block
+  int*    idx;                    // [tracker][N] Particle_index of output slot n (:678-681), written by the resampling stage
   pf_cta_agg* cta_agg;            // [PF_MAX_GRID] (grid mode)
-  pf_accum* accum;                // [3] rotating slots (grid mode) + [3].maxkey = next round mod 3
+  pf_accum* accum;                // [3] rotating slots (grid mode); [3]: maxkey = next round mod 3, minkey_inv = barriers done, cntkey = arrival counter
   // per-tracker records
   pf_frame_const* fconst;         // [tracker]
   pf_tracker_state* state;        // [tracker]
@@ -97,6 +97,7 @@ struct pf_kparams {
   const float* obj_f;             // [tracker][PF_MAX_LED*3]
   const double* obj_d;            // [tracker][PF_MAX_LED*3]
   float K9f[9];
+  int kstd;                       // K has the usual zero pattern (pf_k_is_std)
   double K9d[9];
   pf_score_cfg score;
   double min_ang, max_ang, min_tr, max_tr;   // minAngularNoise.. (track mode recomputes the ranges per frame)

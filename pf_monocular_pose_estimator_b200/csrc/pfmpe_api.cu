@@ -46,11 +46,10 @@ struct pfmpe_handle {
   int force_mode = 0;            // 0 auto, 1 batch, 2 grid (cfg.reserved[0])
   int grid_cap = 0;              // cfg.reserved[1]
   int info[4] = {0, 0, PF_BLOCK, 0};
-  int nblk = 0;                  // entries of the coarse offspring index per tracker
   // device
   float4 *pose0 = nullptr, *pose1 = nullptr, *gather_tmp = nullptr;
   float* w = nullptr;
-  int *kend = nullptr, *idx = nullptr, *tile_kend = nullptr, *gather_idx = nullptr;
+  int *kend = nullptr, *idx = nullptr, *gather_idx = nullptr;
   pf_cta_agg* cta_agg = nullptr;
   pf_accum* accum = nullptr;
   unsigned char* inbox = nullptr;       // [fconst x n_trackers | blobs x n_trackers x max_blobs x 2]
@@ -113,7 +112,7 @@ cudaError_t dev_alloc(T** p, size_t n)
 void free_all(pfmpe_handle* h)
 {
   cudaFree(h->pose0); cudaFree(h->pose1); cudaFree(h->gather_tmp); cudaFree(h->w); cudaFree(h->kend);
-  cudaFree(h->idx); cudaFree(h->tile_kend); cudaFree(h->gather_idx); cudaFree(h->cta_agg); cudaFree(h->accum);
+  cudaFree(h->idx); cudaFree(h->gather_idx); cudaFree(h->cta_agg); cudaFree(h->accum);
   cudaFree(h->inbox); cudaFree(h->state); cudaFree(h->result); cudaFree(h->obj_f); cudaFree(h->obj_d);
   cudaFree(h->rng_tab); cudaFree(h->timeline);
   if (h->seq.owned) { cudaFree(h->seq.blobs); cudaFree(h->seq.counts); cudaFree(h->seq.times); cudaFree(h->seq.seeds); }
@@ -134,10 +133,11 @@ void fill_kparams(const pfmpe_handle* h, pf_kparams& p)
   p.D_max = h->cfg.max_blobs;
   p.want_mean = (h->cfg.flags & PFMPE_FLAG_MEAN_COV) ? 1 : 0;
   p.pose0 = h->pose0; p.pose1 = h->pose1; p.w = h->w; p.kend = h->kend; p.idx = h->idx;
-  p.tile_kend = h->tile_kend; p.cta_agg = h->cta_agg; p.accum = h->accum;
+  p.cta_agg = h->cta_agg; p.accum = h->accum;
   p.fconst = h->fconst; p.state = h->state;
   p.obj_f = h->obj_f; p.obj_d = h->obj_d;
   for (int i = 0; i < 9; ++i) { p.K9d[i] = h->K[i]; p.K9f[i] = (float)h->K[i]; }
+  p.kstd = pf_k_is_std(p.K9f) ? 1 : 0;
   p.score.tol = (float)h->prm.back_projection_pixel_tolerance;
   p.score.inv_tol = (float)(1.0 / h->prm.back_projection_pixel_tolerance);
   p.score.tol_pf = (float)h->prm.back_projection_pixel_tolerance_PF;
@@ -173,7 +173,7 @@ int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_f
   const int N = h->cfg.n_particles;
   frames_kernel_t k = kernel_for(h->cfg.n_leds);
   if (!k) return fail(h, PFMPE_ERR_UNSUPPORTED, "n_leds must be 1..8");
-  const size_t smem = (size_t)h->cfg.max_blobs * sizeof(pf_f2);
+  const size_t smem = (size_t)h->cfg.max_blobs * sizeof(pf_blob);
   bool grid_mode;
   if (h->force_mode == 1) grid_mode = false;
   else if (h->force_mode == 2) grid_mode = true;
@@ -196,32 +196,33 @@ int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_f
     p.tracker_base = t0;
     p.cta_chunk = (N + PF_BLOCK - 1) / PF_BLOCK * PF_BLOCK;
     dim3 grid(1, (unsigned)nt, 1);
-    h->info[0] = 1; h->info[1] = nt; h->info[3] = 0;
+    h->info[0] = 1; h->info[1] = nt; h->info[2] = PF_BLOCK; h->info[3] = 0;
     k<<<grid, PF_BLOCK, smem, h->stream>>>(p);
     PF_CUDA(h, cudaGetLastError());
     h->launches += 1;
   } else {
+    const int block = PF_GRID_BLOCK, warps = block / 32;
     int per_sm = 0;
-    PF_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, PF_BLOCK, smem));
+    PF_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, block, smem));
     int cap = per_sm * h->num_sms;
     if (cap < 1) return fail(h, PFMPE_ERR_CUDA, "kernel cannot be made resident");
     if (cap > PF_MAX_GRID) cap = PF_MAX_GRID;
     if (h->grid_cap > 0 && h->grid_cap < cap) cap = h->grid_cap;
-    // contiguous chunk per CTA: a multiple of PF_BLOCK when the filter is large enough to give every
-    // warp full 32-particle steps, else (forced grid mode on a small filter) a multiple of PF_WARPS
+    // contiguous chunk per CTA: a multiple of the block size when the filter is large enough to give
+    // every warp full 32-particle steps, else (forced grid mode on a small filter) a multiple of `warps`
     int chunk = (N + cap - 1) / cap;
-    if (chunk >= PF_BLOCK || h->force_mode != 2) chunk = (chunk + PF_BLOCK - 1) / PF_BLOCK * PF_BLOCK;
-    else chunk = (chunk + PF_WARPS - 1) / PF_WARPS * PF_WARPS;
+    if (chunk >= block || h->force_mode != 2) chunk = (chunk + block - 1) / block * block;
+    else chunk = (chunk + warps - 1) / warps * warps;
     const int G = (N + chunk - 1) / chunk;
     p.cta_chunk = chunk;
     p.coop = G > 1 ? 1 : 0;
-    h->info[0] = G; h->info[1] = 1; h->info[3] = p.coop;
+    h->info[0] = G; h->info[1] = 1; h->info[2] = block; h->info[3] = p.coop;
     for (int t = t0; t < t0 + nt; ++t) {
       p.tracker_base = t;
       void* args[] = {(void*)&p};
       dim3 grid((unsigned)G, 1, 1);
-      if (p.coop) PF_CUDA(h, cudaLaunchCooperativeKernel((const void*)k, grid, dim3(PF_BLOCK), args, smem, h->stream));
-      else { k<<<grid, PF_BLOCK, smem, h->stream>>>(p); PF_CUDA(h, cudaGetLastError()); }
+      if (p.coop) PF_CUDA(h, cudaLaunchCooperativeKernel((const void*)k, grid, dim3(block), args, smem, h->stream));
+      else { k<<<grid, block, smem, h->stream>>>(p); PF_CUDA(h, cudaGetLastError()); }
       h->launches += 1;
     }
   }
@@ -306,8 +307,8 @@ int pfmpe_create(const pfmpe_config* cfg, pfmpe_handle** out)
   if (!cfg || !out) return PFMPE_ERR_INVALID;
   *out = nullptr;
   if (cfg->n_particles < 2 || cfg->n_trackers < 1 || cfg->n_leds < 1 || cfg->n_leds > PFMPE_MAX_LED ||
-      cfg->max_blobs < 1 || cfg->max_blobs > 4096) {
-    g_create_err = "pfmpe_create: n_particles >= 2, n_trackers >= 1, 1 <= n_leds <= 8, 1 <= max_blobs <= 4096";
+      cfg->max_blobs < 1 || cfg->max_blobs > 2048) {
+    g_create_err = "pfmpe_create: n_particles >= 2, n_trackers >= 1, 1 <= n_leds <= 8, 1 <= max_blobs <= 2048";
     return PFMPE_ERR_INVALID;
   }
   int ndev = 0;
@@ -322,7 +323,6 @@ int pfmpe_create(const pfmpe_config* cfg, pfmpe_handle** out)
   h->force_mode = cfg->reserved[0];
   h->grid_cap = cfg->reserved[1];
   const size_t N = (size_t)cfg->n_particles, T = (size_t)cfg->n_trackers;
-  h->nblk = (int)((N + PF_SEARCH_BLOCK - 1) / PF_SEARCH_BLOCK);
   h->particles_set.assign(T, 0);
   h->markers.assign(T * PF_MAX_LED * 3, 0.0);
   h->last_sum_fx.assign(T, 0);
@@ -350,7 +350,6 @@ int pfmpe_create(const pfmpe_config* cfg, pfmpe_handle** out)
   PF_TRY(dev_alloc(&h->kend, T * N));
   PF_TRY(dev_alloc(&h->idx, T * N));
   PF_TRY(dev_alloc(&h->gather_idx, N));
-  PF_TRY(dev_alloc(&h->tile_kend, T * (size_t)h->nblk));
   PF_TRY(dev_alloc(&h->cta_agg, (size_t)PF_MAX_GRID));
   PF_TRY(dev_alloc(&h->accum, 4));
   h->blobs_off = (T * sizeof(pf_frame_const) + 255) / 256 * 256;
@@ -374,13 +373,17 @@ int pfmpe_create(const pfmpe_config* cfg, pfmpe_handle** out)
   PF_TRY(cudaMemset(h->w, 0, T * N * sizeof(float)));
   PF_TRY(cudaMemset(h->kend, 0, T * N * sizeof(int)));
   PF_TRY(cudaMemset(h->idx, 0, T * N * sizeof(int)));
-  PF_TRY(cudaMemset(h->tile_kend, 0, T * (size_t)h->nblk * sizeof(int)));
   PF_TRY(cudaMemset(h->result, 0, T * sizeof(pf_frame_result)));
   std::memset(h->h_state, 0, T * sizeof(pf_tracker_state));
   PF_TRY(cudaMemcpy(h->state, h->h_state, T * sizeof(pf_tracker_state), cudaMemcpyHostToDevice));
   {
     std::vector<uint32_t> tab(1024);
     build_rng_table(tab.data());
+    if (pf_rng_skip(1u, 384, tab.data()) != PF_RNG_A384) {
+      g_create_err = "pfmpe_create: RNG stride constant mismatch";
+      free_all(h); delete h;
+      return PFMPE_ERR_INVALID;
+    }
     PF_TRY(cudaMemcpy(h->rng_tab, tab.data(), 1024 * sizeof(uint32_t), cudaMemcpyHostToDevice));
   }
 #undef PF_TRY
@@ -558,9 +561,8 @@ static int run_gather(pfmpe_handle* h, int tracker)
   const size_t N = (size_t)h->cfg.n_particles;
   const float4* T = (s.src_buf == 0 ? h->pose0 : h->pose1) + (size_t)tracker * 3 * N;
   const int blocks = (int)((N + PF_BLOCK - 1) / PF_BLOCK);
-  pf_gather_kernel<<<blocks, PF_BLOCK, 0, h->stream>>>(T, h->kend + (size_t)tracker * N,
-                                                      h->tile_kend + (size_t)tracker * h->nblk, h->nblk,
-                                                      (int)N, s.src_mode, h->gather_tmp, h->gather_idx);
+  pf_gather_kernel<<<blocks, PF_BLOCK, 0, h->stream>>>(T, h->idx + (size_t)tracker * N, (int)N, s.src_mode,
+                                                      h->gather_tmp, h->gather_idx);
   PF_CUDA(h, cudaGetLastError());
   h->launches += 1;
   PF_CUDA(h, cudaStreamSynchronize(h->stream));

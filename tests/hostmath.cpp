@@ -26,7 +26,8 @@ float score_particle(const pf_pose& T, const float* K9f, const float* obj, const
                      const pf_score_cfg& sc, unsigned* pairs, int* npairs)
 {
   float u[L], v[L];
-  for (int j = 0; j < L; ++j) pf_project(K9f, T, obj[3 * j], obj[3 * j + 1], obj[3 * j + 2], u[j], v[j]);
+  const bool kstd = pf_k_is_std(K9f);
+  for (int j = 0; j < L; ++j) pf_project(K9f, kstd, T, obj[3 * j], obj[3 * j + 1], obj[3 * j + 2], u[j], v[j]);
   return pf_score<L, true>(blobs, D, u, v, sc, pairs, npairs);
 }
 
@@ -58,6 +59,7 @@ int frame(int N, int D, const double* markers, const double* K9, const double* b
 
   auto pass = [&](int it, float& maxw, int& argmax, int& argmin, long long& S) {
     const bool use_cam = fc.isi > 1, use_pred = use_cam && (it % 10) != 0;
+    const bool cam_mul = use_cam && !(fc.flags & PF_FC_CAM_IDENTITY), small_ang = (fc.flags & PF_FC_SMALL_ANG) != 0;
     const float scale = 1.0f + 0.025f * (float)(it / 10);
     const uint64_t step0 = 12ull * (uint64_t)(N - 2) * (uint64_t)it;
     S = 0;
@@ -68,10 +70,10 @@ int frame(int N, int D, const double* markers, const double* K9, const double* b
       else if (n == 1) for (int i = 0; i < 12; ++i) Tn.p[i] = fc.Tpred[i];
       else {
         pf_pose B = Ef[n];
-        if (use_cam) B = pf_affine_mul(Cm, B);
+        if (cam_mul) B = pf_affine_mul(Cm, B);
         if (use_pred) B = pf_affine_mul(B, Pm);
         uint32_t x = pf_rng_skip(fc.seed_state, step0 + 12ull * (uint64_t)(n - 2), tab.data());
-        Tn = pf_propagate(B, x, fc.noise, scale);
+        Tn = pf_propagate(B, x, fc.noise, scale, small_ang);
       }
       T[n] = Tn;
       unsigned pr[2 * PF_MAX_LED]; int np;

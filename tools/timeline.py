@@ -4,7 +4,7 @@ import numpy as np
 sys.path.insert(0, __import__("os").path.dirname(__import__("os").path.dirname(__import__("os").path.abspath(__file__))))
 from pf_monocular_pose_estimator_b200 import capi, scenes as S
 
-NAMES = ["ctx", "blobs", "score(cta0)", "reduce1", "->scan", "scan(cta0)", "reduce2", "result", "tail", "endsync"]
+NAMES = ["ctx", "blobs", "score(cta0)", "reduce1", "->resample", "resample(cta0)", "reduce2", "result", "tail", "endsync"]
 
 
 def run(N, T=1, nout=10, frames=40, mode=0):
@@ -29,7 +29,7 @@ def run(N, T=1, nout=10, frames=40, mode=0):
     d = np.diff(rows[:, :10], axis=1) / 1e3
     print("N=%d T=%d D=%d grid=%s  launch ms p50=%.4f" % (N, T, 5 + nout, h.launch_info(), np.median(ms[5:])))
     print("  stage us (median): " + "  ".join("%s=%.1f" % (NAMES[i + 1], np.median(d[:, i])) for i in range(9)))
-    print("  in-kernel total us: %.1f" % np.median((rows[:, 9] - rows[:, 0]) / 1e3))
+    print("  in-kernel total us: %.1f   GN us: %.1f  predict us: %.1f" % (np.median((rows[:, 9] - rows[:, 0]) / 1e3), np.median((rows[:, 10] - rows[:, 7]) / 1e3), np.median((rows[:, 11] - rows[:, 10]) / 1e3)))
     h.close()
 
 
