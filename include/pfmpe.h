@@ -159,6 +159,12 @@ int pfmpe_track_attach(pfmpe_handle* h, int n_frames, const void* d_image_points
  * stream; pfmpe_sync() or a getter completes it. */
 int pfmpe_track_run(pfmpe_handle* h, int first_frame, int n_frames);
 
+/* Re-run the PF updates (:475-689) of frames that pfmpe_track_run has already processed, reading each
+ * frame's constants (current/predicted pose, predictionMatrix, noise ranges, seed) from the log the tracked
+ * run left in HBM: the hot path alone, chained frame to frame on the device, without the FP64 tail.  After
+ * pfmpe_track_init has restored the same starting particles the results are identical to the tracked run's. */
+int pfmpe_track_replay(pfmpe_handle* h, int first_frame, int n_frames);
+
 typedef struct {
   int32_t status;       /* 0 not run (track lost earlier), 1 accepted, 4 rejected                   */
   float flag_fail;      /* PubData.Flag_Fail: 1, 1.5 (:699) or 4                                    */
@@ -174,6 +180,24 @@ typedef struct {
   uint32_t correspondences[2 * PFMPE_MAX_LED];
   int32_t reserved;
 } pfmpe_track_result;
+/* One tracked frame with HOST buffers: the PF branch of PoseEstimator::estimateBodyPose (:223-733) minus
+ * detection/ROI -- predictPose (host, FP64), PF update (device: detections and poses go host->device, the result
+ * record comes back), optimiseAndUpdatePose + jump check (host, FP64).  The tracked object (previous/current
+ * pose, times, it_since_initialized_) is the one pfmpe_track_init set up; image_points: n x 2 undistorted pixels.
+ * The batch form does the same for every tracker of the handle with one device launch:
+ * image_points [n_trackers][max_blobs][2], counts / seeds [n_trackers]. */
+int pfmpe_track_frame_host(pfmpe_handle* h, int tracker, double time_to_predict, const double* image_points,
+                           int32_t n_image_points, uint32_t seed, pfmpe_track_result* out);
+int pfmpe_track_frame_host_batch(pfmpe_handle* h, double time_to_predict, const double* image_points,
+                                 const int32_t* counts, const uint32_t* seeds, pfmpe_track_result* out);
+
+/* The same per-frame call in a loop over a sequence held in HOST memory (layouts of pfmpe_track_upload; out
+ * [n_trackers][n_frames]); every frame makes its own host->device / device->host round trip and host tail.
+ * frame_seconds (optional, n_frames): wall time of each frame's call. */
+int pfmpe_track_sequence_host(pfmpe_handle* h, int n_frames, const double* times, const double* image_points,
+                              const int32_t* counts, const uint32_t* seeds, pfmpe_track_result* out,
+                              double* frame_seconds);
+
 /* results of frames [first, first+n) of one tracker */
 int pfmpe_track_results(pfmpe_handle* h, int tracker, int first_frame, int n_frames, pfmpe_track_result* out);
 

@@ -22,7 +22,8 @@ EXPORTS = [
     "pfmpe_update", "pfmpe_update_batch",
     "pfmpe_get_particles", "pfmpe_get_weights", "pfmpe_get_resample_indices", "pfmpe_get_resample_counts",
     "pfmpe_optimise_pose", "pfmpe_predict_pose", "pfmpe_exponential_map", "pfmpe_logarithm_map",
-    "pfmpe_track_init", "pfmpe_track_upload", "pfmpe_track_attach", "pfmpe_track_run", "pfmpe_track_results",
+    "pfmpe_track_init", "pfmpe_track_upload", "pfmpe_track_attach", "pfmpe_track_run", "pfmpe_track_replay", "pfmpe_track_results",
+    "pfmpe_track_frame_host", "pfmpe_track_frame_host_batch", "pfmpe_track_sequence_host",
     "pfmpe_set_stream", "pfmpe_sync", "pfmpe_last_launch_ms", "pfmpe_launch_count", "pfmpe_launch_info", "pfmpe_debug_timeline",
 ]
 
@@ -109,7 +110,13 @@ def lib():
         L.pfmpe_track_upload.argtypes = [C.c_void_p, C.c_int, _dp, C.POINTER(C.c_int32), _dp, C.POINTER(C.c_uint32)]
         L.pfmpe_track_attach.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.pfmpe_track_run.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.pfmpe_track_replay.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.pfmpe_track_results.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(TrackResult)]
+        L.pfmpe_track_frame_host.argtypes = [C.c_void_p, C.c_int, C.c_double, _dp, C.c_int32, C.c_uint32, C.POINTER(TrackResult)]
+        L.pfmpe_track_frame_host_batch.argtypes = [C.c_void_p, C.c_double, _dp, C.POINTER(C.c_int32), C.POINTER(C.c_uint32),
+                                                   C.POINTER(TrackResult)]
+        L.pfmpe_track_sequence_host.argtypes = [C.c_void_p, C.c_int, _dp, _dp, C.POINTER(C.c_int32), C.POINTER(C.c_uint32),
+                                                C.POINTER(TrackResult), _dp]
         L.pfmpe_set_stream.argtypes = [C.c_void_p, C.c_void_p]
         L.pfmpe_sync.argtypes = [C.c_void_p]
         L.pfmpe_last_launch_ms.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
@@ -297,9 +304,42 @@ class Handle:
     def track_run(self, first_frame, n_frames):
         self._chk(lib().pfmpe_track_run(self._h, first_frame, n_frames))
 
+    def track_replay(self, first_frame, n_frames):
+        self._chk(lib().pfmpe_track_replay(self._h, first_frame, n_frames))
+
+    def track_frame_host(self, time_to_predict, image_points, seed, tracker=0):
+        """One tracked frame through the per-frame C-ABI call with host buffers (host predictPose / Gauss-Newton)."""
+        ip = _c64(np.asarray(image_points).reshape(-1, 2))
+        r = TrackResult()
+        self._chk(lib().pfmpe_track_frame_host(self._h, tracker, float(time_to_predict), _d(ip), ip.shape[0], int(seed),
+                                              C.byref(r)))
+        return self._unpack_track([r])[0]
+
+    def track_sequence_host(self, times, image_points, counts, seeds):
+        """Per-frame host-buffer tracking of a whole sequence, looped in C (layouts of track_upload).
+        Returns (results[tracker][frame], seconds per frame)."""
+        ip = _c64(image_points)
+        cn = np.ascontiguousarray(counts, dtype=np.int32)
+        tm = _c64(times)
+        sd = np.ascontiguousarray(seeds, dtype=np.uint32)
+        F = tm.shape[0]
+        assert ip.shape == (self.T, F, self.max_blobs, 2) and cn.shape == (self.T, F) and sd.shape == (self.T, F)
+        arr = (TrackResult * (self.T * F))()
+        secs = np.zeros(F)
+        self._chk(lib().pfmpe_track_sequence_host(self._h, F, _d(tm), _d(ip), cn.ctypes.data_as(C.POINTER(C.c_int32)),
+                                                 sd.ctypes.data_as(C.POINTER(C.c_uint32)), arr, _d(secs)))
+        return arr, secs
+
+    def unpack_track(self, arr, tracker, n_frames):
+        return self._unpack_track([arr[tracker * n_frames + f] for f in range(n_frames)])
+
     def track_results(self, first_frame, n_frames, tracker=0):
         arr = (TrackResult * n_frames)()
         self._chk(lib().pfmpe_track_results(self._h, tracker, first_frame, n_frames, arr))
+        return self._unpack_track(arr)
+
+    @staticmethod
+    def _unpack_track(arr):
         out = []
         for r in arr:
             nc = r.n_correspondences

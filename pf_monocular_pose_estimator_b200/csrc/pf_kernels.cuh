@@ -626,7 +626,7 @@ __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, pf_ctx& cx, pf_t
   const int N = p.N;
   const int lane = threadIdx.x & 31;
   const bool writer = blockIdx.x == 0 && lane == 0;
-  pf_frame_result* res = p.result + (p.mode == 1 ? (size_t)trk * p.total_frames + frame : (size_t)trk);
+  pf_frame_result* res = p.result + (p.mode != 0 ? (size_t)trk * p.total_frames + frame : (size_t)trk);
   const int dst_buf = 1 - cx.src_buf;
   const float4* T = (dst_buf == 0 ? p.pose0 : p.pose1) + (size_t)trk * 3 * (size_t)N;
 
@@ -666,12 +666,6 @@ __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, pf_ctx& cx, pf_t
     res->npairs = npairs;
     res->gn_iters = -1;
     res->flag_fail = accept ? 1.0f : 4.0f;
-  }
-  // particle-set bookkeeping for the next frame (kept in shared memory, mirrored by CTA 0)
-  if (lane == 0) {
-    st.t_buf = dst_buf;
-    if (resampled) { st.src_buf = dst_buf; st.src_mode = 1; }
-    st.frames_done += 1;
   }
   __syncwarp();
   pf_stamp(p, 7);
@@ -806,10 +800,20 @@ __global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid
       if (blockIdx.x == 0 && threadIdx.x == 0) p.result[(size_t)trk * p.total_frames + frame].status = 0;
       continue;
     }
+    if (p.mode == 2) {     // replay: the frame's constants were logged by an earlier track-mode run
+      const uint32_t* h32 = reinterpret_cast<const uint32_t*>(p.fc_log + (size_t)trk * p.total_frames + frame);
+      uint32_t* f32 = reinterpret_cast<uint32_t*>(&cx.fc);
+      for (int i = threadIdx.x; i < (int)(sizeof(pf_frame_const) / 4); i += blockDim.x) f32[i] = h32[i];
+      __syncthreads();
+    } else if (p.mode == 1 && p.fc_log && blockIdx.x == 0) {
+      const uint32_t* f32 = reinterpret_cast<const uint32_t*>(&cx.fc);
+      uint32_t* h32 = reinterpret_cast<uint32_t*>(p.fc_log + (size_t)trk * p.total_frames + frame);
+      for (int i = threadIdx.x; i < (int)(sizeof(pf_frame_const) / 4); i += blockDim.x) h32[i] = f32[i];
+    }
     if (threadIdx.x == 0) { cx.src_buf = st.src_buf; cx.src_mode = st.src_mode; }
     const int D = cx.fc.D;
     if (threadIdx.x < 32) {
-      const double* bsrc = p.blobs + ((size_t)trk * (p.mode == 1 ? p.total_frames : 1) + (p.mode == 1 ? frame : 0)) *
+      const double* bsrc = p.blobs + ((size_t)trk * (p.mode != 0 ? p.total_frames : 1) + (p.mode != 0 ? frame : 0)) *
                                          (size_t)p.D_max * 2;
       pf_stage_blobs(bsrc, D, p.score.tol_pf, cx.bt, blobs, threadIdx.x);
     }
@@ -859,6 +863,13 @@ __global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid
       pf_stamp(p, 6);
     }
 
+    // particle-set bookkeeping for the next frame (shared memory copy of every CTA; CTA 0 mirrors it)
+    if (threadIdx.x == 0) {
+      st.t_buf = 1 - cx.src_buf;
+      if (resampled) { st.src_buf = 1 - cx.src_buf; st.src_mode = 1; }
+      st.frames_done += 1;
+    }
+    __syncwarp();
     if (threadIdx.x < 32 && (p.mode == 1 || blockIdx.x == 0))
       pf_frame_tail<L>(p, cx, st, ts, blobs, trk, frame, iters, best_it, highest, kept, accept, resampled, cnt);
     pf_stamp(p, 8);

@@ -70,7 +70,8 @@ struct pf_kparams {
   int n_trackers;
   int tracker_base;               // first tracker handled by blockIdx.y == 0
   int D_max;                      // capacity of the per-frame blob arrays
-  int mode;                       // 0: per-frame (host tail), 1: device-resident tracking (device tail)
+  int mode;                       // 0: per-frame (host tail), 1: device-resident tracking (device tail),
+                                  // 2: replay of a tracked sequence: PF updates only, constants from fc_log
   int n_frames;                   // frames processed by this launch
   int frame0;                     // index of the first frame in the uploaded sequence (track mode)
   int total_frames;               // frames uploaded (track mode)
@@ -86,6 +87,7 @@ struct pf_kparams {
   pf_accum* accum;                // [3] rotating slots (grid mode); [3]: maxkey = next round mod 3, minkey_inv = barriers done, cntkey = arrival counter
   // per-tracker records
   pf_frame_const* fconst;         // [tracker]
+  pf_frame_const* fc_log;         // [tracker][total_frames] constants of every tracked frame (optional)
   pf_tracker_state* state;        // [tracker]
   pf_frame_result* result;        // per-frame mode: [tracker]; track mode: [tracker][total_frames]
   // inputs

@@ -4,6 +4,7 @@
 // needs the device fails with PFMPE_ERR_NO_DEVICE / PFMPE_ERR_CUDA if it is not usable.
 #include <cuda_runtime.h>
 
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -22,10 +23,21 @@ struct TrackSeq {
   double* times = nullptr;
   uint32_t* seeds = nullptr;
   pf_frame_result* result = nullptr;
+  pf_frame_const* fc_log = nullptr;   // constants of every tracked frame (replay)
   int n_frames = 0;
   bool owned = false;
   int next_frame = -1;     // frame whose constants are currently staged in fconst (track mode)
   int last_frame = -1;     // last frame processed by track_run
+  int tracked_upto = -1;   // highest frame whose constants are in fc_log
+};
+
+// host-side tracked object (previous_pose_, current_pose_, their times, it_since_initialized_, covariance)
+struct HostTrack {
+  pf_aff prev, cur;
+  double t_prev = 0, t_cur = 0;
+  uint32_t isi = 0;
+  double cov[36] = {0};
+  bool valid = false;
 };
 
 }  // namespace
@@ -70,6 +82,9 @@ struct pfmpe_handle {
   std::vector<long long> last_sum_fx;
   bool last_was_track = false;
   TrackSeq seq;
+  std::vector<HostTrack> host_trk;   // host mirror of the tracked objects (pfmpe_track_frame_host)
+  std::vector<pfmpe_frame_in> in_scratch;
+  std::vector<pfmpe_frame_out> out_scratch;
   std::string err;
 };
 
@@ -116,7 +131,7 @@ void free_all(pfmpe_handle* h)
   cudaFree(h->inbox); cudaFree(h->state); cudaFree(h->result); cudaFree(h->obj_f); cudaFree(h->obj_d);
   cudaFree(h->rng_tab); cudaFree(h->timeline);
   if (h->seq.owned) { cudaFree(h->seq.blobs); cudaFree(h->seq.counts); cudaFree(h->seq.times); cudaFree(h->seq.seeds); }
-  cudaFree(h->seq.result);
+  cudaFree(h->seq.result); cudaFree(h->seq.fc_log);
   if (h->h_inbox) cudaFreeHost(h->h_inbox);
   if (h->h_result) cudaFreeHost(h->h_result);
   if (h->h_state) cudaFreeHost(h->h_state);
@@ -184,9 +199,9 @@ int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_f
   p.mode = mode;
   p.frame0 = frame0;
   p.n_frames = n_frames;
-  if (mode == 1) {
+  if (mode != 0) {
     p.blobs = h->seq.blobs; p.blob_count = h->seq.counts; p.times = h->seq.times; p.seeds = h->seq.seeds;
-    p.result = h->seq.result; p.total_frames = h->seq.n_frames;
+    p.result = h->seq.result; p.total_frames = h->seq.n_frames; p.fc_log = h->seq.fc_log;
   } else {
     p.blobs = h->blobs; p.result = h->result; p.total_frames = 1;
   }
@@ -326,6 +341,9 @@ int pfmpe_create(const pfmpe_config* cfg, pfmpe_handle** out)
   h->particles_set.assign(T, 0);
   h->markers.assign(T * PF_MAX_LED * 3, 0.0);
   h->last_sum_fx.assign(T, 0);
+  h->host_trk.assign(T, HostTrack());
+  h->in_scratch.resize(T);
+  h->out_scratch.resize(T);
 #define PF_TRY(call)                                                              \
   do {                                                                            \
     cudaError_t e_ = (call);                                                      \
@@ -708,6 +726,11 @@ int pfmpe_track_init(pfmpe_handle* h, int tracker, const double pose0[16], doubl
   PF_CUDA(h, cudaStreamSynchronize(h->stream));
   s = h->h_state[tracker];
   const pf_aff a0 = pf_aff_from_cm16(pose0), a1 = pf_aff_from_cm16(pose1);
+  {
+    HostTrack& ht = h->host_trk[tracker];
+    ht.prev = a0; ht.cur = a1; ht.t_prev = t0; ht.t_cur = t1; ht.isi = 2; ht.valid = true;
+    for (int i = 0; i < 36; ++i) ht.cov[i] = 0.0;
+  }
   for (int i = 0; i < 12; ++i) { s.prev[i] = a0.a[i]; s.cur[i] = a1.a[i]; s.pred[i] = a1.a[i]; }
   s.t_prev = t0; s.t_cur = t1; s.t_pred = t1;
   for (int i = 0; i < 36; ++i) s.cov[i] = 0.0;
@@ -732,7 +755,7 @@ int pfmpe_track_init(pfmpe_handle* h, int tracker, const double pose0[16], doubl
 static int seq_release(pfmpe_handle* h)
 {
   if (h->seq.owned) { cudaFree(h->seq.blobs); cudaFree(h->seq.counts); cudaFree(h->seq.times); cudaFree(h->seq.seeds); }
-  cudaFree(h->seq.result);
+  cudaFree(h->seq.result); cudaFree(h->seq.fc_log);
   h->seq = TrackSeq();
   return PFMPE_OK;
 }
@@ -742,6 +765,8 @@ static int seq_alloc_results(pfmpe_handle* h, int n_frames)
   const size_t n = (size_t)h->cfg.n_trackers * n_frames;
   PF_CUDA(h, dev_alloc(&h->seq.result, n));
   PF_CUDA(h, cudaMemset(h->seq.result, 0, n * sizeof(pf_frame_result)));
+  PF_CUDA(h, dev_alloc(&h->seq.fc_log, n));
+  PF_CUDA(h, cudaMemset(h->seq.fc_log, 0, n * sizeof(pf_frame_const)));
   return PFMPE_OK;
 }
 
@@ -807,6 +832,25 @@ int pfmpe_track_run(pfmpe_handle* h, int first_frame, int n_frames)
   if (rc) return rc;
   h->seq.next_frame = first_frame + n_frames;   // the tail staged the constants of the following frame
   h->seq.last_frame = first_frame + n_frames - 1;
+  if (h->seq.last_frame > h->seq.tracked_upto) h->seq.tracked_upto = h->seq.last_frame;
+  h->last_was_track = true;
+  return PFMPE_OK;
+}
+
+int pfmpe_track_replay(pfmpe_handle* h, int first_frame, int n_frames)
+{
+  if (!h) return PFMPE_ERR_INVALID;
+  int rc = check_ready(h);
+  if (rc) return rc;
+  if (!h->seq.blobs || h->seq.tracked_upto < 0) return fail(h, PFMPE_ERR_STATE, "track_run must have processed the frames before they can be replayed");
+  if (first_frame < 0 || n_frames < 1 || first_frame + n_frames > h->seq.tracked_upto + 1) return fail(h, PFMPE_ERR_INVALID, "frame range was not tracked yet");
+  for (int t = 0; t < h->cfg.n_trackers; ++t)
+    if (!h->particles_set[t]) return fail(h, PFMPE_ERR_STATE, "track_init must be called for every tracker");
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  rc = launch_frames(h, 2, 0, h->cfg.n_trackers, first_frame, n_frames);
+  if (rc) return rc;
+  h->seq.next_frame = -1;                        // fconst no longer holds the constants of a tracked frame
+  h->seq.last_frame = first_frame + n_frames - 1;
   h->last_was_track = true;
   return PFMPE_OK;
 }
@@ -837,6 +881,96 @@ int pfmpe_track_results(pfmpe_handle* h, int tracker, int first_frame, int n_fra
     pf_aff_to_cm16(T, o->winner_pose);
     o->n_correspondences = s.npairs;
     for (int i = 0; i < 2 * PFMPE_MAX_LED; ++i) o->correspondences[i] = s.pairs[i];
+  }
+  return PFMPE_OK;
+}
+
+// ---- per-frame tracking with HOST buffers: the PF branch of estimateBodyPose (:223-733) minus detection/ROI ----
+// tracker i reads image_points + i * stride (doubles), counts[i * cstride], seeds[i * cstride], writes out[i * ostride]
+static int track_frames_host(pfmpe_handle* h, int t0, int nt, double time_to_predict, const double* image_points,
+                             size_t stride, const int32_t* counts, const uint32_t* seeds, size_t cstride,
+                             pfmpe_track_result* out, size_t ostride)
+{
+  for (int i = 0; i < nt; ++i) {
+    HostTrack& ht = h->host_trk[t0 + i];
+    if (!ht.valid) return fail(h, PFMPE_ERR_STATE, "track_init must precede track_frame_host");
+    pfmpe_frame_in& in = h->in_scratch[i];
+    pf_aff P, pred;
+    pf_predict_pose(ht.prev, ht.cur, ht.t_prev, ht.t_cur, time_to_predict, P, pred);   // :234 -> :995-1010
+    in.image_points = image_points + (size_t)i * stride;
+    in.n_image_points = counts[i * cstride];
+    in.it_since_initialized = ht.isi;
+    pf_aff_to_cm16(ht.cur, in.current_pose);
+    pf_aff_to_cm16(pred, in.predicted_pose);
+    pf_aff_to_cm16(P, in.prediction_matrix);
+    pf_aff_to_cm16(pf_aff_identity(), in.cam_move_inv);
+    in.dt = time_to_predict - ht.t_cur;
+    in.seed = seeds[i * cstride];
+    in.reserved = 0;
+  }
+  int rc = run_update(h, t0, nt, h->in_scratch.data(), h->out_scratch.data());
+  if (rc) return rc;
+  for (int i = 0; i < nt; ++i) {
+    HostTrack& ht = h->host_trk[t0 + i];
+    const pfmpe_frame_out& fo = h->out_scratch[i];
+    pfmpe_track_result* o = out + i * ostride;
+    std::memset(o, 0, sizeof *o);
+    o->status = fo.status; o->flag_fail = (float)fo.status; o->iterations = fo.iterations; o->gn_iterations = -1;
+    o->most_likely_pose_idx = fo.most_likely_pose_idx; o->max_count = fo.max_count;
+    o->highest_prob = fo.highest_prob; o->weight_sum = fo.weight_sum;
+    std::memcpy(o->winner_pose, fo.winner_pose, sizeof o->winner_pose);
+    o->n_correspondences = fo.n_correspondences;
+    std::memcpy(o->correspondences, fo.correspondences, sizeof o->correspondences);
+    if (fo.resampled) {
+      pf_aff pose = pf_aff_from_cm16(fo.winner_pose);       // predicted_pose_ = PoseParticle[q] (:687)
+      const pf_aff before = pose;
+      double c[36];
+      o->gn_iterations = pf_optimise_pose(h->K, &h->markers[(size_t)(t0 + i) * PF_MAX_LED * 3], image_points + (size_t)i * stride,
+                                          fo.correspondences, fo.n_correspondences, pose, c);   // :690 -> :1805-2009
+      if (ht.isi < 2) ++ht.isi;                             // :2027-2030
+      ht.prev = ht.cur; ht.cur = pose;                      // updatePose :2013-2014
+      if (time_to_predict - ht.t_cur > 0.001 || time_to_predict < ht.t_cur) { ht.t_prev = ht.t_cur; ht.t_cur = time_to_predict; }
+      for (int r = 0; r < 3; ++r)
+        for (int q = 0; q < 3; ++q)
+          if (fabs(before.a[4 * r + q] - pose.a[4 * r + q]) >= 0.3) o->flag_fail = 1.5f;   // :693-701
+      for (int r = 0; r < 36; ++r) ht.cov[r] = c[r];
+    } else {
+      ht.isi = 0;                                           // :710: the caller must re-initialise
+    }
+    pf_aff_to_cm16(ht.cur, o->pose);
+    for (int r = 0; r < 6; ++r) for (int q = 0; q < 6; ++q) o->cov[r + 6 * q] = ht.cov[6 * r + q];
+  }
+  return PFMPE_OK;
+}
+
+int pfmpe_track_frame_host(pfmpe_handle* h, int tracker, double time_to_predict, const double* image_points,
+                           int32_t n_image_points, uint32_t seed, pfmpe_track_result* out)
+{
+  if (!h || !out || (n_image_points > 0 && !image_points)) return PFMPE_ERR_INVALID;
+  if (tracker < 0 || tracker >= h->cfg.n_trackers) return fail(h, PFMPE_ERR_INVALID, "tracker out of range");
+  return track_frames_host(h, tracker, 1, time_to_predict, image_points, 0, &n_image_points, &seed, 0, out, 0);
+}
+
+int pfmpe_track_frame_host_batch(pfmpe_handle* h, double time_to_predict, const double* image_points,
+                                 const int32_t* counts, const uint32_t* seeds, pfmpe_track_result* out)
+{
+  if (!h || !out || !image_points || !counts || !seeds) return PFMPE_ERR_INVALID;
+  return track_frames_host(h, 0, h->cfg.n_trackers, time_to_predict, image_points, (size_t)h->cfg.max_blobs * 2, counts, seeds, 1,
+                           out, 1);
+}
+
+int pfmpe_track_sequence_host(pfmpe_handle* h, int n_frames, const double* times, const double* image_points,
+                              const int32_t* counts, const uint32_t* seeds, pfmpe_track_result* out, double* frame_seconds)
+{
+  if (!h || n_frames < 1 || !times || !image_points || !counts || !seeds || !out) return PFMPE_ERR_INVALID;
+  const int T = h->cfg.n_trackers;
+  const size_t D2 = (size_t)h->cfg.max_blobs * 2;
+  for (int f = 0; f < n_frames; ++f) {
+    const auto a = std::chrono::steady_clock::now();
+    const int rc = track_frames_host(h, 0, T, times[f], image_points + (size_t)f * D2, (size_t)n_frames * D2, counts + f, seeds + f,
+                                     (size_t)n_frames, out + f, (size_t)n_frames);
+    if (rc) return rc;
+    if (frame_seconds) frame_seconds[f] = std::chrono::duration<double>(std::chrono::steady_clock::now() - a).count();
   }
   return PFMPE_OK;
 }

@@ -75,6 +75,71 @@ def test_track_mode_batch_of_trackers_follows_truth_and_oracle():
     h.close()
 
 
+@pytest.mark.parametrize("N,T,mode", [(3000, 1, 2), (512, 4, 0)])
+def test_replay_reproduces_tracked_pf_updates(N, T, mode):
+    """pfmpe_track_replay: PF updates alone (no FP64 tail), constants from the tracked run's log -> same
+    winners, counts, correspondences and particle sets as the tracked run."""
+    F = 10
+    scenes = [S.Scene(tracker=t) for t in range(T)]
+    h = capi.Handle(N, n_trackers=T, max_blobs=16, force_mode=mode)
+    h.configure(scenes[0].markers, scenes[0].K, scenes[0].params)
+    with pytest.raises(capi.PfmpeError):
+        h.track_replay(0, 1)
+    _upload(h, scenes, 2, F, 16)
+    for t, sc in enumerate(scenes):
+        h.track_init(sc.pose(0), sc.time(0), sc.pose(1), sc.time(1), tracker=t)
+    h.track_run(0, F)
+    ref = [h.track_results(0, F, tracker=t) for t in range(T)]
+    pr = [h.particles(1, tracker=t) for t in range(T)]
+    for t, sc in enumerate(scenes):
+        h.track_init(sc.pose(0), sc.time(0), sc.pose(1), sc.time(1), tracker=t)
+    h.track_replay(0, 4)
+    h.track_replay(4, F - 4)
+    for t in range(T):
+        got = h.track_results(0, F, tracker=t)
+        for f in range(F):
+            a, b = ref[t][f], got[f]
+            assert b["status"] == a["status"] == 1 and b["iterations"] == a["iterations"]
+            assert b["most_likely_pose_idx"] == a["most_likely_pose_idx"] and b["max_count"] == a["max_count"]
+            assert b["correspondences"].tolist() == a["correspondences"].tolist()
+            assert b["weight_sum"] == a["weight_sum"]
+            np.testing.assert_array_equal(b["winner_pose"], a["winner_pose"])
+        np.testing.assert_array_equal(h.particles(1, tracker=t), pr[t])
+    with pytest.raises(capi.PfmpeError):
+        h.track_replay(F - 1, 2)
+    h.close()
+
+
+def test_track_frame_host_matches_python_host_loop():
+    """pfmpe_track_frame_host / pfmpe_track_sequence_host (C++ host loop around pfmpe_update) against the
+    reference-faithful Python host loop of tests/host_loop.py."""
+    N, F = 400, 8
+    sc = S.Scene()
+    ha = capi.Handle(N, max_blobs=16)
+    ha.configure(sc.markers, sc.K, sc.params)
+    trk = HostTracker(ha, sc)
+    ref = [trk.frame(f) for f in range(2, 2 + F)]
+    hb = capi.Handle(N, max_blobs=16)
+    hb.configure(sc.markers, sc.K, sc.params)
+    hb.track_init(sc.pose(0), sc.time(0), sc.pose(1), sc.time(1))
+    got = [hb.track_frame_host(sc.time(f), sc.blobs(f), sc.seed(f)) for f in range(2, 2 + F // 2)]
+    frames = list(range(2 + F // 2, 2 + F))
+    blobs, counts = S.blob_tensor([sc], frames, d_max=16)
+    arr, secs = hb.track_sequence_host(np.array([sc.time(f) for f in frames]), blobs, counts,
+                                       np.array([[sc.seed(f) for f in frames]], dtype=np.uint32))
+    got += hb.unpack_track(arr, 0, len(frames))
+    assert (secs > 0).all()
+    for a, b in zip(ref, got):
+        assert b["status"] == a["status"] == 1 and b["iterations"] == a["iterations"]
+        assert b["most_likely_pose_idx"] == a["most_likely_pose_idx"] and b["gn_iterations"] == a["gn_iterations"]
+        assert b["correspondences"].tolist() == a["correspondences"].tolist()
+        np.testing.assert_array_equal(b["pose"], a["pose"])
+        np.testing.assert_array_equal(b["cov"], a["cov"])
+        assert b["flag_fail"] == a["flag_fail"]
+    np.testing.assert_array_equal(hb.particles(0), ha.particles(0))
+    ha.close(); hb.close()
+
+
 def test_track_run_errors():
     sc = S.Scene()
     h = capi.Handle(64, max_blobs=16)
