@@ -1,21 +1,31 @@
 #!/usr/bin/env python
 """bench.py -- particle-marker evaluations/sec (PME/s) of the PF tracking core on B200.
 
-A "step" is one PF frame update (propagate -> project -> score loop, normalise, stratified
-resample, winner, FP64 tail) of the workload's filter(s) on synthetic detections.
+A "step" is one PF frame update -- the do/while of fused propagate -> project -> score passes, the
+exact weight sum, stratified resampling and the most-resampled winner (pose_estimator.cpp:475-689) --
+of the workload's filter(s) on synthetic detections.  PME = particles x LEDs x iterations executed.
 
-  N=1  default workload = BASELINE.json configs[1]: README 5-LED scene, 1e5 particles, one tracker,
-       1000-frame synthetic trajectory ("cfg2").  Other workloads: --workload cfg1|cfg3|cfg4|cfg5s.
-  N>1  default workload = configs[3]: 4096 independent trackers x 4096 particles sharded over the
-       ranks (no data-path collective; torch.distributed/NCCL only for the barrier and the max-time).
+Workloads (BASELINE.json configs):
+  cfg2  configs[1]  README 5-LED scene, 1e5 particles, 1 tracker, 15 blobs, 1000-frame trajectory  [default]
+  cfg1  configs[0]  same scene, 100 particles (the reference's own CPU-runnable case)
+  cfg3  configs[2]  5 LEDs + 200 spurious blobs, 1e6 particles
+  cfg4  configs[3]  4096 independent trackers x 4096 particles, sharded by tracker across the ranks
+  cfg5s configs[4]  single filter with 2^26 particles, on one GPU
+With --gpus N > 1 the default stays cfg2: every rank tracks its own independent sequence (tracker id =
+rank: phase-shifted trajectory, own seeds) -- weak scaling, no data-path collective; torch.distributed
+(NCCL) is used for the barrier and the max-over-ranks time only.  A short cfg4 run is reported alongside
+under "batched_trackers" (strong scaling: 4096 trackers split over the ranks).
 
-value : PME/s with every input resident in HBM when the timed region starts (device-resident
-        tracking, one launch per step, device time from CUDA events on the launching stream).
-e2e   : the same metric through the reference-facing per-frame C-ABI call with HOST buffers: per
-        step the detections / poses go host->device, the result record comes back device->host and
-        the reference's host tail (Gauss-Newton + predictPose, FP64) runs between two updates.
---impl reference : the reference's CPU algorithm (oracle port, see oracle/pf_oracle.h) on the
-        host cores, same workload / metric / unit.
+value : PF updates alone with every input resident in HBM when the timed region starts (detections,
+        per-frame poses/prediction/seeds from the log of an untimed tracked run): one launch per step,
+        device time from CUDA events on the launching stream, L2 flushed between steps when the filter
+        state fits L2.
+e2e   : the same metric through the reference-facing per-frame call with HOST buffers
+        (pfmpe_track_frame_host, looped in C): per step the detections and poses go host->device, the
+        result record comes back device->host, and the reference's FP64 host tail (Gauss-Newton +
+        predictPose) runs between two updates.
+--impl reference : the reference's CPU algorithm (oracle port, see oracle/pf_oracle.h) on the host cores,
+        same workload / metric / unit.
 """
 import argparse
 import json
@@ -38,7 +48,7 @@ WORKLOADS = {
     "cfg1": (100, 1, 10, 1000),
     "cfg2": (100_000, 1, 10, 1000),
     "cfg3": (1_000_000, 1, 200, 200),
-    "cfg4": (4096, 4096, 10, 200),
+    "cfg4": (4096, 4096, 10, 100),
     "cfg5s": (1 << 26, 1, 10, 50),
 }
 WORKLOAD_DESC = {
@@ -48,6 +58,7 @@ WORKLOAD_DESC = {
     "cfg4": "BASELINE configs[3]: 4096 independent trackers x 4096 particles, 15 blobs, sharded by tracker",
     "cfg5s": "BASELINE configs[4] on one GPU: single filter with 2^26 particles",
 }
+STATE_BYTES_PER_PARTICLE = 108
 
 
 def alg_bytes_per_frame(n_particles, iters):
@@ -80,7 +91,7 @@ class ClockSampler:
                     self.rows.append([c.strip() for c in out.split(",")])
             except Exception:
                 pass
-            self._stop.wait(0.2)
+            self._stop.wait(0.1)
 
     def __enter__(self):
         self.th.start()
@@ -115,11 +126,13 @@ def make_sequence(trackers, first_frame, n_frames, n_outliers):
 # ---------------------------------------------------------------------------------------------
 # CPU arm: the oracle port of the reference PF
 # ---------------------------------------------------------------------------------------------
-def cpu_run(workload, budget_s, threads):
-    """Time the reference's CPU algorithm (oracle port) on a bounded sample of the workload."""
+def cpu_run(workload, budget_s, threads, tracker0=0):
+    """Time the reference's CPU algorithm (oracle port) on a bounded sample of the workload: `threads`
+    independent filters (the reference itself is single-threaded), each stepping frames of its own
+    sequence until the time budget is used."""
     from oracle import orc
     n_p, n_t, n_out, _ = WORKLOADS[workload]
-    trackers = np.arange(min(n_t, threads))
+    trackers = np.arange(tracker0, tracker0 + threads)
     max_frames = 400
     frames, blobs, counts, times, seeds = make_sequence(trackers, 2, max_frames, n_out)
     sc0 = S.Scene()
@@ -158,170 +171,143 @@ def cpu_run(workload, budget_s, threads):
     frames_done = sum(r[2] for r in results)
     return dict(value=pme / max(max(r[1] for r in results), 1e-9), cores=len(trackers), frames=frames_done,
                 p50_ms=1e3 * lat[len(lat) // 2], wall_s=wall,
-                sample="%d tracker(s) x %d frames of %s (%d particles each), O(N) resampler, double precision" %
-                       (len(trackers), results[0][2], workload, n_p))
+                sample="%d independent filter(s) (one per host thread) x %d frames of %s (%d particles each), O(N) resampler, "
+                       "double precision" % (len(trackers), results[0][2], workload, n_p))
 
 
 # ---------------------------------------------------------------------------------------------
 # B200 arm
 # ---------------------------------------------------------------------------------------------
-def gpu_run(args, rank, world, local_rank):
+def gpu_measure(workload, trackers, K, W, dev, local_rank, barrier, flush_ok=True, with_track=True, e2e_steps=0, clocks=False):
+    """Measure one workload on this rank's GPU for its local `trackers`.  Returns a dict of raw numbers."""
     import torch
     from pf_monocular_pose_estimator_b200 import capi
-    from tests.host_loop import HostTracker
 
-    workload = args.workload
-    n_p, n_t_total, n_out, _ = WORKLOADS[workload]
-    if n_t_total > 1:
-        assert n_t_total % world == 0
-        n_t = n_t_total // world
-        trackers = np.arange(rank * n_t, (rank + 1) * n_t)
-    else:
-        n_t, trackers = 1, np.array([0])          # replicas only
-    K, W = args.steps, args.warmup
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
+    n_p, _, n_out, _ = WORKLOADS[workload]
+    n_t = len(trackers)
     d_max = L_LED + n_out
-    frames, blobs, counts, times, seeds = make_sequence(trackers, 2, W + K, n_out)
+    F = W + K
+    frames, blobs, counts, times, seeds = make_sequence(trackers, 2, F, n_out)
 
     h = capi.Handle(n_p, n_trackers=n_t, n_leds=L_LED, max_blobs=d_max, device=local_rank)
     h.configure(S.MARKERS_5, S.K_README, S.DEFAULT_PARAMS)
     stream = torch.cuda.current_stream(dev)
     h.set_stream(stream.cuda_stream)
-    for i, t in enumerate(trackers):
-        ph = S.tracker_phase(int(t))
-        h.track_init(S.true_pose(0.0, ph), 0.0, S.true_pose(S.DT, ph), S.DT, tracker=i)
-    # inputs resident in HBM before the timed region
+
+    def init_all():
+        for i, t in enumerate(trackers):
+            ph = S.tracker_phase(int(t))
+            h.track_init(S.true_pose(0.0, ph), 0.0, S.true_pose(S.DT, ph), S.DT, tracker=i)
+
+    # inputs resident in HBM before any timed region
     d_blobs = torch.from_numpy(blobs).to(dev)
     d_counts = torch.from_numpy(counts).to(dev)
     d_times = torch.from_numpy(times).to(dev)
     d_seeds = torch.from_numpy(seeds.view(np.int32)).to(dev)
-    h.track_attach(W + K, d_blobs.data_ptr(), d_counts.data_ptr(), d_times.data_ptr(), d_seeds.data_ptr())
+    h.track_attach(F, d_blobs.data_ptr(), d_counts.data_ptr(), d_times.data_ptr(), d_seeds.data_ptr())
 
-    state_bytes = n_p * n_t * 108
+    state_bytes = n_p * n_t * STATE_BYTES_PER_PARTICLE
     flush = None
     l2_note = "working set %.1f MB > L2 (126 MB): no flush needed" % (state_bytes / 1e6)
-    if state_bytes < 400e6 and not args.no_flush:
+    if state_bytes < 400e6 and flush_ok:
         flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
         l2_note = "L2 flushed (256 MiB write, untimed) between steps; filter state is %.1f MB" % (state_bytes / 1e6)
 
-    def barrier():
-        if world > 1:
-            torch.distributed.barrier()
-        torch.cuda.synchronize(dev)
+    out = dict(n_p=n_p, n_t=n_t, d_max=d_max, l2=l2_note)
 
-    for f in range(W):
+    # ---- (1) device-resident tracking (device FP64 tail), one launch per frame: also logs the per-frame constants
+    init_all()
+    track_ms = []
+    for f in range(F):
         if flush is not None:
             flush.zero_()
         h.track_run(f, 1)
+        if with_track and f >= W:
+            track_ms.append(h.last_launch_ms())
+    h.sync()
+    res = [h.track_results(W, K, tracker=i) for i in range(min(n_t, 16))]
+    iters = np.array([[r["iterations"] for r in rr] for rr in res], dtype=np.float64)
+    out["ok"] = all(r["status"] == 1 for rr in res for r in rr)
+    out["mean_iter"] = float(iters.mean())
+    out["track_ms"] = float(np.sum(track_ms)) if track_ms else None
+    out["track_p50_ms"] = float(np.median(track_ms)) if track_ms else None
+
+    # ---- (2) value: replay of the PF updates alone (hot path), inputs resident, one launch per step
+    init_all()
+    for f in range(W):
+        if flush is not None:
+            flush.zero_()
+        h.track_replay(f, 1)
     barrier()
     launches0 = h.launch_count()
     step_ms = []
-    with ClockSampler(local_rank) as clk:
-        t_wall0 = time.perf_counter()
-        for f in range(W, W + K):
-            if flush is not None:
-                flush.zero_()
-            h.track_run(f, 1)
-            step_ms.append(h.last_launch_ms())      # CUDA events recorded on the launching stream
+    sampler = ClockSampler(local_rank) if clocks else None
+    if sampler:
+        sampler.__enter__()
+    t_wall0 = time.perf_counter()
+    for f in range(W, F):
+        if flush is not None:
+            flush.zero_()
+        h.track_replay(f, 1)
+        step_ms.append(h.last_launch_ms())      # CUDA events recorded on the launching stream
+    barrier()
+    out["wall_s"] = time.perf_counter() - t_wall0
+    if sampler:
+        sampler.__exit__()
+        out["clocks"] = sampler.summary()
+    out["launches"] = h.launch_count() - launches0
+    out["dev_ms"] = float(np.sum(step_ms))
+    out["p50_ms"] = float(np.median(step_ms))
+    res2 = [h.track_results(W, K, tracker=i) for i in range(min(n_t, 16))]
+    out["ok"] = out["ok"] and all(a["most_likely_pose_idx"] == b["most_likely_pose_idx"] and a["iterations"] == b["iterations"]
+                                  for ra, rb in zip(res, res2) for a, b in zip(ra, rb))
+    # iterations of ALL trackers (PME counts what was executed): from the result records
+    if n_t > 16:
+        it_all = np.array([[r["iterations"] for r in h.track_results(W, K, tracker=i)] for i in range(n_t)], dtype=np.float64)
+        out["mean_iter"] = float(it_all.mean())
+        out["max_iter"] = int(it_all.max())
+    out["pme"] = float(n_p) * L_LED * out["mean_iter"] * K * n_t
+    out["alg_bytes"] = float(alg_bytes_per_frame(n_p, out["mean_iter"])) * n_t * K
+    out["launch_info"] = dict(zip(["grid_x", "grid_y", "block", "cooperative"], h.launch_info()))
+
+    # ---- (3) all K frames in ONE persistent launch (state stays in L2 when it fits) -- explanatory only
+    init_all()
+    h.track_replay(0, W)
+    h.sync()
+    h.track_replay(W, K)
+    out["single_ms"] = h.last_launch_ms()
+
+    # ---- (4) e2e: per-frame call with HOST buffers + host FP64 tail, looped in C
+    if e2e_steps > 0:
+        Ke = min(K, e2e_steps)
+        n_te = min(n_t, 256)          # bounded sample of the local trackers for the batched workloads
+        he = h
+        if n_te != n_t:
+            he = capi.Handle(n_p, n_trackers=n_te, n_leds=L_LED, max_blobs=d_max, device=local_rank)
+            he.configure(S.MARKERS_5, S.K_README, S.DEFAULT_PARAMS)
+        for i in range(n_te):
+            ph = S.tracker_phase(int(trackers[i]))
+            he.track_init(S.true_pose(0.0, ph), 0.0, S.true_pose(S.DT, ph), S.DT, tracker=i)
+        he.sync()
+        bl = np.ascontiguousarray(blobs[:n_te])
+        arr, _ = he.track_sequence_host(times[:W], bl[:, :W], counts[:n_te, :W], seeds[:n_te, :W])        # warm-up
         barrier()
-        t_wall = time.perf_counter() - t_wall0
-    launches = h.launch_count() - launches0
-    dev_ms = float(np.sum(step_ms))
-    res = [h.track_results(W, K, tracker=i) for i in range(min(n_t, 8))]
-    iters = np.array([[r["iterations"] for r in rr] for rr in res])
-    ok = all(r["status"] == 1 for rr in res for r in rr)
-    mean_iter = float(iters.mean())
-    pme_rank = float(n_p) * L_LED * mean_iter * K * n_t
-    alg_b = alg_bytes_per_frame(n_p, mean_iter) * n_t * K
-
-    # same sequence, all K frames in ONE launch (state stays in L2 when it fits) -- explanatory only
-    for i, t in enumerate(trackers):
-        ph = S.tracker_phase(int(t))
-        h.track_init(S.true_pose(0.0, ph), 0.0, S.true_pose(S.DT, ph), S.DT, tracker=i)
-    h.track_run(0, W)
-    h.sync()
-    h.track_run(W, K)
-    single_ms = h.last_launch_ms()
-
-    if world > 1:
-        tt = torch.tensor([dev_ms, single_ms, pme_rank, alg_b, float(launches), float(ok)], dtype=torch.float64, device=dev)
-        mx = tt.clone(); torch.distributed.all_reduce(mx, op=torch.distributed.ReduceOp.MAX)
-        sm = tt.clone(); torch.distributed.all_reduce(sm, op=torch.distributed.ReduceOp.SUM)
-        mn = tt.clone(); torch.distributed.all_reduce(mn, op=torch.distributed.ReduceOp.MIN)
-        dev_ms, single_ms = float(mx[0]), float(mx[1])
-        pme_total, alg_total, launches, ok = float(sm[2]), float(sm[3]), int(sm[4]), bool(mn[5] > 0)
-    else:
-        pme_total, alg_total = pme_rank, alg_b
-
-    # ---- e2e: per-frame C-ABI calls with host buffers + host FP64 tail (rank-local trackers: first one only
-    # for multi-tracker workloads would under-count, so e2e uses update_batch over all local trackers)
-    e2e = None
-    if not args.no_e2e:
-        e2e = e2e_run(h, capi, HostTracker, trackers, n_p, n_t, blobs, counts, times, seeds, W, min(K, args.e2e_steps), world, dev)
-
-    peak, peak_src = peaks()
-    achieved = alg_total / (dev_ms * 1e-3) / 1e9 / world      # per-GPU GB/s (max-time rank)
-    line = {
-        "metric": "particle_marker_evals_per_sec", "value": pme_total / (dev_ms * 1e-3), "unit": "PME/s",
-        "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": dev_ms / K, "higher_is_better": True,
-        "scaling": "strong" if n_t_total > 1 else "replicas", "vs_baseline": None, "dtype": "f32",
-        "data": "synthetic",
-        "config": {"workload": workload, "desc": WORKLOAD_DESC[workload], "particles": n_p, "trackers": n_t_total,
-                   "leds": L_LED, "blobs": d_max, "mean_iterations": mean_iter, "l2": l2_note,
-                   "launch": dict(zip(["grid_x", "grid_y", "block", "cooperative"], h.launch_info()))},
-        "latency_p50_ms": float(np.median(step_ms)),
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src,
-                     "alg_bytes_per_particle_frame": alg_bytes_per_frame(1, mean_iter), "kernel": "pf_frames_kernel<5>"},
-        "single_launch": {"value": pme_total / (single_ms * 1e-3), "ms_per_step": single_ms / K,
-                          "note": "all %d frames in one persistent launch, no L2 flush" % K},
-        "gpu_launches": launches, "all_frames_accepted": ok, "wall_s": t_wall, "clocks": clk.summary(),
-    }
-    if e2e is not None:
-        line["e2e"] = e2e
+        t0 = time.perf_counter()
+        arr, secs = he.track_sequence_host(times[W:W + Ke], np.ascontiguousarray(bl[:, W:W + Ke]),
+                                           np.ascontiguousarray(counts[:n_te, W:W + Ke]), np.ascontiguousarray(seeds[:n_te, W:W + Ke]))
+        torch.cuda.synchronize(dev)
+        dt = time.perf_counter() - t0
+        r0 = he.unpack_track(arr, 0, Ke)
+        it_e = np.mean([r["iterations"] for r in r0])
+        out["e2e"] = dict(seconds=dt, pme=float(n_p) * L_LED * it_e * Ke * n_te, steps=Ke, trackers=n_te,
+                          p50_ms=1e3 * float(np.median(secs)), ok=all(r["status"] == 1 for r in r0),
+                          h2d=int((224 + 16 * d_max) * n_te), d2h=int(808 * n_te))
+        if he is not h:
+            he.close()
     h.close()
-    return line
-
-
-def e2e_run(h, capi, HostTracker, trackers, n_p, n_t, blobs, counts, times, seeds, W, K, world, dev):
-    """Per-frame pfmpe_update(_batch) with host buffers + host tail, wall-clock with device syncs."""
-    import torch
-    scs = [S.Scene(tracker=int(t)) for t in trackers]
-    trk = [HostTracker(h, scs[i], tracker=i, init_particles=False) for i in range(n_t)]
-    for i in range(n_t):
-        h.track_init(scs[i].pose(0), scs[i].time(0), scs[i].pose(1), scs[i].time(1), tracker=i)   # particles = pose1
-    h.sync()
-
-    def step(f):
-        for i in range(n_t):
-            trk[i].frame(2 + f, img=blobs[i, f, : counts[i, f]], seed=int(seeds[i, f]))
-
-    n_t_run = n_t
-    if n_t > 64:      # per-tracker Python loop: bound the sample, scale the rate
-        n_t_run = 64
-        trk = trk[:n_t_run]
-
-        def step(f):  # noqa: F811
-            for i in range(n_t_run):
-                trk[i].frame(2 + f, img=blobs[i, f, : counts[i, f]], seed=int(seeds[i, f]))
-    for f in range(min(W, 3)):
-        step(f)
-    torch.cuda.synchronize(dev)
-    it_sum, lat = 0, []
-    t0 = time.perf_counter()
-    for f in range(W, W + K):
-        a = time.perf_counter()
-        step(f)
-        lat.append(time.perf_counter() - a)
-    torch.cuda.synchronize(dev)
-    dt = time.perf_counter() - t0
-    pme = float(n_p) * L_LED * K * n_t_run          # iterations == 1 on these sequences (checked in value arm)
-    fc_bytes = 224 + 8 * 2 * blobs.shape[2]
-    val = pme / dt * world * (1.0 if n_t_run == n_t else 1.0)
-    return {"value": val, "unit": "PME/s", "h2d_bytes_per_step": int(fc_bytes * n_t_run), "d2h_bytes_per_step": int(808 * n_t_run),
-            "steps": K, "p50_ms": 1e3 * float(np.median(lat)), "trackers_in_sample": n_t_run,
-            "path": "pfmpe_update per frame (host buffers) + host Gauss-Newton/predictPose, driven from Python ctypes"}
+    del d_blobs, d_counts, d_times, d_seeds, flush
+    torch.cuda.empty_cache()
+    return out
 
 
 def main():
@@ -330,34 +316,39 @@ def main():
     ap.add_argument("--steps", type=int, default=None)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="auto", choices=["auto"] + list(WORKLOADS))
+    ap.add_argument("--workload", default="cfg2", choices=list(WORKLOADS))
     ap.add_argument("--no-flush", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-batched", action="store_true", help="skip the short cfg4 run reported under batched_trackers")
     ap.add_argument("--e2e-steps", type=int, default=300)
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if args.workload == "auto":
-        args.workload = "cfg2" if max(world, args.gpus) == 1 else "cfg4"
     if args.steps is None:
         args.steps = WORKLOADS[args.workload][3]
     args.warmup = max(args.warmup, 3)
+    n_p, n_t_total, n_out, _ = WORKLOADS[args.workload]
+    sharded = n_t_total > 1
+    cfg = {"workload": args.workload, "desc": WORKLOAD_DESC[args.workload], "particles": n_p, "leds": L_LED,
+           "blobs": L_LED + n_out}
+    if sharded:
+        cfg.update(trackers=n_t_total, sharding="%d trackers split evenly over %d rank(s)" % (n_t_total, max(world, args.gpus)))
+    else:
+        cfg.update(trackers=max(world, args.gpus),
+                   sharding="one independent filter + sequence per rank (tracker id = rank), no data-path collective")
 
     if args.impl == "reference":
         if rank != 0:
             return
         threads = os.cpu_count() or 1
         r = cpu_run(args.workload, budget_s=max(10.0, min(60.0, 0.05 * args.steps)), threads=threads)
-        n_p, n_t, n_out, _ = WORKLOADS[args.workload]
         line = {"impl": "reference", "metric": "particle_marker_evals_per_sec", "value": r["value"], "unit": "PME/s",
                 "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["p50_ms"],
-                "higher_is_better": True, "scaling": "strong" if n_t > 1 else "replicas", "vs_baseline": None,
-                "dtype": "f64", "data": "synthetic",
-                "config": {"workload": args.workload, "desc": WORKLOAD_DESC[args.workload], "particles": n_p, "trackers": n_t,
-                           "leds": L_LED, "blobs": L_LED + n_out},
+                "higher_is_better": True, "scaling": "strong" if sharded else "weak", "vs_baseline": None,
+                "dtype": "f64", "data": "synthetic", "config": cfg,
                 "cpu_baseline": {"value": r["value"], "unit": "PME/s", "cores": r["cores"], "kind": "port", "sample": r["sample"]},
                 "e2e": {"value": r["value"], "unit": "PME/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "note": "the reference cannot be compiled here (Eigen/OpenCV/ROS absent): oracle port of pose_estimator.cpp:475-733 "
@@ -365,12 +356,82 @@ def main():
         print(json.dumps(line))
         return
 
+    import torch
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
     if world > 1:
-        import torch
         import torch.distributed as dist
-        torch.cuda.set_device(local_rank)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    line = gpu_run(args, rank, world, local_rank)
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize(dev)
+
+    def allreduce(vals, op):
+        if world == 1:
+            return [float(v) for v in vals]
+        t = torch.tensor([float(v) for v in vals], dtype=torch.float64, device=dev)
+        torch.distributed.all_reduce(t, op=op)
+        return [float(x) for x in t]
+
+    if sharded:
+        assert n_t_total % world == 0
+        n_t = n_t_total // world
+        trackers = np.arange(rank * n_t, (rank + 1) * n_t)
+    else:
+        trackers = np.array([rank])
+    K, W = args.steps, args.warmup
+    m = gpu_measure(args.workload, trackers, K, W, dev, local_rank, barrier, flush_ok=not args.no_flush,
+                    e2e_steps=0 if args.no_e2e else args.e2e_steps, clocks=True)
+
+    RO = torch.distributed.ReduceOp if world > 1 else None
+    dev_ms, single_ms, track_ms = allreduce([m["dev_ms"], m["single_ms"], m["track_ms"] or 0.0], RO.MAX if RO else None)
+    pme_total, alg_total, launches = allreduce([m["pme"], m["alg_bytes"], m["launches"]], RO.SUM if RO else None)
+    (ok,) = allreduce([1.0 if m["ok"] else 0.0], RO.MIN if RO else None)
+    peak, peak_src = peaks()
+    achieved = m["alg_bytes"] / (m["dev_ms"] * 1e-3) / 1e9            # this rank's GB/s
+    (achieved_min,) = allreduce([achieved], RO.MIN if RO else None)
+    cfg.update(mean_iterations=m["mean_iter"], l2=m["l2"], launch=m["launch_info"])
+    line = {
+        "metric": "particle_marker_evals_per_sec", "value": pme_total / (dev_ms * 1e-3), "unit": "PME/s",
+        "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": dev_ms / K, "higher_is_better": True,
+        "scaling": "strong" if sharded else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": cfg,
+        "latency_p50_ms": m["p50_ms"],
+        "roofline": {"bound": "hbm", "achieved": achieved_min, "peak": peak, "unit": "GB/s", "frac": achieved_min / peak,
+                     "traffic": None, "peak_source": peak_src,
+                     "alg_bytes_per_particle_frame": alg_bytes_per_frame(1, m["mean_iter"]), "kernel": "pf_frames_kernel<5>",
+                     "note": "per GPU (slowest rank); algorithmic bytes / device time of the PF-update launches"},
+        "single_launch": {"value": pme_total / (single_ms * 1e-3), "ms_per_step": single_ms / K,
+                          "note": "all %d frames in one persistent launch, no L2 flush" % K},
+        "tracking": {"value": pme_total / (track_ms * 1e-3) if track_ms else None, "ms_per_step": track_ms / K if track_ms else None,
+                     "note": "device-resident tracking: PF update + FP64 Gauss-Newton/predictPose tail on the device, one launch per frame"},
+        "gpu_launches": int(launches), "all_frames_accepted": bool(ok > 0), "wall_s": m["wall_s"], "clocks": m.get("clocks"),
+    }
+    if "e2e" in m:
+        e = m["e2e"]
+        (e_sec,) = allreduce([e["seconds"]], RO.MAX if RO else None)
+        (e_pme,) = allreduce([e["pme"]], RO.SUM if RO else None)
+        line["e2e"] = {"value": e_pme / e_sec, "unit": "PME/s", "h2d_bytes_per_step": e["h2d"], "d2h_bytes_per_step": e["d2h"],
+                       "steps": e["steps"], "p50_ms": e["p50_ms"], "trackers_per_rank": e["trackers"], "all_frames_accepted": e["ok"],
+                       "path": "pfmpe_track_frame_host(_batch) per frame: host predictPose -> H2D -> PF update -> D2H -> host "
+                               "Gauss-Newton (FP64), looped in C by pfmpe_track_sequence_host"}
+
+    # ---- BASELINE configs[3] alongside (short): 4096 trackers x 4096 particles split over the ranks
+    if not sharded and not args.no_batched:
+        nt4 = WORKLOADS["cfg4"][1] // world
+        tr4 = np.arange(rank * nt4, (rank + 1) * nt4)
+        K4, W4 = 20, 3
+        b = gpu_measure("cfg4", tr4, K4, W4, dev, local_rank, barrier, flush_ok=False, with_track=True, e2e_steps=0)
+        b_ms, b_tr = allreduce([b["dev_ms"], b["track_ms"] or 0.0], RO.MAX if RO else None)
+        b_pme, b_alg = allreduce([b["pme"], b["alg_bytes"]], RO.SUM if RO else None)
+        line["batched_trackers"] = {
+            "workload": "cfg4", "desc": WORKLOAD_DESC["cfg4"], "scaling": "strong", "value": b_pme / (b_ms * 1e-3), "unit": "PME/s",
+            "ms_per_step": b_ms / K4, "steps": K4, "warmup": W4, "mean_iterations": b["mean_iter"], "max_iterations": b.get("max_iter"),
+            "tracking_ms_per_step": b_tr / K4 if b_tr else None,
+            "roofline_frac": b_alg / world / (b_ms * 1e-3) / 1e9 / peak, "launch": b["launch_info"], "l2": b["l2"]}
+
     if rank == 0:
         if world == 1 and not args.no_cpu:
             r = cpu_run(args.workload, budget_s=args.cpu_budget, threads=1)
@@ -378,9 +439,8 @@ def main():
                                     "p50_ms": r["p50_ms"]}
         print(json.dumps(line))
     if world > 1:
-        import torch.distributed as dist
-        dist.barrier()
-        dist.destroy_process_group()
+        torch.distributed.barrier()
+        torch.distributed.destroy_process_group()
 
 
 if __name__ == "__main__":

@@ -59,10 +59,63 @@ __device__ __forceinline__ pf_red pf_red_identity()
   pf_red r; r.maxkey = 0ull; r.minkey_inv = 0ull; r.cntkey = 0ull; r.sum = 0ll; return r;
 }
 
-// block-wide reduction of pf_red; result valid in every thread.  red_smem: PF_MAX_WARPS entries.
-__device__ __forceinline__ pf_red pf_block_reduce(pf_red v, pf_red* red_smem)
+// Once-per-pass glue below is latency-critical single-warp code: loops are kept rolled (#pragma
+// unroll 1) on purpose -- its cost is instruction fetch (L0 I-cache ~6 KB, L1.5 32 KB), not issue.
+
+// ordered combination of the warp aggregates of this CTA, by one warp; result in lane 0
+__device__ __forceinline__ pf_sm3 pf_warp0_combine_agg(const pf_sm3* warp_agg, int lane)
 {
-#pragma unroll
+  const int nwarps = blockDim.x >> 5;
+  pf_sm3 a = lane < nwarps ? warp_agg[lane] : pf_sm3_identity();
+#pragma unroll 1
+  for (int o = 1; o < 32; o <<= 1) {
+    pf_sm3 t;
+    t.s = __shfl_down_sync(PF_FULL, a.s, o); t.mx = __shfl_down_sync(PF_FULL, a.mx, o); t.mn = __shfl_down_sync(PF_FULL, a.mn, o);
+    if (lane + o < 32) a = pf_sm3_combine(a, t);
+  }
+  return a;
+}
+
+// Grid-wide barrier (grid mode; all CTAs are co-resident: cooperative launch).  One monotonically
+// increasing 64-bit arrival counter that is never reset: barrier number b (counted across
+// launches, kept in pf_bar) completes when the counter reaches (b + 1) * gridDim.x.  Arrival is a
+// release reduction (no return value to wait for), the wait is an acquire poll by one thread.
+struct pf_bar { unsigned long long done; unsigned round; };
+
+// arrive + wait, called by ONE thread after a __syncthreads that follows every thread's writes
+__device__ __forceinline__ void pf_bar_arrive_wait(const pf_kparams& p, const pf_bar& bar)
+{
+  unsigned long long* c = &p.accum[3].cntkey;
+  const unsigned long long target = (bar.done + 1ull) * gridDim.x;
+  asm volatile("red.release.gpu.global.add.u64 [%0], %1;" ::"l"(c), "l"(1ull) : "memory");
+  unsigned long long v;
+  do {
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(c) : "memory");
+  } while (v < target);
+}
+
+__device__ __forceinline__ void pf_grid_barrier(const pf_kparams& p, pf_bar& bar)
+{
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    pf_bar_arrive_wait(p, bar);
+    __threadfence();
+  }
+  __syncthreads();
+  bar.done += 1ull;
+}
+
+// Reduce pf_red over the CTA and (grid mode) over the grid; result valid in every thread.  Two
+// __syncthreads in total: warps -> shared memory -> warp 0 (shuffle reduction; lane 0 publishes the
+// CTA's prefix aggregate, adds the CTA result to the round's slot, passes the grid barrier and reads
+// the slot back: one reader per CTA) -> shared memory -> everyone.
+// Slot rotation: round e uses slot e%3; slot (e+2)%3 (last read before the barrier of round e) is
+// re-zeroed by CTA 0 after the barrier.  red_smem: PF_MAX_WARPS + 1 entries.
+__device__ __noinline__ pf_red pf_grid_reduce(pf_red v, pf_red* red_smem, const pf_kparams& p, pf_bar& bar,
+                                              const pf_sm3* warp_agg)
+{
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll 1
   for (int o = 16; o > 0; o >>= 1) {
     unsigned long long a = __shfl_xor_sync(PF_FULL, v.maxkey, o);
     unsigned long long b = __shfl_xor_sync(PF_FULL, v.minkey_inv, o);
@@ -73,86 +126,50 @@ __device__ __forceinline__ pf_red pf_block_reduce(pf_red v, pf_red* red_smem)
     v.cntkey = c > v.cntkey ? c : v.cntkey;
     v.sum += s;
   }
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  __syncthreads();                       // protect red_smem reuse
   if (lane == 0) red_smem[warp] = v;
   __syncthreads();
-  pf_red r = red_smem[0];
-  const int nwarps = blockDim.x >> 5;
-  for (int i = 1; i < nwarps; ++i) {
-    pf_red t = red_smem[i];
-    r.maxkey = t.maxkey > r.maxkey ? t.maxkey : r.maxkey;
-    r.minkey_inv = t.minkey_inv > r.minkey_inv ? t.minkey_inv : r.minkey_inv;
-    r.cntkey = t.cntkey > r.cntkey ? t.cntkey : r.cntkey;
-    r.sum += t.sum;
-  }
-  return r;
-}
-
-// Grid mode: publish this CTA's prefix aggregate (ordered combination of its warps' aggregates).
-// Call after a __syncthreads that follows the warps' writes to warp_agg.
-__device__ __forceinline__ void pf_publish_cta_agg(const pf_kparams& p, const pf_sm3* warp_agg)
-{
-  if (p.coop && threadIdx.x == 0) {
-    pf_sm3 a = warp_agg[0];
+  if (warp == 0) {
     const int nwarps = blockDim.x >> 5;
-    for (int i = 1; i < nwarps; ++i) a = pf_sm3_combine(a, warp_agg[i]);
-    pf_cta_agg* g = p.cta_agg + blockIdx.x;
-    g->s = a.s; g->mx = a.mx; g->mn = a.mn;
-  }
-}
-
-// Grid-wide barrier (grid mode; all CTAs are co-resident: cooperative launch).  One monotonically
-// increasing 64-bit arrival counter that is never reset: barrier number b (counted across
-// launches, kept in pf_bar) completes when the counter reaches (b + 1) * gridDim.x.  Arrival is a
-// release reduction (no return value to wait for), the wait is an acquire poll by thread 0.
-struct pf_bar { unsigned long long done; unsigned round; };
-
-__device__ __forceinline__ void pf_grid_barrier(const pf_kparams& p, pf_bar& bar)
-{
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    unsigned long long* c = &p.accum[3].cntkey;
-    const unsigned long long target = (bar.done + 1ull) * gridDim.x;
-    asm volatile("red.release.gpu.global.add.u64 [%0], %1;" ::"l"(c), "l"(1ull) : "memory");
-    unsigned long long v;
-    do {
-      asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(c) : "memory");
-    } while (v < target);
-    __threadfence();
-  }
-  __syncthreads();
-  bar.done += 1ull;
-}
-
-// Combine the CTA results of one reduction round across the grid (grid mode) and return the
-// global result to every thread of every CTA.  Slot rotation: round e uses slot e%3; slot
-// (e+2)%3 (last read before the barrier of round e) is re-zeroed by CTA 0 after the barrier.
-__device__ __forceinline__ pf_red pf_grid_reduce(pf_red v, pf_red* red_smem, const pf_kparams& p, pf_bar& bar,
-                                                 const pf_sm3* warp_agg)
-{
-  pf_red r = pf_block_reduce(v, red_smem);
-  if (p.coop) {
-    if (warp_agg) pf_publish_cta_agg(p, warp_agg);
-    pf_accum* slot = p.accum + (bar.round % 3u);
-    if (threadIdx.x == 0) {
-      atomicMax(&slot->maxkey, r.maxkey);
-      atomicMax(&slot->minkey_inv, r.minkey_inv);
-      atomicMax(&slot->cntkey, r.cntkey);
-      atomicAdd((unsigned long long*)&slot->sum, (unsigned long long)r.sum);
+    pf_red r = lane < nwarps ? red_smem[lane] : pf_red_identity();
+#pragma unroll 1
+    for (int o = 16; o > 0; o >>= 1) {
+      unsigned long long a = __shfl_xor_sync(PF_FULL, r.maxkey, o);
+      unsigned long long b = __shfl_xor_sync(PF_FULL, r.minkey_inv, o);
+      unsigned long long c = __shfl_xor_sync(PF_FULL, r.cntkey, o);
+      long long s = __shfl_xor_sync(PF_FULL, r.sum, o);
+      r.maxkey = a > r.maxkey ? a : r.maxkey;
+      r.minkey_inv = b > r.minkey_inv ? b : r.minkey_inv;
+      r.cntkey = c > r.cntkey ? c : r.cntkey;
+      r.sum += s;
     }
-    pf_grid_barrier(p, bar);
-    r.maxkey = *(volatile unsigned long long*)&slot->maxkey;
-    r.minkey_inv = *(volatile unsigned long long*)&slot->minkey_inv;
-    r.cntkey = *(volatile unsigned long long*)&slot->cntkey;
-    r.sum = *(volatile long long*)&slot->sum;
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-      pf_accum* z = p.accum + ((bar.round + 2u) % 3u);
-      z->maxkey = 0ull; z->minkey_inv = 0ull; z->cntkey = 0ull; z->sum = 0ll;
+    if (p.coop) {
+      pf_sm3 agg = pf_sm3_identity();
+      if (warp_agg) agg = pf_warp0_combine_agg(warp_agg, lane);
+      if (lane == 0) {
+        if (warp_agg) { pf_cta_agg* g = p.cta_agg + blockIdx.x; g->s = agg.s; g->mx = agg.mx; g->mn = agg.mn; }
+        pf_accum* slot = p.accum + (bar.round % 3u);
+        atomicMax(&slot->maxkey, r.maxkey);
+        atomicMax(&slot->minkey_inv, r.minkey_inv);
+        atomicMax(&slot->cntkey, r.cntkey);
+        atomicAdd((unsigned long long*)&slot->sum, (unsigned long long)r.sum);
+        pf_bar_arrive_wait(p, bar);
+        r.maxkey = *(volatile const unsigned long long*)&slot->maxkey;
+        r.minkey_inv = *(volatile const unsigned long long*)&slot->minkey_inv;
+        r.cntkey = *(volatile const unsigned long long*)&slot->cntkey;
+        r.sum = *(volatile const long long*)&slot->sum;
+        if (blockIdx.x == 0) {
+          pf_accum* z = p.accum + ((bar.round + 2u) % 3u);
+          z->maxkey = 0ull; z->minkey_inv = 0ull; z->cntkey = 0ull; z->sum = 0ll;
+        }
+        __threadfence();
+      }
     }
+    if (lane == 0) red_smem[PF_MAX_WARPS] = r;
   }
+  __syncthreads();
+  if (p.coop) bar.done += 1ull;
   bar.round += 1u;
-  return r;
+  return red_smem[PF_MAX_WARPS];
 }
 
 __device__ __forceinline__ void pf_stamp(const pf_kparams& p, int slot)
@@ -421,49 +438,72 @@ __device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_c
   return acc;
 }
 
-// Exclusive combination of the aggregates of CTAs 0..b-1 and the combination of all of them
-// (after barrier 1; batch mode: one CTA, the total is the combination of its warps).
-// scr: 2 * PF_MAX_WARPS entries of shared scratch.  Results valid in every thread.
-__device__ __forceinline__ void pf_cta_prefix(const pf_kparams& p, const pf_sm3* warp_agg, pf_sm3* scr, pf_sm3& excl,
-                                              pf_sm3& total)
+// Prefix bookkeeping between the stages (after barrier 1), done by warp 0 and handed to the other
+// warps through shared memory: scr[w] = (exclusive combination of the aggregates of CTAs 0..b-1)
+// (+) (aggregates of warps 0..w-1 of this CTA) = everything before warp w; scr[PF_MAX_WARPS] = the
+// combination of the whole filter.  Ends with a __syncthreads.
+__device__ __noinline__ void pf_cta_prefix(const pf_kparams& p, const pf_sm3* warp_agg, pf_sm3* scr)
 {
   const int nwarps = blockDim.x >> 5;
-  if (!p.coop) {
-    excl = pf_sm3_identity();
-    total = warp_agg[0];
-    for (int i = 1; i < nwarps; ++i) total = pf_sm3_combine(total, warp_agg[i]);
-    return;
-  }
-  const int b = blockIdx.x, G = gridDim.x;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const volatile pf_cta_agg* g = p.cta_agg;
-  const int seg = (G + (int)blockDim.x - 1) / (int)blockDim.x;
-  pf_sm3 v = pf_sm3_identity(), a = pf_sm3_identity();
-  for (int i = threadIdx.x * seg; i < (threadIdx.x + 1) * seg && i < G; ++i) {
-    pf_sm3 t; t.s = g[i].s; t.mx = g[i].mx; t.mn = g[i].mn;
-    if (i < b) v = pf_sm3_combine(v, t);
-    a = pf_sm3_combine(a, t);
-  }
+  if (threadIdx.x < 32) {
+    const int lane = threadIdx.x;
+    pf_sm3 excl = pf_sm3_identity(), total = pf_sm3_identity();
+    if (p.coop) {
+      // lane l owns the contiguous entries [l*seg, (l+1)*seg); loads are issued 4 at a time before use
+      const int b = blockIdx.x, G = gridDim.x;
+      const long long* g = reinterpret_cast<const long long*>(p.cta_agg);
+      const int seg = (G + 31) / 32;
+      const int i1 = (lane + 1) * seg < G ? (lane + 1) * seg : G;
+      pf_sm3 v = pf_sm3_identity(), a = pf_sm3_identity();
+#pragma unroll 1
+      for (int i0 = lane * seg; i0 < i1; i0 += 4) {
+        pf_sm3 t[4];
 #pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    pf_sm3 t, u;
-    t.s = __shfl_down_sync(PF_FULL, v.s, o);
-    t.mx = __shfl_down_sync(PF_FULL, v.mx, o);
-    t.mn = __shfl_down_sync(PF_FULL, v.mn, o);
-    u.s = __shfl_down_sync(PF_FULL, a.s, o);
-    u.mx = __shfl_down_sync(PF_FULL, a.mx, o);
-    u.mn = __shfl_down_sync(PF_FULL, a.mn, o);
-    if (lane + o < 32) { v = pf_sm3_combine(v, t); a = pf_sm3_combine(a, u); }
+        for (int q = 0; q < 4; ++q) {
+          const int i = i0 + q;
+          if (i < i1) { t[q].s = __ldcg(g + 4 * i); t[q].mx = __ldcg(g + 4 * i + 1); t[q].mn = __ldcg(g + 4 * i + 2); }
+          else t[q] = pf_sm3_identity();
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          if (i0 + q < b) v = pf_sm3_combine(v, t[q]);
+          a = pf_sm3_combine(a, t[q]);
+        }
+      }
+#pragma unroll 1
+      for (int o = 1; o < 32; o <<= 1) {
+        pf_sm3 t, u;
+        t.s = __shfl_down_sync(PF_FULL, v.s, o); t.mx = __shfl_down_sync(PF_FULL, v.mx, o); t.mn = __shfl_down_sync(PF_FULL, v.mn, o);
+        u.s = __shfl_down_sync(PF_FULL, a.s, o); u.mx = __shfl_down_sync(PF_FULL, a.mx, o); u.mn = __shfl_down_sync(PF_FULL, a.mn, o);
+        if (lane + o < 32) { v = pf_sm3_combine(v, t); a = pf_sm3_combine(a, u); }
+      }
+      excl.s = pf_shfl_ll(v.s, 0); excl.mx = pf_shfl_ll(v.mx, 0); excl.mn = pf_shfl_ll(v.mn, 0);
+      total.s = pf_shfl_ll(a.s, 0); total.mx = pf_shfl_ll(a.mx, 0); total.mn = pf_shfl_ll(a.mn, 0);
+    }
+    // inclusive ordered scan of this CTA's warp aggregates (nwarps <= 32: one per lane)
+    pf_sm3 w = lane < nwarps ? warp_agg[lane] : pf_sm3_identity();
+#pragma unroll 1
+    for (int o = 1; o < 32; o <<= 1) {
+      pf_sm3 t;
+      t.s = __shfl_up_sync(PF_FULL, w.s, o); t.mx = __shfl_up_sync(PF_FULL, w.mx, o); t.mn = __shfl_up_sync(PF_FULL, w.mn, o);
+      if (lane >= o) w = pf_sm3_combine(t, w);
+    }
+    pf_sm3 we;                                            // exclusive: aggregates of the warps below `lane`
+    we.s = __shfl_up_sync(PF_FULL, w.s, 1); we.mx = __shfl_up_sync(PF_FULL, w.mx, 1); we.mn = __shfl_up_sync(PF_FULL, w.mn, 1);
+    if (lane == 0) we = pf_sm3_identity();
+    if (lane < nwarps) scr[lane] = pf_sm3_combine(excl, we);
+    if (!p.coop) {                                        // one CTA: the total is the combination of its warps
+      total.s = pf_shfl_ll(w.s, 31); total.mx = pf_shfl_ll(w.mx, 31); total.mn = pf_shfl_ll(w.mn, 31);
+    }
+    if (lane == 0) scr[PF_MAX_WARPS] = total;
   }
   __syncthreads();
-  if (lane == 0) { scr[warp] = v; scr[PF_MAX_WARPS + warp] = a; }
-  __syncthreads();
-  excl = scr[0];
-  total = scr[PF_MAX_WARPS];
-  for (int i = 1; i < nwarps; ++i) {
-    excl = pf_sm3_combine(excl, scr[i]);
-    total = pf_sm3_combine(total, scr[PF_MAX_WARPS + i]);
-  }
+}
+
+// one out-of-line copy of K(m) (two FP64 divisions inside): called twice per resampling stage
+__device__ __noinline__ int pf_count_leq_dev(long long m, const pf_resample_cfg& rc, const uint32_t* tab)
+{
+  return pf_count_leq(m, rc, tab);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -490,8 +530,7 @@ struct pf_fill_list {
 };
 
 __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const pf_ctx& cx, const uint32_t* tab, int trk,
-                                                    long long S_fx, int iters_total, const pf_sm3& cta_excl,
-                                                    const pf_sm3& total3, const pf_sm3* warp_agg, pf_fill_list* fl)
+                                                    long long S_fx, int iters_total, const pf_sm3* scr, pf_fill_list* fl)
 {
   const int N = p.N;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -501,12 +540,6 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
   const long long sg = S_fx < 0 ? -1ll : 1ll;
   const uint32_t x_base = pf_rng_skip(cx.fc.seed_state, 12ull * (uint64_t)(N - 2) * (uint64_t)iters_total, tab);
   const pf_resample_cfg rc = pf_make_resample_cfg(x_base, N, S_fx);
-  int ktot;                                               // K(M) of the whole filter
-  {
-    long long ts_, tm_;
-    pf_sm3_select(total3, sg, ts_, tm_);
-    ktot = pf_count_leq(tm_, rc, tab);
-  }
 
   const int wchunk = p.cta_chunk / (int)(blockDim.x >> 5);
   const long long w0l = (long long)blockIdx.x * p.cta_chunk + (long long)warp * wchunk;
@@ -515,11 +548,18 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
 
   pf_red acc = pf_red_identity();
   if (w0 < w1) {
-    pf_sm3 pre3 = cta_excl;
-    for (int i = 0; i < warp; ++i) pre3 = pf_sm3_combine(pre3, warp_agg[i]);
     pf_sm carry;
-    pf_sm3_select(pre3, sg, carry.s, carry.m);
-    int k_carry = pf_count_leq(carry.m, rc, tab);         // K(M) of everything before this warp
+    pf_sm3_select(scr[warp], sg, carry.s, carry.m);
+    // K(M) of everything before this warp and of the whole filter: one evaluation, two half-warps
+    int k_carry, ktot;
+    {
+      long long ts_, tm_;
+      pf_sm3_select(scr[PF_MAX_WARPS], sg, ts_, tm_);
+      const int kk = pf_count_leq_dev(lane < 16 ? carry.m : tm_, rc, tab);
+      k_carry = __shfl_sync(PF_FULL, kk, 0);
+      ktot = __shfl_sync(PF_FULL, kk, 16);
+    }
+    pf_stamp(p, 13);
 
     for (int base = w0; base < w1; base += 32) {
       const int n = base + lane;
@@ -599,6 +639,7 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
       k_carry = __shfl_sync(PF_FULL, ke, 31);
     }
   }
+  pf_stamp(p, 14);
   __syncthreads();
   {
     const int nl = fl->n < PF_FILL_LIST ? fl->n : PF_FILL_LIST;
@@ -763,9 +804,9 @@ __global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid
   __shared__ pf_ctx cx;
   __shared__ pf_tracker_state st;
   __shared__ pf_tail_smem ts;
-  __shared__ pf_red red_smem[PF_MAX_WARPS];
+  __shared__ pf_red red_smem[PF_MAX_WARPS + 1];   // [PF_MAX_WARPS]: grid result broadcast
   __shared__ pf_sm3 warp_agg[PF_MAX_WARPS];
-  __shared__ pf_sm3 scr[2 * PF_MAX_WARPS];
+  __shared__ pf_sm3 scr[PF_MAX_WARPS + 1];
   __shared__ pf_fill_list fill;
   __shared__ uint32_t tab[1024];         // radix-256 power table of the RNG skip-ahead
 
@@ -825,26 +866,25 @@ __global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid
     float highest = 0.0f;
     int best_it = -1, it = 0;
     pf_red kept = pf_red_identity(), last = pf_red_identity();
+    int iters = 0;
+    bool regen = false;                 // extra pass that regenerates the kept iteration (one call site: one copy of the code)
     for (;;) {
-      pf_red r = pf_stage_score<L>(p, cx, blobs, tab, trk, it, warp_agg);
+      pf_red r = pf_stage_score<L>(p, cx, blobs, tab, trk, regen ? best_it : it, warp_agg);
       if (it == 0) pf_stamp(p, 2);
       r = pf_grid_reduce(r, red_smem, p, bar, warp_agg);
       if (it == 0) pf_stamp(p, 3);
+      if (regen) break;                                              // r == kept (same particles, exact sums)
       const float m = pf_unord((unsigned)(r.maxkey >> 32));
       last = r;
       ++it;
       if (m > highest) { highest = m; best_it = it - 1; kept = r; }   // :608-614 (strict >, from 0)
-      if (!(it < PF_MAX_ITER && m < thr_exit)) break;                // :616
-    }
-    const int iters = it;
-    if (best_it < 0) kept = last;                                    // :619: nothing to restore
-    else if (best_it != iters - 1) {
+      if (it < PF_MAX_ITER && m < thr_exit) continue;                // :616
+      iters = it;
+      if (best_it < 0) { kept = last; break; }                       // :619: nothing to restore
+      if (best_it == iters - 1) break;
       // the kept iteration is not the last one: regenerate its particles, weights and prefix
       // aggregates (exact: the RNG is addressed by (iteration, particle))
-      (void)pf_stage_score<L>(p, cx, blobs, tab, trk, best_it, warp_agg);
-      __syncthreads();
-      pf_publish_cta_agg(p, warp_agg);
-      pf_sync_all(p, bar);
+      regen = true;
     }
 
     // ---- accept test (:633) and resampling (:666-682)
@@ -853,11 +893,10 @@ __global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid
     pf_red cnt = pf_red_identity();
     if (resampled) {
       pf_stamp(p, 4);
-      pf_sm3 cta_excl, total3;
-      if (threadIdx.x == 0) fill.n = 0;                  // ordered before its use by the barriers in pf_cta_prefix / below
-      pf_cta_prefix(p, warp_agg, scr, cta_excl, total3);
-      __syncthreads();
-      cnt = pf_stage_resample(p, cx, tab, trk, kept.sum, iters, cta_excl, total3, warp_agg, &fill);
+      if (threadIdx.x == 0) fill.n = 0;                  // ordered before its use by the barrier in pf_cta_prefix
+      pf_cta_prefix(p, warp_agg, scr);
+      pf_stamp(p, 12);
+      cnt = pf_stage_resample(p, cx, tab, trk, kept.sum, iters, scr, &fill);
       pf_stamp(p, 5);
       cnt = pf_grid_reduce(cnt, red_smem, p, bar, nullptr);
       pf_stamp(p, 6);

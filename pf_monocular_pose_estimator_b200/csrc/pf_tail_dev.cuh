@@ -215,7 +215,7 @@ __device__ __forceinline__ float pf_score_warp(const Blob* blobs, int D, const f
       const unsigned long long k = ((unsigned long long)__float_as_uint(d2) << 32) | (unsigned)z.idx;
       key = k < key ? k : key;
     }
-#pragma unroll
+#pragma unroll 1
     for (int o = 16; o > 0; o >>= 1) {
       const unsigned long long t = __shfl_xor_sync(PF_FULL, key, o);
       key = t < key ? t : key;

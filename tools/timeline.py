@@ -30,6 +30,8 @@ def run(N, T=1, nout=10, frames=40, mode=0):
     print("N=%d T=%d D=%d grid=%s  launch ms p50=%.4f" % (N, T, 5 + nout, h.launch_info(), np.median(ms[5:])))
     print("  stage us (median): " + "  ".join("%s=%.1f" % (NAMES[i + 1], np.median(d[:, i])) for i in range(9)))
     print("  in-kernel total us: %.1f   GN us: %.1f  predict us: %.1f" % (np.median((rows[:, 9] - rows[:, 0]) / 1e3), np.median((rows[:, 10] - rows[:, 7]) / 1e3), np.median((rows[:, 11] - rows[:, 10]) / 1e3)))
+    print("  resample detail us: prefix=%.1f  ktot+kcarry=%.1f  walk=%.1f  sync+list=%.1f" % tuple(
+        np.median((rows[:, b] - rows[:, a]) / 1e3) for a, b in ((4, 12), (12, 13), (13, 14), (14, 5))))
     h.close()
 
 
