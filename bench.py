@@ -73,6 +73,15 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def profiled_traffic(workload):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture (or None)."""
+    p = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    try:
+        return float(json.load(open(p))[workload]["dram_bytes_per_launch"])
+    except Exception:
+        return None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled during the timed region."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
@@ -400,7 +409,8 @@ def main():
         "config": cfg,
         "latency_p50_ms": m["p50_ms"],
         "roofline": {"bound": "hbm", "achieved": achieved_min, "peak": peak, "unit": "GB/s", "frac": achieved_min / peak,
-                     "traffic": None, "peak_source": peak_src,
+                     "traffic": profiled_traffic(args.workload), "traffic_unit": "bytes/launch (ncu dram__bytes_read+write, profiles/r01_traffic.json)",
+                     "alg_bytes_per_launch": alg_bytes_per_frame(n_p, m["mean_iter"]) * len(trackers), "peak_source": peak_src,
                      "alg_bytes_per_particle_frame": alg_bytes_per_frame(1, m["mean_iter"]), "kernel": "pf_frames_kernel<5>",
                      "note": "per GPU (slowest rank); algorithmic bytes / device time of the PF-update launches"},
         "single_launch": {"value": pme_total / (single_ms * 1e-3), "ms_per_step": single_ms / K,
