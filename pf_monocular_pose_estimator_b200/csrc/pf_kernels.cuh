@@ -680,14 +680,9 @@ __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, pf_ctx& cx, pf_t
   const pf_pose Tw = pf_load_pose(T, N, q);
   unsigned pairs[2 * L];
   int npairs = 0;
-  {
-    float u[L], v[L];
 #pragma unroll
-    for (int j = 0; j < L; ++j) pf_project(p.K9f, p.kstd != 0, Tw, cx.obj[3 * j], cx.obj[3 * j + 1], cx.obj[3 * j + 2], u[j], v[j]);
-#pragma unroll
-    for (int j = 0; j < 2 * L; ++j) pairs[j] = 0u;
-    (void)pf_score_warp<L>(blobs, cx.fc.D, u, v, p.score, pairs, &npairs, lane);
-  }
+  for (int j = 0; j < 2 * L; ++j) pairs[j] = 0u;
+  (void)pf_score_warp<L>(blobs, cx.fc.D, p.K9f, p.kstd != 0, Tw, cx.obj, p.score, pairs, &npairs, lane);
   if (writer) {
     res->status = accept ? 1 : 4;
     res->iterations = iters;

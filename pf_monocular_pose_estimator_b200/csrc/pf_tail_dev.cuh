@@ -200,17 +200,20 @@ __device__ __forceinline__ void pf_blk6_inverse(const pf_blk6& f, double* cov)
 // across lanes on a packed key (squared distances are >= 0, so their bit patterns order like the
 // values; ties go to the smaller blob index as in the per-particle loop).
 template <int L, typename Blob>
-__device__ __forceinline__ float pf_score_warp(const Blob* blobs, int D, const float* u, const float* v,
-                                               const pf_score_cfg& sc, unsigned* pairs, int* npairs, int lane)
+__device__ __forceinline__ float pf_score_warp(const Blob* blobs, int D, const float* K9f, bool kstd, const pf_pose& T,
+                                               const float* obj, const pf_score_cfg& sc, unsigned* pairs, int* npairs,
+                                               int lane)
 {
-  float m[L];
-  int am[L];
-#pragma unroll
+  // rolled over the LEDs (once-per-frame code: small beats fast); lane j ends up holding LED j's key
+  unsigned long long mine = ((unsigned long long)__float_as_uint(INFINITY) << 32);
+#pragma unroll 1
   for (int j = 0; j < L; ++j) {
+    float u, v;
+    pf_project(K9f, kstd, T, obj[3 * j], obj[3 * j + 1], obj[3 * j + 2], u, v);
     unsigned long long key = ((unsigned long long)__float_as_uint(INFINITY) << 32);
     for (int i = lane; i < D; i += 32) {
       const Blob z = blobs[i];                            // any order: the key carries the blob index
-      const float dx = z.x - u[j], dy = z.y - v[j];
+      const float dx = z.x - u, dy = z.y - v;
       const float d2 = fmaf(dy, dy, dx * dx);
       const unsigned long long k = ((unsigned long long)__float_as_uint(d2) << 32) | (unsigned)z.idx;
       key = k < key ? k : key;
@@ -220,6 +223,13 @@ __device__ __forceinline__ float pf_score_warp(const Blob* blobs, int D, const f
       const unsigned long long t = __shfl_xor_sync(PF_FULL, key, o);
       key = t < key ? t : key;
     }
+    if (lane == j) mine = key;
+  }
+  float m[L];
+  int am[L];
+#pragma unroll
+  for (int j = 0; j < L; ++j) {
+    const unsigned long long key = __shfl_sync(PF_FULL, mine, j);
     m[j] = __uint_as_float((unsigned)(key >> 32));
     am[j] = (int)(unsigned)(key & 0xFFFFFFFFull);
   }
