@@ -201,6 +201,40 @@ int pfmpe_track_sequence_host(pfmpe_handle* h, int n_frames, const double* times
 /* results of frames [first, first+n) of one tracker */
 int pfmpe_track_results(pfmpe_handle* h, int tracker, int first_frame, int n_frames, pfmpe_track_result* out);
 
+/* ---- one filter sharded over several GPUs (BASELINE configs[4]) ----------------------
+ * One handle per rank owns the contiguous global particles [global_offset, global_offset +
+ * n_particles) of ONE filter of n_global particles (n_trackers must be 1).  The reference loop
+ * (pose_estimator.cpp:535-616 do/while, :621-633 sum / accept, :666-686 resampling) is split at its
+ * global reductions; every stage below is one asynchronous launch on the handle's stream and the
+ * exchange steps between them are the caller's (pf_monocular_pose_estimator_b200/sharded.py uses
+ * torch.distributed: all_gather of the partials = the "weight-sum allreduce", all_to_all of rows
+ * = the "global resample").  RNG, thresholds and tie rules use GLOBAL particle / slot numbers, so
+ * the sharded filter reproduces the single-GPU filter bit for bit.
+ *
+ * d_partial points to 8 int64 in DEVICE memory, written by the stage:
+ *   score:    [0] max key ((ordered f32 bits << 32) | ~global index; compare as unsigned: first argmax)
+ *             [1] inverted min key (same rule for the first argmin), [2] sum of the Q.30 weights,
+ *             [3..5] (sum, max prefix, min prefix) aggregate of this shard's weights
+ *   resample: [0] count key ((offspring count << 32) | ~global index: first most-resampled particle)
+ *             [1] first global output slot owned by this shard's sources, [2] one past the last */
+int pfmpe_shard_configure(pfmpe_handle* h, int64_t global_offset, int64_t n_global);
+/* stage the frame (same constants on every rank; pfmpe_frame_in as for pfmpe_update) */
+int pfmpe_shard_begin_frame(pfmpe_handle* h, const pfmpe_frame_in* in);
+/* one propagate/project/score pass: `iteration` of the do/while (:535-606) */
+int pfmpe_shard_score(pfmpe_handle* h, int iteration, void* d_partial);
+/* normalise + stratified resampling (:627-629, :666-682) with the global weight sum, the number of
+ * do/while iterations executed and the ordered aggregates of the lower ranks / of all ranks */
+int pfmpe_shard_resample(pfmpe_handle* h, int64_t sum_fx, int iterations, const int64_t lower[3], const int64_t all[3],
+                         void* d_partial);
+/* rows (12 floats: rows 0..2 of the pose) of the output slots [first_slot, first_slot + count);
+ * first_owned_slot = partial[1] of pfmpe_shard_resample */
+int pfmpe_shard_export(pfmpe_handle* h, int64_t first_owned_slot, int64_t first_slot, int64_t count, void* d_rows);
+/* n_particles rebalanced rows become this shard's particle set for the next frame */
+int pfmpe_shard_import(pfmpe_handle* h, const void* d_rows);
+/* pose + correspondences (:687-691 / :714-716) of the local particle `local_index` of the last pass;
+ * only winner_pose / correspondences / n_correspondences of `out` are meaningful */
+int pfmpe_shard_winner(pfmpe_handle* h, int local_index, pfmpe_frame_out* out);
+
 /* ---- streams / timing ---------------------------------------------------------------------- */
 int pfmpe_set_stream(pfmpe_handle* h, void* cuda_stream); /* use an external cudaStream_t (e.g. torch's) */
 int pfmpe_sync(pfmpe_handle* h);

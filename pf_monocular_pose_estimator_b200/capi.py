@@ -24,6 +24,8 @@ EXPORTS = [
     "pfmpe_optimise_pose", "pfmpe_predict_pose", "pfmpe_exponential_map", "pfmpe_logarithm_map",
     "pfmpe_track_init", "pfmpe_track_upload", "pfmpe_track_attach", "pfmpe_track_run", "pfmpe_track_replay", "pfmpe_track_results",
     "pfmpe_track_frame_host", "pfmpe_track_frame_host_batch", "pfmpe_track_sequence_host",
+    "pfmpe_shard_configure", "pfmpe_shard_begin_frame", "pfmpe_shard_score", "pfmpe_shard_resample",
+    "pfmpe_shard_export", "pfmpe_shard_import", "pfmpe_shard_winner",
     "pfmpe_set_stream", "pfmpe_sync", "pfmpe_last_launch_ms", "pfmpe_launch_count", "pfmpe_launch_info", "pfmpe_debug_timeline",
 ]
 
@@ -117,6 +119,14 @@ def lib():
                                                    C.POINTER(TrackResult)]
         L.pfmpe_track_sequence_host.argtypes = [C.c_void_p, C.c_int, _dp, _dp, C.POINTER(C.c_int32), C.POINTER(C.c_uint32),
                                                 C.POINTER(TrackResult), _dp]
+        _i3 = C.POINTER(C.c_int64)
+        L.pfmpe_shard_configure.argtypes = [C.c_void_p, C.c_int64, C.c_int64]
+        L.pfmpe_shard_begin_frame.argtypes = [C.c_void_p, C.POINTER(FrameIn)]
+        L.pfmpe_shard_score.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.pfmpe_shard_resample.argtypes = [C.c_void_p, C.c_int64, C.c_int, _i3, _i3, C.c_void_p]
+        L.pfmpe_shard_export.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]
+        L.pfmpe_shard_import.argtypes = [C.c_void_p, C.c_void_p]
+        L.pfmpe_shard_winner.argtypes = [C.c_void_p, C.c_int, C.POINTER(FrameOut)]
         L.pfmpe_set_stream.argtypes = [C.c_void_p, C.c_void_p]
         L.pfmpe_sync.argtypes = [C.c_void_p]
         L.pfmpe_last_launch_ms.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
@@ -314,6 +324,33 @@ class Handle:
         self._chk(lib().pfmpe_track_frame_host(self._h, tracker, float(time_to_predict), _d(ip), ip.shape[0], int(seed),
                                               C.byref(r)))
         return self._unpack_track([r])[0]
+
+    # ---- one filter sharded over several handles / GPUs (device pointers are plain ints) ----
+    def shard_configure(self, global_offset, n_global):
+        self._chk(lib().pfmpe_shard_configure(self._h, int(global_offset), int(n_global)))
+
+    def shard_begin_frame(self, frame_in):
+        self._chk(lib().pfmpe_shard_begin_frame(self._h, C.byref(frame_in)))
+
+    def shard_score(self, iteration, d_partial):
+        self._chk(lib().pfmpe_shard_score(self._h, int(iteration), C.c_void_p(int(d_partial))))
+
+    def shard_resample(self, sum_fx, iterations, lower, total, d_partial):
+        lo = (C.c_int64 * 3)(*[int(v) for v in lower])
+        to = (C.c_int64 * 3)(*[int(v) for v in total])
+        self._chk(lib().pfmpe_shard_resample(self._h, int(sum_fx), int(iterations), lo, to, C.c_void_p(int(d_partial))))
+
+    def shard_export(self, first_owned_slot, first_slot, count, d_rows):
+        self._chk(lib().pfmpe_shard_export(self._h, int(first_owned_slot), int(first_slot), int(count),
+                                           C.c_void_p(int(d_rows))))
+
+    def shard_import(self, d_rows):
+        self._chk(lib().pfmpe_shard_import(self._h, C.c_void_p(int(d_rows))))
+
+    def shard_winner(self, local_index):
+        o = FrameOut()
+        self._chk(lib().pfmpe_shard_winner(self._h, int(local_index), C.byref(o)))
+        return unpack_frame_out(o)
 
     def track_sequence_host(self, times, image_points, counts, seeds):
         """Per-frame host-buffer tracking of a whole sequence, looped in C (layouts of track_upload).

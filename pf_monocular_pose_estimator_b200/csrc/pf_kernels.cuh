@@ -365,8 +365,8 @@ __device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_c
   // with one modular multiplication (exponents mod the group order, so n < 2 is harmless).
   uint32_t xs;
   {
-    const uint64_t e0 = (12ull * (uint64_t)(N - 2) * (uint64_t)it) % PF_RNG_ORDER;
-    const uint64_t ee = (e0 + (uint64_t)PF_RNG_ORDER - 24ull + 12ull * (uint64_t)(w0 + lane)) % PF_RNG_ORDER;
+    const uint64_t e0 = (12ull * (uint64_t)(p.N_global - 2) * (uint64_t)it) % PF_RNG_ORDER;
+    const uint64_t ee = (e0 + (uint64_t)PF_RNG_ORDER - 24ull + 12ull * (uint64_t)(p.goff + w0 + lane)) % PF_RNG_ORDER;
     xs = pf_rng_skip_e(cx.fc.seed_state, (uint32_t)ee, tab);
   }
 
@@ -381,10 +381,11 @@ __device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_c
     if (valid) {
       const int s = cx.src_mode == 1 ? idx[n] : n;      // Particle_index of slot n (:678-681), written by stage B
       pf_pose T;
-      if (n == 0) {
+      const int ng = p.goff + n;                        // global particle index (sharded filter: goff > 0)
+      if (ng == 0) {
 #pragma unroll
         for (int i = 0; i < 12; ++i) T.p[i] = cx.fc.Tcur[i];      // :547
-      } else if (n == 1) {
+      } else if (ng == 1) {
 #pragma unroll
         for (int i = 0; i < 12; ++i) T.p[i] = cx.fc.Tpred[i];     // :551
       } else {
@@ -403,8 +404,8 @@ __device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_c
       const float wn = pf_greedy<L, false>(m, am, cx.fc.D, p.score, nullptr, nullptr);
       w[n] = wn;
       const unsigned o = pf_ord(wn);
-      const unsigned long long kmax = ((unsigned long long)o << 32) | (unsigned)(~(unsigned)n);
-      const unsigned long long kmin = ~(((unsigned long long)o << 32) | (unsigned)n);
+      const unsigned long long kmax = ((unsigned long long)o << 32) | (unsigned)(~(unsigned)ng);
+      const unsigned long long kmin = ~(((unsigned long long)o << 32) | (unsigned)ng);
       acc.maxkey = kmax > acc.maxkey ? kmax : acc.maxkey;
       acc.minkey_inv = kmin > acc.minkey_inv ? kmin : acc.minkey_inv;
       e = pf_w_to_fx(wn);
@@ -434,7 +435,13 @@ __device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_c
       carry = pf_sm3_combine(carry, a);
     }
   }
-  if (lane == 0) warp_agg[warp] = carry;
+  if (lane == 0) {
+    warp_agg[warp] = carry;
+    if (p.mode == 3) {   // sharded filter: the resampling stage is a separate launch
+      pf_cta_agg* g = p.warp_agg_g + (size_t)blockIdx.x * PF_MAX_WARPS + warp;
+      g->s = carry.s; g->mx = carry.mx; g->mn = carry.mn;
+    }
+  }
   return acc;
 }
 
@@ -491,10 +498,15 @@ __device__ __noinline__ void pf_cta_prefix(const pf_kparams& p, const pf_sm3* wa
     pf_sm3 we;                                            // exclusive: aggregates of the warps below `lane`
     we.s = __shfl_up_sync(PF_FULL, w.s, 1); we.mx = __shfl_up_sync(PF_FULL, w.mx, 1); we.mn = __shfl_up_sync(PF_FULL, w.mn, 1);
     if (lane == 0) we = pf_sm3_identity();
+    if (p.mode == 4) {   // sharded filter: everything on the lower ranks comes first
+      pf_sm3 re; re.s = p.rank_excl[0]; re.mx = p.rank_excl[1]; re.mn = p.rank_excl[2];
+      excl = pf_sm3_combine(re, excl);
+    }
     if (lane < nwarps) scr[lane] = pf_sm3_combine(excl, we);
     if (!p.coop) {                                        // one CTA: the total is the combination of its warps
       total.s = pf_shfl_ll(w.s, 31); total.mx = pf_shfl_ll(w.mx, 31); total.mn = pf_shfl_ll(w.mn, 31);
     }
+    if (p.mode == 4) { total.s = p.rank_total[0]; total.mx = p.rank_total[1]; total.mn = p.rank_total[2]; }
     if (lane == 0) scr[PF_MAX_WARPS] = total;
   }
   __syncthreads();
@@ -538,8 +550,9 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
   int* kend = p.kend + (size_t)trk * N;
   int* idx = p.idx + (size_t)trk * N;
   const long long sg = S_fx < 0 ? -1ll : 1ll;
-  const uint32_t x_base = pf_rng_skip(cx.fc.seed_state, 12ull * (uint64_t)(N - 2) * (uint64_t)iters_total, tab);
-  const pf_resample_cfg rc = pf_make_resample_cfg(x_base, N, S_fx);
+  const int Ng = p.N_global;
+  const uint32_t x_base = pf_rng_skip(cx.fc.seed_state, 12ull * (uint64_t)(Ng - 2) * (uint64_t)iters_total, tab);
+  const pf_resample_cfg rc = pf_make_resample_cfg(x_base, Ng, S_fx);
 
   const int wchunk = p.cta_chunk / (int)(blockDim.x >> 5);
   const long long w0l = (long long)blockIdx.x * p.cta_chunk + (long long)warp * wchunk;
@@ -551,13 +564,22 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
     pf_sm carry;
     pf_sm3_select(scr[warp], sg, carry.s, carry.m);
     // K(M) of everything before this warp and of the whole filter: one evaluation, two half-warps
-    int k_carry, ktot;
+    int k_carry, ktot, kbase = 0;     // kbase (sharded filter): first global slot owned by this rank's sources
     {
-      long long ts_, tm_;
+      long long ts_, tm_, rs_ = 0, rm_ = PF_SM_NEG;
       pf_sm3_select(scr[PF_MAX_WARPS], sg, ts_, tm_);
-      const int kk = pf_count_leq_dev(lane < 16 ? carry.m : tm_, rc, tab);
+      if (p.mode == 4) {
+        pf_sm3 re; re.s = p.rank_excl[0]; re.mx = p.rank_excl[1]; re.mn = p.rank_excl[2];
+        pf_sm3_select(re, sg, rs_, rm_);
+      }
+      const int kk = pf_count_leq_dev(lane < 11 ? carry.m : (lane < 22 ? tm_ : rm_), rc, tab);
       k_carry = __shfl_sync(PF_FULL, kk, 0);
-      ktot = __shfl_sync(PF_FULL, kk, 16);
+      ktot = __shfl_sync(PF_FULL, kk, 11);
+      if (p.mode == 4) {
+        kbase = __shfl_sync(PF_FULL, kk, 22);
+        kbase = ktot == 0 ? p.goff : (kbase == ktot ? Ng : kbase);
+        if (blockIdx.x == 0 && threadIdx.x == 0) p.shard_partial[1] = kbase;
+      }
     }
     pf_stamp(p, 13);
 
@@ -596,17 +618,19 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
       if (valid) {
         kend[n] = ke;
         const unsigned cnt = (unsigned)(ke - k_prev);
-        const unsigned long long key = ((unsigned long long)cnt << 32) | (unsigned)(~(unsigned)n);
+        const unsigned long long key = ((unsigned long long)cnt << 32) | (unsigned)(~(unsigned)(p.goff + n));
         acc.cntkey = key > acc.cntkey ? key : acc.cntkey;
       }
       // ---- slot fill: the sources of this step own the contiguous slots [E(k_carry), E(ke of lane 31)),
       // E(k) = N if k == K_total (the last source with offspring also owns the not-found tail, Q7)
       if (ktot == 0) {
-        if (valid) idx[n] = n;                            // nothing was ever found: every slot keeps its own particle
+        if (valid) idx[n] = n;                            // nothing was ever found: every slot keeps its own particle (local)
+        if (p.mode == 4 && valid && n == N - 1) p.shard_partial[2] = (long long)p.goff + N;
       } else {
-        const int Ecur = ke == ktot ? N : ke;
-        const int Eprev = k_prev == ktot ? N : k_prev;
+        const int Ecur = (ke == ktot ? Ng : ke) - kbase;
+        const int Eprev = (k_prev == ktot ? Ng : k_prev) - kbase;
         const int own = Ecur - Eprev;                     // invalid lanes repeat the last prefix: 0
+        if (p.mode == 4 && valid && n == N - 1) p.shard_partial[2] = (long long)Ecur + kbase;   // end of this rank's slots
         const unsigned bigm = __ballot_sync(PF_FULL, own > PF_FILL_WARP);
         if (bigm == 0u) {
           const int E0 = __shfl_sync(PF_FULL, Eprev, 0), R = __shfl_sync(PF_FULL, Ecur, 31) - E0;
@@ -619,7 +643,7 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
               const int v = __shfl_sync(PF_FULL, Ecur, mid);
               if (v > k) hi = mid; else lo = mid + 1;
             }
-            if (q0 + lane < R) idx[k] = base + lo;
+            if (q0 + lane < R && k < p.idx_cap) idx[k] = base + lo;
           }
         } else {
           // rare: a source owns more than PF_FILL_WARP slots; hand those to the whole CTA (list) and
@@ -631,7 +655,7 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
             if (slot < PF_FILL_LIST) { fl->start[slot] = Eprev; fl->end[slot] = Ecur; fl->src[slot] = n; }
           }
           if (!isbig || slot >= PF_FILL_LIST)
-            for (int k = Eprev; k < Ecur; ++k) idx[k] = n;
+            for (int k = Eprev; k < Ecur && k < p.idx_cap; ++k) idx[k] = n;
         }
       }
       carry.s += total;
@@ -645,7 +669,7 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
     const int nl = fl->n < PF_FILL_LIST ? fl->n : PF_FILL_LIST;
     for (int q = 0; q < nl; ++q) {
       const int s0 = fl->start[q], s1 = fl->end[q], src = fl->src[q];
-      for (int k = s0 + (int)threadIdx.x; k < s1; k += (int)blockDim.x) idx[k] = src;
+      for (int k = s0 + (int)threadIdx.x; k < s1 && k < p.idx_cap; k += (int)blockDim.x) idx[k] = src;
     }
   }
   return acc;
@@ -667,7 +691,8 @@ __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, pf_ctx& cx, pf_t
   const int N = p.N;
   const int lane = threadIdx.x & 31;
   const bool writer = blockIdx.x == 0 && lane == 0;
-  pf_frame_result* res = p.result + (p.mode != 0 ? (size_t)trk * p.total_frames + frame : (size_t)trk);
+  const bool seq_mode = p.mode == 1 || p.mode == 2;
+  pf_frame_result* res = p.result + (seq_mode ? (size_t)trk * p.total_frames + frame : (size_t)trk);
   const int dst_buf = 1 - cx.src_buf;
   const float4* T = (dst_buf == 0 ? p.pose0 : p.pose1) + (size_t)trk * 3 * (size_t)N;
 
@@ -676,6 +701,7 @@ __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, pf_ctx& cx, pf_t
   int q;
   if (resampled) q = (int)(~(unsigned)(cnt.cntkey & 0xFFFFFFFFull));   // :686 first max of counterMeas
   else q = kept.sum < 0 ? arg_min : arg_max;                            // :714 on the normalised weights (Q6)
+  if (p.mode == 5) q = p.q_local;                                       // sharded: chosen across the ranks by the host
 
   const pf_pose Tw = pf_load_pose(T, N, q);
   unsigned pairs[2 * L];
@@ -849,7 +875,8 @@ __global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid
     if (threadIdx.x == 0) { cx.src_buf = st.src_buf; cx.src_mode = st.src_mode; }
     const int D = cx.fc.D;
     if (threadIdx.x < 32) {
-      const double* bsrc = p.blobs + ((size_t)trk * (p.mode != 0 ? p.total_frames : 1) + (p.mode != 0 ? frame : 0)) *
+      const bool seq_mode = p.mode == 1 || p.mode == 2;
+      const double* bsrc = p.blobs + ((size_t)trk * (seq_mode ? p.total_frames : 1) + (seq_mode ? frame : 0)) *
                                          (size_t)p.D_max * 2;
       pf_stage_blobs(bsrc, D, p.score.tol_pf, cx.bt, blobs, threadIdx.x);
     }
@@ -863,11 +890,21 @@ __global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid
     pf_red kept = pf_red_identity(), last = pf_red_identity();
     int iters = 0;
     bool regen = false;                 // extra pass that regenerates the kept iteration (one call site: one copy of the code)
-    for (;;) {
-      pf_red r = pf_stage_score<L>(p, cx, blobs, tab, trk, regen ? best_it : it, warp_agg);
+    // Sharded single filter (modes 3-5): one stage per launch; the collectives across the GPUs and the
+    // do/while decision sit between the launches (pf_monocular_pose_estimator_b200/sharded.py).
+    while (p.mode < 4) {
+      pf_red r = pf_stage_score<L>(p, cx, blobs, tab, trk, p.mode == 3 ? p.pass_it : (regen ? best_it : it), warp_agg);
       if (it == 0) pf_stamp(p, 2);
       r = pf_grid_reduce(r, red_smem, p, bar, warp_agg);
       if (it == 0) pf_stamp(p, 3);
+      if (p.mode == 3) {   // this shard's (max, first argmax), (min, first argmin), sum and prefix aggregate
+        pf_cta_prefix(p, warp_agg, scr);
+        if (blockIdx.x == 0 && threadIdx.x == 0) {
+          p.shard_partial[0] = (long long)r.maxkey; p.shard_partial[1] = (long long)r.minkey_inv; p.shard_partial[2] = r.sum;
+          p.shard_partial[3] = scr[PF_MAX_WARPS].s; p.shard_partial[4] = scr[PF_MAX_WARPS].mx; p.shard_partial[5] = scr[PF_MAX_WARPS].mn;
+        }
+        break;
+      }
       if (regen) break;                                              // r == kept (same particles, exact sums)
       const float m = pf_unord((unsigned)(r.maxkey >> 32));
       last = r;
@@ -882,11 +919,25 @@ __global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid
       regen = true;
     }
 
+    if (p.mode == 3) continue;
+    if (p.mode >= 4) {     // the host made the loop / accept decisions from the gathered partials
+      kept.sum = p.S_fx; iters = p.iters_total; highest = INFINITY;
+      if (p.mode == 4) {   // prefix aggregates of the kept score pass (an earlier launch)
+        const int nw = blockDim.x >> 5;
+        if ((int)threadIdx.x < nw) {
+          const pf_cta_agg* g = p.warp_agg_g + (size_t)blockIdx.x * PF_MAX_WARPS + threadIdx.x;
+          pf_sm3 a; a.s = g->s; a.mx = g->mx; a.mn = g->mn;
+          warp_agg[threadIdx.x] = a;
+        }
+        __syncthreads();
+      }
+    }
+
     // ---- accept test (:633) and resampling (:666-682)
     const bool accept = (kept.sum != 0) && (highest > (float)(L * (D < 3 ? D : 3)));
     const bool resampled = accept && cx.fc.isi > 0;
     pf_red cnt = pf_red_identity();
-    if (resampled) {
+    if (resampled && p.mode != 5) {
       pf_stamp(p, 4);
       if (threadIdx.x == 0) fill.n = 0;                  // ordered before its use by the barrier in pf_cta_prefix
       pf_cta_prefix(p, warp_agg, scr);
@@ -897,8 +948,16 @@ __global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid
       pf_stamp(p, 6);
     }
 
+    if (p.mode == 4) {     // sharded: the resampled set is rebalanced across the ranks into the source buffer
+      if (blockIdx.x == 0 && threadIdx.x == 0) {
+        p.shard_partial[0] = (long long)cnt.cntkey;
+        pf_tracker_state* g = p.state + trk;
+        g->t_buf = 1 - cx.src_buf; g->src_mode = 0; g->frames_done = st.frames_done + 1;
+      }
+      continue;
+    }
     // particle-set bookkeeping for the next frame (shared memory copy of every CTA; CTA 0 mirrors it)
-    if (threadIdx.x == 0) {
+    if (threadIdx.x == 0 && p.mode != 5) {
       st.t_buf = 1 - cx.src_buf;
       if (resampled) { st.src_buf = 1 - cx.src_buf; st.src_mode = 1; }
       st.frames_done += 1;
@@ -926,6 +985,31 @@ __global__ void __launch_bounds__(PF_BLOCK) pf_gather_kernel(const float4* T, co
   out[(size_t)N + n] = T[(size_t)N + s];
   out[2 * (size_t)N + n] = T[2 * (size_t)N + s];
   if (idx_out) idx_out[n] = s;
+}
+
+// Sharded filter: rows of the resampled set this rank produced.  Global slot k in [first, first +
+// count) was filled by the local source idx[k - kbase]; a row is the 12 floats of T (3 x float4).
+__global__ void __launch_bounds__(PF_BLOCK) pf_shard_export_kernel(const float4* T, const int* idx, int N, long long kbase,
+                                                                   long long first, long long count, int use_idx,
+                                                                   float4* rows)
+{
+  const long long i = (long long)blockIdx.x * PF_BLOCK + threadIdx.x;
+  if (i >= count) return;
+  const long long k = first + i - kbase;
+  const int s = use_idx ? idx[k] : (int)k;
+  rows[3 * i] = T[s];
+  rows[3 * i + 1] = T[(size_t)N + s];
+  rows[3 * i + 2] = T[2 * (size_t)N + s];
+}
+
+// Sharded filter: the rebalanced rows become the particle set read by the next frame.
+__global__ void __launch_bounds__(PF_BLOCK) pf_shard_import_kernel(const float4* rows, int N, float4* dst)
+{
+  const int n = blockIdx.x * PF_BLOCK + threadIdx.x;
+  if (n >= N) return;
+  dst[n] = rows[3 * (size_t)n];
+  dst[(size_t)N + n] = rows[3 * (size_t)n + 1];
+  dst[2 * (size_t)N + n] = rows[3 * (size_t)n + 2];
 }
 
 #endif  // __CUDACC__

@@ -83,6 +83,11 @@ struct pfmpe_handle {
   bool last_was_track = false;
   TrackSeq seq;
   std::vector<HostTrack> host_trk;   // host mirror of the tracked objects (pfmpe_track_frame_host)
+  // sharded single filter (pfmpe_shard_*): this handle owns global particles [goff, goff + N) of n_global
+  bool sharded = false;
+  int goff = 0, n_global = 0;
+  pf_cta_agg* warp_agg_g = nullptr;
+  long long* shard_partial = nullptr;   // default target of the per-stage partial results
   std::vector<pfmpe_frame_in> in_scratch;
   std::vector<pfmpe_frame_out> out_scratch;
   std::string err;
@@ -129,7 +134,7 @@ void free_all(pfmpe_handle* h)
   cudaFree(h->pose0); cudaFree(h->pose1); cudaFree(h->gather_tmp); cudaFree(h->w); cudaFree(h->kend);
   cudaFree(h->idx); cudaFree(h->gather_idx); cudaFree(h->cta_agg); cudaFree(h->accum);
   cudaFree(h->inbox); cudaFree(h->state); cudaFree(h->result); cudaFree(h->obj_f); cudaFree(h->obj_d);
-  cudaFree(h->rng_tab); cudaFree(h->timeline);
+  cudaFree(h->rng_tab); cudaFree(h->timeline); cudaFree(h->warp_agg_g); cudaFree(h->shard_partial);
   if (h->seq.owned) { cudaFree(h->seq.blobs); cudaFree(h->seq.counts); cudaFree(h->seq.times); cudaFree(h->seq.seeds); }
   cudaFree(h->seq.result); cudaFree(h->seq.fc_log);
   if (h->h_inbox) cudaFreeHost(h->h_inbox);
@@ -162,6 +167,11 @@ void fill_kparams(const pfmpe_handle* h, pf_kparams& p)
   p.min_ang = h->prm.min_angular_noise; p.max_ang = h->prm.max_angular_noise;
   p.min_tr = h->prm.min_transition_noise; p.max_tr = h->prm.max_transition_noise;
   p.rng_tab = h->rng_tab;
+  p.goff = h->sharded ? h->goff : 0;
+  p.N_global = h->sharded ? h->n_global : h->cfg.n_particles;
+  p.idx_cap = p.N_global;
+  p.warp_agg_g = h->warp_agg_g;
+  p.shard_partial = h->shard_partial;
   p.timeline = h->timeline_on ? h->timeline : nullptr;
 }
 
@@ -182,8 +192,17 @@ frames_kernel_t kernel_for(int L)
   }
 }
 
-// Launch the frame kernel for trackers [t0, t0+nt).  mode 0: per-frame, 1: track.
-int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_frames)
+// per-launch arguments of the sharded-filter stages (modes 3-5)
+struct ShardArgs {
+  int pass_it = 0, iters_total = 0, q_local = 0;
+  long long S_fx = 0;
+  long long excl[3] = {0, 0, 0}, total[3] = {0, 0, 0};
+  long long* partial = nullptr;
+};
+
+// Launch the frame kernel for trackers [t0, t0+nt).  mode 0: per-frame, 1: track, 2: replay,
+// 3/4/5: one stage of the sharded filter.
+int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_frames, const ShardArgs* sa = nullptr)
 {
   const int N = h->cfg.n_particles;
   frames_kernel_t k = kernel_for(h->cfg.n_leds);
@@ -199,7 +218,13 @@ int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_f
   p.mode = mode;
   p.frame0 = frame0;
   p.n_frames = n_frames;
-  if (mode != 0) {
+  if (sa) {
+    p.pass_it = sa->pass_it; p.iters_total = sa->iters_total; p.q_local = sa->q_local; p.S_fx = sa->S_fx;
+    for (int i = 0; i < 3; ++i) { p.rank_excl[i] = sa->excl[i]; p.rank_total[i] = sa->total[i]; }
+    if (sa->partial) p.shard_partial = sa->partial;
+    if (mode == 5) grid_mode = false;     // the winner record is one warp of work
+  }
+  if (mode == 1 || mode == 2) {
     p.blobs = h->seq.blobs; p.blob_count = h->seq.counts; p.times = h->seq.times; p.seeds = h->seq.seeds;
     p.result = h->seq.result; p.total_frames = h->seq.n_frames; p.fc_log = h->seq.fc_log;
   } else {
@@ -972,6 +997,124 @@ int pfmpe_track_sequence_host(pfmpe_handle* h, int n_frames, const double* times
     if (rc) return rc;
     if (frame_seconds) frame_seconds[f] = std::chrono::duration<double>(std::chrono::steady_clock::now() - a).count();
   }
+  return PFMPE_OK;
+}
+
+// ---- sharded single filter (BASELINE configs[4]; one handle per rank) ---------------------------
+// The particle set of ONE filter is split into contiguous shards, one per handle/GPU.  Every stage
+// is one launch; the exchange steps between them (all-gather of the 64-byte partials, all-to-all
+// of the resampled rows) belong to the caller (pf_monocular_pose_estimator_b200/sharded.py: NCCL).
+int pfmpe_shard_configure(pfmpe_handle* h, int64_t global_offset, int64_t n_global)
+{
+  if (!h) return PFMPE_ERR_INVALID;
+  if (h->cfg.n_trackers != 1) return fail(h, PFMPE_ERR_UNSUPPORTED, "a sharded filter is one tracked object per handle");
+  const int64_t N = h->cfg.n_particles;
+  if (global_offset < 0 || n_global < 2 || global_offset + N > n_global || n_global > 0x7fffffff)
+    return fail(h, PFMPE_ERR_INVALID, "shard range outside [0, n_global) or n_global >= 2^31");
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  // a shard's sources can own any number of the n_global output slots
+  cudaFree(h->idx); h->idx = nullptr;
+  PF_CUDA(h, dev_alloc(&h->idx, (size_t)n_global));
+  PF_CUDA(h, cudaMemset(h->idx, 0, (size_t)n_global * sizeof(int)));
+  if (!h->warp_agg_g) PF_CUDA(h, dev_alloc(&h->warp_agg_g, (size_t)PF_MAX_GRID * PF_MAX_WARPS));
+  if (!h->shard_partial) PF_CUDA(h, dev_alloc(&h->shard_partial, 8));
+  h->sharded = true;
+  h->goff = (int)global_offset;
+  h->n_global = (int)n_global;
+  return PFMPE_OK;
+}
+
+static int shard_ready(pfmpe_handle* h)
+{
+  if (!h->sharded) return fail(h, PFMPE_ERR_STATE, "pfmpe_shard_configure must be called first");
+  int rc = check_ready(h);
+  if (rc) return rc;
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  return PFMPE_OK;
+}
+
+int pfmpe_shard_begin_frame(pfmpe_handle* h, const pfmpe_frame_in* in)
+{
+  if (!h || !in) return PFMPE_ERR_INVALID;
+  int rc = shard_ready(h);
+  if (rc) return rc;
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));   // the pinned inbox may still be in flight
+  rc = stage_frame(h, 0, in);
+  if (rc) return rc;
+  PF_CUDA(h, cudaMemcpyAsync(h->inbox, h->h_inbox, h->inbox_bytes, cudaMemcpyHostToDevice, h->stream));
+  return PFMPE_OK;
+}
+
+int pfmpe_shard_score(pfmpe_handle* h, int iteration, void* d_partial)
+{
+  if (!h || iteration < 0 || iteration >= PF_MAX_ITER) return PFMPE_ERR_INVALID;
+  int rc = shard_ready(h);
+  if (rc) return rc;
+  ShardArgs sa;
+  sa.pass_it = iteration;
+  sa.partial = static_cast<long long*>(d_partial);
+  return launch_frames(h, 3, 0, 1, 0, 1, &sa);
+}
+
+int pfmpe_shard_resample(pfmpe_handle* h, int64_t sum_fx, int iterations, const int64_t lower[3], const int64_t all[3],
+                         void* d_partial)
+{
+  if (!h || !lower || !all || iterations < 1 || iterations > PF_MAX_ITER) return PFMPE_ERR_INVALID;
+  int rc = shard_ready(h);
+  if (rc) return rc;
+  ShardArgs sa;
+  sa.S_fx = sum_fx;
+  sa.iters_total = iterations;
+  for (int i = 0; i < 3; ++i) { sa.excl[i] = lower[i]; sa.total[i] = all[i]; }
+  sa.partial = static_cast<long long*>(d_partial);
+  return launch_frames(h, 4, 0, 1, 0, 1, &sa);
+}
+
+int pfmpe_shard_export(pfmpe_handle* h, int64_t first_owned_slot, int64_t first_slot, int64_t count, void* d_rows)
+{
+  if (!h || count < 0 || (count > 0 && !d_rows) || first_slot < first_owned_slot) return PFMPE_ERR_INVALID;
+  int rc = shard_ready(h);
+  if (rc) return rc;
+  if (count == 0) return PFMPE_OK;
+  const size_t N = (size_t)h->cfg.n_particles;
+  if (first_slot - first_owned_slot + count > (int64_t)h->n_global)
+    return fail(h, PFMPE_ERR_INVALID, "slot range outside this shard's output");
+  const int blocks = (int)((count + PF_BLOCK - 1) / PF_BLOCK);
+  pf_shard_export_kernel<<<blocks, PF_BLOCK, 0, h->stream>>>(h->pose1, h->idx, (int)N, first_owned_slot, first_slot, count,
+                                                            1, static_cast<float4*>(d_rows));
+  PF_CUDA(h, cudaGetLastError());
+  h->launches += 1;
+  return PFMPE_OK;
+}
+
+int pfmpe_shard_import(pfmpe_handle* h, const void* d_rows)
+{
+  if (!h || !d_rows) return PFMPE_ERR_INVALID;
+  int rc = shard_ready(h);
+  if (rc) return rc;
+  const size_t N = (size_t)h->cfg.n_particles;
+  const int blocks = (int)((N + PF_BLOCK - 1) / PF_BLOCK);
+  pf_shard_import_kernel<<<blocks, PF_BLOCK, 0, h->stream>>>(static_cast<const float4*>(d_rows), (int)N, h->pose0);
+  PF_CUDA(h, cudaGetLastError());
+  h->launches += 1;
+  h->particles_set[0] = 1;
+  return PFMPE_OK;
+}
+
+int pfmpe_shard_winner(pfmpe_handle* h, int local_index, pfmpe_frame_out* out)
+{
+  if (!h || !out || local_index < 0 || local_index >= h->cfg.n_particles) return PFMPE_ERR_INVALID;
+  int rc = shard_ready(h);
+  if (rc) return rc;
+  ShardArgs sa;
+  sa.q_local = local_index;
+  sa.S_fx = 1;
+  rc = launch_frames(h, 5, 0, 1, 0, 1, &sa);
+  if (rc) return rc;
+  PF_CUDA(h, cudaMemcpyAsync(h->h_result, h->result, sizeof(pf_frame_result), cudaMemcpyDeviceToHost, h->stream));
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  unpack_result(h->h_result[0], out);
   return PFMPE_OK;
 }
 

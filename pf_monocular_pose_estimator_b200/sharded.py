@@ -1,0 +1,303 @@
+"""One particle filter sharded over several GPUs (BASELINE configs[4]).
+
+The reference runs ONE filter per tracked object (pose_estimator.cpp:471-735).  For the giant
+single-filter case its particle set is split into `world` contiguous, equal shards, one per GPU /
+process.  The loop is cut at its global reductions; every stage is one launch of the sm_100a frame
+kernel through the C ABI (pfmpe_shard_*, include/pfmpe.h) and this module owns the exchange steps:
+
+  score pass   -> all_gather of one 64-byte partial per rank  (max / min / weight sum / prefix aggregate:
+                  the "NCCL weight-sum allreduce" of the north star; a gather keeps the per-rank
+                  aggregates that the ordered prefix needs, 64 B x world)
+  decision     -> do/while exit, kept iteration, accept test: host scalars, same on every rank (:608-633)
+  resampling   -> every rank resamples its own sources against GLOBAL strata (global slot numbers, the
+                  global RNG stream); all_gather of (count key, first owned slot, end slot)
+  rebalance    -> all_to_all of the produced rows so that every rank again owns n_global / world
+                  particles in global slot order ("global resample")
+  winner       -> first most-resampled particle across ranks (:685-686); its owner computes pose and
+                  correspondences, broadcast to the others
+
+Because RNG addressing, strata, keys and tie rules all use global particle / slot numbers, the sharded
+filter reproduces the single-GPU filter bit for bit (tests/test_cuda_shard.py checks exactly that with
+logical shards on one GPU and with NCCL ranks).
+
+Two communicators: `Loopback` (all shards in this process, exchange = device-local copies; used by
+the single-GPU tests and as the W=1 case) and `TorchDist` (one shard per process, torch.distributed).
+The host logic (`reduce_pass`, `slot_partition`, `lower_aggregates`) is pure numpy/python and is
+covered by the CPU tests, including a world_size-2 gloo run of `TorchDist`.
+"""
+import struct
+
+import numpy as np
+
+from . import capi
+
+Q30 = 1 << 30
+SM_NEG = -(1 << 62)      # PF_SM_NEG / PF_SM_POS of pf_math.cuh ("no prefix yet")
+SM_POS = 1 << 62
+MAX_ITER = 80            # PF_MAX_ITER (:616)
+
+
+# ---------------------------------------------------------------------------------------
+# host logic (no device, no torch)
+# ---------------------------------------------------------------------------------------
+def unord(o):
+    """Inverse of the ordered-uint mapping of an f32 (pf_ord / pf_unord in pf_kernels.cuh)."""
+    o &= 0xFFFFFFFF
+    u = (o ^ 0x80000000) if (o & 0x80000000) else (~o & 0xFFFFFFFF)
+    return struct.unpack("<f", struct.pack("<I", u))[0]
+
+
+def sm3_combine(a, b):
+    """Ordered combination of (sum, max prefix, min prefix) aggregates (pf_sm3_combine)."""
+    tx = SM_NEG if b[1] <= SM_NEG else a[0] + b[1]
+    tn = SM_POS if b[2] >= SM_POS else a[0] + b[2]
+    return (a[0] + b[0], max(a[1], tx), min(a[2], tn))
+
+
+SM3_IDENTITY = (0, SM_NEG, SM_POS)
+
+
+def reduce_pass(partials):
+    """partials: (world, 8) int64 of one score pass -> dict(maxkey, minkey_inv, sum, aggs)."""
+    u = np.ascontiguousarray(partials[:, :2]).view(np.uint64)
+    return dict(maxkey=int(u[:, 0].max()), minkey_inv=int(u[:, 1].max()),
+                sum=int(sum(int(v) for v in partials[:, 2])),
+                aggs=[tuple(int(v) for v in row[3:6]) for row in partials])
+
+
+def lower_aggregates(aggs):
+    """Exclusive ordered prefix over the ranks: (per-rank aggregate of all lower ranks, total)."""
+    lower, run = [], SM3_IDENTITY
+    for a in aggs:
+        lower.append(run)
+        run = sm3_combine(run, a)
+    return lower, run
+
+
+def slot_partition(first, end, n_loc, world):
+    """send[r][d] = number of output slots of [first[r], end[r]) that fall into shard d's range
+    [d * n_loc, (d + 1) * n_loc).  The slot ranges of the ranks tile [0, world * n_loc) in rank order."""
+    send = [[0] * world for _ in range(world)]
+    for r in range(world):
+        for d in range(world):
+            lo, hi = max(int(first[r]), d * n_loc), min(int(end[r]), (d + 1) * n_loc)
+            send[r][d] = max(0, hi - lo)
+    return send
+
+
+def check_tiling(first, end, n_global):
+    pos = 0
+    for a, b in zip(first, end):
+        if int(b) < int(a) or (int(b) > int(a) and int(a) != pos):
+            raise RuntimeError("resampled slot ranges do not tile the filter: %r %r" % (list(first), list(end)))
+        if int(b) > int(a):
+            pos = int(b)
+    if pos != n_global:
+        raise RuntimeError("resampled slot ranges cover %d of %d slots" % (pos, n_global))
+
+
+# ---------------------------------------------------------------------------------------
+# communicators
+# ---------------------------------------------------------------------------------------
+class Loopback:
+    """All `world` shards live in this process on one device; exchange steps are local copies."""
+
+    def __init__(self, world):
+        self.world = world
+        self.local = list(range(world))
+
+    def gather(self, partials):
+        return partials.cpu().numpy()
+
+    def exchange(self, send_rows, send, n_loc):
+        import torch
+        out = []
+        for d in self.local:
+            parts = []
+            for r in self.local:
+                off, c = sum(send[r][:d]), send[r][d]
+                if c:
+                    parts.append(send_rows[r][off:off + c])
+            out.append(torch.cat(parts) if len(parts) != 1 else parts[0].contiguous())
+        return out
+
+    def bcast(self, arr, owner):
+        return arr
+
+
+class TorchDist:
+    """One shard per process (rank = shard); NCCL on GPUs, gloo in the CPU tests."""
+
+    def __init__(self, group=None):
+        import torch.distributed as dist
+        self.dist, self.group = dist, group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.local = [self.rank]
+
+    def gather(self, partials):
+        import torch
+        out = torch.empty((self.world, partials.shape[1]), dtype=partials.dtype, device=partials.device)
+        self.dist.all_gather_into_tensor(out, partials.reshape(-1, partials.shape[1]), group=self.group)
+        return out.cpu().numpy()
+
+    def exchange(self, send_rows, send, n_loc):
+        import torch
+        r = self.rank
+        src = send_rows[0]
+        recv = [send[q][r] for q in range(self.world)]
+        out = torch.empty((sum(recv),) + tuple(src.shape[1:]), dtype=src.dtype, device=src.device)
+        self.dist.all_to_all_single(out, src, output_split_sizes=recv, input_split_sizes=list(send[r]), group=self.group)
+        return [out]
+
+    def bcast(self, arr, owner):
+        import torch
+        dev = "cuda" if self.dist.get_backend(self.group) == "nccl" else "cpu"
+        t = torch.from_numpy(np.ascontiguousarray(arr, dtype=np.float64)).to(dev)
+        src = owner if self.group is None else self.dist.get_global_rank(self.group, owner)
+        self.dist.broadcast(t, src=src, group=self.group)
+        return t.cpu().numpy()
+
+
+# ---------------------------------------------------------------------------------------
+# the sharded filter
+# ---------------------------------------------------------------------------------------
+class ShardedFilter:
+    """Drop-in for capi.Handle.update() on one tracked object whose particles are sharded.
+
+    n_global must be a multiple of comm.world.  With `Loopback` all shards are handles on `device`."""
+
+    def __init__(self, n_global, comm, n_leds=5, max_blobs=32, device=0, **kw):
+        import torch
+        if n_global % comm.world:
+            raise ValueError("n_global must be a multiple of the number of shards")
+        self.torch = torch
+        self.comm, self.W = comm, comm.world
+        self.N, self.n_loc, self.L, self.T = n_global, n_global // comm.world, n_leds, 1
+        self.dev = torch.device("cuda", device)
+        torch.cuda.set_device(self.dev)
+        self.shards = []
+        for r in comm.local:
+            h = capi.Handle(self.n_loc, n_trackers=1, n_leds=n_leds, max_blobs=max_blobs, device=device, **kw)
+            h.shard_configure(r * self.n_loc, n_global)
+            h.set_stream(torch.cuda.current_stream(self.dev).cuda_stream)
+            self.shards.append(h)
+        self.partials = torch.zeros((len(self.shards), 8), dtype=torch.int64, device=self.dev)
+        self.passes = 0          # score passes launched so far (per shard)
+        self.last = None
+
+    def close(self):
+        for h in self.shards:
+            h.close()
+        self.shards = []
+
+    def configure(self, markers, K, params):
+        for h in self.shards:
+            h.configure(markers, K, params)
+
+    def set_particles(self, poses, tracker=0):
+        """poses: (n_global, 4, 4), or (n_loc, 4, 4) per local shard if given as a list."""
+        for i, r in enumerate(self.comm.local):
+            p = poses[i] if isinstance(poses, list) else poses[r * self.n_loc:(r + 1) * self.n_loc]
+            self.shards[i].set_particles(p)
+
+    # -- stages -------------------------------------------------------------------------
+    def _score(self, it):
+        for i, h in enumerate(self.shards):
+            h.shard_score(it, self.partials[i].data_ptr())
+        self.passes += 1
+        return reduce_pass(self.comm.gather(self.partials))
+
+    def update(self, img, T_cur, T_pred, P, Cm, isi, dt, seed, tracker=0):
+        torch = self.torch
+        keep = []
+        fi = capi.make_frame_in(img, T_cur, T_pred, P, Cm, isi, dt, seed, keep)
+        D = int(fi.n_image_points)
+        for h in self.shards:
+            h.shard_begin_frame(fi)
+
+        # ---- do { propagate, project, score } while (iter < 80 && max < L*min(5,D))  (:535-616)
+        thr_exit = np.float32(self.L * min(D, 5))
+        highest, best_it, it = np.float32(0.0), -1, 0
+        kept = last = None
+        while True:
+            r = self._score(it)
+            m = np.float32(unord(r["maxkey"] >> 32))
+            last = r
+            it += 1
+            if m > highest:                                  # :608-614 strict >, from 0
+                highest, best_it, kept = m, it - 1, r
+            if it < MAX_ITER and m < thr_exit:
+                continue
+            break
+        iters = it
+        if best_it < 0:
+            kept = last                                      # :619 nothing to restore
+        elif best_it != iters - 1:
+            kept = self._score(best_it)                      # regenerate the kept iteration (exact: RNG by address)
+
+        S = kept["sum"]
+        accept = S != 0 and highest > np.float32(self.L * min(D, 3))          # :633
+        resampled = bool(accept and isi > 0)
+        arg_max = (~kept["maxkey"]) & 0xFFFFFFFF
+        arg_min = (~kept["minkey_inv"]) & 0xFFFFFFFF
+        max_count = 0
+        if resampled:
+            lower, total = lower_aggregates(kept["aggs"])
+            for i, r_ in enumerate(self.comm.local):
+                self.shards[i].shard_resample(S, iters, lower[r_], total, self.partials[i].data_ptr())
+            part = self.comm.gather(self.partials)
+            cntkey = int(np.ascontiguousarray(part[:, 0]).view(np.uint64).max())
+            q = (~cntkey) & 0xFFFFFFFF                        # :686 first max of counterMeas
+            max_count = cntkey >> 32
+            first, end = part[:, 1], part[:, 2]
+            check_tiling(first, end, self.N)
+            send = slot_partition(first, end, self.n_loc, self.W)
+            rows = []
+            for i, r_ in enumerate(self.comm.local):
+                cnt = int(end[r_] - first[r_])
+                buf = torch.empty((cnt, 12), dtype=torch.float32, device=self.dev)
+                self.shards[i].shard_export(int(first[r_]), int(first[r_]), cnt, buf.data_ptr())
+                rows.append(buf)
+            new = self.comm.exchange(rows, send, self.n_loc)
+            for i, h in enumerate(self.shards):
+                if new[i].shape[0] != self.n_loc:
+                    raise RuntimeError("rebalance delivered %d rows, expected %d" % (new[i].shape[0], self.n_loc))
+                h.shard_import(new[i].data_ptr())
+            self._rows = (rows, new)                          # keep alive until the stream has consumed them
+        else:
+            q = arg_min if S < 0 else arg_max                 # :714 on the normalised weights
+
+        # ---- winner pose + correspondences from its owner
+        owner = q // self.n_loc
+        packed = np.zeros(16 + 1 + 2 * capi.MAX_LED)
+        if owner in self.comm.local:
+            w = self.shards[self.comm.local.index(owner)].shard_winner(q - owner * self.n_loc)
+            packed[:16] = capi.colmajor(w["winner_pose"])
+            c = w["correspondences"].reshape(-1)
+            packed[16] = c.size // 2
+            packed[17:17 + c.size] = c
+        packed = self.comm.bcast(packed, owner)
+        nc = int(packed[16])
+        out = dict(status=1 if accept else 4, iterations=iters, best_iteration=best_it, resampled=int(resampled),
+                   highest_prob=float(highest), weight_sum=S / Q30,
+                   most_likely_particle_idx=(arg_max if best_it >= 0 else -1) if accept else q,
+                   most_likely_pose_idx=q if resampled else -1, max_count=max_count,
+                   correspondences=packed[17:17 + 2 * nc].astype(np.uint32).reshape(-1, 2),
+                   winner_pose=capi.from_colmajor(packed[:16]), sum_fx=S)
+        self.last = out
+        return out
+
+    # -- getters (local shards; concatenate across ranks yourself in distributed runs) ----
+    def particles(self, which=0, tracker=0):
+        return np.concatenate([h.particles(which) for h in self.shards])
+
+    def weights(self, normalised=False, tracker=0):
+        w = np.concatenate([h.weights(False) for h in self.shards])
+        if normalised and self.last and self.last["sum_fx"] != 0:
+            w = w / (self.last["sum_fx"] / Q30)
+        return w
+
+    def sync(self):
+        for h in self.shards:
+            h.sync()
