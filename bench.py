@@ -319,6 +319,49 @@ def gpu_measure(workload, trackers, K, W, dev, local_rank, barrier, flush_ok=Tru
     return out
 
 
+def sharded_filter_measure(world, rank, dev, local_rank, barrier, allreduce, RO, peak, n_global=1 << 26, K=10, W=3):
+    """BASELINE configs[4]: one filter of 2^26 particles, particle shards over the ranks (all_gather of the
+    64-byte partials = weight-sum exchange, all_to_all rebalance = global resample), driven by the same
+    reference-side loop (predictPose -> PF -> Gauss-Newton) as the e2e path.  Host blobs in, pose out."""
+    import torch
+    from pf_monocular_pose_estimator_b200 import scenes as S, sharded as SH
+    from tests.host_loop import HostTracker
+    sc = S.Scene(0)
+    comm = SH.TorchDist() if world > 1 else SH.Loopback(1)
+    sf = SH.ShardedFilter(n_global, comm, n_leds=L_LED, max_blobs=sc.blobs(0).shape[0] + 4, device=local_rank)
+    sf.configure(sc.markers, sc.K, sc.params)
+    trk = HostTracker(sf, sc, init_particles=False)
+    sf.track_init(sc.pose(0), sc.time(0), sc.pose(1), sc.time(1))
+    ok = True
+    for f in range(2, 2 + W):
+        ok = ok and bool(trk.frame(f)["resampled"])
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    p0 = sf.passes
+    t0 = time.perf_counter()
+    e0.record()
+    for f in range(2 + W, 2 + W + K):
+        ok = ok and bool(trk.frame(f)["resampled"])
+    e1.record()
+    torch.cuda.synchronize(dev)
+    wall = time.perf_counter() - t0
+    barrier()
+    passes = sf.passes - p0
+    (ms,) = allreduce([max(e0.elapsed_time(e1), 0.0)], RO.MAX if RO else None)
+    (wall,) = allreduce([wall], RO.MAX if RO else None)
+    (okf,) = allreduce([1.0 if ok else 0.0], RO.MIN if RO else None)
+    pme = float(n_global) * L_LED * passes
+    alg = alg_bytes_per_frame(n_global // world, passes / K) * K + 2 * 96.0 * (n_global // world) * K   # + export/import rows
+    sf.close()
+    return {"workload": "cfg5", "desc": "BASELINE configs[4]: single filter with 2^26 particles sharded by particle over the ranks",
+            "scaling": "strong", "particles": n_global, "particles_per_rank": n_global // world, "value": pme / (wall), "unit": "PME/s",
+            "ms_per_step": 1e3 * wall / K, "device_ms_per_step": ms / K, "steps": K, "warmup": W, "mean_iterations": passes / K,
+            "all_frames_resampled": bool(okf > 0), "roofline_frac": alg / (wall) / 1e9 / peak,
+            "exchange": "all_gather 64 B/rank per pass + per resampling, all_to_all of 48 B/particle rows (torch.distributed %s)"
+                        % ("nccl" if world > 1 else "loopback, 1 rank"),
+            "note": "host-orchestrated stages through pfmpe_shard_*; wall clock of the whole host loop incl. host Gauss-Newton"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -330,6 +373,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-batched", action="store_true", help="skip the short cfg4 run reported under batched_trackers")
+    ap.add_argument("--no-sharded", action="store_true", help="skip the short configs[4] run reported under sharded_filter")
     ap.add_argument("--e2e-steps", type=int, default=300)
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     args = ap.parse_args()
@@ -441,6 +485,10 @@ def main():
             "ms_per_step": b_ms / K4, "steps": K4, "warmup": W4, "mean_iterations": b["mean_iter"], "max_iterations": b.get("max_iter"),
             "tracking_ms_per_step": b_tr / K4 if b_tr else None,
             "roofline_frac": b_alg / world / (b_ms * 1e-3) / 1e9 / peak, "launch": b["launch_info"], "l2": b["l2"]}
+
+    # ---- BASELINE configs[4] alongside (short): ONE filter of 2^26 particles sharded by particle over the ranks
+    if not sharded and not args.no_sharded:
+        line["sharded_filter"] = sharded_filter_measure(world, rank, dev, local_rank, barrier, allreduce, RO, peak)
 
     if rank == 0:
         if world == 1 and not args.no_cpu:

@@ -332,7 +332,7 @@ struct pf_ctx {
 // Stage A: fused propagate -> project -> score over this warp's contiguous particles for
 // iteration `it` (:543-605).  Leaves the warp's sign-agnostic prefix aggregate in warp_agg[warp].
 // ---------------------------------------------------------------------------------------
-template <int L>
+template <int L, bool SH>
 __device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_ctx& cx, const pf_blob* blobs,
                                                  const uint32_t* tab, int trk, int it, pf_sm3* warp_agg)
 {
@@ -365,8 +365,8 @@ __device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_c
   // with one modular multiplication (exponents mod the group order, so n < 2 is harmless).
   uint32_t xs;
   {
-    const uint64_t e0 = (12ull * (uint64_t)(p.N_global - 2) * (uint64_t)it) % PF_RNG_ORDER;
-    const uint64_t ee = (e0 + (uint64_t)PF_RNG_ORDER - 24ull + 12ull * (uint64_t)(p.goff + w0 + lane)) % PF_RNG_ORDER;
+    const uint64_t e0 = (12ull * (uint64_t)((SH ? p.N_global : N) - 2) * (uint64_t)it) % PF_RNG_ORDER;
+    const uint64_t ee = (e0 + (uint64_t)PF_RNG_ORDER - 24ull + 12ull * (uint64_t)((SH ? p.goff : 0) + w0 + lane)) % PF_RNG_ORDER;
     xs = pf_rng_skip_e(cx.fc.seed_state, (uint32_t)ee, tab);
   }
 
@@ -381,7 +381,7 @@ __device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_c
     if (valid) {
       const int s = cx.src_mode == 1 ? idx[n] : n;      // Particle_index of slot n (:678-681), written by stage B
       pf_pose T;
-      const int ng = p.goff + n;                        // global particle index (sharded filter: goff > 0)
+      const int ng = (SH ? p.goff : 0) + n;                        // global particle index (sharded filter: goff > 0)
       if (ng == 0) {
 #pragma unroll
         for (int i = 0; i < 12; ++i) T.p[i] = cx.fc.Tcur[i];      // :547
@@ -437,7 +437,7 @@ __device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_c
   }
   if (lane == 0) {
     warp_agg[warp] = carry;
-    if (p.mode == 3) {   // sharded filter: the resampling stage is a separate launch
+    if ((SH && p.mode == 3)) {   // sharded filter: the resampling stage is a separate launch
       pf_cta_agg* g = p.warp_agg_g + (size_t)blockIdx.x * PF_MAX_WARPS + warp;
       g->s = carry.s; g->mx = carry.mx; g->mn = carry.mn;
     }
@@ -449,6 +449,7 @@ __device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_c
 // warps through shared memory: scr[w] = (exclusive combination of the aggregates of CTAs 0..b-1)
 // (+) (aggregates of warps 0..w-1 of this CTA) = everything before warp w; scr[PF_MAX_WARPS] = the
 // combination of the whole filter.  Ends with a __syncthreads.
+template <bool SH>
 __device__ __noinline__ void pf_cta_prefix(const pf_kparams& p, const pf_sm3* warp_agg, pf_sm3* scr)
 {
   const int nwarps = blockDim.x >> 5;
@@ -498,7 +499,7 @@ __device__ __noinline__ void pf_cta_prefix(const pf_kparams& p, const pf_sm3* wa
     pf_sm3 we;                                            // exclusive: aggregates of the warps below `lane`
     we.s = __shfl_up_sync(PF_FULL, w.s, 1); we.mx = __shfl_up_sync(PF_FULL, w.mx, 1); we.mn = __shfl_up_sync(PF_FULL, w.mn, 1);
     if (lane == 0) we = pf_sm3_identity();
-    if (p.mode == 4) {   // sharded filter: everything on the lower ranks comes first
+    if ((SH && p.mode == 4)) {   // sharded filter: everything on the lower ranks comes first
       pf_sm3 re; re.s = p.rank_excl[0]; re.mx = p.rank_excl[1]; re.mn = p.rank_excl[2];
       excl = pf_sm3_combine(re, excl);
     }
@@ -506,7 +507,7 @@ __device__ __noinline__ void pf_cta_prefix(const pf_kparams& p, const pf_sm3* wa
     if (!p.coop) {                                        // one CTA: the total is the combination of its warps
       total.s = pf_shfl_ll(w.s, 31); total.mx = pf_shfl_ll(w.mx, 31); total.mn = pf_shfl_ll(w.mn, 31);
     }
-    if (p.mode == 4) { total.s = p.rank_total[0]; total.mx = p.rank_total[1]; total.mn = p.rank_total[2]; }
+    if ((SH && p.mode == 4)) { total.s = p.rank_total[0]; total.mx = p.rank_total[1]; total.mn = p.rank_total[2]; }
     if (lane == 0) scr[PF_MAX_WARPS] = total;
   }
   __syncthreads();
@@ -541,6 +542,7 @@ struct pf_fill_list {
   int start[PF_FILL_LIST], end[PF_FILL_LIST], src[PF_FILL_LIST];
 };
 
+template <bool SH>
 __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const pf_ctx& cx, const uint32_t* tab, int trk,
                                                     long long S_fx, int iters_total, const pf_sm3* scr, pf_fill_list* fl)
 {
@@ -550,7 +552,7 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
   int* kend = p.kend + (size_t)trk * N;
   int* idx = p.idx + (size_t)trk * N;
   const long long sg = S_fx < 0 ? -1ll : 1ll;
-  const int Ng = p.N_global;
+  const int Ng = SH ? p.N_global : N;
   const uint32_t x_base = pf_rng_skip(cx.fc.seed_state, 12ull * (uint64_t)(Ng - 2) * (uint64_t)iters_total, tab);
   const pf_resample_cfg rc = pf_make_resample_cfg(x_base, Ng, S_fx);
 
@@ -566,19 +568,26 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
     // K(M) of everything before this warp and of the whole filter: one evaluation, two half-warps
     int k_carry, ktot, kbase = 0;     // kbase (sharded filter): first global slot owned by this rank's sources
     {
-      long long ts_, tm_, rs_ = 0, rm_ = PF_SM_NEG;
+      long long ts_, tm_;
       pf_sm3_select(scr[PF_MAX_WARPS], sg, ts_, tm_);
-      if (p.mode == 4) {
-        pf_sm3 re; re.s = p.rank_excl[0]; re.mx = p.rank_excl[1]; re.mn = p.rank_excl[2];
-        pf_sm3_select(re, sg, rs_, rm_);
-      }
-      const int kk = pf_count_leq_dev(lane < 11 ? carry.m : (lane < 22 ? tm_ : rm_), rc, tab);
-      k_carry = __shfl_sync(PF_FULL, kk, 0);
-      ktot = __shfl_sync(PF_FULL, kk, 11);
-      if (p.mode == 4) {
-        kbase = __shfl_sync(PF_FULL, kk, 22);
-        kbase = ktot == 0 ? p.goff : (kbase == ktot ? Ng : kbase);
-        if (blockIdx.x == 0 && threadIdx.x == 0) p.shard_partial[1] = kbase;
+      if (SH) {          // three values in one evaluation: lanes 0-10, 11-21, 22-31
+        long long rs_ = 0, rm_ = PF_SM_NEG;
+        if (p.mode == 4) {
+          pf_sm3 re; re.s = p.rank_excl[0]; re.mx = p.rank_excl[1]; re.mn = p.rank_excl[2];
+          pf_sm3_select(re, sg, rs_, rm_);
+        }
+        const int kk = pf_count_leq_dev(lane < 11 ? carry.m : (lane < 22 ? tm_ : rm_), rc, tab);
+        k_carry = __shfl_sync(PF_FULL, kk, 0);
+        ktot = __shfl_sync(PF_FULL, kk, 11);
+        if (p.mode == 4) {
+          kbase = __shfl_sync(PF_FULL, kk, 22);
+          kbase = ktot == 0 ? p.goff : (kbase == ktot ? Ng : kbase);
+          if (blockIdx.x == 0 && threadIdx.x == 0) p.shard_partial[1] = kbase;
+        }
+      } else {
+        const int kk = pf_count_leq_dev(lane < 16 ? carry.m : tm_, rc, tab);
+        k_carry = __shfl_sync(PF_FULL, kk, 0);
+        ktot = __shfl_sync(PF_FULL, kk, 16);
       }
     }
     pf_stamp(p, 13);
@@ -618,19 +627,19 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
       if (valid) {
         kend[n] = ke;
         const unsigned cnt = (unsigned)(ke - k_prev);
-        const unsigned long long key = ((unsigned long long)cnt << 32) | (unsigned)(~(unsigned)(p.goff + n));
+        const unsigned long long key = ((unsigned long long)cnt << 32) | (unsigned)(~(unsigned)((SH ? p.goff : 0) + n));
         acc.cntkey = key > acc.cntkey ? key : acc.cntkey;
       }
       // ---- slot fill: the sources of this step own the contiguous slots [E(k_carry), E(ke of lane 31)),
       // E(k) = N if k == K_total (the last source with offspring also owns the not-found tail, Q7)
       if (ktot == 0) {
         if (valid) idx[n] = n;                            // nothing was ever found: every slot keeps its own particle (local)
-        if (p.mode == 4 && valid && n == N - 1) p.shard_partial[2] = (long long)p.goff + N;
+        if ((SH && p.mode == 4) && valid && n == N - 1) p.shard_partial[2] = (long long)p.goff + N;
       } else {
         const int Ecur = (ke == ktot ? Ng : ke) - kbase;
         const int Eprev = (k_prev == ktot ? Ng : k_prev) - kbase;
         const int own = Ecur - Eprev;                     // invalid lanes repeat the last prefix: 0
-        if (p.mode == 4 && valid && n == N - 1) p.shard_partial[2] = (long long)Ecur + kbase;   // end of this rank's slots
+        if ((SH && p.mode == 4) && valid && n == N - 1) p.shard_partial[2] = (long long)Ecur + kbase;   // end of this rank's slots
         const unsigned bigm = __ballot_sync(PF_FULL, own > PF_FILL_WARP);
         if (bigm == 0u) {
           const int E0 = __shfl_sync(PF_FULL, Eprev, 0), R = __shfl_sync(PF_FULL, Ecur, 31) - E0;
@@ -643,7 +652,7 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
               const int v = __shfl_sync(PF_FULL, Ecur, mid);
               if (v > k) hi = mid; else lo = mid + 1;
             }
-            if (q0 + lane < R && k < p.idx_cap) idx[k] = base + lo;
+            if (q0 + lane < R && (!SH || k < p.idx_cap)) idx[k] = base + lo;
           }
         } else {
           // rare: a source owns more than PF_FILL_WARP slots; hand those to the whole CTA (list) and
@@ -655,7 +664,7 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
             if (slot < PF_FILL_LIST) { fl->start[slot] = Eprev; fl->end[slot] = Ecur; fl->src[slot] = n; }
           }
           if (!isbig || slot >= PF_FILL_LIST)
-            for (int k = Eprev; k < Ecur && k < p.idx_cap; ++k) idx[k] = n;
+            for (int k = Eprev; k < Ecur && (!SH || k < p.idx_cap); ++k) idx[k] = n;
         }
       }
       carry.s += total;
@@ -669,7 +678,7 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
     const int nl = fl->n < PF_FILL_LIST ? fl->n : PF_FILL_LIST;
     for (int q = 0; q < nl; ++q) {
       const int s0 = fl->start[q], s1 = fl->end[q], src = fl->src[q];
-      for (int k = s0 + (int)threadIdx.x; k < s1 && k < p.idx_cap; k += (int)blockDim.x) idx[k] = src;
+      for (int k = s0 + (int)threadIdx.x; k < s1 && (!SH || k < p.idx_cap); k += (int)blockDim.x) idx[k] = src;
     }
   }
   return acc;
@@ -682,7 +691,7 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
 // track mode also Gauss-Newton + updatePose + next frame's prediction
 // (:685-703, :707-719, :2011-2035, :995-1010).
 // ---------------------------------------------------------------------------------------
-template <int L>
+template <int L, bool SH>
 __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, pf_ctx& cx, pf_tracker_state& st, pf_tail_smem& ts,
                                            const pf_blob* blobs, int trk, int frame, int iters, int best_it,
                                            float highest, const pf_red& kept, bool accept, bool resampled,
@@ -701,7 +710,7 @@ __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, pf_ctx& cx, pf_t
   int q;
   if (resampled) q = (int)(~(unsigned)(cnt.cntkey & 0xFFFFFFFFull));   // :686 first max of counterMeas
   else q = kept.sum < 0 ? arg_min : arg_max;                            // :714 on the normalised weights (Q6)
-  if (p.mode == 5) q = p.q_local;                                       // sharded: chosen across the ranks by the host
+  if ((SH && p.mode == 5)) q = p.q_local;                                       // sharded: chosen across the ranks by the host
 
   const pf_pose Tw = pf_load_pose(T, N, q);
   unsigned pairs[2 * L];
@@ -817,7 +826,9 @@ __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, pf_ctx& cx, pf_t
 // ---------------------------------------------------------------------------------------
 // The persistent frame kernel.
 // ---------------------------------------------------------------------------------------
-template <int L>
+// SH = true: the stage-per-launch variants of the sharded filter (modes 3-5); a separate
+// instantiation so that the single-GPU kernel carries none of their code.
+template <int L, bool SH>
 __global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid_constant__ pf_kparams p)
 {
   extern __shared__ __align__(16) unsigned char pf_dyn_smem[];
@@ -892,13 +903,13 @@ __global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid
     bool regen = false;                 // extra pass that regenerates the kept iteration (one call site: one copy of the code)
     // Sharded single filter (modes 3-5): one stage per launch; the collectives across the GPUs and the
     // do/while decision sit between the launches (pf_monocular_pose_estimator_b200/sharded.py).
-    while (p.mode < 4) {
-      pf_red r = pf_stage_score<L>(p, cx, blobs, tab, trk, p.mode == 3 ? p.pass_it : (regen ? best_it : it), warp_agg);
+    while (!SH || p.mode < 4) {
+      pf_red r = pf_stage_score<L, SH>(p, cx, blobs, tab, trk, (SH && p.mode == 3) ? p.pass_it : (regen ? best_it : it), warp_agg);
       if (it == 0) pf_stamp(p, 2);
       r = pf_grid_reduce(r, red_smem, p, bar, warp_agg);
       if (it == 0) pf_stamp(p, 3);
-      if (p.mode == 3) {   // this shard's (max, first argmax), (min, first argmin), sum and prefix aggregate
-        pf_cta_prefix(p, warp_agg, scr);
+      if ((SH && p.mode == 3)) {   // this shard's (max, first argmax), (min, first argmin), sum and prefix aggregate
+        pf_cta_prefix<SH>(p, warp_agg, scr);
         if (blockIdx.x == 0 && threadIdx.x == 0) {
           p.shard_partial[0] = (long long)r.maxkey; p.shard_partial[1] = (long long)r.minkey_inv; p.shard_partial[2] = r.sum;
           p.shard_partial[3] = scr[PF_MAX_WARPS].s; p.shard_partial[4] = scr[PF_MAX_WARPS].mx; p.shard_partial[5] = scr[PF_MAX_WARPS].mn;
@@ -919,10 +930,10 @@ __global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid
       regen = true;
     }
 
-    if (p.mode == 3) continue;
-    if (p.mode >= 4) {     // the host made the loop / accept decisions from the gathered partials
+    if ((SH && p.mode == 3)) continue;
+    if (SH && p.mode >= 4) {     // the host made the loop / accept decisions from the gathered partials
       kept.sum = p.S_fx; iters = p.iters_total; highest = INFINITY;
-      if (p.mode == 4) {   // prefix aggregates of the kept score pass (an earlier launch)
+      if ((SH && p.mode == 4)) {   // prefix aggregates of the kept score pass (an earlier launch)
         const int nw = blockDim.x >> 5;
         if ((int)threadIdx.x < nw) {
           const pf_cta_agg* g = p.warp_agg_g + (size_t)blockIdx.x * PF_MAX_WARPS + threadIdx.x;
@@ -937,18 +948,18 @@ __global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid
     const bool accept = (kept.sum != 0) && (highest > (float)(L * (D < 3 ? D : 3)));
     const bool resampled = accept && cx.fc.isi > 0;
     pf_red cnt = pf_red_identity();
-    if (resampled && p.mode != 5) {
+    if (resampled && !(SH && p.mode == 5)) {
       pf_stamp(p, 4);
       if (threadIdx.x == 0) fill.n = 0;                  // ordered before its use by the barrier in pf_cta_prefix
-      pf_cta_prefix(p, warp_agg, scr);
+      pf_cta_prefix<SH>(p, warp_agg, scr);
       pf_stamp(p, 12);
-      cnt = pf_stage_resample(p, cx, tab, trk, kept.sum, iters, scr, &fill);
+      cnt = pf_stage_resample<SH>(p, cx, tab, trk, kept.sum, iters, scr, &fill);
       pf_stamp(p, 5);
       cnt = pf_grid_reduce(cnt, red_smem, p, bar, nullptr);
       pf_stamp(p, 6);
     }
 
-    if (p.mode == 4) {     // sharded: the resampled set is rebalanced across the ranks into the source buffer
+    if ((SH && p.mode == 4)) {     // sharded: the resampled set is rebalanced across the ranks into the source buffer
       if (blockIdx.x == 0 && threadIdx.x == 0) {
         p.shard_partial[0] = (long long)cnt.cntkey;
         pf_tracker_state* g = p.state + trk;
@@ -957,14 +968,14 @@ __global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid
       continue;
     }
     // particle-set bookkeeping for the next frame (shared memory copy of every CTA; CTA 0 mirrors it)
-    if (threadIdx.x == 0 && p.mode != 5) {
+    if (threadIdx.x == 0 && !(SH && p.mode == 5)) {
       st.t_buf = 1 - cx.src_buf;
       if (resampled) { st.src_buf = 1 - cx.src_buf; st.src_mode = 1; }
       st.frames_done += 1;
     }
     __syncwarp();
     if (threadIdx.x < 32 && (p.mode == 1 || blockIdx.x == 0))
-      pf_frame_tail<L>(p, cx, st, ts, blobs, trk, frame, iters, best_it, highest, kept, accept, resampled, cnt);
+      pf_frame_tail<L, SH>(p, cx, st, ts, blobs, trk, frame, iters, best_it, highest, kept, accept, resampled, cnt);
     pf_stamp(p, 8);
     pf_stamp(p, 9);
   }

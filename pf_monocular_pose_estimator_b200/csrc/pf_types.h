@@ -77,16 +77,6 @@ struct pf_kparams {
   int total_frames;               // frames uploaded (track mode)
   int coop;                       // 1: grid-wide cooperation (gridDim.x > 1)
   int want_mean;                  // compute weighted mean / covariance
-  // sharded single filter (modes 3-5): this handle owns global particles [goff, goff + N) of N_global
-  int goff, N_global;
-  int pass_it;                    // mode 3: iteration to run
-  int iters_total;                // modes 4/5: do/while iterations executed (all shards)
-  int q_local;                    // mode 5: local index of the winner
-  int idx_cap;                    // capacity of idx[] (slots this shard's sources may own)
-  long long S_fx;                 // modes 4/5: global weight sum, Q.30
-  long long rank_excl[3], rank_total[3];   // mode 4: (sum, max, min) aggregate of the lower ranks / of all ranks
-  long long* shard_partial;       // [8] per-stage results of this shard (device)
-  pf_cta_agg* warp_agg_g;         // [grid][PF_MAX_WARPS] per-warp prefix aggregates of the last score pass
   int cta_chunk;                  // particles owned by one CTA (multiple of 32 * warps per CTA); warp w owns the w-th part
   // particle state
   float4* pose0; float4* pose1;   // [tracker][3 planes][N]
@@ -115,4 +105,14 @@ struct pf_kparams {
   double min_ang, max_ang, min_tr, max_tr;   // minAngularNoise.. (track mode recomputes the ranges per frame)
   const uint32_t* rng_tab;        // [4*256]
   unsigned long long* timeline;   // optional [16] globaltimer stamps of the last frame (CTA 0, thread 0)
+  // sharded single filter (modes 3-5): this handle owns global particles [goff, goff + N) of N_global
+  int goff, N_global;
+  int pass_it;                    // mode 3: iteration to run
+  int iters_total;                // modes 4/5: do/while iterations executed (all shards)
+  int q_local;                    // mode 5: local index of the winner
+  int idx_cap;                    // capacity of idx[] (slots this shard's sources may own)
+  long long S_fx;                 // modes 4/5: global weight sum, Q.30
+  long long rank_excl[3], rank_total[3];   // mode 4: (sum, max, min) aggregate of the lower ranks / of all ranks
+  long long* shard_partial;       // [8] per-stage results of this shard (device)
+  pf_cta_agg* warp_agg_g;         // [grid][PF_MAX_WARPS] per-warp prefix aggregates of the last score pass
 };

@@ -177,20 +177,23 @@ void fill_kparams(const pfmpe_handle* h, pf_kparams& p)
 
 typedef void (*frames_kernel_t)(const pf_kparams);
 
-frames_kernel_t kernel_for(int L)
+template <bool SH>
+frames_kernel_t kernel_for_sh(int L)
 {
   switch (L) {
-    case 1: return pf_frames_kernel<1>;
-    case 2: return pf_frames_kernel<2>;
-    case 3: return pf_frames_kernel<3>;
-    case 4: return pf_frames_kernel<4>;
-    case 5: return pf_frames_kernel<5>;
-    case 6: return pf_frames_kernel<6>;
-    case 7: return pf_frames_kernel<7>;
-    case 8: return pf_frames_kernel<8>;
+    case 1: return pf_frames_kernel<1, SH>;
+    case 2: return pf_frames_kernel<2, SH>;
+    case 3: return pf_frames_kernel<3, SH>;
+    case 4: return pf_frames_kernel<4, SH>;
+    case 5: return pf_frames_kernel<5, SH>;
+    case 6: return pf_frames_kernel<6, SH>;
+    case 7: return pf_frames_kernel<7, SH>;
+    case 8: return pf_frames_kernel<8, SH>;
     default: return nullptr;
   }
 }
+
+frames_kernel_t kernel_for(int L, bool shard) { return shard ? kernel_for_sh<true>(L) : kernel_for_sh<false>(L); }
 
 // per-launch arguments of the sharded-filter stages (modes 3-5)
 struct ShardArgs {
@@ -205,7 +208,7 @@ struct ShardArgs {
 int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_frames, const ShardArgs* sa = nullptr)
 {
   const int N = h->cfg.n_particles;
-  frames_kernel_t k = kernel_for(h->cfg.n_leds);
+  frames_kernel_t k = kernel_for(h->cfg.n_leds, mode >= 3);
   if (!k) return fail(h, PFMPE_ERR_UNSUPPORTED, "n_leds must be 1..8");
   const size_t smem = (size_t)h->cfg.max_blobs * sizeof(pf_blob);
   bool grid_mode;

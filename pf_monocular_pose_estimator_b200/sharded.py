@@ -201,6 +201,11 @@ class ShardedFilter:
             p = poses[i] if isinstance(poses, list) else poses[r * self.n_loc:(r + 1) * self.n_loc]
             self.shards[i].set_particles(p)
 
+    def track_init(self, pose0, t0, pose1, t1):
+        """Every particle = pose1, filled on the device (no host-side particle array)."""
+        for h in self.shards:
+            h.track_init(pose0, t0, pose1, t1)
+
     # -- stages -------------------------------------------------------------------------
     def _score(self, it):
         for i, h in enumerate(self.shards):

@@ -8,7 +8,7 @@ out = subprocess.run(["nvdisasm", "-g", "-c", os.path.join(tmp, cub)], capture_o
 insec = False; cur = None; cnt = collections.Counter()
 for l in out.splitlines():
     if l.startswith("//---") and ".text." in l:
-        insec = "pf_frames_kernelILi5" in l or "pf_frame_tailILi5" in l
+        insec = "pf_frames_kernelILi5ELb0" in l or "pf_frame_tailILi5ELb0" in l
         continue
     if not insec: continue
     m = re.search(r'//## File "([^"]+)", line (\d+)', l)
