@@ -532,10 +532,14 @@ __device__ __noinline__ int pf_count_leq_dev(long long m, const pf_resample_cfg&
 // ("not found keeps the previous index", Q7).  The 32 sources of a warp step own one contiguous
 // slot range: the warp fills it with coalesced stores, each slot finding its source lane by a
 // 5-step shuffle search over the lanes' cumulative counts; a source with more than PF_FILL_WARP
-// slots is handed to the whole CTA after the walk.
+// slots is handed to the whole CTA after the walk (batch mode).  In grid mode a step that owns more
+// than PF_FILL_STEP slots is listed instead and filled by the whole grid after the stage's barrier
+// (pf_grid_fill).
 // ---------------------------------------------------------------------------------------
 #define PF_FILL_WARP 4096
 #define PF_FILL_LIST 32
+#define PF_FILL_STEP 256     /* grid mode: a step that owns more slots than this is listed for pf_grid_fill */
+#define PF_FILL_SPLIT 8192   /* ... in pieces of at most this many slots */
 
 struct pf_fill_list {
   int n;
@@ -640,9 +644,30 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
         const int Eprev = (k_prev == ktot ? Ng : k_prev) - kbase;
         const int own = Ecur - Eprev;                     // invalid lanes repeat the last prefix: 0
         if ((SH && p.mode == 4) && valid && n == N - 1) p.shard_partial[2] = (long long)Ecur + kbase;   // end of this rank's slots
-        const unsigned bigm = __ballot_sync(PF_FULL, own > PF_FILL_WARP);
-        if (bigm == 0u) {
-          const int E0 = __shfl_sync(PF_FULL, Eprev, 0), R = __shfl_sync(PF_FULL, Ecur, 31) - E0;
+        const int E0 = __shfl_sync(PF_FULL, Eprev, 0), R = __shfl_sync(PF_FULL, Ecur, 31) - E0;
+        bool listed = false;
+        if (p.coop && R > PF_FILL_STEP) {
+          // heavy step (grid mode): its slots are filled after the stage's barrier by whichever warp of
+          // the grid picks the entry up (pf_grid_fill); pieces of at most PF_FILL_SPLIT slots
+          const int parts = (R + PF_FILL_SPLIT - 1) / PF_FILL_SPLIT;
+          int q = 0;
+          if (lane == 0) {
+            q = atomicAdd(&p.gfill->n, parts);
+            if (q + parts > p.gfill_cap) { atomicSub(&p.gfill->n, parts); q = -1; }
+            else { p.gfill->ktot = ktot; p.gfill->kbase = kbase; acc.sum += parts; }   // the count rides on the stage's reduction
+          }
+          q = __shfl_sync(PF_FULL, q, 0);
+          if (q >= 0) {
+            for (int j = lane; j < parts; j += 32) {
+              const int off = j * PF_FILL_SPLIT;
+              p.gfill->ent[q + j] = make_int4(base, E0 + off, R - off < PF_FILL_SPLIT ? R - off : PF_FILL_SPLIT, 0);
+            }
+            listed = true;
+          }
+        }
+        const unsigned bigm = p.coop ? 0u : __ballot_sync(PF_FULL, own > PF_FILL_WARP);
+        if (listed) {
+        } else if (bigm == 0u) {
           for (int q0 = 0; q0 < R; q0 += 32) {            // warp-uniform trip count: every lane serves the shuffles
             const int k = E0 + q0 + lane;
             int lo = 0, hi = 31;                          // smallest lane whose Ecur > k
@@ -655,16 +680,23 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
             if (q0 + lane < R && (!SH || k < p.idx_cap)) idx[k] = base + lo;
           }
         } else {
-          // rare: a source owns more than PF_FILL_WARP slots; hand those to the whole CTA (list) and
-          // fill the rest lane by lane
+          // one CTA per filter (batch mode): a source with more than PF_FILL_WARP slots is handed to the
+          // whole CTA (list, after the walk); every other source of this step -- and list overflow -- is
+          // filled by the whole warp, one source at a time (warp-uniform loop: the mask is a ballot)
           const bool isbig = (bigm >> lane) & 1u;
-          int slot = -1;
+          bool handed = false;
           if (isbig) {
-            slot = atomicAdd(&fl->n, 1);
-            if (slot < PF_FILL_LIST) { fl->start[slot] = Eprev; fl->end[slot] = Ecur; fl->src[slot] = n; }
+            const int slot = atomicAdd(&fl->n, 1);
+            if (slot < PF_FILL_LIST) { fl->start[slot] = Eprev; fl->end[slot] = Ecur; fl->src[slot] = n; handed = true; }
           }
-          if (!isbig || slot >= PF_FILL_LIST)
-            for (int k = Eprev; k < Ecur && (!SH || k < p.idx_cap); ++k) idx[k] = n;
+          unsigned todo = __ballot_sync(PF_FULL, own > 0 && !handed);
+          while (todo) {
+            const int l = __ffs(todo) - 1;
+            todo &= todo - 1u;
+            const int s0 = __shfl_sync(PF_FULL, Eprev, l), s1 = __shfl_sync(PF_FULL, Ecur, l);
+            for (int k = s0 + lane; k < s1; k += 32)
+              if (!SH || k < p.idx_cap) idx[k] = base + l;
+          }
         }
       }
       carry.s += total;
@@ -682,6 +714,45 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
     }
   }
   return acc;
+}
+
+// Grid-wide part of the slot fill (grid mode).  A source-centric fill is only as balanced as the
+// offspring counts: after a few frames the heavy particles of a large filter are neighbours (they
+// descend from the same few particles), so a handful of warps would write most of idx[].  Heavy
+// steps are therefore listed during the walk and filled here, after the barrier that ends the
+// resampling stage, by all warps of the grid round-robin, with the same shuffle search over the 32
+// cumulative counts (re-read from kend[]).  The list length comes out of that stage's grid
+// reduction (pf_red.sum), so every CTA sees the same value and takes the same decision about the
+// extra barrier that orders this fill before the next score pass reads idx[].
+__device__ __noinline__ void pf_grid_fill(const pf_kparams& p, int trk, pf_bar& bar, int n, int Ng, bool check_cap)
+{
+  const int N = p.N;
+  const int ktot = __ldcg(&p.gfill->ktot), kbase = __ldcg(&p.gfill->kbase);
+  const int* kend = p.kend + (size_t)trk * N;
+  int* idx = p.idx + (size_t)trk * N;
+  const int lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  const int tw = (int)gridDim.x * nw;
+#pragma unroll 1
+  for (int q = (int)blockIdx.x + (int)(threadIdx.x >> 5) * (int)gridDim.x; q < n; q += tw) {   // neighbouring entries -> different SMs
+    const int4 e = __ldcg(&p.gfill->ent[q]);
+    const int nn = e.x + lane < N ? e.x + lane : N - 1;
+    const int ke = __ldcg(kend + nn);
+    const int Ecur = (ke == ktot ? Ng : ke) - kbase;
+#pragma unroll 1
+    for (int q0 = 0; q0 < e.z; q0 += 32) {
+      const int k = e.y + q0 + lane;
+      int lo = 0, hi = 31;
+#pragma unroll
+      for (int t = 0; t < 5; ++t) {
+        const int mid = (lo + hi) >> 1;
+        const int v = __shfl_sync(PF_FULL, Ecur, mid);
+        if (v > k) hi = mid; else lo = mid + 1;
+      }
+      if (q0 + lane < e.z && (!check_cap || k < p.idx_cap)) idx[k] = e.x + lo;
+    }
+  }
+  pf_grid_barrier(p, bar);
+  if (blockIdx.x == 0 && threadIdx.x == 0) p.gfill->n = 0;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -956,6 +1027,7 @@ __global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid
       cnt = pf_stage_resample<SH>(p, cx, tab, trk, kept.sum, iters, scr, &fill);
       pf_stamp(p, 5);
       cnt = pf_grid_reduce(cnt, red_smem, p, bar, nullptr);
+      if (p.coop && cnt.sum > 0) pf_grid_fill(p, trk, bar, (int)cnt.sum, SH ? p.N_global : N, SH);
       pf_stamp(p, 6);
     }
 

@@ -65,6 +65,17 @@ struct pf_cta_agg {
   long long s, mx, mn, pad;
 };
 
+// grid mode: heavy steps of the current resampling, filled by the whole grid (pf_grid_fill).
+// ent = (first source of the step, first slot, number of slots, 0)
+struct pf_gfill {
+  int n, ktot, kbase, pad;
+#if defined(__CUDACC__)
+  int4 ent[1];
+#else
+  int ent[4];
+#endif
+};
+
 struct pf_kparams {
   int N;                          // particles per tracker
   int n_trackers;
@@ -105,6 +116,8 @@ struct pf_kparams {
   double min_ang, max_ang, min_tr, max_tr;   // minAngularNoise.. (track mode recomputes the ranges per frame)
   const uint32_t* rng_tab;        // [4*256]
   unsigned long long* timeline;   // optional [16] globaltimer stamps of the last frame (CTA 0, thread 0)
+  pf_gfill* gfill;                // grid mode: list of the heavy steps of the current resampling
+  int gfill_cap;                  // entries it can hold
   // sharded single filter (modes 3-5): this handle owns global particles [goff, goff + N) of N_global
   int goff, N_global;
   int pass_it;                    // mode 3: iteration to run

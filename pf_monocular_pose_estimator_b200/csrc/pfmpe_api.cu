@@ -64,6 +64,8 @@ struct pfmpe_handle {
   int *kend = nullptr, *idx = nullptr, *gather_idx = nullptr;
   pf_cta_agg* cta_agg = nullptr;
   pf_accum* accum = nullptr;
+  pf_gfill* gfill = nullptr;
+  int gfill_cap = 0;
   unsigned char* inbox = nullptr;       // [fconst x n_trackers | blobs x n_trackers x max_blobs x 2]
   pf_frame_const* fconst = nullptr;     // = inbox
   double* blobs = nullptr;              // = inbox + ...
@@ -134,7 +136,7 @@ void free_all(pfmpe_handle* h)
   cudaFree(h->pose0); cudaFree(h->pose1); cudaFree(h->gather_tmp); cudaFree(h->w); cudaFree(h->kend);
   cudaFree(h->idx); cudaFree(h->gather_idx); cudaFree(h->cta_agg); cudaFree(h->accum);
   cudaFree(h->inbox); cudaFree(h->state); cudaFree(h->result); cudaFree(h->obj_f); cudaFree(h->obj_d);
-  cudaFree(h->rng_tab); cudaFree(h->timeline); cudaFree(h->warp_agg_g); cudaFree(h->shard_partial);
+  cudaFree(h->rng_tab); cudaFree(h->timeline); cudaFree(h->warp_agg_g); cudaFree(h->shard_partial); cudaFree(h->gfill);
   if (h->seq.owned) { cudaFree(h->seq.blobs); cudaFree(h->seq.counts); cudaFree(h->seq.times); cudaFree(h->seq.seeds); }
   cudaFree(h->seq.result); cudaFree(h->seq.fc_log);
   if (h->h_inbox) cudaFreeHost(h->h_inbox);
@@ -153,7 +155,7 @@ void fill_kparams(const pfmpe_handle* h, pf_kparams& p)
   p.D_max = h->cfg.max_blobs;
   p.want_mean = (h->cfg.flags & PFMPE_FLAG_MEAN_COV) ? 1 : 0;
   p.pose0 = h->pose0; p.pose1 = h->pose1; p.w = h->w; p.kend = h->kend; p.idx = h->idx;
-  p.cta_agg = h->cta_agg; p.accum = h->accum;
+  p.cta_agg = h->cta_agg; p.accum = h->accum; p.gfill = h->gfill; p.gfill_cap = h->gfill_cap;
   p.fconst = h->fconst; p.state = h->state;
   p.obj_f = h->obj_f; p.obj_d = h->obj_d;
   for (int i = 0; i < 9; ++i) { p.K9d[i] = h->K[i]; p.K9f[i] = (float)h->K[i]; }
@@ -398,6 +400,9 @@ int pfmpe_create(const pfmpe_config* cfg, pfmpe_handle** out)
   PF_TRY(dev_alloc(&h->gather_idx, N));
   PF_TRY(dev_alloc(&h->cta_agg, (size_t)PF_MAX_GRID));
   PF_TRY(dev_alloc(&h->accum, 4));
+  h->gfill_cap = (int)(N / 128 + 4096);   // > N / PF_FILL_STEP + N / PF_FILL_SPLIT pieces
+  PF_TRY(cudaMalloc((void**)&h->gfill, sizeof(pf_gfill) + (size_t)h->gfill_cap * 16));
+  PF_TRY(cudaMemset(h->gfill, 0, sizeof(pf_gfill)));
   h->blobs_off = (T * sizeof(pf_frame_const) + 255) / 256 * 256;
   h->inbox_bytes = h->blobs_off + T * (size_t)cfg->max_blobs * 2 * sizeof(double);
   PF_TRY(cudaMalloc((void**)&h->inbox, h->inbox_bytes));

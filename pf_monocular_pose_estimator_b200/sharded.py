@@ -185,6 +185,17 @@ class ShardedFilter:
         self.partials = torch.zeros((len(self.shards), 8), dtype=torch.int64, device=self.dev)
         self.passes = 0          # score passes launched so far (per shard)
         self.last = None
+        self.stage_s = None      # set to {} to collect per-stage wall times (synchronises after every stage)
+
+    def _mark(self, name, t0):
+        """Profiling aid: with stage_s set, wait for the device and book the time since t0 under `name`."""
+        if self.stage_s is None:
+            return 0.0
+        import time
+        self.torch.cuda.synchronize(self.dev)
+        t1 = time.perf_counter()
+        self.stage_s[name] = self.stage_s.get(name, 0.0) + (t1 - t0)
+        return t1
 
     def close(self):
         for h in self.shards:
@@ -208,16 +219,22 @@ class ShardedFilter:
 
     # -- stages -------------------------------------------------------------------------
     def _score(self, it):
+        t = self._mark("other", self._t)
         for i, h in enumerate(self.shards):
             h.shard_score(it, self.partials[i].data_ptr())
         self.passes += 1
-        return reduce_pass(self.comm.gather(self.partials))
+        t = self._mark("score", t)
+        r = reduce_pass(self.comm.gather(self.partials))
+        self._t = self._mark("gather", t)
+        return r
 
     def update(self, img, T_cur, T_pred, P, Cm, isi, dt, seed, tracker=0):
         torch = self.torch
         keep = []
         fi = capi.make_frame_in(img, T_cur, T_pred, P, Cm, isi, dt, seed, keep)
         D = int(fi.n_image_points)
+        import time
+        self._t = time.perf_counter() if self.stage_s is not None else 0.0
         for h in self.shards:
             h.shard_begin_frame(fi)
 
@@ -249,9 +266,12 @@ class ShardedFilter:
         max_count = 0
         if resampled:
             lower, total = lower_aggregates(kept["aggs"])
+            t = self._mark("other", self._t)
             for i, r_ in enumerate(self.comm.local):
                 self.shards[i].shard_resample(S, iters, lower[r_], total, self.partials[i].data_ptr())
+            t = self._mark("resample", t)
             part = self.comm.gather(self.partials)
+            t = self._mark("gather", t)
             cntkey = int(np.ascontiguousarray(part[:, 0]).view(np.uint64).max())
             q = (~cntkey) & 0xFFFFFFFF                        # :686 first max of counterMeas
             max_count = cntkey >> 32
@@ -264,11 +284,14 @@ class ShardedFilter:
                 buf = torch.empty((cnt, 12), dtype=torch.float32, device=self.dev)
                 self.shards[i].shard_export(int(first[r_]), int(first[r_]), cnt, buf.data_ptr())
                 rows.append(buf)
+            t = self._mark("export", t)
             new = self.comm.exchange(rows, send, self.n_loc)
+            t = self._mark("exchange", t)
             for i, h in enumerate(self.shards):
                 if new[i].shape[0] != self.n_loc:
                     raise RuntimeError("rebalance delivered %d rows, expected %d" % (new[i].shape[0], self.n_loc))
                 h.shard_import(new[i].data_ptr())
+            self._t = self._mark("import", t)
             self._rows = (rows, new)                          # keep alive until the stream has consumed them
         else:
             q = arg_min if S < 0 else arg_max                 # :714 on the normalised weights
@@ -283,6 +306,7 @@ class ShardedFilter:
             packed[16] = c.size // 2
             packed[17:17 + c.size] = c
         packed = self.comm.bcast(packed, owner)
+        self._t = self._mark("winner", self._t)
         nc = int(packed[16])
         out = dict(status=1 if accept else 4, iterations=iters, best_iteration=best_it, resampled=int(resampled),
                    highest_prob=float(highest), weight_sum=S / Q30,

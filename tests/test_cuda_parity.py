@@ -147,6 +147,31 @@ def test_dominant_particles_fill_tiers(N, mode):
     h.close()
 
 
+def test_huge_slot_ranges_are_filled_by_the_grid():
+    """Three survivors of 400k particles own > 65536 output slots each: grid-wide fill after the stage barrier
+    (plus the extra barrier before the next frame reads idx)."""
+    N = 400000
+    fi = frame_inputs(2000, frame=14)
+    E = np.repeat(fi["E"][:1], N, axis=0)
+    E[:, 0, 3] += 5.0
+    E[1000] = fi["E"][3]
+    E[1001] = fi["E"][4]
+    E[250000] = fi["E"][5]
+    fi["E"] = E
+    ora = _oracle(fi, N)
+    assert ora["resampled"] == 1
+    h = make_handle(fi, N)
+    got = run_frame(h, fi)
+    res = parity.check_frame(fi, got, ora)
+    assert res["index_mismatch"] == 0
+    assert got["count"].max() > 65536
+    assert (np.bincount(got["idx"], minlength=N) == got["count"]).all()
+    # the next frame reads its sources through idx[] inside the same tracker state
+    out2 = h.update(fi["img"], fi["T_cur"], fi["T_pred"], fi["P"], fi["Cm"], fi["isi"], fi["dt"], fi["seed"] + 1)
+    assert out2["status"] == 1
+    h.close()
+
+
 def test_grid_and_batch_paths_are_bit_identical():
     # exact fixed-point sums + exact thresholds: any decomposition gives the same weights, kend, indices
     N = 3000

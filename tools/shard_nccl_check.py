@@ -29,30 +29,48 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--particles", type=int, default=1 << 18)
     ap.add_argument("--frames", type=int, default=6)
+    ap.add_argument("--no-compare", action="store_true", help="timing only (large filters: the getters copy everything to the host)")
+    ap.add_argument("--stages", action="store_true", help="per-stage wall times (synchronises after every stage)")
     a = ap.parse_args()
-    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ.get("LOCAL_RANK", 0))
+    rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     N = a.particles // world * world
     n_loc = N // world
     sc = scenes.Scene(0)
     D = sc.blobs(0).shape[0] + 4
-    ref = capi.Handle(N, n_trackers=1, n_leds=5, max_blobs=D, device=local)
-    ref.configure(sc.markers, sc.K, sc.params)
-    sh = sharded.ShardedFilter(N, sharded.TorchDist(), n_leds=5, max_blobs=D, device=local)
+    cmp_ = not a.no_compare
+    if cmp_:
+        ref = capi.Handle(N, n_trackers=1, n_leds=5, max_blobs=D, device=local)
+        ref.configure(sc.markers, sc.K, sc.params)
+        ta = HostTracker(ref, sc, init_particles=False)
+        ref.track_init(sc.pose(0), sc.time(0), sc.pose(1), sc.time(1))
+    sh = sharded.ShardedFilter(N, sharded.TorchDist() if world > 1 else sharded.Loopback(1), n_leds=5, max_blobs=D, device=local)
     sh.configure(sc.markers, sc.K, sc.params)
-    ta = HostTracker(ref, sc)
     tb = HostTracker(sh, sc, init_particles=False)
-    sh.set_particles([np.repeat(tb.cur[None], n_loc, axis=0)])
+    sh.track_init(sc.pose(0), sc.time(0), sc.pose(1), sc.time(1))
     bad, t_sh = 0, []
+    if a.stages:
+        sh.stage_s = {}
     for f in range(2, 2 + a.frames):
-        ra = ta.frame(f)
+        if cmp_:
+            ra = ta.frame(f)
         torch.cuda.synchronize()
-        dist.barrier()
+        if world > 1:
+            dist.barrier()
         t0 = time.perf_counter()
         rb = tb.frame(f)
         torch.cuda.synchronize()
         t_sh.append(time.perf_counter() - t0)
+        if a.stages and rank == 0:
+            w = sh.weights(False)
+            nz = np.flatnonzero(w > 0)
+            print("frame", f, {k: round(1e3 * v, 3) for k, v in sh.stage_s.items()}, "max_count", rb["max_count"], "iters", rb["iterations"],
+                  "nonzero", nz.size, "span", (int(nz[0]), int(nz[-1])) if nz.size else None, "wmax", float(w.max()), flush=True)
+            sh.stage_s = {}
+        if not cmp_:
+            continue
         for k in FIELDS:
             bad += int(ra[k] != rb[k])
         bad += int(not (ra["pose"] == rb["pose"]).all()) + int(not (ra["correspondences"] == rb["correspondences"]).all())
@@ -62,11 +80,14 @@ def main():
         if ra["resampled"]:
             bad += int(not (ref.particles(1)[sl] == sh.particles(1)).all())
     t = torch.tensor([bad], device="cuda")
-    dist.all_reduce(t)
+    if world > 1:
+        dist.all_reduce(t)
     if rank == 0:
         print(json.dumps(dict(check="shard_nccl", world=world, particles=N, frames=a.frames, mismatches=int(t.item()),
-                              ms_per_frame_host_loop=round(1e3 * float(np.median(t_sh)), 3))))
-    dist.destroy_process_group()
+                              ms_per_frame_host_loop=round(1e3 * float(np.median(t_sh)), 3),
+                              all_ms=[round(1e3 * v, 2) for v in t_sh])))
+    if world > 1:
+        dist.destroy_process_group()
     sys.exit(1 if int(t.item()) else 0)
 
 
