@@ -229,8 +229,11 @@ int pfmpe_shard_resample(pfmpe_handle* h, int64_t sum_fx, int iterations, const 
 /* rows (12 floats: rows 0..2 of the pose) of the output slots [first_slot, first_slot + count);
  * first_owned_slot = partial[1] of pfmpe_shard_resample */
 int pfmpe_shard_export(pfmpe_handle* h, int64_t first_owned_slot, int64_t first_slot, int64_t count, void* d_rows);
-/* n_particles rebalanced rows become this shard's particle set for the next frame */
-int pfmpe_shard_import(pfmpe_handle* h, const void* d_rows);
+/* output slots [first_slot, first_slot + count) stay on this rank: they become local particles
+ * [local_offset, local_offset + count) of the next frame's set, device to device, no row buffer */
+int pfmpe_shard_keep(pfmpe_handle* h, int64_t first_owned_slot, int64_t first_slot, int64_t count, int64_t local_offset);
+/* `count` rows received from other ranks become local particles [local_offset, local_offset + count) */
+int pfmpe_shard_import(pfmpe_handle* h, const void* d_rows, int64_t local_offset, int64_t count);
 /* pose + correspondences (:687-691 / :714-716) of the local particle `local_index` of the last pass;
  * only winner_pose / correspondences / n_correspondences of `out` are meaningful */
 int pfmpe_shard_winner(pfmpe_handle* h, int local_index, pfmpe_frame_out* out);

@@ -25,7 +25,7 @@ EXPORTS = [
     "pfmpe_track_init", "pfmpe_track_upload", "pfmpe_track_attach", "pfmpe_track_run", "pfmpe_track_replay", "pfmpe_track_results",
     "pfmpe_track_frame_host", "pfmpe_track_frame_host_batch", "pfmpe_track_sequence_host",
     "pfmpe_shard_configure", "pfmpe_shard_begin_frame", "pfmpe_shard_score", "pfmpe_shard_resample",
-    "pfmpe_shard_export", "pfmpe_shard_import", "pfmpe_shard_winner",
+    "pfmpe_shard_export", "pfmpe_shard_keep", "pfmpe_shard_import", "pfmpe_shard_winner",
     "pfmpe_set_stream", "pfmpe_sync", "pfmpe_last_launch_ms", "pfmpe_launch_count", "pfmpe_launch_info", "pfmpe_debug_timeline",
 ]
 
@@ -125,7 +125,8 @@ def lib():
         L.pfmpe_shard_score.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         L.pfmpe_shard_resample.argtypes = [C.c_void_p, C.c_int64, C.c_int, _i3, _i3, C.c_void_p]
         L.pfmpe_shard_export.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]
-        L.pfmpe_shard_import.argtypes = [C.c_void_p, C.c_void_p]
+        L.pfmpe_shard_import.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64]
+        L.pfmpe_shard_keep.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64]
         L.pfmpe_shard_winner.argtypes = [C.c_void_p, C.c_int, C.POINTER(FrameOut)]
         L.pfmpe_set_stream.argtypes = [C.c_void_p, C.c_void_p]
         L.pfmpe_sync.argtypes = [C.c_void_p]
@@ -344,8 +345,11 @@ class Handle:
         self._chk(lib().pfmpe_shard_export(self._h, int(first_owned_slot), int(first_slot), int(count),
                                            C.c_void_p(int(d_rows))))
 
-    def shard_import(self, d_rows):
-        self._chk(lib().pfmpe_shard_import(self._h, C.c_void_p(int(d_rows))))
+    def shard_import(self, d_rows, local_offset, count):
+        self._chk(lib().pfmpe_shard_import(self._h, C.c_void_p(int(d_rows)), int(local_offset), int(count)))
+
+    def shard_keep(self, first_owned_slot, first_slot, count, local_offset):
+        self._chk(lib().pfmpe_shard_keep(self._h, int(first_owned_slot), int(first_slot), int(count), int(local_offset)))
 
     def shard_winner(self, local_index):
         o = FrameOut()

@@ -1085,14 +1085,30 @@ __global__ void __launch_bounds__(PF_BLOCK) pf_shard_export_kernel(const float4*
   rows[3 * i + 2] = T[2 * (size_t)N + s];
 }
 
-// Sharded filter: the rebalanced rows become the particle set read by the next frame.
-__global__ void __launch_bounds__(PF_BLOCK) pf_shard_import_kernel(const float4* rows, int N, float4* dst)
+// Sharded filter: rows received from other ranks become local particles [off, off + count) of the
+// set read by the next frame.
+__global__ void __launch_bounds__(PF_BLOCK) pf_shard_import_kernel(const float4* rows, int N, int off, int count, float4* dst)
 {
-  const int n = blockIdx.x * PF_BLOCK + threadIdx.x;
-  if (n >= N) return;
-  dst[n] = rows[3 * (size_t)n];
-  dst[(size_t)N + n] = rows[3 * (size_t)n + 1];
-  dst[2 * (size_t)N + n] = rows[3 * (size_t)n + 2];
+  const int i = blockIdx.x * PF_BLOCK + threadIdx.x;
+  if (i >= count) return;
+  const int n = off + i;
+  dst[n] = rows[3 * (size_t)i];
+  dst[(size_t)N + n] = rows[3 * (size_t)i + 1];
+  dst[2 * (size_t)N + n] = rows[3 * (size_t)i + 2];
+}
+
+// Sharded filter: output slots that stay on this rank go straight from T (through idx) to the
+// next frame's particle set, plane to plane: slot first + i -> local particle off + i.
+__global__ void __launch_bounds__(PF_BLOCK) pf_shard_keep_kernel(const float4* T, const int* idx, int N, long long kbase,
+                                                                 long long first, int count, int off, float4* dst)
+{
+  const int i = blockIdx.x * PF_BLOCK + threadIdx.x;
+  if (i >= count) return;
+  const int s = idx[first + i - kbase];
+  const int n = off + i;
+  dst[n] = T[s];
+  dst[(size_t)N + n] = T[(size_t)N + s];
+  dst[2 * (size_t)N + n] = T[2 * (size_t)N + s];
 }
 
 #endif  // __CUDACC__

@@ -1096,17 +1096,37 @@ int pfmpe_shard_export(pfmpe_handle* h, int64_t first_owned_slot, int64_t first_
   return PFMPE_OK;
 }
 
-int pfmpe_shard_import(pfmpe_handle* h, const void* d_rows)
+int pfmpe_shard_import(pfmpe_handle* h, const void* d_rows, int64_t local_offset, int64_t count)
 {
-  if (!h || !d_rows) return PFMPE_ERR_INVALID;
+  if (!h || count < 0 || (count > 0 && !d_rows)) return PFMPE_ERR_INVALID;
   int rc = shard_ready(h);
   if (rc) return rc;
   const size_t N = (size_t)h->cfg.n_particles;
-  const int blocks = (int)((N + PF_BLOCK - 1) / PF_BLOCK);
-  pf_shard_import_kernel<<<blocks, PF_BLOCK, 0, h->stream>>>(static_cast<const float4*>(d_rows), (int)N, h->pose0);
+  if (local_offset < 0 || local_offset + count > (int64_t)N) return fail(h, PFMPE_ERR_INVALID, "rows outside this shard");
+  h->particles_set[0] = 1;
+  if (count == 0) return PFMPE_OK;
+  const int blocks = (int)((count + PF_BLOCK - 1) / PF_BLOCK);
+  pf_shard_import_kernel<<<blocks, PF_BLOCK, 0, h->stream>>>(static_cast<const float4*>(d_rows), (int)N, (int)local_offset,
+                                                            (int)count, h->pose0);
   PF_CUDA(h, cudaGetLastError());
   h->launches += 1;
-  h->particles_set[0] = 1;
+  return PFMPE_OK;
+}
+
+int pfmpe_shard_keep(pfmpe_handle* h, int64_t first_owned_slot, int64_t first_slot, int64_t count, int64_t local_offset)
+{
+  if (!h || count < 0 || first_slot < first_owned_slot) return PFMPE_ERR_INVALID;
+  int rc = shard_ready(h);
+  if (rc) return rc;
+  const size_t N = (size_t)h->cfg.n_particles;
+  if (local_offset < 0 || local_offset + count > (int64_t)N) return fail(h, PFMPE_ERR_INVALID, "slots outside this shard");
+  if (first_slot - first_owned_slot + count > (int64_t)h->n_global) return fail(h, PFMPE_ERR_INVALID, "slot range outside this shard's output");
+  if (count == 0) return PFMPE_OK;
+  const int blocks = (int)((count + PF_BLOCK - 1) / PF_BLOCK);
+  pf_shard_keep_kernel<<<blocks, PF_BLOCK, 0, h->stream>>>(h->pose1, h->idx, (int)N, first_owned_slot, first_slot, (int)count,
+                                                          (int)local_offset, h->pose0);
+  PF_CUDA(h, cudaGetLastError());
+  h->launches += 1;
   return PFMPE_OK;
 }
 

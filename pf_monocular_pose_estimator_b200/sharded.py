@@ -11,8 +11,9 @@ kernel through the C ABI (pfmpe_shard_*, include/pfmpe.h) and this module owns t
   decision     -> do/while exit, kept iteration, accept test: host scalars, same on every rank (:608-633)
   resampling   -> every rank resamples its own sources against GLOBAL strata (global slot numbers, the
                   global RNG stream); all_gather of (count key, first owned slot, end slot)
-  rebalance    -> all_to_all of the produced rows so that every rank again owns n_global / world
-                  particles in global slot order ("global resample")
+  rebalance    -> every rank again owns n_global / world particles in global slot order ("global
+                  resample"): slots that stay on their rank are copied on the device, the others
+                  travel in one all_to_all
   winner       -> first most-resampled particle across ranks (:685-686); its owner computes pose and
                   correspondences, broadcast to the others
 
@@ -109,17 +110,17 @@ class Loopback:
     def gather(self, partials):
         return partials.cpu().numpy()
 
-    def exchange(self, send_rows, send, n_loc):
+    def exchange(self, send_rows, send, outs):
+        """send_rows[r]: rows leaving shard r ordered by destination; outs[d]: rows arriving, ordered by source."""
         import torch
-        out = []
         for d in self.local:
             parts = []
             for r in self.local:
                 off, c = sum(send[r][:d]), send[r][d]
                 if c:
                     parts.append(send_rows[r][off:off + c])
-            out.append(torch.cat(parts) if len(parts) != 1 else parts[0].contiguous())
-        return out
+            if parts:
+                torch.cat(parts, out=outs[d])
 
     def bcast(self, arr, owner):
         return arr
@@ -141,14 +142,11 @@ class TorchDist:
         self.dist.all_gather_into_tensor(out, partials.reshape(-1, partials.shape[1]), group=self.group)
         return out.cpu().numpy()
 
-    def exchange(self, send_rows, send, n_loc):
-        import torch
+    def exchange(self, send_rows, send, outs):
         r = self.rank
-        src = send_rows[0]
         recv = [send[q][r] for q in range(self.world)]
-        out = torch.empty((sum(recv),) + tuple(src.shape[1:]), dtype=src.dtype, device=src.device)
-        self.dist.all_to_all_single(out, src, output_split_sizes=recv, input_split_sizes=list(send[r]), group=self.group)
-        return [out]
+        self.dist.all_to_all_single(outs[0], send_rows[0], output_split_sizes=recv, input_split_sizes=list(send[r]),
+                                    group=self.group)
 
     def bcast(self, arr, owner):
         import torch
@@ -183,9 +181,19 @@ class ShardedFilter:
             h.set_stream(torch.cuda.current_stream(self.dev).cuda_stream)
             self.shards.append(h)
         self.partials = torch.zeros((len(self.shards), 8), dtype=torch.int64, device=self.dev)
+        self._bufs = {}
         self.passes = 0          # score passes launched so far (per shard)
         self.last = None
         self.stage_s = None      # set to {} to collect per-stage wall times (synchronises after every stage)
+
+    def _buffer(self, kind, i, rows):
+        """Grow-only row buffers (12 floats per row): no allocator traffic in the frame loop."""
+        key = (kind, i)
+        buf = self._bufs.get(key)
+        if buf is None or buf.shape[0] < rows:
+            buf = self.torch.empty((max(rows + rows // 4, 1024), 12), dtype=self.torch.float32, device=self.dev)
+            self._bufs[key] = buf
+        return buf[:rows]
 
     def _mark(self, name, t0):
         """Profiling aid: with stage_s set, wait for the device and book the time since t0 under `name`."""
@@ -278,21 +286,32 @@ class ShardedFilter:
             first, end = part[:, 1], part[:, 2]
             check_tiling(first, end, self.N)
             send = slot_partition(first, end, self.n_loc, self.W)
+            # slots that stay on their rank go plane to plane on the device; only the rest is exchanged
+            send_x = [[0 if d == r_ else c for d, c in enumerate(row)] for r_, row in enumerate(send)]
             rows = []
             for i, r_ in enumerate(self.comm.local):
-                cnt = int(end[r_] - first[r_])
-                buf = torch.empty((cnt, 12), dtype=torch.float32, device=self.dev)
-                self.shards[i].shard_export(int(first[r_]), int(first[r_]), cnt, buf.data_ptr())
+                lo, hi, f0, e0 = r_ * self.n_loc, (r_ + 1) * self.n_loc, int(first[r_]), int(end[r_])
+                below = (f0, max(f0, min(e0, lo)))                 # to lower ranks
+                above = (min(e0, max(f0, hi)), e0)                 # to higher ranks
+                nb, na = below[1] - below[0], above[1] - above[0]
+                assert nb + na == sum(send_x[r_]) and nb + na + send[r_][r_] == e0 - f0
+                buf = self._buffer("send", i, nb + na)
+                self.shards[i].shard_export(f0, below[0], nb, buf.data_ptr())
+                self.shards[i].shard_export(f0, above[0], na, buf.data_ptr() + 48 * nb)
+                self.shards[i].shard_keep(f0, below[1], send[r_][r_], below[1] - lo if send[r_][r_] else 0)
                 rows.append(buf)
             t = self._mark("export", t)
-            new = self.comm.exchange(rows, send, self.n_loc)
+            outs = [self._buffer("recv", i, sum(send_x[q][r_] for q in range(self.W))) for i, r_ in enumerate(self.comm.local)]
+            self.comm.exchange(rows, send_x, outs)
             t = self._mark("exchange", t)
-            for i, h in enumerate(self.shards):
-                if new[i].shape[0] != self.n_loc:
-                    raise RuntimeError("rebalance delivered %d rows, expected %d" % (new[i].shape[0], self.n_loc))
-                h.shard_import(new[i].data_ptr())
+            for i, r_ in enumerate(self.comm.local):
+                a = sum(send_x[q][r_] for q in range(r_))
+                b = sum(send_x[q][r_] for q in range(r_ + 1, self.W))
+                if a + send[r_][r_] + b != self.n_loc:
+                    raise RuntimeError("rebalance delivers %d rows to shard %d, expected %d" % (a + send[r_][r_] + b, r_, self.n_loc))
+                self.shards[i].shard_import(outs[i].data_ptr(), 0, a)
+                self.shards[i].shard_import(outs[i].data_ptr() + 48 * a, self.n_loc - b, b)
             self._t = self._mark("import", t)
-            self._rows = (rows, new)                          # keep alive until the stream has consumed them
         else:
             q = arg_min if S < 0 else arg_max                 # :714 on the normalised weights
 

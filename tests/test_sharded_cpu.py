@@ -93,8 +93,9 @@ def _gloo_worker(rank, world, port, q):
         cnt = end[rank] - first[rank]
         rows = (torch.arange(first[rank], end[rank], dtype=torch.float32)[:, None] * torch.ones((1, 12))).contiguous()
         assert rows.shape == (cnt, 12)
-        new = comm.exchange([rows], send, n_loc)[0]
-        ok = ok and new.shape == (n_loc, 12) and bool((new[:, 0] == torch.arange(rank * n_loc, (rank + 1) * n_loc)).all())
+        new = torch.empty((n_loc, 12))
+        comm.exchange([rows], send, [new])
+        ok = ok and bool((new[:, 0] == torch.arange(rank * n_loc, (rank + 1) * n_loc)).all())
         b = comm.bcast(np.arange(5.0) * (rank + 1), 1)
         ok = ok and (b == np.arange(5.0) * 2).all()
         q.put((rank, bool(ok)))
