@@ -234,6 +234,19 @@ int pfmpe_shard_export(pfmpe_handle* h, int64_t first_owned_slot, int64_t first_
 int pfmpe_shard_keep(pfmpe_handle* h, int64_t first_owned_slot, int64_t first_slot, int64_t count, int64_t local_offset);
 /* `count` rows received from other ranks become local particles [local_offset, local_offset + count) */
 int pfmpe_shard_import(pfmpe_handle* h, const void* d_rows, int64_t local_offset, int64_t count);
+/* Peer-memory rebalance (replaces export / all_to_all / keep / import by ONE kernel): every rank
+ * publishes the base of its next-frame particle planes (pfmpe_shard_local_ptr within a process,
+ * pfmpe_shard_ipc_export -> pfmpe_shard_ipc_open across processes: CUDA IPC, NVLink peer access),
+ * pfmpe_shard_set_peers installs the table of all `world` bases (rank order, equal shards) and
+ * pfmpe_shard_scatter writes every output slot this rank produced -- `count` slots from
+ * first_owned_slot, both from pfmpe_shard_resample's partial -- into the owning rank's planes
+ * with local or NVLink peer stores.  The caller orders the scatter of all ranks before the next
+ * pfmpe_shard_score (a barrier on the ranks' streams). */
+int pfmpe_shard_local_ptr(pfmpe_handle* h, void** d_ptr);
+int pfmpe_shard_ipc_export(pfmpe_handle* h, unsigned char handle[64]);
+int pfmpe_shard_ipc_open(pfmpe_handle* h, const unsigned char handle[64], void** d_ptr);
+int pfmpe_shard_set_peers(pfmpe_handle* h, int world, void* const* d_ptrs);
+int pfmpe_shard_scatter(pfmpe_handle* h, int64_t first_owned_slot, int64_t count);
 /* pose + correspondences (:687-691 / :714-716) of the local particle `local_index` of the last pass;
  * only winner_pose / correspondences / n_correspondences of `out` are meaningful */
 int pfmpe_shard_winner(pfmpe_handle* h, int local_index, pfmpe_frame_out* out);

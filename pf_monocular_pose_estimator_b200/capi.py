@@ -26,6 +26,7 @@ EXPORTS = [
     "pfmpe_track_frame_host", "pfmpe_track_frame_host_batch", "pfmpe_track_sequence_host",
     "pfmpe_shard_configure", "pfmpe_shard_begin_frame", "pfmpe_shard_score", "pfmpe_shard_resample",
     "pfmpe_shard_export", "pfmpe_shard_keep", "pfmpe_shard_import", "pfmpe_shard_winner",
+    "pfmpe_shard_local_ptr", "pfmpe_shard_ipc_export", "pfmpe_shard_ipc_open", "pfmpe_shard_set_peers", "pfmpe_shard_scatter",
     "pfmpe_set_stream", "pfmpe_sync", "pfmpe_last_launch_ms", "pfmpe_launch_count", "pfmpe_launch_info", "pfmpe_debug_timeline",
 ]
 
@@ -127,6 +128,11 @@ def lib():
         L.pfmpe_shard_export.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]
         L.pfmpe_shard_import.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64]
         L.pfmpe_shard_keep.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64]
+        L.pfmpe_shard_local_ptr.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
+        L.pfmpe_shard_ipc_export.argtypes = [C.c_void_p, C.c_char_p]
+        L.pfmpe_shard_ipc_open.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_void_p)]
+        L.pfmpe_shard_set_peers.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]
+        L.pfmpe_shard_scatter.argtypes = [C.c_void_p, C.c_int64, C.c_int64]
         L.pfmpe_shard_winner.argtypes = [C.c_void_p, C.c_int, C.POINTER(FrameOut)]
         L.pfmpe_set_stream.argtypes = [C.c_void_p, C.c_void_p]
         L.pfmpe_sync.argtypes = [C.c_void_p]
@@ -350,6 +356,28 @@ class Handle:
 
     def shard_keep(self, first_owned_slot, first_slot, count, local_offset):
         self._chk(lib().pfmpe_shard_keep(self._h, int(first_owned_slot), int(first_slot), int(count), int(local_offset)))
+
+    def shard_local_ptr(self):
+        q = C.c_void_p()
+        self._chk(lib().pfmpe_shard_local_ptr(self._h, C.byref(q)))
+        return int(q.value)
+
+    def shard_ipc_export(self):
+        buf = C.create_string_buffer(64)
+        self._chk(lib().pfmpe_shard_ipc_export(self._h, buf))
+        return buf.raw
+
+    def shard_ipc_open(self, handle_bytes):
+        q = C.c_void_p()
+        self._chk(lib().pfmpe_shard_ipc_open(self._h, C.create_string_buffer(bytes(handle_bytes), 64), C.byref(q)))
+        return int(q.value)
+
+    def shard_set_peers(self, ptrs):
+        arr = (C.c_void_p * len(ptrs))(*[int(v) for v in ptrs])
+        self._chk(lib().pfmpe_shard_set_peers(self._h, len(ptrs), arr))
+
+    def shard_scatter(self, first_owned_slot, count):
+        self._chk(lib().pfmpe_shard_scatter(self._h, int(first_owned_slot), int(count)))
 
     def shard_winner(self, local_index):
         o = FrameOut()

@@ -1111,4 +1111,26 @@ __global__ void __launch_bounds__(PF_BLOCK) pf_shard_keep_kernel(const float4* T
   dst[2 * (size_t)N + n] = T[2 * (size_t)N + s];
 }
 
+// Sharded filter, peer-memory rebalance: every output slot this rank produced is written straight
+// into the particle set of the rank that owns the slot -- its own HBM or, through NVLink peer
+// stores, another GPU's (peers[d] = base of rank d's next-frame particle planes, N particles per
+// rank).  Slot k = kbase + i -> rank k / N, local particle k % N.  One kernel replaces the row
+// export, the all_to_all and the import; remote and local stores overlap across CTAs.
+__global__ void __launch_bounds__(PF_BLOCK) pf_shard_scatter_kernel(const float4* T, const int* idx, int N, long long kbase,
+                                                                    long long count, float4* const* peers)
+{
+  const long long stride = (long long)gridDim.x * PF_BLOCK;
+  for (long long i = (long long)blockIdx.x * PF_BLOCK + threadIdx.x; i < count; i += stride) {
+    const long long k = kbase + i;
+    const int d = (int)(k / N);
+    const int n = (int)(k - (long long)d * N);
+    const int s = idx[i];
+    float4* dst = peers[d];
+    const float4 r0 = T[s], r1 = T[(size_t)N + s], r2 = T[2 * (size_t)N + s];
+    dst[n] = r0;
+    dst[(size_t)N + n] = r1;
+    dst[2 * (size_t)N + n] = r2;
+  }
+}
+
 #endif  // __CUDACC__

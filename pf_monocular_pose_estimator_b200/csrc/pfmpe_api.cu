@@ -90,6 +90,9 @@ struct pfmpe_handle {
   int goff = 0, n_global = 0;
   pf_cta_agg* warp_agg_g = nullptr;
   long long* shard_partial = nullptr;   // default target of the per-stage partial results
+  float4** peers_dev = nullptr;         // [peer_world] next-frame particle planes of every rank (peer memory)
+  int peer_world = 0;
+  std::vector<void*> ipc_opened;
   std::vector<pfmpe_frame_in> in_scratch;
   std::vector<pfmpe_frame_out> out_scratch;
   std::string err;
@@ -136,6 +139,8 @@ void free_all(pfmpe_handle* h)
   cudaFree(h->pose0); cudaFree(h->pose1); cudaFree(h->gather_tmp); cudaFree(h->w); cudaFree(h->kend);
   cudaFree(h->idx); cudaFree(h->gather_idx); cudaFree(h->cta_agg); cudaFree(h->accum);
   cudaFree(h->inbox); cudaFree(h->state); cudaFree(h->result); cudaFree(h->obj_f); cudaFree(h->obj_d);
+  for (void* q : h->ipc_opened) cudaIpcCloseMemHandle(q);
+  cudaFree(h->peers_dev);
   cudaFree(h->rng_tab); cudaFree(h->timeline); cudaFree(h->warp_agg_g); cudaFree(h->shard_partial); cudaFree(h->gfill);
   if (h->seq.owned) { cudaFree(h->seq.blobs); cudaFree(h->seq.counts); cudaFree(h->seq.times); cudaFree(h->seq.seeds); }
   cudaFree(h->seq.result); cudaFree(h->seq.fc_log);
@@ -1125,6 +1130,76 @@ int pfmpe_shard_keep(pfmpe_handle* h, int64_t first_owned_slot, int64_t first_sl
   const int blocks = (int)((count + PF_BLOCK - 1) / PF_BLOCK);
   pf_shard_keep_kernel<<<blocks, PF_BLOCK, 0, h->stream>>>(h->pose1, h->idx, (int)N, first_owned_slot, first_slot, (int)count,
                                                           (int)local_offset, h->pose0);
+  PF_CUDA(h, cudaGetLastError());
+  h->launches += 1;
+  return PFMPE_OK;
+}
+
+// ---- peer-memory rebalance (NVLink P2P stores instead of the row exchange) -----------------------
+int pfmpe_shard_local_ptr(pfmpe_handle* h, void** d_ptr)
+{
+  if (!h || !d_ptr) return PFMPE_ERR_INVALID;
+  *d_ptr = h->pose0;
+  return PFMPE_OK;
+}
+
+int pfmpe_shard_ipc_export(pfmpe_handle* h, unsigned char handle[64])
+{
+  if (!h || !handle) return PFMPE_ERR_INVALID;
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  cudaIpcMemHandle_t m;
+  PF_CUDA(h, cudaIpcGetMemHandle(&m, h->pose0));
+  std::memcpy(handle, &m, 64);
+  return PFMPE_OK;
+}
+
+int pfmpe_shard_ipc_open(pfmpe_handle* h, const unsigned char handle[64], void** d_ptr)
+{
+  if (!h || !handle || !d_ptr) return PFMPE_ERR_INVALID;
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  cudaIpcMemHandle_t m;
+  std::memcpy(&m, handle, 64);
+  void* q = nullptr;
+  cudaError_t e = cudaIpcOpenMemHandle(&q, m, cudaIpcMemLazyEnablePeerAccess);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    h->err = std::string("cudaIpcOpenMemHandle: ") + cudaGetErrorString(e);
+    return PFMPE_ERR_COMM;
+  }
+  h->ipc_opened.push_back(q);
+  *d_ptr = q;
+  return PFMPE_OK;
+}
+
+int pfmpe_shard_set_peers(pfmpe_handle* h, int world, void* const* d_ptrs)
+{
+  if (!h || world < 1 || world > 1024 || !d_ptrs) return PFMPE_ERR_INVALID;
+  if (!h->sharded) return fail(h, PFMPE_ERR_STATE, "pfmpe_shard_configure must be called first");
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  if ((int64_t)world * h->cfg.n_particles != (int64_t)h->n_global) return fail(h, PFMPE_ERR_INVALID, "peer rebalance needs equal shards");
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  cudaFree(h->peers_dev); h->peers_dev = nullptr;
+  PF_CUDA(h, cudaMalloc((void**)&h->peers_dev, sizeof(float4*) * (size_t)world));
+  PF_CUDA(h, cudaMemcpy(h->peers_dev, d_ptrs, sizeof(float4*) * (size_t)world, cudaMemcpyHostToDevice));
+  h->peer_world = world;
+  return PFMPE_OK;
+}
+
+int pfmpe_shard_scatter(pfmpe_handle* h, int64_t first_owned_slot, int64_t count)
+{
+  if (!h || count < 0 || first_owned_slot < 0) return PFMPE_ERR_INVALID;
+  int rc = shard_ready(h);
+  if (rc) return rc;
+  if (!h->peers_dev) return fail(h, PFMPE_ERR_STATE, "pfmpe_shard_set_peers must be called first");
+  if (first_owned_slot + count > (int64_t)h->n_global) return fail(h, PFMPE_ERR_INVALID, "slot range outside the filter");
+  h->particles_set[0] = 1;
+  if (count == 0) return PFMPE_OK;
+  const int N = h->cfg.n_particles;
+  long long blocks = (count + PF_BLOCK - 1) / PF_BLOCK;
+  const long long cap = (long long)h->num_sms * 32;
+  if (blocks > cap) blocks = cap;
+  pf_shard_scatter_kernel<<<(int)blocks, PF_BLOCK, 0, h->stream>>>(h->pose1, h->idx, N, first_owned_slot, count, h->peers_dev);
   PF_CUDA(h, cudaGetLastError());
   h->launches += 1;
   return PFMPE_OK;

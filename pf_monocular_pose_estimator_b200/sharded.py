@@ -125,6 +125,16 @@ class Loopback:
     def bcast(self, arr, owner):
         return arr
 
+    def barrier(self, dev):
+        pass
+
+    def all_ok(self, ok, dev):
+        return bool(ok)
+
+    def peer_pointers(self, shards, dev):
+        """Bases of every shard's next-frame particle planes (same process: plain device pointers)."""
+        return [h.shard_local_ptr() for h in shards]
+
 
 class TorchDist:
     """One shard per process (rank = shard); NCCL on GPUs, gloo in the CPU tests."""
@@ -148,6 +158,29 @@ class TorchDist:
         self.dist.all_to_all_single(outs[0], send_rows[0], output_split_sizes=recv, input_split_sizes=list(send[r]),
                                     group=self.group)
 
+    def barrier(self, dev):
+        """Stream-ordered: every rank's earlier work on its current stream precedes everybody's later work."""
+        import torch
+        if not hasattr(self, "_one"):
+            self._one = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.dist.all_reduce(self._one, group=self.group)
+
+    def all_ok(self, ok, dev):
+        import torch
+        t = torch.tensor([1 if ok else 0], dtype=torch.int32, device=dev)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MIN, group=self.group)
+        return bool(int(t.item()))
+
+    def peer_pointers(self, shards, dev):
+        """CUDA IPC: every rank publishes its buffer, opens the others (NVLink peer access)."""
+        import torch
+        mine = torch.tensor(list(shards[0].shard_ipc_export()), dtype=torch.uint8, device=dev)
+        allh = torch.empty((self.world, 64), dtype=torch.uint8, device=dev)
+        self.dist.all_gather_into_tensor(allh, mine.reshape(1, 64), group=self.group)
+        allh = allh.cpu().numpy()
+        return [shards[0].shard_local_ptr() if q == self.rank else shards[0].shard_ipc_open(allh[q].tobytes())
+                for q in range(self.world)]
+
     def bcast(self, arr, owner):
         import torch
         dev = "cuda" if self.dist.get_backend(self.group) == "nccl" else "cpu"
@@ -165,7 +198,7 @@ class ShardedFilter:
 
     n_global must be a multiple of comm.world.  With `Loopback` all shards are handles on `device`."""
 
-    def __init__(self, n_global, comm, n_leds=5, max_blobs=32, device=0, **kw):
+    def __init__(self, n_global, comm, n_leds=5, max_blobs=32, device=0, rebalance="auto", **kw):
         import torch
         if n_global % comm.world:
             raise ValueError("n_global must be a multiple of the number of shards")
@@ -182,6 +215,21 @@ class ShardedFilter:
             self.shards.append(h)
         self.partials = torch.zeros((len(self.shards), 8), dtype=torch.int64, device=self.dev)
         self._bufs = {}
+        # rebalance of the resampled set: "p2p" = one scatter kernel with NVLink peer stores (CUDA IPC),
+        # "exchange" = row export + all_to_all + import; "auto" tries p2p and falls back for every rank
+        self.rebalance, self.p2p_error = "exchange", None
+        if rebalance in ("auto", "p2p"):
+            ok = True
+            try:
+                ptrs = comm.peer_pointers(self.shards, self.dev)
+                for h in self.shards:
+                    h.shard_set_peers(ptrs)
+            except capi.PfmpeError as e:
+                ok, self.p2p_error = False, str(e)
+            if comm.all_ok(ok, self.dev):
+                self.rebalance = "p2p"
+            elif rebalance == "p2p":
+                raise RuntimeError("peer-memory rebalance unavailable: %s" % (self.p2p_error or "a peer rank failed"))
         self.passes = 0          # score passes launched so far (per shard)
         self.last = None
         self.stage_s = None      # set to {} to collect per-stage wall times (synchronises after every stage)
@@ -286,35 +334,46 @@ class ShardedFilter:
             first, end = part[:, 1], part[:, 2]
             check_tiling(first, end, self.N)
             send = slot_partition(first, end, self.n_loc, self.W)
-            # slots that stay on their rank go plane to plane on the device; only the rest is exchanged
-            send_x = [[0 if d == r_ else c for d, c in enumerate(row)] for r_, row in enumerate(send)]
-            rows = []
-            for i, r_ in enumerate(self.comm.local):
-                lo, hi, f0, e0 = r_ * self.n_loc, (r_ + 1) * self.n_loc, int(first[r_]), int(end[r_])
-                below = (f0, max(f0, min(e0, lo)))                 # to lower ranks
-                above = (min(e0, max(f0, hi)), e0)                 # to higher ranks
-                nb, na = below[1] - below[0], above[1] - above[0]
-                assert nb + na == sum(send_x[r_]) and nb + na + send[r_][r_] == e0 - f0
-                buf = self._buffer("send", i, nb + na)
-                self.shards[i].shard_export(f0, below[0], nb, buf.data_ptr())
-                self.shards[i].shard_export(f0, above[0], na, buf.data_ptr() + 48 * nb)
-                self.shards[i].shard_keep(f0, below[1], send[r_][r_], below[1] - lo if send[r_][r_] else 0)
-                rows.append(buf)
-            t = self._mark("export", t)
-            outs = [self._buffer("recv", i, sum(send_x[q][r_] for q in range(self.W))) for i, r_ in enumerate(self.comm.local)]
-            self.comm.exchange(rows, send_x, outs)
-            t = self._mark("exchange", t)
-            for i, r_ in enumerate(self.comm.local):
-                a = sum(send_x[q][r_] for q in range(r_))
-                b = sum(send_x[q][r_] for q in range(r_ + 1, self.W))
-                if a + send[r_][r_] + b != self.n_loc:
-                    raise RuntimeError("rebalance delivers %d rows to shard %d, expected %d" % (a + send[r_][r_] + b, r_, self.n_loc))
-                self.shards[i].shard_import(outs[i].data_ptr(), 0, a)
-                self.shards[i].shard_import(outs[i].data_ptr() + 48 * a, self.n_loc - b, b)
-            self._t = self._mark("import", t)
+            if self.rebalance == "p2p":
+                for i, r_ in enumerate(self.comm.local):
+                    self.shards[i].shard_scatter(int(first[r_]), int(end[r_] - first[r_]))
+                self.comm.barrier(self.dev)                  # all scatters land before anyone's next score pass
+                self._t = self._mark("scatter", t)
+            else:
+                self._rebalance_exchange(send, first, end, t)
         else:
             q = arg_min if S < 0 else arg_max                 # :714 on the normalised weights
+        return self._finish(q, S, accept, resampled, iters, best_it, highest, arg_max, max_count)
 
+    def _rebalance_exchange(self, send, first, end, t):
+        # slots that stay on their rank go plane to plane on the device; only the rest is exchanged
+        send_x = [[0 if d == r_ else c for d, c in enumerate(row)] for r_, row in enumerate(send)]
+        rows = []
+        for i, r_ in enumerate(self.comm.local):
+            lo, hi, f0, e0 = r_ * self.n_loc, (r_ + 1) * self.n_loc, int(first[r_]), int(end[r_])
+            below = (f0, max(f0, min(e0, lo)))                 # to lower ranks
+            above = (min(e0, max(f0, hi)), e0)                 # to higher ranks
+            nb, na = below[1] - below[0], above[1] - above[0]
+            assert nb + na == sum(send_x[r_]) and nb + na + send[r_][r_] == e0 - f0
+            buf = self._buffer("send", i, nb + na)
+            self.shards[i].shard_export(f0, below[0], nb, buf.data_ptr())
+            self.shards[i].shard_export(f0, above[0], na, buf.data_ptr() + 48 * nb)
+            self.shards[i].shard_keep(f0, below[1], send[r_][r_], below[1] - lo if send[r_][r_] else 0)
+            rows.append(buf)
+        t = self._mark("export", t)
+        outs = [self._buffer("recv", i, sum(send_x[q][r_] for q in range(self.W))) for i, r_ in enumerate(self.comm.local)]
+        self.comm.exchange(rows, send_x, outs)
+        t = self._mark("exchange", t)
+        for i, r_ in enumerate(self.comm.local):
+            a = sum(send_x[q][r_] for q in range(r_))
+            b = sum(send_x[q][r_] for q in range(r_ + 1, self.W))
+            if a + send[r_][r_] + b != self.n_loc:
+                raise RuntimeError("rebalance delivers %d rows to shard %d, expected %d" % (a + send[r_][r_] + b, r_, self.n_loc))
+            self.shards[i].shard_import(outs[i].data_ptr(), 0, a)
+            self.shards[i].shard_import(outs[i].data_ptr() + 48 * a, self.n_loc - b, b)
+        self._t = self._mark("import", t)
+
+    def _finish(self, q, S, accept, resampled, iters, best_it, highest, arg_max, max_count):
         # ---- winner pose + correspondences from its owner
         owner = q // self.n_loc
         packed = np.zeros(16 + 1 + 2 * capi.MAX_LED)

@@ -36,8 +36,8 @@ def _same_frame(a, b, ha, hb):
         assert (ha.particles(1) == hb.particles(1)).all()
 
 
-@pytest.mark.parametrize("N,W,kw", [(4096, 8, {}), (8192, 4, {}), (6144, 2, dict(force_mode=2, grid_cap=3)),
-                                    (200000, 2, {}), (40960, 5, {})])
+@pytest.mark.parametrize("N,W,kw", [(4096, 8, {}), (8192, 4, dict(rebalance="exchange")), (6144, 2, dict(force_mode=2, grid_cap=3)),
+                                    (200000, 2, {}), (200000, 2, dict(rebalance="exchange")), (40960, 5, {})])
 def test_logical_shards_match_unsharded_filter(N, W, kw):
     fi = frame_inputs(N, frame=7)
     ref = make_handle(fi, N)
@@ -54,7 +54,8 @@ def test_logical_shards_match_unsharded_filter(N, W, kw):
     sh.close()
 
 
-def test_sharded_dominant_sources_and_empty_ranks():
+@pytest.mark.parametrize("rebalance", ["p2p", "exchange"])
+def test_sharded_dominant_sources_and_empty_ranks(rebalance):
     """A handful of sources (all on shard 0) own every output slot: the other shards produce nothing and
     receive their whole particle set through the rebalance; then a single dominant source."""
     N, W = 32768, 4
@@ -63,7 +64,8 @@ def test_sharded_dominant_sources_and_empty_ranks():
     far[:, 0, 3] += 5.0
     fi["E"][40:] = far
     ref = make_handle(fi, N)
-    sh = _make_sharded(fi, N, W)
+    sh = _make_sharded(fi, N, W, rebalance=rebalance)
+    assert sh.rebalance == rebalance
     args = (fi["img"], fi["T_cur"], fi["T_pred"], fi["P"], fi["Cm"], fi["isi"], fi["dt"], fi["seed"])
     for step in range(2):
         ref.set_particles(fi["E"])
