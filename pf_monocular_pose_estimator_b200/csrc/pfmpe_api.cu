@@ -14,6 +14,7 @@
 
 #include "../../include/pfmpe.h"
 #include "pf_kernels.cuh"
+#include "pf_meancov.cuh"
 
 namespace {
 
@@ -65,6 +66,8 @@ struct pfmpe_handle {
   pf_cta_agg* cta_agg = nullptr;
   pf_accum* accum = nullptr;
   pf_gfill* gfill = nullptr;
+  double *mc_part = nullptr, *mc_mean = nullptr;   // K7 (PFMPE_FLAG_MEAN_COV): per-block partials, mean poses
+  int mc_blocks = 0;
   int gfill_cap = 0;
   unsigned char* inbox = nullptr;       // [fconst x n_trackers | blobs x n_trackers x max_blobs x 2]
   pf_frame_const* fconst = nullptr;     // = inbox
@@ -140,7 +143,7 @@ void free_all(pfmpe_handle* h)
   cudaFree(h->idx); cudaFree(h->gather_idx); cudaFree(h->cta_agg); cudaFree(h->accum);
   cudaFree(h->inbox); cudaFree(h->state); cudaFree(h->result); cudaFree(h->obj_f); cudaFree(h->obj_d);
   for (void* q : h->ipc_opened) cudaIpcCloseMemHandle(q);
-  cudaFree(h->peers_dev);
+  cudaFree(h->peers_dev); cudaFree(h->mc_part); cudaFree(h->mc_mean);
   cudaFree(h->rng_tab); cudaFree(h->timeline); cudaFree(h->warp_agg_g); cudaFree(h->shard_partial); cudaFree(h->gfill);
   if (h->seq.owned) { cudaFree(h->seq.blobs); cudaFree(h->seq.counts); cudaFree(h->seq.times); cudaFree(h->seq.seeds); }
   cudaFree(h->seq.result); cudaFree(h->seq.fc_log);
@@ -209,6 +212,25 @@ struct ShardArgs {
   long long excl[3] = {0, 0, 0}, total[3] = {0, 0, 0};
   long long* partial = nullptr;
 };
+
+// K7: weighted mean pose + covariance of trackers [t0, t0+nt) from the kept iteration's particles and
+// scores (two streaming passes + two one-block combines), written into the result records.
+int launch_meancov(pfmpe_handle* h, int t0, int nt)
+{
+  pf_kparams p;
+  fill_kparams(h, p);
+  p.tracker_base = t0;
+  p.result = h->result;
+  const dim3 grid((unsigned)h->mc_blocks, (unsigned)nt, 1);
+  double* mean = h->mc_mean + (size_t)t0 * 12;
+  pf_meancov_pass1<<<grid, PF_MC_THREADS, 0, h->stream>>>(p, h->mc_part);
+  pf_meancov_mean<<<nt, 32, 0, h->stream>>>(p, h->mc_part, h->mc_blocks, mean);
+  pf_meancov_pass2<<<grid, PF_MC_THREADS, 0, h->stream>>>(p, mean, h->mc_part);
+  pf_meancov_cov<<<nt, 32, 0, h->stream>>>(p, h->mc_part, h->mc_blocks);
+  PF_CUDA(h, cudaGetLastError());
+  h->launches += 4;
+  return PFMPE_OK;
+}
 
 // Launch the frame kernel for trackers [t0, t0+nt).  mode 0: per-frame, 1: track, 2: replay,
 // 3/4/5: one stage of the sharded filter.
@@ -418,6 +440,12 @@ int pfmpe_create(const pfmpe_config* cfg, pfmpe_handle** out)
   PF_TRY(dev_alloc(&h->obj_f, T * PF_MAX_LED * 3));
   PF_TRY(dev_alloc(&h->obj_d, T * PF_MAX_LED * 3));
   PF_TRY(dev_alloc(&h->rng_tab, 1024));
+  if (cfg->flags & PFMPE_FLAG_MEAN_COV) {
+    const size_t nb = (N + PF_MC_THREADS - 1) / PF_MC_THREADS, lim = T == 1 ? PF_MC_MAXBLK : 16;
+    h->mc_blocks = (int)(nb < lim ? nb : lim);
+    PF_TRY(dev_alloc(&h->mc_part, T * (size_t)h->mc_blocks * 21));
+    PF_TRY(dev_alloc(&h->mc_mean, T * 12));
+  }
   PF_TRY(dev_alloc(&h->timeline, 16));
   PF_TRY(cudaMemset(h->timeline, 0, 16 * sizeof(unsigned long long)));
   PF_TRY(cudaMallocHost((void**)&h->h_inbox, h->inbox_bytes));
@@ -578,6 +606,10 @@ static int run_update(pfmpe_handle* h, int t0, int nt, const pfmpe_frame_in* in,
   }
   rc = launch_frames(h, 0, t0, nt, 0, 1);
   if (rc) return rc;
+  if (h->cfg.flags & PFMPE_FLAG_MEAN_COV) {
+    rc = launch_meancov(h, t0, nt);
+    if (rc) return rc;
+  }
   PF_CUDA(h, cudaMemcpyAsync(h->h_result + t0, h->result + t0, sizeof(pf_frame_result) * nt, cudaMemcpyDeviceToHost, h->stream));
   PF_CUDA(h, cudaStreamSynchronize(h->stream));
   for (int i = 0; i < nt; ++i) {

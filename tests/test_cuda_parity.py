@@ -267,3 +267,42 @@ def test_full_size_properties():
         v, _ = orc.score(fi["params"], fi["img"], uv)
         assert abs(v - w[n]) <= 1e-5 * max(1.0, abs(v)) or abs(v - w[n]) > 4.0   # (gate ties jump by ~L)
     h.close()
+
+
+@pytest.mark.parametrize("N,mode", [(100, 0), (30000, 0), (5000, 1)])
+def test_weighted_mean_pose_and_covariance(N, mode):
+    """K7 (north-star extra; no reference counterpart): weighted mean pose + 6x6 covariance of
+    the kept iteration's particles, against the CPU restatement fed with the CUDA path's own T and weights."""
+    fi = frame_inputs(N, frame=11)
+    h = make_handle(fi, N, flags=capi.FLAG_MEAN_COV, force_mode=mode)
+    got = run_frame(h, fi)
+    assert got["resampled"] == 1
+    w = got["w_raw"] / got["weight_sum"]
+    mean, cov = orc.weighted_mean_cov(got["T"], w)
+    np.testing.assert_allclose(got["mean_pose"], mean, rtol=1e-9, atol=1e-12)
+    np.testing.assert_allclose(got["mean_cov"], cov, rtol=1e-7, atol=1e-16)
+    R = got["mean_pose"][:3, :3]
+    assert abs(np.linalg.det(R) - 1) < 1e-12 and np.abs(R @ R.T - np.eye(3)).max() < 1e-12
+    assert np.abs(got["mean_pose"][:3, 3] - fi["truth"][:3, 3]).max() < 0.1
+    assert np.all(np.linalg.eigvalsh(got["mean_cov"]) > -1e-15)
+    # without the flag the fields stay zero
+    h2 = make_handle(fi, N)
+    g2 = run_frame(h2, fi)
+    assert not g2["mean_cov"].any()
+    h.close(); h2.close()
+
+
+def test_weighted_mean_cov_batched_trackers():
+    N, T = 2048, 3
+    fis = [frame_inputs(N, frame=6 + t, tracker=t) for t in range(T)]
+    h = make_handle(fis[0], N, n_trackers=T, flags=capi.FLAG_MEAN_COV)
+    for t in range(T):
+        h.set_particles(fis[t]["E"], tracker=t)
+    outs = h.update_batch([dict(img=f["img"], T_cur=f["T_cur"], T_pred=f["T_pred"], P=f["P"], Cm=f["Cm"], isi=f["isi"],
+                                dt=f["dt"], seed=f["seed"]) for f in fis])
+    for t in range(T):
+        Tt, w = h.particles(0, tracker=t), h.weights(False, tracker=t) / outs[t]["weight_sum"]
+        mean, cov = orc.weighted_mean_cov(Tt, w)
+        np.testing.assert_allclose(outs[t]["mean_pose"], mean, rtol=1e-9, atol=1e-12)
+        np.testing.assert_allclose(outs[t]["mean_cov"], cov, rtol=1e-7, atol=1e-16)
+    h.close()
