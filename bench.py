@@ -351,14 +351,19 @@ def sharded_filter_measure(world, rank, dev, local_rank, barrier, allreduce, RO,
     (wall,) = allreduce([wall], RO.MAX if RO else None)
     (okf,) = allreduce([1.0 if ok else 0.0], RO.MIN if RO else None)
     pme = float(n_global) * L_LED * passes
-    alg = alg_bytes_per_frame(n_global // world, passes / K) * K + 2 * 96.0 * (n_global // world) * K   # + export/import rows
+    # + the rebalance: every resampled particle is read once through idx (48 + 4 B) and written once (48 B)
+    alg = (alg_bytes_per_frame(n_global // world, passes / K) + 100.0 * (n_global // world)) * K
+    rebalance = sf.rebalance
     sf.close()
     return {"workload": "cfg5", "desc": "BASELINE configs[4]: single filter with 2^26 particles sharded by particle over the ranks",
             "scaling": "strong", "particles": n_global, "particles_per_rank": n_global // world, "value": pme / (wall), "unit": "PME/s",
             "ms_per_step": 1e3 * wall / K, "device_ms_per_step": ms / K, "steps": K, "warmup": W, "mean_iterations": passes / K,
             "all_frames_resampled": bool(okf > 0), "roofline_frac": alg / (wall) / 1e9 / peak,
-            "exchange": "all_gather 64 B/rank per pass + per resampling, all_to_all of 48 B/particle rows (torch.distributed %s)"
-                        % ("nccl" if world > 1 else "loopback, 1 rank"),
+            "exchange": "all_gather of 64 B/rank per score pass and per resampling (torch.distributed %s); rebalance = %s"
+                        % ("nccl" if world > 1 else "loopback, 1 rank",
+                           "one scatter kernel, local + NVLink peer stores (CUDA IPC)" if rebalance == "p2p" else
+                           "row export + all_to_all + import"),
+            "rebalance": rebalance,
             "note": "host-orchestrated stages through pfmpe_shard_*; wall clock of the whole host loop incl. host Gauss-Newton"}
 
 
