@@ -201,6 +201,16 @@ int pfmpe_track_sequence_host(pfmpe_handle* h, int n_frames, const double* times
 /* results of frames [first, first+n) of one tracker */
 int pfmpe_track_results(pfmpe_handle* h, int tracker, int first_frame, int n_frames, pfmpe_track_result* out);
 
+/* ---- ROI prediction for the LED detector ------------------------------------------
+ * predictMarkerPositionsInImage (pose_estimator.cpp:1036-1052, called :396) + the extreme-value loop of
+ * LEDDetector::determineROI (led_detector.cpp:221-244): every LED through every resampled particle as
+ * cam_move_inv * newPoseEstimation[j] * prediction_matrix, and through predicted_pose;
+ * roi = {x_min, y_min, x_max, y_max} with the reference's start values (+INF, +INF, 0, 0).  The caller
+ * passes the two corner points on to determineROI (distortion, border, clamping: :246-260) instead of
+ * the N*L + L predicted pixel positions.  FP32 projection (1e-5 relative of the reference's doubles). */
+int pfmpe_predict_roi(pfmpe_handle* h, int tracker, const double cam_move_inv[16], const double prediction_matrix[16],
+                      const double predicted_pose[16], double roi[4]);
+
 /* ---- one filter sharded over several GPUs (BASELINE configs[4]) ----------------------
  * One handle per rank owns the contiguous global particles [global_offset, global_offset +
  * n_particles) of ONE filter of n_global particles (n_trackers must be 1).  The reference loop

@@ -100,6 +100,7 @@ def lib():
         L.orc_tracker_frame.restype = C.c_float
         L.orc_tracker_frame.argtypes = [C.POINTER(Tracker), C.c_double, C.c_int, _dp, C.c_uint32]
         L.orc_weighted_mean_cov.argtypes = [C.c_int, _dp, _dp, _dp, _dp]
+        L.orc_predict_roi.argtypes = [C.c_int, _dp, _dp, _dp, _dp, _dp, C.c_int, _dp, _dp]
         L.orc_mat4_inv.argtypes = [_dp, _dp]
         _lib = L
     return _lib
@@ -249,6 +250,14 @@ def project2d(K, T, X):
     Kc = _c64(K).reshape(9); t = colmajor(T); x = _c64(X); uv = np.zeros(2)
     lib().orc_project2d(_d(Kc), _d(t), _d(x), _d(uv))
     return uv
+
+
+def predict_roi(E, Cm, P, pred, markers, K):
+    """(x_min, y_min, x_max, y_max) of predictMarkerPositionsInImage + determineROI's extreme-value loop."""
+    e = colmajor(E); m = _c64(markers)[:, :3].copy(); out = np.zeros(4)
+    lib().orc_predict_roi(e.shape[0], _d(e), _d(colmajor(Cm)), _d(colmajor(P)), _d(colmajor(pred)), _d(m), m.shape[0],
+                          _d(_c64(K).reshape(9)), _d(out))
+    return out
 
 
 def weighted_mean_cov(T, w):

@@ -777,3 +777,34 @@ void orc_weighted_mean_cov(int N, const double *T, const double *w, double mean_
     for (int c = 0; c < 6; ++c) for (int r = 0; r < 6; ++r) cov[r + 6 * c] += w[n] * xi[r] * xi[c];
   }
 }
+
+/* ======================================================================= */
+/* ROI prediction                                     */
+/* ======================================================================= */
+/* predictMarkerPositionsInImage (pose_estimator.cpp:1036-1052): every LED through every resampled
+ * particle as camMoveInv * newPoseEstimation[j] * predictionMatrix, then through predicted_pose_;
+ * followed by the extreme-value loop of LEDDetector::determineROI (led_detector.cpp:221-244):
+ * x_min, y_min start at +INF, x_max, y_max start at 0, strict comparisons (a NaN never wins).
+ * out = {x_min, y_min, x_max, y_max}: the two corner points determineROI goes on to distort/clamp. */
+void orc_predict_roi(int N, const double *E, const double Cm[16], const double P[16], const double pred[16],
+                     const double *markers_xyz, int L, const double K[9], double out[4])
+{
+  double x_min = INFINITY, x_max = 0, y_min = INFINITY, y_max = 0;
+  for (int i = 0; i < L; ++i) {
+    const double X[4] = { markers_xyz[3 * i], markers_xyz[3 * i + 1], markers_xyz[3 * i + 2], 1.0 };
+    for (int j = 0; j <= N; ++j) {
+      double T[16], uv[2];
+      if (j < N) {
+        double CE[16];
+        orc_mat4_mul(Cm, E + 16 * (size_t)j, CE);
+        orc_mat4_mul(CE, P, T);
+      } else memcpy(T, pred, sizeof T);
+      orc_project2d(K, T, X, uv);
+      if (uv[0] < x_min) x_min = uv[0];
+      if (uv[0] > x_max) x_max = uv[0];
+      if (uv[1] < y_min) y_min = uv[1];
+      if (uv[1] > y_max) y_max = uv[1];
+    }
+  }
+  out[0] = x_min; out[1] = y_min; out[2] = x_max; out[3] = y_max;
+}

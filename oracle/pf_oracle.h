@@ -154,6 +154,10 @@ void orc_tracker_free(orc_tracker *t);
 float orc_tracker_frame(orc_tracker *t, double time_to_predict, int D, const double *img, uint32_t seed);
 
 /* ---- north_star extra, no reference counterpart: parity unpinned */
+/* ROI prediction: pose_estimator.cpp:1036-1052 + the min/max loop of led_detector.cpp:221-244 */
+void orc_predict_roi(int N, const double *E, const double Cm[16], const double P[16], const double pred[16],
+                     const double *markers_xyz, int L, const double K[9], double out[4]);
+
 void orc_weighted_mean_cov(int N, const double *T, const double *w, double mean_pose[16], double cov[36]);
 
 #ifdef __cplusplus

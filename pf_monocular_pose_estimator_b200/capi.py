@@ -24,6 +24,7 @@ EXPORTS = [
     "pfmpe_optimise_pose", "pfmpe_predict_pose", "pfmpe_exponential_map", "pfmpe_logarithm_map",
     "pfmpe_track_init", "pfmpe_track_upload", "pfmpe_track_attach", "pfmpe_track_run", "pfmpe_track_replay", "pfmpe_track_results",
     "pfmpe_track_frame_host", "pfmpe_track_frame_host_batch", "pfmpe_track_sequence_host",
+    "pfmpe_predict_roi",
     "pfmpe_shard_configure", "pfmpe_shard_begin_frame", "pfmpe_shard_score", "pfmpe_shard_resample",
     "pfmpe_shard_export", "pfmpe_shard_keep", "pfmpe_shard_import", "pfmpe_shard_winner",
     "pfmpe_shard_local_ptr", "pfmpe_shard_ipc_export", "pfmpe_shard_ipc_open", "pfmpe_shard_set_peers", "pfmpe_shard_scatter",
@@ -120,6 +121,7 @@ def lib():
                                                    C.POINTER(TrackResult)]
         L.pfmpe_track_sequence_host.argtypes = [C.c_void_p, C.c_int, _dp, _dp, C.POINTER(C.c_int32), C.POINTER(C.c_uint32),
                                                 C.POINTER(TrackResult), _dp]
+        L.pfmpe_predict_roi.argtypes = [C.c_void_p, C.c_int, _dp, _dp, _dp, _dp]
         _i3 = C.POINTER(C.c_int64)
         L.pfmpe_shard_configure.argtypes = [C.c_void_p, C.c_int64, C.c_int64]
         L.pfmpe_shard_begin_frame.argtypes = [C.c_void_p, C.POINTER(FrameIn)]
@@ -331,6 +333,12 @@ class Handle:
         self._chk(lib().pfmpe_track_frame_host(self._h, tracker, float(time_to_predict), _d(ip), ip.shape[0], int(seed),
                                               C.byref(r)))
         return self._unpack_track([r])[0]
+
+    def predict_roi(self, Cm, P, pred, tracker=0):
+        """(x_min, y_min, x_max, y_max) over all resampled particles x LEDs + the predicted pose."""
+        out = np.zeros(4)
+        self._chk(lib().pfmpe_predict_roi(self._h, tracker, _d(colmajor(Cm)), _d(colmajor(P)), _d(colmajor(pred)), _d(out)))
+        return out
 
     # ---- one filter sharded over several handles / GPUs (device pointers are plain ints) ----
     def shard_configure(self, global_offset, n_global):

@@ -15,6 +15,7 @@
 #include "../../include/pfmpe.h"
 #include "pf_kernels.cuh"
 #include "pf_meancov.cuh"
+#include "pf_roi.cuh"
 
 namespace {
 
@@ -66,6 +67,9 @@ struct pfmpe_handle {
   pf_cta_agg* cta_agg = nullptr;
   pf_accum* accum = nullptr;
   pf_gfill* gfill = nullptr;
+  unsigned* roi_keys = nullptr;   // K8: [tracker][4] ordered-float keys, then the floats
+  float* roi_out = nullptr;
+  float* h_roi = nullptr;
   double *mc_part = nullptr, *mc_mean = nullptr;   // K7 (PFMPE_FLAG_MEAN_COV): per-block partials, mean poses
   int mc_blocks = 0;
   int gfill_cap = 0;
@@ -143,7 +147,8 @@ void free_all(pfmpe_handle* h)
   cudaFree(h->idx); cudaFree(h->gather_idx); cudaFree(h->cta_agg); cudaFree(h->accum);
   cudaFree(h->inbox); cudaFree(h->state); cudaFree(h->result); cudaFree(h->obj_f); cudaFree(h->obj_d);
   for (void* q : h->ipc_opened) cudaIpcCloseMemHandle(q);
-  cudaFree(h->peers_dev); cudaFree(h->mc_part); cudaFree(h->mc_mean);
+  cudaFree(h->peers_dev); cudaFree(h->mc_part); cudaFree(h->mc_mean); cudaFree(h->roi_keys); cudaFree(h->roi_out);
+  if (h->h_roi) cudaFreeHost(h->h_roi);
   cudaFree(h->rng_tab); cudaFree(h->timeline); cudaFree(h->warp_agg_g); cudaFree(h->shard_partial); cudaFree(h->gfill);
   if (h->seq.owned) { cudaFree(h->seq.blobs); cudaFree(h->seq.counts); cudaFree(h->seq.times); cudaFree(h->seq.seeds); }
   cudaFree(h->seq.result); cudaFree(h->seq.fc_log);
@@ -440,6 +445,9 @@ int pfmpe_create(const pfmpe_config* cfg, pfmpe_handle** out)
   PF_TRY(dev_alloc(&h->obj_f, T * PF_MAX_LED * 3));
   PF_TRY(dev_alloc(&h->obj_d, T * PF_MAX_LED * 3));
   PF_TRY(dev_alloc(&h->rng_tab, 1024));
+  PF_TRY(dev_alloc(&h->roi_keys, T * 4));
+  PF_TRY(dev_alloc(&h->roi_out, T * 4));
+  PF_TRY(cudaMallocHost((void**)&h->h_roi, T * 4 * sizeof(float)));
   if (cfg->flags & PFMPE_FLAG_MEAN_COV) {
     const size_t nb = (N + PF_MC_THREADS - 1) / PF_MC_THREADS, lim = T == 1 ? PF_MC_MAXBLK : 16;
     h->mc_blocks = (int)(nb < lim ? nb : lim);
@@ -1042,6 +1050,51 @@ int pfmpe_track_sequence_host(pfmpe_handle* h, int n_frames, const double* times
     if (rc) return rc;
     if (frame_seconds) frame_seconds[f] = std::chrono::duration<double>(std::chrono::steady_clock::now() - a).count();
   }
+  return PFMPE_OK;
+}
+
+// ---- ROI prediction (K8) -------------------------------------------------------
+namespace {
+typedef void (*roi_kernel_t)(const pf_kparams, const pf_pose, const pf_pose, const pf_pose, unsigned*);
+roi_kernel_t roi_kernel_for(int L)
+{
+  switch (L) {
+    case 1: return pf_roi_kernel<1>; case 2: return pf_roi_kernel<2>; case 3: return pf_roi_kernel<3>;
+    case 4: return pf_roi_kernel<4>; case 5: return pf_roi_kernel<5>; case 6: return pf_roi_kernel<6>;
+    case 7: return pf_roi_kernel<7>; case 8: return pf_roi_kernel<8>; default: return nullptr;
+  }
+}
+}  // namespace
+
+int pfmpe_predict_roi(pfmpe_handle* h, int tracker, const double cam_move_inv[16], const double prediction_matrix[16],
+                      const double predicted_pose[16], double roi[4])
+{
+  if (!h || !cam_move_inv || !prediction_matrix || !predicted_pose || !roi) return PFMPE_ERR_INVALID;
+  if (tracker < 0 || tracker >= h->cfg.n_trackers) return fail(h, PFMPE_ERR_INVALID, "tracker out of range");
+  int rc = check_ready(h);
+  if (rc) return rc;
+  if (!h->particles_set[tracker]) return fail(h, PFMPE_ERR_STATE, "set_particles / track_init must precede predict_roi");
+  roi_kernel_t k = roi_kernel_for(h->cfg.n_leds);
+  if (!k) return fail(h, PFMPE_ERR_UNSUPPORTED, "n_leds must be 1..8");
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  pf_kparams p;
+  fill_kparams(h, p);
+  p.tracker_base = tracker;
+  const pf_pose Cm = pf_aff_to_f32(pf_aff_from_cm16(cam_move_inv)), Pm = pf_aff_to_f32(pf_aff_from_cm16(prediction_matrix)),
+                pr = pf_aff_to_f32(pf_aff_from_cm16(predicted_pose));
+  const int N = h->cfg.n_particles;
+  int blocks = (N + PF_BLOCK) / PF_BLOCK;
+  if (blocks > h->num_sms * 8) blocks = h->num_sms * 8;
+  unsigned* keys = h->roi_keys + 4 * (size_t)tracker;
+  pf_roi_init_kernel<<<1, 32, 0, h->stream>>>(keys, 1);
+  k<<<dim3((unsigned)blocks, 1, 1), PF_BLOCK, 0, h->stream>>>(p, Cm, Pm, pr, h->roi_keys);
+  pf_roi_finish_kernel<<<1, 32, 0, h->stream>>>(keys, h->roi_out + 4 * (size_t)tracker, 4);
+  PF_CUDA(h, cudaGetLastError());
+  h->launches += 3;
+  PF_CUDA(h, cudaMemcpyAsync(h->h_roi + 4 * (size_t)tracker, h->roi_out + 4 * (size_t)tracker, 4 * sizeof(float),
+                             cudaMemcpyDeviceToHost, h->stream));
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  for (int i = 0; i < 4; ++i) roi[i] = (double)h->h_roi[4 * (size_t)tracker + i];
   return PFMPE_OK;
 }
 

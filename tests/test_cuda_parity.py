@@ -306,3 +306,32 @@ def test_weighted_mean_cov_batched_trackers():
         np.testing.assert_allclose(outs[t]["mean_pose"], mean, rtol=1e-9, atol=1e-12)
         np.testing.assert_allclose(outs[t]["mean_cov"], cov, rtol=1e-7, atol=1e-16)
     h.close()
+
+
+@pytest.mark.parametrize("N,mode", [(100, 0), (20000, 0), (3000, 1)])
+def test_roi_prediction_matches_oracle(N, mode):
+    """K8 (row f1): bounding corners of all resampled particles x LEDs + predicted pose, against
+    predictMarkerPositionsInImage :1036-1052 + determineROI's extreme-value loop (led_detector.cpp:221-244)."""
+    fi = frame_inputs(N, frame=12)
+    h = make_handle(fi, N, force_mode=mode)
+    h.set_particles(fi["E"])
+    Cm = np.eye(4); Cm[0, 3] = 0.01
+    args = (Cm, fi["P"], fi["T_pred"])
+    # before any update: newPoseEstimation is what initialise() left behind
+    np.testing.assert_allclose(h.predict_roi(*args), orc.predict_roi(fi["E"], Cm, fi["P"], fi["T_pred"], fi["markers"], fi["K"]),
+                               rtol=1e-5, atol=2e-3)
+    got = run_frame(h, fi, set_particles=False)
+    assert got["resampled"] == 1
+    roi = h.predict_roi(*args)                      # through idx[]: the resampled set is never materialised
+    ref = orc.predict_roi(h.particles(1), Cm, fi["P"], fi["T_pred"], fi["markers"], fi["K"])
+    np.testing.assert_allclose(roi, ref, rtol=1e-5, atol=2e-3)
+    assert roi[0] < roi[2] and roi[1] < roi[3]
+    # the reference's start values: x_max / y_max never drop below 0, x_min / y_min follow the data
+    E = fi["E"].copy(); E[:, 0, 3] -= 5.0; E[:, 1, 3] -= 5.0
+    h.set_particles(E)
+    pred = fi["T_pred"].copy(); pred[0, 3] -= 5.0; pred[1, 3] -= 5.0
+    roi = h.predict_roi(np.eye(4), np.eye(4), pred)
+    ref = orc.predict_roi(E, np.eye(4), np.eye(4), pred, fi["markers"], fi["K"])
+    assert ref[2] == 0.0 and ref[3] == 0.0 and roi[2] == 0.0 and roi[3] == 0.0
+    np.testing.assert_allclose(roi, ref, rtol=1e-5, atol=2e-3)
+    h.close()

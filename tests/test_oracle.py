@@ -223,3 +223,19 @@ def test_weighted_mean_cov_definition():
     np.testing.assert_allclose(mp[:3, 3], (w[:, None] * T[:, :3, 3]).sum(0), atol=1e-12)
     assert np.abs(mp[:3, :3] - base[:3, :3]).max() < 0.01
     assert np.allclose(cov, cov.T) and (np.linalg.eigvalsh(cov) > -1e-15).all()
+
+
+def test_predict_roi_matches_a_direct_numpy_evaluation():
+    """K8 oracle (pose_estimator.cpp:1036-1052 + led_detector.cpp:221-244 loop) against plain numpy."""
+    import numpy as np
+    from oracle import orc
+    from tests.util import frame_inputs
+    fi = frame_inputs(64, frame=8)
+    Cm = np.eye(4); Cm[1, 3] = -0.02
+    roi = orc.predict_roi(fi["E"], Cm, fi["P"], fi["T_pred"], fi["markers"], fi["K"])
+    X = np.c_[np.asarray(fi["markers"])[:, :3], np.ones(len(fi["markers"]))]
+    Ts = np.concatenate([Cm @ fi["E"] @ fi["P"], fi["T_pred"][None]])
+    cam = np.einsum("nij,lj->nli", Ts, X)[..., :3]
+    uvw = cam @ np.asarray(fi["K"]).reshape(3, 3).T
+    u, v = uvw[..., 0] / uvw[..., 2], uvw[..., 1] / uvw[..., 2]
+    np.testing.assert_allclose(roi, [u.min(), v.min(), max(0.0, u.max()), max(0.0, v.max())], rtol=1e-12)
