@@ -41,6 +41,10 @@ typedef struct pfmpe_handle pfmpe_handle;
 
 /* flags */
 #define PFMPE_FLAG_MEAN_COV 1u /* also reduce to a weighted mean pose + covariance (north_star extra) */
+#define PFMPE_FLAG_DISTORT 2u  /* project through K AND the plumb_bob coefficients of pfmpe_set_camera (model of
+                                * LEDDetector::distortPoints, led_detector.cpp:371-414): image_points are then the raw,
+                                * still-distorted blob centres.  Not what the reference PF does (it scores undistorted
+                                * points with K only); per-frame API only. */
 
 typedef struct {
   int32_t n_particles;  /* N_Particle (pose_estimator.h:139)                                  */

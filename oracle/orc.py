@@ -44,7 +44,7 @@ class PfIn(C.Structure):
                 ("obj", _dp), ("img", _dp), ("K", _dp), ("E", _dp),
                 ("T_cur", _dp), ("T_pred", _dp), ("P", _dp), ("C", _dp),
                 ("isi", C.c_uint), ("dt", C.c_double), ("seed", C.c_uint32),
-                ("resampler", C.c_int), ("max_iter", C.c_int)]
+                ("resampler", C.c_int), ("max_iter", C.c_int), ("dist", _dp)]
 
 
 class PfOut(C.Structure):
@@ -100,6 +100,7 @@ def lib():
         L.orc_tracker_frame.restype = C.c_float
         L.orc_tracker_frame.argtypes = [C.POINTER(Tracker), C.c_double, C.c_int, _dp, C.c_uint32]
         L.orc_weighted_mean_cov.argtypes = [C.c_int, _dp, _dp, _dp, _dp]
+        L.orc_distort_point.argtypes = [_dp, _dp, _dp, _dp]
         L.orc_predict_roi.argtypes = [C.c_int, _dp, _dp, _dp, _dp, _dp, C.c_int, _dp, _dp]
         L.orc_mat4_inv.argtypes = [_dp, _dp]
         _lib = L
@@ -156,7 +157,7 @@ def score(params, img, proj):
     return v, pairs[: 2 * n.value].reshape(-1, 2).copy()
 
 
-def pf_update(params, markers, K, img, E, T_cur, T_pred, P, Cm, isi, dt, seed, resampler=1, max_iter=80):
+def pf_update(params, markers, K, img, E, T_cur, T_pred, P, Cm, isi, dt, seed, resampler=1, max_iter=80, dist=None):
     """One PF update.  All poses are (4,4) numpy matrices (E: (N,4,4)).  Returns a dict."""
     obj = obj_h(markers)
     L = obj.shape[0]
@@ -172,6 +173,8 @@ def pf_update(params, markers, K, img, E, T_cur, T_pred, P, Cm, isi, dt, seed, r
     i.obj, i.img, i.K, i.E = _d(obj), _d(img), _d(Kc), _d(Ec)
     i.T_cur, i.T_pred, i.P, i.C = _d(tc), _d(tp), _d(pc), _d(cc)
     i.isi, i.dt, i.seed, i.resampler, i.max_iter = isi, dt, seed & 0xFFFFFFFF, resampler, max_iter
+    dc = None if dist is None else _c64(dist).reshape(5)
+    i.dist = None if dc is None else _d(dc)
     o = PfOut()
     T = np.zeros((N, 16)); w_raw = np.zeros(N); w = np.zeros(N)
     pairs = np.zeros((N, 2 * MAX_LED), dtype=np.uint32); npairs = np.zeros(N, dtype=np.int32)
@@ -250,6 +253,14 @@ def project2d(K, T, X):
     Kc = _c64(K).reshape(9); t = colmajor(T); x = _c64(X); uv = np.zeros(2)
     lib().orc_project2d(_d(Kc), _d(t), _d(x), _d(uv))
     return uv
+
+
+def distort_points(K, D5, pts):
+    """LEDDetector::distortPoints on an (n, 2) array."""
+    pts = _c64(pts).reshape(-1, 2); out = np.zeros_like(pts); Kc = _c64(K).reshape(9); d = _c64(D5).reshape(5)
+    for a, b in zip(pts, out):
+        lib().orc_distort_point(_d(Kc), _d(d), _d(a), _d(b))
+    return out
 
 
 def predict_roi(E, Cm, P, pred, markers, K):

@@ -149,6 +149,22 @@ void orc_project2d(const double K[9], const double T[16], const double X[4], dou
   uv[1] = t[1] / t[2];
 }
 
+/* LEDDetector::distortPoints (led_detector.cpp:371-414), one point: normalise with K, plumb_bob
+ * radial (k1,k2,k3) + tangential (p1,p2) terms, back to pixels.  D5 = (k1,k2,p1,p2,k3). */
+void orc_distort_point(const double K[9], const double D5[5], const double in[2], double out[2])
+{
+  const double fx = K[0], fy = K[4], cx = K[2], cy = K[5];
+  const double k1 = D5[0], k2 = D5[1], p1 = D5[2], p2 = D5[3], k3 = D5[4];
+  const double x = (in[0] - cx) / fx, y = (in[1] - cy) / fy;
+  const double r2 = x * x + y * y;
+  double xc = x * (1. + k1 * r2 + k2 * r2 * r2 + k3 * r2 * r2 * r2);
+  double yc = y * (1. + k1 * r2 + k2 * r2 * r2 + k3 * r2 * r2 * r2);
+  xc = xc + (2. * p1 * x * y + p2 * (r2 + 2. * x * x));
+  yc = yc + (p1 * (r2 + 2. * y * y) + 2. * p2 * x * y);
+  out[0] = xc * fx + cx;
+  out[1] = yc * fy + cy;
+}
+
 /* ======================================================================= */
 /* calculateEstimationProbability  :2385-2445                               */
 /* ======================================================================= */
@@ -316,7 +332,10 @@ int orc_pf_update(const orc_params *prm, const orc_pf_in *in, orc_pf_out *out)
         M4(Tn, 2, 3) = M4(B, 2, 3) + orc_rng_uniform(&g, tZa, tZb) * s; /* :587 */
         steps0 += 6;
       }
-      for (int j = 0; j < L; ++j) orc_project2d(in->K, Tn, in->obj + 4 * j, proj + 2 * j); /* :596-599 */
+      for (int j = 0; j < L; ++j) {
+        orc_project2d(in->K, Tn, in->obj + 4 * j, proj + 2 * j); /* :596-599 */
+        if (in->dist) orc_distort_point(in->K, in->dist, proj + 2 * j, proj + 2 * j); /* option f3, not in the reference PF */
+      }
       w[n] = orc_score(prm, L, D, in->img, proj, pairs + PS * (size_t)n, npairs + n);      /* :602 */
     }
     iter++; /* :606 */

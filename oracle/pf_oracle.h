@@ -51,6 +51,9 @@ void orc_mat4_identity(double *A);
 /* ---- project2d  (pose_estimator.cpp:1017-1034) ------------------------ */
 void orc_project2d(const double K[9], const double T[16], const double X[4], double uv[2]);
 
+/* ---- LEDDetector::distortPoints, one point (led_detector.cpp:371-414) -- */
+void orc_distort_point(const double K[9], const double D5[5], const double in[2], double out[2]);
+
 /* ---- PF parameters (pose_estimator.h:139-155, cfg :25-38) ------------- */
 typedef struct {
   double min_angular_noise, max_angular_noise;         /* minAngularNoise / maxAngularNoise       */
@@ -81,6 +84,8 @@ typedef struct {
   uint32_t seed;         /* injected value of rd() (:476-477) -- the one permitted edit  */
   int      resampler;    /* 0 = literal O(N^2) scan (:668-682); 1 = O(N) first-crossing  */
   int      max_iter;     /* 80 in the reference (:616); exposed for tests                */
+  const double *dist;    /* NULL (reference behaviour) or 5 plumb_bob coefficients: option f3, projections go
+                            through orc_distort_point and img holds raw blob centres      */
 } orc_pf_in;
 
 typedef struct {

@@ -15,6 +15,7 @@ MAX_LED = 8
 
 OK, ERR_INVALID, ERR_CUDA, ERR_NO_DEVICE, ERR_STATE, ERR_UNSUPPORTED, ERR_COMM = 0, -1, -2, -3, -4, -5, -6
 FLAG_MEAN_COV = 1
+FLAG_DISTORT = 2
 
 EXPORTS = [
     "pfmpe_create", "pfmpe_destroy", "pfmpe_strerror", "pfmpe_last_error", "pfmpe_version",
@@ -257,9 +258,9 @@ class Handle:
         a = colmajor(poses)
         self._chk(lib().pfmpe_set_particles(self._h, tracker, _d(a), a.shape[0]))
 
-    def configure(self, markers, K, params):
+    def configure(self, markers, K, params, D5=None):
         self.set_markers(markers)
-        self.set_camera(K)
+        self.set_camera(K, D5)
         self.set_params(params)
 
     # hot path

@@ -332,10 +332,11 @@ struct pf_ctx {
 // Stage A: fused propagate -> project -> score over this warp's contiguous particles for
 // iteration `it` (:543-605).  Leaves the warp's sign-agnostic prefix aggregate in warp_agg[warp].
 // ---------------------------------------------------------------------------------------
-template <int L, bool SH>
+template <int L, int V>
 __device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_ctx& cx, const pf_blob* blobs,
                                                  const uint32_t* tab, int trk, int it, pf_sm3* warp_agg)
 {
+  constexpr bool SH = V == 1, DIST = V == 2;   // kernel variants: 1 sharded stages, 2 plumb_bob projection
   const int N = p.N;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const size_t tb = (size_t)trk * 3 * (size_t)N;
@@ -397,7 +398,10 @@ __device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_c
       pf_store_pose(dst, N, n, T);
       float u[L], v[L];
 #pragma unroll
-      for (int j = 0; j < L; ++j) pf_project(p.K9f, kstd, T, cx.obj[3 * j], cx.obj[3 * j + 1], cx.obj[3 * j + 2], u[j], v[j]);
+      for (int j = 0; j < L; ++j) {
+        pf_project(p.K9f, kstd, T, cx.obj[3 * j], cx.obj[3 * j + 1], cx.obj[3 * j + 2], u[j], v[j]);
+        if (DIST) pf_distort(p.K9f, p.dist, u[j], v[j]);   // row f3: score against the raw (distorted) blob centres
+      }
       float m[L];
       int am[L];
       pf_nearest_pruned<L>(cx.bt, blobs, u, v, m, am);
@@ -762,12 +766,13 @@ __device__ __noinline__ void pf_grid_fill(const pf_kparams& p, int trk, pf_bar& 
 // track mode also Gauss-Newton + updatePose + next frame's prediction
 // (:685-703, :707-719, :2011-2035, :995-1010).
 // ---------------------------------------------------------------------------------------
-template <int L, bool SH>
+template <int L, int V>
 __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, pf_ctx& cx, pf_tracker_state& st, pf_tail_smem& ts,
                                            const pf_blob* blobs, int trk, int frame, int iters, int best_it,
                                            float highest, const pf_red& kept, bool accept, bool resampled,
                                            const pf_red& cnt)
 {
+  constexpr bool SH = V == 1, DIST = V == 2;
   const int N = p.N;
   const int lane = threadIdx.x & 31;
   const bool writer = blockIdx.x == 0 && lane == 0;
@@ -788,7 +793,7 @@ __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, pf_ctx& cx, pf_t
   int npairs = 0;
 #pragma unroll
   for (int j = 0; j < 2 * L; ++j) pairs[j] = 0u;
-  (void)pf_score_warp<L>(blobs, cx.fc.D, p.K9f, p.kstd != 0, Tw, cx.obj, p.score, pairs, &npairs, lane);
+  (void)pf_score_warp<L>(blobs, cx.fc.D, p.K9f, p.kstd != 0, DIST ? p.dist : nullptr, Tw, cx.obj, p.score, pairs, &npairs, lane);
   if (writer) {
     res->status = accept ? 1 : 4;
     res->iterations = iters;
@@ -897,11 +902,13 @@ __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, pf_ctx& cx, pf_t
 // ---------------------------------------------------------------------------------------
 // The persistent frame kernel.
 // ---------------------------------------------------------------------------------------
-// SH = true: the stage-per-launch variants of the sharded filter (modes 3-5); a separate
-// instantiation so that the single-GPU kernel carries none of their code.
-template <int L, bool SH>
+// Variants (separate instantiations, so that the plain single-GPU kernel carries none of their code):
+// V = 1: the stage-per-launch forms of the sharded filter (modes 3-5); V = 2: forward plumb_bob
+// distortion in the projection (row f3).
+template <int L, int V>
 __global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid_constant__ pf_kparams p)
 {
+  constexpr bool SH = V == 1;
   extern __shared__ __align__(16) unsigned char pf_dyn_smem[];
   pf_blob* blobs = reinterpret_cast<pf_blob*>(pf_dyn_smem);
   __shared__ pf_ctx cx;
@@ -975,7 +982,7 @@ __global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid
     // Sharded single filter (modes 3-5): one stage per launch; the collectives across the GPUs and the
     // do/while decision sit between the launches (pf_monocular_pose_estimator_b200/sharded.py).
     while (!SH || p.mode < 4) {
-      pf_red r = pf_stage_score<L, SH>(p, cx, blobs, tab, trk, (SH && p.mode == 3) ? p.pass_it : (regen ? best_it : it), warp_agg);
+      pf_red r = pf_stage_score<L, V>(p, cx, blobs, tab, trk, (SH && p.mode == 3) ? p.pass_it : (regen ? best_it : it), warp_agg);
       if (it == 0) pf_stamp(p, 2);
       r = pf_grid_reduce(r, red_smem, p, bar, warp_agg);
       if (it == 0) pf_stamp(p, 3);
@@ -1047,7 +1054,7 @@ __global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid
     }
     __syncwarp();
     if (threadIdx.x < 32 && (p.mode == 1 || blockIdx.x == 0))
-      pf_frame_tail<L, SH>(p, cx, st, ts, blobs, trk, frame, iters, best_it, highest, kept, accept, resampled, cnt);
+      pf_frame_tail<L, V>(p, cx, st, ts, blobs, trk, frame, iters, best_it, highest, kept, accept, resampled, cnt);
     pf_stamp(p, 8);
     pf_stamp(p, 9);
   }

@@ -222,6 +222,22 @@ PF_HD void pf_project(const float* __restrict__ K9, bool kstd, const pf_pose& T,
   v = p1 * r;
 }
 
+// Forward plumb_bob distortion of a projected pixel (row f3): the model of LEDDetector::distortPoints
+// (led_detector.cpp:371-414) -- normalise with K, radial (k1, k2, k3) and tangential (p1, p2) terms, back
+// to pixels -- so that particles can be scored against the raw, still-distorted blob centres.
+// d = (k1, k2, p1, p2, k3), the CameraInfo.D order.
+PF_HD void pf_distort(const float* K9, const float* d, float& u, float& v)
+{
+  const float fx = K9[0], fy = K9[4], cx = K9[2], cy = K9[5];
+  const float x = (u - cx) / fx, y = (v - cy) / fy;
+  const float r2 = x * x + y * y;
+  const float rad = 1.0f + d[0] * r2 + d[1] * r2 * r2 + d[4] * r2 * r2 * r2;
+  const float xc = x * rad + (2.0f * d[2] * x * y + d[3] * (r2 + 2.0f * x * x));
+  const float yc = y * rad + (d[2] * (r2 + 2.0f * y * y) + 2.0f * d[3] * x * y);
+  u = xc * fx + cx;
+  v = yc * fy + cy;
+}
+
 // ----------------------------------------------------------------------------------------
 // Scoring (:2385-2445) in the per-LED-minimum form: for every LED the nearest
 // blob (ties -> smallest blob index), then LEDs in ascending (min, j) order, at most

@@ -200,7 +200,7 @@ __device__ __forceinline__ void pf_blk6_inverse(const pf_blk6& f, double* cov)
 // across lanes on a packed key (squared distances are >= 0, so their bit patterns order like the
 // values; ties go to the smaller blob index as in the per-particle loop).
 template <int L, typename Blob>
-__device__ __forceinline__ float pf_score_warp(const Blob* blobs, int D, const float* K9f, bool kstd, const pf_pose& T,
+__device__ __forceinline__ float pf_score_warp(const Blob* blobs, int D, const float* K9f, bool kstd, const float* dist, const pf_pose& T,
                                                const float* obj, const pf_score_cfg& sc, unsigned* pairs, int* npairs,
                                                int lane)
 {
@@ -210,6 +210,7 @@ __device__ __forceinline__ float pf_score_warp(const Blob* blobs, int D, const f
   for (int j = 0; j < L; ++j) {
     float u, v;
     pf_project(K9f, kstd, T, obj[3 * j], obj[3 * j + 1], obj[3 * j + 2], u, v);
+    if (dist) pf_distort(K9f, dist, u, v);
     unsigned long long key = ((unsigned long long)__float_as_uint(INFINITY) << 32);
     for (int i = lane; i < D; i += 32) {
       const Blob z = blobs[i];                            // any order: the key carries the blob index

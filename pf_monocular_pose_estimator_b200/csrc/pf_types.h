@@ -116,6 +116,7 @@ struct pf_kparams {
   double min_ang, max_ang, min_tr, max_tr;   // minAngularNoise.. (track mode recomputes the ranges per frame)
   const uint32_t* rng_tab;        // [4*256]
   unsigned long long* timeline;   // optional [16] globaltimer stamps of the last frame (CTA 0, thread 0)
+  float dist[5];                  // plumb_bob (k1, k2, p1, p2, k3), used by the V = 2 kernel (PFMPE_FLAG_DISTORT)
   pf_gfill* gfill;                // grid mode: list of the heavy steps of the current resampling
   int gfill_cap;                  // entries it can hold
   // sharded single filter (modes 3-5): this handle owns global particles [goff, goff + N) of N_global

@@ -51,6 +51,7 @@ struct pfmpe_handle {
   std::vector<char> particles_set;
   std::vector<double> markers;   // [tracker][PF_MAX_LED*3]
   double K[9]{};
+  double D5[5]{};
   cudaStream_t stream = nullptr;
   bool own_stream = false;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -173,6 +174,7 @@ void fill_kparams(const pfmpe_handle* h, pf_kparams& p)
   p.obj_f = h->obj_f; p.obj_d = h->obj_d;
   for (int i = 0; i < 9; ++i) { p.K9d[i] = h->K[i]; p.K9f[i] = (float)h->K[i]; }
   p.kstd = pf_k_is_std(p.K9f) ? 1 : 0;
+  for (int i = 0; i < 5; ++i) p.dist[i] = (float)h->D5[i];
   p.score.tol = (float)h->prm.back_projection_pixel_tolerance;
   p.score.inv_tol = (float)(1.0 / h->prm.back_projection_pixel_tolerance);
   p.score.tol_pf = (float)h->prm.back_projection_pixel_tolerance_PF;
@@ -192,7 +194,7 @@ void fill_kparams(const pfmpe_handle* h, pf_kparams& p)
 
 typedef void (*frames_kernel_t)(const pf_kparams);
 
-template <bool SH>
+template <int SH>
 frames_kernel_t kernel_for_sh(int L)
 {
   switch (L) {
@@ -208,7 +210,10 @@ frames_kernel_t kernel_for_sh(int L)
   }
 }
 
-frames_kernel_t kernel_for(int L, bool shard) { return shard ? kernel_for_sh<true>(L) : kernel_for_sh<false>(L); }
+frames_kernel_t kernel_for(int L, int variant)
+{
+  return variant == 1 ? kernel_for_sh<1>(L) : (variant == 2 ? kernel_for_sh<2>(L) : kernel_for_sh<0>(L));
+}
 
 // per-launch arguments of the sharded-filter stages (modes 3-5)
 struct ShardArgs {
@@ -242,7 +247,9 @@ int launch_meancov(pfmpe_handle* h, int t0, int nt)
 int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_frames, const ShardArgs* sa = nullptr)
 {
   const int N = h->cfg.n_particles;
-  frames_kernel_t k = kernel_for(h->cfg.n_leds, mode >= 3);
+  const bool distort = (h->cfg.flags & PFMPE_FLAG_DISTORT) != 0;
+  if (distort && mode != 0) return fail(h, PFMPE_ERR_UNSUPPORTED, "PFMPE_FLAG_DISTORT: per-frame API only (the Gauss-Newton tail needs undistorted points)");
+  frames_kernel_t k = kernel_for(h->cfg.n_leds, mode >= 3 ? 1 : (distort ? 2 : 0));
   if (!k) return fail(h, PFMPE_ERR_UNSUPPORTED, "n_leds must be 1..8");
   const size_t smem = (size_t)h->cfg.max_blobs * sizeof(pf_blob);
   bool grid_mode;
@@ -513,9 +520,10 @@ int pfmpe_set_markers(pfmpe_handle* h, int tracker, const double* xyz, int n_led
 
 int pfmpe_set_camera(pfmpe_handle* h, const double K[9], const double* D5)
 {
-  (void)D5;   // the PF projects with K only (project2d); D is accepted for interface parity
+  // the reference's PF projects with K only (project2d); D is used by PFMPE_FLAG_DISTORT (row f3)
   if (!h || !K) return PFMPE_ERR_INVALID;
   std::memcpy(h->K, K, sizeof h->K);
+  for (int i = 0; i < 5; ++i) h->D5[i] = D5 ? D5[i] : 0.0;
   h->have_camera = true;
   return PFMPE_OK;
 }

@@ -8,7 +8,7 @@ from pf_monocular_pose_estimator_b200 import capi
 def make_handle(fi, N, n_trackers=1, max_blobs=None, **kw):
     D = np.asarray(fi["img"]).reshape(-1, 2).shape[0]
     h = capi.Handle(N, n_trackers=n_trackers, n_leds=fi["markers"].shape[0], max_blobs=max_blobs or max(D, 1), **kw)
-    h.configure(fi["markers"], fi["K"], fi["params"])
+    h.configure(fi["markers"], fi["K"], fi["params"], fi.get("D5"))
     return h
 
 

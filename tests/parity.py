@@ -29,6 +29,8 @@ def _near_tie_particles(fi, T_oracle):
         return flagged
     for n in range(N):
         uv = S.project(fi["K"], T_oracle[n], fi["markers"])
+        if fi.get("D5") is not None:
+            uv = orc.distort_points(fi["K"], fi["D5"], uv)
         d = np.sqrt(((img[:, None, :] - uv[None, :, :]) ** 2).sum(-1))   # (D, L)
         ds = np.sort(d, axis=0)
         if (np.abs(ds[0] - tol_pf) < GATE_EPS).any():

@@ -335,3 +335,31 @@ def test_roi_prediction_matches_oracle(N, mode):
     assert ref[2] == 0.0 and ref[3] == 0.0 and roi[2] == 0.0 and roi[3] == 0.0
     np.testing.assert_allclose(roi, ref, rtol=1e-5, atol=2e-3)
     h.close()
+
+
+@pytest.mark.parametrize("N,mode", [(100, 0), (20000, 0), (2000, 1)])
+def test_plumb_bob_projection_option(N, mode):
+    """Row f3 (PFMPE_FLAG_DISTORT): particles are projected through K and the plumb_bob model of
+    LEDDetector::distortPoints (led_detector.cpp:371-414) and scored against the raw blob centres."""
+    D5 = np.array([-0.28, 0.09, 1.2e-3, -7e-4, 0.01])
+    fi = frame_inputs(N, frame=13)
+    fi["img"] = orc.distort_points(fi["K"], D5, fi["img"])
+    fi["D5"] = D5
+    ora = orc.pf_update(resampler=(0 if N <= 1000 else 1), dist=D5, **{k: v for k, v in fi.items() if k not in ("truth", "D5")})
+    assert ora["resampled"] == 1
+    h = make_handle(fi, N, flags=capi.FLAG_DISTORT, force_mode=mode)
+    got = run_frame(h, fi)
+    res = parity.check_frame(fi, got, ora)
+    assert res["index_mismatch"] == 0
+    _check_pairs(got, ora)
+    # the same raw detections through the undistorted model give different scores: the option is doing something
+    h0 = make_handle(fi, N, force_mode=mode)
+    g0 = run_frame(h0, fi)
+    assert np.abs(g0["w_raw"] - got["w_raw"]).max() > 1e-3
+    # the device-resident tracking modes need undistorted points for Gauss-Newton: refused, not silently wrong
+    with pytest.raises(capi.PfmpeError):
+        h.track_init(fi["T_cur"], 0.0, fi["T_pred"], 0.02)
+        sc = S.Scene(0)
+        h.track_upload(np.zeros((1, 1, h.max_blobs, 2)), np.zeros((1, 1), dtype=np.int32), np.array([0.04]), np.ones((1, 1), dtype=np.uint32))
+        h.track_run(0, 1)
+    h.close(); h0.close()

@@ -239,3 +239,21 @@ def test_predict_roi_matches_a_direct_numpy_evaluation():
     uvw = cam @ np.asarray(fi["K"]).reshape(3, 3).T
     u, v = uvw[..., 0] / uvw[..., 2], uvw[..., 1] / uvw[..., 2]
     np.testing.assert_allclose(roi, [u.min(), v.min(), max(0.0, u.max()), max(0.0, v.max())], rtol=1e-12)
+
+
+def test_distort_point_is_the_plumb_bob_model():
+    """orc_distort_point (led_detector.cpp:371-414) against the closed form; zero coefficients = identity."""
+    import numpy as np
+    from oracle import orc
+    from pf_monocular_pose_estimator_b200 import scenes as S
+    K = np.asarray(S.K_README, dtype=float).reshape(3, 3)
+    pts = np.array([[100.0, 50.0], [376.0, 240.0], [700.5, 470.25]])
+    assert np.abs(orc.distort_points(K, np.zeros(5), pts) - pts).max() < 1e-10
+    k1, k2, p1, p2, k3 = D5 = np.array([-0.3, 0.1, 1e-3, -2e-3, 0.02])
+    x, y = (pts[:, 0] - K[0, 2]) / K[0, 0], (pts[:, 1] - K[1, 2]) / K[1, 1]
+    r2 = x * x + y * y
+    rad = 1 + k1 * r2 + k2 * r2 ** 2 + k3 * r2 ** 3
+    xd = x * rad + 2 * p1 * x * y + p2 * (r2 + 2 * x * x)
+    yd = y * rad + p1 * (r2 + 2 * y * y) + 2 * p2 * x * y
+    ref = np.c_[xd * K[0, 0] + K[0, 2], yd * K[1, 1] + K[1, 2]]
+    np.testing.assert_allclose(orc.distort_points(K, D5, pts), ref, rtol=1e-13)
