@@ -379,6 +379,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-batched", action="store_true", help="skip the short cfg4 run reported under batched_trackers")
     ap.add_argument("--no-sharded", action="store_true", help="skip the short configs[4] run reported under sharded_filter")
+    ap.add_argument("--trackers", type=int, default=None, help="override the tracker count of the workload (experiments)")
     ap.add_argument("--e2e-steps", type=int, default=300)
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     args = ap.parse_args()
@@ -389,6 +390,8 @@ def main():
         args.steps = WORKLOADS[args.workload][3]
     args.warmup = max(args.warmup, 3)
     n_p, n_t_total, n_out, _ = WORKLOADS[args.workload]
+    if args.trackers:
+        n_t_total = args.trackers
     sharded = n_t_total > 1
     cfg = {"workload": args.workload, "desc": WORKLOAD_DESC[args.workload], "particles": n_p, "leds": L_LED,
            "blobs": L_LED + n_out}

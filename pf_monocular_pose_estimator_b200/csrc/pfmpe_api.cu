@@ -61,6 +61,8 @@ struct pfmpe_handle {
   int force_mode = 0;            // 0 auto, 1 batch, 2 grid (cfg.reserved[0])
   int grid_cap = 0;              // cfg.reserved[1]
   int info[4] = {0, 0, PF_BLOCK, 0};
+  int batch_nt = -1, batch_block = PF_BLOCK;   // cached block-size choice of the batch shape
+  const void* batch_kernel = nullptr;
   // device
   float4 *pose0 = nullptr, *pose1 = nullptr, *gather_tmp = nullptr;
   float* w = nullptr;
@@ -278,10 +280,30 @@ int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_f
   if (!grid_mode) {
     p.coop = 0;
     p.tracker_base = t0;
-    p.cta_chunk = (N + PF_BLOCK - 1) / PF_BLOCK * PF_BLOCK;
+    // Block size of the one-CTA-per-filter shape: the CTAs of a batch run in waves over the resident
+    // slots (SMs x CTAs per SM), so the size that needs the fewest (waves x steps per thread) wins:
+    // e.g. 512 filters on 148 SMs fit one wave of 192-thread CTAs (4 per SM) but need two of 256-thread ones.
+    int block = PF_BLOCK;
+    if (nt > 1 && mode != 5 && h->batch_nt == nt && h->batch_kernel == (const void*)k) block = h->batch_block;
+    else if (nt > 1 && mode != 5) {
+      long long best = -1, cost256 = -1;
+      for (int b = PF_BLOCK; b >= 128; b -= 32) {
+        int per_sm = 0;
+        PF_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, b, smem));
+        if (per_sm < 1) continue;
+        const long long slots = (long long)per_sm * h->num_sms;
+        const long long cost = ((nt + slots - 1) / slots) * ((N + b - 1) / b);
+        if (b == PF_BLOCK) cost256 = cost;
+        if (best < 0 || cost < best) { best = cost; block = b; }
+      }
+      if (cost256 > 0 && best * 10 > cost256 * 9) block = PF_BLOCK;   // the model is coarse: only a clear win changes the default
+      if (const char* e = std::getenv("PFMPE_BATCH_BLOCK")) { const int b = std::atoi(e); if (b >= 32 && b <= PF_BLOCK && b % 32 == 0) block = b; }
+      h->batch_nt = nt; h->batch_kernel = (const void*)k; h->batch_block = block;
+    }
+    p.cta_chunk = (N + block - 1) / block * block;
     dim3 grid(1, (unsigned)nt, 1);
-    h->info[0] = 1; h->info[1] = nt; h->info[2] = PF_BLOCK; h->info[3] = 0;
-    k<<<grid, PF_BLOCK, smem, h->stream>>>(p);
+    h->info[0] = 1; h->info[1] = nt; h->info[2] = block; h->info[3] = 0;
+    k<<<grid, block, smem, h->stream>>>(p);
     PF_CUDA(h, cudaGetLastError());
     h->launches += 1;
   } else {
