@@ -477,8 +477,10 @@ def main():
         (e_pme,) = allreduce([e["pme"]], RO.SUM if RO else None)
         line["e2e"] = {"value": e_pme / e_sec, "unit": "PME/s", "h2d_bytes_per_step": e["h2d"], "d2h_bytes_per_step": e["d2h"],
                        "steps": e["steps"], "p50_ms": e["p50_ms"], "trackers_per_rank": e["trackers"], "all_frames_accepted": e["ok"],
-                       "path": "pfmpe_track_frame_host(_batch) per frame: host predictPose -> H2D -> PF update -> D2H -> host "
-                               "Gauss-Newton (FP64), looped in C by pfmpe_track_sequence_host"}
+                       "path": "pfmpe_track_frame_host(_batch) per frame from HOST buffers: host predictPose -> PF update launch "
+                               "(one tracker: the frame's inputs travel inside the kernel parameter block; batches: pinned "
+                               "H2D copy) -> result record written by the kernel into pinned host memory -> host "
+                               "Gauss-Newton (FP64); looped in C by pfmpe_track_sequence_host"}
 
     # ---- BASELINE configs[3] alongside (short): 4096 trackers x 4096 particles split over the ranks
     if not sharded and not args.no_batched:

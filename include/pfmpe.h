@@ -268,7 +268,8 @@ int pfmpe_shard_winner(pfmpe_handle* h, int local_index, pfmpe_frame_out* out);
 /* ---- streams / timing ---------------------------------------------------------------------- */
 int pfmpe_set_stream(pfmpe_handle* h, void* cuda_stream); /* use an external cudaStream_t (e.g. torch's) */
 int pfmpe_sync(pfmpe_handle* h);
-/* device time of the most recent pfmpe_update* / pfmpe_track_run launch (CUDA events on the handle's stream) */
+/* device time of the most recent pfmpe_track_run / pfmpe_track_replay launch (CUDA events on the handle's
+ * stream); the per-frame calls (pfmpe_update*) are the latency path and record no events */
 int pfmpe_last_launch_ms(pfmpe_handle* h, float* ms);
 /* number of kernels this handle has launched so far */
 int pfmpe_launch_count(const pfmpe_handle* h, uint64_t* n);

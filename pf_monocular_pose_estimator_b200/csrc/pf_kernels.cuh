@@ -933,7 +933,7 @@ __global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid
     const uint32_t* g32 = reinterpret_cast<const uint32_t*>(p.state + trk);
     uint32_t* s32 = reinterpret_cast<uint32_t*>(&st);
     for (int i = threadIdx.x; i < (int)(sizeof(pf_tracker_state) / 4); i += blockDim.x) s32[i] = g32[i];
-    const uint32_t* h32 = reinterpret_cast<const uint32_t*>(p.fconst + trk);
+    const uint32_t* h32 = reinterpret_cast<const uint32_t*>(p.inline_in ? &p.fc_inline : p.fconst + trk);
     uint32_t* f32 = reinterpret_cast<uint32_t*>(&cx.fc);
     for (int i = threadIdx.x; i < (int)(sizeof(pf_frame_const) / 4); i += blockDim.x) f32[i] = h32[i];
     if (threadIdx.x < 3 * L) {
@@ -965,8 +965,9 @@ __global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid
     const int D = cx.fc.D;
     if (threadIdx.x < 32) {
       const bool seq_mode = p.mode == 1 || p.mode == 2;
-      const double* bsrc = p.blobs + ((size_t)trk * (seq_mode ? p.total_frames : 1) + (seq_mode ? frame : 0)) *
-                                         (size_t)p.D_max * 2;
+      const double* bsrc = p.inline_in ? p.blobs_inline
+                                       : p.blobs + ((size_t)trk * (seq_mode ? p.total_frames : 1) + (seq_mode ? frame : 0)) *
+                                                       (size_t)p.D_max * 2;
       pf_stage_blobs(bsrc, D, p.score.tol_pf, cx.bt, blobs, threadIdx.x);
     }
     __syncthreads();

@@ -65,6 +65,8 @@ struct pf_cta_agg {
   long long s, mx, mn, pad;
 };
 
+#define PF_INLINE_BLOBS 32
+
 // grid mode: heavy steps of the current resampling, filled by the whole grid (pf_grid_fill).
 // ent = (first source of the step, first slot, number of slots, 0)
 struct pf_gfill {
@@ -116,6 +118,11 @@ struct pf_kparams {
   double min_ang, max_ang, min_tr, max_tr;   // minAngularNoise.. (track mode recomputes the ranges per frame)
   const uint32_t* rng_tab;        // [4*256]
   unsigned long long* timeline;   // optional [16] globaltimer stamps of the last frame (CTA 0, thread 0)
+  // per-frame API, one tracker, few detections: the frame's inputs travel in the parameter block
+  // (no host->device copy before the launch)
+  int inline_in;
+  pf_frame_const fc_inline;
+  double blobs_inline[2 * PF_INLINE_BLOBS];
   float dist[5];                  // plumb_bob (k1, k2, p1, p2, k3), used by the V = 2 kernel (PFMPE_FLAG_DISTORT)
   pf_gfill* gfill;                // grid mode: list of the heavy steps of the current resampling
   int gfill_cap;                  // entries it can hold

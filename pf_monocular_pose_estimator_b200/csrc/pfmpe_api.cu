@@ -194,6 +194,7 @@ void fill_kparams(const pfmpe_handle* h, pf_kparams& p)
   p.timeline = h->timeline_on ? h->timeline : nullptr;
 }
 
+static_assert(sizeof(pf_kparams) <= 4096, "kernel parameter block must stay within the classic 4 KB limit");
 typedef void (*frames_kernel_t)(const pf_kparams);
 
 template <int SH>
@@ -244,9 +245,18 @@ int launch_meancov(pfmpe_handle* h, int t0, int nt)
   return PFMPE_OK;
 }
 
+// per-frame API, latency path: inputs inside the parameter block, result record written to pinned host memory
+struct InlineArgs {
+  const pf_frame_const* fc = nullptr;
+  const double* blobs = nullptr;   // D x 2, D <= PF_INLINE_BLOBS
+  int D = 0;
+  pf_frame_result* result = nullptr;   // device-accessible (mapped pinned) array indexed by tracker
+};
+
 // Launch the frame kernel for trackers [t0, t0+nt).  mode 0: per-frame, 1: track, 2: replay,
 // 3/4/5: one stage of the sharded filter.
-int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_frames, const ShardArgs* sa = nullptr)
+int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_frames, const ShardArgs* sa = nullptr,
+                  const InlineArgs* ia = nullptr)
 {
   const int N = h->cfg.n_particles;
   const bool distort = (h->cfg.flags & PFMPE_FLAG_DISTORT) != 0;
@@ -276,7 +286,18 @@ int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_f
   } else {
     p.blobs = h->blobs; p.result = h->result; p.total_frames = 1;
   }
-  PF_CUDA(h, cudaEventRecord(h->ev0, h->stream));
+  if (ia) {
+    if (ia->result) p.result = ia->result;
+    if (ia->fc) {
+      p.inline_in = 1;
+      p.fc_inline = *ia->fc;
+      std::memcpy(p.blobs_inline, ia->blobs, sizeof(double) * 2 * (size_t)ia->D);
+    }
+  }
+  // CUDA events bracket the launches of the sequence modes (pfmpe_last_launch_ms); the per-frame
+  // latency path does without them
+  const bool timed = mode == 1 || mode == 2;
+  if (timed) PF_CUDA(h, cudaEventRecord(h->ev0, h->stream));
   if (!grid_mode) {
     p.coop = 0;
     p.tracker_base = t0;
@@ -332,8 +353,8 @@ int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_f
       h->launches += 1;
     }
   }
-  PF_CUDA(h, cudaEventRecord(h->ev1, h->stream));
-  h->timing_valid = true;
+  if (timed) PF_CUDA(h, cudaEventRecord(h->ev1, h->stream));
+  h->timing_valid = timed;
   return PFMPE_OK;
 }
 
@@ -633,7 +654,16 @@ static int run_update(pfmpe_handle* h, int t0, int nt, const pfmpe_frame_in* in,
     if (rc) return rc;
   }
   const int T = h->cfg.n_trackers;
-  if (nt == T) {
+  const bool want_mean = (h->cfg.flags & PFMPE_FLAG_MEAN_COV) != 0;
+  // latency path: one tracker with few detections carries its inputs in the kernel parameters; the
+  // result record is written by the kernel straight into pinned host memory (no copies either way)
+  InlineArgs ia;
+  const bool inline_in = nt == 1 && in[0].n_image_points <= PF_INLINE_BLOBS;
+  if (inline_in) {
+    ia.fc = reinterpret_cast<const pf_frame_const*>(h->h_inbox) + t0;
+    ia.blobs = reinterpret_cast<const double*>(h->h_inbox + h->blobs_off) + (size_t)t0 * h->cfg.max_blobs * 2;
+    ia.D = in[0].n_image_points;
+  } else if (nt == T) {
     PF_CUDA(h, cudaMemcpyAsync(h->inbox, h->h_inbox, h->inbox_bytes, cudaMemcpyHostToDevice, h->stream));
   } else {
     PF_CUDA(h, cudaMemcpyAsync(h->fconst + t0, reinterpret_cast<pf_frame_const*>(h->h_inbox) + t0,
@@ -642,13 +672,14 @@ static int run_update(pfmpe_handle* h, int t0, int nt, const pfmpe_frame_in* in,
     PF_CUDA(h, cudaMemcpyAsync(h->blobs + off, reinterpret_cast<double*>(h->h_inbox + h->blobs_off) + off,
                                sizeof(double) * 2 * (size_t)h->cfg.max_blobs * nt, cudaMemcpyHostToDevice, h->stream));
   }
-  rc = launch_frames(h, 0, t0, nt, 0, 1);
+  if (!want_mean) ia.result = h->h_result;
+  rc = launch_frames(h, 0, t0, nt, 0, 1, nullptr, &ia);
   if (rc) return rc;
-  if (h->cfg.flags & PFMPE_FLAG_MEAN_COV) {
+  if (want_mean) {
     rc = launch_meancov(h, t0, nt);
     if (rc) return rc;
+    PF_CUDA(h, cudaMemcpyAsync(h->h_result + t0, h->result + t0, sizeof(pf_frame_result) * nt, cudaMemcpyDeviceToHost, h->stream));
   }
-  PF_CUDA(h, cudaMemcpyAsync(h->h_result + t0, h->result + t0, sizeof(pf_frame_result) * nt, cudaMemcpyDeviceToHost, h->stream));
   PF_CUDA(h, cudaStreamSynchronize(h->stream));
   for (int i = 0; i < nt; ++i) {
     unpack_result(h->h_result[t0 + i], out + i);
