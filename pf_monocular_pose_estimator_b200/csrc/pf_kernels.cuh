@@ -813,6 +813,10 @@ __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, pf_ctx& cx, pf_t
     res->npairs = npairs;
     res->gn_iters = -1;
     res->flag_fail = accept ? 1.0f : 4.0f;
+    if (p.done_seq) {     // per-frame latency path: the host polls this word instead of waiting for the kernel to retire
+      __threadfence_system();
+      *reinterpret_cast<volatile int32_t*>(&res->pad) = p.done_seq;
+    }
   }
   __syncwarp();
   pf_stamp(p, 7);

@@ -4,6 +4,7 @@
 // needs the device fails with PFMPE_ERR_NO_DEVICE / PFMPE_ERR_CUDA if it is not usable.
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -56,6 +57,7 @@ struct pfmpe_handle {
   bool own_stream = false;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   bool timing_valid = false;
+  int done_seq = 0;
   uint64_t launches = 0;
   int num_sms = 0;
   int force_mode = 0;            // 0 auto, 1 batch, 2 grid (cfg.reserved[0])
@@ -251,6 +253,7 @@ struct InlineArgs {
   const double* blobs = nullptr;   // D x 2, D <= PF_INLINE_BLOBS
   int D = 0;
   pf_frame_result* result = nullptr;   // device-accessible (mapped pinned) array indexed by tracker
+  int done_seq = 0;                    // != 0: publish the record with this sequence number (host polls)
 };
 
 // Launch the frame kernel for trackers [t0, t0+nt).  mode 0: per-frame, 1: track, 2: replay,
@@ -288,6 +291,7 @@ int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_f
   }
   if (ia) {
     if (ia->result) p.result = ia->result;
+    p.done_seq = ia->done_seq;
     if (ia->fc) {
       p.inline_in = 1;
       p.fc_inline = *ia->fc;
@@ -673,8 +677,33 @@ static int run_update(pfmpe_handle* h, int t0, int nt, const pfmpe_frame_in* in,
                                sizeof(double) * 2 * (size_t)h->cfg.max_blobs * nt, cudaMemcpyHostToDevice, h->stream));
   }
   if (!want_mean) ia.result = h->h_result;
+  const bool poll = !want_mean && nt == 1;
+  if (poll) {
+    h->done_seq = h->done_seq == 0x7fffffff ? 1 : h->done_seq + 1;
+    ia.done_seq = h->done_seq;
+    reinterpret_cast<volatile int32_t*>(&h->h_result[t0].pad)[0] = 0;
+  }
   rc = launch_frames(h, 0, t0, nt, 0, 1, nullptr, &ia);
   if (rc) return rc;
+  if (poll) {
+    // the record is complete as soon as its sequence word arrives (written last, after a system-scope
+    // fence); the rest of the kernel (state mirror, CTA exit) overlaps with the host tail.  Later calls
+    // are ordered behind it on the stream.  cudaStreamQuery guards against a failed launch.
+    volatile int32_t* flag = reinterpret_cast<volatile int32_t*>(&h->h_result[t0].pad);
+    for (unsigned spin = 1;; ++spin) {
+      if (*flag == ia.done_seq) break;
+      if ((spin & 0x3fffu) == 0) {
+        const cudaError_t q = cudaStreamQuery(h->stream);
+        if (q == cudaSuccess) { if (*flag == ia.done_seq) break; return fail(h, PFMPE_ERR_CUDA, "frame kernel retired without a result"); }
+        if (q != cudaErrorNotReady) { h->err = std::string("frame kernel: ") + cudaGetErrorString(q); return PFMPE_ERR_CUDA; }
+      }
+    }
+    std::atomic_thread_fence(std::memory_order_acquire);
+    unpack_result(h->h_result[t0], out);
+    h->last_sum_fx[t0] = h->h_result[t0].sum_fx;
+    h->last_was_track = false;
+    return PFMPE_OK;
+  }
   if (want_mean) {
     rc = launch_meancov(h, t0, nt);
     if (rc) return rc;
