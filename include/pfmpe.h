@@ -261,6 +261,26 @@ int pfmpe_shard_ipc_export(pfmpe_handle* h, unsigned char handle[64]);
 int pfmpe_shard_ipc_open(pfmpe_handle* h, const unsigned char handle[64], void** d_ptr);
 int pfmpe_shard_set_peers(pfmpe_handle* h, int world, void* const* d_ptrs);
 int pfmpe_shard_scatter(pfmpe_handle* h, int64_t first_owned_slot, int64_t count);
+/* Peer mailboxes (replace the NCCL all_gather / barrier / broadcast and their device->host copies):
+ * every rank creates a mailbox (pfmpe_shard_mail_create returns its device pointer and, for other
+ * processes, a CUDA IPC handle to open with pfmpe_shard_ipc_open) and installs the table of all
+ * ranks' mailboxes (pfmpe_shard_mail_set_peers, rank order, world <= 32).  From then on
+ *   - pfmpe_shard_score / pfmpe_shard_resample deliver their partial from inside the kernel to every
+ *     rank with NVLink peer stores; pfmpe_shard_collect(h, -1, table) returns all of them
+ *     (table[world][32] int64; word 2 of the resample partial is not exchanged: a rank's end slot is
+ *     the next rank's first slot);
+ *   - pfmpe_shard_barrier is a stream-ordered barrier across the ranks (no host wait);
+ *   - pfmpe_shard_winner_publish (owner only) sends winner pose + correspondences to every rank:
+ *     words 0-5 = 12 floats, 6-13 = 16 uint32 pairs, 14 = n; the other ranks call
+ *     pfmpe_shard_advance; everybody reads it with pfmpe_shard_collect(h, owner, table).
+ * Every rank must take part in every exchange in the same order.  PFMPE_ERR_COMM if a message does
+ * not arrive within ~2 s. */
+int pfmpe_shard_mail_create(pfmpe_handle* h, int world, int rank, void** d_ptr, unsigned char ipc_handle[64]);
+int pfmpe_shard_mail_set_peers(pfmpe_handle* h, void* const* d_ptrs);
+int pfmpe_shard_collect(pfmpe_handle* h, int only_rank, int64_t* table);
+int pfmpe_shard_advance(pfmpe_handle* h);
+int pfmpe_shard_barrier(pfmpe_handle* h);
+int pfmpe_shard_winner_publish(pfmpe_handle* h, int local_index);
 /* pose + correspondences (:687-691 / :714-716) of the local particle `local_index` of the last pass;
  * only winner_pose / correspondences / n_correspondences of `out` are meaningful */
 int pfmpe_shard_winner(pfmpe_handle* h, int local_index, pfmpe_frame_out* out);

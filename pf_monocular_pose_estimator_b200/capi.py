@@ -28,6 +28,8 @@ EXPORTS = [
     "pfmpe_predict_roi",
     "pfmpe_shard_configure", "pfmpe_shard_begin_frame", "pfmpe_shard_score", "pfmpe_shard_resample",
     "pfmpe_shard_export", "pfmpe_shard_keep", "pfmpe_shard_import", "pfmpe_shard_winner",
+    "pfmpe_shard_mail_create", "pfmpe_shard_mail_set_peers", "pfmpe_shard_collect", "pfmpe_shard_advance",
+    "pfmpe_shard_barrier", "pfmpe_shard_winner_publish",
     "pfmpe_shard_local_ptr", "pfmpe_shard_ipc_export", "pfmpe_shard_ipc_open", "pfmpe_shard_set_peers", "pfmpe_shard_scatter",
     "pfmpe_set_stream", "pfmpe_sync", "pfmpe_last_launch_ms", "pfmpe_launch_count", "pfmpe_launch_info", "pfmpe_debug_timeline",
 ]
@@ -136,6 +138,12 @@ def lib():
         L.pfmpe_shard_ipc_open.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_void_p)]
         L.pfmpe_shard_set_peers.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]
         L.pfmpe_shard_scatter.argtypes = [C.c_void_p, C.c_int64, C.c_int64]
+        L.pfmpe_shard_mail_create.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p), C.c_char_p]
+        L.pfmpe_shard_mail_set_peers.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
+        L.pfmpe_shard_collect.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int64)]
+        L.pfmpe_shard_advance.argtypes = [C.c_void_p]
+        L.pfmpe_shard_barrier.argtypes = [C.c_void_p]
+        L.pfmpe_shard_winner_publish.argtypes = [C.c_void_p, C.c_int]
         L.pfmpe_shard_winner.argtypes = [C.c_void_p, C.c_int, C.POINTER(FrameOut)]
         L.pfmpe_set_stream.argtypes = [C.c_void_p, C.c_void_p]
         L.pfmpe_sync.argtypes = [C.c_void_p]
@@ -387,6 +395,31 @@ class Handle:
 
     def shard_scatter(self, first_owned_slot, count):
         self._chk(lib().pfmpe_shard_scatter(self._h, int(first_owned_slot), int(count)))
+
+    def shard_mail_create(self, world, rank):
+        """-> (device pointer of this rank's mailbox, its 64-byte CUDA IPC handle)"""
+        q = C.c_void_p()
+        buf = C.create_string_buffer(64)
+        self._chk(lib().pfmpe_shard_mail_create(self._h, world, rank, C.byref(q), buf))
+        return int(q.value), buf.raw
+
+    def shard_mail_set_peers(self, ptrs):
+        arr = (C.c_void_p * len(ptrs))(*[int(v) for v in ptrs])
+        self._chk(lib().pfmpe_shard_mail_set_peers(self._h, arr))
+
+    def shard_collect(self, world, only_rank=-1):
+        out = np.zeros((world, 32), dtype=np.int64)
+        self._chk(lib().pfmpe_shard_collect(self._h, int(only_rank), out.ctypes.data_as(C.POINTER(C.c_int64))))
+        return out
+
+    def shard_advance(self):
+        self._chk(lib().pfmpe_shard_advance(self._h))
+
+    def shard_barrier(self):
+        self._chk(lib().pfmpe_shard_barrier(self._h))
+
+    def shard_winner_publish(self, local_index):
+        self._chk(lib().pfmpe_shard_winner_publish(self._h, int(local_index)))
 
     def shard_winner(self, local_index):
         o = FrameOut()

@@ -903,6 +903,22 @@ __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, pf_ctx& cx, pf_t
   }
 }
 
+// Sharded filter: CTA 0 delivers this rank's partial (nwords payload words + sequence number) to the
+// mailbox of every rank -- its own included -- with peer stores; the sequence word is written last,
+// after a system-scope fence, and the receivers poll for it (pf_shard_wait_kernel).  Replaces the
+// NCCL all_gather + device->host copy between the stages.
+__device__ __forceinline__ void pf_shard_publish(const pf_kparams& p, int nwords)
+{
+  if (!p.xmail_peers || blockIdx.x != 0) return;
+  __syncthreads();                                   // the partial written by this CTA's thread 0
+  if ((int)threadIdx.x < p.xworld) {
+    long long* dst = p.xmail_peers[threadIdx.x] + ((size_t)p.xslot * p.xworld + p.xrank) * PF_XMAIL_WORDS;
+    for (int i = 0; i < nwords; ++i) dst[i] = __ldcg(p.shard_partial + i);
+    __threadfence_system();
+    *reinterpret_cast<volatile long long*>(dst + PF_XMAIL_WORDS - 1) = p.xseq;
+  }
+}
+
 // ---------------------------------------------------------------------------------------
 // The persistent frame kernel.
 // ---------------------------------------------------------------------------------------
@@ -997,6 +1013,7 @@ __global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid
           p.shard_partial[0] = (long long)r.maxkey; p.shard_partial[1] = (long long)r.minkey_inv; p.shard_partial[2] = r.sum;
           p.shard_partial[3] = scr[PF_MAX_WARPS].s; p.shard_partial[4] = scr[PF_MAX_WARPS].mx; p.shard_partial[5] = scr[PF_MAX_WARPS].mn;
         }
+        pf_shard_publish(p, 6);
         break;
       }
       if (regen) break;                                              // r == kept (same particles, exact sums)
@@ -1049,6 +1066,7 @@ __global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid
         pf_tracker_state* g = p.state + trk;
         g->t_buf = 1 - cx.src_buf; g->src_mode = 0; g->frames_done = st.frames_done + 1;
       }
+      pf_shard_publish(p, 2);
       continue;
     }
     // particle-set bookkeeping for the next frame (shared memory copy of every CTA; CTA 0 mirrors it)
@@ -1060,6 +1078,17 @@ __global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid
     __syncwarp();
     if (threadIdx.x < 32 && (p.mode == 1 || blockIdx.x == 0))
       pf_frame_tail<L, V>(p, cx, st, ts, blobs, trk, frame, iters, best_it, highest, kept, accept, resampled, cnt);
+    if (SH && p.mode == 5 && p.xmail_peers) {   // winner pose + correspondences to every rank: 15 words
+      if (blockIdx.x == 0 && threadIdx.x == 0) {
+        const pf_frame_result* res = p.result + trk;
+        const unsigned* wp = reinterpret_cast<const unsigned*>(res->winner_pose);
+        for (int i = 0; i < 6; ++i) p.shard_partial[i] = (long long)(((unsigned long long)wp[2 * i + 1] << 32) | wp[2 * i]);
+        for (int i = 0; i < PF_MAX_LED; ++i)
+          p.shard_partial[6 + i] = (long long)(((unsigned long long)res->pairs[2 * i + 1] << 32) | res->pairs[2 * i]);
+        p.shard_partial[6 + PF_MAX_LED] = res->npairs;
+      }
+      pf_shard_publish(p, 7 + PF_MAX_LED);
+    }
     pf_stamp(p, 8);
     pf_stamp(p, 9);
   }
@@ -1142,6 +1171,43 @@ __global__ void __launch_bounds__(PF_BLOCK) pf_shard_scatter_kernel(const float4
     dst[n] = r0;
     dst[(size_t)N + n] = r1;
     dst[2 * (size_t)N + n] = r2;
+  }
+}
+
+// Sharded filter: wait until the message of exchange `seq` has arrived from every rank (or from
+// `only` alone), sent with peer stores by pf_shard_publish, then -- if host_out is given -- hand the
+// table to the host through pinned memory: [world][PF_XMAIL_WORDS] words followed by the sequence
+// number (or -1 after ~2 s without a complete set: a peer is gone).  Without host_out it is a
+// stream-ordered barrier across the ranks.
+__global__ void pf_shard_wait_kernel(const long long* mail, int slot, int world, int only, long long seq, long long* host_out)
+{
+  const int d = threadIdx.x;
+  bool ok = true;
+  if (d < world && (only < 0 || d == only)) {
+    const volatile long long* m = mail + ((size_t)slot * world + d) * PF_XMAIL_WORDS;
+    const long long t0 = clock64();
+    while (m[PF_XMAIL_WORDS - 1] != seq) {
+      if (clock64() - t0 > 4000000000ll) { ok = false; break; }
+    }
+    __threadfence_system();
+    if (host_out)
+      for (int i = 0; i < PF_XMAIL_WORDS; ++i) host_out[d * PF_XMAIL_WORDS + i] = m[i];
+  }
+  ok = __all_sync(0xffffffffu, ok);
+  if (host_out) {
+    __threadfence_system();
+    __syncwarp();
+    if (d == 0) *reinterpret_cast<volatile long long*>(host_out + (size_t)world * PF_XMAIL_WORDS) = ok ? seq : -1ll;
+  }
+}
+
+// Sharded filter: an empty message to every rank (the sending half of a stream-ordered barrier)
+__global__ void pf_shard_signal_kernel(long long* const* peers, int world, int rank, int slot, long long seq)
+{
+  if ((int)threadIdx.x < world) {
+    __threadfence_system();
+    long long* dst = peers[threadIdx.x] + ((size_t)slot * world + rank) * PF_XMAIL_WORDS;
+    *reinterpret_cast<volatile long long*>(dst + PF_XMAIL_WORDS - 1) = seq;
   }
 }
 

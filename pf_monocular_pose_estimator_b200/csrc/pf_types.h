@@ -66,6 +66,8 @@ struct pf_cta_agg {
 };
 
 #define PF_INLINE_BLOBS 32
+#define PF_XMAIL_RING 4
+#define PF_XMAIL_WORDS 32   /* message: up to 31 payload words + the sequence number in the last word */
 
 // grid mode: heavy steps of the current resampling, filled by the whole grid (pf_grid_fill).
 // ent = (first source of the step, first slot, number of slots, 0)
@@ -137,4 +139,8 @@ struct pf_kparams {
   long long rank_excl[3], rank_total[3];   // mode 4: (sum, max, min) aggregate of the lower ranks / of all ranks
   long long* shard_partial;       // [8] per-stage results of this shard (device)
   pf_cta_agg* warp_agg_g;         // [grid][PF_MAX_WARPS] per-warp prefix aggregates of the last score pass
+  // peer mailboxes (optional): the stage kernel itself delivers its partial to every rank, NVLink peer stores
+  long long* const* xmail_peers;  // [xworld] base of every rank's mailbox: [PF_XMAIL_RING][xworld][PF_XMAIL_WORDS] int64
+  int xworld, xrank, xslot;
+  long long xseq;                 // sequence number of this exchange (word 7 of the message, written last)
 };

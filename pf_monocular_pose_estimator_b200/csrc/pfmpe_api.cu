@@ -102,6 +102,11 @@ struct pfmpe_handle {
   int goff = 0, n_global = 0;
   pf_cta_agg* warp_agg_g = nullptr;
   long long* shard_partial = nullptr;   // default target of the per-stage partial results
+  long long* xmail = nullptr;           // this rank's mailbox [PF_XMAIL_RING][world][PF_XMAIL_WORDS]
+  long long** xmail_peers_dev = nullptr;
+  long long* h_xtable = nullptr;        // pinned: [world][PF_XMAIL_WORDS] + sequence word
+  int xworld = 0, xrank = 0;
+  long long xseq = 0;
   float4** peers_dev = nullptr;         // [peer_world] next-frame particle planes of every rank (peer memory)
   int peer_world = 0;
   std::vector<void*> ipc_opened;
@@ -152,6 +157,8 @@ void free_all(pfmpe_handle* h)
   cudaFree(h->idx); cudaFree(h->gather_idx); cudaFree(h->cta_agg); cudaFree(h->accum);
   cudaFree(h->inbox); cudaFree(h->state); cudaFree(h->result); cudaFree(h->obj_f); cudaFree(h->obj_d);
   for (void* q : h->ipc_opened) cudaIpcCloseMemHandle(q);
+  cudaFree(h->xmail); cudaFree(h->xmail_peers_dev);
+  if (h->h_xtable) cudaFreeHost(h->h_xtable);
   cudaFree(h->peers_dev); cudaFree(h->mc_part); cudaFree(h->mc_mean); cudaFree(h->roi_keys); cudaFree(h->roi_out);
   if (h->h_roi) cudaFreeHost(h->h_roi);
   cudaFree(h->rng_tab); cudaFree(h->timeline); cudaFree(h->warp_agg_g); cudaFree(h->shard_partial); cudaFree(h->gfill);
@@ -226,6 +233,7 @@ struct ShardArgs {
   long long S_fx = 0;
   long long excl[3] = {0, 0, 0}, total[3] = {0, 0, 0};
   long long* partial = nullptr;
+  bool publish = false;        // mode 5: send the winner record to every rank's mailbox
 };
 
 // K7: weighted mean pose + covariance of trackers [t0, t0+nt) from the kept iteration's particles and
@@ -281,6 +289,11 @@ int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_f
     p.pass_it = sa->pass_it; p.iters_total = sa->iters_total; p.q_local = sa->q_local; p.S_fx = sa->S_fx;
     for (int i = 0; i < 3; ++i) { p.rank_excl[i] = sa->excl[i]; p.rank_total[i] = sa->total[i]; }
     if (sa->partial) p.shard_partial = sa->partial;
+    if (h->xmail_peers_dev && (mode == 3 || mode == 4 || (mode == 5 && sa->publish))) {   // deliver the partial to every rank's mailbox
+      h->xseq += 1;
+      p.xmail_peers = h->xmail_peers_dev; p.xworld = h->xworld; p.xrank = h->xrank;
+      p.xseq = h->xseq; p.xslot = (int)(h->xseq % PF_XMAIL_RING);
+    }
     if (mode == 5) grid_mode = false;     // the winner record is one warp of work
   }
   if (mode == 1 || mode == 2) {
@@ -1206,7 +1219,7 @@ int pfmpe_shard_configure(pfmpe_handle* h, int64_t global_offset, int64_t n_glob
   PF_CUDA(h, dev_alloc(&h->idx, (size_t)n_global));
   PF_CUDA(h, cudaMemset(h->idx, 0, (size_t)n_global * sizeof(int)));
   if (!h->warp_agg_g) PF_CUDA(h, dev_alloc(&h->warp_agg_g, (size_t)PF_MAX_GRID * PF_MAX_WARPS));
-  if (!h->shard_partial) PF_CUDA(h, dev_alloc(&h->shard_partial, 8));
+  if (!h->shard_partial) PF_CUDA(h, dev_alloc(&h->shard_partial, PF_XMAIL_WORDS));
   h->sharded = true;
   h->goff = (int)global_offset;
   h->n_global = (int)n_global;
@@ -1378,6 +1391,113 @@ int pfmpe_shard_scatter(pfmpe_handle* h, int64_t first_owned_slot, int64_t count
   PF_CUDA(h, cudaGetLastError());
   h->launches += 1;
   return PFMPE_OK;
+}
+
+// ---- peer mailboxes: the 64-byte partials travel by NVLink peer stores from inside the stage kernels ----
+int pfmpe_shard_mail_create(pfmpe_handle* h, int world, int rank, void** d_ptr, unsigned char ipc_handle[64])
+{
+  if (!h || world < 1 || world > 32 || rank < 0 || rank >= world || !d_ptr) return PFMPE_ERR_INVALID;
+  if (!h->sharded) return fail(h, PFMPE_ERR_STATE, "pfmpe_shard_configure must be called first");
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  if (!h->xmail) {
+    const size_t n = (size_t)PF_XMAIL_RING * world * PF_XMAIL_WORDS;
+    PF_CUDA(h, dev_alloc(&h->xmail, n));
+    PF_CUDA(h, cudaMemset(h->xmail, 0, n * sizeof(long long)));
+    const size_t hb = ((size_t)world * PF_XMAIL_WORDS + 1) * sizeof(long long);
+    PF_CUDA(h, cudaMallocHost((void**)&h->h_xtable, hb));
+    std::memset(h->h_xtable, 0, hb);
+  }
+  h->xworld = world; h->xrank = rank;
+  *d_ptr = h->xmail;
+  if (ipc_handle) {
+    cudaIpcMemHandle_t m;
+    PF_CUDA(h, cudaIpcGetMemHandle(&m, h->xmail));
+    std::memcpy(ipc_handle, &m, 64);
+  }
+  return PFMPE_OK;
+}
+
+int pfmpe_shard_mail_set_peers(pfmpe_handle* h, void* const* d_ptrs)
+{
+  if (!h || !d_ptrs) return PFMPE_ERR_INVALID;
+  if (!h->xmail) return fail(h, PFMPE_ERR_STATE, "pfmpe_shard_mail_create must be called first");
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  cudaFree(h->xmail_peers_dev); h->xmail_peers_dev = nullptr;
+  PF_CUDA(h, cudaMalloc((void**)&h->xmail_peers_dev, sizeof(void*) * (size_t)h->xworld));
+  PF_CUDA(h, cudaMemcpy(h->xmail_peers_dev, d_ptrs, sizeof(void*) * (size_t)h->xworld, cudaMemcpyHostToDevice));
+  h->xseq = 0;
+  return PFMPE_OK;
+}
+
+static int mail_ready(pfmpe_handle* h)
+{
+  if (!h->xmail_peers_dev) return fail(h, PFMPE_ERR_STATE, "pfmpe_shard_mail_set_peers must be called first");
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  return PFMPE_OK;
+}
+
+int pfmpe_shard_advance(pfmpe_handle* h)
+{
+  if (!h) return PFMPE_ERR_INVALID;
+  int rc = mail_ready(h);
+  if (rc) return rc;
+  h->xseq += 1;
+  return PFMPE_OK;
+}
+
+int pfmpe_shard_collect(pfmpe_handle* h, int only_rank, int64_t* table /* [world][PF_XMAIL_WORDS] */)
+{
+  if (!h || !table) return PFMPE_ERR_INVALID;
+  int rc = mail_ready(h);
+  if (rc) return rc;
+  if (h->xseq == 0 || only_rank >= h->xworld) return fail(h, PFMPE_ERR_STATE, "no exchange is in flight");
+  const int W = h->xworld;
+  volatile long long* flag = h->h_xtable + (size_t)W * PF_XMAIL_WORDS;
+  *flag = 0;
+  pf_shard_wait_kernel<<<1, 32, 0, h->stream>>>(h->xmail, (int)(h->xseq % PF_XMAIL_RING), W, only_rank, h->xseq, h->h_xtable);
+  PF_CUDA(h, cudaGetLastError());
+  h->launches += 1;
+  for (unsigned spin = 1;; ++spin) {
+    const long long v = *flag;
+    if (v == h->xseq) break;
+    if (v == -1) return fail(h, PFMPE_ERR_COMM, "a peer's message did not arrive (timeout)");
+    if ((spin & 0x3fffu) == 0) {
+      const cudaError_t q = cudaStreamQuery(h->stream);
+      if (q != cudaSuccess && q != cudaErrorNotReady) { h->err = std::string("exchange: ") + cudaGetErrorString(q); return PFMPE_ERR_CUDA; }
+    }
+  }
+  std::atomic_thread_fence(std::memory_order_acquire);
+  for (int i = 0; i < W * PF_XMAIL_WORDS; ++i) table[i] = h->h_xtable[i];
+  return PFMPE_OK;
+}
+
+int pfmpe_shard_barrier(pfmpe_handle* h)
+{
+  if (!h) return PFMPE_ERR_INVALID;
+  int rc = mail_ready(h);
+  if (rc) return rc;
+  h->xseq += 1;
+  const int slot = (int)(h->xseq % PF_XMAIL_RING);
+  pf_shard_signal_kernel<<<1, 32, 0, h->stream>>>(h->xmail_peers_dev, h->xworld, h->xrank, slot, h->xseq);
+  pf_shard_wait_kernel<<<1, 32, 0, h->stream>>>(h->xmail, slot, h->xworld, -1, h->xseq, nullptr);
+  PF_CUDA(h, cudaGetLastError());
+  h->launches += 2;
+  return PFMPE_OK;
+}
+
+int pfmpe_shard_winner_publish(pfmpe_handle* h, int local_index)
+{
+  if (!h || local_index < 0 || local_index >= h->cfg.n_particles) return PFMPE_ERR_INVALID;
+  int rc = shard_ready(h);
+  if (rc) return rc;
+  rc = mail_ready(h);
+  if (rc) return rc;
+  ShardArgs sa;
+  sa.q_local = local_index;
+  sa.S_fx = 1;
+  sa.publish = true;
+  return launch_frames(h, 5, 0, 1, 0, 1, &sa);
 }
 
 int pfmpe_shard_winner(pfmpe_handle* h, int local_index, pfmpe_frame_out* out)

@@ -131,9 +131,15 @@ class Loopback:
     def all_ok(self, ok, dev):
         return bool(ok)
 
+    def device_barrier(self, shards):
+        pass                                                 # one stream: already ordered
+
     def peer_pointers(self, shards, dev):
         """Bases of every shard's next-frame particle planes (same process: plain device pointers)."""
         return [h.shard_local_ptr() for h in shards]
+
+    def mail_pointers(self, shards, dev):
+        return [h.shard_mail_create(self.world, r)[0] for r, h in enumerate(shards)]
 
 
 class TorchDist:
@@ -165,6 +171,9 @@ class TorchDist:
             self._one = torch.zeros(1, dtype=torch.int32, device=dev)
         self.dist.all_reduce(self._one, group=self.group)
 
+    def device_barrier(self, shards):
+        shards[0].shard_barrier()                            # signal + wait kernels through the peer mailboxes
+
     def all_ok(self, ok, dev):
         import torch
         t = torch.tensor([1 if ok else 0], dtype=torch.int32, device=dev)
@@ -180,6 +189,15 @@ class TorchDist:
         allh = allh.cpu().numpy()
         return [shards[0].shard_local_ptr() if q == self.rank else shards[0].shard_ipc_open(allh[q].tobytes())
                 for q in range(self.world)]
+
+    def mail_pointers(self, shards, dev):
+        import torch
+        ptr, handle = shards[0].shard_mail_create(self.world, self.rank)
+        mine = torch.tensor(list(handle), dtype=torch.uint8, device=dev)
+        allh = torch.empty((self.world, 64), dtype=torch.uint8, device=dev)
+        self.dist.all_gather_into_tensor(allh, mine.reshape(1, 64), group=self.group)
+        allh = allh.cpu().numpy()
+        return [ptr if q == self.rank else shards[0].shard_ipc_open(allh[q].tobytes()) for q in range(self.world)]
 
     def bcast(self, arr, owner):
         import torch
@@ -198,7 +216,7 @@ class ShardedFilter:
 
     n_global must be a multiple of comm.world.  With `Loopback` all shards are handles on `device`."""
 
-    def __init__(self, n_global, comm, n_leds=5, max_blobs=32, device=0, rebalance="auto", **kw):
+    def __init__(self, n_global, comm, n_leds=5, max_blobs=32, device=0, rebalance="auto", mail=True, **kw):
         import torch
         if n_global % comm.world:
             raise ValueError("n_global must be a multiple of the number of shards")
@@ -213,7 +231,7 @@ class ShardedFilter:
             h.shard_configure(r * self.n_loc, n_global)
             h.set_stream(torch.cuda.current_stream(self.dev).cuda_stream)
             self.shards.append(h)
-        self.partials = torch.zeros((len(self.shards), 8), dtype=torch.int64, device=self.dev)
+        self.partials = torch.zeros((len(self.shards), 32), dtype=torch.int64, device=self.dev)
         self._bufs = {}
         # rebalance of the resampled set: "p2p" = one scatter kernel with NVLink peer stores (CUDA IPC),
         # "exchange" = row export + all_to_all + import; "auto" tries p2p and falls back for every rank
@@ -230,6 +248,21 @@ class ShardedFilter:
                 self.rebalance = "p2p"
             elif rebalance == "p2p":
                 raise RuntimeError("peer-memory rebalance unavailable: %s" % (self.p2p_error or "a peer rank failed"))
+        # exchange of the 64-byte partials: "mail" = peer stores from inside the stage kernels + a wait
+        # kernel that hands the table to the host through pinned memory (needs peer access, like p2p);
+        # otherwise all_gather + device->host copy
+        self.partial_exchange = "all_gather"
+        if self.rebalance == "p2p" and mail and self.W <= 32:
+            ok = True
+            try:
+                ptrs = comm.mail_pointers(self.shards, self.dev)
+                for h in self.shards:
+                    h.shard_mail_set_peers(ptrs)
+            except capi.PfmpeError as e:
+                ok, self.p2p_error = False, str(e)
+            if comm.all_ok(ok, self.dev):
+                self.partial_exchange = "mail"
+                comm.barrier(self.dev)                       # every mailbox is installed before the first message
         self.passes = 0          # score passes launched so far (per shard)
         self.last = None
         self.stage_s = None      # set to {} to collect per-stage wall times (synchronises after every stage)
@@ -274,13 +307,19 @@ class ShardedFilter:
             h.track_init(pose0, t0, pose1, t1)
 
     # -- stages -------------------------------------------------------------------------
+    def _gather(self):
+        """Partials of the stage just launched on every rank -> (world, 8) int64 on the host."""
+        if self.partial_exchange == "mail":
+            return self.shards[0].shard_collect(self.W)[:, :8]
+        return self.comm.gather(self.partials)[:, :8]
+
     def _score(self, it):
         t = self._mark("other", self._t)
         for i, h in enumerate(self.shards):
             h.shard_score(it, self.partials[i].data_ptr())
         self.passes += 1
         t = self._mark("score", t)
-        r = reduce_pass(self.comm.gather(self.partials))
+        r = reduce_pass(self._gather())
         self._t = self._mark("gather", t)
         return r
 
@@ -326,18 +365,26 @@ class ShardedFilter:
             for i, r_ in enumerate(self.comm.local):
                 self.shards[i].shard_resample(S, iters, lower[r_], total, self.partials[i].data_ptr())
             t = self._mark("resample", t)
-            part = self.comm.gather(self.partials)
+            part = self._gather()
             t = self._mark("gather", t)
             cntkey = int(np.ascontiguousarray(part[:, 0]).view(np.uint64).max())
             q = (~cntkey) & 0xFFFFFFFF                        # :686 first max of counterMeas
             max_count = cntkey >> 32
-            first, end = part[:, 1], part[:, 2]
+            first = part[:, 1]
+            # a rank's slots end where the next rank's begin (its sources own nothing beyond); the last one ends at N
+            end = np.concatenate([first[1:], [self.N]])
+            if self.partial_exchange != "mail":
+                assert (end == part[:, 2]).all(), (first, part[:, 2])
             check_tiling(first, end, self.N)
             send = slot_partition(first, end, self.n_loc, self.W)
             if self.rebalance == "p2p":
                 for i, r_ in enumerate(self.comm.local):
                     self.shards[i].shard_scatter(int(first[r_]), int(end[r_] - first[r_]))
-                self.comm.barrier(self.dev)                  # all scatters land before anyone's next score pass
+                # all scatters land before anyone's next score pass: a barrier on the ranks' streams
+                if self.partial_exchange == "mail":
+                    self.comm.device_barrier(self.shards)
+                else:
+                    self.comm.barrier(self.dev)
                 self._t = self._mark("scatter", t)
             else:
                 self._rebalance_exchange(send, first, end, t)
@@ -377,13 +424,28 @@ class ShardedFilter:
         # ---- winner pose + correspondences from its owner
         owner = q // self.n_loc
         packed = np.zeros(16 + 1 + 2 * capi.MAX_LED)
-        if owner in self.comm.local:
-            w = self.shards[self.comm.local.index(owner)].shard_winner(q - owner * self.n_loc)
-            packed[:16] = capi.colmajor(w["winner_pose"])
-            c = w["correspondences"].reshape(-1)
-            packed[16] = c.size // 2
-            packed[17:17 + c.size] = c
-        packed = self.comm.bcast(packed, owner)
+        if self.partial_exchange == "mail":
+            # the owner's kernel sends pose + correspondences to every rank's mailbox (peer stores)
+            for i, r_ in enumerate(self.comm.local):
+                if r_ == owner:
+                    self.shards[i].shard_winner_publish(q - owner * self.n_loc)
+                else:
+                    self.shards[i].shard_advance()
+            row = np.ascontiguousarray(self.shards[0].shard_collect(self.W, only_rank=owner)[owner])
+            pose = np.eye(4)
+            pose[:3, :] = row[:6].view(np.float32).astype(np.float64).reshape(3, 4)
+            nc = int(row[6 + capi.MAX_LED])
+            packed[:16] = capi.colmajor(pose)
+            packed[16] = nc
+            packed[17:17 + 2 * nc] = row[6:6 + capi.MAX_LED].view(np.uint32)[:2 * nc]
+        else:
+            if owner in self.comm.local:
+                w = self.shards[self.comm.local.index(owner)].shard_winner(q - owner * self.n_loc)
+                packed[:16] = capi.colmajor(w["winner_pose"])
+                c = w["correspondences"].reshape(-1)
+                packed[16] = c.size // 2
+                packed[17:17 + c.size] = c
+            packed = self.comm.bcast(packed, owner)
         self._t = self._mark("winner", self._t)
         nc = int(packed[16])
         out = dict(status=1 if accept else 4, iterations=iters, best_iteration=best_it, resampled=int(resampled),

@@ -37,11 +37,13 @@ def _same_frame(a, b, ha, hb):
 
 
 @pytest.mark.parametrize("N,W,kw", [(4096, 8, {}), (8192, 4, dict(rebalance="exchange")), (6144, 2, dict(force_mode=2, grid_cap=3)),
-                                    (200000, 2, {}), (200000, 2, dict(rebalance="exchange")), (40960, 5, {})])
+                                    (200000, 2, {}), (200000, 2, dict(rebalance="exchange")), (40960, 5, {}),
+                                    (8192, 4, dict(mail=False))])
 def test_logical_shards_match_unsharded_filter(N, W, kw):
     fi = frame_inputs(N, frame=7)
     ref = make_handle(fi, N)
     sh = _make_sharded(fi, N, W, **kw)
+    assert sh.partial_exchange == ("mail" if kw.get("mail", True) and kw.get("rebalance") != "exchange" else "all_gather")
     ref.set_particles(fi["E"])
     sh.set_particles(fi["E"])
     args = (fi["img"], fi["T_cur"], fi["T_pred"], fi["P"], fi["Cm"], fi["isi"], fi["dt"])
