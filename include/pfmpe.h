@@ -215,6 +215,40 @@ int pfmpe_track_results(pfmpe_handle* h, int tracker, int first_frame, int n_fra
 int pfmpe_predict_roi(pfmpe_handle* h, int tracker, const double cam_move_inv[16], const double prediction_matrix[16],
                       const double predicted_pose[16], double roi[4]);
 
+/* ---- correspondence vote of the brute-force (re-)initialisation --------------------
+ * The histogram loop of PoseEstimator::initialise (pose_estimator.cpp:1524-1717): Kneip's P3P
+ * (P3P::computePoses / solveQuartic, p3p.cpp:65-292) for every triple of detections x every ordered
+ * triple of LEDs, back-projection of the LEDs that were not used through each finite solution
+ * (project2d :1017-1034, calculateMinDistancesAndPairs :2093-2137) and the votes of :1692-1712, with the
+ * pre-filters of :1556-1581 and calculateImageVectors (:1072-1085) for the bearing vectors.  FP64 on the
+ * device, like the reference.  image_points: n x 2 undistorted pixels (3 <= n <= 1024); markers, K and
+ * back_projection_pixel_tolerance are the handle's.  hist: n x n_leds, row-major = hist_corr(detection, LED);
+ * the caller feeds it to correspondencesFromHistogram (:1134-1288) / checkCorrespondences (:1312-1501)
+ * unchanged.  Counts are integers: identical to the reference except where a vote sits within rounding of
+ * the tolerance or a conjugate root pair collapses within rounding. */
+typedef struct {
+  uint64_t triples;             /* detection triples that pass the pre-filters (:1561-1581)            */
+  uint64_t p3p_solved;          /* computePoses calls that returned 0                                  */
+  uint64_t solutions_projected; /* finite solutions not dropped by the duplicate test (:1659-1670)     */
+  uint64_t solutions_voted;     /* solutions with at least one detection inside the tolerance (:1692)  */
+  float device_ms;              /* device time of the vote (CUDA events on the handle's stream)        */
+  int32_t reserved;
+} pfmpe_p3p_stats;
+int pfmpe_p3p_histogram(pfmpe_handle* h, int tracker, const double* image_points, int32_t n_image_points,
+                        uint32_t* hist, pfmpe_p3p_stats* stats);
+/* The same with image_points already resident in device memory (no host->device copy of the detections;
+ * hist still comes back to the host: it is the result). */
+int pfmpe_p3p_histogram_dev(pfmpe_handle* h, int tracker, const double* d_image_points, int32_t n_image_points,
+                            uint32_t* hist, pfmpe_p3p_stats* stats);
+
+/* Batched P3P::computePoses (p3p.cpp:65-236), one problem per device thread -- what checkCorrespondences
+ * (:1382) and P3P_short (:2506-) call per correspondence triple.  feature_vectors, world_points: n x 9,
+ * each a column-major 3x3 (columns = the three unit bearing vectors / world points, Eigen::Matrix3d
+ * layout); solutions: n x 4 x 12, each a column-major 3x4 [R | C]; rc: n, 0 or -1 (colinear world points,
+ * solutions untouched). */
+int pfmpe_p3p_solve(pfmpe_handle* h, int32_t n, const double* feature_vectors, const double* world_points,
+                    double* solutions, int32_t* rc);
+
 /* ---- one filter sharded over several GPUs (BASELINE configs[4]) ----------------------
  * One handle per rank owns the contiguous global particles [global_offset, global_offset +
  * n_particles) of ONE filter of n_global particles (n_trackers must be 1).  The reference loop

@@ -18,7 +18,7 @@ MAX_LED = 8
 
 def build(force=False):
     """Compile the oracle (gcc) if missing or stale."""
-    src = [os.path.join(_HERE, f) for f in ("pf_oracle.c", "pf_oracle.h", "Makefile")]
+    src = [os.path.join(_HERE, f) for f in ("pf_oracle.c", "pf_oracle.h", "p3p_oracle.cpp", "Makefile")]
     stale = (not os.path.exists(_LIB_PATH)) or any(
         os.path.getmtime(s) > os.path.getmtime(_LIB_PATH) for s in src)
     if stale or force:
@@ -103,6 +103,15 @@ def lib():
         L.orc_distort_point.argtypes = [_dp, _dp, _dp, _dp]
         L.orc_predict_roi.argtypes = [C.c_int, _dp, _dp, _dp, _dp, _dp, C.c_int, _dp, _dp]
         L.orc_mat4_inv.argtypes = [_dp, _dp]
+        L.orc_p3p_solve_quartic.argtypes = [_dp, _dp]
+        L.orc_p3p_compute_poses.restype = C.c_int
+        L.orc_p3p_compute_poses.argtypes = [_dp, _dp, _dp]
+        L.orc_image_vectors.argtypes = [_dp, C.c_int, _dp, _dp]
+        L.orc_p3p_histogram.restype = C.c_int
+        L.orc_p3p_histogram.argtypes = [_dp, C.c_int, _dp, C.c_int, _dp, C.c_double, _up, C.POINTER(C.c_uint64)]
+        L.orc_p3p_histogram_mode.restype = C.c_int
+        L.orc_p3p_histogram_mode.argtypes = [_dp, C.c_int, _dp, C.c_int, _dp, C.c_double, C.c_int, _up,
+                                             C.POINTER(C.c_uint64)]
         _lib = L
     return _lib
 
@@ -269,6 +278,42 @@ def predict_roi(E, Cm, P, pred, markers, K):
     lib().orc_predict_roi(e.shape[0], _d(e), _d(colmajor(Cm)), _d(colmajor(P)), _d(colmajor(pred)), _d(m), m.shape[0],
                           _d(_c64(K).reshape(9)), _d(out))
     return out
+
+
+def p3p_solve_quartic(factors):
+    """P3P::solveQuartic (p3p.cpp:238-292): real parts of the four roots."""
+    f = _c64(factors).reshape(5); r = np.zeros(4)
+    lib().orc_p3p_solve_quartic(_d(f), _d(r))
+    return r
+
+
+def p3p_compute_poses(feature_vectors, world_points):
+    """P3P::computePoses (p3p.cpp:65-236).  feature_vectors / world_points: (3, 3) arrays whose COLUMNS are the
+    three unit bearing vectors / world points.  Returns (rc, solutions (4, 3, 4) = [R | C])."""
+    fv = np.ascontiguousarray(np.asarray(feature_vectors, dtype=np.float64).T).reshape(9)   # column-major
+    wp = np.ascontiguousarray(np.asarray(world_points, dtype=np.float64).T).reshape(9)
+    sol = np.zeros(48)
+    rc = lib().orc_p3p_compute_poses(_d(fv), _d(wp), _d(sol))
+    return rc, sol.reshape(4, 4, 3).transpose(0, 2, 1).copy()
+
+
+def image_vectors(K, img):
+    """calculateImageVectors (pose_estimator.cpp:1072-1085): (D, 3) unit bearing vectors."""
+    im = _c64(img).reshape(-1, 2); out = np.zeros((im.shape[0], 3))
+    lib().orc_image_vectors(_d(_c64(K).reshape(9)), im.shape[0], _d(im), _d(out))
+    return out
+
+
+def p3p_histogram(K, markers, img, tol, dup_mode=0):
+    """hist_corr of PoseEstimator::initialise (pose_estimator.cpp:1524-1717): (D, L) uint32 votes and the counters
+    (triples, p3p_solved, solutions_projected, solutions_voted).  dup_mode: 0 the reference's duplicate-solution
+    rule (:1659-1663), 1 never drop (upper bracket), 2 drop every near-duplicate (lower bracket)."""
+    im = _c64(img).reshape(-1, 2); ob = obj_h(np.asarray(markers)[:, :3])
+    D, L = im.shape[0], ob.shape[0]
+    hist = np.zeros((D, L), dtype=np.uint32); st = (C.c_uint64 * 4)()
+    lib().orc_p3p_histogram_mode(_d(_c64(K).reshape(9)), L, _d(ob), D, _d(im), float(tol), int(dup_mode),
+                                 hist.ctypes.data_as(_up), st)
+    return hist, tuple(int(x) for x in st)
 
 
 def weighted_mean_cov(T, w):

@@ -25,7 +25,7 @@ EXPORTS = [
     "pfmpe_optimise_pose", "pfmpe_predict_pose", "pfmpe_exponential_map", "pfmpe_logarithm_map",
     "pfmpe_track_init", "pfmpe_track_upload", "pfmpe_track_attach", "pfmpe_track_run", "pfmpe_track_replay", "pfmpe_track_results",
     "pfmpe_track_frame_host", "pfmpe_track_frame_host_batch", "pfmpe_track_sequence_host",
-    "pfmpe_predict_roi",
+    "pfmpe_predict_roi", "pfmpe_p3p_histogram", "pfmpe_p3p_histogram_dev", "pfmpe_p3p_solve",
     "pfmpe_shard_configure", "pfmpe_shard_begin_frame", "pfmpe_shard_score", "pfmpe_shard_resample",
     "pfmpe_shard_export", "pfmpe_shard_keep", "pfmpe_shard_import", "pfmpe_shard_winner",
     "pfmpe_shard_mail_create", "pfmpe_shard_mail_set_peers", "pfmpe_shard_collect", "pfmpe_shard_advance",
@@ -70,6 +70,11 @@ class FrameOut(C.Structure):
                 ("max_count", C.c_uint32), ("n_correspondences", C.c_int32),
                 ("correspondences", C.c_uint32 * (2 * MAX_LED)),
                 ("winner_pose", C.c_double * 16), ("mean_pose", C.c_double * 16), ("mean_cov", C.c_double * 36)]
+
+
+class P3pStats(C.Structure):
+    _fields_ = [("triples", C.c_uint64), ("p3p_solved", C.c_uint64), ("solutions_projected", C.c_uint64),
+                ("solutions_voted", C.c_uint64), ("device_ms", C.c_float), ("reserved", C.c_int32)]
 
 
 class TrackResult(C.Structure):
@@ -125,6 +130,10 @@ def lib():
         L.pfmpe_track_sequence_host.argtypes = [C.c_void_p, C.c_int, _dp, _dp, C.POINTER(C.c_int32), C.POINTER(C.c_uint32),
                                                 C.POINTER(TrackResult), _dp]
         L.pfmpe_predict_roi.argtypes = [C.c_void_p, C.c_int, _dp, _dp, _dp, _dp]
+        L.pfmpe_p3p_histogram.argtypes = [C.c_void_p, C.c_int, _dp, C.c_int32, C.POINTER(C.c_uint32), C.POINTER(P3pStats)]
+        L.pfmpe_p3p_histogram_dev.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int32, C.POINTER(C.c_uint32),
+                                              C.POINTER(P3pStats)]
+        L.pfmpe_p3p_solve.argtypes = [C.c_void_p, C.c_int32, _dp, _dp, _dp, C.POINTER(C.c_int32)]
         _i3 = C.POINTER(C.c_int64)
         L.pfmpe_shard_configure.argtypes = [C.c_void_p, C.c_int64, C.c_int64]
         L.pfmpe_shard_begin_frame.argtypes = [C.c_void_p, C.POINTER(FrameIn)]
@@ -348,6 +357,33 @@ class Handle:
         out = np.zeros(4)
         self._chk(lib().pfmpe_predict_roi(self._h, tracker, _d(colmajor(Cm)), _d(colmajor(P)), _d(colmajor(pred)), _d(out)))
         return out
+
+    def p3p_histogram(self, image_points, tracker=0, d_image_points=None):
+        """hist_corr of PoseEstimator::initialise (pose_estimator.cpp:1524-1717): (D, L) uint32 votes + counters.
+        d_image_points: device pointer (int) of D x 2 doubles already resident in HBM; image_points then only
+        gives the shape."""
+        im = _c64(image_points).reshape(-1, 2)
+        D, L = im.shape[0], self.L
+        hist = np.zeros((D, L), dtype=np.uint32)
+        st = P3pStats()
+        hp = hist.ctypes.data_as(C.POINTER(C.c_uint32))
+        if d_image_points is None:
+            self._chk(lib().pfmpe_p3p_histogram(self._h, tracker, _d(im), D, hp, C.byref(st)))
+        else:
+            self._chk(lib().pfmpe_p3p_histogram_dev(self._h, tracker, C.c_void_p(int(d_image_points)), D, hp, C.byref(st)))
+        return hist, dict(triples=int(st.triples), p3p_solved=int(st.p3p_solved),
+                          solutions_projected=int(st.solutions_projected), solutions_voted=int(st.solutions_voted),
+                          device_ms=float(st.device_ms))
+
+    def p3p_solve(self, feature_vectors, world_points):
+        """Batched P3P::computePoses (p3p.cpp:65-236).  feature_vectors, world_points: (n, 3, 3) with the three
+        vectors / points as COLUMNS.  Returns rc (n,) and solutions (n, 4, 3, 4) = [R | C]."""
+        fv = np.ascontiguousarray(np.asarray(feature_vectors, dtype=np.float64).transpose(0, 2, 1)).reshape(-1, 9)
+        wp = np.ascontiguousarray(np.asarray(world_points, dtype=np.float64).transpose(0, 2, 1)).reshape(-1, 9)
+        n = fv.shape[0]
+        sol = np.zeros((n, 48)); rc = np.zeros(n, dtype=np.int32)
+        self._chk(lib().pfmpe_p3p_solve(self._h, n, _d(fv), _d(wp), _d(sol), rc.ctypes.data_as(C.POINTER(C.c_int32))))
+        return rc, sol.reshape(n, 4, 4, 3).transpose(0, 1, 3, 2).copy()
 
     # ---- one filter sharded over several handles / GPUs (device pointers are plain ints) ----
     def shard_configure(self, global_offset, n_global):

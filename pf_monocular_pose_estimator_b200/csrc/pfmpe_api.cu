@@ -17,6 +17,7 @@
 #include "pf_kernels.cuh"
 #include "pf_meancov.cuh"
 #include "pf_roi.cuh"
+#include "pf_p3p.cuh"
 
 namespace {
 
@@ -75,6 +76,10 @@ struct pfmpe_handle {
   unsigned* roi_keys = nullptr;   // K8: [tracker][4] ordered-float keys, then the floats
   float* roi_out = nullptr;
   float* h_roi = nullptr;
+  unsigned char* p3p_buf = nullptr;     // K9 scratch: detections, sorted copy, bearing vectors, counters, histogram
+  size_t p3p_bytes = 0;
+  double* p3p_io = nullptr;             // batched solver scratch
+  size_t p3p_io_bytes = 0;
   double *mc_part = nullptr, *mc_mean = nullptr;   // K7 (PFMPE_FLAG_MEAN_COV): per-block partials, mean poses
   int mc_blocks = 0;
   int gfill_cap = 0;
@@ -161,6 +166,7 @@ void free_all(pfmpe_handle* h)
   if (h->h_xtable) cudaFreeHost(h->h_xtable);
   cudaFree(h->peers_dev); cudaFree(h->mc_part); cudaFree(h->mc_mean); cudaFree(h->roi_keys); cudaFree(h->roi_out);
   if (h->h_roi) cudaFreeHost(h->h_roi);
+  cudaFree(h->p3p_buf); cudaFree(h->p3p_io);
   cudaFree(h->rng_tab); cudaFree(h->timeline); cudaFree(h->warp_agg_g); cudaFree(h->shard_partial); cudaFree(h->gfill);
   if (h->seq.owned) { cudaFree(h->seq.blobs); cudaFree(h->seq.counts); cudaFree(h->seq.times); cudaFree(h->seq.seeds); }
   cudaFree(h->seq.result); cudaFree(h->seq.fc_log);
@@ -1198,6 +1204,104 @@ int pfmpe_predict_roi(pfmpe_handle* h, int tracker, const double cam_move_inv[16
                              cudaMemcpyDeviceToHost, h->stream));
   PF_CUDA(h, cudaStreamSynchronize(h->stream));
   for (int i = 0; i < 4; ++i) roi[i] = (double)h->h_roi[4 * (size_t)tracker + i];
+  return PFMPE_OK;
+}
+
+// ---- K9: correspondence vote of initialise() ----------------------------------
+namespace {
+int p3p_histogram_impl(pfmpe_handle* h, int tracker, const double* image_points, bool on_device, int32_t D,
+                       uint32_t* hist, pfmpe_p3p_stats* stats)
+{
+  if (!h || !image_points || !hist) return PFMPE_ERR_INVALID;
+  if (tracker < 0 || tracker >= h->cfg.n_trackers) return fail(h, PFMPE_ERR_INVALID, "tracker out of range");
+  int rc = check_ready(h);
+  if (rc) return rc;
+  const int L = h->cfg.n_leds;
+  if (L < 3) return fail(h, PFMPE_ERR_UNSUPPORTED, "P3P needs at least 3 LEDs");
+  if (D < 3 || D > PF_P3P_MAX_D) return fail(h, PFMPE_ERR_INVALID, "n_image_points must be 3..1024");
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  // scratch layout: img 2D | simg 2D | vec 3D | stats 4 (all 8-byte) | hist D*L u32 | sidx D i32
+  const size_t need = (size_t)D * 7 * 8 + 32 + (size_t)D * L * 4 + (size_t)D * 4;
+  if (need > h->p3p_bytes) {
+    PF_CUDA(h, cudaStreamSynchronize(h->stream));
+    cudaFree(h->p3p_buf); h->p3p_buf = nullptr; h->p3p_bytes = 0;
+    PF_CUDA(h, cudaMalloc((void**)&h->p3p_buf, need));
+    h->p3p_bytes = need;
+  }
+  pf_p3p_params p;
+  std::memset(&p, 0, sizeof p);
+  p.D = D; p.L = L;
+  for (int i = 0; i < 9; ++i) p.K[i] = h->K[i];
+  for (int i = 0; i < 3 * L; ++i) p.obj[i] = h->markers[(size_t)tracker * PF_MAX_LED * 3 + i];
+  p.tol = h->prm.back_projection_pixel_tolerance;
+  double* base = reinterpret_cast<double*>(h->p3p_buf);
+  double* d_img = base;
+  p.simg = base + 2 * (size_t)D;
+  p.vec = base + 4 * (size_t)D;
+  p.stats = reinterpret_cast<unsigned long long*>(base + 7 * (size_t)D);
+  p.hist = reinterpret_cast<unsigned*>(base + 7 * (size_t)D + 4);
+  p.sidx = reinterpret_cast<int*>(p.hist + (size_t)D * L);
+  if (on_device) p.img = image_points;
+  else {
+    PF_CUDA(h, cudaMemcpyAsync(d_img, image_points, (size_t)D * 2 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    p.img = d_img;
+  }
+  PF_CUDA(h, cudaEventRecord(h->ev0, h->stream));
+  PF_CUDA(h, pf_p3p_launch_hist(p, h->stream));
+  PF_CUDA(h, cudaEventRecord(h->ev1, h->stream));
+  h->launches += 2;
+  h->timing_valid = false;
+  unsigned long long st[4];
+  PF_CUDA(h, cudaMemcpyAsync(hist, p.hist, (size_t)D * L * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
+  PF_CUDA(h, cudaMemcpyAsync(st, p.stats, sizeof st, cudaMemcpyDeviceToHost, h->stream));
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  if (stats) {
+    stats->triples = st[0]; stats->p3p_solved = st[1]; stats->solutions_projected = st[2]; stats->solutions_voted = st[3];
+    stats->reserved = 0;
+    PF_CUDA(h, cudaEventElapsedTime(&stats->device_ms, h->ev0, h->ev1));
+  }
+  return PFMPE_OK;
+}
+}  // namespace
+
+int pfmpe_p3p_histogram(pfmpe_handle* h, int tracker, const double* image_points, int32_t n_image_points,
+                        uint32_t* hist, pfmpe_p3p_stats* stats)
+{
+  return p3p_histogram_impl(h, tracker, image_points, false, n_image_points, hist, stats);
+}
+
+int pfmpe_p3p_histogram_dev(pfmpe_handle* h, int tracker, const double* d_image_points, int32_t n_image_points,
+                            uint32_t* hist, pfmpe_p3p_stats* stats)
+{
+  return p3p_histogram_impl(h, tracker, d_image_points, true, n_image_points, hist, stats);
+}
+
+int pfmpe_p3p_solve(pfmpe_handle* h, int32_t n, const double* feature_vectors, const double* world_points,
+                    double* solutions, int32_t* rc_out)
+{
+  if (!h || !feature_vectors || !world_points || !solutions || !rc_out) return PFMPE_ERR_INVALID;
+  if (n < 0) return fail(h, PFMPE_ERR_INVALID, "n < 0");
+  if (n == 0) return PFMPE_OK;
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  const size_t need = (size_t)n * (9 + 9 + 48) * sizeof(double) + (size_t)n * sizeof(int);
+  if (need > h->p3p_io_bytes) {
+    PF_CUDA(h, cudaStreamSynchronize(h->stream));
+    cudaFree(h->p3p_io); h->p3p_io = nullptr; h->p3p_io_bytes = 0;
+    PF_CUDA(h, cudaMalloc((void**)&h->p3p_io, need));
+    h->p3p_io_bytes = need;
+  }
+  double* d_fv = h->p3p_io;
+  double* d_wp = d_fv + 9 * (size_t)n;
+  double* d_sol = d_wp + 9 * (size_t)n;
+  int* d_rc = reinterpret_cast<int*>(d_sol + 48 * (size_t)n);
+  PF_CUDA(h, cudaMemcpyAsync(d_fv, feature_vectors, (size_t)n * 9 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  PF_CUDA(h, cudaMemcpyAsync(d_wp, world_points, (size_t)n * 9 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  PF_CUDA(h, cudaMemsetAsync(d_sol, 0, (size_t)n * 48 * sizeof(double), h->stream));
+  PF_CUDA(h, pf_p3p_launch_solve(n, d_fv, d_wp, d_sol, d_rc, h->stream));
+  h->launches += 1;
+  PF_CUDA(h, cudaMemcpyAsync(solutions, d_sol, (size_t)n * 48 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  PF_CUDA(h, cudaMemcpyAsync(rc_out, d_rc, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
   return PFMPE_OK;
 }
 
