@@ -1,6 +1,8 @@
 // pf_p3p.cu -- kernels of K9; see pf_p3p.cuh.  Built with -fmad=false.
 #include "pf_p3p.cuh"
 
+#include <cstdlib>
+
 struct pf_cxd { double re, im; };
 
 __device__ __forceinline__ pf_cxd pf_cx(double re, double im) { pf_cxd z; z.re = re; z.im = im; return z; }
@@ -52,14 +54,28 @@ __device__ __noinline__ pf_cxd pf_cx_sqrt(pf_cxd z)
 
 // std::pow(std::complex<double>, double) as libstdc++ defines it: a positive real base stays real, everything
 // else goes through polar(exp(y * log|z|), y * arg z) -- which gives a negative real base a tiny imaginary part
-__device__ __noinline__ pf_cxd pf_cx_pow(pf_cxd z, double y)
+// cube_root: y is fl(1/3); for a positive real base cbrt() stands in for pow(x, fl(1/3)) -- the two agree to
+// within an ulp (x^(fl(1/3) - 1/3) = 1 - 2e-17 ln x) and cbrt is a fraction of pow's code and time.
+__device__ __noinline__ pf_cxd pf_cx_pow(pf_cxd z, double y, bool cube_root)
 {
-  if (z.im == 0.0 && z.re > 0.0) return pf_cx(pow(z.re, y), 0.0);
+  if (z.im == 0.0 && z.re > 0.0) return pf_cx(cube_root ? cbrt(z.re) : pow(z.re, y), 0.0);
   const double lr = log(hypot(z.re, z.im)), th = atan2(z.im, z.re);
   const double rho = exp(y * lr);
   double sn, cs;
   sincos(y * th, &sn, &cs);
   return pf_cx(rho * cs, rho * sn);
+}
+
+// pow(complex(x, +0), n) for n = 2, 3 under the same rules: positive x stays real (x^n is formed by multiplication:
+// within an ulp of pow); otherwise arg = pi exactly, so the polar form is exp(n log|x|) * (cos, sin)(n * fl(pi)),
+// two constants: cos(2 fl(pi)) = 1, sin(2 fl(pi)) = -2.4492935982947064e-16, cos(3 fl(pi)) = -1,
+// sin(3 fl(pi)) = 3.6739403974420594e-16 (this is where the reference's "real" quartic gets its imaginary dust).
+__device__ __forceinline__ pf_cxd pf_cx_pow_real_int(double x, int n)
+{
+  if (x > 0.0) return pf_cx(n == 2 ? x * x : x * x * x, 0.0);
+  if (x == 0.0 && !signbit(x)) return pf_cx(0.0, 0.0);   // arg(+0 + 0i) = 0
+  const double rho = exp((double)n * log(fabs(x)));
+  return n == 2 ? pf_cx(rho * 1.0, rho * -2.4492935982947064e-16) : pf_cx(rho * -1.0, rho * 3.6739403974420594e-16);
 }
 
 // P3P::solveQuartic (p3p.cpp:238-292): Ferrari's closed form, real parts of the four roots
@@ -73,13 +89,13 @@ __device__ __noinline__ void pf_p3p_quartic(const double f[5], double roots[4])
   const double alpha2 = alpha * alpha, alpha3 = alpha2 * alpha;
   const pf_cxd P = pf_cx(-alpha2 / 12 - gamma, 0.0);
   const pf_cxd Q = pf_cx(-alpha3 / 108 + alpha * gamma / 3 - beta * beta / 8, 0.0);
-  const pf_cxd disc = pf_cx_add(pf_cx_divs(pf_cx_pow(Q, 2.0), 4.0), pf_cx_divs(pf_cx_pow(P, 3.0), 27.0));
+  const pf_cxd disc = pf_cx_add(pf_cx_divs(pf_cx_pow_real_int(Q.re, 2), 4.0), pf_cx_divs(pf_cx_pow_real_int(P.re, 3), 27.0));
   const pf_cxd R = pf_cx_add(pf_cx_divs(pf_cx_neg(Q), 2.0), pf_cx_sqrt(disc));
-  const pf_cxd U = pf_cx_pow(R, 1.0 / 3.0);
+  const pf_cxd U = pf_cx_pow(R, 1.0 / 3.0, true);
   const double a56 = -5.0 * alpha / 6.0;
   pf_cxd y;
   if (U.re == 0.0) {
-    const pf_cxd q3 = pf_cx_pow(Q, 1.0 / 3.0);
+    const pf_cxd q3 = pf_cx_pow(Q, 1.0 / 3.0, true);
     y = pf_cx(a56 - q3.re, -q3.im);
   } else {
     const pf_cxd t = pf_cx_div(P, pf_cx_scale(U, 3.0));
@@ -98,7 +114,7 @@ __device__ __noinline__ void pf_p3p_quartic(const double f[5], double roots[4])
   roots[3] = sh + 0.5 * (-w.re - sm.re);
 }
 
-struct pf_d3 { double x, y, z; };
+typedef pf_p3p_d3 pf_d3;
 __device__ __forceinline__ pf_d3 pf_d3m(double x, double y, double z) { pf_d3 v; v.x = x; v.y = y; v.z = z; return v; }
 __device__ __forceinline__ pf_d3 pf_d3_sub(pf_d3 a, pf_d3 b) { return pf_d3m(a.x - b.x, a.y - b.y, a.z - b.z); }
 __device__ __forceinline__ pf_d3 pf_d3_cross(pf_d3 a, pf_d3 b)
@@ -109,44 +125,62 @@ __device__ __forceinline__ double pf_d3_dot(pf_d3 a, pf_d3 b) { return a.x * b.x
 __device__ __forceinline__ double pf_d3_norm(pf_d3 a) { return sqrt(pf_d3_dot(a, a)); }
 __device__ __forceinline__ pf_d3 pf_d3_divs(pf_d3 a, double s) { return pf_d3m(a.x / s, a.y / s, a.z / s); }
 
-// Frame data of one P3P problem that the four back-substitutions share.
-struct pf_p3p_frame {
+// One P3P problem = a camera part (depends on the three bearing vectors only), a world part (depends on the
+// three LEDs and on whether the camera part swapped the first two correspondences) and the quartic that joins
+// them.  The vote shares the camera part between all LED permutations of a detection triple and reads the world
+// parts from a table the prologue fills; the operations and their order are those of P3P::computePoses either way.
+struct pf_p3p_cam {
   pf_d3 e1, e2, e3;     // rows of T (intermediate camera frame)
-  pf_d3 n1, n2, n3;     // rows of N (intermediate world frame)
-  pf_d3 P1;
-  double f_1, f_2, p_1, p_2, d_12, b;
-  double roots[4];
+  double f_1, f_2, b;
+  int swapped;          // :104-125 took the branch f3(2) > 0
 };
 
-// P3P::computePoses up to the roots (p3p.cpp:65-179).  Returns false for colinear world points (:78-84).
-__device__ __noinline__ bool pf_p3p_setup(pf_d3 f1, pf_d3 f2, pf_d3 f3in, pf_d3 P1, pf_d3 P2, pf_d3 P3, pf_p3p_frame& F)
+__device__ __forceinline__ void pf_p3p_cam_frame(pf_d3 f1, pf_d3 f2, pf_d3 f3in, pf_p3p_cam& Cc)
 {
-  if (pf_d3_norm(pf_d3_cross(pf_d3_sub(P2, P1), pf_d3_sub(P3, P1))) == 0.0) return false;
   pf_d3 e1 = f1, e3 = pf_d3_cross(f1, f2);
   e3 = pf_d3_divs(e3, pf_d3_norm(e3));
   pf_d3 e2 = pf_d3_cross(e3, e1);
   pf_d3 f3 = pf_d3m(pf_d3_dot(e1, f3in), pf_d3_dot(e2, f3in), pf_d3_dot(e3, f3in));
+  Cc.swapped = 0;
   if (f3.z > 0.0) {   // :104-125: swap the first two correspondences so that theta lies in [0, pi]
-    pf_d3 t = f1; f1 = f2; f2 = t;
+    const pf_d3 t = f1; f1 = f2; f2 = t;
     e1 = f1; e3 = pf_d3_cross(f1, f2);
     e3 = pf_d3_divs(e3, pf_d3_norm(e3));
     e2 = pf_d3_cross(e3, e1);
     f3 = pf_d3m(pf_d3_dot(e1, f3in), pf_d3_dot(e2, f3in), pf_d3_dot(e3, f3in));
-    t = P1; P1 = P2; P2 = t;
+    Cc.swapped = 1;
   }
+  Cc.e1 = e1; Cc.e2 = e2; Cc.e3 = e3;
+  Cc.f_1 = f3.x / f3.z; Cc.f_2 = f3.y / f3.z;
+  const double cos_beta = pf_d3_dot(f1, f2);
+  const double b = 1 / (1 - cos_beta * cos_beta) - 1;
+  Cc.b = cos_beta < 0 ? -sqrt(b) : sqrt(b);
+}
+
+// :78-84, on the world points in the caller's order
+__device__ __forceinline__ bool pf_p3p_colinear(pf_d3 P1, pf_d3 P2, pf_d3 P3)
+{
+  return pf_d3_norm(pf_d3_cross(pf_d3_sub(P2, P1), pf_d3_sub(P3, P1))) == 0.0;
+}
+
+// world part for the LEDs (P1, P2, P3) in the order the solver uses them (already swapped if the camera part says so)
+__device__ __forceinline__ void pf_p3p_world_frame(pf_d3 P1, pf_d3 P2, pf_d3 P3, pf_p3p_world& W)
+{
   pf_d3 n1 = pf_d3_sub(P2, P1);
   n1 = pf_d3_divs(n1, pf_d3_norm(n1));
   pf_d3 n3 = pf_d3_cross(n1, pf_d3_sub(P3, P1));
   n3 = pf_d3_divs(n3, pf_d3_norm(n3));
   const pf_d3 n2 = pf_d3_cross(n3, n1);
   const pf_d3 d3 = pf_d3_sub(P3, P1);
-  const double p_1 = pf_d3_dot(n1, d3), p_2 = pf_d3_dot(n2, d3);
-  const double d_12 = pf_d3_norm(pf_d3_sub(P2, P1));
-  const double f_1 = f3.x / f3.z, f_2 = f3.y / f3.z;
-  const double cos_beta = pf_d3_dot(f1, f2);
-  double b = 1 / (1 - cos_beta * cos_beta) - 1;
-  b = cos_beta < 0 ? -sqrt(b) : sqrt(b);
+  W.n1 = n1; W.n2 = n2; W.n3 = n3; W.P1 = P1;
+  W.p_1 = pf_d3_dot(n1, d3); W.p_2 = pf_d3_dot(n2, d3);
+  W.d_12 = pf_d3_norm(pf_d3_sub(P2, P1));
+}
 
+// coefficients of the quartic (:150-173) and its roots
+__device__ __forceinline__ void pf_p3p_roots(const pf_p3p_cam& Cc, const pf_p3p_world& W, double roots[4])
+{
+  const double f_1 = Cc.f_1, f_2 = Cc.f_2, b = Cc.b, p_1 = W.p_1, p_2 = W.p_2, d_12 = W.d_12;
   const double f_1_pw2 = f_1 * f_1, f_2_pw2 = f_2 * f_2, p_1_pw2 = p_1 * p_1, p_1_pw3 = p_1_pw2 * p_1,
                p_1_pw4 = p_1_pw3 * p_1, p_2_pw2 = p_2 * p_2, p_2_pw3 = p_2_pw2 * p_2, p_2_pw4 = p_2_pw3 * p_2,
                d_12_pw2 = d_12 * d_12, b_pw2 = b * b;
@@ -162,32 +196,28 @@ __device__ __noinline__ bool pf_p3p_setup(pf_d3 f1, pf_d3 f2, pf_d3 f3in, pf_d3 
   fac[4] = -2 * f_2 * p_2_pw2 * f_1 * p_1 * d_12 * b + f_2_pw2 * p_2_pw2 * d_12_pw2 + 2 * p_1_pw3 * d_12 -
            p_1_pw2 * d_12_pw2 + f_2_pw2 * p_2_pw2 * p_1_pw2 - p_1_pw4 - 2 * f_2_pw2 * p_2_pw2 * p_1 * d_12 +
            p_2_pw2 * f_1_pw2 * p_1_pw2 + f_2_pw2 * p_2_pw2 * d_12_pw2 * b_pw2;
-  pf_p3p_quartic(fac, F.roots);
-  F.e1 = e1; F.e2 = e2; F.e3 = e3; F.n1 = n1; F.n2 = n2; F.n3 = n3; F.P1 = P1;
-  F.f_1 = f_1; F.f_2 = f_2; F.p_1 = p_1; F.p_2 = p_2; F.d_12 = d_12; F.b = b;
-  return true;
+  pf_p3p_quartic(fac, roots);
 }
 
-// Back-substitution of root i (p3p.cpp:181-233): S = [R | C] column-major 3x4, R = N^T R'^T T, C = P1 + N^T C'
-__device__ __noinline__ void pf_p3p_backsub(const pf_p3p_frame& F, int i, double S[12])
+// Back-substitution of one root (p3p.cpp:181-233): S = [R | C] column-major 3x4, R = N^T R'^T T, C = P1 + N^T C'
+__device__ __forceinline__ void pf_p3p_backsub(const pf_p3p_cam& Cc, const pf_p3p_world& W, double r, double S[12])
 {
-  const double r = F.roots[i];
-  const double cot_alpha = (-F.f_1 * F.p_1 / F.f_2 - r * F.p_2 + F.d_12 * F.b) / (-F.f_1 * r * F.p_2 / F.f_2 + F.p_1 - F.d_12);
+  const double cot_alpha = (-Cc.f_1 * W.p_1 / Cc.f_2 - r * W.p_2 + W.d_12 * Cc.b) / (-Cc.f_1 * r * W.p_2 / Cc.f_2 + W.p_1 - W.d_12);
   const double cos_theta = r, sin_theta = sqrt(1 - r * r);
   const double sin_alpha = sqrt(1 / (cot_alpha * cot_alpha + 1));
   double cos_alpha = sqrt(1 - sin_alpha * sin_alpha);
   if (cot_alpha < 0) cos_alpha = -cos_alpha;
-  const double k = sin_alpha * F.b + cos_alpha;
-  const double Cx = F.d_12 * cos_alpha * k, Cy = cos_theta * F.d_12 * sin_alpha * k, Cz = sin_theta * F.d_12 * sin_alpha * k;
-  S[9] = F.P1.x + (F.n1.x * Cx + F.n2.x * Cy + F.n3.x * Cz);
-  S[10] = F.P1.y + (F.n1.y * Cx + F.n2.y * Cy + F.n3.y * Cz);
-  S[11] = F.P1.z + (F.n1.z * Cx + F.n2.z * Cy + F.n3.z * Cz);
+  const double k = sin_alpha * Cc.b + cos_alpha;
+  const double Cx = W.d_12 * cos_alpha * k, Cy = cos_theta * W.d_12 * sin_alpha * k, Cz = sin_theta * W.d_12 * sin_alpha * k;
+  S[9] = W.P1.x + (W.n1.x * Cx + W.n2.x * Cy + W.n3.x * Cz);
+  S[10] = W.P1.y + (W.n1.y * Cx + W.n2.y * Cy + W.n3.y * Cz);
+  S[11] = W.P1.z + (W.n1.z * Cx + W.n2.z * Cy + W.n3.z * Cz);
   // R' as written at :205-214; M1 = N^T R'^T : M1(r,c) = sum_k N(k,r) R'(c,k)
   const double Rp[3][3] = {{-cos_alpha, -sin_alpha * cos_theta, -sin_alpha * sin_theta},
                            {sin_alpha, -cos_alpha * cos_theta, -cos_alpha * sin_theta},
                            {0.0, -sin_theta, cos_theta}};
-  const double Nm[3][3] = {{F.n1.x, F.n1.y, F.n1.z}, {F.n2.x, F.n2.y, F.n2.z}, {F.n3.x, F.n3.y, F.n3.z}};
-  const double Tm[3][3] = {{F.e1.x, F.e1.y, F.e1.z}, {F.e2.x, F.e2.y, F.e2.z}, {F.e3.x, F.e3.y, F.e3.z}};
+  const double Nm[3][3] = {{W.n1.x, W.n1.y, W.n1.z}, {W.n2.x, W.n2.y, W.n2.z}, {W.n3.x, W.n3.y, W.n3.z}};
+  const double Tm[3][3] = {{Cc.e1.x, Cc.e1.y, Cc.e1.z}, {Cc.e2.x, Cc.e2.y, Cc.e2.z}, {Cc.e3.x, Cc.e3.y, Cc.e3.z}};
 #pragma unroll
   for (int rr = 0; rr < 3; ++rr) {
     double m[3];
@@ -206,28 +236,47 @@ __global__ void __launch_bounds__(PF_P3P_BLOCK) pf_p3p_solve_kernel(int n, const
   if (i >= n) return;
   const double* f = fv + 9 * (size_t)i;
   const double* w = wp + 9 * (size_t)i;
-  pf_p3p_frame F;
-  const bool ok = pf_p3p_setup(pf_d3m(f[0], f[1], f[2]), pf_d3m(f[3], f[4], f[5]), pf_d3m(f[6], f[7], f[8]),
-                               pf_d3m(w[0], w[1], w[2]), pf_d3m(w[3], w[4], w[5]), pf_d3m(w[6], w[7], w[8]), F);
+  const pf_d3 P1 = pf_d3m(w[0], w[1], w[2]), P2 = pf_d3m(w[3], w[4], w[5]), P3 = pf_d3m(w[6], w[7], w[8]);
+  pf_p3p_cam Cc;
+  pf_p3p_world W;
+  pf_p3p_cam_frame(pf_d3m(f[0], f[1], f[2]), pf_d3m(f[3], f[4], f[5]), pf_d3m(f[6], f[7], f[8]), Cc);
+  if (Cc.swapped) pf_p3p_world_frame(P2, P1, P3, W); else pf_p3p_world_frame(P1, P2, P3, W);
+  const bool ok = !pf_p3p_colinear(P1, P2, P3);
   rc[i] = ok ? 0 : -1;
   if (!ok) return;
+  double roots[4];
+  pf_p3p_roots(Cc, W, roots);
+#pragma unroll 1
   for (int k = 0; k < 4; ++k) {
     double S[12];
-    pf_p3p_backsub(F, k, S);
+    pf_p3p_backsub(Cc, W, k == 0 ? roots[0] : k == 1 ? roots[1] : k == 2 ? roots[2] : roots[3], S);
     for (int e = 0; e < 12; ++e) sol[48 * (size_t)i + 12 * k + e] = S[e];
   }
 }
 
-// ---- prologue: bearing vectors, cleared outputs ------------------------------------------------------------------
+// LED permutation number -> (j0, j1, j2), all different, lexicographic in (j0, j1, j2)
+__device__ __forceinline__ void pf_p3p_perm(int pr, int L, int& j0, int& j1, int& j2)
+{
+  j0 = pr / ((L - 1) * (L - 2));
+  pr -= j0 * (L - 1) * (L - 2);
+  j1 = pr / (L - 2); j2 = pr % (L - 2);
+  j1 += j1 >= j0 ? 1 : 0;
+  const int lo = j0 < j1 ? j0 : j1, hi = j0 < j1 ? j1 : j0;
+  j2 += j2 >= lo ? 1 : 0;
+  j2 += j2 >= hi ? 1 : 0;
+}
+
+// ---- prologue: bearing vectors, sorted detections, world-frame table, cleared outputs -----------------------------
 __global__ void pf_p3p_prep_kernel(pf_p3p_params p)
 {
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < p.D; i += gridDim.x * blockDim.x) {
+  const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gsz = gridDim.x * blockDim.x;
+  for (int i = gtid; i < p.D; i += gsz) {
     pf_d3 v = pf_d3m((p.img[2 * i] - p.K[2]) / p.K[0], (p.img[2 * i + 1] - p.K[5]) / p.K[4], 1.0);
     v = pf_d3_divs(v, pf_d3_norm(v));
     p.vec[3 * i] = v.x; p.vec[3 * i + 1] = v.y; p.vec[3 * i + 2] = v.z;
   }
   // detections sorted by x (rank sort; a NaN column sorts last and is never inside a window)
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < p.D; i += gridDim.x * blockDim.x) {
+  for (int i = gtid; i < p.D; i += gsz) {
     const double xi = p.img[2 * i], ki = xi != xi ? INFINITY : xi;
     int rank = 0;
     for (int j = 0; j < p.D; ++j) {
@@ -237,8 +286,21 @@ __global__ void pf_p3p_prep_kernel(pf_p3p_params p)
     p.simg[2 * rank] = xi; p.simg[2 * rank + 1] = p.img[2 * i + 1];
     p.sidx[rank] = i;
   }
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < p.D * p.L; i += gridDim.x * blockDim.x) p.hist[i] = 0u;
-  if (blockIdx.x == 0 && threadIdx.x < 4) p.stats[threadIdx.x] = 0ull;
+  // world part of every LED permutation, as given and with the first two LEDs swapped (:122-124)
+  const int nperm = p.L * (p.L - 1) * (p.L - 2);
+  for (int e = gtid; e < 2 * nperm; e += gsz) {
+    int j0, j1, j2;
+    pf_p3p_perm(e >> 1, p.L, j0, j1, j2);
+    const pf_d3 P1 = pf_d3m(p.obj[3 * j0], p.obj[3 * j0 + 1], p.obj[3 * j0 + 2]),
+                P2 = pf_d3m(p.obj[3 * j1], p.obj[3 * j1 + 1], p.obj[3 * j1 + 2]),
+                P3 = pf_d3m(p.obj[3 * j2], p.obj[3 * j2 + 1], p.obj[3 * j2 + 2]);
+    pf_p3p_world W;
+    if (e & 1) pf_p3p_world_frame(P2, P1, P3, W); else pf_p3p_world_frame(P1, P2, P3, W);
+    W.colinear = pf_p3p_colinear(P1, P2, P3) ? 1.0 : 0.0;
+    p.wtab[e] = W;
+  }
+  for (int i = gtid; i < p.D * p.L; i += gsz) p.hist[i] = 0u;
+  if (gtid < 4) p.stats[gtid] = 0ull;
 }
 
 __device__ __forceinline__ double pf_sqd2(double ax, double ay, double bx, double by)
@@ -247,23 +309,24 @@ __device__ __forceinline__ double pf_sqd2(double ax, double ay, double bx, doubl
   return dx * dx + dy * dy;
 }
 
+// number of triples whose first element is < a, out of D elements: C(D,3) - C(D-a,3)
+__device__ __forceinline__ long long pf_c3(long long m) { return m * (m - 1) * (m - 2) / 6; }
+__device__ __forceinline__ long long pf_c2(long long m) { return m * (m - 1) / 2; }
+
 // ---- the vote (pose_estimator.cpp:1540-1717) ---------------------------------------------------------------------
-// grid: one CTA per pair (i0 < i1); dynamic shared memory: hist [D*L] u32 | sxy [D] double2 | sid [D] int | pass [D] u8
-__global__ void __launch_bounds__(PF_P3P_BLOCK) pf_p3p_hist_kernel(pf_p3p_params p)
+// One thread owns one detection triple (i0 < i1 < i2, lexicographic rank = its number) and a slice of the LED
+// permutations (p.nchunk slices per triple, so that small problems still fill the GPU): pre-filters and camera part
+// once, then per permutation the quartic, four back-substitutions, back-projection and votes.
+// dynamic shared memory: sxy [D] double2 | hist [D*L] u32 | sid [D] int
+template <int MINB>
+__global__ void __launch_bounds__(PF_P3P_BLOCK, MINB) pf_p3p_hist_kernel(pf_p3p_params p)
 {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int D = p.D, L = p.L;
   double2* sxy = reinterpret_cast<double2*>(smem_raw);
   unsigned* sh = reinterpret_cast<unsigned*>(sxy + D);
   int* sid = reinterpret_cast<int*>(sh + D * L);
-  unsigned char* pass = reinterpret_cast<unsigned char*>(sid + D);
   const int tid = threadIdx.x;
-
-  // pair index -> (i0, i1), i0 < i1 < D - 1 (a third detection must follow)
-  int i0 = 0, rem = blockIdx.x;
-  while (rem >= D - 2 - i0) { rem -= D - 2 - i0; ++i0; }
-  const int i1 = i0 + 1 + rem;
-
   for (int i = tid; i < D; i += PF_P3P_BLOCK) {
     sxy[i] = make_double2(p.simg[2 * i], p.simg[2 * i + 1]);
     sid[i] = p.sidx[i];
@@ -271,69 +334,80 @@ __global__ void __launch_bounds__(PF_P3P_BLOCK) pf_p3p_hist_kernel(pf_p3p_params
   for (int i = tid; i < D * L; i += PF_P3P_BLOCK) sh[i] = 0u;
   __syncthreads();
 
-  const double thresh = 10000.0 * 100.0;   // threshDist, threshDist2 (:1558-1559)
-  const double d1x = p.img[2 * i0], d1y = p.img[2 * i0 + 1], d2x = p.img[2 * i1], d2y = p.img[2 * i1 + 1];
-  unsigned n_triples = 0, n_solved = 0, n_proj = 0, n_vote = 0;
-
-  // pre-filters of the triple (:1561-1581), once per i2
-  for (int k = i1 + 1 + tid; k < D; k += PF_P3P_BLOCK) {
-    const double d3x = p.img[2 * k], d3y = p.img[2 * k + 1];
-    bool ok = !(pf_sqd2(d1x, d1y, d2x, d2y) > thresh) && !(pf_sqd2(d1x, d1y, d3x, d3y) > thresh) &&
-              !(pf_sqd2(d2x, d2y, d3x, d3y) > thresh);
-    if (ok) {
-      const double mx = (d1x + d2x + d3x) / 3, my = (d1y + d2y + d3y) / 3;
-      int cd = 0;
-      for (int q = 0; q < D; ++q) cd += pf_sqd2(mx, my, sxy[q].x, sxy[q].y) < thresh ? 1 : 0;
-      ok = cd >= 5;
-    }
-    pass[k] = ok ? 1 : 0;
-    n_triples += ok ? 1u : 0u;
+  const long long n_triples_all = pf_c3(D);
+  const long long gid = (long long)blockIdx.x * PF_P3P_BLOCK + tid;
+  const long long triple = gid / p.nchunk;
+  const int chunk = (int)(gid % p.nchunk);
+  const bool in_range = triple < n_triples_all;
+  // unrank: i0 = largest a with C(D,3) - C(D-a,3) <= triple; then the pair (i1, i2) inside the D-1-i0 that follow
+  int i0 = 0, i1 = 1, i2 = 2;
+  if (in_range) {
+    const long long rest = n_triples_all - triple;            // triples from this one to the end, >= 1
+    int m = (int)cbrt(6.0 * (double)rest) + 2;                // smallest m with C(m,3) >= rest, then fix up
+    if (m > D) m = D;
+    while (m > 3 && pf_c3(m - 1) >= rest) --m;
+    while (pf_c3(m) < rest) ++m;
+    i0 = D - m;
+    const long long r2 = triple - (n_triples_all - pf_c3(m));  // rank of (i1, i2) among pairs of the m-1 followers
+    const long long rest2 = pf_c2(m - 1) - r2;                 // >= 1
+    int q = (int)sqrt(2.0 * (double)rest2) + 2;                // smallest q with C(q,2) >= rest2
+    if (q > m - 1) q = m - 1;
+    while (q > 2 && pf_c2(q - 1) >= rest2) --q;
+    while (pf_c2(q) < rest2) ++q;
+    i1 = D - q;
+    i2 = i1 + 1 + (int)(r2 - (pf_c2(m - 1) - pf_c2(q)));
   }
-  __syncthreads();
 
+  const double thresh = 10000.0 * 100.0;   // threshDist, threshDist2 (:1558-1559)
+  const double d1x = p.img[2 * i0], d1y = p.img[2 * i0 + 1], d2x = p.img[2 * i1], d2y = p.img[2 * i1 + 1],
+               d3x = p.img[2 * i2], d3y = p.img[2 * i2 + 1];
+  const double mx = (d1x + d2x + d3x) / 3, my = (d1y + d2y + d3y) / 3;
+  // pre-filters of the triple (:1561-1581)
+  bool pass = in_range && !(pf_sqd2(d1x, d1y, d2x, d2y) > thresh) && !(pf_sqd2(d1x, d1y, d3x, d3y) > thresh) &&
+              !(pf_sqd2(d2x, d2y, d3x, d3y) > thresh);
+  if (pass) {
+    int cd = 0;
+    for (int q = 0; q < D; ++q) cd += pf_sqd2(mx, my, sxy[q].x, sxy[q].y) < thresh ? 1 : 0;
+    pass = cd >= 5;
+  }
+  unsigned n_triples = (pass && chunk == 0) ? 1u : 0u, n_solved = 0, n_proj = 0, n_vote = 0;
+
+  pf_p3p_cam Cc;
+  pf_p3p_cam_frame(pf_d3m(p.vec[3 * i0], p.vec[3 * i0 + 1], p.vec[3 * i0 + 2]),
+                   pf_d3m(p.vec[3 * i1], p.vec[3 * i1 + 1], p.vec[3 * i1 + 2]),
+                   pf_d3m(p.vec[3 * i2], p.vec[3 * i2 + 1], p.vec[3 * i2 + 2]), Cc);
   const int nperm = L * (L - 1) * (L - 2);
-  const int items = (D - 1 - i1) * nperm;
-  const pf_d3 f1 = pf_d3m(p.vec[3 * i0], p.vec[3 * i0 + 1], p.vec[3 * i0 + 2]);
-  const pf_d3 f2 = pf_d3m(p.vec[3 * i1], p.vec[3 * i1 + 1], p.vec[3 * i1 + 2]);
+  const int per = (nperm + p.nchunk - 1) / p.nchunk;
+  const int pr_begin = chunk * per, pr_end = min(nperm, pr_begin + per);
   const double tol = p.tol;
   const double reach = tol + 1e-6;   // column window; every candidate is then tested exactly
   const int n_un = L - 3;
 
-  // The loop is written so that a warp stays converged: every thread runs the same number of steps, dead
-  // threads (past the end, filtered triple, colinear LEDs) skip the bodies, and the warp re-joins after every
-  // solution -- left to itself the compiler lets the threads that voted drift apart for the rest of the CTA.
-  for (int base = 0; base < items; base += PF_P3P_BLOCK) {
-    const int it = base + tid;
-    const bool in_range = it < items;
-    const int i2 = i1 + 1 + (in_range ? it : 0) / nperm;
-    int pr = (in_range ? it : 0) % nperm;
-    const int j0 = pr / ((L - 1) * (L - 2));
-    pr -= j0 * (L - 1) * (L - 2);
-    int j1 = pr / (L - 2), j2 = pr % (L - 2);
-    j1 += j1 >= j0 ? 1 : 0;
-    const int lo = j0 < j1 ? j0 : j1, hi = j0 < j1 ? j1 : j0;
-    j2 += j2 >= lo ? 1 : 0;
-    j2 += j2 >= hi ? 1 : 0;
-
-    const pf_d3 f3 = pf_d3m(p.vec[3 * i2], p.vec[3 * i2 + 1], p.vec[3 * i2 + 2]);
-    pf_p3p_frame F;
-    bool live = in_range && pass[i2] != 0;
-    if (live)
-      live = pf_p3p_setup(f1, f2, f3, pf_d3m(p.obj[3 * j0], p.obj[3 * j0 + 1], p.obj[3 * j0 + 2]),
-                          pf_d3m(p.obj[3 * j1], p.obj[3 * j1 + 1], p.obj[3 * j1 + 2]),
-                          pf_d3m(p.obj[3 * j2], p.obj[3 * j2 + 1], p.obj[3 * j2 + 2]), F);
-    __syncwarp();
+  // The loops are written so that a warp stays converged: every thread runs `per` steps, dead threads skip the
+  // bodies, and the warp re-joins after every solution.
+#pragma unroll 1
+  for (int step = 0; step < per; ++step) {
+    const int pr = pr_begin + step;
+    bool live = pass && pr < pr_end;
+    int j0, j1, j2;
+    pf_p3p_perm(live ? pr : 0, L, j0, j1, j2);
+    const pf_p3p_world W = p.wtab[2 * (live ? pr : 0) + Cc.swapped];
+    live = live && W.colinear == 0.0;
     n_solved += live ? 1u : 0u;
-    const double d3x = p.img[2 * i2], d3y = p.img[2 * i2 + 1];
-    const double mx = (d1x + d2x + d3x) / 3, my = (d1y + d2y + d3y) / 3;
-
+    double r0 = 0, r1 = 0, r2 = 0, r3 = 0;
+    if (live) {
+      double roots[4];
+      pf_p3p_roots(Cc, W, roots);
+      r0 = roots[0]; r1 = roots[1]; r2 = roots[2]; r3 = roots[3];
+    }
+    __syncwarp();
     double Sprev[12];
 #pragma unroll 1
     for (int k = 0; k < 4; ++k) {
       double S[12];
       bool use = false;
       if (live) {
-        pf_p3p_backsub(F, k, S);
+        pf_p3p_backsub(Cc, W, k == 0 ? r0 : k == 1 ? r1 : k == 2 ? r2 : r3, S);
         bool skip = false;
         if (k > 0) {   // :1659-1663: a solution is dropped when ANY entry equals the previous solution's
 #pragma unroll
@@ -346,64 +420,64 @@ __global__ void __launch_bounds__(PF_P3P_BLOCK) pf_p3p_hist_kernel(pf_p3p_params
       }
       __syncwarp();
       if (use) {
-      ++n_proj;
-      // inverse of [R C; 0 1] by cofactors: Ai = adj(R) / det(R), ti = -Ai C
-      const double a00 = S[0], a10 = S[1], a20 = S[2], a01 = S[3], a11 = S[4], a21 = S[5], a02 = S[6], a12 = S[7], a22 = S[8];
-      const double c00 = a11 * a22 - a12 * a21, c01 = a12 * a20 - a10 * a22, c02 = a10 * a21 - a11 * a20;
-      const double det = a00 * c00 + a01 * c01 + a02 * c02;
-      const double i00 = c00 / det, i01 = (a02 * a21 - a01 * a22) / det, i02 = (a01 * a12 - a02 * a11) / det;
-      const double i10 = c01 / det, i11 = (a00 * a22 - a02 * a20) / det, i12 = (a02 * a10 - a00 * a12) / det;
-      const double i20 = c02 / det, i21 = (a01 * a20 - a00 * a21) / det, i22 = (a00 * a11 - a01 * a10) / det;
-      const double t0 = -(i00 * S[9] + i01 * S[10] + i02 * S[11]), t1 = -(i10 * S[9] + i11 * S[10] + i12 * S[11]),
-                   t2 = -(i20 * S[9] + i21 * S[10] + i22 * S[11]);
-      // project the unused LEDs (ascending LED number, :1637-1656) with the full K (project2d :1017-1034)
-      double pu[PF_P3P_MAX_L - 3], pv[PF_P3P_MAX_L - 3];
-      int pl[PF_P3P_MAX_L - 3];
-      int m = 0;
-      for (int ll = 0; ll < L; ++ll) {
-        if (ll == j0 || ll == j1 || ll == j2) continue;
-        const double X = p.obj[3 * ll], Y = p.obj[3 * ll + 1], Z = p.obj[3 * ll + 2];
-        const double xc = i00 * X + i01 * Y + i02 * Z + t0, yc = i10 * X + i11 * Y + i12 * Z + t1,
-                     zc = i20 * X + i21 * Y + i22 * Z + t2;
-        const double q0 = p.K[0] * xc + p.K[1] * yc + p.K[2] * zc, q1 = p.K[3] * xc + p.K[4] * yc + p.K[5] * zc,
-                     q2 = p.K[6] * xc + p.K[7] * yc + p.K[8] * zc;
-        pu[m] = q0 / q2; pv[m] = q1 / q2; pl[m] = ll;
-        ++m;
-      }
-      // votes (:1680-1712): every unused detection close to the triple's centroid whose nearest projected LED is
-      // closer than tol votes for (detection, that LED); if any did, the triple's own three pairs vote too
-      unsigned votes = 0;
-      for (int a = 0; a < n_un; ++a) {
-        const double u = pu[a], xlo = u - reach, xhi = u + reach;
-        int lb = 0, ub = D;
-        while (lb < ub) {   // first sorted detection with x >= xlo
-          const int mid = (lb + ub) >> 1;
-          if (sxy[mid].x < xlo) lb = mid + 1; else ub = mid;
+        ++n_proj;
+        // inverse of [R C; 0 1] by cofactors: Ai = adj(R) / det(R), ti = -Ai C
+        const double a00 = S[0], a10 = S[1], a20 = S[2], a01 = S[3], a11 = S[4], a21 = S[5], a02 = S[6], a12 = S[7], a22 = S[8];
+        const double c00 = a11 * a22 - a12 * a21, c01 = a12 * a20 - a10 * a22, c02 = a10 * a21 - a11 * a20;
+        const double det = a00 * c00 + a01 * c01 + a02 * c02;
+        const double i00 = c00 / det, i01 = (a02 * a21 - a01 * a22) / det, i02 = (a01 * a12 - a02 * a11) / det;
+        const double i10 = c01 / det, i11 = (a00 * a22 - a02 * a20) / det, i12 = (a02 * a10 - a00 * a12) / det;
+        const double i20 = c02 / det, i21 = (a01 * a20 - a00 * a21) / det, i22 = (a00 * a11 - a01 * a10) / det;
+        const double t0 = -(i00 * S[9] + i01 * S[10] + i02 * S[11]), t1 = -(i10 * S[9] + i11 * S[10] + i12 * S[11]),
+                     t2 = -(i20 * S[9] + i21 * S[10] + i22 * S[11]);
+        // project the unused LEDs (ascending LED number, :1637-1656) with the full K (project2d :1017-1034)
+        double pu[PF_P3P_MAX_L - 3], pv[PF_P3P_MAX_L - 3];
+        int pl[PF_P3P_MAX_L - 3];
+        int m = 0;
+        for (int ll = 0; ll < L; ++ll) {
+          if (ll == j0 || ll == j1 || ll == j2) continue;
+          const double X = p.obj[3 * ll], Y = p.obj[3 * ll + 1], Z = p.obj[3 * ll + 2];
+          const double xc = i00 * X + i01 * Y + i02 * Z + t0, yc = i10 * X + i11 * Y + i12 * Z + t1,
+                       zc = i20 * X + i21 * Y + i22 * Z + t2;
+          const double q0 = p.K[0] * xc + p.K[1] * yc + p.K[2] * zc, q1 = p.K[3] * xc + p.K[4] * yc + p.K[5] * zc,
+                       q2 = p.K[6] * xc + p.K[7] * yc + p.K[8] * zc;
+          pu[m] = q0 / q2; pv[m] = q1 / q2; pl[m] = ll;
+          ++m;
         }
-        for (int q = lb; q < D && sxy[q].x <= xhi; ++q) {
-          const int det_i = sid[q];
-          if (det_i == i0 || det_i == i1 || det_i == i2) continue;
-          const double bx = sxy[q].x, by = sxy[q].y;
-          if (!(pf_sqd2(mx, my, bx, by) < thresh)) continue;   // :1598
-          double best = INFINITY;
-          int bj = -1;
-          for (int c = 0; c < n_un; ++c) {   // calculateMinDistancesAndPairs (:2093-2137): first strict minimum
-            const double d2 = pf_sqd2(bx, by, pu[c], pv[c]);
-            if (d2 < best) { best = d2; bj = c; }
+        // votes (:1680-1712): every unused detection close to the triple's centroid whose nearest projected LED is
+        // closer than tol votes for (detection, that LED); if any did, the triple's own three pairs vote too
+        unsigned votes = 0;
+        for (int a = 0; a < n_un; ++a) {
+          const double u = pu[a], xlo = u - reach, xhi = u + reach;
+          int lb = 0, ub = D;
+          while (lb < ub) {   // first sorted detection with x >= xlo
+            const int mid = (lb + ub) >> 1;
+            if (sxy[mid].x < xlo) lb = mid + 1; else ub = mid;
           }
-          if (bj == a && sqrt(best) < tol) {
-            atomicAdd(&sh[det_i * L + pl[a]], 1u);
-            ++votes;
+          for (int q = lb; q < D && sxy[q].x <= xhi; ++q) {
+            const int det_i = sid[q];
+            if (det_i == i0 || det_i == i1 || det_i == i2) continue;
+            const double bx = sxy[q].x, by = sxy[q].y;
+            if (!(pf_sqd2(mx, my, bx, by) < thresh)) continue;   // :1598
+            double best = INFINITY;
+            int bj = -1;
+            for (int c = 0; c < n_un; ++c) {   // calculateMinDistancesAndPairs (:2093-2137): first strict minimum
+              const double d2 = pf_sqd2(bx, by, pu[c], pv[c]);
+              if (d2 < best) { best = d2; bj = c; }
+            }
+            if (bj == a && sqrt(best) < tol) {
+              atomicAdd(&sh[det_i * L + pl[a]], 1u);
+              ++votes;
+            }
           }
         }
+        if (votes) {
+          ++n_vote;
+          atomicAdd(&sh[i0 * L + j0], 1u);
+          atomicAdd(&sh[i1 * L + j1], 1u);
+          atomicAdd(&sh[i2 * L + j2], 1u);
+        }
       }
-      if (votes) {
-        ++n_vote;
-        atomicAdd(&sh[i0 * L + j0], 1u);
-        atomicAdd(&sh[i1 * L + j1], 1u);
-        atomicAdd(&sh[i2 * L + j2], 1u);
-      }
-      }   // use
       __syncwarp();
     }
   }
@@ -430,19 +504,27 @@ __global__ void __launch_bounds__(PF_P3P_BLOCK) pf_p3p_hist_kernel(pf_p3p_params
 
 size_t pf_p3p_smem_bytes(int D, int L)
 {
-  return (size_t)D * 16 + (size_t)D * L * 4 + (size_t)D * 4 + (size_t)D + 16;
+  return (size_t)D * 16 + (size_t)D * L * 4 + (size_t)D * 4 + 16;
 }
 
 cudaError_t pf_p3p_launch_hist(const pf_p3p_params& p, cudaStream_t stream)
 {
   const size_t smem = pf_p3p_smem_bytes(p.D, p.L);
+  // resident CTAs per SM = register budget 168 / 128 / 96: the kernel waits on FP64 dependency chains, so more
+  // warps beat fewer spills (measured, D = 205: 77.4 / 70.4 / 66.9 ms; D = 45: 0.90 / 0.74 / 0.81 ms).
+  // PFMPE_P3P_OCC = 3 | 4 | 5 overrides (tuning aid).
+  static int occ_env = -1;
+  if (occ_env < 0) { const char* e = getenv("PFMPE_P3P_OCC"); occ_env = e ? atoi(e) : 0; }
+  const int occ = occ_env ? occ_env : (p.D >= 100 ? 5 : 4);
+  void (*kern)(pf_p3p_params) = occ == 5 ? pf_p3p_hist_kernel<5> : occ == 4 ? pf_p3p_hist_kernel<4> : pf_p3p_hist_kernel<3>;
   if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(pf_p3p_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
   }
-  const unsigned pairs = (unsigned)((p.D - 1) * (p.D - 2) / 2);
-  pf_p3p_prep_kernel<<<(p.D + 127) / 128, 128, 0, stream>>>(p);
-  pf_p3p_hist_kernel<<<pairs, PF_P3P_BLOCK, smem, stream>>>(p);
+  const long long triples = (long long)p.D * (p.D - 1) * (p.D - 2) / 6;
+  const long long threads = triples * p.nchunk;
+  pf_p3p_prep_kernel<<<(p.D + 127) / 128 + 2, 128, 0, stream>>>(p);
+  kern<<<(unsigned)((threads + PF_P3P_BLOCK - 1) / PF_P3P_BLOCK), PF_P3P_BLOCK, smem, stream>>>(p);
   return cudaGetLastError();
 }
 

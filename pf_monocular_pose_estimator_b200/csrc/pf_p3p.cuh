@@ -21,6 +21,15 @@
 #define PF_P3P_MAX_D 1024
 #define PF_P3P_MAX_L 8
 
+struct pf_p3p_d3 { double x, y, z; };
+// world part of one P3P problem (intermediate world frame of p3p.cpp:127-148), 16 doubles
+struct pf_p3p_world {
+  pf_p3p_d3 n1, n2, n3;   // rows of N
+  pf_p3p_d3 P1;
+  double p_1, p_2, d_12;
+  double colinear;        // table entries only: != 0 when the three LEDs are colinear (:78-84), no solution
+};
+
 struct pf_p3p_params {
   int D, L;
   double K[9];                 // row-major
@@ -30,6 +39,8 @@ struct pf_p3p_params {
   double* simg;                // [D][2] detections sorted by x (written by the prologue)
   int* sidx;                   // [D] caller index of sorted detection
   double* vec;                 // [D][3] unit bearing vectors (calculateImageVectors :1072-1085), caller order
+  pf_p3p_world* wtab;          // [L(L-1)(L-2)][2] world parts: LED permutation as given / first two swapped
+  int nchunk;                  // slices of the permutation list per detection triple (divides the work of small D)
   unsigned* hist;              // [D][L]
   unsigned long long* stats;   // [4] triples passing the pre-filters, P3P solved, solutions projected, solutions voting
 };

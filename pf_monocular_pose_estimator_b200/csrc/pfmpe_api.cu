@@ -1220,8 +1220,10 @@ int p3p_histogram_impl(pfmpe_handle* h, int tracker, const double* image_points,
   if (L < 3) return fail(h, PFMPE_ERR_UNSUPPORTED, "P3P needs at least 3 LEDs");
   if (D < 3 || D > PF_P3P_MAX_D) return fail(h, PFMPE_ERR_INVALID, "n_image_points must be 3..1024");
   PF_CUDA(h, cudaSetDevice(h->cfg.device));
-  // scratch layout: img 2D | simg 2D | vec 3D | stats 4 (all 8-byte) | hist D*L u32 | sidx D i32
-  const size_t need = (size_t)D * 7 * 8 + 32 + (size_t)D * L * 4 + (size_t)D * 4;
+  // scratch layout: img 2D | simg 2D | vec 3D | stats 4 | wtab 2*nperm*16 (all 8-byte) | hist D*L u32 | sidx D i32
+  const int nperm = L * (L - 1) * (L - 2);
+  const size_t wtab_doubles = (size_t)2 * nperm * (sizeof(pf_p3p_world) / sizeof(double));
+  const size_t need = ((size_t)D * 7 + 4 + wtab_doubles) * 8 + (size_t)D * L * 4 + (size_t)D * 4;
   if (need > h->p3p_bytes) {
     PF_CUDA(h, cudaStreamSynchronize(h->stream));
     cudaFree(h->p3p_buf); h->p3p_buf = nullptr; h->p3p_bytes = 0;
@@ -1239,7 +1241,13 @@ int p3p_histogram_impl(pfmpe_handle* h, int tracker, const double* image_points,
   p.simg = base + 2 * (size_t)D;
   p.vec = base + 4 * (size_t)D;
   p.stats = reinterpret_cast<unsigned long long*>(base + 7 * (size_t)D);
-  p.hist = reinterpret_cast<unsigned*>(base + 7 * (size_t)D + 4);
+  p.wtab = reinterpret_cast<pf_p3p_world*>(base + 7 * (size_t)D + 4);
+  p.hist = reinterpret_cast<unsigned*>(base + 7 * (size_t)D + 4 + wtab_doubles);
+  // enough threads to fill the GPU even for a handful of detections: slice the permutation list of a triple
+  const long long triples = (long long)D * (D - 1) * (D - 2) / 6;
+  const long long want_threads = (long long)h->num_sms * 3 * PF_P3P_BLOCK * 2;
+  long long nchunk = (want_threads + triples - 1) / triples;
+  p.nchunk = (int)(nchunk < 1 ? 1 : nchunk > nperm ? nperm : nchunk);
   p.sidx = reinterpret_cast<int*>(p.hist + (size_t)D * L);
   if (on_device) p.img = image_points;
   else {
