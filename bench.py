@@ -367,6 +367,47 @@ def sharded_filter_measure(world, rank, dev, local_rank, barrier, allreduce, RO,
             "note": "host-orchestrated stages through pfmpe_shard_*; wall clock of the whole host loop incl. host Gauss-Newton"}
 
 
+def p3p_vote_measure(dev, with_cpu, n_detections=205, K=5, W=2):
+    """SURVEY 8 row f4 alongside (rank 0 only, short): the correspondence vote of the brute-force initialisation on the
+    outlier-heavy scene of BASELINE configs[2] (5 LEDs + 200 spurious blobs): C(205,3) * 60 = 8.5e7 P3P solves."""
+    import torch
+    from pf_monocular_pose_estimator_b200 import capi
+    from tests.p3p_util import vote_scene
+    sc, img, _ = vote_scene(n_detections - 5)
+    h = capi.Handle(1000, n_leds=5, max_blobs=32, device=dev)
+    h.configure(sc.markers, sc.K, sc.params)
+    d_img = torch.from_numpy(img).to("cuda:%d" % dev)
+    dev_ms, wall = [], []
+    st = None
+    for i in range(W + K):
+        _, st = h.p3p_histogram(img, d_image_points=d_img.data_ptr())     # detections resident in HBM
+        if i >= W:
+            dev_ms.append(st["device_ms"])
+    for i in range(W + K):
+        t0 = time.perf_counter()
+        hist, st2 = h.p3p_histogram(img)                                  # C-ABI call from HOST buffers
+        if i >= W:
+            wall.append(time.perf_counter() - t0)
+    h.close()
+    solves = st["p3p_solved"]
+    out = {"workload": "initialisation vote, %d detections x 5 LEDs" % n_detections, "p3p_solves": solves,
+           "value": solves / (float(np.median(dev_ms)) * 1e-3), "unit": "P3P solves/s", "ms_per_step": float(np.median(dev_ms)),
+           "e2e": {"value": solves / float(np.median(wall)), "unit": "P3P solves/s", "ms": 1e3 * float(np.median(wall)),
+                   "h2d_bytes_per_step": int(img.nbytes), "d2h_bytes_per_step": int(hist.nbytes) + 32},
+           "dtype": "f64", "votes": int(hist.sum()), "steps": K, "warmup": W,
+           "note": "pfmpe_p3p_histogram: FP64 Kneip P3P + back-projection + votes in one kernel (K9); FP64-pipe/latency bound, "
+                   "no HBM traffic to speak of (profiles/r01e_ncu_lines_p3p.txt)"}
+    if with_cpu:
+        from oracle import orc
+        sc2, img2, _ = vote_scene(40)
+        t0 = time.perf_counter()
+        _, so = orc.p3p_histogram(sc2.K, sc2.markers, img2, sc2.params["back_projection_pixel_tolerance"])
+        dt = time.perf_counter() - t0
+        out["cpu_baseline"] = {"value": so[1] / dt, "unit": "P3P solves/s", "cores": 1, "kind": "port",
+                               "sample": "one vote with 45 detections (%d solves, %.2f s)" % (so[1], dt)}
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -379,6 +420,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-batched", action="store_true", help="skip the short cfg4 run reported under batched_trackers")
     ap.add_argument("--no-sharded", action="store_true", help="skip the short configs[4] run reported under sharded_filter")
+    ap.add_argument("--no-p3p", action="store_true", help="skip the short initialisation-vote run reported under p3p_vote")
     ap.add_argument("--trackers", type=int, default=None, help="override the tracker count of the workload (experiments)")
     ap.add_argument("--e2e-steps", type=int, default=300)
     ap.add_argument("--cpu-budget", type=float, default=15.0)
@@ -499,6 +541,9 @@ def main():
     # ---- BASELINE configs[4] alongside (short): ONE filter of 2^26 particles sharded by particle over the ranks
     if not sharded and not args.no_sharded:
         line["sharded_filter"] = sharded_filter_measure(world, rank, dev, local_rank, barrier, allreduce, RO, peak)
+
+    if rank == 0 and not sharded and not args.no_p3p:
+        line["p3p_vote"] = p3p_vote_measure(local_rank, with_cpu=(world == 1 and not args.no_cpu))
 
     if rank == 0:
         if world == 1 and not args.no_cpu:
