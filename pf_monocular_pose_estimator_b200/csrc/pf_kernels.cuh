@@ -925,8 +925,11 @@ __device__ __forceinline__ void pf_shard_publish(const pf_kparams& p, int nwords
 // Variants (separate instantiations, so that the plain single-GPU kernel carries none of their code):
 // V = 1: the stage-per-launch forms of the sharded filter (modes 3-5); V = 2: forward plumb_bob
 // distortion in the projection (row f3).
+// V = 3: the plain kernel again, compiled for the one-CTA-per-filter (batch) shape only: 256-thread CTAs, 4 per SM
+// (64 registers instead of 80): the batch shape is bound by issue latency, and a third more resident warps buys
+// 7-10 % on BASELINE configs[3] (4096 filters x 4096 particles: 1.43 -> 1.32 ms/step).
 template <int L, int V>
-__global__ void __launch_bounds__(PF_MAX_BLOCK, 1) pf_frames_kernel(const __grid_constant__ pf_kparams p)
+__global__ void __launch_bounds__(V == 3 ? PF_BLOCK : PF_MAX_BLOCK, V == 3 ? 4 : 1) pf_frames_kernel(const __grid_constant__ pf_kparams p)
 {
   constexpr bool SH = V == 1;
   extern __shared__ __align__(16) unsigned char pf_dyn_smem[];

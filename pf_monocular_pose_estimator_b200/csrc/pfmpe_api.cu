@@ -230,7 +230,7 @@ frames_kernel_t kernel_for_sh(int L)
 
 frames_kernel_t kernel_for(int L, int variant)
 {
-  return variant == 1 ? kernel_for_sh<1>(L) : (variant == 2 ? kernel_for_sh<2>(L) : kernel_for_sh<0>(L));
+  return variant == 1 ? kernel_for_sh<1>(L) : (variant == 2 ? kernel_for_sh<2>(L) : (variant == 3 ? kernel_for_sh<3>(L) : kernel_for_sh<0>(L)));
 }
 
 // per-launch arguments of the sharded-filter stages (modes 3-5)
@@ -285,6 +285,7 @@ int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_f
   if (h->force_mode == 1) grid_mode = false;
   else if (h->force_mode == 2) grid_mode = true;
   else grid_mode = (nt == 1) ? (N > 1024) : (N > 16384);
+  if (!grid_mode && mode < 3 && !distort) k = kernel_for(h->cfg.n_leds, 3);   // batch shape: the 64-register build
 
   pf_kparams p;
   fill_kparams(h, p);
