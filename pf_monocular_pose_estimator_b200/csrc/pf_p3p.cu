@@ -455,9 +455,10 @@ __global__ void __launch_bounds__(PF_P3P_BLOCK, MINB) pf_p3p_hist_kernel(pf_p3p_
             if (sxy[mid].x < xlo) lb = mid + 1; else ub = mid;
           }
           for (int q = lb; q < D && sxy[q].x <= xhi; ++q) {
+            const double bx = sxy[q].x, by = sxy[q].y;
+            if (!(fabs(by - pv[a]) <= reach)) continue;          // farther than tol from this LED: cannot vote for it
             const int det_i = sid[q];
             if (det_i == i0 || det_i == i1 || det_i == i2) continue;
-            const double bx = sxy[q].x, by = sxy[q].y;
             if (!(pf_sqd2(mx, my, bx, by) < thresh)) continue;   // :1598
             double best = INFINITY;
             int bj = -1;
@@ -465,7 +466,7 @@ __global__ void __launch_bounds__(PF_P3P_BLOCK, MINB) pf_p3p_hist_kernel(pf_p3p_
               const double d2 = pf_sqd2(bx, by, pu[c], pv[c]);
               if (d2 < best) { best = d2; bj = c; }
             }
-            if (bj == a && sqrt(best) < tol) {
+            if (bj == a && best <= reach * reach && sqrt(best) < tol) {
               atomicAdd(&sh[det_i * L + pl[a]], 1u);
               ++votes;
             }

@@ -2,7 +2,7 @@
 set -x
 export PYTHONPATH=.
 mkdir -p gpurun_out
-B="--steps 30 --warmup 5 --no-cpu --no-e2e --no-batched --no-sharded --no-p3p"
+B="--steps 30 --warmup 5 --no-cpu --no-e2e --no-batched --no-sharded --no-p3p --no-outlier"
 python bench.py $B > gpurun_out/prof_bench.json 2> gpurun_out/prof_bench.err || exit 1
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_cfg2.csv \
     python bench.py $B > gpurun_out/ncu_launches.log 2>&1
