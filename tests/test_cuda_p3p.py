@@ -148,3 +148,32 @@ def test_vote_full_size_properties():
     assert (got_p == got[:, order]).all() and st_p["solutions_voted"] == st["solutions_voted"]
     h2.close()
     h.close()
+
+
+def test_vote_eight_leds_and_large_shared_memory():
+    """PFMPE_MAX_LED LEDs (five unused LEDs per solution, 336 permutations) against the oracle, and a detection count
+    whose shared-memory tables need the opt-in carve-out (D x L x 4 + D x 20 > 48 KB)."""
+    markers = np.concatenate([S.MARKERS_5, [[0.12, 0.02, 0.06], [0.20, -0.05, 0.03], [0.05, -0.09, 0.08]]])
+    h = _handle(markers)
+    sc, img, true_blob = vote_scene(16, markers=markers)
+    ref, st_ref = orc.p3p_histogram(sc.K, sc.markers, img, 5.0)
+    lo, _ = orc.p3p_histogram(sc.K, sc.markers, img, 5.0, dup_mode=2)
+    hi, _ = orc.p3p_histogram(sc.K, sc.markers, img, 5.0, dup_mode=1)
+    got, st = h.p3p_histogram(img)
+    assert st["triples"] == comb(24, 3) and st["p3p_solved"] == st_ref[1] == comb(24, 3) * 336
+    g = got.astype(np.int64)
+    assert int(np.maximum(lo.astype(np.int64) - g, 0).sum() + np.maximum(g - hi.astype(np.int64), 0).sum()) <= 2
+    assert int(np.abs(g - ref.astype(np.int64)).sum()) <= max(4, int(ref.sum()) // 500)
+    # Near the documented maximum of 1024 detections the shared-memory tables (D x (20 + 4 L) bytes) need the opt-in
+    # carve-out above 48 KB.  990 detections on a 5000-px lattice (no two within the 1000-px pre-filter distance,
+    # :1556-1566) + two clusters of 6: only the 2 x C(6,3) triples inside the clusters reach the solver.
+    gx, gy = np.meshgrid(np.arange(33), np.arange(30))
+    lattice = np.stack([gx.ravel(), gy.ravel()], axis=1)[:990] * 5000.0 + 20000.0
+    rng = np.random.default_rng(2)
+    clusters = np.concatenate([rng.uniform(0, 50, (6, 2)) + [300.0, 200.0], rng.uniform(0, 50, (6, 2)) + [3000.0, 2000.0]])
+    big = np.concatenate([lattice, clusters])
+    perm = rng.permutation(big.shape[0])
+    hist, st = h.p3p_histogram(big[perm])
+    assert st["triples"] == 2 * comb(6, 3) and st["p3p_solved"] == 2 * comb(6, 3) * 336
+    assert hist[np.isin(perm, np.arange(990))].sum() == 0      # lattice points never vote or get voted for
+    h.close()
