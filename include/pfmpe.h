@@ -288,8 +288,12 @@ int pfmpe_shard_import(pfmpe_handle* h, const void* d_rows, int64_t local_offset
  * pfmpe_shard_set_peers installs the table of all `world` bases (rank order, equal shards) and
  * pfmpe_shard_scatter writes every output slot this rank produced -- `count` slots from
  * first_owned_slot, both from pfmpe_shard_resample's partial -- into the owning rank's planes
- * with local or NVLink peer stores.  The caller orders the scatter of all ranks before the next
- * pfmpe_shard_score (a barrier on the ranks' streams). */
+ * with local or NVLink peer stores.  Resampling replicates, so a run of slots with the same source
+ * inside one destination's range travels as ONE row (stored at the run's first slot) plus a 4-byte
+ * leader index per slot (lead[], which lives behind the planes in the same allocation); the next score
+ * pass gathers through lead[].  The caller orders the scatter of all ranks before the next
+ * pfmpe_shard_score (a barrier on the ranks' streams).  pfmpe_shard_set_peers(h, 0, NULL) removes the
+ * table again (row exchange: full rows at every slot). */
 int pfmpe_shard_local_ptr(pfmpe_handle* h, void** d_ptr);
 int pfmpe_shard_ipc_export(pfmpe_handle* h, unsigned char handle[64]);
 int pfmpe_shard_ipc_open(pfmpe_handle* h, const unsigned char handle[64], void** d_ptr);

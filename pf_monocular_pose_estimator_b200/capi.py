@@ -426,8 +426,8 @@ class Handle:
         return int(q.value)
 
     def shard_set_peers(self, ptrs):
-        arr = (C.c_void_p * len(ptrs))(*[int(v) for v in ptrs])
-        self._chk(lib().pfmpe_shard_set_peers(self._h, len(ptrs), arr))
+        arr = (C.c_void_p * max(len(ptrs), 1))(*[int(v) for v in ptrs])
+        self._chk(lib().pfmpe_shard_set_peers(self._h, len(ptrs), arr))   # empty list: back to the row exchange
 
     def shard_scatter(self, first_owned_slot, count):
         self._chk(lib().pfmpe_shard_scatter(self._h, int(first_owned_slot), int(count)))

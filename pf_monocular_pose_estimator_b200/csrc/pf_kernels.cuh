@@ -344,7 +344,8 @@ __device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_c
   const float4* src = (cx.src_buf == 0 ? p.pose0 : p.pose1) + tb;
   float4* dst = (cx.src_buf == 0 ? p.pose1 : p.pose0) + tb;
   float* w = p.w + (size_t)trk * N;
-  const int* idx = p.idx + (size_t)trk * N;
+  // sharded filter: the rebalance delivers lead[] (slot -> local slot that holds its row), idx[] is the stage-B output
+  const int* idx = (SH && p.lead) ? p.lead : p.idx + (size_t)trk * N;
 
   pf_pose Pm, Cm;
 #pragma unroll
@@ -1067,7 +1068,7 @@ __global__ void __launch_bounds__(V == 3 ? PF_BLOCK : PF_MAX_BLOCK, V == 3 ? 4 :
       if (blockIdx.x == 0 && threadIdx.x == 0) {
         p.shard_partial[0] = (long long)cnt.cntkey;
         pf_tracker_state* g = p.state + trk;
-        g->t_buf = 1 - cx.src_buf; g->src_mode = 0; g->frames_done = st.frames_done + 1;
+        g->t_buf = 1 - cx.src_buf; g->src_mode = p.lead_mode ? 1 : 0; g->frames_done = st.frames_done + 1;
       }
       pf_shard_publish(p, 2);
       continue;
@@ -1160,20 +1161,37 @@ __global__ void __launch_bounds__(PF_BLOCK) pf_shard_keep_kernel(const float4* T
 // stores, another GPU's (peers[d] = base of rank d's next-frame particle planes, N particles per
 // rank).  Slot k = kbase + i -> rank k / N, local particle k % N.  One kernel replaces the row
 // export, the all_to_all and the import; remote and local stores overlap across CTAs.
-__global__ void __launch_bounds__(PF_BLOCK) pf_shard_scatter_kernel(const float4* T, const int* idx, int N, long long kbase,
-                                                                    long long count, float4* const* peers)
+// Every rank's allocation is [3 N float4 planes | N int lead].
+__global__ void __launch_bounds__(PF_BLOCK) pf_shard_scatter_kernel(const float4* T, const int* idx, const int* kend, int N,
+                                                                    long long kbase, long long count, float4* const* peers)
 {
+  // Resampling replicates: the slots of one source are consecutive, and after a few frames a handful of sources
+  // own most of them (measured on 2^26 particles over 8 GPUs: 3 398 surviving sources on one rank, which then had to
+  // push 7/8 of ALL rows through its NVLink ports: 2.8 ms).  So a run of equal sources inside one destination's
+  // range travels as ONE row, stored at the run's first slot (its leader), plus a 4-byte leader index per slot
+  // (lead[], behind the destination's planes); the destination's next score pass gathers through lead[], the way
+  // the single-GPU filter gathers through idx[].  A slot that continues a run has a source with >= 2 offspring, so
+  // the run starts at kend[s - 1] (the rank's first slot for s = 0), clamped to the destination's first slot.
   const long long stride = (long long)gridDim.x * PF_BLOCK;
   for (long long i = (long long)blockIdx.x * PF_BLOCK + threadIdx.x; i < count; i += stride) {
     const long long k = kbase + i;
     const int d = (int)(k / N);
-    const int n = (int)(k - (long long)d * N);
+    const long long d0 = (long long)d * N;
+    const int n = (int)(k - d0);
     const int s = idx[i];
+    const bool starts = i == 0 || k == d0 || idx[i - 1] != s;
     float4* dst = peers[d];
-    const float4 r0 = T[s], r1 = T[(size_t)N + s], r2 = T[2 * (size_t)N + s];
-    dst[n] = r0;
-    dst[(size_t)N + n] = r1;
-    dst[2 * (size_t)N + n] = r2;
+    int* lead = reinterpret_cast<int*>(dst + 3 * (size_t)N);
+    if (starts) {
+      const float4 r0 = T[s], r1 = T[(size_t)N + s], r2 = T[2 * (size_t)N + s];
+      dst[n] = r0;
+      dst[(size_t)N + n] = r1;
+      dst[2 * (size_t)N + n] = r2;
+      lead[n] = n;
+    } else {
+      const long long fs = s > 0 ? (long long)kend[s - 1] : kbase;
+      lead[n] = (int)((fs > d0 ? fs : d0) - d0);
+    }
   }
 }
 

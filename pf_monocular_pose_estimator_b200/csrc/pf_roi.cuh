@@ -29,7 +29,7 @@ __global__ void __launch_bounds__(PF_BLOCK) pf_roi_kernel(const pf_kparams p, co
   const int trk = p.tracker_base + blockIdx.y, N = p.N;
   const pf_tracker_state* st = p.state + trk;
   const float4* src = (st->src_buf == 0 ? p.pose0 : p.pose1) + (size_t)trk * 3 * (size_t)N;
-  const int* idx = p.idx + (size_t)trk * N;
+  const int* idx = p.lead ? p.lead : p.idx + (size_t)trk * N;   // sharded filter: lead[] (pf_shard_scatter_kernel)
   const bool through_idx = st->src_mode == 1;
   const bool kstd = p.kstd != 0;
   float obj[3 * L];

@@ -135,6 +135,8 @@ struct pf_kparams {
   int iters_total;                // modes 4/5: do/while iterations executed (all shards)
   int q_local;                    // mode 5: local index of the winner
   int idx_cap;                    // capacity of idx[] (slots this shard's sources may own)
+  int lead_mode;                  // mode 4: the rebalance leaves one row per run of equal sources + lead[] (pf_shard_scatter_kernel)
+  const int* lead;                // sharded: [N] local slot that holds the row of slot n (gather indirection of the score pass)
   long long S_fx;                 // modes 4/5: global weight sum, Q.30
   long long rank_excl[3], rank_total[3];   // mode 4: (sum, max, min) aggregate of the lower ranks / of all ranks
   long long* shard_partial;       // [8] per-stage results of this shard (device)

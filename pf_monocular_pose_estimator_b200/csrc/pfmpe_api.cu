@@ -76,6 +76,7 @@ struct pfmpe_handle {
   unsigned* roi_keys = nullptr;   // K8: [tracker][4] ordered-float keys, then the floats
   float* roi_out = nullptr;
   float* h_roi = nullptr;
+  int* lead = nullptr;                  // sharded: [N] gather indirection, lives behind pose0's planes (one IPC allocation)
   unsigned char* p3p_buf = nullptr;     // K9 scratch: detections, sorted copy, bearing vectors, counters, histogram
   size_t p3p_bytes = 0;
   double* p3p_io = nullptr;             // batched solver scratch
@@ -206,6 +207,8 @@ void fill_kparams(const pfmpe_handle* h, pf_kparams& p)
   p.idx_cap = p.N_global;
   p.warp_agg_g = h->warp_agg_g;
   p.shard_partial = h->shard_partial;
+  p.lead = h->sharded ? h->lead : nullptr;
+  p.lead_mode = (h->sharded && h->peers_dev) ? 1 : 0;
   p.timeline = h->timeline_on ? h->timeline : nullptr;
 }
 
@@ -767,7 +770,7 @@ static int run_gather(pfmpe_handle* h, int tracker)
   const size_t N = (size_t)h->cfg.n_particles;
   const float4* T = (s.src_buf == 0 ? h->pose0 : h->pose1) + (size_t)tracker * 3 * N;
   const int blocks = (int)((N + PF_BLOCK - 1) / PF_BLOCK);
-  pf_gather_kernel<<<blocks, PF_BLOCK, 0, h->stream>>>(T, h->idx + (size_t)tracker * N, (int)N, s.src_mode,
+  pf_gather_kernel<<<blocks, PF_BLOCK, 0, h->stream>>>(T, (h->sharded && h->lead) ? h->lead : h->idx + (size_t)tracker * N, (int)N, s.src_mode,
                                                       h->gather_tmp, h->gather_idx);
   PF_CUDA(h, cudaGetLastError());
   h->launches += 1;
@@ -1331,6 +1334,12 @@ int pfmpe_shard_configure(pfmpe_handle* h, int64_t global_offset, int64_t n_glob
   cudaFree(h->idx); h->idx = nullptr;
   PF_CUDA(h, dev_alloc(&h->idx, (size_t)n_global));
   PF_CUDA(h, cudaMemset(h->idx, 0, (size_t)n_global * sizeof(int)));
+  // pose0 receives the rebalanced set: its allocation grows by the lead[] array the peers write next to the rows
+  if (h->particles_set[0]) return fail(h, PFMPE_ERR_STATE, "pfmpe_shard_configure must precede set_particles / track_init");
+  cudaFree(h->pose0); h->pose0 = nullptr; h->lead = nullptr;
+  PF_CUDA(h, cudaMalloc((void**)&h->pose0, (size_t)N * (3 * sizeof(float4) + sizeof(int))));
+  PF_CUDA(h, cudaMemset(h->pose0, 0, (size_t)N * (3 * sizeof(float4) + sizeof(int))));
+  h->lead = reinterpret_cast<int*>(h->pose0 + 3 * (size_t)N);
   if (!h->warp_agg_g) PF_CUDA(h, dev_alloc(&h->warp_agg_g, (size_t)PF_MAX_GRID * PF_MAX_WARPS));
   if (!h->shard_partial) PF_CUDA(h, dev_alloc(&h->shard_partial, PF_XMAIL_WORDS));
   h->sharded = true;
@@ -1475,9 +1484,14 @@ int pfmpe_shard_ipc_open(pfmpe_handle* h, const unsigned char handle[64], void**
 
 int pfmpe_shard_set_peers(pfmpe_handle* h, int world, void* const* d_ptrs)
 {
-  if (!h || world < 1 || world > 1024 || !d_ptrs) return PFMPE_ERR_INVALID;
+  if (!h || world < 0 || world > 1024 || (world > 0 && !d_ptrs)) return PFMPE_ERR_INVALID;
   if (!h->sharded) return fail(h, PFMPE_ERR_STATE, "pfmpe_shard_configure must be called first");
   PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  if (world == 0) {   // back to the row exchange (full rows at every slot, no lead[] indirection)
+    PF_CUDA(h, cudaStreamSynchronize(h->stream));
+    cudaFree(h->peers_dev); h->peers_dev = nullptr; h->peer_world = 0;
+    return PFMPE_OK;
+  }
   if ((int64_t)world * h->cfg.n_particles != (int64_t)h->n_global) return fail(h, PFMPE_ERR_INVALID, "peer rebalance needs equal shards");
   PF_CUDA(h, cudaStreamSynchronize(h->stream));
   cudaFree(h->peers_dev); h->peers_dev = nullptr;
@@ -1500,7 +1514,7 @@ int pfmpe_shard_scatter(pfmpe_handle* h, int64_t first_owned_slot, int64_t count
   long long blocks = (count + PF_BLOCK - 1) / PF_BLOCK;
   const long long cap = (long long)h->num_sms * 32;
   if (blocks > cap) blocks = cap;
-  pf_shard_scatter_kernel<<<(int)blocks, PF_BLOCK, 0, h->stream>>>(h->pose1, h->idx, N, first_owned_slot, count, h->peers_dev);
+  pf_shard_scatter_kernel<<<(int)blocks, PF_BLOCK, 0, h->stream>>>(h->pose1, h->idx, h->kend, N, first_owned_slot, count, h->peers_dev);
   PF_CUDA(h, cudaGetLastError());
   h->launches += 1;
   return PFMPE_OK;

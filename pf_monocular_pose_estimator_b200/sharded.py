@@ -248,6 +248,9 @@ class ShardedFilter:
                 self.rebalance = "p2p"
             elif rebalance == "p2p":
                 raise RuntimeError("peer-memory rebalance unavailable: %s" % (self.p2p_error or "a peer rank failed"))
+            else:
+                for h in self.shards:                        # the peer tables also switch the kernels to lead[] gathers
+                    h.shard_set_peers([])
         # exchange of the 64-byte partials: "mail" = peer stores from inside the stage kernels + a wait
         # kernel that hands the table to the host through pinned memory (needs peer access, like p2p);
         # otherwise all_gather + device->host copy
