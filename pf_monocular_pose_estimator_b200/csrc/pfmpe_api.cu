@@ -1086,8 +1086,9 @@ extern "C++" {
 template <typename F>
 static void host_parallel_for(int n, F body)
 {
-  unsigned hw = std::thread::hardware_concurrency();
-  int nth = (int)(hw ? hw : 1);
+  if (n < 64) { for (int i = 0; i < n; ++i) body(i); return; }   // the single-object latency path never gets here
+  static const int hw = (int)std::thread::hardware_concurrency();  // queried once: it reads /sys on Linux
+  int nth = hw > 0 ? hw : 1;
   if (nth > n / 32) nth = n / 32;
   if (nth <= 1) { for (int i = 0; i < n; ++i) body(i); return; }
   std::vector<std::thread> th;
