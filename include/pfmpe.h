@@ -241,6 +241,30 @@ int pfmpe_p3p_histogram(pfmpe_handle* h, int tracker, const double* image_points
 int pfmpe_p3p_histogram_dev(pfmpe_handle* h, int tracker, const double* d_image_points, int32_t n_image_points,
                             uint32_t* hist, pfmpe_p3p_stats* stats);
 
+/* The per-combination body of PoseEstimator::checkCorrespondences (pose_estimator.cpp:1340-1445), batched over
+ * n_sets candidate correspondence sets (the entries of correspondencesFromHistogram's list, :1733-1751): for every
+ * combination of three pairs of a set (Combinations::combinationsNoReplacement order = lexicographic) P3P on the
+ * three, back-projection of the set's other LEDs through each finite solution, squared reprojection error and
+ * certainty against their detections (calculateSquaredReprojectionErrorAndCertainty, :1087-1132, tolerance =
+ * back_projection_pixel_tolerance), and the best solution that reaches certainty_threshold (:1412-1420).
+ * correspondences: n_sets rows of 2*PFMPE_MAX_LED uint32 = pairs (LED, detection), 1-based; counts[s] = pairs in
+ * row s (3..PFMPE_MAX_LED).  results: n_sets x PFMPE_P3P_CHECK_STRIDE records, record [s][c] for combination c
+ * (those beyond C(counts[s], 3) are zeroed).  The caller counts the valid ones against
+ * valid_correspondence_threshold_ (:1469), averages pose * object_points (:1447-1451) and seeds PoseParticle with
+ * the poses (:1432-1438). */
+#define PFMPE_P3P_CHECK_STRIDE 56
+typedef struct {
+  int32_t rc;           /* computePoses' return value (0, -1 colinear LEDs), -2 = a pair outside 1..n_leds / 1..n   */
+  int32_t valid;        /* valid_correspondence_found (:1412)                                                    */
+  int32_t best;         /* smallest_error_idx (:1419), -1 if none                                                */
+  int32_t reserved;
+  double squared_error; /* min_squared_error (:1418)                                                              */
+  double pose[16];      /* temp_solution.inverse() (:1437, :1449), column-major                                  */
+} pfmpe_p3p_check_result;
+int pfmpe_p3p_check(pfmpe_handle* h, int tracker, const double* image_points, int32_t n_image_points,
+                    const uint32_t* correspondences, const int32_t* counts, int32_t n_sets, double certainty_threshold,
+                    pfmpe_p3p_check_result* results);
+
 /* Batched P3P::computePoses (p3p.cpp:65-236), one problem per device thread -- what checkCorrespondences
  * (:1382) and P3P_short (:2506-) call per correspondence triple.  feature_vectors, world_points: n x 9,
  * each a column-major 3x3 (columns = the three unit bearing vectors / world points, Eigen::Matrix3d

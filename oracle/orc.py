@@ -109,6 +109,11 @@ def lib():
         L.orc_image_vectors.argtypes = [_dp, C.c_int, _dp, _dp]
         L.orc_p3p_histogram.restype = C.c_int
         L.orc_p3p_histogram.argtypes = [_dp, C.c_int, _dp, C.c_int, _dp, C.c_double, _up, C.POINTER(C.c_uint64)]
+        L.orc_combinations.restype = C.c_int
+        L.orc_combinations.argtypes = [C.c_uint, C.c_uint, _up, C.c_int]
+        L.orc_check_correspondences.restype = C.c_int
+        L.orc_check_correspondences.argtypes = [_dp, C.c_int, _dp, C.c_int, _dp, C.c_int, _up, C.c_double, C.c_double, _ip, _ip,
+                                                _ip, _dp, _dp]
         L.orc_p3p_histogram_mode.restype = C.c_int
         L.orc_p3p_histogram_mode.argtypes = [_dp, C.c_int, _dp, C.c_int, _dp, C.c_double, C.c_int, _up,
                                              C.POINTER(C.c_uint64)]
@@ -314,6 +319,29 @@ def p3p_histogram(K, markers, img, tol, dup_mode=0):
     lib().orc_p3p_histogram_mode(_d(_c64(K).reshape(9)), L, _d(ob), D, _d(im), float(tol), int(dup_mode),
                                  hist.ctypes.data_as(_up), st)
     return hist, tuple(int(x) for x in st)
+
+
+def combinations(n, k):
+    """Combinations::combinationsNoReplacement(n, k) (combinations.cpp:52-128): rows of 1-based indices."""
+    from math import comb
+    out = np.zeros((comb(n, k), k), dtype=np.uint32)
+    rows = lib().orc_combinations(n, k, out.ctypes.data_as(_up), out.shape[0])
+    return out[:rows]
+
+
+def check_correspondences(K, markers, img, corr, tol, certainty_threshold):
+    """Per-combination body of checkCorrespondences (pose_estimator.cpp:1340-1445) for one correspondence set
+    ((n, 2) 1-based (LED, detection) pairs): list of dicts (rc, valid, best, squared_error, pose)."""
+    im = _c64(img).reshape(-1, 2); ob = obj_h(np.asarray(markers)[:, :3])
+    c = np.ascontiguousarray(np.asarray(corr, dtype=np.uint32).reshape(-1, 2))
+    cap = 1024
+    rc = np.zeros(cap, dtype=np.int32); valid = np.zeros(cap, dtype=np.int32); best = np.zeros(cap, dtype=np.int32)
+    err = np.zeros(cap); pose = np.zeros((cap, 16))
+    nc = lib().orc_check_correspondences(_d(_c64(K).reshape(9)), ob.shape[0], _d(ob), im.shape[0], _d(im), c.shape[0],
+                                         c.ctypes.data_as(_up), float(tol), float(certainty_threshold),
+                                         rc.ctypes.data_as(_ip), valid.ctypes.data_as(_ip), best.ctypes.data_as(_ip), _d(err), _d(pose))
+    return [dict(rc=int(rc[i]), valid=int(valid[i]), best=int(best[i]), squared_error=float(err[i]), pose=from_colmajor(pose[i]))
+            for i in range(nc)]
 
 
 def weighted_mean_cov(T, w):

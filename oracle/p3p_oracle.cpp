@@ -343,3 +343,111 @@ int orc_p3p_histogram_mode(const double K[9], int L, const double *obj, int D, c
 }
 
 } /* extern "C" */
+
+extern "C" {
+
+/* Combinations::combinationsNoReplacement(N, K) (combinations.cpp:52-128), restated literally: rows of K 1-based
+ * indices.  out: capacity rows x K; returns the number of rows. */
+int orc_combinations(unsigned N, unsigned K, unsigned *out, int capacity)
+{
+  if (K == 1) { for (unsigned i = 0; i < N && (int)i < capacity; ++i) out[i] = i + 1; return (int)N; }
+  if (K == N) { for (unsigned j = 0; j < K; ++j) out[j] = j + 1; return 1; }
+  unsigned long long num = 1, den = 1;
+  for (unsigned v = N - K + 1; v <= N; ++v) num *= v;   /* consecutiveProduct(N-K+1, N) */
+  for (unsigned v = 1; v <= K; ++v) den *= v;           /* consecutiveProduct(1, K)     */
+  const unsigned bc = (unsigned)(num / den);
+  if ((int)bc > capacity) return -1;
+  std::vector<unsigned> wv(K);
+  for (unsigned j = 0; j < K; ++j) wv[j] = j + 1;
+  unsigned lim = K, idx = 1, step, flag;
+  for (unsigned j = 0; j < K; ++j) out[j] = wv[j];
+  for (unsigned i = 2; i + 1 <= bc; ++i) {
+    if (idx + lim < N) { step = idx; flag = 0; } else { step = 1; flag = 1; }
+    for (unsigned j = 1; j <= step; ++j) wv[K + j - idx - 1] = lim + j;
+    for (unsigned j = 0; j < K; ++j) out[(size_t)(i - 1) * K + j] = wv[j];
+    idx = idx * flag + 1;
+    lim = wv[K - idx];
+  }
+  for (unsigned j = 0; j < K; ++j) out[(size_t)(bc - 1) * K + j] = N - K + 1 + j;
+  return (int)bc;
+}
+
+/* calculateSquaredReprojectionErrorAndCertainty (pose_estimator.cpp:1087-1132): paired points, n each */
+double orc_sq_reprojection_error_and_certainty(int n, const double *image_pts, const double *object_pts, double tol,
+                                               double *certainty)
+{
+  std::vector<double> d(n > 0 ? n : 1);
+  for (int i = 0; i < n; ++i) d[i] = sqdist2(image_pts + 2 * i, object_pts + 2 * i);
+  double squared_error = 0;
+  unsigned num = 0;
+  const double tol2 = std::pow(tol, 2);
+  for (int j = 1; j <= n; ++j) {
+    int r = 0;   /* minCoeff: first minimum; a NaN entry never compares smaller */
+    for (int i = 1; i < n; ++i) if (d[i] < d[r]) r = i;
+    const double mv = d[r];
+    if (mv <= tol2) { squared_error += mv; num++; d[r] = std::numeric_limits<double>::infinity(); }
+    else break;
+  }
+  *certainty = (double)num / n;   /* 0/0 = NaN when there is no unused correspondence: never >= a threshold */
+  return squared_error;
+}
+
+/* The per-combination body of PoseEstimator::checkCorrespondences (pose_estimator.cpp:1340-1445) for one
+ * correspondence set.  corr: ncorr x 2 (LED, detection), 1-based.  Per combination c (reference order):
+ * valid[c] (a solution reached the certainty threshold, :1412), best[c] (its index, :1416-1420), err[c] (its squared
+ * error), pose[c] (16 doubles, column-major: temp_solution.inverse() -- the particle seeded at :1437 and the
+ * transform applied at :1449).  rc[c] is computePoses' return value.  Returns the number of combinations. */
+int orc_check_correspondences(const double K[9], int L, const double *obj, int D, const double *img, int ncorr,
+                              const unsigned *corr, double tol, double certainty_threshold, int *rc, int *valid,
+                              int *best, double *err, double *pose)
+{
+  if (ncorr < 3) return 0;
+  std::vector<double> vec(3 * (size_t)D);
+  orc_image_vectors(K, D, img, vec.data());
+  std::vector<unsigned> comb(3 * 1024);
+  const int nc = orc_combinations((unsigned)ncorr, 3, comb.data(), 1024);
+  for (int c = 0; c < nc; ++c) {
+    const unsigned *cc = &comb[3 * (size_t)c];
+    double fv[9], wp[9];
+    for (int k = 0; k < 3; ++k) {
+      const unsigned led = corr[2 * (cc[k] - 1)] - 1, det = corr[2 * (cc[k] - 1) + 1] - 1;
+      for (int r = 0; r < 3; ++r) { wp[3 * k + r] = obj[4 * led + r]; fv[3 * k + r] = vec[3 * det + r]; }
+    }
+    double un_obj[4 * 16], un_im[2 * 16];
+    int n_un = 0;
+    for (int l = 0; l < ncorr; ++l) {
+      if ((unsigned)l == cc[0] - 1 || (unsigned)l == cc[1] - 1 || (unsigned)l == cc[2] - 1) continue;
+      const unsigned led = corr[2 * l] - 1, det = corr[2 * l + 1] - 1;
+      for (int r = 0; r < 4; ++r) un_obj[4 * n_un + r] = obj[4 * led + r];
+      un_im[2 * n_un] = img[2 * det]; un_im[2 * n_un + 1] = img[2 * det + 1];
+      n_un++;
+    }
+    double sol[48];
+    rc[c] = compute_poses(fv, wp, sol);
+    valid[c] = 0; best[c] = -1; err[c] = std::numeric_limits<double>::infinity();
+    for (int e = 0; e < 16; ++e) pose[16 * (size_t)c + e] = 0;
+    if (rc[c] != 0) continue;
+    for (int j = 0; j < 4; ++j) {
+      double H[16];
+      for (int q = 0; q < 4; ++q) {
+        for (int r = 0; r < 3; ++r) H[4 * q + r] = sol[12 * j + 3 * q + r];
+        H[4 * q + 3] = (q == 3) ? 1.0 : 0.0;
+      }
+      bool finite = true;
+      for (int e = 0; e < 16; ++e) if (!((H[e] - H[e]) == (H[e] - H[e]))) finite = false;
+      if (!finite) continue;
+      double Hinv[16], proj[2 * 16];
+      orc_mat4_inv(H, Hinv);
+      for (int m = 0; m < n_un; ++m) orc_project2d(K, Hinv, un_obj + 4 * m, proj + 2 * m);
+      double certainty;
+      const double se = orc_sq_reprojection_error_and_certainty(n_un, un_im, proj, tol, &certainty);
+      if (certainty >= certainty_threshold) {
+        valid[c] = 1;
+        if (se < err[c]) { err[c] = se; best[c] = j; for (int e = 0; e < 16; ++e) pose[16 * (size_t)c + e] = Hinv[e]; }
+      }
+    }
+  }
+  return nc;
+}
+
+} /* extern "C" */

@@ -25,7 +25,7 @@ EXPORTS = [
     "pfmpe_optimise_pose", "pfmpe_predict_pose", "pfmpe_exponential_map", "pfmpe_logarithm_map",
     "pfmpe_track_init", "pfmpe_track_upload", "pfmpe_track_attach", "pfmpe_track_run", "pfmpe_track_replay", "pfmpe_track_results",
     "pfmpe_track_frame_host", "pfmpe_track_frame_host_batch", "pfmpe_track_sequence_host",
-    "pfmpe_predict_roi", "pfmpe_p3p_histogram", "pfmpe_p3p_histogram_dev", "pfmpe_p3p_solve",
+    "pfmpe_predict_roi", "pfmpe_p3p_histogram", "pfmpe_p3p_histogram_dev", "pfmpe_p3p_solve", "pfmpe_p3p_check",
     "pfmpe_shard_configure", "pfmpe_shard_begin_frame", "pfmpe_shard_score", "pfmpe_shard_resample",
     "pfmpe_shard_export", "pfmpe_shard_keep", "pfmpe_shard_import", "pfmpe_shard_winner",
     "pfmpe_shard_mail_create", "pfmpe_shard_mail_set_peers", "pfmpe_shard_collect", "pfmpe_shard_advance",
@@ -75,6 +75,14 @@ class FrameOut(C.Structure):
 class P3pStats(C.Structure):
     _fields_ = [("triples", C.c_uint64), ("p3p_solved", C.c_uint64), ("solutions_projected", C.c_uint64),
                 ("solutions_voted", C.c_uint64), ("device_ms", C.c_float), ("reserved", C.c_int32)]
+
+
+class P3pCheckResult(C.Structure):
+    _fields_ = [("rc", C.c_int32), ("valid", C.c_int32), ("best", C.c_int32), ("reserved", C.c_int32),
+                ("squared_error", C.c_double), ("pose", C.c_double * 16)]
+
+
+P3P_CHECK_STRIDE = 56
 
 
 class TrackResult(C.Structure):
@@ -134,6 +142,8 @@ def lib():
         L.pfmpe_p3p_histogram_dev.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int32, C.POINTER(C.c_uint32),
                                               C.POINTER(P3pStats)]
         L.pfmpe_p3p_solve.argtypes = [C.c_void_p, C.c_int32, _dp, _dp, _dp, C.POINTER(C.c_int32)]
+        L.pfmpe_p3p_check.argtypes = [C.c_void_p, C.c_int, _dp, C.c_int32, C.POINTER(C.c_uint32), C.POINTER(C.c_int32), C.c_int32,
+                                      C.c_double, C.POINTER(P3pCheckResult)]
         _i3 = C.POINTER(C.c_int64)
         L.pfmpe_shard_configure.argtypes = [C.c_void_p, C.c_int64, C.c_int64]
         L.pfmpe_shard_begin_frame.argtypes = [C.c_void_p, C.POINTER(FrameIn)]
@@ -374,6 +384,27 @@ class Handle:
         return hist, dict(triples=int(st.triples), p3p_solved=int(st.p3p_solved),
                           solutions_projected=int(st.solutions_projected), solutions_voted=int(st.solutions_voted),
                           device_ms=float(st.device_ms))
+
+    def p3p_check(self, image_points, correspondence_sets, certainty_threshold, tracker=0):
+        """Per-combination body of checkCorrespondences (pose_estimator.cpp:1340-1445) for a list of correspondence
+        sets (each an (n, 2) array of 1-based (LED, detection) pairs).  Returns, per set, a list of dicts
+        (rc, valid, best, squared_error, pose (4, 4)) in the reference's combination order."""
+        im = _c64(image_points).reshape(-1, 2)
+        M = len(correspondence_sets)
+        corr = np.zeros((M, 16), dtype=np.uint32); cnt = np.zeros(M, dtype=np.int32)
+        for i, c in enumerate(correspondence_sets):
+            c = np.asarray(c, dtype=np.uint32).reshape(-1, 2)
+            cnt[i] = c.shape[0]
+            corr[i, :2 * c.shape[0]] = c.reshape(-1)
+        res = (P3pCheckResult * (M * P3P_CHECK_STRIDE))()
+        self._chk(lib().pfmpe_p3p_check(self._h, tracker, _d(im), im.shape[0], corr.ctypes.data_as(C.POINTER(C.c_uint32)),
+                                        cnt.ctypes.data_as(C.POINTER(C.c_int32)), M, float(certainty_threshold), res))
+        out = []
+        for i in range(M):
+            n = int(cnt[i]); nc = n * (n - 1) * (n - 2) // 6 if n >= 3 else 0
+            out.append([dict(rc=r.rc, valid=r.valid, best=r.best, squared_error=r.squared_error,
+                             pose=from_colmajor(np.array(r.pose[:]))) for r in res[i * P3P_CHECK_STRIDE:i * P3P_CHECK_STRIDE + nc]])
+        return out
 
     def p3p_solve(self, feature_vectors, world_points):
         """Batched P3P::computePoses (p3p.cpp:65-236).  feature_vectors, world_points: (n, 3, 3) with the three

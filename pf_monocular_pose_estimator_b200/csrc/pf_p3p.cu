@@ -254,6 +254,106 @@ __global__ void __launch_bounds__(PF_P3P_BLOCK) pf_p3p_solve_kernel(int n, const
   }
 }
 
+__device__ __forceinline__ double pf_sqd2(double ax, double ay, double bx, double by)
+{
+  const double dx = ax - bx, dy = ay - by;
+  return dx * dx + dy * dy;
+}
+
+// ---- checkCorrespondences (pose_estimator.cpp:1312-1501): the per-combination body, batched ----------------------
+// One thread per (correspondence set, combination of three of its pairs): P3P on the three, back-projection of the
+// other pairs' LEDs, calculateSquaredReprojectionErrorAndCertainty (:1087-1132) against their detections, selection
+// of the best solution that reaches the certainty threshold (:1412-1420) and its inverse -- the pose the reference
+// seeds a particle with (:1437) and averages the marker positions through (:1449).
+__global__ void __launch_bounds__(PF_P3P_BLOCK) pf_p3p_check_kernel(pf_p3p_params p, int M, const unsigned* corr, const int* counts,
+                                                                    double certainty_threshold, pf_p3p_check_rec* out)
+{
+  const int gid = blockIdx.x * PF_P3P_BLOCK + threadIdx.x;
+  const int m = gid / PF_P3P_CHECK_STRIDE, c = gid % PF_P3P_CHECK_STRIDE;
+  if (m >= M) return;
+  const int n = counts[m];
+  if (n < 3 || n > PF_P3P_MAX_L || c >= n * (n - 1) * (n - 2) / 6) return;
+  // lexicographic unranking of (a < b < g) out of n (Combinations::combinationsNoReplacement's order)
+  int a = 0, rem = c;
+  while (rem >= (n - 1 - a) * (n - 2 - a) / 2) { rem -= (n - 1 - a) * (n - 2 - a) / 2; ++a; }
+  int b = a + 1;
+  while (rem >= n - 1 - b) { rem -= n - 1 - b; ++b; }
+  const int g = b + 1 + rem;
+  const unsigned* row = corr + (size_t)m * 2 * PF_P3P_MAX_L;
+  pf_p3p_check_rec R;
+  R.rc = 0; R.valid = 0; R.best = -1; R.reserved = 0; R.squared_error = INFINITY;
+#pragma unroll
+  for (int e = 0; e < 16; ++e) R.pose[e] = 0.0;
+  bool bad = false;
+  for (int l = 0; l < n; ++l) bad |= row[2 * l] < 1u || row[2 * l] > (unsigned)p.L || row[2 * l + 1] < 1u || row[2 * l + 1] > (unsigned)p.D;
+  if (bad) { R.rc = -2; out[(size_t)m * PF_P3P_CHECK_STRIDE + c] = R; return; }
+  const int tri[3] = {a, b, g};
+  pf_d3 f[3], P[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const int led = (int)row[2 * tri[k]] - 1, det = (int)row[2 * tri[k] + 1] - 1;
+    P[k] = pf_d3m(p.obj[3 * led], p.obj[3 * led + 1], p.obj[3 * led + 2]);
+    pf_d3 v = pf_d3m((p.img[2 * det] - p.K[2]) / p.K[0], (p.img[2 * det + 1] - p.K[5]) / p.K[4], 1.0);   // :1072-1085
+    f[k] = pf_d3_divs(v, pf_d3_norm(v));
+  }
+  if (pf_p3p_colinear(P[0], P[1], P[2])) { R.rc = -1; out[(size_t)m * PF_P3P_CHECK_STRIDE + c] = R; return; }
+  pf_p3p_cam Cc;
+  pf_p3p_world W;
+  pf_p3p_cam_frame(f[0], f[1], f[2], Cc);
+  if (Cc.swapped) pf_p3p_world_frame(P[1], P[0], P[2], W); else pf_p3p_world_frame(P[0], P[1], P[2], W);
+  double roots[4];
+  pf_p3p_roots(Cc, W, roots);
+  const double tol2 = p.tol * p.tol;
+#pragma unroll 1
+  for (int j = 0; j < 4; ++j) {
+    double S[12];
+    pf_p3p_backsub(Cc, W, j == 0 ? roots[0] : j == 1 ? roots[1] : j == 2 ? roots[2] : roots[3], S);
+    bool finite = true;
+#pragma unroll
+    for (int e = 0; e < 12; ++e) finite &= ((S[e] - S[e]) == (S[e] - S[e]));
+    if (!finite) continue;
+    const double a00 = S[0], a10 = S[1], a20 = S[2], a01 = S[3], a11 = S[4], a21 = S[5], a02 = S[6], a12 = S[7], a22 = S[8];
+    const double c00 = a11 * a22 - a12 * a21, c01 = a12 * a20 - a10 * a22, c02 = a10 * a21 - a11 * a20;
+    const double det = a00 * c00 + a01 * c01 + a02 * c02;
+    const double i00 = c00 / det, i01 = (a02 * a21 - a01 * a22) / det, i02 = (a01 * a12 - a02 * a11) / det;
+    const double i10 = c01 / det, i11 = (a00 * a22 - a02 * a20) / det, i12 = (a02 * a10 - a00 * a12) / det;
+    const double i20 = c02 / det, i21 = (a01 * a20 - a00 * a21) / det, i22 = (a00 * a11 - a01 * a10) / det;
+    const double t0 = -(i00 * S[9] + i01 * S[10] + i02 * S[11]), t1 = -(i10 * S[9] + i11 * S[10] + i12 * S[11]),
+                 t2 = -(i20 * S[9] + i21 * S[10] + i22 * S[11]);
+    double d[PF_P3P_MAX_L];
+    int n_un = 0;
+    for (int l = 0; l < n; ++l) {
+      if (l == a || l == b || l == g) continue;
+      const int led = (int)row[2 * l] - 1, dt = (int)row[2 * l + 1] - 1;
+      const double X = p.obj[3 * led], Y = p.obj[3 * led + 1], Z = p.obj[3 * led + 2];
+      const double xc = i00 * X + i01 * Y + i02 * Z + t0, yc = i10 * X + i11 * Y + i12 * Z + t1, zc = i20 * X + i21 * Y + i22 * Z + t2;
+      const double q0 = p.K[0] * xc + p.K[1] * yc + p.K[2] * zc, q1 = p.K[3] * xc + p.K[4] * yc + p.K[5] * zc,
+                   q2 = p.K[6] * xc + p.K[7] * yc + p.K[8] * zc;
+      d[n_un++] = pf_sqd2(p.img[2 * dt], p.img[2 * dt + 1], q0 / q2, q1 / q2);
+    }
+    double se = 0.0;
+    int num = 0;
+    for (int r = 0; r < n_un; ++r) {   // minCoeff / set to INF until the minimum exceeds tol^2 (:1112-1126)
+      int best = 0;
+      for (int i = 1; i < n_un; ++i) if (d[i] < d[best]) best = i;
+      if (!(d[best] <= tol2)) break;
+      se += d[best]; ++num; d[best] = INFINITY;
+    }
+    const double certainty = (double)num / (double)n_un;   // 0/0 = NaN without unused pairs: never reaches a threshold
+    if (certainty >= certainty_threshold) {
+      R.valid = 1;
+      if (se < R.squared_error) {
+        R.squared_error = se; R.best = j;
+        R.pose[0] = i00; R.pose[1] = i10; R.pose[2] = i20; R.pose[3] = 0.0;
+        R.pose[4] = i01; R.pose[5] = i11; R.pose[6] = i21; R.pose[7] = 0.0;
+        R.pose[8] = i02; R.pose[9] = i12; R.pose[10] = i22; R.pose[11] = 0.0;
+        R.pose[12] = t0; R.pose[13] = t1; R.pose[14] = t2; R.pose[15] = 1.0;
+      }
+    }
+  }
+  out[(size_t)m * PF_P3P_CHECK_STRIDE + c] = R;
+}
+
 // LED permutation number -> (j0, j1, j2), all different, lexicographic in (j0, j1, j2)
 __device__ __forceinline__ void pf_p3p_perm(int pr, int L, int& j0, int& j1, int& j2)
 {
@@ -301,12 +401,6 @@ __global__ void pf_p3p_prep_kernel(pf_p3p_params p)
   }
   for (int i = gtid; i < p.D * p.L; i += gsz) p.hist[i] = 0u;
   if (gtid < 4) p.stats[gtid] = 0ull;
-}
-
-__device__ __forceinline__ double pf_sqd2(double ax, double ay, double bx, double by)
-{
-  const double dx = ax - bx, dy = ay - by;
-  return dx * dx + dy * dy;
 }
 
 // number of triples whose first element is < a, out of D elements: C(D,3) - C(D-a,3)
@@ -526,6 +620,15 @@ cudaError_t pf_p3p_launch_hist(const pf_p3p_params& p, cudaStream_t stream)
   const long long threads = triples * p.nchunk;
   pf_p3p_prep_kernel<<<(p.D + 127) / 128 + 2, 128, 0, stream>>>(p);
   kern<<<(unsigned)((threads + PF_P3P_BLOCK - 1) / PF_P3P_BLOCK), PF_P3P_BLOCK, smem, stream>>>(p);
+  return cudaGetLastError();
+}
+
+cudaError_t pf_p3p_launch_check(const pf_p3p_params& p, int M, const unsigned* corr, const int* counts, double certainty_threshold,
+                                pf_p3p_check_rec* out, cudaStream_t stream)
+{
+  const long long threads = (long long)M * PF_P3P_CHECK_STRIDE;
+  pf_p3p_check_kernel<<<(unsigned)((threads + PF_P3P_BLOCK - 1) / PF_P3P_BLOCK), PF_P3P_BLOCK, 0, stream>>>(p, M, corr, counts,
+                                                                                                        certainty_threshold, out);
   return cudaGetLastError();
 }
 

@@ -1312,6 +1312,51 @@ int pfmpe_p3p_histogram_dev(pfmpe_handle* h, int tracker, const double* d_image_
   return p3p_histogram_impl(h, tracker, d_image_points, true, n_image_points, hist, stats);
 }
 
+int pfmpe_p3p_check(pfmpe_handle* h, int tracker, const double* image_points, int32_t D, const uint32_t* correspondences,
+                    const int32_t* counts, int32_t M, double certainty_threshold, pfmpe_p3p_check_result* results)
+{
+  static_assert(sizeof(pfmpe_p3p_check_result) == sizeof(pf_p3p_check_rec) && PFMPE_P3P_CHECK_STRIDE == PF_P3P_CHECK_STRIDE,
+                "ABI record and kernel record must agree");
+  if (!h || !image_points || !correspondences || !counts || !results) return PFMPE_ERR_INVALID;
+  if (tracker < 0 || tracker >= h->cfg.n_trackers) return fail(h, PFMPE_ERR_INVALID, "tracker out of range");
+  int rc = check_ready(h);
+  if (rc) return rc;
+  const int L = h->cfg.n_leds;
+  if (L < 3) return fail(h, PFMPE_ERR_UNSUPPORTED, "P3P needs at least 3 LEDs");
+  if (D < 3 || D > PF_P3P_MAX_D || M < 0 || M > (1 << 22)) return fail(h, PFMPE_ERR_INVALID, "n_image_points must be 3..1024, n_sets 0..2^22");
+  if (M == 0) return PFMPE_OK;
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  // scratch: img 2D doubles | results M*56 records | corr M*16 u32 | counts M i32
+  const size_t rec_bytes = (size_t)M * PF_P3P_CHECK_STRIDE * sizeof(pf_p3p_check_rec);
+  const size_t need = (size_t)D * 16 + rec_bytes + (size_t)M * (2 * PF_P3P_MAX_L * 4 + 4);
+  if (need > h->p3p_io_bytes) {
+    PF_CUDA(h, cudaStreamSynchronize(h->stream));
+    cudaFree(h->p3p_io); h->p3p_io = nullptr; h->p3p_io_bytes = 0;
+    PF_CUDA(h, cudaMalloc((void**)&h->p3p_io, need));
+    h->p3p_io_bytes = need;
+  }
+  double* d_img = h->p3p_io;
+  pf_p3p_check_rec* d_rec = reinterpret_cast<pf_p3p_check_rec*>(d_img + 2 * (size_t)D);
+  unsigned* d_corr = reinterpret_cast<unsigned*>(reinterpret_cast<unsigned char*>(d_rec) + rec_bytes);
+  int* d_cnt = reinterpret_cast<int*>(d_corr + (size_t)M * 2 * PF_P3P_MAX_L);
+  pf_p3p_params p;
+  std::memset(&p, 0, sizeof p);
+  p.D = D; p.L = L;
+  for (int i = 0; i < 9; ++i) p.K[i] = h->K[i];
+  for (int i = 0; i < 3 * L; ++i) p.obj[i] = h->markers[(size_t)tracker * PF_MAX_LED * 3 + i];
+  p.tol = h->prm.back_projection_pixel_tolerance;
+  p.img = d_img;
+  PF_CUDA(h, cudaMemcpyAsync(d_img, image_points, (size_t)D * 16, cudaMemcpyHostToDevice, h->stream));
+  PF_CUDA(h, cudaMemcpyAsync(d_corr, correspondences, (size_t)M * 2 * PF_P3P_MAX_L * 4, cudaMemcpyHostToDevice, h->stream));
+  PF_CUDA(h, cudaMemcpyAsync(d_cnt, counts, (size_t)M * 4, cudaMemcpyHostToDevice, h->stream));
+  PF_CUDA(h, cudaMemsetAsync(d_rec, 0, rec_bytes, h->stream));
+  PF_CUDA(h, pf_p3p_launch_check(p, M, d_corr, d_cnt, certainty_threshold, d_rec, h->stream));
+  h->launches += 1;
+  PF_CUDA(h, cudaMemcpyAsync(results, d_rec, rec_bytes, cudaMemcpyDeviceToHost, h->stream));
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  return PFMPE_OK;
+}
+
 int pfmpe_p3p_solve(pfmpe_handle* h, int32_t n, const double* feature_vectors, const double* world_points,
                     double* solutions, int32_t* rc_out)
 {

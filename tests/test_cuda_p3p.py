@@ -177,3 +177,33 @@ def test_vote_eight_leds_and_large_shared_memory():
     assert st["triples"] == 2 * comb(6, 3) and st["p3p_solved"] == 2 * comb(6, 3) * 336
     assert hist[np.isin(perm, np.arange(990))].sum() == 0      # lattice points never vote or get voted for
     h.close()
+
+
+def test_check_correspondences_matches_oracle():
+    """pfmpe_p3p_check (checkCorrespondences' per-combination body, :1340-1445) against the oracle for a batch of
+    candidate sets: the true pairing, pairings with swapped / outlier detections, shorter sets, an invalid index."""
+    h = _handle()
+    sc, img, true_blob = vote_scene(10)
+    true = np.array([[j + 1, true_blob[j] + 1] for j in range(5)])
+    rng = np.random.default_rng(4)
+    sets = [true, true[:4], true[:3], true[[4, 2, 0, 1, 3]]]
+    for _ in range(40):
+        c = true.copy()
+        k = rng.integers(1, 3)
+        c[rng.choice(5, k, replace=False), 1] = rng.integers(1, img.shape[0] + 1, k)
+        sets.append(c[: rng.integers(4, 6)])
+    got = h.p3p_check(img, sets, 0.75)
+    n_valid = 0
+    for s, g in zip(sets, got):
+        want = orc.check_correspondences(sc.K, sc.markers, img, s, 5.0, 0.75)
+        assert len(g) == len(want)
+        for a, b in zip(g, want):
+            assert a["rc"] == b["rc"] and a["valid"] == b["valid"] and a["best"] == b["best"], (s, a, b)
+            if b["valid"] and b["best"] >= 0:
+                n_valid += 1
+                assert abs(a["squared_error"] - b["squared_error"]) <= 1e-7 * max(1.0, b["squared_error"])
+                np.testing.assert_allclose(a["pose"], b["pose"], rtol=0, atol=1e-8)
+    assert n_valid >= 10 + 4
+    bad = true.copy(); bad[2, 0] = 9
+    assert all(r["rc"] == -2 for r in h.p3p_check(img, [bad], 0.75)[0])
+    h.close()

@@ -122,3 +122,30 @@ def test_vote_golden_fixture():
         np.testing.assert_array_equal(img, np.array(case["image_points"]))
         hist, st = orc.p3p_histogram(sc.K, sc.markers, img, g["tol"])
         assert hist.tolist() == case["hist"] and list(st) == case["stats"]
+
+
+def test_combinations_follow_the_reference_order():
+    """Combinations::combinationsNoReplacement restated literally (combinations.cpp:60-128) = lexicographic order."""
+    from itertools import combinations
+    for n in (3, 4, 5, 6, 8):
+        assert orc.combinations(n, 3).tolist() == [list(c) for c in combinations(range(1, n + 1), 3)]
+    assert orc.combinations(5, 1).reshape(-1).tolist() == [1, 2, 3, 4, 5]
+
+
+def test_check_correspondences_accepts_the_true_pairing_only():
+    sc, img, true_blob = vote_scene(10)
+    corr = np.array([[j + 1, true_blob[j] + 1] for j in range(5)])
+    r = orc.check_correspondences(sc.K, sc.markers, img, corr, 5.0, 0.75)
+    assert len(r) == 10 and all(x["rc"] == 0 and x["valid"] == 1 and 0 <= x["best"] < 4 for x in r)
+    dev = [np.abs(x["pose"] - sc.pose(7)).max() for x in r]   # the selected solution is the object's pose, up to what
+    assert np.median(dev) < 0.03 and max(dev) < 0.2           # 0.3 px of blob noise does to a three-point pose
+    assert all(x["squared_error"] <= 2 * 5.0 ** 2 for x in r)
+    swapped = corr.copy()
+    swapped[[0, 1], 1] = swapped[[1, 0], 1]
+    assert not any(x["valid"] for x in orc.check_correspondences(sc.K, sc.markers, img, swapped, 5.0, 0.75))
+    # three pairs: nothing is left to verify with, the certainty is 0/0 and never reaches a threshold (:1131, :1412)
+    r3 = orc.check_correspondences(sc.K, sc.markers, img, corr[:3], 5.0, 0.75)
+    assert len(r3) == 1 and r3[0]["valid"] == 0
+    # four pairs, certainty threshold 1: the single unused pair must reproject within the tolerance
+    r4 = orc.check_correspondences(sc.K, sc.markers, img, corr[:4], 5.0, 1.0)
+    assert len(r4) == 4 and all(x["valid"] for x in r4)
