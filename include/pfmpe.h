@@ -152,6 +152,11 @@ int pfmpe_logarithm_map(const double pose[16], double twist[6]);    /* :2228-229
  * every particle = pose1 (:106-109,:190-191). */
 int pfmpe_track_init(pfmpe_handle* h, int tracker, const double pose0[16], double t0, const double pose1[16],
                      double t1);
+/* The same for a filter whose particles were seeded individually (pfmpe_set_particles first): what initialise() +
+ * optimiseAndUpdatePose leave behind at :166-186 -- previous_pose_ / current_pose_ and their times,
+ * it_since_initialized_ (1 right after an initialisation), PoseParticle = newPoseEstimation = the P3P seeds. */
+int pfmpe_track_set_state(pfmpe_handle* h, int tracker, const double previous_pose[16], double previous_time,
+                          const double current_pose[16], double current_time, uint32_t it_since_initialized);
 /* Upload a sequence: image_points [n_trackers][n_frames][max_blobs][2], counts [n_trackers][n_frames],
  * times [n_frames] (time_to_predict per frame), seeds [n_trackers][n_frames]. */
 int pfmpe_track_upload(pfmpe_handle* h, int n_frames, const double* image_points, const int32_t* counts,

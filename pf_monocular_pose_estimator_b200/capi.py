@@ -23,7 +23,7 @@ EXPORTS = [
     "pfmpe_update", "pfmpe_update_batch",
     "pfmpe_get_particles", "pfmpe_get_weights", "pfmpe_get_resample_indices", "pfmpe_get_resample_counts",
     "pfmpe_optimise_pose", "pfmpe_predict_pose", "pfmpe_exponential_map", "pfmpe_logarithm_map",
-    "pfmpe_track_init", "pfmpe_track_upload", "pfmpe_track_attach", "pfmpe_track_run", "pfmpe_track_replay", "pfmpe_track_results",
+    "pfmpe_track_init", "pfmpe_track_set_state", "pfmpe_track_upload", "pfmpe_track_attach", "pfmpe_track_run", "pfmpe_track_replay", "pfmpe_track_results",
     "pfmpe_track_frame_host", "pfmpe_track_frame_host_batch", "pfmpe_track_sequence_host",
     "pfmpe_predict_roi", "pfmpe_p3p_histogram", "pfmpe_p3p_histogram_dev", "pfmpe_p3p_solve", "pfmpe_p3p_check",
     "pfmpe_shard_configure", "pfmpe_shard_begin_frame", "pfmpe_shard_score", "pfmpe_shard_resample",
@@ -127,6 +127,7 @@ def lib():
         L.pfmpe_exponential_map.argtypes = [_dp, _dp]
         L.pfmpe_logarithm_map.argtypes = [_dp, _dp]
         L.pfmpe_track_init.argtypes = [C.c_void_p, C.c_int, _dp, C.c_double, _dp, C.c_double]
+        L.pfmpe_track_set_state.argtypes = [C.c_void_p, C.c_int, _dp, C.c_double, _dp, C.c_double, C.c_uint32]
         L.pfmpe_track_upload.argtypes = [C.c_void_p, C.c_int, _dp, C.POINTER(C.c_int32), _dp, C.POINTER(C.c_uint32)]
         L.pfmpe_track_attach.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.pfmpe_track_run.argtypes = [C.c_void_p, C.c_int, C.c_int]
@@ -333,6 +334,11 @@ class Handle:
     def track_init(self, pose0, t0, pose1, t1, tracker=0):
         a, b = colmajor(pose0), colmajor(pose1)
         self._chk(lib().pfmpe_track_init(self._h, tracker, _d(a), t0, _d(b), t1))
+
+    def track_set_state(self, prev_pose, t_prev, cur_pose, t_cur, isi, tracker=0):
+        """previous_pose_ / current_pose_ / it_since_initialized_ of a filter seeded with set_particles (:166-186)."""
+        self._chk(lib().pfmpe_track_set_state(self._h, tracker, _d(colmajor(prev_pose)), float(t_prev), _d(colmajor(cur_pose)),
+                                              float(t_cur), int(isi)))
 
     def track_upload(self, image_points, counts, times, seeds):
         ip = _c64(image_points)

@@ -944,6 +944,29 @@ int pfmpe_track_init(pfmpe_handle* h, int tracker, const double pose0[16], doubl
   return PFMPE_OK;
 }
 
+int pfmpe_track_set_state(pfmpe_handle* h, int tracker, const double previous_pose[16], double previous_time,
+                          const double current_pose[16], double current_time, uint32_t it_since_initialized)
+{
+  if (!h || !previous_pose || !current_pose) return PFMPE_ERR_INVALID;
+  if (tracker < 0 || tracker >= h->cfg.n_trackers) return fail(h, PFMPE_ERR_INVALID, "tracker out of range");
+  if (!h->particles_set[tracker]) return fail(h, PFMPE_ERR_STATE, "set_particles must precede track_set_state");
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  PF_CUDA(h, cudaMemcpy(h->h_state + tracker, h->state + tracker, sizeof(pf_tracker_state), cudaMemcpyDeviceToHost));
+  pf_tracker_state& s = h->h_state[tracker];
+  const pf_aff a0 = pf_aff_from_cm16(previous_pose), a1 = pf_aff_from_cm16(current_pose);
+  HostTrack& ht = h->host_trk[tracker];
+  ht.prev = a0; ht.cur = a1; ht.t_prev = previous_time; ht.t_cur = current_time; ht.isi = it_since_initialized; ht.valid = true;
+  for (int i = 0; i < 36; ++i) ht.cov[i] = 0.0;
+  for (int i = 0; i < 12; ++i) { s.prev[i] = a0.a[i]; s.cur[i] = a1.a[i]; s.pred[i] = a1.a[i]; }
+  s.t_prev = previous_time; s.t_cur = current_time; s.t_pred = current_time;
+  for (int i = 0; i < 36; ++i) s.cov[i] = 0.0;
+  s.isi = it_since_initialized; s.failed = 0; s.frames_done = 0;
+  PF_CUDA(h, cudaMemcpy(h->state + tracker, &s, sizeof s, cudaMemcpyHostToDevice));
+  h->seq.next_frame = -1;
+  return PFMPE_OK;
+}
+
 static int seq_release(pfmpe_handle* h)
 {
   if (h->seq.owned) { cudaFree(h->seq.blobs); cudaFree(h->seq.counts); cudaFree(h->seq.times); cudaFree(h->seq.seeds); }
