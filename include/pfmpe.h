@@ -253,8 +253,8 @@ int pfmpe_p3p_histogram_dev(pfmpe_handle* h, int tracker, const double* d_image_
  * certainty against their detections (calculateSquaredReprojectionErrorAndCertainty, :1087-1132, tolerance =
  * back_projection_pixel_tolerance), and the best solution that reaches certainty_threshold (:1412-1420).
  * correspondences: n_sets rows of 2*PFMPE_MAX_LED uint32 = pairs (LED, detection), 1-based; counts[s] = pairs in
- * row s (3..PFMPE_MAX_LED).  results: n_sets x PFMPE_P3P_CHECK_STRIDE records, record [s][c] for combination c
- * (those beyond C(counts[s], 3) are zeroed).  The caller counts the valid ones against
+ * row s (3..PFMPE_MAX_LED).  results: n_sets x stride records, record [s][c] for combination c (those beyond
+ * C(counts[s], 3) are zeroed); stride >= C(max counts, 3), at most PFMPE_P3P_CHECK_STRIDE = C(8, 3).  The caller counts the valid ones against
  * valid_correspondence_threshold_ (:1469), averages pose * object_points (:1447-1451) and seeds PoseParticle with
  * the poses (:1432-1438). */
 #define PFMPE_P3P_CHECK_STRIDE 56
@@ -267,8 +267,8 @@ typedef struct {
   double pose[16];      /* temp_solution.inverse() (:1437, :1449), column-major                                  */
 } pfmpe_p3p_check_result;
 int pfmpe_p3p_check(pfmpe_handle* h, int tracker, const double* image_points, int32_t n_image_points,
-                    const uint32_t* correspondences, const int32_t* counts, int32_t n_sets, double certainty_threshold,
-                    pfmpe_p3p_check_result* results);
+                    const uint32_t* correspondences, const int32_t* counts, int32_t n_sets, int32_t stride,
+                    double certainty_threshold, pfmpe_p3p_check_result* results);
 
 /* Batched P3P::computePoses (p3p.cpp:65-236), one problem per device thread -- what checkCorrespondences
  * (:1382) and P3P_short (:2506-) call per correspondence triple.  feature_vectors, world_points: n x 9,

@@ -247,10 +247,13 @@ class PoseEstimator {
     double sum = 0;
     for (size_t i = 0; i < v_prob_comb.size(); ++i) sum += v_prob_comb[i];
     for (size_t i = 0; i < v_prob_comb.size(); ++i) v_prob_comb[i] = v_prob_comb[i] / sum;
-    for (size_t bb = 0; bb < v_prob_comb.size(); ++bb) {
-      const size_t row_idx = (size_t)(std::max_element(v_prob_comb.begin(), v_prob_comb.end()) - v_prob_comb.begin());
-      v_prob_comb[row_idx] = 0;
-      const std::vector<int>& det = v_comb[row_idx];
+    // the reference picks max_element N times (first maximum wins, O(N^2)); a stable sort by descending probability
+    // visits the candidates in exactly that order
+    std::vector<size_t> order(v_prob_comb.size());
+    for (size_t i = 0; i < order.size(); ++i) order[i] = i;
+    std::stable_sort(order.begin(), order.end(), [&](size_t a, size_t b) { return v_prob_comb[a] > v_prob_comb[b]; });
+    for (size_t bb = 0; bb < order.size(); ++bb) {
+      const std::vector<int>& det = v_comb[order[bb]];
       if (bInitialisation && checkAmbiguity(det)) continue;         // occlusions are only allowed when re-initialising
       VectorXuPairs pairs;
       for (unsigned led = 0; led < numCols; ++led)
@@ -341,32 +344,40 @@ class PoseEstimator {
     if (all_zero) { setFlag(objectNumber, 12.f); return 0; }                               // :1780
     const std::vector<VectorXuPairs> correspondencesVector = correspondencesFromHistogram(hist_corr, D, L, true);
     if (correspondencesVector.empty()) setFlag(objectNumber, 11.f);                        // :1723
-    // device: the per-combination body of checkCorrespondences for every candidate set that is long enough
+    // checkCorrespondences for every candidate set (:1733-1751): the per-combination bodies run on the device, a chunk
+    // of candidate sets per call; the loop ends early once every particle is seeded (no later set can be accepted:
+    // :1741 needs NumberOfP3PEstimation < N_Particle), which only changes which failure flag is left behind
     const int M = (int)correspondencesVector.size();
-    std::vector<uint32_t> rows((size_t)M * 2 * PFMPE_MAX_LED, 0u);
-    std::vector<int32_t> counts(M, 0);
-    for (int s = 0; s < M; ++s) {
-      const VectorXuPairs& c = correspondencesVector[s];
-      counts[s] = (int32_t)c.size();
-      for (size_t i = 0; i < c.size() && i < PFMPE_MAX_LED; ++i) { rows[((size_t)s * PFMPE_MAX_LED + i) * 2] = c[i].first; rows[((size_t)s * PFMPE_MAX_LED + i) * 2 + 1] = c[i].second; }
-    }
-    std::vector<pfmpe_p3p_check_result> chk((size_t)M * PFMPE_P3P_CHECK_STRIDE);
+    const int stride = (int)(L * (L - 1) * (L - 2) / 6), chunk_sets = 16384;
     std::vector<double> pts(2 * (size_t)D);
     for (unsigned i = 0; i < D; ++i) { pts[2 * i] = image_points_[i][0]; pts[2 * i + 1] = image_points_[i][1]; }
-    if (M > 0 && !check(pfmpe_p3p_check(h_, objectNumber, pts.data(), (int32_t)D, rows.data(), counts.data(), M, certainty_threshold_, chk.data()))) {
-      setFlag(objectNumber, 13.f);
-      return 0;
-    }
     PoseParticle_.assign((size_t)N_Particle, identity());
     int foundSol = 0, NumberOfP3PEstimation = 1, firstMatch = 0;
     VectorXuPairs correspondences_optimisation;
     Matrix4d predicted_pose_optimisation = identity();
-    for (int s = 0; s < M; ++s) {                                                          // :1733-1751
-      correspondences_ = correspondencesVector[s];
-      if (checkCorrespondences(&chk[(size_t)s * PFMPE_P3P_CHECK_STRIDE], NumberOfP3PEstimation, objectNumber, (int)L) == 1 &&
-          NumberOfP3PEstimation < N_Particle) {
-        foundSol = 1;
-        if (firstMatch == 0) { firstMatch++; correspondences_optimisation = correspondences_; predicted_pose_optimisation = predicted_pose_; }
+    std::vector<uint32_t> rows;
+    std::vector<int32_t> counts;
+    std::vector<pfmpe_p3p_check_result> chk;
+    for (int s0 = 0; s0 < M && NumberOfP3PEstimation <= N_Particle; s0 += chunk_sets) {
+      const int m = std::min(chunk_sets, M - s0);
+      rows.assign((size_t)m * 2 * PFMPE_MAX_LED, 0u);
+      counts.assign(m, 0);
+      for (int s = 0; s < m; ++s) {
+        const VectorXuPairs& c = correspondencesVector[s0 + s];
+        counts[s] = (int32_t)c.size();
+        for (size_t i = 0; i < c.size() && i < PFMPE_MAX_LED; ++i) { rows[((size_t)s * PFMPE_MAX_LED + i) * 2] = c[i].first; rows[((size_t)s * PFMPE_MAX_LED + i) * 2 + 1] = c[i].second; }
+      }
+      chk.resize((size_t)m * stride);
+      if (!check(pfmpe_p3p_check(h_, objectNumber, pts.data(), (int32_t)D, rows.data(), counts.data(), m, stride, certainty_threshold_, chk.data()))) {
+        setFlag(objectNumber, 13.f);
+        return 0;
+      }
+      for (int s = 0; s < m && NumberOfP3PEstimation <= N_Particle; ++s) {
+        correspondences_ = correspondencesVector[s0 + s];
+        if (checkCorrespondences(&chk[(size_t)s * stride], NumberOfP3PEstimation, objectNumber, (int)L) == 1 && NumberOfP3PEstimation < N_Particle) {
+          foundSol = 1;
+          if (firstMatch == 0) { firstMatch++; correspondences_optimisation = correspondences_; predicted_pose_optimisation = predicted_pose_; }
+        }
       }
     }
     const int NumOfReasonableEstimations = NumberOfP3PEstimation - 1;                      // :1753-1758

@@ -144,7 +144,7 @@ def lib():
                                               C.POINTER(P3pStats)]
         L.pfmpe_p3p_solve.argtypes = [C.c_void_p, C.c_int32, _dp, _dp, _dp, C.POINTER(C.c_int32)]
         L.pfmpe_p3p_check.argtypes = [C.c_void_p, C.c_int, _dp, C.c_int32, C.POINTER(C.c_uint32), C.POINTER(C.c_int32), C.c_int32,
-                                      C.c_double, C.POINTER(P3pCheckResult)]
+                                      C.c_int32, C.c_double, C.POINTER(P3pCheckResult)]
         _i3 = C.POINTER(C.c_int64)
         L.pfmpe_shard_configure.argtypes = [C.c_void_p, C.c_int64, C.c_int64]
         L.pfmpe_shard_begin_frame.argtypes = [C.c_void_p, C.POINTER(FrameIn)]
@@ -402,14 +402,16 @@ class Handle:
             c = np.asarray(c, dtype=np.uint32).reshape(-1, 2)
             cnt[i] = c.shape[0]
             corr[i, :2 * c.shape[0]] = c.reshape(-1)
-        res = (P3pCheckResult * (M * P3P_CHECK_STRIDE))()
+        nmax = max(3, int(cnt.max())) if M else 3
+        stride = nmax * (nmax - 1) * (nmax - 2) // 6
+        res = (P3pCheckResult * (M * stride))()
         self._chk(lib().pfmpe_p3p_check(self._h, tracker, _d(im), im.shape[0], corr.ctypes.data_as(C.POINTER(C.c_uint32)),
-                                        cnt.ctypes.data_as(C.POINTER(C.c_int32)), M, float(certainty_threshold), res))
+                                        cnt.ctypes.data_as(C.POINTER(C.c_int32)), M, stride, float(certainty_threshold), res))
         out = []
         for i in range(M):
             n = int(cnt[i]); nc = n * (n - 1) * (n - 2) // 6 if n >= 3 else 0
             out.append([dict(rc=r.rc, valid=r.valid, best=r.best, squared_error=r.squared_error,
-                             pose=from_colmajor(np.array(r.pose[:]))) for r in res[i * P3P_CHECK_STRIDE:i * P3P_CHECK_STRIDE + nc]])
+                             pose=from_colmajor(np.array(r.pose[:]))) for r in res[i * stride:i * stride + nc]])
         return out
 
     def p3p_solve(self, feature_vectors, world_points):

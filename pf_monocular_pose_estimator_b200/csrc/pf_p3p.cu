@@ -265,14 +265,14 @@ __device__ __forceinline__ double pf_sqd2(double ax, double ay, double bx, doubl
 // other pairs' LEDs, calculateSquaredReprojectionErrorAndCertainty (:1087-1132) against their detections, selection
 // of the best solution that reaches the certainty threshold (:1412-1420) and its inverse -- the pose the reference
 // seeds a particle with (:1437) and averages the marker positions through (:1449).
-__global__ void __launch_bounds__(PF_P3P_BLOCK) pf_p3p_check_kernel(pf_p3p_params p, int M, const unsigned* corr, const int* counts,
-                                                                    double certainty_threshold, pf_p3p_check_rec* out)
+__global__ void __launch_bounds__(PF_P3P_BLOCK) pf_p3p_check_kernel(pf_p3p_params p, int M, int stride, const unsigned* corr,
+                                                                    const int* counts, double certainty_threshold, pf_p3p_check_rec* out)
 {
-  const int gid = blockIdx.x * PF_P3P_BLOCK + threadIdx.x;
-  const int m = gid / PF_P3P_CHECK_STRIDE, c = gid % PF_P3P_CHECK_STRIDE;
+  const long long gid = (long long)blockIdx.x * PF_P3P_BLOCK + threadIdx.x;
+  const int m = (int)(gid / stride), c = (int)(gid % stride);
   if (m >= M) return;
   const int n = counts[m];
-  if (n < 3 || n > PF_P3P_MAX_L || c >= n * (n - 1) * (n - 2) / 6) return;
+  if (n < 3 || n > PF_P3P_MAX_L || c >= n * (n - 1) * (n - 2) / 6) return;   // stride >= C(n, 3) is checked on the host
   // lexicographic unranking of (a < b < g) out of n (Combinations::combinationsNoReplacement's order)
   int a = 0, rem = c;
   while (rem >= (n - 1 - a) * (n - 2 - a) / 2) { rem -= (n - 1 - a) * (n - 2 - a) / 2; ++a; }
@@ -286,7 +286,7 @@ __global__ void __launch_bounds__(PF_P3P_BLOCK) pf_p3p_check_kernel(pf_p3p_param
   for (int e = 0; e < 16; ++e) R.pose[e] = 0.0;
   bool bad = false;
   for (int l = 0; l < n; ++l) bad |= row[2 * l] < 1u || row[2 * l] > (unsigned)p.L || row[2 * l + 1] < 1u || row[2 * l + 1] > (unsigned)p.D;
-  if (bad) { R.rc = -2; out[(size_t)m * PF_P3P_CHECK_STRIDE + c] = R; return; }
+  if (bad) { R.rc = -2; out[(size_t)m * stride + c] = R; return; }
   const int tri[3] = {a, b, g};
   pf_d3 f[3], P[3];
 #pragma unroll
@@ -296,7 +296,7 @@ __global__ void __launch_bounds__(PF_P3P_BLOCK) pf_p3p_check_kernel(pf_p3p_param
     pf_d3 v = pf_d3m((p.img[2 * det] - p.K[2]) / p.K[0], (p.img[2 * det + 1] - p.K[5]) / p.K[4], 1.0);   // :1072-1085
     f[k] = pf_d3_divs(v, pf_d3_norm(v));
   }
-  if (pf_p3p_colinear(P[0], P[1], P[2])) { R.rc = -1; out[(size_t)m * PF_P3P_CHECK_STRIDE + c] = R; return; }
+  if (pf_p3p_colinear(P[0], P[1], P[2])) { R.rc = -1; out[(size_t)m * stride + c] = R; return; }
   pf_p3p_cam Cc;
   pf_p3p_world W;
   pf_p3p_cam_frame(f[0], f[1], f[2], Cc);
@@ -351,7 +351,7 @@ __global__ void __launch_bounds__(PF_P3P_BLOCK) pf_p3p_check_kernel(pf_p3p_param
       }
     }
   }
-  out[(size_t)m * PF_P3P_CHECK_STRIDE + c] = R;
+  out[(size_t)m * stride + c] = R;
 }
 
 // LED permutation number -> (j0, j1, j2), all different, lexicographic in (j0, j1, j2)
@@ -623,11 +623,11 @@ cudaError_t pf_p3p_launch_hist(const pf_p3p_params& p, cudaStream_t stream)
   return cudaGetLastError();
 }
 
-cudaError_t pf_p3p_launch_check(const pf_p3p_params& p, int M, const unsigned* corr, const int* counts, double certainty_threshold,
-                                pf_p3p_check_rec* out, cudaStream_t stream)
+cudaError_t pf_p3p_launch_check(const pf_p3p_params& p, int M, int stride, const unsigned* corr, const int* counts,
+                                double certainty_threshold, pf_p3p_check_rec* out, cudaStream_t stream)
 {
-  const long long threads = (long long)M * PF_P3P_CHECK_STRIDE;
-  pf_p3p_check_kernel<<<(unsigned)((threads + PF_P3P_BLOCK - 1) / PF_P3P_BLOCK), PF_P3P_BLOCK, 0, stream>>>(p, M, corr, counts,
+  const long long threads = (long long)M * stride;
+  pf_p3p_check_kernel<<<(unsigned)((threads + PF_P3P_BLOCK - 1) / PF_P3P_BLOCK), PF_P3P_BLOCK, 0, stream>>>(p, M, stride, corr, counts,
                                                                                                         certainty_threshold, out);
   return cudaGetLastError();
 }

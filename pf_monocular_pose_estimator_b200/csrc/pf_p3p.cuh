@@ -45,7 +45,7 @@ struct pf_p3p_params {
   unsigned long long* stats;   // [4] triples passing the pre-filters, P3P solved, solutions projected, solutions voting
 };
 
-#define PF_P3P_CHECK_STRIDE 56   // C(8,3): result records per correspondence set
+#define PF_P3P_CHECK_STRIDE 56   // C(8,3): the largest number of result records a correspondence set can need
 // one (correspondence set, combination) of checkCorrespondences; same layout as pfmpe_p3p_check_result
 struct pf_p3p_check_rec {
   int rc, valid, best, reserved;
@@ -57,6 +57,6 @@ struct pf_p3p_check_rec {
 // contraction, and the duplicate-solution test of :1659-1663 compares doubles for exact equality)
 size_t pf_p3p_smem_bytes(int D, int L);
 cudaError_t pf_p3p_launch_hist(const pf_p3p_params& p, cudaStream_t stream);   // prologue + vote, 2 kernels
-cudaError_t pf_p3p_launch_check(const pf_p3p_params& p, int M, const unsigned* corr, const int* counts, double certainty_threshold,
-                                pf_p3p_check_rec* out, cudaStream_t stream);
+cudaError_t pf_p3p_launch_check(const pf_p3p_params& p, int M, int stride, const unsigned* corr, const int* counts,
+                                double certainty_threshold, pf_p3p_check_rec* out, cudaStream_t stream);
 cudaError_t pf_p3p_launch_solve(int n, const double* fv, const double* wp, double* sol, int* rc, cudaStream_t stream);

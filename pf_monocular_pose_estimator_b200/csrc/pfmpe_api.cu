@@ -1336,7 +1336,7 @@ int pfmpe_p3p_histogram_dev(pfmpe_handle* h, int tracker, const double* d_image_
 }
 
 int pfmpe_p3p_check(pfmpe_handle* h, int tracker, const double* image_points, int32_t D, const uint32_t* correspondences,
-                    const int32_t* counts, int32_t M, double certainty_threshold, pfmpe_p3p_check_result* results)
+                    const int32_t* counts, int32_t M, int32_t stride, double certainty_threshold, pfmpe_p3p_check_result* results)
 {
   static_assert(sizeof(pfmpe_p3p_check_result) == sizeof(pf_p3p_check_rec) && PFMPE_P3P_CHECK_STRIDE == PF_P3P_CHECK_STRIDE,
                 "ABI record and kernel record must agree");
@@ -1348,9 +1348,14 @@ int pfmpe_p3p_check(pfmpe_handle* h, int tracker, const double* image_points, in
   if (L < 3) return fail(h, PFMPE_ERR_UNSUPPORTED, "P3P needs at least 3 LEDs");
   if (D < 3 || D > PF_P3P_MAX_D || M < 0 || M > (1 << 22)) return fail(h, PFMPE_ERR_INVALID, "n_image_points must be 3..1024, n_sets 0..2^22");
   if (M == 0) return PFMPE_OK;
+  if (stride < 1 || stride > PF_P3P_CHECK_STRIDE) return fail(h, PFMPE_ERR_INVALID, "stride must be 1..56");
+  for (int s = 0; s < M; ++s) {
+    const int n = counts[s];
+    if (n >= 3 && n <= PF_P3P_MAX_L && n * (n - 1) * (n - 2) / 6 > stride) return fail(h, PFMPE_ERR_INVALID, "stride < C(counts[s], 3)");
+  }
   PF_CUDA(h, cudaSetDevice(h->cfg.device));
-  // scratch: img 2D doubles | results M*56 records | corr M*16 u32 | counts M i32
-  const size_t rec_bytes = (size_t)M * PF_P3P_CHECK_STRIDE * sizeof(pf_p3p_check_rec);
+  // scratch: img 2D doubles | results M*stride records | corr M*16 u32 | counts M i32
+  const size_t rec_bytes = (size_t)M * stride * sizeof(pf_p3p_check_rec);
   const size_t need = (size_t)D * 16 + rec_bytes + (size_t)M * (2 * PF_P3P_MAX_L * 4 + 4);
   if (need > h->p3p_io_bytes) {
     PF_CUDA(h, cudaStreamSynchronize(h->stream));
@@ -1373,7 +1378,7 @@ int pfmpe_p3p_check(pfmpe_handle* h, int tracker, const double* image_points, in
   PF_CUDA(h, cudaMemcpyAsync(d_corr, correspondences, (size_t)M * 2 * PF_P3P_MAX_L * 4, cudaMemcpyHostToDevice, h->stream));
   PF_CUDA(h, cudaMemcpyAsync(d_cnt, counts, (size_t)M * 4, cudaMemcpyHostToDevice, h->stream));
   PF_CUDA(h, cudaMemsetAsync(d_rec, 0, rec_bytes, h->stream));
-  PF_CUDA(h, pf_p3p_launch_check(p, M, d_corr, d_cnt, certainty_threshold, d_rec, h->stream));
+  PF_CUDA(h, pf_p3p_launch_check(p, M, stride, d_corr, d_cnt, certainty_threshold, d_rec, h->stream));
   h->launches += 1;
   PF_CUDA(h, cudaMemcpyAsync(results, d_rec, rec_bytes, cudaMemcpyDeviceToHost, h->stream));
   PF_CUDA(h, cudaStreamSynchronize(h->stream));
