@@ -134,7 +134,8 @@ int pfmpe_get_resample_indices(pfmpe_handle* h, int tracker, int32_t* idx /* n *
 int pfmpe_get_resample_counts(pfmpe_handle* h, int tracker, uint32_t* count /* n */);
 
 /* ---- host tail (FP64), used by the reference-side shim between two updates ----------------- */
-/* optimisePose (:1805-2009): pose in/out, cov 6x6; *iters = PubData.numIter or -1. */
+/* optimisePose (:1805-2009): pose in/out, cov 6x6; *iters = PubData.numIter or -1.  correspondences: pairs
+ * (LED, detection), 1-based; a pair outside 1..n_leds / 1..n_image_points is PFMPE_ERR_INVALID. */
 int pfmpe_optimise_pose(const double K[9], const double* markers_xyz, int n_leds, const double* image_points,
                         int n_image_points, const uint32_t* correspondences, int n_correspondences,
                         double pose[16], double cov[36], int* iters);
@@ -154,7 +155,9 @@ int pfmpe_track_init(pfmpe_handle* h, int tracker, const double pose0[16], doubl
                      double t1);
 /* The same for a filter whose particles were seeded individually (pfmpe_set_particles first): what initialise() +
  * optimiseAndUpdatePose leave behind at :166-186 -- previous_pose_ / current_pose_ and their times,
- * it_since_initialized_ (1 right after an initialisation), PoseParticle = newPoseEstimation = the P3P seeds. */
+ * it_since_initialized_ (1 right after an initialisation), PoseParticle = newPoseEstimation = the P3P seeds.
+ * previous_time == current_time is rejected (PFMPE_ERR_INVALID; also t0 == t1 in pfmpe_track_init): the next
+ * predictPose divides by their difference (:1002). */
 int pfmpe_track_set_state(pfmpe_handle* h, int tracker, const double previous_pose[16], double previous_time,
                           const double current_pose[16], double current_time, uint32_t it_since_initialized);
 /* Upload a sequence: image_points [n_trackers][n_frames][max_blobs][2], counts [n_trackers][n_frames],

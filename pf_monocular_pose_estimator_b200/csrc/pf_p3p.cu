@@ -131,7 +131,7 @@ __device__ __forceinline__ pf_d3 pf_d3_divs(pf_d3 a, double s) { return pf_d3m(a
 // parts from a table the prologue fills; the operations and their order are those of P3P::computePoses either way.
 struct pf_p3p_cam {
   pf_d3 e1, e2, e3;     // rows of T (intermediate camera frame)
-  double f_1, f_2, b;
+  double phi1, phi2, b;
   int swapped;          // :104-125 took the branch f3(2) > 0
 };
 
@@ -151,7 +151,7 @@ __device__ __forceinline__ void pf_p3p_cam_frame(pf_d3 f1, pf_d3 f2, pf_d3 f3in,
     Cc.swapped = 1;
   }
   Cc.e1 = e1; Cc.e2 = e2; Cc.e3 = e3;
-  Cc.f_1 = f3.x / f3.z; Cc.f_2 = f3.y / f3.z;
+  Cc.phi1 = f3.x / f3.z; Cc.phi2 = f3.y / f3.z;
   const double cos_beta = pf_d3_dot(f1, f2);
   const double b = 1 / (1 - cos_beta * cos_beta) - 1;
   Cc.b = cos_beta < 0 ? -sqrt(b) : sqrt(b);
@@ -173,42 +173,46 @@ __device__ __forceinline__ void pf_p3p_world_frame(pf_d3 P1, pf_d3 P2, pf_d3 P3,
   const pf_d3 n2 = pf_d3_cross(n3, n1);
   const pf_d3 d3 = pf_d3_sub(P3, P1);
   W.n1 = n1; W.n2 = n2; W.n3 = n3; W.P1 = P1;
-  W.p_1 = pf_d3_dot(n1, d3); W.p_2 = pf_d3_dot(n2, d3);
-  W.d_12 = pf_d3_norm(pf_d3_sub(P2, P1));
+  W.p1 = pf_d3_dot(n1, d3); W.p2 = pf_d3_dot(n2, d3);
+  W.d12 = pf_d3_norm(pf_d3_sub(P2, P1));
 }
 
-// coefficients of the quartic (:150-173) and its roots
+// Coefficients a[0..4] of Kneip's quartic in cos(theta) (Kneip, Scaramuzza, Siegwart, CVPR 2011, eq. 11: phi1, phi2 = the
+// third bearing vector's ratios, p1, p2 = the third world point in the intermediate world frame, d12 = |P2 - P1|,
+// b = cot(beta)) and its roots.  The terms are summed in the order of the published polynomial as the reference
+// evaluates it (p3p.cpp:150-173): FP64 addition is not associative and the duplicate test downstream compares doubles
+// for exact equality.
 __device__ __forceinline__ void pf_p3p_roots(const pf_p3p_cam& Cc, const pf_p3p_world& W, double roots[4])
 {
-  const double f_1 = Cc.f_1, f_2 = Cc.f_2, b = Cc.b, p_1 = W.p_1, p_2 = W.p_2, d_12 = W.d_12;
-  const double f_1_pw2 = f_1 * f_1, f_2_pw2 = f_2 * f_2, p_1_pw2 = p_1 * p_1, p_1_pw3 = p_1_pw2 * p_1,
-               p_1_pw4 = p_1_pw3 * p_1, p_2_pw2 = p_2 * p_2, p_2_pw3 = p_2_pw2 * p_2, p_2_pw4 = p_2_pw3 * p_2,
-               d_12_pw2 = d_12 * d_12, b_pw2 = b * b;
-  double fac[5];
-  fac[0] = -f_2_pw2 * p_2_pw4 - p_2_pw4 * f_1_pw2 - p_2_pw4;
-  fac[1] = 2 * p_2_pw3 * d_12 * b + 2 * f_2_pw2 * p_2_pw3 * d_12 * b - 2 * f_2 * p_2_pw3 * f_1 * d_12;
-  fac[2] = -f_2_pw2 * p_2_pw2 * p_1_pw2 - f_2_pw2 * p_2_pw2 * d_12_pw2 * b_pw2 - f_2_pw2 * p_2_pw2 * d_12_pw2 +
-           f_2_pw2 * p_2_pw4 + p_2_pw4 * f_1_pw2 + 2 * p_1 * p_2_pw2 * d_12 +
-           2 * f_1 * f_2 * p_1 * p_2_pw2 * d_12 * b - p_2_pw2 * p_1_pw2 * f_1_pw2 +
-           2 * p_1 * p_2_pw2 * f_2_pw2 * d_12 - p_2_pw2 * d_12_pw2 * b_pw2 - 2 * p_1_pw2 * p_2_pw2;
-  fac[3] = 2 * p_1_pw2 * p_2 * d_12 * b + 2 * f_2 * p_2_pw3 * f_1 * d_12 - 2 * f_2_pw2 * p_2_pw3 * d_12 * b -
-           2 * p_1 * p_2 * d_12_pw2 * b;
-  fac[4] = -2 * f_2 * p_2_pw2 * f_1 * p_1 * d_12 * b + f_2_pw2 * p_2_pw2 * d_12_pw2 + 2 * p_1_pw3 * d_12 -
-           p_1_pw2 * d_12_pw2 + f_2_pw2 * p_2_pw2 * p_1_pw2 - p_1_pw4 - 2 * f_2_pw2 * p_2_pw2 * p_1 * d_12 +
-           p_2_pw2 * f_1_pw2 * p_1_pw2 + f_2_pw2 * p_2_pw2 * d_12_pw2 * b_pw2;
-  pf_p3p_quartic(fac, roots);
+  const double phi1 = Cc.phi1, phi2 = Cc.phi2, b = Cc.b, p1 = W.p1, p2 = W.p2, d12 = W.d12;
+  const double phi1_sq = phi1 * phi1, phi2_sq = phi2 * phi2, p1_sq = p1 * p1, p1_cu = p1_sq * p1,
+               p1_qu = p1_cu * p1, p2_sq = p2 * p2, p2_cu = p2_sq * p2, p2_qu = p2_cu * p2,
+               d12_sq = d12 * d12, b_sq = b * b;
+  double a[5];
+  a[0] = -phi2_sq * p2_qu - p2_qu * phi1_sq - p2_qu;
+  a[1] = 2 * p2_cu * d12 * b + 2 * phi2_sq * p2_cu * d12 * b - 2 * phi2 * p2_cu * phi1 * d12;
+  a[2] = -phi2_sq * p2_sq * p1_sq - phi2_sq * p2_sq * d12_sq * b_sq - phi2_sq * p2_sq * d12_sq +
+           phi2_sq * p2_qu + p2_qu * phi1_sq + 2 * p1 * p2_sq * d12 +
+           2 * phi1 * phi2 * p1 * p2_sq * d12 * b - p2_sq * p1_sq * phi1_sq +
+           2 * p1 * p2_sq * phi2_sq * d12 - p2_sq * d12_sq * b_sq - 2 * p1_sq * p2_sq;
+  a[3] = 2 * p1_sq * p2 * d12 * b + 2 * phi2 * p2_cu * phi1 * d12 - 2 * phi2_sq * p2_cu * d12 * b -
+           2 * p1 * p2 * d12_sq * b;
+  a[4] = -2 * phi2 * p2_sq * phi1 * p1 * d12 * b + phi2_sq * p2_sq * d12_sq + 2 * p1_cu * d12 -
+           p1_sq * d12_sq + phi2_sq * p2_sq * p1_sq - p1_qu - 2 * phi2_sq * p2_sq * p1 * d12 +
+           p2_sq * phi1_sq * p1_sq + phi2_sq * p2_sq * d12_sq * b_sq;
+  pf_p3p_quartic(a, roots);
 }
 
 // Back-substitution of one root (p3p.cpp:181-233): S = [R | C] column-major 3x4, R = N^T R'^T T, C = P1 + N^T C'
 __device__ __forceinline__ void pf_p3p_backsub(const pf_p3p_cam& Cc, const pf_p3p_world& W, double r, double S[12])
 {
-  const double cot_alpha = (-Cc.f_1 * W.p_1 / Cc.f_2 - r * W.p_2 + W.d_12 * Cc.b) / (-Cc.f_1 * r * W.p_2 / Cc.f_2 + W.p_1 - W.d_12);
+  const double cot_alpha = (-Cc.phi1 * W.p1 / Cc.phi2 - r * W.p2 + W.d12 * Cc.b) / (-Cc.phi1 * r * W.p2 / Cc.phi2 + W.p1 - W.d12);
   const double cos_theta = r, sin_theta = sqrt(1 - r * r);
   const double sin_alpha = sqrt(1 / (cot_alpha * cot_alpha + 1));
   double cos_alpha = sqrt(1 - sin_alpha * sin_alpha);
   if (cot_alpha < 0) cos_alpha = -cos_alpha;
   const double k = sin_alpha * Cc.b + cos_alpha;
-  const double Cx = W.d_12 * cos_alpha * k, Cy = cos_theta * W.d_12 * sin_alpha * k, Cz = sin_theta * W.d_12 * sin_alpha * k;
+  const double Cx = W.d12 * cos_alpha * k, Cy = cos_theta * W.d12 * sin_alpha * k, Cz = sin_theta * W.d12 * sin_alpha * k;
   S[9] = W.P1.x + (W.n1.x * Cx + W.n2.x * Cy + W.n3.x * Cz);
   S[10] = W.P1.y + (W.n1.y * Cx + W.n2.y * Cy + W.n3.y * Cz);
   S[11] = W.P1.z + (W.n1.z * Cx + W.n2.z * Cy + W.n3.z * Cz);

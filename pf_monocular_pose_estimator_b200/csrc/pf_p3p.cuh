@@ -26,7 +26,7 @@ struct pf_p3p_d3 { double x, y, z; };
 struct pf_p3p_world {
   pf_p3p_d3 n1, n2, n3;   // rows of N
   pf_p3p_d3 P1;
-  double p_1, p_2, d_12;
+  double p1, p2, d12;
   double colinear;        // table entries only: != 0 when the three LEDs are colinear (:78-84), no solution
 };
 

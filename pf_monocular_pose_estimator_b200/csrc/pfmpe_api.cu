@@ -864,11 +864,12 @@ int pfmpe_optimise_pose(const double K[9], const double* markers_xyz, int n_leds
                         int n_image_points, const uint32_t* correspondences, int n_correspondences,
                         double pose[16], double cov[36], int* iters)
 {
-  if (!K || !markers_xyz || !pose || !cov || n_correspondences < 0 || (n_correspondences > 0 && (!correspondences || !image_points)))
+  if (!K || !markers_xyz || !pose || !cov || n_correspondences < 0 || n_image_points < 0 ||
+      (n_correspondences > 0 && (!correspondences || !image_points || n_image_points == 0)))
     return PFMPE_ERR_INVALID;
-  for (int i = 0; i < n_correspondences; ++i) {
-    if (correspondences[2 * i] < 1 || (int)correspondences[2 * i] > n_leds) return PFMPE_ERR_INVALID;
-    if ((int)correspondences[2 * i + 1] > n_image_points) return PFMPE_ERR_INVALID;
+  for (int i = 0; i < n_correspondences; ++i) {   // pairs are 1-based: LED in 1..n_leds, detection in 1..n_image_points
+    if (correspondences[2 * i] < 1 || correspondences[2 * i] > (unsigned)n_leds) return PFMPE_ERR_INVALID;
+    if (correspondences[2 * i + 1] < 1 || correspondences[2 * i + 1] > (unsigned)n_image_points) return PFMPE_ERR_INVALID;
   }
   pf_aff T = pf_aff_from_cm16(pose);
   double c[36];
@@ -912,6 +913,7 @@ int pfmpe_track_init(pfmpe_handle* h, int tracker, const double pose0[16], doubl
 {
   if (!h || !pose0 || !pose1) return PFMPE_ERR_INVALID;
   if (tracker < 0 || tracker >= h->cfg.n_trackers) return fail(h, PFMPE_ERR_INVALID, "tracker out of range");
+  if (!(t1 != t0)) return fail(h, PFMPE_ERR_INVALID, "t0 and t1 must differ (predictPose divides by their difference, :1002)");
   PF_CUDA(h, cudaSetDevice(h->cfg.device));
   pf_tracker_state s;
   PF_CUDA(h, cudaMemcpyAsync(&h->h_state[tracker], h->state + tracker, sizeof s, cudaMemcpyDeviceToHost, h->stream));
@@ -950,6 +952,8 @@ int pfmpe_track_set_state(pfmpe_handle* h, int tracker, const double previous_po
   if (!h || !previous_pose || !current_pose) return PFMPE_ERR_INVALID;
   if (tracker < 0 || tracker >= h->cfg.n_trackers) return fail(h, PFMPE_ERR_INVALID, "tracker out of range");
   if (!h->particles_set[tracker]) return fail(h, PFMPE_ERR_STATE, "set_particles must precede track_set_state");
+  // predictPose divides by (current_time - previous_time) (:1002): equal times would hand inf / NaN constants to the kernel
+  if (!(current_time != previous_time)) return fail(h, PFMPE_ERR_INVALID, "previous_time and current_time must differ");
   PF_CUDA(h, cudaSetDevice(h->cfg.device));
   PF_CUDA(h, cudaStreamSynchronize(h->stream));
   PF_CUDA(h, cudaMemcpy(h->h_state + tracker, h->state + tracker, sizeof(pf_tracker_state), cudaMemcpyDeviceToHost));

@@ -10,3 +10,28 @@ if ROOT not in sys.path:
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+def _device_count():
+    """CUDA devices as libpfmpe.so sees them (pfmpe_create is what fails without one; there is no CPU fallback)."""
+    try:
+        import ctypes
+        rt = ctypes.CDLL("libcudart.so.12")
+        n = ctypes.c_int(0)
+        return n.value if rt.cudaGetDeviceCount(ctypes.byref(n)) == 0 else 0
+    except OSError:
+        try:
+            import torch
+            return torch.cuda.device_count()
+        except Exception:
+            return 0
+
+
+def pytest_collection_modifyitems(config, items):
+    """`pytest tests` on a host without a device: the gpu tests are skipped, not failed (`-m gpu` on the B200 box runs them)."""
+    if _device_count() > 0:
+        return
+    skip = pytest.mark.skip(reason="no CUDA device on this host (the product has no CPU fallback)")
+    for it in items:
+        if "gpu" in it.keywords:
+            it.add_marker(skip)

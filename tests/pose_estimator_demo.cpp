@@ -46,7 +46,7 @@ int main(int argc, char** argv)
     const pfmpe::Matrix4d pose = trackable_object_.getPredictedPose(0);                                                // :305
     const pfmpe::Matrix6d cov = trackable_object_.getPoseCovariance(0);                                                // :304
     const pfmpe::PoseEstimator::PubData_struct pd = trackable_object_.getPublisherData();                              // :418
-    std::printf("%d %.1f %d", found[0] ? 1 : 0, pd.Flag_Fail[0], pd.numIter);
+    std::printf("%d %.1f %d", found[0] ? 1 : 0, pd.Flag_Fail[0], (int)pd.numIter);
     for (int i = 0; i < 16; ++i) std::printf(" %.17g", pose[i]);
     double tr = 0;
     for (int i = 0; i < 6; ++i) tr += cov[7 * i];

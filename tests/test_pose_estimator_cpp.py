@@ -1,6 +1,6 @@
 """include/pfmpe_pose_estimator.hpp -- the C++ mirror of the reference's PoseEstimator interface -- compiled with
 g++ against libpfmpe.so and driven like MPENode drives the reference.  CPU: it builds, and without a CUDA device
-every frame fails loudly (Flag_Fail 13, no CPU fallback).  GPU: its poses equal the ctypes path bit for bit."""
+every frame fails loudly (Flag_Fail 100 = kFlagFailNoDevice, no CPU fallback).  GPU: its poses equal the ctypes path bit for bit."""
 import os
 import subprocess
 
@@ -57,7 +57,7 @@ def test_cpp_mirror_builds_and_fails_loudly_without_device(tmp_path):
     _, seq = _sequence(tmp_path)
     out = subprocess.run([exe, seq], capture_output=True, text=True, check=True).stdout.splitlines()
     frames = [l for l in out if l[:2] in ("0 ", "1 ")]
-    assert len(frames) == F and all(l.startswith("0 13.0") for l in frames)     # found = false, Flag_Fail = 13
+    assert len(frames) == F and all(l.startswith("0 100.0") for l in frames)     # found = false, Flag_Fail = kFlagFailNoDevice
     assert any("no usable CUDA device" in l or "no device" in l for l in out)
 
 

@@ -1,7 +1,9 @@
-"""The initialisation side of include/pfmpe_pose_estimator.hpp (C++ mirror of PoseEstimator::initialise and the
-branch of estimateBodyPose that calls it).  CPU: its host functions -- correspondencesFromHistogram (:1134-1288),
-computeTransformation (:2139-2161) -- against NumPy restatements.  GPU: initialiseBodyPose on a synthetic frame finds
-the true LED / detection pairing and the object's pose, and the particle filter tracks on from the seeded particles."""
+"""The initialisation side: the device stand-ins of the C++ mirror (correspondenceHistogram,
+checkCorrespondenceSets, seedInitialisedObject) strung together by tests/pose_estimator_init.cpp with the reference's
+host tail of initialise(), which is restated in oracle/initialise_host.hpp (test infrastructure).  CPU: the oracle's
+host functions -- correspondencesFromHistogram (:1134-1288), computeTransformation (:2139-2161) -- against independent
+NumPy restatements.  GPU: the initialisation of a synthetic frame finds the true LED / detection pairing and the object's
+pose, and the particle filter tracks on from the seeded particles (one object, and two objects at one timestamp)."""
 import os
 import subprocess
 
@@ -119,14 +121,14 @@ def test_compute_transformation_matches_svd(tmp_path):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("n_out", [0, 5, 10])
-def test_initialise_then_track(tmp_path, n_out):
+@pytest.mark.parametrize("n_out,n_obj", [(0, 1), (5, 1), (10, 1), (3, 2)])
+def test_initialise_then_track(tmp_path, n_out, n_obj):
     exe = _build(tmp_path)
     sc = S.Scene(n_outliers=n_out)
     f0, F, N = 7, 10, 2000
     p = tmp_path / "init.txt"
     with open(p, "w") as f:
-        f.write("%d %d %d\n" % (N, 5, S.pf_seed(f0 + 1)))
+        f.write("%d %d %d %d\n" % (N, 5, S.pf_seed(f0 + 1), n_obj))
         for m in sc.markers:
             f.write("%r %r %r\n" % tuple(float(v) for v in m))
         f.write(" ".join(repr(float(v)) for v in sc.K.reshape(-1)) + "\n")
@@ -151,3 +153,5 @@ def test_initialise_then_track(tmp_path, n_out):
         assert tok[0] == "1", (i, line)                                                  # the PF tracks on from the seeds
         pose = np.array([float(v) for v in tok[2:18]]).reshape(4, 4).T
         assert np.abs(pose[:3, 3] - sc.pose(f0 + 1 + i)[:3, 3]).max() < 0.03
+        last = np.array([float(v) for v in tok[18:34]]).reshape(4, 4).T                   # the last object (same detections)
+        assert np.isfinite(last).all() and np.abs(last[:3, 3] - sc.pose(f0 + 1 + i)[:3, 3]).max() < 0.03

@@ -1,0 +1,15 @@
+# round 2, first GPU call: state of HEAD (tests, stage timeline) + source-level ncu captures that guide the instruction diet
+set -x
+export PYTHONPATH=.
+mkdir -p gpurun_out
+nvidia-smi -L
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/r02a_pytest.log 2>&1; tail -3 gpurun_out/r02a_pytest.log
+timeout 300 python tools/timeline.py > gpurun_out/r02a_timeline.txt 2>&1; cat gpurun_out/r02a_timeline.txt
+timeout 300 python tools/one_cfg.py 4096 1024 10 6 > gpurun_out/one_cfg4.log 2>&1 &&
+timeout 600 ncu --set full --import-source on --clock-control none -k regex:pf_frames -s 3 -c 1 -o gpurun_out/r02a_full_cfg4 \
+    python tools/one_cfg.py 4096 1024 10 6 > gpurun_out/ncu_cfg4.log 2>&1
+timeout 300 python tools/one_cfg.py 16777216 1 10 6 > gpurun_out/one_cfg5s.log 2>&1 &&
+timeout 600 ncu --set full --import-source on --clock-control none -k regex:pf_frames -s 3 -c 1 -o gpurun_out/r02a_full_cfg5s \
+    python tools/one_cfg.py 16777216 1 10 6 > gpurun_out/ncu_cfg5s.log 2>&1
+cat gpurun_out/one_cfg4.log gpurun_out/one_cfg5s.log; tail -2 gpurun_out/ncu_cfg4.log gpurun_out/ncu_cfg5s.log
+ls -la gpurun_out

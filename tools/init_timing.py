@@ -1,4 +1,5 @@
-"""Wall time of pfmpe::PoseEstimator::initialiseBodyPose (C++ mirror) for a few outlier counts; needs a GPU."""
+"""Wall time of the whole initialisation (device vote + device checkCorrespondences bodies + the reference's host
+tail, tests/pose_estimator_init.cpp) for a few outlier counts; needs a GPU."""
 import os, subprocess, sys, tempfile
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -14,7 +15,7 @@ for n_out in (0, 10, 20, 40):
     sc = S.Scene(n_outliers=n_out)
     p = os.path.join(d, "s.txt")
     with open(p, "w") as f:
-        f.write("2000 5 3\n" + "\n".join("%r %r %r" % tuple(map(float, m)) for m in sc.markers) + "\n")
+        f.write("2000 5 3 1\n" + "\n".join("%r %r %r" % tuple(map(float, m)) for m in sc.markers) + "\n")
         f.write(" ".join(repr(float(v)) for v in sc.K.reshape(-1)) + "\n")
         b = sc.blobs(7)
         f.write("%r %d\n" % (sc.time(7), b.shape[0]) + "\n".join("%r %r" % (float(q[0]), float(q[1])) for q in b) + "\n0\n")
