@@ -216,105 +216,148 @@ __device__ __forceinline__ long long pf_warp_sum_nonneg(long long e)
 __device__ __forceinline__ long long pf_shfl_ll(long long v, int src) { return __shfl_sync(PF_FULL, v, src); }
 
 // ---------------------------------------------------------------------------------------
-// Detections of the frame in shared memory, bucketed by image column.
+// Detections of the frame in shared memory: candidate lists per image column.
 //
 // The score (:2385-2445) depends, per LED, only on the nearest blob if it lies within the gate
 // tol_PF (the greedy loop stops at the first LED whose nearest blob is farther, :2414/:2438).  A
-// blob within the gate has |dx| <= tol_PF, so the search is restricted to the column buckets that
-// intersect [u - r, u + r], r slightly above tol_PF: same minimum, same index, same ties as the
-// reference's full scan whenever the result matters, at a fraction of the distance evaluations.
-// col() is a monotone function of x (subtract, scale by a positive constant, clamp, floor), which
-// is all the argument needs; NaN coordinates fall into bucket 0 and never win a comparison.
+// blob within the gate has |dx| <= tol_PF, so the search is restricted to blobs whose x lies within
+// r of the projected LED, r slightly above tol_PF.  The image is cut into at most PF_NCOL columns of
+// width >= 1.01 r over [min x - r, max x + r]; column c lists (cand[desc.start .. desc.end)) every
+// blob whose interval [x - r, x + r] touches it -- at most three columns per blob -- in ascending
+// blob index, as full (x, y, index) records, so that a query is: one column number (an FFMA, a
+// saturating conversion, a min), one descriptor load, and a strict-< scan of typically one or two
+// records.  pf_col() is a monotone function of x (one correctly rounded FMA, truncation, clamp),
+// which is all the exactness argument needs: |u - x_i| <= tol_PF < r  =>  x_i - r <= u <= x_i + r
+// =>  col(x_i - r) <= col(u) <= col(x_i + r)  =>  blob i is listed in col(u).  Same minimum, same
+// index (ties go to the smaller blob index: lists are ascending, the comparison is strict) as the
+// reference's full scan whenever the result matters.  NaN coordinates fall into column 0 and never
+// win a comparison.
 // ---------------------------------------------------------------------------------------
 #define PF_NCOL 128
+#define PF_CAND_PER_BLOB 3
 struct pf_blob { float x, y; int idx; int pad; };          // 16 B: one LDS.128
 struct pf_blobtab {
-  float x0, inv_cw, r;
-  int D;
-  unsigned short colstart[PF_NCOL + 2];
-  int work[PF_NCOL];                                      // histogram, then insertion cursors
+  float kx, c0, r;
+  int D, ncol;
+  unsigned desc[PF_NCOL];                                  // (count << 16) | start into cand[]; during the build: counts
 };
-
-__device__ __forceinline__ int pf_col(const pf_blobtab& bt, float x)
+// cand[0] is a sentinel record at infinity: an empty column points to it with count 0, so that a query can load and
+// test "the first candidate" unconditionally (distance +inf) and only loops for a second, third, ... candidate.
+// dynamic shared memory of the frame kernel: blobs[D_max] (index order) | cand[1 + 3 D_max] | span[D_max] (u16)
+__host__ __device__ __forceinline__ size_t pf_blob_smem_bytes(int d_max)
 {
-  const float t = fminf(fmaxf((x - bt.x0) * bt.inv_cw, 0.0f), (float)(PF_NCOL - 1));
-  return (int)t;                                          // t >= 0: truncation == floor
+  return (size_t)d_max * (sizeof(pf_blob) * (1 + PF_CAND_PER_BLOB)) + sizeof(pf_blob) + (((size_t)d_max * 2 + 15) & ~(size_t)15);
 }
 
-// executed by warp 0; bsrc: D x 2 doubles in global memory
-__device__ __forceinline__ void pf_stage_blobs(const double* bsrc, int D, float tol_pf, pf_blobtab& bt, pf_blob* blobs, int lane)
+__device__ __forceinline__ unsigned pf_col(const pf_blobtab& bt, float x)
 {
-  float lo = INFINITY, hi = -INFINITY;
-  for (int i = lane; i < D; i += 32) {
-    const float x = (float)bsrc[2 * i];
-    lo = fminf(lo, x); hi = fmaxf(hi, x);
+  const unsigned c = __float2uint_rz(fmaf(x, bt.kx, bt.c0));   // saturating: negative / NaN -> 0, huge -> 2^32 - 1
+  return min(c, (unsigned)(bt.ncol - 1));
+}
+
+// executed by ALL threads of the CTA (contains __syncthreads); bsrc: D x 2 doubles in global memory
+__device__ __noinline__ void pf_stage_blobs(const double* bsrc, int D, float tol_pf, pf_blobtab& bt, pf_blob* blobs, int d_max)
+{
+  pf_blob* cand = blobs + d_max;
+  unsigned short* span = reinterpret_cast<unsigned short*>(cand + 1 + (size_t)PF_CAND_PER_BLOB * d_max);
+  const int tid = threadIdx.x, nt = blockDim.x;
+  if (tid == 0) { pf_blob z; z.x = INFINITY; z.y = INFINITY; z.idx = 0; z.pad = 0; cand[0] = z; }
+  for (int i = tid; i < D; i += nt) {
+    pf_blob b;
+    b.x = (float)bsrc[2 * i]; b.y = (float)bsrc[2 * i + 1]; b.idx = i; b.pad = 0;
+    blobs[i] = b;
   }
+  __syncthreads();
+  if (tid < 32) {
+    float lo = INFINITY, hi = -INFINITY;
+    for (int i = tid; i < D; i += 32) { const float x = blobs[i].x; lo = fminf(lo, x); hi = fmaxf(hi, x); }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    lo = fminf(lo, __shfl_xor_sync(PF_FULL, lo, o));
-    hi = fmaxf(hi, __shfl_xor_sync(PF_FULL, hi, o));
+    for (int o = 16; o > 0; o >>= 1) {
+      lo = fminf(lo, __shfl_xor_sync(PF_FULL, lo, o));
+      hi = fmaxf(hi, __shfl_xor_sync(PF_FULL, hi, o));
+    }
+    if (tid == 0) {
+      const float r = tol_pf * 1.0001f + 1.0e-3f;
+      const float span_x = (hi - lo) + 2.0f * r;
+      int ncol = 1;
+      float kx = 0.0f, c0 = 0.0f;
+      if (D > 0 && span_x > 0.0f && span_x < 3.0e38f && r > 0.0f) {
+        const float q = span_x / (1.01f * r);
+        ncol = q < (float)PF_NCOL ? (int)q : PF_NCOL;
+        if (ncol < 1) ncol = 1;
+        kx = (float)ncol / span_x;
+        c0 = -(lo - r) * kx;
+      }
+      bt.kx = kx; bt.c0 = c0; bt.r = r; bt.D = D; bt.ncol = ncol;
+    }
   }
-  const float span = hi - lo;
-  if (lane == 0) {
-    bt.x0 = D > 0 ? lo : 0.0f;
-    bt.inv_cw = (D > 0 && span > 0.0f && span < 3.0e38f) ? (float)PF_NCOL / span : 0.0f;
-    bt.r = tol_pf * 1.0001f + 1.0e-3f;
-    bt.D = D;
+  __syncthreads();
+  for (int i = tid; i < D; i += nt) {
+    const float x = blobs[i].x;
+    span[i] = (unsigned short)(pf_col(bt, x - bt.r) | (pf_col(bt, x + bt.r) << 8));
   }
-#pragma unroll
-  for (int c = lane; c < PF_NCOL; c += 32) bt.work[c] = 0;
-  __syncwarp();
-  for (int i = lane; i < D; i += 32) atomicAdd(&bt.work[pf_col(bt, (float)bsrc[2 * i])], 1);
-  __syncwarp();
-  {
+  __syncthreads();
+  // one thread per column: count, (ordered prefix by warp 0), fill -- the fill scans the blobs in index order
+  int cnt = 0;
+  if (tid < PF_NCOL) {
+    if (tid < bt.ncol)
+      for (int i = 0; i < D; ++i) { const unsigned sp = span[i]; cnt += ((sp & 255u) <= (unsigned)tid && (unsigned)tid <= (sp >> 8)) ? 1 : 0; }
+    bt.desc[tid] = (unsigned)cnt;
+  }
+  __syncthreads();
+  if (tid < 32) {
     int h[PF_NCOL / 32], sum = 0;
 #pragma unroll
-    for (int q = 0; q < PF_NCOL / 32; ++q) { h[q] = bt.work[lane * (PF_NCOL / 32) + q]; sum += h[q]; }
+    for (int q = 0; q < PF_NCOL / 32; ++q) { h[q] = (int)bt.desc[tid * (PF_NCOL / 32) + q]; sum += h[q]; }
     int inc = sum;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       const int t = __shfl_up_sync(PF_FULL, inc, o);
-      if (lane >= o) inc += t;
+      if (tid >= o) inc += t;
     }
-    int run = inc - sum;
+    int run = inc - sum + 1;                                 // lists start behind the sentinel
 #pragma unroll
-    for (int q = 0; q < PF_NCOL / 32; ++q) {
-      bt.colstart[lane * (PF_NCOL / 32) + q] = (unsigned short)run;
-      bt.work[lane * (PF_NCOL / 32) + q] = run;
-      run += h[q];
-    }
-    if (lane == 31) { bt.colstart[PF_NCOL] = (unsigned short)run; bt.colstart[PF_NCOL + 1] = (unsigned short)run; }
+    for (int q = 0; q < PF_NCOL / 32; ++q) { bt.desc[tid * (PF_NCOL / 32) + q] = (unsigned)run; run += h[q]; }
   }
-  __syncwarp();
-  for (int i = lane; i < D; i += 32) {
-    pf_blob b;
-    b.x = (float)bsrc[2 * i]; b.y = (float)bsrc[2 * i + 1]; b.idx = i; b.pad = 0;
-    const int pos = atomicAdd(&bt.work[pf_col(bt, b.x)], 1);
-    blobs[pos] = b;
+  __syncthreads();
+  if (tid < PF_NCOL) {
+    const int start = (int)bt.desc[tid];
+    int k = start;
+    const int cap = 1 + PF_CAND_PER_BLOB * d_max;            // never reached (<= 3 columns per blob); memory safety only
+    if (tid < bt.ncol)
+      for (int i = 0; i < D; ++i) {
+        const unsigned sp = span[i];
+        if ((sp & 255u) <= (unsigned)tid && (unsigned)tid <= (sp >> 8) && k < cap) cand[k++] = blobs[i];
+      }
+    __syncwarp();
+    bt.desc[tid] = k > start ? (((unsigned)(k - start) << 16) | (unsigned)start) : 0u;
   }
+  __syncthreads();
 }
 
-// nearest blob of every projected LED among the buckets within the gate radius; m[j] = +inf,
-// am[j] = 0 if there is none.  Ties go to the smaller blob index (packed-key minimum).
-template <int L>
-__device__ __forceinline__ void pf_nearest_pruned(const pf_blobtab& bt, const pf_blob* blobs, const float* u, const float* v,
-                                                  float* m, int* am)
+// nearest blob of a projected LED among the candidates of its column; m = +inf, am = 0 if there is none.
+// The first record is tested without a branch (cand[0], the sentinel, for an empty column); the loop over further
+// candidates is kept rolled: it runs zero times for most LEDs, and an unrolled remainder cascade costs more than it saves.
+__device__ __forceinline__ void pf_nearest_one(const pf_blobtab& bt, const pf_blob* cand, float u, float v, float& m, int& am)
 {
-#pragma unroll
-  for (int j = 0; j < L; ++j) {
-    const int c0 = pf_col(bt, u[j] - bt.r), c1 = pf_col(bt, u[j] + bt.r);
-    const int a = bt.colstart[c0], b = bt.colstart[c1 + 1];
-    unsigned long long key = ((unsigned long long)0x7F800000u << 32);
-    for (int k = a; k < b; ++k) {
-      const float4 z = *reinterpret_cast<const float4*>(&blobs[k]);
-      const float dx = z.x - u[j], dy = z.y - v[j];
+  const unsigned d = bt.desc[pf_col(bt, u)];
+  const pf_blob* q = cand + (d & 0xFFFFu);
+  const float4 z0 = *reinterpret_cast<const float4*>(q);
+  const float dx0 = z0.x - u, dy0 = z0.y - v;
+  float best = fmaf(dy0, dy0, dx0 * dx0);
+  int bi = __float_as_int(z0.z);                            // a NaN distance (non-finite projection) is never accepted downstream
+  if (d >= (2u << 16)) {
+    const pf_blob* qe = q + (d >> 16);
+#pragma unroll 1
+    for (++q; q < qe; ++q) {
+      const float4 z = *reinterpret_cast<const float4*>(q);
+      const float dx = z.x - u, dy = z.y - v;
       const float d2 = fmaf(dy, dy, dx * dx);
-      const unsigned long long kk = ((unsigned long long)__float_as_uint(d2) << 32) | (unsigned)__float_as_int(z.z);
-      key = kk < key ? kk : key;
+      if (d2 < best) { best = d2; bi = __float_as_int(z.z); }
     }
-    m[j] = __uint_as_float((unsigned)(key >> 32));
-    am[j] = (int)(unsigned)(key & 0xFFFFFFFFull);
   }
+  m = best;
+  am = bi;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -346,21 +389,22 @@ __device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_c
   float* w = p.w + (size_t)trk * N;
   // sharded filter: the rebalance delivers lead[] (slot -> local slot that holds its row), idx[] is the stage-B output
   const int* idx = (SH && p.lead) ? p.lead : p.idx + (size_t)trk * N;
+  const pf_blob* cand = blobs + p.D_max;
 
-  pf_pose Pm, Cm;
-#pragma unroll
-  for (int i = 0; i < 12; ++i) { Pm.p[i] = cx.fc.P[i]; Cm.p[i] = cx.fc.C[i]; }
   const bool use_cam = cx.fc.isi > 1;                       // :555-560
   const bool use_pred = use_cam && (it % 10) != 0;
   const bool cam_mul = use_cam && !(cx.fc.flags & PF_FC_CAM_IDENTITY);
-  const bool small_ang = (cx.fc.flags & PF_FC_SMALL_ANG) != 0;
+  const int ang_mode = (cx.fc.flags & PF_FC_TINY_ANG) ? 2 : ((cx.fc.flags & PF_FC_SMALL_ANG) ? 1 : 0);
   const bool kstd = p.kstd != 0;
+  const int steps = cx.fc.D < L ? cx.fc.D : L;              // :2409
+  const bool gather = cx.src_mode == 1;
   const float scale = 1.0f + 0.025f * (float)(it / 10);    // :563 (integer division)
 
   const int wchunk = p.cta_chunk / (int)(blockDim.x >> 5); // multiple of 32
   const long long w0l = (long long)blockIdx.x * p.cta_chunk + (long long)warp * wchunk;
   const int w0 = w0l < (long long)N ? (int)w0l : N;
   const int w1 = (w0l + wchunk) < (long long)N ? (int)(w0l + wchunk) : N;
+  const int goff = SH ? p.goff : 0;
 
   // RNG: particle n >= 2 starts at engine step 12*((N-2)*it + n-2).  Each lane keeps the
   // state of "its" particle of the current step and advances it by 32 particles = 384 engine steps
@@ -368,67 +412,83 @@ __device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_c
   uint32_t xs;
   {
     const uint64_t e0 = (12ull * (uint64_t)((SH ? p.N_global : N) - 2) * (uint64_t)it) % PF_RNG_ORDER;
-    const uint64_t ee = (e0 + (uint64_t)PF_RNG_ORDER - 24ull + 12ull * (uint64_t)((SH ? p.goff : 0) + w0 + lane)) % PF_RNG_ORDER;
+    const uint64_t ee = (e0 + (uint64_t)PF_RNG_ORDER - 24ull + 12ull * (uint64_t)(goff + w0 + lane)) % PF_RNG_ORDER;
     xs = pf_rng_skip_e(cx.fc.seed_state, (uint32_t)ee, tab);
   }
 
-  pf_red acc = pf_red_identity();
-  pf_sm3 carry = pf_sm3_identity();
-  for (int base = w0; base < w1; base += 32) {
-    const int n = base + lane;
-    const bool valid = n < w1;
-    long long e = 0;
+  // per-thread running (max, first index) / (min, first index) as plain floats -- a thread visits its particles in
+  // ascending order, so strict comparisons keep the first -- packed into the order-preserving keys once, at the end
+  float bmax = -INFINITY, bmin = INFINITY;
+  int imax = -1, imin = -1;
+  long long tsum = 0;
+  int s_next = (gather && w0 + lane < w1) ? idx[w0 + lane] : 0;   // Particle_index of the first step's slot (:678-681)
+  for (int n = w0 + lane; n < w1; n += 32) {                // full steps except possibly the last: no warp-level code inside
     const uint32_t x = xs;
     xs = pf_modmul(xs, PF_RNG_A384);
-    if (valid) {
-      const int s = cx.src_mode == 1 ? idx[n] : n;      // Particle_index of slot n (:678-681), written by stage B
-      pf_pose T;
-      const int ng = (SH ? p.goff : 0) + n;                        // global particle index (sharded filter: goff > 0)
-      if (ng == 0) {
-#pragma unroll
-        for (int i = 0; i < 12; ++i) T.p[i] = cx.fc.Tcur[i];      // :547
-      } else if (ng == 1) {
-#pragma unroll
-        for (int i = 0; i < 12; ++i) T.p[i] = cx.fc.Tpred[i];     // :551
-      } else {
-        pf_pose B = pf_load_pose(src, N, s);
-        if (cam_mul) B = pf_affine_mul(Cm, B);
-        if (use_pred) B = pf_affine_mul(B, Pm);
-        T = pf_propagate(B, x, cx.fc.noise, scale, small_ang);
-      }
-      pf_store_pose(dst, N, n, T);
-      float u[L], v[L];
-#pragma unroll
-      for (int j = 0; j < L; ++j) {
-        pf_project(p.K9f, kstd, T, cx.obj[3 * j], cx.obj[3 * j + 1], cx.obj[3 * j + 2], u[j], v[j]);
-        if (DIST) pf_distort(p.K9f, p.dist, u[j], v[j]);   // row f3: score against the raw (distorted) blob centres
-      }
-      float m[L];
-      int am[L];
-      pf_nearest_pruned<L>(cx.bt, blobs, u, v, m, am);
-      const float wn = pf_greedy<L, false>(m, am, cx.fc.D, p.score, nullptr, nullptr);
-      w[n] = wn;
-      const unsigned o = pf_ord(wn);
-      const unsigned long long kmax = ((unsigned long long)o << 32) | (unsigned)(~(unsigned)ng);
-      const unsigned long long kmin = ~(((unsigned long long)o << 32) | (unsigned)ng);
-      acc.maxkey = kmax > acc.maxkey ? kmax : acc.maxkey;
-      acc.minkey_inv = kmin > acc.minkey_inv ? kmin : acc.minkey_inv;
-      e = pf_w_to_fx(wn);
-      acc.sum += e;
-    }
-    // ordered aggregate of the 32 particles of this step, appended to the warp's carry
-    if (!__any_sync(PF_FULL, e < 0)) {
-      // prefix is non-decreasing inside the step: min at its first element, max at its end
-      const long long total = pf_warp_sum_nonneg(e);
-      const long long first = pf_shfl_ll(e, 0);
-      const long long lo = carry.s + first;
-      carry.mn = carry.mn < lo ? carry.mn : lo;
-      carry.s += total;
-      carry.mx = carry.mx > carry.s ? carry.mx : carry.s;
+    const int s = gather ? s_next : n;
+    if (gather && n + 32 < w1) s_next = idx[n + 32];      // one step ahead: shortens the idx -> rows dependent chain
+    pf_pose T;
+    const int ng = goff + n;                               // global particle index (sharded filter: goff > 0)
+    if (ng >= 2) {
+      pf_pose B = pf_load_pose(src, N, s);
+      if (cam_mul) { pf_pose Cm; for (int i = 0; i < 12; ++i) Cm.p[i] = cx.fc.C[i]; B = pf_affine_mul(Cm, B); }
+      if (use_pred) { pf_pose Pm; for (int i = 0; i < 12; ++i) Pm.p[i] = cx.fc.P[i]; B = pf_affine_mul(B, Pm); }
+      T = pf_propagate(B, x, cx.fc.noise, scale, ang_mode);
     } else {
-      pf_sm3 a;
-      if (valid) { a.s = e; a.mx = e; a.mn = e; } else a = pf_sm3_identity();
+      const float* t0 = ng == 0 ? cx.fc.Tcur : cx.fc.Tpred;   // :547, :551
 #pragma unroll
+      for (int i = 0; i < 12; ++i) T.p[i] = t0[i];
+    }
+    pf_store_pose(dst, N, n, T);
+    // camera coordinates of every LED first, then one (uniform) branch on the shape of K for all of them
+    float xc[L], yc[L], zc[L];
+#pragma unroll
+    for (int j = 0; j < L; ++j) pf_to_camera(T, cx.obj[3 * j], cx.obj[3 * j + 1], cx.obj[3 * j + 2], xc[j], yc[j], zc[j]);
+    float u[L], v[L];
+    if (kstd) {
+#pragma unroll
+      for (int j = 0; j < L; ++j) pf_to_pixel(p.K9f, true, xc[j], yc[j], zc[j], u[j], v[j]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < L; ++j) pf_to_pixel(p.K9f, false, xc[j], yc[j], zc[j], u[j], v[j]);
+    }
+    float m[L];
+    int am[L];
+#pragma unroll
+    for (int j = 0; j < L; ++j) {
+      if (DIST) pf_distort(p.K9f, p.dist, u[j], v[j]);     // row f3: score against the raw (distorted) blob centres
+      pf_nearest_one(cx.bt, cand, u[j], v[j], m[j], am[j]);
+    }
+    const float wn = pf_weight_unordered<L>(m, am, steps, p.score);
+    w[n] = wn;
+    if (wn > bmax) { bmax = wn; imax = ng; }
+    if (wn < bmin) { bmin = wn; imin = ng; }
+    tsum += pf_w_to_fx(wn);
+  }
+  pf_red acc = pf_red_identity();
+  acc.sum = tsum;
+  if (imax >= 0) {
+    acc.maxkey = ((unsigned long long)pf_ord(bmax) << 32) | (unsigned)(~(unsigned)imax);
+    acc.minkey_inv = ~(((unsigned long long)pf_ord(bmin) << 32) | (unsigned)imin);
+  }
+  // The warp's sign-agnostic prefix aggregate (sum, running max, running min of the prefix of its particles in order).
+  // Without a negative weight the prefix is non-decreasing: max = the total, min = the first element -- no per-step
+  // reductions.  A warp that did see one (penalties can outweigh the gains, :2423-2432) re-reads its weights and runs
+  // the ordered scan.
+  pf_sm3 carry = pf_sm3_identity();
+  __syncwarp();
+  if (!__any_sync(PF_FULL, bmin < 0.0f)) {                 // the thread's minimum weight tells whether it saw a negative one
+    long long tot = tsum;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(PF_FULL, tot, o);
+    if (w0 < w1 && lane == 0) { carry.s = tot; carry.mx = tot; carry.mn = pf_w_to_fx(w[w0]); }   // lane 0 wrote w[w0] itself; only its carry is used
+  } else {
+#pragma unroll 1
+    for (int base = w0; base < w1; base += 32) {
+      const int n = base + lane;
+      pf_sm3 a;
+      if (n < w1) { const long long e = pf_w_to_fx(w[n]); a.s = e; a.mx = e; a.mn = e; } else a = pf_sm3_identity();
+#pragma unroll 1
       for (int o = 1; o < 32; o <<= 1) {
         pf_sm3 t;
         t.s = __shfl_down_sync(PF_FULL, a.s, o);
@@ -601,10 +661,13 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
     }
     pf_stamp(p, 13);
 
+    float w_next = w0 + lane < w1 ? w[w0 + lane] : 0.0f;
     for (int base = w0; base < w1; base += 32) {
       const int n = base + lane;
       const bool valid = n < w1;
-      const long long e = valid ? sg * pf_w_to_fx(w[n]) : 0ll;
+      const float w_cur = w_next;
+      if (n + 32 < w1) w_next = w[n + 32];                // one step ahead of the dependent chain scan -> K(M) -> fill
+      const long long e0 = valid ? pf_w_to_fx(w_cur) : 0ll, e = sg < 0 ? -e0 : e0;
       long long M, total;
       if (!__any_sync(PF_FULL, e < 0)) {
         long long ps = e;                                 // inclusive prefix sum inside the step
@@ -671,7 +734,19 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
           }
         }
         const unsigned bigm = p.coop ? 0u : __ballot_sync(PF_FULL, own > PF_FILL_WARP);
+        const int maxown = listed ? 0 : __reduce_max_sync(PF_FULL, own);
         if (listed) {
+        } else if (bigm == 0u && maxown <= 6 * ((R + 31) >> 5)) {
+          // balanced step (the usual case: offspring counts of a few): every source writes its own slots, one per
+          // round; the lanes' slot ranges are adjacent, so a round's stores fall into a window of at most R slots
+          int* q = idx + Eprev;
+          const int lim = SH ? min(own, p.idx_cap - Eprev) : own;
+#pragma unroll
+          for (int t = 0; t < 4; ++t) if (t < lim) q[t] = n;          // predicated stores, no loop
+          if (maxown > 4) {
+#pragma unroll 1
+            for (int t = 4; t < maxown; ++t) if (t < lim) q[t] = n;   // warp-uniform trip count
+          }
         } else if (bigm == 0u) {
           for (int q0 = 0; q0 < R; q0 += 32) {            // warp-uniform trip count: every lane serves the shuffles
             const int k = E0 + q0 + lane;
@@ -942,7 +1017,7 @@ __global__ void __launch_bounds__(V == 3 ? PF_BLOCK : PF_MAX_BLOCK, V == 3 ? 4 :
   __shared__ pf_sm3 warp_agg[PF_MAX_WARPS];
   __shared__ pf_sm3 scr[PF_MAX_WARPS + 1];
   __shared__ pf_fill_list fill;
-  __shared__ uint32_t tab[1024];         // radix-256 power table of the RNG skip-ahead
+  __shared__ uint32_t tab[PF_RNG_TAB_WORDS];   // radix-512 power tables of the RNG skip-ahead
 
   const int trk = p.tracker_base + blockIdx.y;
   const int N = p.N;
@@ -964,7 +1039,7 @@ __global__ void __launch_bounds__(V == 3 ? PF_BLOCK : PF_MAX_BLOCK, V == 3 ? 4 :
       cx.obj[threadIdx.x] = p.obj_f[(size_t)trk * PF_MAX_LED * 3 + threadIdx.x];
       cx.objd[threadIdx.x] = p.obj_d[(size_t)trk * PF_MAX_LED * 3 + threadIdx.x];
     }
-    for (int i = threadIdx.x; i < 1024; i += blockDim.x) tab[i] = p.rng_tab[i];
+    for (int i = threadIdx.x; i < PF_RNG_TAB_WORDS; i += blockDim.x) tab[i] = p.rng_tab[i];
   }
 
   for (int f = 0; f < p.n_frames; ++f) {
@@ -985,16 +1060,15 @@ __global__ void __launch_bounds__(V == 3 ? PF_BLOCK : PF_MAX_BLOCK, V == 3 ? 4 :
       uint32_t* h32 = reinterpret_cast<uint32_t*>(p.fc_log + (size_t)trk * p.total_frames + frame);
       for (int i = threadIdx.x; i < (int)(sizeof(pf_frame_const) / 4); i += blockDim.x) h32[i] = f32[i];
     }
-    if (threadIdx.x == 0) { cx.src_buf = st.src_buf; cx.src_mode = st.src_mode; }
+    if (threadIdx.x == 0) { cx.src_buf = st.src_buf; cx.src_mode = st.src_mode; }   // visible after the barriers of the staging
     const int D = cx.fc.D;
-    if (threadIdx.x < 32) {
+    {
       const bool seq_mode = p.mode == 1 || p.mode == 2;
       const double* bsrc = p.inline_in ? p.blobs_inline
                                        : p.blobs + ((size_t)trk * (seq_mode ? p.total_frames : 1) + (seq_mode ? frame : 0)) *
                                                        (size_t)p.D_max * 2;
-      pf_stage_blobs(bsrc, D, p.score.tol_pf, cx.bt, blobs, threadIdx.x);
+      pf_stage_blobs(bsrc, D, p.score.tol_pf, cx.bt, blobs, p.D_max);
     }
-    __syncthreads();
     pf_stamp(p, 1);
 
     // ---- do { propagate, project, score } while (iter < 80 && max < L*min(5,numLED))  (:535-616)

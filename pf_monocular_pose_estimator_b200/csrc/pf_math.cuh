@@ -57,26 +57,49 @@ PF_HD uint32_t pf_rng_next(uint32_t x)
   return s < t ? s : t;
 }
 
-// tab[d*256 + v] = 16807^(v * 256^d) mod m, d = 0..3 (built on the host, pfmpe_api.cu)
-// pf_rng_skip_e: exponent already reduced mod PF_RNG_ORDER (16807 is a primitive root of 2^31-1).
-PF_HD uint32_t pf_rng_skip_e(uint32_t x, uint32_t e, const uint32_t* tab)
+// two engine steps at once: x * 16807^2 mod m.  16807^2 = 282475249 < 2^29, so the product is < 2^60, one fold leaves
+// s < 2^31 + 2^29 and one conditional subtraction finishes (s == m would need x == 0 mod m: impossible for a live state)
+#define PF_RNG_A2 282475249u
+PF_HD uint32_t pf_rng_next2(uint32_t x)
 {
-  x = pf_modmul(x, tab[e & 255u]);
-  x = pf_modmul(x, tab[256 + ((e >> 8) & 255u)]);
-  x = pf_modmul(x, tab[512 + ((e >> 16) & 255u)]);
-  x = pf_modmul(x, tab[768 + (e >> 24)]);
+  const uint64_t p = (uint64_t)x * (uint64_t)PF_RNG_A2;
+  const uint32_t s = (uint32_t)(p & PF_RNG_M) + (uint32_t)(p >> 31);
+  const uint32_t t = s - PF_RNG_M;
+  return s < t ? s : t;
+}
+
+// Skip-ahead: radix-512 power tables, tab[d*512 + v] = 16807^(v * 512^d) mod m, d = 0..3 (36 exponent bits >= 31);
+// x * 16807^e = one table entry + one modular multiplication per 9-bit digit of e.  Exponents are taken mod
+// PF_RNG_ORDER (16807 is a primitive root of 2^31-1).
+#define PF_RNG_DIGIT_BITS 9
+#define PF_RNG_TAB_WORDS (4 << PF_RNG_DIGIT_BITS)
+inline void pf_build_rng_table(uint32_t* tab)     // host
+{
+  const int R = 1 << PF_RNG_DIGIT_BITS;
+  uint32_t base = PF_RNG_A;
+  for (int d = 0; d < 4; ++d) {
+    tab[d * R] = 1u;
+    for (int v = 1; v < R; ++v) tab[d * R + v] = pf_modmul(tab[d * R + v - 1], base);
+    base = pf_modmul(tab[d * R + R - 1], base);   // base^R
+  }
+}
+// nd = number of digits that can be non-zero (uniform per call site: the exponent is below 512^nd)
+PF_HD uint32_t pf_rng_skip_nd(uint32_t x, uint32_t e, const uint32_t* tab, int nd)
+{
+  const uint32_t M9 = (1u << PF_RNG_DIGIT_BITS) - 1u;
+  x = pf_modmul(x, tab[e & M9]);
+  x = pf_modmul(x, tab[(1 << PF_RNG_DIGIT_BITS) + ((e >> PF_RNG_DIGIT_BITS) & M9)]);
+  if (nd > 2) x = pf_modmul(x, tab[(2 << PF_RNG_DIGIT_BITS) + ((e >> (2 * PF_RNG_DIGIT_BITS)) & M9)]);
+  if (nd > 3) x = pf_modmul(x, tab[(3 << PF_RNG_DIGIT_BITS) + (e >> (3 * PF_RNG_DIGIT_BITS))]);
   return x;
 }
+// pf_rng_skip_e: exponent already reduced mod PF_RNG_ORDER
+PF_HD uint32_t pf_rng_skip_e(uint32_t x, uint32_t e, const uint32_t* tab) { return pf_rng_skip_nd(x, e, tab, 4); }
 #define PF_RNG_A384 1618907920u /* 16807^384 mod (2^31-1): 32 particles x 12 engine steps (checked in pfmpe_api.cu) */
 
 PF_HD uint32_t pf_rng_skip(uint32_t x, uint64_t steps, const uint32_t* __restrict__ tab)
 {
-  uint32_t e = (uint32_t)(steps % PF_RNG_ORDER);
-  x = pf_modmul(x, tab[e & 255u]);
-  x = pf_modmul(x, tab[256 + ((e >> 8) & 255u)]);
-  x = pf_modmul(x, tab[512 + ((e >> 16) & 255u)]);
-  x = pf_modmul(x, tab[768 + (e >> 24)]);
-  return x;
+  return pf_rng_skip_nd(x, (uint32_t)(steps % PF_RNG_ORDER), tab, 4);
 }
 
 // generate_canonical<double,53> from two consecutive engine outputs, bit-exact with libstdc++
@@ -104,6 +127,42 @@ PF_HD float pf_canonical_f32(uint32_t g1, uint32_t g2)
   const float invR = 1.0f / 2147483646.0f;
   float hi = (float)(g2 - 1u), lo = (float)(g1 - 1u);
   return fminf(fmaf(lo, invR, hi) * invR, 0.99999994f);
+}
+
+// The motion noise only needs the high engine output of a draw: generate_canonical's value is
+// ((g1-1) + (g2-1) R) / R^2 = (g2-1)/R + (g1-1)/R^2, and the second term is below 2^-31 -- under half an ulp_f32 of
+// every value the first term can take except the few below 2^-7, where it still moves the noise by less than 1e-11 of
+// its range.  The engine is stepped twice per draw all the same (pf_rng_next2), so the stream stays the reference's.
+PF_HD float pf_canonical_f32_hi(uint32_t g2)
+{
+  const float invR = 1.0f / 2147483646.0f;
+  return fminf((float)(g2 - 1u) * invR, 0.99999994f);
+}
+
+// Fast reciprocal / square root of the scoring path.  Device: the SFU approximation (1 ulp); the reciprocal gets one
+// Newton step (it scales pixel coordinates of several hundred, where an ulp is 3e-5 px: the 1e-5 bar on the weights
+// leaves no room for a second ulp), the square root does not (it yields distances below the gate, a few pixels, whose
+// ulp is 5e-7 px).  No slow-path branches: a zero / denormal / infinite argument gives inf, 0 or NaN, which the callers
+// treat like the IEEE results (a NaN or inf distance is never within the gate).
+PF_HD float pf_rcp_nr(float x)
+{
+#if defined(__CUDA_ARCH__)
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return fmaf(fmaf(-x, r, 1.0f), r, r);
+#else
+  return 1.0f / x;
+#endif
+}
+PF_HD float pf_sqrt_fast(float x)
+{
+#if defined(__CUDA_ARCH__)
+  float r;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+#else
+  return sqrtf(x);
+#endif
 }
 
 // ----------------------------------------------------------------------------------------
@@ -150,21 +209,38 @@ PF_HD void pf_sincos_small(float x, float& s, float& c)
   c = fmaf(q, x2, 1.0f);
 }
 
-PF_HD pf_pose pf_propagate(const pf_pose& base, uint32_t x, const pf_noise_cfg& nc, float scale, bool small_ang)
+// sin/cos for |x| <= 0.03 (truncation: x^5/120 < 2.1e-10, x^6/720 < 1.1e-12 absolute)
+PF_HD void pf_sincos_tiny(float x, float& s, float& c)
 {
+  const float x2 = x * x;
+  s = x * fmaf(x2, -1.6666667e-1f, 1.0f);
+  c = fmaf(fmaf(x2, 4.1666667e-2f, -0.5f), x2, 1.0f);
+}
+
+// ang_mode: 0 = libm sincosf, 1 = every possible draw within +-0.3 rad (PF_FC_SMALL_ANG), 2 = within +-0.03 rad
+// (PF_FC_TINY_ANG: the default noise ranges, +-0.015 rad x facRot x scale).
+// The six noise values are  (c_d * span + lo) * scale  with c_d = (g2 - 1) / R (pf_canonical_f32_hi); with the two
+// uniform factors folded that is one conversion and one FMA per draw: g2 * (span * scale / R) + lo * scale.  (g2 - 1
+// and the clamp below 1 of the canonical value are dropped with the same argument as g1: they move the noise by
+// less than 2^-31 of its range.)
+PF_HD pf_pose pf_propagate(const pf_pose& base, uint32_t x, const pf_noise_cfg& nc, float scale, int ang_mode)
+{
+  const float invR = 1.0f / 2147483646.0f;
+  const float ka = nc.ang_span * scale * invR, la = nc.ang_lo * scale;
+  const float kt = nc.tr_span * scale * invR, lt = nc.tr_lo * scale;
   float c6[6];
 #pragma unroll
   for (int d = 0; d < 6; ++d) {
-    uint32_t g1 = pf_rng_next(x);
-    uint32_t g2 = pf_rng_next(g1);
-    x = g2;
-    c6[d] = pf_canonical_f32(g1, g2);
+    x = pf_rng_next2(x);             // g2 of this draw (g1 = the step in between is not needed, see pf_canonical_f32_hi)
+    c6[d] = (float)x;
   }
-  const float a = fmaf(c6[0], nc.ang_span, nc.ang_lo) * scale;
-  const float b = fmaf(c6[1], nc.ang_span, nc.ang_lo) * scale;
-  const float c = fmaf(c6[2], nc.ang_span, nc.ang_lo) * scale;
+  const float a = fmaf(c6[0], ka, la);
+  const float b = fmaf(c6[1], ka, la);
+  const float c = fmaf(c6[2], ka, la);
   float sa, ca, sb, cb, sc, cc;
-  if (small_ang) {   // uniform per frame (PF_FC_SMALL_ANG): every possible draw is within +-0.3 rad
+  if (ang_mode == 2) {
+    pf_sincos_tiny(a, sa, ca); pf_sincos_tiny(b, sb, cb); pf_sincos_tiny(c, sc, cc);
+  } else if (ang_mode == 1) {
     pf_sincos_small(a, sa, ca); pf_sincos_small(b, sb, cb); pf_sincos_small(c, sc, cc);
   } else {
 #if defined(__CUDA_ARCH__)
@@ -190,23 +266,26 @@ PF_HD pf_pose pf_propagate(const pf_pose& base, uint32_t x, const pf_noise_cfg& 
     }
   }
   // translation added separately (:585-587)
-  T.p[3]  = base.p[3]  + fmaf(c6[3], nc.tr_span, nc.tr_lo) * scale;
-  T.p[7]  = base.p[7]  + fmaf(c6[4], nc.tr_span, nc.tr_lo) * scale;
-  T.p[11] = base.p[11] + fmaf(c6[5], nc.tr_span, nc.tr_lo) * scale;
+  T.p[3]  = base.p[3]  + fmaf(c6[3], kt, lt);
+  T.p[7]  = base.p[7]  + fmaf(c6[4], kt, lt);
+  T.p[11] = base.p[11] + fmaf(c6[5], kt, lt);
   return T;
 }
 
 // project2d (:1017-1034): p = K (R X + t), (u,v) = (p0/p2, p1/p2); full 3x3 K, no cheirality test.
 // kstd (uniform): K has the usual zero pattern (K01 = K10 = K20 = K21 = 0, K22 = 1); the skipped
 // terms are exact zeros, so both branches give the same bits for finite inputs.  The two
-// divisions share one correctly rounded reciprocal (<= 1 ulp from the quotient).
+// divisions share one reciprocal (pf_rcp_nr: <= 1 ulp from the quotient).
 PF_HD bool pf_k_is_std(const float* K9) { return K9[1] == 0.0f && K9[3] == 0.0f && K9[6] == 0.0f && K9[7] == 0.0f && K9[8] == 1.0f; }
 
-PF_HD void pf_project(const float* __restrict__ K9, bool kstd, const pf_pose& T, float X, float Y, float Z, float& u, float& v)
+PF_HD void pf_to_camera(const pf_pose& T, float X, float Y, float Z, float& xc, float& yc, float& zc)
 {
-  float xc = fmaf(T.p[0], X, fmaf(T.p[1], Y, fmaf(T.p[2], Z, T.p[3])));
-  float yc = fmaf(T.p[4], X, fmaf(T.p[5], Y, fmaf(T.p[6], Z, T.p[7])));
-  float zc = fmaf(T.p[8], X, fmaf(T.p[9], Y, fmaf(T.p[10], Z, T.p[11])));
+  xc = fmaf(T.p[0], X, fmaf(T.p[1], Y, fmaf(T.p[2], Z, T.p[3])));
+  yc = fmaf(T.p[4], X, fmaf(T.p[5], Y, fmaf(T.p[6], Z, T.p[7])));
+  zc = fmaf(T.p[8], X, fmaf(T.p[9], Y, fmaf(T.p[10], Z, T.p[11])));
+}
+PF_HD void pf_to_pixel(const float* __restrict__ K9, bool kstd, float xc, float yc, float zc, float& u, float& v)
+{
   float p0, p1, p2;
   if (kstd) {
     p0 = fmaf(K9[0], xc, K9[2] * zc);
@@ -217,9 +296,15 @@ PF_HD void pf_project(const float* __restrict__ K9, bool kstd, const pf_pose& T,
     p1 = fmaf(K9[3], xc, fmaf(K9[4], yc, K9[5] * zc));
     p2 = fmaf(K9[6], xc, fmaf(K9[7], yc, K9[8] * zc));
   }
-  const float r = 1.0f / p2;
+  const float r = pf_rcp_nr(p2);
   u = p0 * r;
   v = p1 * r;
+}
+PF_HD void pf_project(const float* __restrict__ K9, bool kstd, const pf_pose& T, float X, float Y, float Z, float& u, float& v)
+{
+  float xc, yc, zc;
+  pf_to_camera(T, X, Y, Z, xc, yc, zc);
+  pf_to_pixel(K9, kstd, xc, yc, zc, u, v);
 }
 
 // Forward plumb_bob distortion of a projected pixel (row f3): the model of LEDDetector::distortPoints
@@ -247,7 +332,12 @@ struct pf_score_cfg {
   float tol, inv_tol;   // back_projection_pixel_tolerance_ (gain)        :2416
   float tol_pf;         // back_projection_pixel_tolerance_PF (gate)      :2414
   unsigned dg_mask;     // bMarkerDowngrade bits (first five LEDs only)   :2431
+  float led_base[PF_MAX_LED];   // L, or L - 2 for a downgraded LED: the constant part of an accepted LED's term (:2416, :2431-2432)
 };
+PF_HD void pf_score_cfg_finish(pf_score_cfg& sc, int L)
+{
+  for (int j = 0; j < PF_MAX_LED; ++j) sc.led_base[j] = (float)((j < 5 && ((sc.dg_mask >> j) & 1u)) ? L - 2 : L);
+}
 
 // Greedy part (:2409-2438) on the per-LED nearest-blob results (m[j] = squared distance >= 0 or
 // +inf, am[j] = blob index < 65536).  The reference takes the LEDs in ascending (distance, LED)
@@ -310,6 +400,53 @@ PF_HD float pf_greedy(const float* m, const int* am, int D, const pf_score_cfg& 
   return P;
 }
 
+// The weight alone, without the sort.  The greedy loop accepts LEDs in ascending distance order until the first one
+// beyond the gate: the accepted set is simply {j : d_j <= tol_PF}, every accepted LED contributes L + g_j^2 (- 2 if
+// downgraded), and the shared-blob penalty 3 + 6 + ... (:2421-2424) depends only on HOW MANY accepted LEDs find their
+// blob already taken by an earlier one = accepted - distinct blobs among them, whatever the order.  What the order does
+// change is the FP32 rounding of the sum (terms are added in LED order here), far below the 1e-5 bar against the FP64
+// reference.  Used by the score pass of every particle; the winner's correspondences still come from pf_greedy.
+template <int L>
+PF_HD float pf_weight_unordered(const float* m, const int* am, int steps, const pf_score_cfg& sc)
+{
+  // steps = min(D, L) (:2409).  With fewer detections than LEDs only the `steps` nearest LEDs (ascending distance, ties
+  // to the smaller LED index) are looked at: rank_j = number of LEDs that precede j in that order.
+  int rank[L];
+  PF_UNROLL
+  for (int j = 0; j < L; ++j) rank[j] = 0;
+  if (steps < L) {
+    PF_UNROLL
+    for (int i = 0; i < L; ++i) {
+      PF_UNROLL
+      for (int j = i + 1; j < L; ++j) {
+        const bool i_first = m[i] <= m[j] || !(m[j] == m[j]);   // NaN distances sort last
+        rank[j] += i_first ? 1 : 0;
+        rank[i] += i_first ? 0 : 1;
+      }
+    }
+  }
+  float P = 0.0f;
+  int key[L];
+  PF_UNROLL
+  for (int j = 0; j < L; ++j) {
+    const float d = pf_sqrt_fast(m[j]);                                  // :2412
+    const bool acc = d <= sc.tol_pf && rank[j] < steps;                  // :2414 (NaN / inf: not accepted)
+    const float g = (sc.tol - d) * sc.inv_tol;
+    const float t = fmaf(g, g, sc.led_base[j]);                          // :2416, :2431-2432
+    P += acc ? t : 0.0f;
+    key[j] = acc ? am[j] : -1 - j;                                       // rejected LEDs never match anything
+  }
+  int dup = 0;
+  PF_UNROLL
+  for (int k = 1; k < L; ++k) {
+    bool taken = false;
+    PF_UNROLL
+    for (int q = 0; q < k; ++q) taken = taken || (key[q] == key[k]);
+    dup += taken ? 1 : 0;
+  }
+  return P - 1.5f * (float)(dup * (dup + 1));                            // 3 * (1 + 2 + ... + dup), :2423-2424
+}
+
 template <int L, bool WANT_PAIRS>
 PF_HD float pf_score(const pf_f2* __restrict__ blobs, int D, const float* u, const float* v,
                      const pf_score_cfg& sc, unsigned* pairs, int* npairs)
@@ -327,6 +464,7 @@ PF_HD float pf_score(const pf_f2* __restrict__ blobs, int D, const float* u, con
       if (d2 < m[j]) { m[j] = d2; am[j] = i; }
     }
   }
+  if (!WANT_PAIRS) return pf_weight_unordered<L>(m, am, D < L ? D : L, sc);
   return pf_greedy<L, WANT_PAIRS>(m, am, D, sc, pairs, npairs);
 }
 
@@ -341,7 +479,7 @@ PF_HD float pf_score(const pf_f2* __restrict__ blobs, int D, const float* u, con
 PF_HD long long pf_w_to_fx(float w)
 {
 #if defined(__CUDA_ARCH__)
-  return __double2ll_rn((double)w * 1073741824.0);
+  return __float2ll_rn(w * 1073741824.0f);     // the scaling is exact (power of two), one rounding: same value as the FP64 form
 #else
   return (long long)llrint((double)w * 1073741824.0);
 #endif
@@ -354,6 +492,8 @@ struct pf_resample_cfg {
   double Sabs;       // (double)|S_fx|
   double NdS;        // Nd / Sabs (estimate only; the threshold test itself is exact)
   double margin;     // fast-path guard, see pf_count_leq
+  double invN;       // 1 / Nd (estimate only)
+  int nd;            // radix-512 digits of the largest skip exponent 2 (N - 1) (pf_rng_skip_nd)
 };
 
 PF_HD pf_resample_cfg pf_make_resample_cfg(uint32_t x_base, int N, long long S_fx)
@@ -366,12 +506,19 @@ PF_HD pf_resample_cfg pf_make_resample_cfg(uint32_t x_base, int N, long long S_f
   c.Sabs = (double)a;
   c.NdS = c.Nd / (c.Sabs > 0 ? c.Sabs : 1.0);
   c.margin = 8.0 * 2.220446049250313e-16 * c.Nd + 2.0 * c.NdS + 1e-12;
+  c.invN = 1.0 / c.Nd;
+  c.nd = N <= (1 << 17) ? 2 : (N <= (1 << 26) ? 3 : 4);
   return c;
 }
 
 // t_k = ceil( ((k + r_k)/N) * |S_fx| ), r_k = draw k of randResample (:671), double ops as in
 // the reference ((k + r)/N is an IEEE add and an IEEE divide).  Non-decreasing in k.
-PF_HD long long pf_threshold(int k, const pf_resample_cfg& rc, const uint32_t* __restrict__ tab)
+#if defined(__CUDA_ARCH__)
+#define PF_HD_COLD __device__ __noinline__     /* rare paths: one out-of-line copy keeps the hot loop's code small */
+#else
+#define PF_HD_COLD inline
+#endif
+PF_HD_COLD long long pf_threshold(int k, const pf_resample_cfg& rc, const uint32_t* __restrict__ tab)
 {
   uint32_t x = pf_rng_skip(rc.x_base, 2ull * (uint64_t)k, tab);
   uint32_t g1 = pf_rng_next(x), g2 = pf_rng_next(g1);
@@ -397,8 +544,21 @@ PF_HD int pf_count_leq(long long m, const pf_resample_cfg& rc, const uint32_t* _
   int kf;
   if (!(x < rc.Nd)) kf = rc.N; else kf = (int)x;   // floor, x >= 0
   double frac = x - (double)kf;
-  if (kf < rc.N && frac > rc.margin && frac < 1.0 - rc.margin)
+  if (kf < rc.N && frac > rc.margin && frac < 1.0 - rc.margin) {
+    // The answer is kf + [t_kf <= m].  t_kf = ceil(td) with td = ((kf + r) / N) * |S|, and for the integer m
+    // ceil(td) <= m  <=>  td <= m.  td is first estimated with reciprocal multiplications instead of the two
+    // divisions (relative error below 1e-15: six roundings + two rounded constants); the estimate decides unless it
+    // lies within 4e-15 relative of m, in which case the exact, division-based threshold does.
+    const uint32_t xs = pf_rng_skip_nd(rc.x_base, 2u * (uint32_t)kf, tab, rc.nd);   // 2 kf < 2^31 - 2: no reduction needed
+    const uint32_t g1 = pf_rng_next(xs), g2 = pf_rng_next(g1);
+    const double sum = (double)(g1 - 1u) + (double)(g2 - 1u) * 2147483646.0;
+    const double r = sum * (1.0 / (2147483646.0 * 2147483646.0));
+    const double td = ((double)kf + r) * rc.invN * rc.Sabs;
+    const double md = (double)m, band = td * 4.0e-15;
+    if (td < md - band) return kf + 1;
+    if (td > md + band) return kf;
     return kf + (pf_threshold(kf, rc, tab) <= m ? 1 : 0);
+  }
   int K = kf;
   while (K < rc.N && pf_threshold(K, rc, tab) <= m) ++K;
   while (K > 0 && pf_threshold(K - 1, rc, tab) > m) --K;

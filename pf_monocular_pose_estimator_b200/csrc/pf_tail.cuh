@@ -342,6 +342,7 @@ struct pf_frame_const {
 };
 #define PF_FC_CAM_IDENTITY 1u                /* camMoveInv is exactly I: C*E == E bit for bit, product skipped */
 #define PF_FC_SMALL_ANG 2u                   /* every angle draw of the frame is within +-0.3 rad              */
+#define PF_FC_TINY_ANG 4u                    /* ... within +-0.03 rad (the default noise ranges)               */
 
 // ---------------------------------------------------------------------------------------
 // frame constants from tracker inputs (host: pfmpe_update; device: track-mode tail)
@@ -377,6 +378,6 @@ PF_HD void pf_make_frame_const(pf_frame_const& fc, const pf_aff& cur, const pf_a
   bool ident = true;
   for (int i = 0; i < 12; ++i) ident = ident && (C.a[i] == ((i == 0 || i == 5 || i == 10) ? 1.0 : 0.0));
   const double amax = (fabs(alo) > fabs(ahi) ? fabs(alo) : fabs(ahi)) * (1.0 + 0.025 * 7);   // scale <= 1.175 (:563)
-  fc.flags = (ident ? PF_FC_CAM_IDENTITY : 0u) | (amax <= 0.3 ? PF_FC_SMALL_ANG : 0u);
+  fc.flags = (ident ? PF_FC_CAM_IDENTITY : 0u) | (amax <= 0.3 ? PF_FC_SMALL_ANG : 0u) | (amax <= 0.03 ? PF_FC_TINY_ANG : 0u);
 }
 

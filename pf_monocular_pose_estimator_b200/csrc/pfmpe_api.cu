@@ -141,17 +141,6 @@ int fail(pfmpe_handle* h, int code, const char* msg)
   return code;
 }
 
-void build_rng_table(uint32_t* tab)
-{
-  uint32_t base = PF_RNG_A;
-  for (int d = 0; d < 4; ++d) {
-    tab[d * 256] = 1u;
-    for (int v = 1; v < 256; ++v) tab[d * 256 + v] = pf_modmul(tab[d * 256 + v - 1], base);
-    uint32_t nb = pf_modmul(tab[d * 256 + 255], base);   // base^256
-    base = nb;
-  }
-}
-
 template <typename T>
 cudaError_t dev_alloc(T** p, size_t n)
 {
@@ -200,6 +189,7 @@ void fill_kparams(const pfmpe_handle* h, pf_kparams& p)
   unsigned m = 0;
   for (int i = 0; i < 5; ++i) if (h->prm.marker_downgrade[i]) m |= 1u << i;
   p.score.dg_mask = m;
+  pf_score_cfg_finish(p.score, h->cfg.n_leds);
   p.min_ang = h->prm.min_angular_noise; p.max_ang = h->prm.max_angular_noise;
   p.min_tr = h->prm.min_transition_noise; p.max_tr = h->prm.max_transition_noise;
   p.rng_tab = h->rng_tab;
@@ -220,14 +210,16 @@ template <int SH>
 frames_kernel_t kernel_for_sh(int L)
 {
   switch (L) {
+#ifndef PF_DEV_ONLY_L5   /* development builds (make DEV=1) instantiate the 5-LED kernels only: 8x shorter compile */
     case 1: return pf_frames_kernel<1, SH>;
     case 2: return pf_frames_kernel<2, SH>;
     case 3: return pf_frames_kernel<3, SH>;
     case 4: return pf_frames_kernel<4, SH>;
-    case 5: return pf_frames_kernel<5, SH>;
     case 6: return pf_frames_kernel<6, SH>;
     case 7: return pf_frames_kernel<7, SH>;
     case 8: return pf_frames_kernel<8, SH>;
+#endif
+    case 5: return pf_frames_kernel<5, SH>;
     default: return nullptr;
   }
 }
@@ -284,12 +276,14 @@ int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_f
   if (distort && mode != 0) return fail(h, PFMPE_ERR_UNSUPPORTED, "PFMPE_FLAG_DISTORT: per-frame API only (the Gauss-Newton tail needs undistorted points)");
   frames_kernel_t k = kernel_for(h->cfg.n_leds, mode >= 3 ? 1 : (distort ? 2 : 0));
   if (!k) return fail(h, PFMPE_ERR_UNSUPPORTED, "n_leds must be 1..8");
-  const size_t smem = (size_t)h->cfg.max_blobs * sizeof(pf_blob);
+  const size_t smem = pf_blob_smem_bytes(h->cfg.max_blobs);
   bool grid_mode;
   if (h->force_mode == 1) grid_mode = false;
   else if (h->force_mode == 2) grid_mode = true;
   else grid_mode = (nt == 1) ? (N > 1024) : (N > 16384);
   if (!grid_mode && mode < 3 && !distort) k = kernel_for(h->cfg.n_leds, 3);   // batch shape: the 64-register build
+  if (smem > 48 * 1024)   // candidate lists of a large max_blobs: opt in to more than the default 48 KB of dynamic shared memory
+    PF_CUDA(h, cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 
   pf_kparams p;
   fill_kparams(h, p);
@@ -522,7 +516,7 @@ int pfmpe_create(const pfmpe_config* cfg, pfmpe_handle** out)
   PF_TRY(dev_alloc(&h->result, T));
   PF_TRY(dev_alloc(&h->obj_f, T * PF_MAX_LED * 3));
   PF_TRY(dev_alloc(&h->obj_d, T * PF_MAX_LED * 3));
-  PF_TRY(dev_alloc(&h->rng_tab, 1024));
+  PF_TRY(dev_alloc(&h->rng_tab, PF_RNG_TAB_WORDS));
   PF_TRY(dev_alloc(&h->roi_keys, T * 4));
   PF_TRY(dev_alloc(&h->roi_out, T * 4));
   PF_TRY(cudaMallocHost((void**)&h->h_roi, T * 4 * sizeof(float)));
@@ -547,14 +541,14 @@ int pfmpe_create(const pfmpe_config* cfg, pfmpe_handle** out)
   std::memset(h->h_state, 0, T * sizeof(pf_tracker_state));
   PF_TRY(cudaMemcpy(h->state, h->h_state, T * sizeof(pf_tracker_state), cudaMemcpyHostToDevice));
   {
-    std::vector<uint32_t> tab(1024);
-    build_rng_table(tab.data());
+    std::vector<uint32_t> tab(PF_RNG_TAB_WORDS);
+    pf_build_rng_table(tab.data());
     if (pf_rng_skip(1u, 384, tab.data()) != PF_RNG_A384) {
       g_create_err = "pfmpe_create: RNG stride constant mismatch";
       free_all(h); delete h;
       return PFMPE_ERR_INVALID;
     }
-    PF_TRY(cudaMemcpy(h->rng_tab, tab.data(), 1024 * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    PF_TRY(cudaMemcpy(h->rng_tab, tab.data(), PF_RNG_TAB_WORDS * sizeof(uint32_t), cudaMemcpyHostToDevice));
   }
 #undef PF_TRY
   *out = h;

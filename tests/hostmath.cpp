@@ -11,16 +11,6 @@
 
 namespace {
 
-void build_rng_table(uint32_t* tab)
-{
-  uint32_t base = PF_RNG_A;
-  for (int d = 0; d < 4; ++d) {
-    tab[d * 256] = 1u;
-    for (int v = 1; v < 256; ++v) tab[d * 256 + v] = pf_modmul(tab[d * 256 + v - 1], base);
-    base = pf_modmul(tab[d * 256 + 255], base);
-  }
-}
-
 template <int L>
 float score_particle(const pf_pose& T, const float* K9f, const float* obj, const pf_f2* blobs, int D,
                      const pf_score_cfg& sc, unsigned* pairs, int* npairs)
@@ -28,7 +18,11 @@ float score_particle(const pf_pose& T, const float* K9f, const float* obj, const
   float u[L], v[L];
   const bool kstd = pf_k_is_std(K9f);
   for (int j = 0; j < L; ++j) pf_project(K9f, kstd, T, obj[3 * j], obj[3 * j + 1], obj[3 * j + 2], u[j], v[j]);
-  return pf_score<L, true>(blobs, D, u, v, sc, pairs, npairs);
+  // the device computes every particle's weight with the unsorted form (D >= L) and only the winner's correspondences
+  // with the sorted greedy loop: same here
+  const float wgt = pf_score<L, false>(blobs, D, u, v, sc, nullptr, nullptr);
+  (void)pf_score<L, true>(blobs, D, u, v, sc, pairs, npairs);
+  return wgt;
 }
 
 template <int L>
@@ -37,8 +31,8 @@ int frame(int N, int D, const double* markers, const double* K9, const double* b
           uint32_t seed, const double* prm, const int* dg, float* T_out, float* w_out, int* kend_out, int* idx_out,
           int* sc_out, long long* sum_fx, unsigned* pairs_out)
 {
-  std::vector<uint32_t> tab(1024);
-  build_rng_table(tab.data());
+  std::vector<uint32_t> tab(PF_RNG_TAB_WORDS);
+  pf_build_rng_table(tab.data());
   pf_frame_const fc;
   pf_make_frame_const(fc, pf_aff_from_cm16(cur), pf_aff_from_cm16(pred), pf_aff_from_cm16(P), pf_aff_from_cm16(C), isi,
                       dt, seed, D, prm[0], prm[1], prm[2], prm[3]);
@@ -46,6 +40,7 @@ int frame(int N, int D, const double* markers, const double* K9, const double* b
   sc.tol = (float)prm[4]; sc.inv_tol = (float)(1.0 / prm[4]); sc.tol_pf = (float)prm[5];
   sc.dg_mask = 0;
   for (int i = 0; i < 5; ++i) if (dg[i]) sc.dg_mask |= 1u << i;
+  pf_score_cfg_finish(sc, L);
   float K9f[9], obj[PF_MAX_LED * 3];
   for (int i = 0; i < 9; ++i) K9f[i] = (float)K9[i];
   for (int i = 0; i < 3 * L; ++i) obj[i] = (float)markers[i];
@@ -59,7 +54,8 @@ int frame(int N, int D, const double* markers, const double* K9, const double* b
 
   auto pass = [&](int it, float& maxw, int& argmax, int& argmin, long long& S) {
     const bool use_cam = fc.isi > 1, use_pred = use_cam && (it % 10) != 0;
-    const bool cam_mul = use_cam && !(fc.flags & PF_FC_CAM_IDENTITY), small_ang = (fc.flags & PF_FC_SMALL_ANG) != 0;
+    const bool cam_mul = use_cam && !(fc.flags & PF_FC_CAM_IDENTITY);
+    const int ang_mode = (fc.flags & PF_FC_TINY_ANG) ? 2 : ((fc.flags & PF_FC_SMALL_ANG) ? 1 : 0);
     const float scale = 1.0f + 0.025f * (float)(it / 10);
     const uint64_t step0 = 12ull * (uint64_t)(N - 2) * (uint64_t)it;
     S = 0;
@@ -73,7 +69,7 @@ int frame(int N, int D, const double* markers, const double* K9, const double* b
         if (cam_mul) B = pf_affine_mul(Cm, B);
         if (use_pred) B = pf_affine_mul(B, Pm);
         uint32_t x = pf_rng_skip(fc.seed_state, step0 + 12ull * (uint64_t)(n - 2), tab.data());
-        Tn = pf_propagate(B, x, fc.noise, scale, small_ang);
+        Tn = pf_propagate(B, x, fc.noise, scale, ang_mode);
       }
       T[n] = Tn;
       unsigned pr[2 * PF_MAX_LED]; int np;
@@ -150,8 +146,8 @@ int hm_frame(int N, int L, int D, const double* markers, const double* K9, const
 // resampling stage alone on given raw FP32 weights: kend + source indices
 int hm_resample(int N, const float* w, uint32_t seed, int iters, int* kend_out, int* idx_out, long long* sum_fx)
 {
-  std::vector<uint32_t> tab(1024);
-  build_rng_table(tab.data());
+  std::vector<uint32_t> tab(PF_RNG_TAB_WORDS);
+  pf_build_rng_table(tab.data());
   long long S = 0;
   for (int i = 0; i < N; ++i) S += pf_w_to_fx(w[i]);
   *sum_fx = S;
@@ -179,8 +175,8 @@ int hm_resample(int N, const float* w, uint32_t seed, int iters, int* kend_out, 
 
 uint32_t hm_rng_skip(uint32_t x, uint64_t steps)
 {
-  std::vector<uint32_t> tab(1024);
-  build_rng_table(tab.data());
+  std::vector<uint32_t> tab(PF_RNG_TAB_WORDS);
+  pf_build_rng_table(tab.data());
   return pf_rng_skip(x, steps, tab.data());
 }
 
