@@ -240,6 +240,7 @@ struct pf_blobtab {
   float kx, c0, r;
   int D, ncol;
   unsigned desc[PF_NCOL];                                  // (count << 16) | start into cand[]; during the build: counts
+  unsigned start[PF_NCOL];                                 // build scratch
 };
 // cand[0] is a sentinel record at infinity: an empty column points to it with count 0, so that a query can load and
 // test "the first candidate" unconditionally (distance +inf) and only loops for a second, third, ... candidate.
@@ -255,13 +256,17 @@ __device__ __forceinline__ unsigned pf_col(const pf_blobtab& bt, float x)
   return min(c, (unsigned)(bt.ncol - 1));
 }
 
-// executed by ALL threads of the CTA (contains __syncthreads); bsrc: D x 2 doubles in global memory
+// executed by ALL threads of the CTA (contains __syncthreads); bsrc: D x 2 doubles in global memory.
+// Counting sort by column, parallel over the blobs: every blob adds itself to the counters of the (at most three)
+// columns it touches, warp 0 turns the counters into list starts, and every (blob, column) pair finds its place in the
+// list -- ascending blob index -- as the number of lower-numbered blobs that touch the same column.
 __device__ __noinline__ void pf_stage_blobs(const double* bsrc, int D, float tol_pf, pf_blobtab& bt, pf_blob* blobs, int d_max)
 {
   pf_blob* cand = blobs + d_max;
   unsigned short* span = reinterpret_cast<unsigned short*>(cand + 1 + (size_t)PF_CAND_PER_BLOB * d_max);
   const int tid = threadIdx.x, nt = blockDim.x;
   if (tid == 0) { pf_blob z; z.x = INFINITY; z.y = INFINITY; z.idx = 0; z.pad = 0; cand[0] = z; }
+  for (int c = tid; c < PF_NCOL; c += nt) bt.desc[c] = 0u;
   for (int i = tid; i < D; i += nt) {
     pf_blob b;
     b.x = (float)bsrc[2 * i]; b.y = (float)bsrc[2 * i + 1]; b.idx = i; b.pad = 0;
@@ -294,15 +299,9 @@ __device__ __noinline__ void pf_stage_blobs(const double* bsrc, int D, float tol
   __syncthreads();
   for (int i = tid; i < D; i += nt) {
     const float x = blobs[i].x;
-    span[i] = (unsigned short)(pf_col(bt, x - bt.r) | (pf_col(bt, x + bt.r) << 8));
-  }
-  __syncthreads();
-  // one thread per column: count, (ordered prefix by warp 0), fill -- the fill scans the blobs in index order
-  int cnt = 0;
-  if (tid < PF_NCOL) {
-    if (tid < bt.ncol)
-      for (int i = 0; i < D; ++i) { const unsigned sp = span[i]; cnt += ((sp & 255u) <= (unsigned)tid && (unsigned)tid <= (sp >> 8)) ? 1 : 0; }
-    bt.desc[tid] = (unsigned)cnt;
+    const unsigned clo = pf_col(bt, x - bt.r), chi = pf_col(bt, x + bt.r);
+    span[i] = (unsigned short)(clo | (chi << 8));
+    for (unsigned c = clo; c <= chi && c < clo + PF_CAND_PER_BLOB; ++c) atomicAdd(&bt.desc[c], 1u);
   }
   __syncthreads();
   if (tid < 32) {
@@ -317,20 +316,23 @@ __device__ __noinline__ void pf_stage_blobs(const double* bsrc, int D, float tol
     }
     int run = inc - sum + 1;                                 // lists start behind the sentinel
 #pragma unroll
-    for (int q = 0; q < PF_NCOL / 32; ++q) { bt.desc[tid * (PF_NCOL / 32) + q] = (unsigned)run; run += h[q]; }
+    for (int q = 0; q < PF_NCOL / 32; ++q) {
+      const int c = tid * (PF_NCOL / 32) + q;
+      bt.start[c] = (unsigned)run;
+      bt.desc[c] = h[q] > 0 ? (((unsigned)h[q] << 16) | (unsigned)run) : 0u;
+      run += h[q];
+    }
   }
   __syncthreads();
-  if (tid < PF_NCOL) {
-    const int start = (int)bt.desc[tid];
-    int k = start;
-    const int cap = 1 + PF_CAND_PER_BLOB * d_max;            // never reached (<= 3 columns per blob); memory safety only
-    if (tid < bt.ncol)
-      for (int i = 0; i < D; ++i) {
-        const unsigned sp = span[i];
-        if ((sp & 255u) <= (unsigned)tid && (unsigned)tid <= (sp >> 8) && k < cap) cand[k++] = blobs[i];
-      }
-    __syncwarp();
-    bt.desc[tid] = k > start ? (((unsigned)(k - start) << 16) | (unsigned)start) : 0u;
+  for (int t = tid; t < PF_CAND_PER_BLOB * D; t += nt) {
+    const int i = t / PF_CAND_PER_BLOB;
+    const unsigned sp = span[i];
+    const unsigned c = (sp & 255u) + (unsigned)(t - i * PF_CAND_PER_BLOB);
+    if (c <= (sp >> 8)) {
+      int rank = 0;
+      for (int q = 0; q < i; ++q) { const unsigned sq = span[q]; rank += ((sq & 255u) <= c && c <= (sq >> 8)) ? 1 : 0; }
+      cand[bt.start[c] + rank] = blobs[i];
+    }
   }
   __syncthreads();
 }

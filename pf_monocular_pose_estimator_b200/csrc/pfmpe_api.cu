@@ -350,7 +350,11 @@ int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_f
     PF_CUDA(h, cudaGetLastError());
     h->launches += 1;
   } else {
-    const int block = PF_GRID_BLOCK, warps = block / 32;
+    int block = PF_GRID_BLOCK;
+    if (const char* e = std::getenv("PFMPE_GRID_BLOCK")) {   // experiment: the 64-register build, 256-thread CTAs, 4 per SM
+      if (std::atoi(e) == 256 && mode < 3 && !distort) { block = 256; k = kernel_for(h->cfg.n_leds, 3); }
+    }
+    const int warps = block / 32;
     int per_sm = 0;
     PF_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, block, smem));
     int cap = per_sm * h->num_sms;
