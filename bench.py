@@ -3,29 +3,31 @@
 
 A "step" is one PF frame update -- the do/while of fused propagate -> project -> score passes, the
 exact weight sum, stratified resampling and the most-resampled winner (pose_estimator.cpp:475-689) --
-of the workload's filter(s) on synthetic detections.  PME = particles x LEDs x iterations executed.
+of every filter of the workload on synthetic detections.  PME = particles x LEDs x iterations executed.
 
-Workloads (BASELINE.json configs):
-  cfg2  configs[1]  README 5-LED scene, 1e5 particles, 1 tracker, 15 blobs, 1000-frame trajectory  [default]
-  cfg1  configs[0]  same scene, 100 particles (the reference's own CPU-runnable case)
-  cfg3  configs[2]  5 LEDs + 200 spurious blobs, 1e6 particles
-  cfg4  configs[3]  4096 independent trackers x 4096 particles, sharded by tracker across the ranks
-  cfg5s configs[4]  single filter with 2^26 particles, on one GPU
-With --gpus N > 1 the default stays cfg2: every rank tracks its own independent sequence (tracker id =
-rank: phase-shifted trajectory, own seeds) -- weak scaling, no data-path collective; torch.distributed
-(NCCL) is used for the barrier and the max-over-ranks time only.  A short cfg4 run is reported alongside
-under "batched_trackers" (strong scaling: 4096 trackers split over the ranks).
+Headline workload (every --gpus N): cfg4 = BASELINE configs[3], 4096 independent trackers x 4096 particles,
+the configuration BASELINE.json quotes the metric on at 1/2/4/8 B200 ("near-linear scaling to 8 GPUs on the
+batched-tracker config").  The trackers are split evenly over the ranks -- strong scaling, no data-path
+collective; torch.distributed (NCCL) carries the barrier and the max-over-ranks time only.
+Alongside, each with its own value / ms_per_step / roofline / e2e (/ cpu_baseline on one GPU):
+  single_filter   cfg2  configs[1]  README 5-LED scene, 1e5 particles, 15 blobs: the latency half of the metric (p50)
+  outlier_heavy   cfg3  configs[2]  5 LEDs + 200 spurious blobs, 1e6 particles
+  sharded_filter  cfg5  configs[4]  ONE filter of 2^26 particles sharded by particle over the ranks
+  cpu_case        cfg1  configs[0]  100 particles (the reference's own CPU-runnable case)
+  p3p_vote        row f4: the correspondence vote of the brute-force initialisation, 205 detections
 
 value : PF updates alone with every input resident in HBM when the timed region starts (detections,
-        per-frame poses/prediction/seeds from the log of an untimed tracked run): one launch per step,
-        device time from CUDA events on the launching stream, L2 flushed between steps when the filter
-        state fits L2.
+        per-frame poses / prediction / seeds from the log of an untimed tracked run): one launch per step,
+        device time from CUDA events on the launching stream, max over ranks; L2 flushed between steps when
+        the filter state fits L2.
 e2e   : the same metric through the reference-facing per-frame call with HOST buffers
-        (pfmpe_track_frame_host, looped in C): per step the detections and poses go host->device, the
-        result record comes back device->host, and the reference's FP64 host tail (Gauss-Newton +
-        predictPose) runs between two updates.
---impl reference : the reference's CPU algorithm (oracle port, see oracle/pf_oracle.h) on the host cores,
-        same workload / metric / unit.
+        (pfmpe_track_frame_host(_batch), looped in C by pfmpe_track_sequence_host): per step the detections go
+        host->device, the result records come back device->host, and the reference's FP64 host tail
+        (predictPose before, Gauss-Newton after the update) runs for every tracker.  Wall clock.
+cpu_baseline / --impl reference : the reference's CPU algorithm (oracle port, oracle/pf_oracle.c) on the host
+        cores, same workload / metric / unit, O(N) resampler (the literal O(N^2) scan of :668-682 is timed by
+        tools/cpu_faithful.py).  Pairing: compare `e2e` with the reference arm (both are whole
+        tracked frames from host buffers, Gauss-Newton included); `value` and `roofline` explain the kernel.
 """
 import argparse
 import json
@@ -44,12 +46,12 @@ from pf_monocular_pose_estimator_b200 import scenes as S  # noqa: E402
 
 L_LED = 5
 WORKLOADS = {
-    # name: (particles, trackers, outliers, default frames)
-    "cfg1": (100, 1, 10, 1000),
-    "cfg2": (100_000, 1, 10, 1000),
-    "cfg3": (1_000_000, 1, 200, 200),
-    "cfg4": (4096, 4096, 10, 100),
-    "cfg5s": (1 << 26, 1, 10, 50),
+    # name: (particles, trackers, outliers)
+    "cfg1": (100, 1, 10),
+    "cfg2": (100_000, 1, 10),
+    "cfg3": (1_000_000, 1, 200),
+    "cfg4": (4096, 4096, 10),
+    "cfg5s": (1 << 26, 1, 10),
 }
 WORKLOAD_DESC = {
     "cfg1": "BASELINE configs[0]: 5-LED README scene, 100 particles, 1 tracker, 15 blobs",
@@ -59,6 +61,8 @@ WORKLOAD_DESC = {
     "cfg5s": "BASELINE configs[4] on one GPU: single filter with 2^26 particles",
 }
 STATE_BYTES_PER_PARTICLE = 108
+MIN_SUB_STEPS = 50                  # sub-lines run at least this many timed steps whatever --steps says
+MIN_E2E_FRAMES = {"cfg1": 300, "cfg2": 300, "cfg3": 60, "cfg4": 60}
 
 
 def alg_bytes_per_frame(n_particles, iters):
@@ -75,11 +79,13 @@ def peaks():
 
 def profiled_traffic(workload):
     """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture (or None)."""
-    p = os.path.join(ROOT, "profiles", "r01_traffic.json")
-    try:
-        return float(json.load(open(p))[workload]["dram_bytes_per_launch"])
-    except Exception:
-        return None
+    for name in ("r02_traffic.json", "r01_traffic.json"):
+        try:
+            d = json.load(open(os.path.join(ROOT, "profiles", name)))[workload]
+            return float(d["dram_bytes_per_launch"]), "profiles/" + name + (": " + d["note"] if "note" in d else "")
+        except Exception:
+            continue
+    return None, None
 
 
 class ClockSampler:
@@ -135,14 +141,13 @@ def make_sequence(trackers, first_frame, n_frames, n_outliers):
 # ---------------------------------------------------------------------------------------------
 # CPU arm: the oracle port of the reference PF
 # ---------------------------------------------------------------------------------------------
-def cpu_run(workload, budget_s, threads, tracker0=0):
+def cpu_run(workload, budget_s, threads, tracker0=0, resampler=1, max_frames=400):
     """Time the reference's CPU algorithm (oracle port) on a bounded sample of the workload: `threads`
     independent filters (the reference itself is single-threaded), each stepping frames of its own
-    sequence until the time budget is used."""
+    sequence -- whole tracked frames: predictPose, PF update, Gauss-Newton -- until the time budget is used."""
     from oracle import orc
-    n_p, n_t, n_out, _ = WORKLOADS[workload]
+    n_p, n_t, n_out = WORKLOADS[workload]
     trackers = np.arange(tracker0, tracker0 + threads)
-    max_frames = 400
     frames, blobs, counts, times, seeds = make_sequence(trackers, 2, max_frames, n_out)
     sc0 = S.Scene()
     results = [None] * len(trackers)
@@ -151,7 +156,7 @@ def cpu_run(workload, budget_s, threads, tracker0=0):
         t = int(trackers[i])
         ph = S.tracker_phase(t)
         trk = orc.OracleTracker(n_p, S.MARKERS_5, S.K_README, sc0.params, S.true_pose(0.0, ph), 0.0,
-                                S.true_pose(S.DT, ph), S.DT, resampler=1)
+                                S.true_pose(S.DT, ph), S.DT, resampler=resampler)
         # one untimed frame (page-in), then time frames until the budget is used
         trk.frame(times[0], blobs[i, 0, : counts[i, 0]], int(seeds[i, 0]))
         pme, nfr, lat = 0, 0, []
@@ -180,23 +185,30 @@ def cpu_run(workload, budget_s, threads, tracker0=0):
     frames_done = sum(r[2] for r in results)
     return dict(value=pme / max(max(r[1] for r in results), 1e-9), cores=len(trackers), frames=frames_done,
                 p50_ms=1e3 * lat[len(lat) // 2], wall_s=wall,
-                sample="%d independent filter(s) (one per host thread) x %d frames of %s (%d particles each), O(N) resampler, "
-                       "double precision" % (len(trackers), results[0][2], workload, n_p))
+                sample="%d independent filter(s) (one per host thread) x %d tracked frames of %s (%d particles each, %d blobs): "
+                       "predictPose + PF update + Gauss-Newton, %s resampler, double precision"
+                       % (len(trackers), results[0][2], workload, n_p, L_LED + n_out,
+                          "O(N)" if resampler == 1 else "literal O(N^2) (:668-682)"))
+
+
+def cpu_baseline_obj(workload, budget_s, threads=1):
+    r = cpu_run(workload, budget_s=budget_s, threads=threads)
+    return {"value": r["value"], "unit": "PME/s", "cores": r["cores"], "kind": "port", "sample": r["sample"], "p50_ms": r["p50_ms"]}
 
 
 # ---------------------------------------------------------------------------------------------
 # B200 arm
 # ---------------------------------------------------------------------------------------------
-def gpu_measure(workload, trackers, K, W, dev, local_rank, barrier, flush_ok=True, with_track=True, e2e_steps=0, clocks=False):
+def gpu_measure(workload, trackers, K, W, dev, local_rank, barrier, flush_ok=True, with_track=True, e2e_frames=0, clocks=False):
     """Measure one workload on this rank's GPU for its local `trackers`.  Returns a dict of raw numbers."""
     import torch
     from pf_monocular_pose_estimator_b200 import capi
 
-    n_p, _, n_out, _ = WORKLOADS[workload]
+    n_p, _, n_out = WORKLOADS[workload]
     n_t = len(trackers)
     d_max = L_LED + n_out
     F = W + K
-    frames, blobs, counts, times, seeds = make_sequence(trackers, 2, F, n_out)
+    frames, blobs, counts, times, seeds = make_sequence(trackers, 2, max(F, W + e2e_frames), n_out)
 
     h = capi.Handle(n_p, n_trackers=n_t, n_leds=L_LED, max_blobs=d_max, device=local_rank)
     h.configure(S.MARKERS_5, S.K_README, S.DEFAULT_PARAMS)
@@ -209,10 +221,10 @@ def gpu_measure(workload, trackers, K, W, dev, local_rank, barrier, flush_ok=Tru
             h.track_init(S.true_pose(0.0, ph), 0.0, S.true_pose(S.DT, ph), S.DT, tracker=i)
 
     # inputs resident in HBM before any timed region
-    d_blobs = torch.from_numpy(blobs).to(dev)
-    d_counts = torch.from_numpy(counts).to(dev)
-    d_times = torch.from_numpy(times).to(dev)
-    d_seeds = torch.from_numpy(seeds.view(np.int32)).to(dev)
+    d_blobs = torch.from_numpy(np.ascontiguousarray(blobs[:, :F])).to(dev)
+    d_counts = torch.from_numpy(np.ascontiguousarray(counts[:, :F])).to(dev)
+    d_times = torch.from_numpy(times[:F]).to(dev)
+    d_seeds = torch.from_numpy(np.ascontiguousarray(seeds[:, :F]).view(np.int32)).to(dev)
     h.track_attach(F, d_blobs.data_ptr(), d_counts.data_ptr(), d_times.data_ptr(), d_seeds.data_ptr())
 
     state_bytes = n_p * n_t * STATE_BYTES_PER_PARTICLE
@@ -222,7 +234,7 @@ def gpu_measure(workload, trackers, K, W, dev, local_rank, barrier, flush_ok=Tru
         flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
         l2_note = "L2 flushed (256 MiB write, untimed) between steps; filter state is %.1f MB" % (state_bytes / 1e6)
 
-    out = dict(n_p=n_p, n_t=n_t, d_max=d_max, l2=l2_note)
+    out = dict(n_p=n_p, n_t=n_t, d_max=d_max, l2=l2_note, steps=K, warmup=W)
 
     # ---- (1) device-resident tracking (device FP64 tail), one launch per frame: also logs the per-frame constants
     init_all()
@@ -239,7 +251,6 @@ def gpu_measure(workload, trackers, K, W, dev, local_rank, barrier, flush_ok=Tru
     out["ok"] = all(r["status"] == 1 for rr in res for r in rr)
     out["mean_iter"] = float(iters.mean())
     out["track_ms"] = float(np.sum(track_ms)) if track_ms else None
-    out["track_p50_ms"] = float(np.median(track_ms)) if track_ms else None
 
     # ---- (2) value: replay of the PF updates alone (hot path), inputs resident, one launch per step
     init_all()
@@ -286,85 +297,129 @@ def gpu_measure(workload, trackers, K, W, dev, local_rank, barrier, flush_ok=Tru
     h.track_replay(W, K)
     out["single_ms"] = h.last_launch_ms()
 
-    # ---- (4) e2e: per-frame call with HOST buffers + host FP64 tail, looped in C
-    if e2e_steps > 0:
-        Ke = min(K, e2e_steps)
-        n_te = min(n_t, 256)          # bounded sample of the local trackers for the batched workloads
-        he = h
-        if n_te != n_t:
-            he = capi.Handle(n_p, n_trackers=n_te, n_leds=L_LED, max_blobs=d_max, device=local_rank)
-            he.configure(S.MARKERS_5, S.K_README, S.DEFAULT_PARAMS)
-        for i in range(n_te):
+    # ---- (4) e2e: per-frame call with HOST buffers + host FP64 tail for every local tracker, looped in C
+    if e2e_frames > 0:
+        Ke = e2e_frames
+        for i in range(n_t):
             ph = S.tracker_phase(int(trackers[i]))
-            he.track_init(S.true_pose(0.0, ph), 0.0, S.true_pose(S.DT, ph), S.DT, tracker=i)
-        he.sync()
-        bl = np.ascontiguousarray(blobs[:n_te])
-        arr, _ = he.track_sequence_host(times[:W], bl[:, :W], counts[:n_te, :W], seeds[:n_te, :W])        # warm-up
+            h.track_init(S.true_pose(0.0, ph), 0.0, S.true_pose(S.DT, ph), S.DT, tracker=i)
+        h.sync()
+        h.track_sequence_host(times[:W], np.ascontiguousarray(blobs[:, :W]), np.ascontiguousarray(counts[:, :W]),
+                              np.ascontiguousarray(seeds[:, :W]))                                       # warm-up
+        bl = np.ascontiguousarray(blobs[:, W:W + Ke])
+        cn = np.ascontiguousarray(counts[:, W:W + Ke])
+        sd = np.ascontiguousarray(seeds[:, W:W + Ke])
         barrier()
         t0 = time.perf_counter()
-        arr, secs = he.track_sequence_host(times[W:W + Ke], np.ascontiguousarray(bl[:, W:W + Ke]),
-                                           np.ascontiguousarray(counts[:n_te, W:W + Ke]), np.ascontiguousarray(seeds[:n_te, W:W + Ke]))
+        arr, secs = h.track_sequence_host(times[W:W + Ke], bl, cn, sd)
         torch.cuda.synchronize(dev)
         dt = time.perf_counter() - t0
-        r0 = he.unpack_track(arr, 0, Ke)
-        it_e = np.mean([r["iterations"] for r in r0])
-        out["e2e"] = dict(seconds=dt, pme=float(n_p) * L_LED * it_e * Ke * n_te, steps=Ke, trackers=n_te,
+        barrier()
+        it_e = np.mean([[r["iterations"] for r in h.unpack_track(arr, i, Ke)] for i in range(min(n_t, 16))])
+        r0 = h.unpack_track(arr, 0, Ke)
+        inline = n_t == 1 and d_max <= 32
+        out["e2e"] = dict(seconds=dt, pme=float(n_p) * L_LED * it_e * Ke * n_t, steps=Ke, trackers=n_t,
                           p50_ms=1e3 * float(np.median(secs)), ok=all(r["status"] == 1 for r in r0),
-                          h2d=int((224 + 16 * d_max) * n_te), d2h=int(808 * n_te))
-        if he is not h:
-            he.close()
+                          h2d=int((224 + 16 * d_max) * n_t), d2h=int(808 * n_t), inline=inline)
     h.close()
     del d_blobs, d_counts, d_times, d_seeds, flush
     torch.cuda.empty_cache()
     return out
 
 
-def sharded_filter_measure(world, rank, dev, local_rank, barrier, allreduce, RO, peak, n_global=1 << 26, K=10, W=3):
-    """BASELINE configs[4]: one filter of 2^26 particles, particle shards over the ranks (all_gather of the
-    64-byte partials = weight-sum exchange, all_to_all rebalance = global resample), driven by the same
-    reference-side loop (predictPose -> PF -> Gauss-Newton) as the e2e path.  Host blobs in, pose out."""
+E2E_PATH = ("pfmpe_track_frame_host(_batch) per frame from HOST buffers: host predictPose -> PF update launch (one tracker with <= 32 "
+            "detections: the frame's inputs travel inside the kernel parameter block; otherwise a pinned H2D copy) -> result records "
+            "written by the kernel into pinned host memory -> host Gauss-Newton (FP64) per tracker; looped in C by pfmpe_track_sequence_host")
+
+
+def contract(workload, m, world, reduce_max, reduce_sum, reduce_min, peak, peak_src):
+    """One measured workload -> the JSON object of the measurement contract (value, roofline, e2e, ...).  m holds this rank's raw
+    numbers; times are reduced with MAX over the ranks, work with SUM (world == 1: identity)."""
+    n_p, n_t_total, n_out = WORKLOADS[workload]
+    K = m["steps"]
+    (dev_ms, single_ms, track_ms) = reduce_max([m["dev_ms"], m["single_ms"], m["track_ms"] or 0.0])
+    (pme_total, launches) = reduce_sum([m["pme"], m["launches"]])
+    achieved = m["alg_bytes"] / (m["dev_ms"] * 1e-3) / 1e9            # this rank's GB/s
+    (achieved_min, ok) = reduce_min([achieved, 1.0 if m["ok"] else 0.0])
+    traffic, traffic_src = profiled_traffic(workload)
+    o = {"workload": workload, "desc": WORKLOAD_DESC[workload],
+         "value": pme_total / (dev_ms * 1e-3), "unit": "PME/s", "ms_per_step": dev_ms / K, "latency_p50_ms": m["p50_ms"],
+         "steps": K, "warmup": m["warmup"], "mean_iterations": m["mean_iter"], "max_iterations": m.get("max_iter"),
+         "gpu_launches": int(launches), "all_frames_accepted": bool(ok > 0), "launch": m["launch_info"], "l2": m["l2"],
+         "roofline": {"bound": "hbm", "achieved": achieved_min, "peak": peak, "unit": "GB/s", "frac": achieved_min / peak,
+                      "traffic": traffic, "traffic_source": traffic_src,
+                      "alg_bytes_per_launch": alg_bytes_per_frame(n_p, m["mean_iter"]) * m["n_t"], "peak_source": peak_src,
+                      "alg_bytes_per_particle_frame": alg_bytes_per_frame(1, m["mean_iter"]), "kernel": "pf_frames_kernel<5>",
+                      "note": "per GPU (slowest rank); SURVEY 8(d) algorithmic bytes (136 B per particle and frame at one "
+                              "iteration) / device time of the PF-update launches"},
+         "single_launch": {"value": pme_total / (single_ms * 1e-3), "ms_per_step": single_ms / K,
+                           "note": "all %d frames in one persistent launch, no L2 flush" % K},
+         "tracking": {"value": pme_total / (track_ms * 1e-3) if track_ms else None, "ms_per_step": track_ms / K if track_ms else None,
+                      "note": "device-resident tracking: PF update + FP64 Gauss-Newton / predictPose tail on the device, one launch per frame"}}
+    if "e2e" in m:
+        e = m["e2e"]
+        (e_sec,) = reduce_max([e["seconds"]])
+        (e_pme,) = reduce_sum([e["pme"]])
+        o["e2e"] = {"value": e_pme / e_sec, "unit": "PME/s", "h2d_bytes_per_step": e["h2d"], "d2h_bytes_per_step": e["d2h"],
+                    "steps": e["steps"], "ms_per_step": 1e3 * e_sec / e["steps"], "p50_ms": e["p50_ms"], "trackers_per_rank": e["trackers"],
+                    "all_frames_accepted": e["ok"], "path": E2E_PATH}
+    return o
+
+
+def sharded_filter_measure(world, rank, dev, local_rank, barrier, allreduce, RO, peak, n_global=1 << 26, K=MIN_SUB_STEPS, W=3):
+    """BASELINE configs[4]: one filter of 2^26 particles, particle shards over the ranks, driven by the C frame call
+    pfmpe_shard_track_frame_host (predictPose -> sharded PF update -> Gauss-Newton; host blobs in, pose + covariance out)."""
     import torch
     from pf_monocular_pose_estimator_b200 import scenes as S, sharded as SH
-    from tests.host_loop import HostTracker
     sc = S.Scene(0)
     comm = SH.TorchDist() if world > 1 else SH.Loopback(1)
     sf = SH.ShardedFilter(n_global, comm, n_leds=L_LED, max_blobs=sc.blobs(0).shape[0] + 4, device=local_rank)
     sf.configure(sc.markers, sc.K, sc.params)
-    trk = HostTracker(sf, sc, init_particles=False)
     sf.track_init(sc.pose(0), sc.time(0), sc.pose(1), sc.time(1))
     ok = True
     for f in range(2, 2 + W):
-        ok = ok and bool(trk.frame(f)["resampled"])
+        ok = ok and bool(sf.track_frame_host(sc.time(f), sc.blobs(f), sc.seed(f))["resampled"])
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     p0 = sf.passes
+    lat = []
     t0 = time.perf_counter()
     e0.record()
     for f in range(2 + W, 2 + W + K):
-        ok = ok and bool(trk.frame(f)["resampled"])
+        a = time.perf_counter()
+        ok = ok and bool(sf.track_frame_host(sc.time(f), sc.blobs(f), sc.seed(f))["resampled"])
+        lat.append(time.perf_counter() - a)
     e1.record()
     torch.cuda.synchronize(dev)
     wall = time.perf_counter() - t0
     barrier()
     passes = sf.passes - p0
+    checks = sf.state_checksums()                       # device-side, position-keyed: comparable with the unsharded filter's
     (ms,) = allreduce([max(e0.elapsed_time(e1), 0.0)], RO.MAX if RO else None)
     (wall,) = allreduce([wall], RO.MAX if RO else None)
     (okf,) = allreduce([1.0 if ok else 0.0], RO.MIN if RO else None)
     pme = float(n_global) * L_LED * passes
-    # + the rebalance: every resampled particle is read once through idx (48 + 4 B) and written once (48 B)
-    alg = (alg_bytes_per_frame(n_global // world, passes / K) + 100.0 * (n_global // world)) * K
-    rebalance = sf.rebalance
+    n_loc = n_global // world
+    alg = alg_bytes_per_frame(n_loc, passes / K) * K                      # SURVEY 8(d): 136 B per particle and frame
+    alg_reb = alg + 100.0 * n_loc * K                                     # + the rebalance: idx 4 + row read 48 + row write 48
+    rebalance, loop = sf.rebalance, sf.loop
+    nblob = sc.blobs(2).shape[0]
     sf.close()
     return {"workload": "cfg5", "desc": "BASELINE configs[4]: single filter with 2^26 particles sharded by particle over the ranks",
-            "scaling": "strong", "particles": n_global, "particles_per_rank": n_global // world, "value": pme / (wall), "unit": "PME/s",
-            "ms_per_step": 1e3 * wall / K, "device_ms_per_step": ms / K, "steps": K, "warmup": W, "mean_iterations": passes / K,
-            "all_frames_resampled": bool(okf > 0), "roofline_frac": alg / (wall) / 1e9 / peak,
-            "exchange": "all_gather of 64 B/rank per score pass and per resampling (torch.distributed %s); rebalance = %s"
-                        % ("nccl" if world > 1 else "loopback, 1 rank",
-                           "one scatter kernel, local + NVLink peer stores (CUDA IPC)" if rebalance == "p2p" else
-                           "row export + all_to_all + import"),
-            "rebalance": rebalance,
-            "note": "host-orchestrated stages through pfmpe_shard_*; wall clock of the whole host loop incl. host Gauss-Newton"}
+            "scaling": "strong", "particles": n_global, "particles_per_rank": n_loc, "value": pme / wall, "unit": "PME/s",
+            "ms_per_step": 1e3 * wall / K, "latency_p50_ms": 1e3 * float(np.median(lat)), "device_ms_per_step": ms / K,
+            "steps": K, "warmup": W, "mean_iterations": passes / K, "all_frames_resampled": bool(okf > 0),
+            "roofline": {"bound": "hbm", "achieved": alg / wall / 1e9, "peak": peak, "unit": "GB/s", "frac": alg / wall / 1e9 / peak,
+                         "traffic": None, "alg_bytes_per_particle_frame": alg_bytes_per_frame(1, passes / K),
+                         "frac_incl_rebalance": alg_reb / wall / 1e9 / peak,
+                         "note": "per GPU; SURVEY 8(d) figure (136 B per particle and frame) / wall time of the frame call; "
+                                 "frac_incl_rebalance adds the 100 B per particle the cross-GPU rebalance reads and writes"},
+            "e2e": {"value": pme / wall, "unit": "PME/s", "h2d_bytes_per_step": 224 + 16 * nblob, "d2h_bytes_per_step": 808,
+                    "note": "this sub-line IS the end-to-end figure: host detections in, pose + covariance out, every frame"},
+            "state_checksums": ["%016x" % c for c in checks],
+            "exchange": "64-byte partials by NVLink peer stores into every rank's mailbox (no NCCL call in the frame loop); rebalance = %s"
+                        % ("one scatter kernel, local + NVLink peer stores (CUDA IPC)" if rebalance == "p2p" else "row export + all_to_all + import"),
+            "rebalance": rebalance, "host_loop": loop}
 
 
 def p3p_vote_measure(dev, with_cpu, n_detections=205, K=5, W=2):
@@ -396,8 +451,7 @@ def p3p_vote_measure(dev, with_cpu, n_detections=205, K=5, W=2):
                    "h2d_bytes_per_step": int(img.nbytes), "d2h_bytes_per_step": int(hist.nbytes) + 32},
            "dtype": "f64", "votes": int(hist.sum()), "steps": K, "warmup": W,
            "note": "pfmpe_p3p_histogram: FP64 Kneip P3P + back-projection + votes in one kernel (K9); bound by FP64 dependency chains and "
-                   "instruction fetch (ncu: FP64 pipe 27 % active, issue-active 38 %, profiles/r01e_ncu_full_p3p_raw.csv); "
-                   "inputs 3 KB, output 4 KB"}
+                   "instruction fetch, not by memory (inputs 3 KB, output 4 KB): no HBM roofline applies"}
     if with_cpu:
         from oracle import orc
         sc2, img2, _ = vote_scene(40)
@@ -412,52 +466,52 @@ def p3p_vote_measure(dev, with_cpu, n_detections=205, K=5, W=2):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=None)
-    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="cfg2", choices=list(WORKLOADS))
+    ap.add_argument("--workload", default="cfg4", choices=list(WORKLOADS), help="headline workload (default: cfg4, see the docstring)")
     ap.add_argument("--no-flush", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--no-batched", action="store_true", help="skip the short cfg4 run reported under batched_trackers")
-    ap.add_argument("--no-sharded", action="store_true", help="skip the short configs[4] run reported under sharded_filter")
-    ap.add_argument("--no-outlier", action="store_true", help="skip the short configs[2] run reported under outlier_heavy")
-    ap.add_argument("--no-p3p", action="store_true", help="skip the short initialisation-vote run reported under p3p_vote")
+    ap.add_argument("--no-single", action="store_true", help="skip the cfg2 sub-line (single_filter)")
+    ap.add_argument("--no-sharded", action="store_true", help="skip the configs[4] sub-line (sharded_filter)")
+    ap.add_argument("--no-outlier", action="store_true", help="skip the configs[2] sub-line (outlier_heavy)")
+    ap.add_argument("--no-cpu-case", action="store_true", help="skip the configs[0] sub-line (cpu_case)")
+    ap.add_argument("--no-p3p", action="store_true", help="skip the initialisation-vote sub-line (p3p_vote)")
+    ap.add_argument("--only", action="store_true", help="headline workload only (all sub-lines off)")
     ap.add_argument("--trackers", type=int, default=None, help="override the tracker count of the workload (experiments)")
-    ap.add_argument("--e2e-steps", type=int, default=300)
-    ap.add_argument("--cpu-budget", type=float, default=15.0)
+    ap.add_argument("--cpu-budget", type=float, default=6.0, help="seconds of CPU work per cpu_baseline sample")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if args.steps is None:
-        args.steps = WORKLOADS[args.workload][3]
     args.warmup = max(args.warmup, 3)
-    n_p, n_t_total, n_out, _ = WORKLOADS[args.workload]
+    if args.only:
+        args.no_single = args.no_sharded = args.no_outlier = args.no_cpu_case = args.no_p3p = True
+    n_p, n_t_total, n_out = WORKLOADS[args.workload]
     if args.trackers:
         n_t_total = args.trackers
-    sharded = n_t_total > 1
+    split = n_t_total > 1
     cfg = {"workload": args.workload, "desc": WORKLOAD_DESC[args.workload], "particles": n_p, "leds": L_LED,
-           "blobs": L_LED + n_out}
-    if sharded:
-        cfg.update(trackers=n_t_total, sharding="%d trackers split evenly over %d rank(s)" % (n_t_total, max(world, args.gpus)))
-    else:
-        cfg.update(trackers=max(world, args.gpus),
-                   sharding="one independent filter + sequence per rank (tracker id = rank), no data-path collective")
+           "blobs": L_LED + n_out, "trackers": n_t_total if split else max(world, args.gpus),
+           "sharding": ("%d trackers split evenly over %d rank(s), no data-path collective" % (n_t_total, max(world, args.gpus))) if split
+           else "one independent filter + sequence per rank (tracker id = rank), no data-path collective"}
 
     if args.impl == "reference":
         if rank != 0:
             return
         threads = os.cpu_count() or 1
-        r = cpu_run(args.workload, budget_s=max(10.0, min(60.0, 0.05 * args.steps)), threads=threads)
+        r = cpu_run(args.workload, budget_s=max(8.0, min(40.0, 0.2 * args.steps)), threads=threads)
         line = {"impl": "reference", "metric": "particle_marker_evals_per_sec", "value": r["value"], "unit": "PME/s",
                 "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["p50_ms"],
-                "higher_is_better": True, "scaling": "strong" if sharded else "weak", "vs_baseline": None,
+                "higher_is_better": True, "scaling": "strong" if split else "weak", "vs_baseline": None,
                 "dtype": "f64", "data": "synthetic", "config": cfg,
                 "cpu_baseline": {"value": r["value"], "unit": "PME/s", "cores": r["cores"], "kind": "port", "sample": r["sample"]},
                 "e2e": {"value": r["value"], "unit": "PME/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "note": "the reference cannot be compiled here (Eigen/OpenCV/ROS absent): oracle port of pose_estimator.cpp:475-733 "
-                        "+ :1805-2009, one filter per host thread (the reference itself is single-threaded)"}
+                        "+ :1805-2009, one independent filter of the workload per host thread (the reference itself is single-threaded; "
+                        "for the tracker-batched workload that is exactly the workload's own decomposition); ms_per_step = p50 of one "
+                        "filter's frame.  config differs from the b200 arm's only in the keys that describe its launch (mean_iterations, l2, launch)"}
         print(json.dumps(line))
         return
 
@@ -480,94 +534,71 @@ def main():
         torch.distributed.all_reduce(t, op=op)
         return [float(x) for x in t]
 
-    if sharded:
+    RO = torch.distributed.ReduceOp if world > 1 else None
+    rmax = lambda v: allreduce(v, RO.MAX if RO else None)      # noqa: E731
+    rsum = lambda v: allreduce(v, RO.SUM if RO else None)      # noqa: E731
+    rmin = lambda v: allreduce(v, RO.MIN if RO else None)      # noqa: E731
+    ident = lambda v: [float(x) for x in v]                    # noqa: E731
+    peak, peak_src = peaks()
+
+    if split:
         assert n_t_total % world == 0
         n_t = n_t_total // world
         trackers = np.arange(rank * n_t, (rank + 1) * n_t)
     else:
         trackers = np.array([rank])
     K, W = args.steps, args.warmup
+    e2e_frames = 0 if args.no_e2e else MIN_E2E_FRAMES.get(args.workload, 60)
     m = gpu_measure(args.workload, trackers, K, W, dev, local_rank, barrier, flush_ok=not args.no_flush,
-                    e2e_steps=0 if args.no_e2e else args.e2e_steps, clocks=True)
+                    e2e_frames=e2e_frames, clocks=True)
+    c = contract(args.workload, m, world, rmax, rsum, rmin, peak, peak_src)
+    cfg.update(mean_iterations=c["mean_iterations"], l2=c["l2"], launch=c["launch"])
+    line = {"metric": "particle_marker_evals_per_sec", "value": c["value"], "unit": "PME/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": c["ms_per_step"], "higher_is_better": True, "scaling": "strong" if split else "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": cfg, "latency_p50_ms": c["latency_p50_ms"], "roofline": c["roofline"],
+            "single_launch": c["single_launch"], "tracking": c["tracking"], "gpu_launches": c["gpu_launches"],
+            "all_frames_accepted": c["all_frames_accepted"], "wall_s": m["wall_s"], "clocks": m.get("clocks"),
+            "pairing": "headline speed-up = e2e / the reference arm (both: whole tracked frames from host buffers, Gauss-Newton "
+                       "included); value / roofline time the PF-update kernel alone"}
+    if "e2e" in c:
+        line["e2e"] = c["e2e"]
 
-    RO = torch.distributed.ReduceOp if world > 1 else None
-    dev_ms, single_ms, track_ms = allreduce([m["dev_ms"], m["single_ms"], m["track_ms"] or 0.0], RO.MAX if RO else None)
-    pme_total, alg_total, launches = allreduce([m["pme"], m["alg_bytes"], m["launches"]], RO.SUM if RO else None)
-    (ok,) = allreduce([1.0 if m["ok"] else 0.0], RO.MIN if RO else None)
-    peak, peak_src = peaks()
-    achieved = m["alg_bytes"] / (m["dev_ms"] * 1e-3) / 1e9            # this rank's GB/s
-    (achieved_min,) = allreduce([achieved], RO.MIN if RO else None)
-    cfg.update(mean_iterations=m["mean_iter"], l2=m["l2"], launch=m["launch_info"])
-    line = {
-        "metric": "particle_marker_evals_per_sec", "value": pme_total / (dev_ms * 1e-3), "unit": "PME/s",
-        "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": dev_ms / K, "higher_is_better": True,
-        "scaling": "strong" if sharded else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": cfg,
-        "latency_p50_ms": m["p50_ms"],
-        "roofline": {"bound": "hbm", "achieved": achieved_min, "peak": peak, "unit": "GB/s", "frac": achieved_min / peak,
-                     "traffic": profiled_traffic(args.workload), "traffic_unit": "bytes/launch (ncu dram__bytes_read+write, profiles/r01_traffic.json)",
-                     "alg_bytes_per_launch": alg_bytes_per_frame(n_p, m["mean_iter"]) * len(trackers), "peak_source": peak_src,
-                     "alg_bytes_per_particle_frame": alg_bytes_per_frame(1, m["mean_iter"]), "kernel": "pf_frames_kernel<5>",
-                     "note": "per GPU (slowest rank); algorithmic bytes / device time of the PF-update launches"},
-        "single_launch": {"value": pme_total / (single_ms * 1e-3), "ms_per_step": single_ms / K,
-                          "note": "all %d frames in one persistent launch, no L2 flush" % K},
-        "tracking": {"value": pme_total / (track_ms * 1e-3) if track_ms else None, "ms_per_step": track_ms / K if track_ms else None,
-                     "note": "device-resident tracking: PF update + FP64 Gauss-Newton/predictPose tail on the device, one launch per frame"},
-        "gpu_launches": int(launches), "all_frames_accepted": bool(ok > 0), "wall_s": m["wall_s"], "clocks": m.get("clocks"),
-    }
-    if "e2e" in m:
-        e = m["e2e"]
-        (e_sec,) = allreduce([e["seconds"]], RO.MAX if RO else None)
-        (e_pme,) = allreduce([e["pme"]], RO.SUM if RO else None)
-        line["e2e"] = {"value": e_pme / e_sec, "unit": "PME/s", "h2d_bytes_per_step": e["h2d"], "d2h_bytes_per_step": e["d2h"],
-                       "steps": e["steps"], "p50_ms": e["p50_ms"], "trackers_per_rank": e["trackers"], "all_frames_accepted": e["ok"],
-                       "path": "pfmpe_track_frame_host(_batch) per frame from HOST buffers: host predictPose -> PF update launch "
-                               "(one tracker: the frame's inputs travel inside the kernel parameter block; batches: pinned "
-                               "H2D copy) -> result record written by the kernel into pinned host memory -> host "
-                               "Gauss-Newton (FP64); looped in C by pfmpe_track_sequence_host"}
-
-    # ---- BASELINE configs[3] alongside (short): 4096 trackers x 4096 particles split over the ranks
-    if not sharded and not args.no_batched:
-        nt4 = WORKLOADS["cfg4"][1] // world
-        tr4 = np.arange(rank * nt4, (rank + 1) * nt4)
-        K4, W4 = 20, 3
-        b = gpu_measure("cfg4", tr4, K4, W4, dev, local_rank, barrier, flush_ok=False, with_track=True, e2e_steps=0)
-        b_ms, b_tr = allreduce([b["dev_ms"], b["track_ms"] or 0.0], RO.MAX if RO else None)
-        b_pme, b_alg = allreduce([b["pme"], b["alg_bytes"]], RO.SUM if RO else None)
-        line["batched_trackers"] = {
-            "workload": "cfg4", "desc": WORKLOAD_DESC["cfg4"], "scaling": "strong", "value": b_pme / (b_ms * 1e-3), "unit": "PME/s",
-            "ms_per_step": b_ms / K4, "steps": K4, "warmup": W4, "mean_iterations": b["mean_iter"], "max_iterations": b.get("max_iter"),
-            "tracking_ms_per_step": b_tr / K4 if b_tr else None,
-            "roofline_frac": b_alg / world / (b_ms * 1e-3) / 1e9 / peak, "launch": b["launch_info"], "l2": b["l2"]}
-
-    # ---- BASELINE configs[2] alongside (short, rank 0): outlier-heavy scene, 1e6 particles, 205 blobs
-    if rank == 0 and not sharded and not args.no_outlier and args.workload != "cfg3":
-        K3, W3 = 20, 3
-        o = gpu_measure("cfg3", np.array([0]), K3, W3, dev, local_rank, lambda: None, flush_ok=True, with_track=True, e2e_steps=0)
-        f_alg = 210 + 27 * L_LED + 6 * L_LED * 205 + 55           # algorithmic flops per particle-iteration at D = 205
-        line["outlier_heavy"] = {
-            "workload": "cfg3", "desc": WORKLOAD_DESC["cfg3"], "value": o["pme"] / (o["dev_ms"] * 1e-3), "unit": "PME/s",
-            "ms_per_step": o["dev_ms"] / K3, "steps": K3, "warmup": W3, "mean_iterations": o["mean_iter"],
-            "tracking_ms_per_step": o["track_ms"] / K3 if o["track_ms"] else None,
-            "roofline_frac": o["alg_bytes"] / (o["dev_ms"] * 1e-3) / 1e9 / peak,
-            "alg_tflops": f_alg * o["pme"] / L_LED / (o["dev_ms"] * 1e-3) / 1e12,
-            "alg_tflops_note": "reference-algorithm flops (full D x L distance scan, %d per particle) per second; the kernel's "
-                               "column-bucketed search evaluates ~5 of the 205 distances per LED, so this exceeds what the FP32 "
-                               "pipe (66.6 TFLOP/s FFMA measured, tools/micro/fp64_rate.cu) could do literally" % f_alg,
-            "launch": o["launch_info"], "l2": o["l2"], "all_frames_accepted": bool(o["ok"])}
-
-    # ---- BASELINE configs[4] alongside (short): ONE filter of 2^26 particles sharded by particle over the ranks
-    if not sharded and not args.no_sharded:
+    on0 = rank == 0
+    # ---- BASELINE configs[1] alongside (rank 0): one filter of 1e5 particles -- the latency half of the metric
+    if not args.no_single and args.workload != "cfg2":
+        if on0:
+            s = gpu_measure("cfg2", np.array([0]), max(K, MIN_SUB_STEPS), W, dev, local_rank, lambda: torch.cuda.synchronize(dev),
+                            e2e_frames=0 if args.no_e2e else MIN_E2E_FRAMES["cfg2"])
+            line["single_filter"] = contract("cfg2", s, 1, ident, ident, ident, peak, peak_src)
+        barrier()
+    # ---- BASELINE configs[2] alongside (rank 0): outlier-heavy scene, 1e6 particles, 205 blobs
+    if not args.no_outlier and args.workload != "cfg3":
+        if on0:
+            o = gpu_measure("cfg3", np.array([0]), MIN_SUB_STEPS, 3, dev, local_rank, lambda: torch.cuda.synchronize(dev),
+                            e2e_frames=0 if args.no_e2e else MIN_E2E_FRAMES["cfg3"])
+            line["outlier_heavy"] = contract("cfg3", o, 1, ident, ident, ident, peak, peak_src)
+            line["outlier_heavy"]["note"] = ("the column-bucketed candidate search makes 205 blobs cost what 15 do: the kernel stays "
+                                             "memory / issue bound, SURVEY 8(d)'s FP32 bound for a full 205-blob scan does not apply")
+        barrier()
+    # ---- BASELINE configs[0] alongside (rank 0): the reference's own CPU-runnable case, 100 particles
+    if not args.no_cpu_case and args.workload != "cfg1":
+        if on0:
+            o = gpu_measure("cfg1", np.array([0]), MIN_SUB_STEPS, 3, dev, local_rank, lambda: torch.cuda.synchronize(dev),
+                            e2e_frames=0 if args.no_e2e else MIN_E2E_FRAMES["cfg1"])
+            line["cpu_case"] = contract("cfg1", o, 1, ident, ident, ident, peak, peak_src)
+        barrier()
+    # ---- BASELINE configs[4] alongside: ONE filter of 2^26 particles sharded by particle over the ranks
+    if not args.no_sharded:
         line["sharded_filter"] = sharded_filter_measure(world, rank, dev, local_rank, barrier, allreduce, RO, peak)
-
-    if rank == 0 and not sharded and not args.no_p3p:
+    if on0 and not args.no_p3p:
         line["p3p_vote"] = p3p_vote_measure(local_rank, with_cpu=(world == 1 and not args.no_cpu))
 
-    if rank == 0:
+    if on0:
         if world == 1 and not args.no_cpu:
-            r = cpu_run(args.workload, budget_s=args.cpu_budget, threads=1)
-            line["cpu_baseline"] = {"value": r["value"], "unit": "PME/s", "cores": 1, "kind": "port", "sample": r["sample"],
-                                    "p50_ms": r["p50_ms"]}
+            line["cpu_baseline"] = cpu_baseline_obj(args.workload, args.cpu_budget)
+            for key, wl in (("single_filter", "cfg2"), ("outlier_heavy", "cfg3"), ("cpu_case", "cfg1")):
+                if key in line:
+                    line[key]["cpu_baseline"] = cpu_baseline_obj(wl, args.cpu_budget)
         print(json.dumps(line))
     if world > 1:
         torch.distributed.barrier()

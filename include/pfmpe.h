@@ -349,11 +349,35 @@ int pfmpe_shard_mail_create(pfmpe_handle* h, int world, int rank, void** d_ptr, 
 int pfmpe_shard_mail_set_peers(pfmpe_handle* h, void* const* d_ptrs);
 int pfmpe_shard_collect(pfmpe_handle* h, int only_rank, int64_t* table);
 int pfmpe_shard_advance(pfmpe_handle* h);
-int pfmpe_shard_barrier(pfmpe_handle* h);
+int pfmpe_shard_barrier(pfmpe_handle* h);   /* = pfmpe_shard_signal + pfmpe_shard_wait */
+int pfmpe_shard_signal(pfmpe_handle* h);    /* the sending half: an empty message to every rank, stream-ordered */
+int pfmpe_shard_wait(pfmpe_handle* h);      /* the waiting half: a kernel that returns when every rank's message is in */
 int pfmpe_shard_winner_publish(pfmpe_handle* h, int local_index);
 /* pose + correspondences (:687-691 / :714-716) of the local particle `local_index` of the last pass;
  * only winner_pose / correspondences / n_correspondences of `out` are meaningful */
 int pfmpe_shard_winner(pfmpe_handle* h, int local_index, pfmpe_frame_out* out);
+
+/* One whole PF update of the sharded filter with the host logic in C (pose_estimator.cpp:535-616 do/while + max test,
+ * :627-633 sum / accept, :666-688 resampling + winner, taken from the partials of ALL ranks, which the stage kernels
+ * deliver into this process's mailbox by NVLink peer stores): score passes until the loop exits, regeneration of the kept
+ * iteration, resampling against the global strata, the peer-memory rebalance, a stream-ordered barrier, the winner record
+ * from its owner.  `shards` are the handles of this process: one per process in a multi-GPU run (every rank makes the same
+ * call with the same inputs and gets the same outputs), or all `world` logical shards of a single-GPU run (they must then
+ * share one stream).  Needs pfmpe_shard_configure, pfmpe_shard_set_peers and pfmpe_shard_mail_set_peers on every shard. */
+int pfmpe_shard_frame(pfmpe_handle* const* shards, int n_local, const pfmpe_frame_in* in, pfmpe_frame_out* out);
+/* The tracked frame around it, as pfmpe_track_frame_host does for an unsharded filter: predictPose (host, FP64), the
+ * sharded PF update, optimiseAndUpdatePose + jump check (host, FP64); pfmpe_track_init on every shard first. */
+int pfmpe_shard_track_frame_host(pfmpe_handle* const* shards, int n_local, double time_to_predict, const double* image_points,
+                                 int32_t n_image_points, uint32_t seed, pfmpe_track_result* out);
+/* score passes pfmpe_shard_frame has launched on this shard so far */
+int pfmpe_shard_passes(const pfmpe_handle* h, uint64_t* n);
+
+/* ---- full-size parity aid ------------------------------------------------------------------ */
+/* Position-keyed 64-bit checksums of one tracker's device state, computed on the device: [0] PoseParticle (propagated
+ * set of the kept iteration), [1] its raw weights, [2] newPoseEstimation (the resampled set).  Every word is mixed with
+ * its GLOBAL particle / slot number and the results are summed mod 2^64, so the checksums of the shards of a sharded
+ * filter add up to those of the unsharded filter exactly when the states are identical (no host copy of 2^26 poses). */
+int pfmpe_state_checksum(pfmpe_handle* h, int tracker, uint64_t out[3]);
 
 /* ---- streams / timing ---------------------------------------------------------------------- */
 int pfmpe_set_stream(pfmpe_handle* h, void* cuda_stream); /* use an external cudaStream_t (e.g. torch's) */

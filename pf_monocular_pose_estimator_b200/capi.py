@@ -29,7 +29,8 @@ EXPORTS = [
     "pfmpe_shard_configure", "pfmpe_shard_begin_frame", "pfmpe_shard_score", "pfmpe_shard_resample",
     "pfmpe_shard_export", "pfmpe_shard_keep", "pfmpe_shard_import", "pfmpe_shard_winner",
     "pfmpe_shard_mail_create", "pfmpe_shard_mail_set_peers", "pfmpe_shard_collect", "pfmpe_shard_advance",
-    "pfmpe_shard_barrier", "pfmpe_shard_winner_publish",
+    "pfmpe_shard_barrier", "pfmpe_shard_signal", "pfmpe_shard_wait", "pfmpe_shard_winner_publish",
+    "pfmpe_shard_frame", "pfmpe_shard_track_frame_host", "pfmpe_shard_passes", "pfmpe_state_checksum",
     "pfmpe_shard_local_ptr", "pfmpe_shard_ipc_export", "pfmpe_shard_ipc_open", "pfmpe_shard_set_peers", "pfmpe_shard_scatter",
     "pfmpe_set_stream", "pfmpe_sync", "pfmpe_last_launch_ms", "pfmpe_launch_count", "pfmpe_launch_info", "pfmpe_debug_timeline",
 ]
@@ -163,6 +164,13 @@ def lib():
         L.pfmpe_shard_collect.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int64)]
         L.pfmpe_shard_advance.argtypes = [C.c_void_p]
         L.pfmpe_shard_barrier.argtypes = [C.c_void_p]
+        L.pfmpe_shard_signal.argtypes = [C.c_void_p]
+        L.pfmpe_shard_wait.argtypes = [C.c_void_p]
+        L.pfmpe_shard_frame.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.POINTER(FrameIn), C.POINTER(FrameOut)]
+        L.pfmpe_shard_track_frame_host.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_double, _dp, C.c_int32, C.c_uint32,
+                                                   C.POINTER(TrackResult)]
+        L.pfmpe_shard_passes.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
+        L.pfmpe_state_checksum.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint64)]
         L.pfmpe_shard_winner_publish.argtypes = [C.c_void_p, C.c_int]
         L.pfmpe_shard_winner.argtypes = [C.c_void_p, C.c_int, C.POINTER(FrameOut)]
         L.pfmpe_set_stream.argtypes = [C.c_void_p, C.c_void_p]
@@ -493,6 +501,17 @@ class Handle:
     def shard_barrier(self):
         self._chk(lib().pfmpe_shard_barrier(self._h))
 
+    def state_checksum(self, tracker=0):
+        """Position-keyed device checksums: [PoseParticle, raw weights, newPoseEstimation] (pfmpe_state_checksum)."""
+        out = (C.c_uint64 * 3)()
+        self._chk(lib().pfmpe_state_checksum(self._h, tracker, out))
+        return [int(v) for v in out]
+
+    def shard_passes(self):
+        n = C.c_uint64()
+        self._chk(lib().pfmpe_shard_passes(self._h, C.byref(n)))
+        return int(n.value)
+
     def shard_winner_publish(self, local_index):
         self._chk(lib().pfmpe_shard_winner_publish(self._h, int(local_index)))
 
@@ -566,6 +585,26 @@ class Handle:
 
 
 # ---- host tail (FP64, no device needed) --------------------------------------------------
+def shard_frame(handles, frame_in):
+    """pfmpe_shard_frame: one PF update of a sharded filter for this process's shard handles (host logic in C)."""
+    arr = (C.c_void_p * len(handles))(*[h._h for h in handles])
+    fo = FrameOut()
+    handles[0]._chk(lib().pfmpe_shard_frame(arr, len(handles), C.byref(frame_in), C.byref(fo)))
+    return unpack_frame_out(fo)
+
+
+def shard_track_frame_host(handles, time_to_predict, image_points, seed):
+    """pfmpe_shard_track_frame_host: predictPose -> sharded PF update -> Gauss-Newton, all in C."""
+    arr = (C.c_void_p * len(handles))(*[h._h for h in handles])
+    img = _c64(image_points).reshape(-1, 2)
+    tr = TrackResult()
+    handles[0]._chk(lib().pfmpe_shard_track_frame_host(arr, len(handles), float(time_to_predict), _d(img), img.shape[0],
+                                                       int(seed) & 0xFFFFFFFF, C.byref(tr)))
+    r = Handle._unpack_track((TrackResult * 1)(tr))[0]
+    r["resampled"] = 1 if r["most_likely_pose_idx"] >= 0 else 0
+    return r
+
+
 def optimise_pose(K, markers, img, pairs, pose):
     k = _c64(K).reshape(9)
     m = _c64(markers).reshape(-1, 3)

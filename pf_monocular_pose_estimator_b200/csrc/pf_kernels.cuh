@@ -1282,9 +1282,11 @@ __global__ void pf_shard_wait_kernel(const long long* mail, int slot, int world,
   bool ok = true;
   if (d < world && (only < 0 || d == only)) {
     const volatile long long* m = mail + ((size_t)slot * world + d) * PF_XMAIL_WORDS;
-    const long long t0 = clock64();
+    unsigned long long t0, t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
     while (m[PF_XMAIL_WORDS - 1] != seq) {
-      if (clock64() - t0 > 4000000000ll) { ok = false; break; }
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+      if (t1 - t0 > 2000000000ull) { ok = false; break; }      // 2 s of wall time (nanosecond timer: clock independent)
     }
     __threadfence_system();
     if (host_out)
@@ -1296,6 +1298,41 @@ __global__ void pf_shard_wait_kernel(const long long* mail, int slot, int world,
     __syncwarp();
     if (d == 0) *reinterpret_cast<volatile long long*>(host_out + (size_t)world * PF_XMAIL_WORDS) = ok ? seq : -1ll;
   }
+}
+
+// Position-keyed checksums of one tracker's state: [0] the propagated set (PoseParticle, kept iteration), [1] its raw
+// weights, [2] the resampled set (newPoseEstimation = rows gathered through idx / lead).  Every 32-bit word is mixed
+// with its GLOBAL position (particle or slot number x word number) and the 64-bit results are summed: the sum does not
+// depend on how the particles are split over CTAs, handles or GPUs, so the sums of the shards of a sharded filter add
+// up to the checksum of the unsharded one exactly when every word sits at the same global position.
+__device__ __forceinline__ unsigned long long pf_mix64(unsigned long long pos, unsigned v)
+{
+  unsigned long long z = pos * 0x9E3779B97F4A7C15ull + ((unsigned long long)v + 1ull) * 0xBF58476D1CE4E5B9ull;
+  z ^= z >> 31; z *= 0x94D049BB133111EBull; z ^= z >> 29;
+  return z;
+}
+__global__ void __launch_bounds__(PF_BLOCK) pf_checksum_kernel(const float4* T, const float* w, const float4* src, const int* idx,
+                                                               int src_mode, int N, unsigned long long goff, unsigned long long* out)
+{
+  unsigned long long a = 0, b = 0, c = 0;
+  for (long long n = (long long)blockIdx.x * PF_BLOCK + threadIdx.x; n < N; n += (long long)gridDim.x * PF_BLOCK) {
+    const unsigned long long g = goff + (unsigned long long)n;
+    const int s = src_mode == 1 ? idx[n] : (int)n;
+#pragma unroll
+    for (int pl = 0; pl < 3; ++pl) {
+      const float4 t = T[(size_t)pl * N + n], r = src[(size_t)pl * N + s];
+      a += pf_mix64(g * 16 + 4 * pl + 0, __float_as_uint(t.x)) + pf_mix64(g * 16 + 4 * pl + 1, __float_as_uint(t.y)) +
+           pf_mix64(g * 16 + 4 * pl + 2, __float_as_uint(t.z)) + pf_mix64(g * 16 + 4 * pl + 3, __float_as_uint(t.w));
+      c += pf_mix64(g * 16 + 4 * pl + 0, __float_as_uint(r.x)) + pf_mix64(g * 16 + 4 * pl + 1, __float_as_uint(r.y)) +
+           pf_mix64(g * 16 + 4 * pl + 2, __float_as_uint(r.z)) + pf_mix64(g * 16 + 4 * pl + 3, __float_as_uint(r.w));
+    }
+    b += pf_mix64(g, __float_as_uint(w[n]));
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    a += __shfl_xor_sync(PF_FULL, a, o); b += __shfl_xor_sync(PF_FULL, b, o); c += __shfl_xor_sync(PF_FULL, c, o);
+  }
+  if ((threadIdx.x & 31) == 0) { atomicAdd(out, a); atomicAdd(out + 1, b); atomicAdd(out + 2, c); }
 }
 
 // Sharded filter: an empty message to every rank (the sending half of a stream-ordered barrier)

@@ -6,6 +6,10 @@
 
 #include <atomic>
 #include <chrono>
+#include <condition_variable>
+#include <functional>
+#include <memory>
+#include <mutex>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -34,6 +38,68 @@ struct TrackSeq {
   int next_frame = -1;     // frame whose constants are currently staged in fconst (track mode)
   int last_frame = -1;     // last frame processed by track_run
   int tracked_upto = -1;   // highest frame whose constants are in fc_log
+};
+
+// Persistent host workers for the per-tracker FP64 tail of a batch (predictPose before, Gauss-Newton after the PF update)
+// and the staging / unpacking of its records: independent per tracked object, so a batch of thousands is spread over the
+// host cores (the reference's `for objectNumber` loop, :89, is serial).  Workers sleep on a condition variable between
+// calls (no spinning: several ranks may share one host); the caller takes a share of the work itself.
+class HostPool {
+ public:
+  explicit HostPool(int workers)
+  {
+    for (int i = 0; i < workers; ++i) th_.emplace_back([this, i]() { loop(i); });
+  }
+  ~HostPool()
+  {
+    { std::lock_guard<std::mutex> g(m_); stop_ = true; ++gen_; }
+    cv_.notify_all();
+    for (auto& t : th_) t.join();
+  }
+  int size() const { return (int)th_.size(); }
+  // body(i) for i in [0, n): contiguous chunks, one per worker + one for the caller
+  void run(int n, const std::function<void(int)>& body)
+  {
+    const int parts = (int)th_.size() + 1, per = (n + parts - 1) / parts;
+    {
+      std::lock_guard<std::mutex> g(m_);
+      body_ = &body; n_ = n; per_ = per; pending_ = (int)th_.size(); ++gen_;
+    }
+    cv_.notify_all();
+    for (int i = (parts - 1) * per; i < n; ++i) body(i);        // the caller's chunk (the last one)
+    std::unique_lock<std::mutex> g(m_);
+    done_.wait(g, [this]() { return pending_ == 0; });
+    body_ = nullptr;
+  }
+
+ private:
+  void loop(int id)
+  {
+    unsigned long long seen = 0;
+    for (;;) {
+      const std::function<void(int)>* body;
+      int n, per;
+      {
+        std::unique_lock<std::mutex> g(m_);
+        cv_.wait(g, [&]() { return gen_ != seen; });
+        seen = gen_;
+        if (stop_) return;
+        body = body_; n = n_; per = per_;
+      }
+      for (int i = id * per; i < n && i < (id + 1) * per; ++i) (*body)(i);
+      {
+        std::lock_guard<std::mutex> g(m_);
+        if (--pending_ == 0) done_.notify_one();
+      }
+    }
+  }
+  std::vector<std::thread> th_;
+  std::mutex m_;
+  std::condition_variable cv_, done_;
+  const std::function<void(int)>* body_ = nullptr;
+  int n_ = 0, per_ = 0, pending_ = 0;
+  unsigned long long gen_ = 0;
+  bool stop_ = false;
 };
 
 // host-side tracked object (previous_pose_, current_pose_, their times, it_since_initialized_, covariance)
@@ -117,10 +183,15 @@ struct pfmpe_handle {
   float4** peers_dev = nullptr;         // [peer_world] next-frame particle planes of every rank (peer memory)
   int peer_world = 0;
   std::vector<void*> ipc_opened;
+  std::unique_ptr<HostPool> pool;       // host workers of the batched host tail (created on first use)
+  uint64_t shard_passes = 0;            // score passes launched by pfmpe_shard_frame
+  unsigned long long* cksum = nullptr;  // pfmpe_state_checksum scratch
   std::vector<pfmpe_frame_in> in_scratch;
   std::vector<pfmpe_frame_out> out_scratch;
   std::string err;
 };
+
+static void host_parallel_for(pfmpe_handle* h, int n, const std::function<void(int)>& body);
 
 namespace {
 
@@ -157,7 +228,7 @@ void free_all(pfmpe_handle* h)
   if (h->h_xtable) cudaFreeHost(h->h_xtable);
   cudaFree(h->peers_dev); cudaFree(h->mc_part); cudaFree(h->mc_mean); cudaFree(h->roi_keys); cudaFree(h->roi_out);
   if (h->h_roi) cudaFreeHost(h->h_roi);
-  cudaFree(h->p3p_buf); cudaFree(h->p3p_io);
+  cudaFree(h->p3p_buf); cudaFree(h->p3p_io); cudaFree(h->cksum);
   cudaFree(h->rng_tab); cudaFree(h->timeline); cudaFree(h->warp_agg_g); cudaFree(h->shard_partial); cudaFree(h->gfill);
   if (h->seq.owned) { cudaFree(h->seq.blobs); cudaFree(h->seq.counts); cudaFree(h->seq.times); cudaFree(h->seq.seeds); }
   cudaFree(h->seq.result); cudaFree(h->seq.fc_log);
@@ -633,11 +704,16 @@ static int check_ready(pfmpe_handle* h)
   return PFMPE_OK;
 }
 
-static int stage_frame(pfmpe_handle* h, int t, const pfmpe_frame_in* in)
+static int check_frame(pfmpe_handle* h, int t, const pfmpe_frame_in* in)
 {
   if (!h->particles_set[t]) return fail(h, PFMPE_ERR_STATE, "set_particles / track_init must precede update");
   if (in->n_image_points < 0 || in->n_image_points > h->cfg.max_blobs) return fail(h, PFMPE_ERR_INVALID, "n_image_points exceeds max_blobs");
   if (in->n_image_points > 0 && !in->image_points) return fail(h, PFMPE_ERR_INVALID, "image_points is NULL");
+  return PFMPE_OK;
+}
+
+static int stage_frame(pfmpe_handle* h, int t, const pfmpe_frame_in* in)
+{
   pf_frame_const* fc = reinterpret_cast<pf_frame_const*>(h->h_inbox) + t;
   pf_make_frame_const(*fc, pf_aff_from_cm16(in->current_pose), pf_aff_from_cm16(in->predicted_pose),
                       pf_aff_from_cm16(in->prediction_matrix), pf_aff_from_cm16(in->cam_move_inv),
@@ -676,9 +752,10 @@ static int run_update(pfmpe_handle* h, int t0, int nt, const pfmpe_frame_in* in,
   if (rc) return rc;
   PF_CUDA(h, cudaSetDevice(h->cfg.device));
   for (int i = 0; i < nt; ++i) {
-    rc = stage_frame(h, t0 + i, in + i);
+    rc = check_frame(h, t0 + i, in + i);
     if (rc) return rc;
   }
+  host_parallel_for(h, nt, [&](int i) { stage_frame(h, t0 + i, in + i); });
   const int T = h->cfg.n_trackers;
   const bool want_mean = (h->cfg.flags & PFMPE_FLAG_MEAN_COV) != 0;
   // latency path: one tracker with few detections carries its inputs in the kernel parameters; the
@@ -732,10 +809,10 @@ static int run_update(pfmpe_handle* h, int t0, int nt, const pfmpe_frame_in* in,
     PF_CUDA(h, cudaMemcpyAsync(h->h_result + t0, h->result + t0, sizeof(pf_frame_result) * nt, cudaMemcpyDeviceToHost, h->stream));
   }
   PF_CUDA(h, cudaStreamSynchronize(h->stream));
-  for (int i = 0; i < nt; ++i) {
+  host_parallel_for(h, nt, [&](int i) {
     unpack_result(h->h_result[t0 + i], out + i);
     h->last_sum_fx[t0 + i] = h->h_result[t0 + i].sum_fx;
-  }
+  });
   h->last_was_track = false;
   return PFMPE_OK;
 }
@@ -1107,24 +1184,21 @@ int pfmpe_track_results(pfmpe_handle* h, int tracker, int first_frame, int n_fra
 // The FP64 host tail of a batch (predictPose before, Gauss-Newton after the PF update) is independent per tracked
 // object: above a few dozen objects it is spread over the host cores (the reference's `for objectNumber` loop, :89, is
 // serial; 4096 objects x ~3 us would otherwise dwarf the 1.3 ms the device needs).
-extern "C++" {
-template <typename F>
-static void host_parallel_for(int n, F body)
+}  // extern "C" (C++ helper with internal linkage follows)
+static void host_parallel_for(pfmpe_handle* h, int n, const std::function<void(int)>& body)
 {
   if (n < 64) { for (int i = 0; i < n; ++i) body(i); return; }   // the single-object latency path never gets here
-  static const int hw = (int)std::thread::hardware_concurrency();  // queried once: it reads /sys on Linux
-  int nth = hw > 0 ? hw : 1;
-  if (nth > n / 32) nth = n / 32;
-  if (nth <= 1) { for (int i = 0; i < n; ++i) body(i); return; }
-  std::vector<std::thread> th;
-  th.reserve((size_t)nth - 1);
-  const int per = (n + nth - 1) / nth;
-  for (int t = 1; t < nth; ++t)
-    th.emplace_back([=]() { for (int i = t * per; i < n && i < (t + 1) * per; ++i) body(i); });
-  for (int i = 0; i < per && i < n; ++i) body(i);
-  for (auto& x : th) x.join();
+  if (!h->pool) {
+    int nth = (int)std::thread::hardware_concurrency();
+    if (const char* e = std::getenv("PFMPE_HOST_THREADS")) nth = std::atoi(e);
+    if (nth > 32) nth = 32;
+    if (nth < 1) nth = 1;
+    h->pool.reset(new HostPool(nth - 1));
+  }
+  if (h->pool->size() == 0) { for (int i = 0; i < n; ++i) body(i); return; }
+  h->pool->run(n, body);
 }
-}  // extern "C++"
+extern "C" {
 
 static int track_frames_host(pfmpe_handle* h, int t0, int nt, double time_to_predict, const double* image_points,
                              size_t stride, const int32_t* counts, const uint32_t* seeds, size_t cstride,
@@ -1132,7 +1206,7 @@ static int track_frames_host(pfmpe_handle* h, int t0, int nt, double time_to_pre
 {
   for (int i = 0; i < nt; ++i)
     if (!h->host_trk[t0 + i].valid) return fail(h, PFMPE_ERR_STATE, "track_init must precede track_frame_host");
-  host_parallel_for(nt, [&](int i) {
+  host_parallel_for(h, nt, [&](int i) {
     HostTrack& ht = h->host_trk[t0 + i];
     pfmpe_frame_in& in = h->in_scratch[i];
     pf_aff P, pred;
@@ -1150,7 +1224,7 @@ static int track_frames_host(pfmpe_handle* h, int t0, int nt, double time_to_pre
   });
   int rc = run_update(h, t0, nt, h->in_scratch.data(), h->out_scratch.data());
   if (rc) return rc;
-  host_parallel_for(nt, [&](int i) {
+  host_parallel_for(h, nt, [&](int i) {
     HostTrack& ht = h->host_trk[t0 + i];
     const pfmpe_frame_out& fo = h->out_scratch[i];
     pfmpe_track_result* o = out + i * ostride;
@@ -1462,8 +1536,9 @@ int pfmpe_shard_begin_frame(pfmpe_handle* h, const pfmpe_frame_in* in)
   int rc = shard_ready(h);
   if (rc) return rc;
   PF_CUDA(h, cudaStreamSynchronize(h->stream));   // the pinned inbox may still be in flight
-  rc = stage_frame(h, 0, in);
+  rc = check_frame(h, 0, in);
   if (rc) return rc;
+  stage_frame(h, 0, in);
   PF_CUDA(h, cudaMemcpyAsync(h->inbox, h->h_inbox, h->inbox_bytes, cudaMemcpyHostToDevice, h->stream));
   return PFMPE_OK;
 }
@@ -1698,18 +1773,33 @@ int pfmpe_shard_collect(pfmpe_handle* h, int only_rank, int64_t* table /* [world
   return PFMPE_OK;
 }
 
-int pfmpe_shard_barrier(pfmpe_handle* h)
+int pfmpe_shard_signal(pfmpe_handle* h)
 {
   if (!h) return PFMPE_ERR_INVALID;
   int rc = mail_ready(h);
   if (rc) return rc;
   h->xseq += 1;
-  const int slot = (int)(h->xseq % PF_XMAIL_RING);
-  pf_shard_signal_kernel<<<1, 32, 0, h->stream>>>(h->xmail_peers_dev, h->xworld, h->xrank, slot, h->xseq);
-  pf_shard_wait_kernel<<<1, 32, 0, h->stream>>>(h->xmail, slot, h->xworld, -1, h->xseq, nullptr);
+  pf_shard_signal_kernel<<<1, 32, 0, h->stream>>>(h->xmail_peers_dev, h->xworld, h->xrank, (int)(h->xseq % PF_XMAIL_RING), h->xseq);
   PF_CUDA(h, cudaGetLastError());
-  h->launches += 2;
+  h->launches += 1;
   return PFMPE_OK;
+}
+
+int pfmpe_shard_wait(pfmpe_handle* h)
+{
+  if (!h) return PFMPE_ERR_INVALID;
+  int rc = mail_ready(h);
+  if (rc) return rc;
+  pf_shard_wait_kernel<<<1, 32, 0, h->stream>>>(h->xmail, (int)(h->xseq % PF_XMAIL_RING), h->xworld, -1, h->xseq, nullptr);
+  PF_CUDA(h, cudaGetLastError());
+  h->launches += 1;
+  return PFMPE_OK;
+}
+
+int pfmpe_shard_barrier(pfmpe_handle* h)
+{
+  const int rc = pfmpe_shard_signal(h);
+  return rc ? rc : pfmpe_shard_wait(h);
 }
 
 int pfmpe_shard_winner_publish(pfmpe_handle* h, int local_index)
@@ -1739,6 +1829,249 @@ int pfmpe_shard_winner(pfmpe_handle* h, int local_index, pfmpe_frame_out* out)
   PF_CUDA(h, cudaMemcpyAsync(h->h_result, h->result, sizeof(pf_frame_result), cudaMemcpyDeviceToHost, h->stream));
   PF_CUDA(h, cudaStreamSynchronize(h->stream));
   unpack_result(h->h_result[0], out);
+  return PFMPE_OK;
+}
+
+// ---- the whole sharded update, host logic in C++ ------------------------------------------------------
+// Mirrors the reference loop at its global reductions (pose_estimator.cpp:535-616 do/while + max test, :627-633 sum /
+// accept, :666-688 resampling + winner): stage launches on every local shard, the 64-byte partials of ALL ranks arrive
+// in this process's mailbox by peer stores, and the decisions -- identical on every rank -- are taken here.
+namespace {
+inline float shard_unord(unsigned long long key_hi32)
+{
+  unsigned o = (unsigned)key_hi32;
+  unsigned u = (o & 0x80000000u) ? (o ^ 0x80000000u) : ~o;
+  float f;
+  std::memcpy(&f, &u, 4);
+  return f;
+}
+struct ShardPass {
+  unsigned long long maxkey = 0, minkey_inv = 0;
+  long long sum = 0;
+  std::vector<pf_sm3> aggs;
+};
+}  // namespace
+
+int pfmpe_shard_frame(pfmpe_handle* const* hs, int n_local, const pfmpe_frame_in* in, pfmpe_frame_out* out)
+{
+  if (!hs || n_local < 1 || !in || !out) return PFMPE_ERR_INVALID;
+  for (int i = 0; i < n_local; ++i) if (!hs[i]) return PFMPE_ERR_INVALID;
+  pfmpe_handle* h0 = hs[0];
+  const int W = h0->xworld, L = h0->cfg.n_leds;
+  const long long Ng = h0->n_global, n_loc = h0->cfg.n_particles;
+  for (int i = 0; i < n_local; ++i) {
+    pfmpe_handle* h = hs[i];
+    if (!h->sharded || !h->xmail_peers_dev || !h->peers_dev)
+      return fail(h, PFMPE_ERR_STATE, "pfmpe_shard_frame needs pfmpe_shard_configure, the peer mailboxes and the peer particle planes");
+    if (h->xworld != W || h->n_global != Ng || h->cfg.n_particles != n_loc || h->xseq != h0->xseq)
+      return fail(h, PFMPE_ERR_STATE, "the local shards do not belong to one filter / are out of step");
+    if (n_local > 1 && h->stream != h0->stream)   // stage kernels of co-located shards wait on one another through the mailboxes:
+      return fail(h, PFMPE_ERR_STATE, "shards that share a process must share one stream");   // stream order is what makes that safe
+  }
+  if ((long long)W * n_loc != Ng) return fail(h0, PFMPE_ERR_STATE, "the sharded frame call needs equal shards");
+  int rc;
+  for (int i = 0; i < n_local; ++i) if ((rc = pfmpe_shard_begin_frame(hs[i], in)) != PFMPE_OK) return rc;
+  const int D = in->n_image_points;
+  std::vector<int64_t> table((size_t)W * PF_XMAIL_WORDS);
+
+  auto score_pass = [&](int it, ShardPass& r) -> int {
+    for (int i = 0; i < n_local; ++i) {
+      int e = pfmpe_shard_score(hs[i], it, nullptr);
+      if (e) return e;
+      hs[i]->shard_passes += 1;
+    }
+    int e = pfmpe_shard_collect(h0, -1, table.data());
+    if (e) return e;
+    r = ShardPass();
+    r.aggs.resize(W);
+    for (int q = 0; q < W; ++q) {
+      const int64_t* row = &table[(size_t)q * PF_XMAIL_WORDS];
+      const unsigned long long a = (unsigned long long)row[0], b = (unsigned long long)row[1];
+      if (a > r.maxkey) r.maxkey = a;
+      if (b > r.minkey_inv) r.minkey_inv = b;
+      r.sum += row[2];
+      r.aggs[q].s = row[3]; r.aggs[q].mx = row[4]; r.aggs[q].mn = row[5];
+    }
+    return PFMPE_OK;
+  };
+
+  // ---- do { propagate, project, score } while (iter < 80 && max < L*min(5,D))  (:535-616)
+  const float thr_exit = (float)(L * (D < 5 ? D : 5));
+  float highest = 0.0f;
+  int best_it = -1, it = 0;
+  ShardPass kept, last;
+  for (;;) {
+    ShardPass r;
+    if ((rc = score_pass(it, r)) != PFMPE_OK) return rc;
+    const float m = shard_unord(r.maxkey >> 32);
+    last = r;
+    ++it;
+    if (m > highest) { highest = m; best_it = it - 1; kept = r; }       // :608-614 strict >, from 0
+    if (it < PF_MAX_ITER && m < thr_exit) continue;                      // :616
+    break;
+  }
+  const int iters = it;
+  if (best_it < 0) kept = last;                                          // :619 nothing to restore
+  else if (best_it != iters - 1) { if ((rc = score_pass(best_it, kept)) != PFMPE_OK) return rc; }   // regenerate (exact: RNG by address)
+
+  const long long S = kept.sum;
+  const bool accept = S != 0 && highest > (float)(L * (D < 3 ? D : 3));  // :633
+  const bool resampled = accept && in->it_since_initialized > 0;
+  const long long arg_max = (long long)((~kept.maxkey) & 0xFFFFFFFFull), arg_min = (long long)((~kept.minkey_inv) & 0xFFFFFFFFull);
+  long long q = S < 0 ? arg_min : arg_max;                               // :714 on the normalised weights
+  unsigned max_count = 0;
+  if (resampled) {
+    std::vector<pf_sm3> lower(W);
+    pf_sm3 run = pf_sm3_identity();
+    for (int r = 0; r < W; ++r) { lower[r] = run; run = pf_sm3_combine(run, kept.aggs[r]); }
+    for (int i = 0; i < n_local; ++i) {
+      const int r = hs[i]->xrank;
+      const int64_t lo[3] = {lower[r].s, lower[r].mx, lower[r].mn}, all[3] = {run.s, run.mx, run.mn};
+      if ((rc = pfmpe_shard_resample(hs[i], S, iters, lo, all, nullptr)) != PFMPE_OK) return rc;
+    }
+    if ((rc = pfmpe_shard_collect(h0, -1, table.data())) != PFMPE_OK) return rc;
+    unsigned long long cntkey = 0;
+    std::vector<long long> first(W + 1);
+    for (int r = 0; r < W; ++r) {
+      const unsigned long long c = (unsigned long long)table[(size_t)r * PF_XMAIL_WORDS];
+      if (c > cntkey) cntkey = c;
+      first[r] = table[(size_t)r * PF_XMAIL_WORDS + 1];
+    }
+    first[W] = Ng;      // a rank's slots end where the next rank's begin (its sources own nothing beyond); the last one ends at N
+    long long pos = 0;
+    for (int r = 0; r < W; ++r) {
+      if (first[r + 1] < first[r] || (first[r + 1] > first[r] && first[r] != pos)) return fail(h0, PFMPE_ERR_COMM, "resampled slot ranges do not tile the filter");
+      if (first[r + 1] > first[r]) pos = first[r + 1];
+    }
+    if (pos != Ng) return fail(h0, PFMPE_ERR_COMM, "resampled slot ranges do not cover the filter");
+    q = (long long)((~cntkey) & 0xFFFFFFFFull);                          // :686 first max of counterMeas
+    max_count = (unsigned)(cntkey >> 32);
+    for (int i = 0; i < n_local; ++i) {
+      const int r = hs[i]->xrank;
+      if ((rc = pfmpe_shard_scatter(hs[i], first[r], first[r + 1] - first[r])) != PFMPE_OK) return rc;
+    }
+    // every rank's scatter lands before anyone's next score pass: a barrier on the ranks' streams (co-located shards
+    // share a stream, which already orders them: all signals first, then one wait)
+    for (int i = 0; i < n_local; ++i) if ((rc = pfmpe_shard_signal(hs[i])) != PFMPE_OK) return rc;
+    if ((rc = pfmpe_shard_wait(h0)) != PFMPE_OK) return rc;
+  }
+  // ---- winner pose + correspondences from its owner (:687-691 / :714-716)
+  const int owner = (int)(q / n_loc);
+  for (int i = 0; i < n_local; ++i) {
+    if (hs[i]->xrank == owner) rc = pfmpe_shard_winner_publish(hs[i], (int)(q - (long long)owner * n_loc));
+    else rc = pfmpe_shard_advance(hs[i]);
+    if (rc) return rc;
+  }
+  if ((rc = pfmpe_shard_collect(h0, owner, table.data())) != PFMPE_OK) return rc;
+  const int64_t* row = &table[(size_t)owner * PF_XMAIL_WORDS];
+  std::memset(out, 0, sizeof *out);
+  out->status = accept ? 1 : 4;
+  out->iterations = iters;
+  out->best_iteration = best_it;
+  out->resampled = resampled ? 1 : 0;
+  out->highest_prob = (double)highest;
+  out->weight_sum = (double)S / 1073741824.0;
+  out->most_likely_particle_idx = accept ? (best_it >= 0 ? (int)arg_max : -1) : (int)q;
+  out->most_likely_pose_idx = resampled ? (int)q : -1;
+  out->max_count = max_count;
+  {
+    float wp[12];
+    std::memcpy(wp, row, sizeof wp);
+    pf_aff T;
+    for (int i = 0; i < 12; ++i) T.a[i] = (double)wp[i];
+    pf_aff_to_cm16(T, out->winner_pose);
+    uint32_t pr[2 * PF_MAX_LED];
+    std::memcpy(pr, row + 6, sizeof pr);
+    const int nc = (int)row[6 + PF_MAX_LED];
+    out->n_correspondences = nc;
+    for (int i = 0; i < 2 * PF_MAX_LED; ++i) out->correspondences[i] = i < 2 * nc ? pr[i] : 0u;
+  }
+  for (int i = 0; i < n_local; ++i) hs[i]->last_sum_fx[0] = S;
+  return PFMPE_OK;
+}
+
+int pfmpe_shard_track_frame_host(pfmpe_handle* const* hs, int n_local, double time_to_predict, const double* image_points,
+                                 int32_t n_image_points, uint32_t seed, pfmpe_track_result* out)
+{
+  if (!hs || n_local < 1 || !hs[0] || !out || (n_image_points > 0 && !image_points)) return PFMPE_ERR_INVALID;
+  pfmpe_handle* h = hs[0];
+  HostTrack& ht = h->host_trk[0];
+  if (!ht.valid) return fail(h, PFMPE_ERR_STATE, "track_init must precede track_frame_host");
+  pfmpe_frame_in in;
+  std::memset(&in, 0, sizeof in);
+  pf_aff P, pred;
+  pf_predict_pose(ht.prev, ht.cur, ht.t_prev, ht.t_cur, time_to_predict, P, pred);   // :234 -> :995-1010
+  in.image_points = image_points;
+  in.n_image_points = n_image_points;
+  in.it_since_initialized = ht.isi;
+  pf_aff_to_cm16(ht.cur, in.current_pose);
+  pf_aff_to_cm16(pred, in.predicted_pose);
+  pf_aff_to_cm16(P, in.prediction_matrix);
+  pf_aff_to_cm16(pf_aff_identity(), in.cam_move_inv);
+  in.dt = time_to_predict - ht.t_cur;
+  in.seed = seed;
+  pfmpe_frame_out fo;
+  const int rc = pfmpe_shard_frame(hs, n_local, &in, &fo);
+  if (rc) return rc;
+  std::memset(out, 0, sizeof *out);
+  out->status = fo.status; out->flag_fail = (float)fo.status; out->iterations = fo.iterations; out->gn_iterations = -1;
+  out->most_likely_pose_idx = fo.most_likely_pose_idx; out->max_count = fo.max_count;
+  out->highest_prob = fo.highest_prob; out->weight_sum = fo.weight_sum;
+  std::memcpy(out->winner_pose, fo.winner_pose, sizeof out->winner_pose);
+  out->n_correspondences = fo.n_correspondences;
+  std::memcpy(out->correspondences, fo.correspondences, sizeof out->correspondences);
+  if (fo.resampled) {
+    pf_aff pose = pf_aff_from_cm16(fo.winner_pose);         // predicted_pose_ = PoseParticle[q] (:687)
+    const pf_aff before = pose;
+    double c[36];
+    out->gn_iterations = pf_optimise_pose(h->K, &h->markers[0], image_points, fo.correspondences, fo.n_correspondences, pose, c);   // :690
+    if (ht.isi < 2) ++ht.isi;                               // :2027-2030
+    ht.prev = ht.cur; ht.cur = pose;                        // updatePose :2013-2014
+    if (time_to_predict - ht.t_cur > 0.001 || time_to_predict < ht.t_cur) { ht.t_prev = ht.t_cur; ht.t_cur = time_to_predict; }
+    for (int r = 0; r < 3; ++r)
+      for (int q = 0; q < 3; ++q)
+        if (fabs(before.a[4 * r + q] - pose.a[4 * r + q]) >= 0.3) out->flag_fail = 1.5f;   // :693-701
+    for (int r = 0; r < 36; ++r) ht.cov[r] = c[r];
+  } else {
+    ht.isi = 0;                                             // :710: the caller must re-initialise
+  }
+  for (int i = 1; i < n_local; ++i) hs[i]->host_trk[0] = ht;   // co-located shards track the same object
+  pf_aff_to_cm16(ht.cur, out->pose);
+  for (int r = 0; r < 6; ++r) for (int q = 0; q < 6; ++q) out->cov[r + 6 * q] = ht.cov[6 * r + q];
+  return PFMPE_OK;
+}
+
+int pfmpe_shard_passes(const pfmpe_handle* h, uint64_t* n)
+{
+  if (!h || !n) return PFMPE_ERR_INVALID;
+  *n = h->shard_passes;
+  return PFMPE_OK;
+}
+
+// ---- position-keyed checksums of the filter state (full-size parity checks without a host copy) ----------
+int pfmpe_state_checksum(pfmpe_handle* h, int tracker, uint64_t out[3])
+{
+  if (!h || !out) return PFMPE_ERR_INVALID;
+  if (tracker < 0 || tracker >= h->cfg.n_trackers) return fail(h, PFMPE_ERR_INVALID, "tracker out of range");
+  int rc = fetch_state(h, tracker);
+  if (rc) return rc;
+  const pf_tracker_state& s = h->h_state[tracker];
+  const size_t N = (size_t)h->cfg.n_particles;
+  if (!h->cksum) PF_CUDA(h, cudaMalloc((void**)&h->cksum, 3 * sizeof(unsigned long long)));
+  PF_CUDA(h, cudaMemsetAsync(h->cksum, 0, 3 * sizeof(unsigned long long), h->stream));
+  const float4* T = (s.t_buf == 0 ? h->pose0 : h->pose1) + (size_t)tracker * 3 * N;
+  const float4* src = (s.src_buf == 0 ? h->pose0 : h->pose1) + (size_t)tracker * 3 * N;
+  const int* gidx = (h->sharded && h->lead) ? h->lead : h->idx + (size_t)tracker * N;
+  int blocks = (int)((N + PF_BLOCK - 1) / PF_BLOCK);
+  if (blocks > h->num_sms * 16) blocks = h->num_sms * 16;
+  pf_checksum_kernel<<<blocks, PF_BLOCK, 0, h->stream>>>(T, h->w + (size_t)tracker * N, src, gidx, s.src_mode, (int)N,
+                                                          (unsigned long long)(h->sharded ? h->goff : 0), h->cksum);
+  PF_CUDA(h, cudaGetLastError());
+  h->launches += 1;
+  unsigned long long c[3];
+  PF_CUDA(h, cudaMemcpyAsync(c, h->cksum, sizeof c, cudaMemcpyDeviceToHost, h->stream));
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  for (int i = 0; i < 3; ++i) out[i] = c[i];
   return PFMPE_OK;
 }
 

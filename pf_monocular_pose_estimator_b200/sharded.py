@@ -216,7 +216,7 @@ class ShardedFilter:
 
     n_global must be a multiple of comm.world.  With `Loopback` all shards are handles on `device`."""
 
-    def __init__(self, n_global, comm, n_leds=5, max_blobs=32, device=0, rebalance="auto", mail=True, **kw):
+    def __init__(self, n_global, comm, n_leds=5, max_blobs=32, device=0, rebalance="auto", mail=True, loop="auto", **kw):
         import torch
         if n_global % comm.world:
             raise ValueError("n_global must be a multiple of the number of shards")
@@ -266,7 +266,14 @@ class ShardedFilter:
             if comm.all_ok(ok, self.dev):
                 self.partial_exchange = "mail"
                 comm.barrier(self.dev)                       # every mailbox is installed before the first message
-        self.passes = 0          # score passes launched so far (per shard)
+        # host loop of the frame: "c" = pfmpe_shard_frame (the product path: decisions in C from the mailbox partials; needs
+        # the peer mailboxes and the peer-memory rebalance), "python" = the stage-by-stage loop below (torch.distributed
+        # fallbacks and the per-stage profiling aid)
+        c_ok = self.partial_exchange == "mail" and self.rebalance == "p2p"
+        if loop == "c" and not c_ok:
+            raise RuntimeError("loop='c' needs the peer mailboxes and the peer-memory rebalance")
+        self.loop = "c" if (c_ok and loop in ("auto", "c")) else "python"
+        self._passes = 0         # score passes launched by the python loop (per shard)
         self.last = None
         self.stage_s = None      # set to {} to collect per-stage wall times (synchronises after every stage)
 
@@ -289,10 +296,29 @@ class ShardedFilter:
         self.stage_s[name] = self.stage_s.get(name, 0.0) + (t1 - t0)
         return t1
 
+    @property
+    def passes(self):
+        """Score passes launched so far (per shard)."""
+        return self._passes + (self.shards[0].shard_passes() if self.shards else 0)
+
     def close(self):
         for h in self.shards:
             h.close()
         self.shards = []
+
+    def state_checksums(self):
+        """Position-keyed device checksums summed over the LOCAL shards (add the ranks' values mod 2^64 for the filter's)."""
+        tot = [0, 0, 0]
+        for h in self.shards:
+            c = h.state_checksum()
+            tot = [(a + b) & 0xFFFFFFFFFFFFFFFF for a, b in zip(tot, c)]
+        return tot
+
+    def track_frame_host(self, time_to_predict, image_points, seed):
+        """One tracked frame from host buffers (predictPose -> sharded PF update -> Gauss-Newton), in C when the C loop is on."""
+        if self.loop == "c":
+            return capi.shard_track_frame_host(self.shards, time_to_predict, image_points, seed)
+        raise RuntimeError("track_frame_host needs loop='c' (use tests.host_loop.HostTracker around update() otherwise)")
 
     def configure(self, markers, K, params):
         for h in self.shards:
@@ -320,7 +346,7 @@ class ShardedFilter:
         t = self._mark("other", self._t)
         for i, h in enumerate(self.shards):
             h.shard_score(it, self.partials[i].data_ptr())
-        self.passes += 1
+        self._passes += 1
         t = self._mark("score", t)
         r = reduce_pass(self._gather())
         self._t = self._mark("gather", t)
@@ -330,6 +356,11 @@ class ShardedFilter:
         torch = self.torch
         keep = []
         fi = capi.make_frame_in(img, T_cur, T_pred, P, Cm, isi, dt, seed, keep)
+        if self.loop == "c" and self.stage_s is None:
+            out = capi.shard_frame(self.shards, fi)
+            out["sum_fx"] = int(round(out["weight_sum"] * Q30))
+            self.last = out
+            return out
         D = int(fi.n_image_points)
         import time
         self._t = time.perf_counter() if self.stage_s is not None else 0.0

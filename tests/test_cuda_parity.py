@@ -260,12 +260,7 @@ def test_full_size_properties():
     # expected offspring ~ N * w / S within one stratum
     exp = N * w / got["weight_sum"]
     assert np.abs(cnt - exp).max() < 2.0
-    # spot-check 2000 random particles against the oracle score of the reported pose
-    rng = np.random.default_rng(0)
-    for n in rng.integers(0, N, 2000):
-        uv = S.project(fi["K"], got["T"][n], fi["markers"])
-        v, _ = orc.score(fi["params"], fi["img"], uv)
-        assert abs(v - w[n]) <= 1e-5 * max(1.0, abs(v)) or abs(v - w[n]) > 4.0   # (gate ties jump by ~L)
+    # (every weight of this configuration is compared with the oracle in tests/test_cuda_fullsize.py)
     h.close()
 
 
