@@ -111,8 +111,14 @@ __device__ __forceinline__ void pf_grid_barrier(const pf_kparams& p, pf_bar& bar
 // the slot back: one reader per CTA) -> shared memory -> everyone.
 // Slot rotation: round e uses slot e%3; slot (e+2)%3 (last read before the barrier of round e) is
 // re-zeroed by CTA 0 after the barrier.  red_smem: PF_MAX_WARPS + 1 entries.
+// Cluster-pair mode (p.coop == 2: the two CTAs of a thread-block cluster share one filter): the CTA results and prefix
+// aggregates are exchanged through distributed shared memory -- each CTA stores its entry into both CTAs' xch[] -- and
+// one cluster barrier replaces the global atomics and the polling barrier.  xch is double-buffered by round parity: a
+// CTA that runs ahead writes the next round's buffer while its partner may still be reading this round's.
+struct pf_xch { pf_red r; pf_sm3 agg; };
+
 __device__ __noinline__ pf_red pf_grid_reduce(pf_red v, pf_red* red_smem, const pf_kparams& p, pf_bar& bar,
-                                              const pf_sm3* warp_agg)
+                                              const pf_sm3* warp_agg, pf_xch (*xch)[2])
 {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 #pragma unroll 1
@@ -142,7 +148,18 @@ __device__ __noinline__ pf_red pf_grid_reduce(pf_red v, pf_red* red_smem, const 
       r.cntkey = c > r.cntkey ? c : r.cntkey;
       r.sum += s;
     }
-    if (p.coop) {
+    if (p.coop == 2) {
+      pf_sm3 agg = pf_sm3_identity();
+      if (warp_agg) agg = pf_warp0_combine_agg(warp_agg, lane);          // valid in lane 0
+      agg.s = __shfl_sync(PF_FULL, agg.s, 0); agg.mx = __shfl_sync(PF_FULL, agg.mx, 0); agg.mn = __shfl_sync(PF_FULL, agg.mn, 0);
+      if (lane < 2) {                                     // lane d delivers this CTA's entry to CTA d of the pair (r: all lanes hold it)
+        cg::cluster_group cl = cg::this_cluster();
+        pf_xch* dst = cl.map_shared_rank(&xch[bar.round & 1u][0], lane);
+        pf_xch e;
+        e.r = r; e.agg = agg;
+        dst[cl.block_rank()] = e;
+      }
+    } else if (p.coop == 1) {
       pf_sm3 agg = pf_sm3_identity();
       if (warp_agg) agg = pf_warp0_combine_agg(warp_agg, lane);
       if (lane == 0) {
@@ -166,8 +183,19 @@ __device__ __noinline__ pf_red pf_grid_reduce(pf_red v, pf_red* red_smem, const 
     }
     if (lane == 0) red_smem[PF_MAX_WARPS] = r;
   }
+  if (p.coop == 2) {
+    cg::this_cluster().sync();                            // both entries of this round are in place (release / acquire)
+    const pf_xch* x = xch[bar.round & 1u];
+    pf_red r;
+    r.maxkey = x[0].r.maxkey > x[1].r.maxkey ? x[0].r.maxkey : x[1].r.maxkey;
+    r.minkey_inv = x[0].r.minkey_inv > x[1].r.minkey_inv ? x[0].r.minkey_inv : x[1].r.minkey_inv;
+    r.cntkey = x[0].r.cntkey > x[1].r.cntkey ? x[0].r.cntkey : x[1].r.cntkey;
+    r.sum = x[0].r.sum + x[1].r.sum;
+    bar.round += 1u;
+    return r;
+  }
   __syncthreads();
-  if (p.coop) bar.done += 1ull;
+  if (p.coop == 1) bar.done += 1ull;
   bar.round += 1u;
   return red_smem[PF_MAX_WARPS];
 }
@@ -183,7 +211,7 @@ __device__ __forceinline__ void pf_stamp(const pf_kparams& p, int slot)
 
 __device__ __forceinline__ void pf_sync_all(const pf_kparams& p, pf_bar& bar)
 {
-  if (p.coop) pf_grid_barrier(p, bar); else __syncthreads();
+  if (p.coop == 1) pf_grid_barrier(p, bar); else if (p.coop == 2) cg::this_cluster().sync(); else __syncthreads();
 }
 
 __device__ __forceinline__ pf_pose pf_load_pose(const float4* base, int N, int n)
@@ -517,13 +545,16 @@ __device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_c
 // (+) (aggregates of warps 0..w-1 of this CTA) = everything before warp w; scr[PF_MAX_WARPS] = the
 // combination of the whole filter.  Ends with a __syncthreads.
 template <bool SH>
-__device__ __noinline__ void pf_cta_prefix(const pf_kparams& p, const pf_sm3* warp_agg, pf_sm3* scr)
+__device__ __noinline__ void pf_cta_prefix(const pf_kparams& p, const pf_sm3* warp_agg, pf_sm3* scr, const pf_xch* xlast)
 {
   const int nwarps = blockDim.x >> 5;
   if (threadIdx.x < 32) {
     const int lane = threadIdx.x;
     pf_sm3 excl = pf_sm3_identity(), total = pf_sm3_identity();
-    if (p.coop) {
+    if (p.coop == 2) {                                    // the pair's aggregates of the last score pass (xlast[0], xlast[1])
+      if (blockIdx.x == 1) excl = xlast[0].agg;
+      total = pf_sm3_combine(xlast[0].agg, xlast[1].agg);
+    } else if (p.coop) {
       // lane l owns the contiguous entries [l*seg, (l+1)*seg); loads are issued 4 at a time before use
       const int b = blockIdx.x, G = gridDim.x;
       const long long* g = reinterpret_cast<const long long*>(p.cta_agg);
@@ -571,7 +602,7 @@ __device__ __noinline__ void pf_cta_prefix(const pf_kparams& p, const pf_sm3* wa
       excl = pf_sm3_combine(re, excl);
     }
     if (lane < nwarps) scr[lane] = pf_sm3_combine(excl, we);
-    if (!p.coop) {                                        // one CTA: the total is the combination of its warps
+    if (p.coop == 0) {                                    // one CTA: the total is the combination of its warps
       total.s = pf_shfl_ll(w.s, 31); total.mx = pf_shfl_ll(w.mx, 31); total.mn = pf_shfl_ll(w.mn, 31);
     }
     if ((SH && p.mode == 4)) { total.s = p.rank_total[0]; total.mx = p.rank_total[1]; total.mn = p.rank_total[2]; }
@@ -716,7 +747,7 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
         if ((SH && p.mode == 4) && valid && n == N - 1) p.shard_partial[2] = (long long)Ecur + kbase;   // end of this rank's slots
         const int E0 = __shfl_sync(PF_FULL, Eprev, 0), R = __shfl_sync(PF_FULL, Ecur, 31) - E0;
         bool listed = false;
-        if (p.coop && R > PF_FILL_STEP) {
+        if (p.coop == 1 && R > PF_FILL_STEP) {
           // heavy step (grid mode): its slots are filled after the stage's barrier by whichever warp of
           // the grid picks the entry up (pf_grid_fill); pieces of at most PF_FILL_SPLIT slots
           const int parts = (R + PF_FILL_SPLIT - 1) / PF_FILL_SPLIT;
@@ -735,7 +766,7 @@ __device__ __forceinline__ pf_red pf_stage_resample(const pf_kparams& p, const p
             listed = true;
           }
         }
-        const unsigned bigm = p.coop ? 0u : __ballot_sync(PF_FULL, own > PF_FILL_WARP);
+        const unsigned bigm = p.coop == 1 ? 0u : __ballot_sync(PF_FULL, own > PF_FILL_WARP);
         const int maxown = listed ? 0 : __reduce_max_sync(PF_FULL, own);
         if (listed) {
         } else if (bigm == 0u && maxown <= 6 * ((R + 31) >> 5)) {
@@ -1019,6 +1050,7 @@ __global__ void __launch_bounds__(V == 3 ? PF_BLOCK : PF_MAX_BLOCK, V == 3 ? 4 :
   __shared__ pf_sm3 warp_agg[PF_MAX_WARPS];
   __shared__ pf_sm3 scr[PF_MAX_WARPS + 1];
   __shared__ pf_fill_list fill;
+  __shared__ pf_xch xch[2][2];          // cluster-pair mode: [round parity][CTA of the pair]
   __shared__ uint32_t tab[PF_RNG_TAB_WORDS];   // radix-512 power tables of the RNG skip-ahead
 
   const int trk = p.tracker_base + blockIdx.y;
@@ -1026,8 +1058,8 @@ __global__ void __launch_bounds__(V == 3 ? PF_BLOCK : PF_MAX_BLOCK, V == 3 ? 4 :
   // reduction-slot rotation and the barrier count continue across launches (accum[3]); every CTA
   // reads them before its first barrier, CTA 0 writes them back after its last one
   pf_bar bar;
-  bar.round = p.coop ? (unsigned)(*(volatile unsigned long long*)&p.accum[3].maxkey) : 0u;
-  bar.done = p.coop ? *(volatile unsigned long long*)&p.accum[3].minkey_inv : 0ull;
+  bar.round = p.coop == 1 ? (unsigned)(*(volatile unsigned long long*)&p.accum[3].maxkey) : 0u;
+  bar.done = p.coop == 1 ? *(volatile unsigned long long*)&p.accum[3].minkey_inv : 0ull;
 
   // tracker state and the staged constants of the first frame: global -> shared (every CTA)
   {
@@ -1085,10 +1117,10 @@ __global__ void __launch_bounds__(V == 3 ? PF_BLOCK : PF_MAX_BLOCK, V == 3 ? 4 :
     while (!SH || p.mode < 4) {
       pf_red r = pf_stage_score<L, V>(p, cx, blobs, tab, trk, (SH && p.mode == 3) ? p.pass_it : (regen ? best_it : it), warp_agg);
       if (it == 0) pf_stamp(p, 2);
-      r = pf_grid_reduce(r, red_smem, p, bar, warp_agg);
+      r = pf_grid_reduce(r, red_smem, p, bar, warp_agg, xch);
       if (it == 0) pf_stamp(p, 3);
       if ((SH && p.mode == 3)) {   // this shard's (max, first argmax), (min, first argmin), sum and prefix aggregate
-        pf_cta_prefix<SH>(p, warp_agg, scr);
+        pf_cta_prefix<SH>(p, warp_agg, scr, xch[(bar.round + 1u) & 1u]);
         if (blockIdx.x == 0 && threadIdx.x == 0) {
           p.shard_partial[0] = (long long)r.maxkey; p.shard_partial[1] = (long long)r.minkey_inv; p.shard_partial[2] = r.sum;
           p.shard_partial[3] = scr[PF_MAX_WARPS].s; p.shard_partial[4] = scr[PF_MAX_WARPS].mx; p.shard_partial[5] = scr[PF_MAX_WARPS].mn;
@@ -1131,12 +1163,12 @@ __global__ void __launch_bounds__(V == 3 ? PF_BLOCK : PF_MAX_BLOCK, V == 3 ? 4 :
     if (resampled && !(SH && p.mode == 5)) {
       pf_stamp(p, 4);
       if (threadIdx.x == 0) fill.n = 0;                  // ordered before its use by the barrier in pf_cta_prefix
-      pf_cta_prefix<SH>(p, warp_agg, scr);
+      pf_cta_prefix<SH>(p, warp_agg, scr, xch[(bar.round + 1u) & 1u]);
       pf_stamp(p, 12);
       cnt = pf_stage_resample<SH>(p, cx, tab, trk, kept.sum, iters, scr, &fill);
       pf_stamp(p, 5);
-      cnt = pf_grid_reduce(cnt, red_smem, p, bar, nullptr);
-      if (p.coop && cnt.sum > 0) pf_grid_fill(p, trk, bar, (int)cnt.sum, SH ? p.N_global : N, SH);
+      cnt = pf_grid_reduce(cnt, red_smem, p, bar, nullptr, xch);
+      if (p.coop == 1 && cnt.sum > 0) pf_grid_fill(p, trk, bar, (int)cnt.sum, SH ? p.N_global : N, SH);
       pf_stamp(p, 6);
     }
 
@@ -1172,7 +1204,7 @@ __global__ void __launch_bounds__(V == 3 ? PF_BLOCK : PF_MAX_BLOCK, V == 3 ? 4 :
     pf_stamp(p, 8);
     pf_stamp(p, 9);
   }
-  if (p.coop && blockIdx.x == 0 && threadIdx.x == 0) {
+  if (p.coop == 1 && blockIdx.x == 0 && threadIdx.x == 0) {
     p.accum[3].maxkey = (unsigned long long)(bar.round % 3u);
     p.accum[3].minkey_inv = bar.done;
   }

@@ -349,7 +349,7 @@ int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_f
   if (!k) return fail(h, PFMPE_ERR_UNSUPPORTED, "n_leds must be 1..8");
   const size_t smem = pf_blob_smem_bytes(h->cfg.max_blobs);
   bool grid_mode;
-  if (h->force_mode == 1) grid_mode = false;
+  if (h->force_mode == 1 || h->force_mode == 3) grid_mode = false;
   else if (h->force_mode == 2) grid_mode = true;
   else grid_mode = (nt == 1) ? (N > 1024) : (N > 16384);
   if (!grid_mode && mode < 3 && !distort) k = kernel_for(h->cfg.n_leds, 3);   // batch shape: the 64-register build
@@ -414,12 +414,41 @@ int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_f
       if (const char* e = std::getenv("PFMPE_BATCH_BLOCK")) { const int b = std::atoi(e); if (b >= 32 && b <= PF_BLOCK && b % 32 == 0) block = b; }
       h->batch_nt = nt; h->batch_kernel = (const void*)k; h->batch_block = block;
     }
+    // Cluster-pair shape (opt-in: cfg.reserved[0] = 3 or PFMPE_CLUSTER=1): every filter is split over a thread-block
+    // cluster of two 128-thread CTAs that reduce through distributed shared memory -- twice as many, half as large
+    // units for batches that leave the SMs unevenly loaded (512 filters on 148 SMs).  Measured on one B200
+    // (profiles/r02_cluster_ab.txt) it is a wash -- 512 filters 0.1136 -> 0.1121 ms, 4096 filters 0.723 -> 0.758 ms: what
+    // a small batch loses is not the 4-versus-3 CTAs per SM but the phase lock of a single wave (every CTA stages its
+    // detections, then every CTA reduces, then every CTA writes its record at the same time) -- so it is not the default.
+    bool pair = h->force_mode == 3 && mode <= 2 && !distort;
+    if (const char* e = std::getenv("PFMPE_CLUSTER")) pair = std::atoi(e) != 0 && nt >= 1 && mode <= 2 && !distort && h->force_mode != 1;
+    if (pair) {
+      const int cblock = 128;
+      p.coop = 2;
+      p.cta_chunk = ((N + 1) / 2 + cblock - 1) / cblock * cblock;
+      h->info[0] = 2; h->info[1] = nt; h->info[2] = cblock; h->info[3] = 2;
+      cudaLaunchConfig_t lc;
+      std::memset(&lc, 0, sizeof lc);
+      lc.gridDim = dim3(2, (unsigned)nt, 1);
+      lc.blockDim = dim3(cblock, 1, 1);
+      lc.dynamicSmemBytes = smem;
+      lc.stream = h->stream;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeClusterDimension;
+      at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+      lc.attrs = at;
+      lc.numAttrs = 1;
+      void* args[] = {(void*)&p};
+      PF_CUDA(h, cudaLaunchKernelExC(&lc, (const void*)k, args));
+      h->launches += 1;
+    } else {
     p.cta_chunk = (N + block - 1) / block * block;
     dim3 grid(1, (unsigned)nt, 1);
     h->info[0] = 1; h->info[1] = nt; h->info[2] = block; h->info[3] = 0;
     k<<<grid, block, smem, h->stream>>>(p);
     PF_CUDA(h, cudaGetLastError());
     h->launches += 1;
+    }
   } else {
     int block = PF_GRID_BLOCK;
     if (const char* e = std::getenv("PFMPE_GRID_BLOCK")) {   // experiment: the 64-register build, 256-thread CTAs, 4 per SM

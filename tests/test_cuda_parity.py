@@ -32,6 +32,8 @@ CASES = [
     (5000, 31, 2, 10, 2, 0),        # look-back over 5 scan tiles
     (300, 17, 2, 200, 0, 0),        # outlier-heavy (config 3 shape)
     (100000, 40, 2, 10, 0, 0),      # config 2 size, auto geometry
+    (5000, 31, 2, 10, 3, 0),        # cluster pair: two 128-thread CTAs share the filter through distributed shared memory
+    (100, 5, 2, 10, 3, 0),          # ... with an (almost) empty second CTA
 ]
 
 
@@ -177,7 +179,7 @@ def test_grid_and_batch_paths_are_bit_identical():
     N = 3000
     fi = frame_inputs(N, frame=19)
     outs = []
-    for mode, cap in [(1, 0), (2, 2), (2, 5), (2, 0)]:
+    for mode, cap in [(1, 0), (2, 2), (2, 5), (2, 0), (3, 0)]:
         h = make_handle(fi, N, force_mode=mode, grid_cap=cap)
         outs.append(run_frame(h, fi))
         h.close()
@@ -206,14 +208,16 @@ def test_second_frame_gathers_through_resample_indices(N, mode):
     h.close()
 
 
-def test_update_batch_matches_single_updates():
-    N, T = 512, 5
+@pytest.mark.parametrize("N,T,mode,shape", [(512, 5, 0, [1, 5, 256, 0]), (4096, 6, 3, [2, 6, 128, 2])])
+def test_update_batch_matches_single_updates(N, T, mode, shape):
+    """One launch for all trackers: one CTA per filter, or (force_mode 3) a cluster pair per filter."""
     fis = [frame_inputs(N, frame=10 + t, tracker=t) for t in range(T)]
-    hb = make_handle(fis[0], N, n_trackers=T)
+    hb = make_handle(fis[0], N, n_trackers=T, force_mode=mode)
     for t in range(T):
         hb.set_particles(fis[t]["E"], tracker=t)
     outs = hb.update_batch([dict(img=f["img"], T_cur=f["T_cur"], T_pred=f["T_pred"], P=f["P"], Cm=f["Cm"], isi=f["isi"],
                                  dt=f["dt"], seed=f["seed"]) for f in fis])
+    assert hb.launch_info() == shape
     for t in range(T):
         got = collect(hb, outs[t], tracker=t)
         ora = _oracle(fis[t], N)

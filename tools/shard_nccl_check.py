@@ -83,7 +83,7 @@ def main():
     if world > 1:
         dist.all_reduce(t)
     if rank == 0:
-        print(json.dumps(dict(check="shard_nccl", rebalance=sh.rebalance, partials=sh.partial_exchange, p2p_error=sh.p2p_error, world=world, particles=N, frames=a.frames, mismatches=int(t.item()),
+        print(json.dumps(dict(check="shard_nccl", loop=sh.loop, rebalance=sh.rebalance, partials=sh.partial_exchange, p2p_error=sh.p2p_error, world=world, particles=N, frames=a.frames, mismatches=int(t.item()),
                               ms_per_frame_host_loop=round(1e3 * float(np.median(t_sh)), 3),
                               all_ms=[round(1e3 * v, 2) for v in t_sh])))
     if world > 1:
