@@ -214,20 +214,22 @@ __device__ __forceinline__ void pf_sync_all(const pf_kparams& p, pf_bar& bar)
   if (p.coop == 1) pf_grid_barrier(p, bar); else if (p.coop == 2) cg::this_cluster().sync(); else __syncthreads();
 }
 
-__device__ __forceinline__ pf_pose pf_load_pose(const float4* base, int N, int n)
+// base: three planes of float4 (row i of [R|t] in plane i), S = plane stride in float4 (= particles per tracker; twice that
+// for a sharded filter, whose planes carry a receive area behind the shard's own rows)
+__device__ __forceinline__ pf_pose pf_load_pose(const float4* base, int S, int n)
 {
-  const float4 r0 = base[n], r1 = base[(size_t)N + n], r2 = base[2 * (size_t)N + n];
+  const float4 r0 = base[n], r1 = base[(size_t)S + n], r2 = base[2 * (size_t)S + n];
   pf_pose T;
   T.p[0] = r0.x; T.p[1] = r0.y; T.p[2] = r0.z; T.p[3] = r0.w;
   T.p[4] = r1.x; T.p[5] = r1.y; T.p[6] = r1.z; T.p[7] = r1.w;
   T.p[8] = r2.x; T.p[9] = r2.y; T.p[10] = r2.z; T.p[11] = r2.w;
   return T;
 }
-__device__ __forceinline__ void pf_store_pose(float4* base, int N, int n, const pf_pose& T)
+__device__ __forceinline__ void pf_store_pose(float4* base, int S, int n, const pf_pose& T)
 {
   base[n] = make_float4(T.p[0], T.p[1], T.p[2], T.p[3]);
-  base[(size_t)N + n] = make_float4(T.p[4], T.p[5], T.p[6], T.p[7]);
-  base[2 * (size_t)N + n] = make_float4(T.p[8], T.p[9], T.p[10], T.p[11]);
+  base[(size_t)S + n] = make_float4(T.p[4], T.p[5], T.p[6], T.p[7]);
+  base[2 * (size_t)S + n] = make_float4(T.p[8], T.p[9], T.p[10], T.p[11]);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -412,7 +414,8 @@ __device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_c
   constexpr bool SH = V == 1, DIST = V == 2;   // kernel variants: 1 sharded stages, 2 plumb_bob projection
   const int N = p.N;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const size_t tb = (size_t)trk * 3 * (size_t)N;
+  const int S = p.pstride;
+  const size_t tb = (size_t)trk * 3 * (size_t)S;
   // no __restrict__/const on buffers that other stages of this launch write
   const float4* src = (cx.src_buf == 0 ? p.pose0 : p.pose1) + tb;
   float4* dst = (cx.src_buf == 0 ? p.pose1 : p.pose0) + tb;
@@ -460,7 +463,7 @@ __device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_c
     pf_pose T;
     const int ng = goff + n;                               // global particle index (sharded filter: goff > 0)
     if (ng >= 2) {
-      pf_pose B = pf_load_pose(src, N, s);
+      pf_pose B = pf_load_pose(src, S, s);
       if (cam_mul) { pf_pose Cm; for (int i = 0; i < 12; ++i) Cm.p[i] = cx.fc.C[i]; B = pf_affine_mul(Cm, B); }
       if (use_pred) { pf_pose Pm; for (int i = 0; i < 12; ++i) Pm.p[i] = cx.fc.P[i]; B = pf_affine_mul(B, Pm); }
       T = pf_propagate(B, x, cx.fc.noise, scale, ang_mode);
@@ -469,7 +472,7 @@ __device__ __forceinline__ pf_red pf_stage_score(const pf_kparams& p, const pf_c
 #pragma unroll
       for (int i = 0; i < 12; ++i) T.p[i] = t0[i];
     }
-    pf_store_pose(dst, N, n, T);
+    pf_store_pose(dst, S, n, T);
     // camera coordinates of every LED first, then one (uniform) branch on the shape of K for all of them
     float xc[L], yc[L], zc[L];
 #pragma unroll
@@ -887,8 +890,8 @@ __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, pf_ctx& cx, pf_t
   const bool writer = blockIdx.x == 0 && lane == 0;
   const bool seq_mode = p.mode == 1 || p.mode == 2;
   pf_frame_result* res = p.result + (seq_mode ? (size_t)trk * p.total_frames + frame : (size_t)trk);
-  const int dst_buf = 1 - cx.src_buf;
-  const float4* T = (dst_buf == 0 ? p.pose0 : p.pose1) + (size_t)trk * 3 * (size_t)N;
+  const int dst_buf = (SH && p.mode == 5) ? st.t_buf : 1 - cx.src_buf;   // sharded winner stage: a launch of its own, after the resampling may have made T the source
+  const float4* T = (dst_buf == 0 ? p.pose0 : p.pose1) + (size_t)trk * 3 * (size_t)p.pstride;
 
   const int arg_max = (int)(~(unsigned)(kept.maxkey & 0xFFFFFFFFull));
   const int arg_min = (int)(unsigned)((~kept.minkey_inv) & 0xFFFFFFFFull);
@@ -897,7 +900,7 @@ __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, pf_ctx& cx, pf_t
   else q = kept.sum < 0 ? arg_min : arg_max;                            // :714 on the normalised weights (Q6)
   if ((SH && p.mode == 5)) q = p.q_local;                                       // sharded: chosen across the ranks by the host
 
-  const pf_pose Tw = pf_load_pose(T, N, q);
+  const pf_pose Tw = pf_load_pose(T, p.pstride, q);
   unsigned pairs[2 * L];
   int npairs = 0;
 #pragma unroll
@@ -1122,6 +1125,7 @@ __global__ void __launch_bounds__(V == 3 ? PF_BLOCK : PF_MAX_BLOCK, V == 3 ? 4 :
       if ((SH && p.mode == 3)) {   // this shard's (max, first argmax), (min, first argmin), sum and prefix aggregate
         pf_cta_prefix<SH>(p, warp_agg, scr, xch[(bar.round + 1u) & 1u]);
         if (blockIdx.x == 0 && threadIdx.x == 0) {
+          p.state[trk].t_buf = 1 - cx.src_buf;        // where this pass left PoseParticle (getters, winner stage)
           p.shard_partial[0] = (long long)r.maxkey; p.shard_partial[1] = (long long)r.minkey_inv; p.shard_partial[2] = r.sum;
           p.shard_partial[3] = scr[PF_MAX_WARPS].s; p.shard_partial[4] = scr[PF_MAX_WARPS].mx; p.shard_partial[5] = scr[PF_MAX_WARPS].mn;
         }
@@ -1176,7 +1180,11 @@ __global__ void __launch_bounds__(V == 3 ? PF_BLOCK : PF_MAX_BLOCK, V == 3 ? 4 :
       if (blockIdx.x == 0 && threadIdx.x == 0) {
         p.shard_partial[0] = (long long)cnt.cntkey;
         pf_tracker_state* g = p.state + trk;
-        g->t_buf = 1 - cx.src_buf; g->src_mode = p.lead_mode ? 1 : 0; g->frames_done = st.frames_done + 1;
+        // peer-memory rebalance: the propagated set itself becomes the source (rows that stay on their rank are not moved;
+        // lead[] indexes the shard's own rows [0, N) and the receive area [N, 2N) behind them).  Row exchange: full rows
+        // are written over the old source set, no indirection.
+        g->t_buf = 1 - cx.src_buf; g->frames_done = st.frames_done + 1;
+        if (p.lead_mode) { g->src_buf = 1 - cx.src_buf; g->src_mode = 1; } else g->src_mode = 0;
       }
       pf_shard_publish(p, 2);
       continue;
@@ -1211,21 +1219,21 @@ __global__ void __launch_bounds__(V == 3 ? PF_BLOCK : PF_MAX_BLOCK, V == 3 ? 4 :
 }
 
 // Materialise newPoseEstimation (the resampled set) for the getters / ROI: out[n] = T[idx[n]].
-__global__ void __launch_bounds__(PF_BLOCK) pf_gather_kernel(const float4* T, const int* idx, int N, int src_mode,
+__global__ void __launch_bounds__(PF_BLOCK) pf_gather_kernel(const float4* T, const int* idx, int N, int S, int src_mode,
                                                              float4* out, int* idx_out)
 {
   const int n = blockIdx.x * PF_BLOCK + threadIdx.x;
   if (n >= N) return;
   const int s = src_mode == 1 ? idx[n] : n;
   out[n] = T[s];
-  out[(size_t)N + n] = T[(size_t)N + s];
-  out[2 * (size_t)N + n] = T[2 * (size_t)N + s];
+  out[(size_t)N + n] = T[(size_t)S + s];
+  out[2 * (size_t)N + n] = T[2 * (size_t)S + s];
   if (idx_out) idx_out[n] = s;
 }
 
 // Sharded filter: rows of the resampled set this rank produced.  Global slot k in [first, first +
 // count) was filled by the local source idx[k - kbase]; a row is the 12 floats of T (3 x float4).
-__global__ void __launch_bounds__(PF_BLOCK) pf_shard_export_kernel(const float4* T, const int* idx, int N, long long kbase,
+__global__ void __launch_bounds__(PF_BLOCK) pf_shard_export_kernel(const float4* T, const int* idx, int S, long long kbase,
                                                                    long long first, long long count, int use_idx,
                                                                    float4* rows)
 {
@@ -1234,25 +1242,25 @@ __global__ void __launch_bounds__(PF_BLOCK) pf_shard_export_kernel(const float4*
   const long long k = first + i - kbase;
   const int s = use_idx ? idx[k] : (int)k;
   rows[3 * i] = T[s];
-  rows[3 * i + 1] = T[(size_t)N + s];
-  rows[3 * i + 2] = T[2 * (size_t)N + s];
+  rows[3 * i + 1] = T[(size_t)S + s];
+  rows[3 * i + 2] = T[2 * (size_t)S + s];
 }
 
 // Sharded filter: rows received from other ranks become local particles [off, off + count) of the
 // set read by the next frame.
-__global__ void __launch_bounds__(PF_BLOCK) pf_shard_import_kernel(const float4* rows, int N, int off, int count, float4* dst)
+__global__ void __launch_bounds__(PF_BLOCK) pf_shard_import_kernel(const float4* rows, int S, int off, int count, float4* dst)
 {
   const int i = blockIdx.x * PF_BLOCK + threadIdx.x;
   if (i >= count) return;
   const int n = off + i;
   dst[n] = rows[3 * (size_t)i];
-  dst[(size_t)N + n] = rows[3 * (size_t)i + 1];
-  dst[2 * (size_t)N + n] = rows[3 * (size_t)i + 2];
+  dst[(size_t)S + n] = rows[3 * (size_t)i + 1];
+  dst[2 * (size_t)S + n] = rows[3 * (size_t)i + 2];
 }
 
 // Sharded filter: output slots that stay on this rank go straight from T (through idx) to the
 // next frame's particle set, plane to plane: slot first + i -> local particle off + i.
-__global__ void __launch_bounds__(PF_BLOCK) pf_shard_keep_kernel(const float4* T, const int* idx, int N, long long kbase,
+__global__ void __launch_bounds__(PF_BLOCK) pf_shard_keep_kernel(const float4* T, const int* idx, int S, long long kbase,
                                                                  long long first, int count, int off, float4* dst)
 {
   const int i = blockIdx.x * PF_BLOCK + threadIdx.x;
@@ -1260,26 +1268,24 @@ __global__ void __launch_bounds__(PF_BLOCK) pf_shard_keep_kernel(const float4* T
   const int s = idx[first + i - kbase];
   const int n = off + i;
   dst[n] = T[s];
-  dst[(size_t)N + n] = T[(size_t)N + s];
-  dst[2 * (size_t)N + n] = T[2 * (size_t)N + s];
+  dst[(size_t)S + n] = T[(size_t)S + s];
+  dst[2 * (size_t)S + n] = T[2 * (size_t)S + s];
 }
 
-// Sharded filter, peer-memory rebalance: every output slot this rank produced is written straight
-// into the particle set of the rank that owns the slot -- its own HBM or, through NVLink peer
-// stores, another GPU's (peers[d] = base of rank d's next-frame particle planes, N particles per
-// rank).  Slot k = kbase + i -> rank k / N, local particle k % N.  One kernel replaces the row
-// export, the all_to_all and the import; remote and local stores overlap across CTAs.
-// Every rank's allocation is [3 N float4 planes | N int lead].
-__global__ void __launch_bounds__(PF_BLOCK) pf_shard_scatter_kernel(const float4* T, const int* idx, const int* kend, int N,
-                                                                    long long kbase, long long count, float4* const* peers)
+// Sharded filter, peer-memory rebalance.  Every output slot this rank produced (slot k = kbase + i, filled by the local
+// source idx[i]) belongs to rank k / N as its local slot k % N.  Nothing is copied for a slot that stays on its rank: the
+// propagated set T is the next frame's source set, and the slot's entry of lead[] simply names the source row.  A slot of
+// ANOTHER rank gets its row through NVLink peer stores into the receive area behind that rank's rows (plane entries
+// [N, 2N)), and lead[] points there.  Resampling replicates, so a run of slots with the same source inside one
+// destination's range travels as ONE row (stored at the run's first slot) and every slot of the run points to it; a slot
+// that continues a run has a source with >= 2 offspring, so the run starts at kend[s - 1] (the rank's first slot for
+// s = 0), clamped to the destination's first slot.  In a balanced frame the pass therefore moves 8 bytes per slot (idx
+// in, lead out) instead of 100 (idx, row in, row out).  bases[d] = rank d's allocation [pose0 planes | pose1 planes |
+// lead], tsel = which pose buffer holds T (the same on every rank), S = plane stride = 2 N.
+__global__ void __launch_bounds__(PF_BLOCK) pf_shard_scatter_kernel(const float4* T, const int* idx, const int* kend, int N, int S,
+                                                                    long long kbase, long long count, float4* const* bases,
+                                                                    int tsel, int me)
 {
-  // Resampling replicates: the slots of one source are consecutive, and after a few frames a handful of sources
-  // own most of them (measured on 2^26 particles over 8 GPUs: 3 398 surviving sources on one rank, which then had to
-  // push 7/8 of ALL rows through its NVLink ports: 2.8 ms).  So a run of equal sources inside one destination's
-  // range travels as ONE row, stored at the run's first slot (its leader), plus a 4-byte leader index per slot
-  // (lead[], behind the destination's planes); the destination's next score pass gathers through lead[], the way
-  // the single-GPU filter gathers through idx[].  A slot that continues a run has a source with >= 2 offspring, so
-  // the run starts at kend[s - 1] (the rank's first slot for s = 0), clamped to the destination's first slot.
   const long long stride = (long long)gridDim.x * PF_BLOCK;
   for (long long i = (long long)blockIdx.x * PF_BLOCK + threadIdx.x; i < count; i += stride) {
     const long long k = kbase + i;
@@ -1287,18 +1293,23 @@ __global__ void __launch_bounds__(PF_BLOCK) pf_shard_scatter_kernel(const float4
     const long long d0 = (long long)d * N;
     const int n = (int)(k - d0);
     const int s = idx[i];
-    const bool starts = i == 0 || k == d0 || idx[i - 1] != s;
-    float4* dst = peers[d];
-    int* lead = reinterpret_cast<int*>(dst + 3 * (size_t)N);
-    if (starts) {
-      const float4 r0 = T[s], r1 = T[(size_t)N + s], r2 = T[2 * (size_t)N + s];
-      dst[n] = r0;
-      dst[(size_t)N + n] = r1;
-      dst[2 * (size_t)N + n] = r2;
-      lead[n] = n;
+    float4* base = bases[d];
+    int* lead = reinterpret_cast<int*>(base + 6 * (size_t)S);
+    if (d == me) {
+      lead[n] = s;
     } else {
-      const long long fs = s > 0 ? (long long)kend[s - 1] : kbase;
-      lead[n] = (int)((fs > d0 ? fs : d0) - d0);
+      float4* dst = base + (tsel ? 3 * (size_t)S : 0) + N;            // receive area of the destination's T buffer
+      const bool starts = i == 0 || k == d0 || idx[i - 1] != s;
+      if (starts) {
+        const float4 r0 = T[s], r1 = T[(size_t)S + s], r2 = T[2 * (size_t)S + s];
+        dst[n] = r0;
+        dst[(size_t)S + n] = r1;
+        dst[2 * (size_t)S + n] = r2;
+        lead[n] = N + n;
+      } else {
+        const long long fs = s > 0 ? (long long)kend[s - 1] : kbase;
+        lead[n] = N + (int)((fs > d0 ? fs : d0) - d0);
+      }
     }
   }
 }
@@ -1344,7 +1355,7 @@ __device__ __forceinline__ unsigned long long pf_mix64(unsigned long long pos, u
   return z;
 }
 __global__ void __launch_bounds__(PF_BLOCK) pf_checksum_kernel(const float4* T, const float* w, const float4* src, const int* idx,
-                                                               int src_mode, int N, unsigned long long goff, unsigned long long* out)
+                                                               int src_mode, int N, int S, unsigned long long goff, unsigned long long* out)
 {
   unsigned long long a = 0, b = 0, c = 0;
   for (long long n = (long long)blockIdx.x * PF_BLOCK + threadIdx.x; n < N; n += (long long)gridDim.x * PF_BLOCK) {
@@ -1352,7 +1363,7 @@ __global__ void __launch_bounds__(PF_BLOCK) pf_checksum_kernel(const float4* T, 
     const int s = src_mode == 1 ? idx[n] : (int)n;
 #pragma unroll
     for (int pl = 0; pl < 3; ++pl) {
-      const float4 t = T[(size_t)pl * N + n], r = src[(size_t)pl * N + s];
+      const float4 t = T[(size_t)pl * S + n], r = src[(size_t)pl * S + s];
       a += pf_mix64(g * 16 + 4 * pl + 0, __float_as_uint(t.x)) + pf_mix64(g * 16 + 4 * pl + 1, __float_as_uint(t.y)) +
            pf_mix64(g * 16 + 4 * pl + 2, __float_as_uint(t.z)) + pf_mix64(g * 16 + 4 * pl + 3, __float_as_uint(t.w));
       c += pf_mix64(g * 16 + 4 * pl + 0, __float_as_uint(r.x)) + pf_mix64(g * 16 + 4 * pl + 1, __float_as_uint(r.y)) +

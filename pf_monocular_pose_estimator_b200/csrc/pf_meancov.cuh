@@ -44,7 +44,7 @@ __device__ __forceinline__ void pf_mc_block_sum(double (&v)[K], double* smem /* 
 __device__ __forceinline__ const float4* pf_mc_T(const pf_kparams& p, int trk)
 {
   const int tb = p.state[trk].t_buf;
-  return (tb == 0 ? p.pose0 : p.pose1) + (size_t)trk * 3 * (size_t)p.N;
+  return (tb == 0 ? p.pose0 : p.pose1) + (size_t)trk * 3 * (size_t)p.pstride;
 }
 
 __device__ __forceinline__ double pf_mc_inv_sum(const pf_kparams& p, int trk)
@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(PF_MC_THREADS) pf_meancov_pass1(const pf_kpara
 #pragma unroll
   for (int j = 0; j < 12; ++j) acc[j] = 0;
   for (int n = blockIdx.x * PF_MC_THREADS + threadIdx.x; n < N; n += gridDim.x * PF_MC_THREADS) {
-    const float4 r0 = T[n], r1 = T[(size_t)N + n], r2 = T[2 * (size_t)N + n];
+    const float4 r0 = T[n], r1 = T[(size_t)p.pstride + n], r2 = T[2 * (size_t)p.pstride + n];
     const double wn = (double)w[n] * inv;
     acc[0] += wn * r0.x; acc[1] += wn * r0.y; acc[2] += wn * r0.z; acc[3] += wn * r0.w;
     acc[4] += wn * r1.x; acc[5] += wn * r1.y; acc[6] += wn * r1.z; acc[7] += wn * r1.w;
@@ -153,7 +153,7 @@ __global__ void __launch_bounds__(PF_MC_THREADS) pf_meancov_pass2(const pf_kpara
 #pragma unroll
   for (int j = 0; j < 21; ++j) acc[j] = 0;
   for (int n = blockIdx.x * PF_MC_THREADS + threadIdx.x; n < N; n += gridDim.x * PF_MC_THREADS) {
-    const float4 r0 = T[n], r1 = T[(size_t)N + n], r2 = T[2 * (size_t)N + n];
+    const float4 r0 = T[n], r1 = T[(size_t)p.pstride + n], r2 = T[2 * (size_t)p.pstride + n];
     const double Rn[9] = {r0.x, r0.y, r0.z, r1.x, r1.y, r1.z, r2.x, r2.y, r2.z};
     pf_aff D = pf_aff_identity();                        // Rbar^T R_n, zero translation
 #pragma unroll

@@ -28,7 +28,7 @@ __global__ void __launch_bounds__(PF_BLOCK) pf_roi_kernel(const pf_kparams p, co
   __shared__ float red[4][PF_BLOCK / 32];
   const int trk = p.tracker_base + blockIdx.y, N = p.N;
   const pf_tracker_state* st = p.state + trk;
-  const float4* src = (st->src_buf == 0 ? p.pose0 : p.pose1) + (size_t)trk * 3 * (size_t)N;
+  const float4* src = (st->src_buf == 0 ? p.pose0 : p.pose1) + (size_t)trk * 3 * (size_t)p.pstride;
   const int* idx = p.lead ? p.lead : p.idx + (size_t)trk * N;   // sharded filter: lead[] (pf_shard_scatter_kernel)
   const bool through_idx = st->src_mode == 1;
   const bool kstd = p.kstd != 0;
@@ -40,7 +40,7 @@ __global__ void __launch_bounds__(PF_BLOCK) pf_roi_kernel(const pf_kparams p, co
     pf_pose T;
     if (n < N) {
       const int s = through_idx ? idx[n] : n;
-      T = pf_affine_mul(pf_affine_mul(Cm, pf_load_pose(src, N, s)), Pm);
+      T = pf_affine_mul(pf_affine_mul(Cm, pf_load_pose(src, p.pstride, s)), Pm);
     } else T = pred;                                  // :1047-1050
 #pragma unroll
     for (int j = 0; j < L; ++j) {

@@ -93,8 +93,9 @@ struct pf_kparams {
   int coop;                       // 1: grid-wide cooperation (gridDim.x > 1)
   int want_mean;                  // compute weighted mean / covariance
   int cta_chunk;                  // particles owned by one CTA (multiple of 32 * warps per CTA); warp w owns the w-th part
+  int pstride;                    // plane stride of the pose buffers in float4: N, or 2 N for a sharded filter (receive area)
   // particle state
-  float4* pose0; float4* pose1;   // [tracker][3 planes][N]
+  float4* pose0; float4* pose1;   // [tracker][3 planes][pstride]
   float*  w;                      // [tracker][N] raw scores of the kept iteration
   int*    kend;                   // [tracker][N] cumulative offspring count K(M_i)
   int*    idx;                    // [tracker][N] Particle_index of output slot n (:678-681), written by the resampling stage

@@ -143,7 +143,10 @@ struct pfmpe_handle {
   unsigned* roi_keys = nullptr;   // K8: [tracker][4] ordered-float keys, then the floats
   float* roi_out = nullptr;
   float* h_roi = nullptr;
-  int* lead = nullptr;                  // sharded: [N] gather indirection, lives behind pose0's planes (one IPC allocation)
+  int* lead = nullptr;                  // sharded: [N] gather indirection, behind the pose planes (one IPC allocation)
+  size_t pstride = 0;                   // plane stride of pose0 / pose1 in float4: N, or 2 N for a sharded filter
+  bool shard_alloc = false;             // pose0 / pose1 / lead are one allocation (freed through pose0)
+  int sh_src = 0;                       // sharded: host mirror of the source-buffer selector (stage calls are issued in order)
   unsigned char* p3p_buf = nullptr;     // K9 scratch: detections, sorted copy, bearing vectors, counters, histogram
   size_t p3p_bytes = 0;
   double* p3p_io = nullptr;             // batched solver scratch
@@ -220,7 +223,7 @@ cudaError_t dev_alloc(T** p, size_t n)
 
 void free_all(pfmpe_handle* h)
 {
-  cudaFree(h->pose0); cudaFree(h->pose1); cudaFree(h->gather_tmp); cudaFree(h->w); cudaFree(h->kend);
+  cudaFree(h->pose0); if (!h->shard_alloc) cudaFree(h->pose1); cudaFree(h->gather_tmp); cudaFree(h->w); cudaFree(h->kend);
   cudaFree(h->idx); cudaFree(h->gather_idx); cudaFree(h->cta_agg); cudaFree(h->accum);
   cudaFree(h->inbox); cudaFree(h->state); cudaFree(h->result); cudaFree(h->obj_f); cudaFree(h->obj_d);
   for (void* q : h->ipc_opened) cudaIpcCloseMemHandle(q);
@@ -247,6 +250,7 @@ void fill_kparams(const pfmpe_handle* h, pf_kparams& p)
   p.n_trackers = h->cfg.n_trackers;
   p.D_max = h->cfg.max_blobs;
   p.want_mean = (h->cfg.flags & PFMPE_FLAG_MEAN_COV) ? 1 : 0;
+  p.pstride = (int)h->pstride;
   p.pose0 = h->pose0; p.pose1 = h->pose1; p.w = h->w; p.kend = h->kend; p.idx = h->idx;
   p.cta_agg = h->cta_agg; p.accum = h->accum; p.gfill = h->gfill; p.gfill_cap = h->gfill_cap;
   p.fconst = h->fconst; p.state = h->state;
@@ -503,13 +507,13 @@ void planes_to_cm16(const float* planes, int N, double* poses)
   }
 }
 
-__global__ void pf_fill_kernel(float4* base, int N, float4 r0, float4 r1, float4 r2)
+__global__ void pf_fill_kernel(float4* base, int N, int S, float4 r0, float4 r1, float4 r2)
 {
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= N) return;
   base[n] = r0;
-  base[(size_t)N + n] = r1;
-  base[2 * (size_t)N + n] = r2;
+  base[(size_t)S + n] = r1;
+  base[2 * (size_t)S + n] = r2;
 }
 
 // track mode: stage the constants of `frame` from the device-resident tracker state
@@ -599,6 +603,7 @@ int pfmpe_create(const pfmpe_config* cfg, pfmpe_handle** out)
   h->own_stream = true;
   PF_TRY(cudaEventCreate(&h->ev0));
   PF_TRY(cudaEventCreate(&h->ev1));
+  h->pstride = N;
   PF_TRY(dev_alloc(&h->pose0, T * 3 * N));
   PF_TRY(dev_alloc(&h->pose1, T * 3 * N));
   PF_TRY(dev_alloc(&h->gather_tmp, 3 * N));
@@ -716,8 +721,12 @@ int pfmpe_set_particles(pfmpe_handle* h, int tracker, const double* poses, int n
   cm16_to_planes(poses, n, planes.data());
   PF_CUDA(h, cudaSetDevice(h->cfg.device));
   PF_CUDA(h, cudaStreamSynchronize(h->stream));
-  PF_CUDA(h, cudaMemcpy(h->pose0 + (size_t)tracker * 3 * N, planes.data(), planes.size() * sizeof(float), cudaMemcpyHostToDevice));
-  PF_CUDA(h, cudaMemcpy(h->pose1 + (size_t)tracker * 3 * N, planes.data(), planes.size() * sizeof(float), cudaMemcpyHostToDevice));
+  const size_t S = h->pstride;
+  for (int pl = 0; pl < 3; ++pl) {
+    PF_CUDA(h, cudaMemcpy(h->pose0 + (size_t)tracker * 3 * S + pl * S, planes.data() + (size_t)pl * N * 4, N * sizeof(float4), cudaMemcpyHostToDevice));
+    PF_CUDA(h, cudaMemcpy(h->pose1 + (size_t)tracker * 3 * S + pl * S, planes.data() + (size_t)pl * N * 4, N * sizeof(float4), cudaMemcpyHostToDevice));
+  }
+  h->sh_src = 0;
   PF_CUDA(h, cudaMemcpy(h->h_state + tracker, h->state + tracker, sizeof(pf_tracker_state), cudaMemcpyDeviceToHost));
   pf_tracker_state& s = h->h_state[tracker];
   s.src_buf = 0; s.src_mode = 0; s.t_buf = 1; s.failed = 0;
@@ -873,9 +882,9 @@ static int run_gather(pfmpe_handle* h, int tracker)
 {
   const pf_tracker_state& s = h->h_state[tracker];
   const size_t N = (size_t)h->cfg.n_particles;
-  const float4* T = (s.src_buf == 0 ? h->pose0 : h->pose1) + (size_t)tracker * 3 * N;
+  const float4* T = (s.src_buf == 0 ? h->pose0 : h->pose1) + (size_t)tracker * 3 * h->pstride;
   const int blocks = (int)((N + PF_BLOCK - 1) / PF_BLOCK);
-  pf_gather_kernel<<<blocks, PF_BLOCK, 0, h->stream>>>(T, (h->sharded && h->lead) ? h->lead : h->idx + (size_t)tracker * N, (int)N, s.src_mode,
+  pf_gather_kernel<<<blocks, PF_BLOCK, 0, h->stream>>>(T, (h->sharded && h->lead) ? h->lead : h->idx + (size_t)tracker * N, (int)N, (int)h->pstride, s.src_mode,
                                                       h->gather_tmp, h->gather_idx);
   PF_CUDA(h, cudaGetLastError());
   h->launches += 1;
@@ -892,14 +901,17 @@ int pfmpe_get_particles(pfmpe_handle* h, int tracker, int which, double* poses)
   const size_t N = (size_t)h->cfg.n_particles;
   std::vector<float> planes(3 * N * 4);
   const float4* src;
+  size_t S = N;
   if (which == 0) {
-    src = (h->h_state[tracker].t_buf == 0 ? h->pose0 : h->pose1) + (size_t)tracker * 3 * N;
+    S = h->pstride;
+    src = (h->h_state[tracker].t_buf == 0 ? h->pose0 : h->pose1) + (size_t)tracker * 3 * S;
   } else {
     rc = run_gather(h, tracker);
     if (rc) return rc;
     src = h->gather_tmp;
   }
-  PF_CUDA(h, cudaMemcpy(planes.data(), src, planes.size() * sizeof(float), cudaMemcpyDeviceToHost));
+  for (int pl = 0; pl < 3; ++pl)
+    PF_CUDA(h, cudaMemcpy(planes.data() + (size_t)pl * N * 4, src + pl * S, N * sizeof(float4), cudaMemcpyDeviceToHost));
   planes_to_cm16(planes.data(), (int)N, poses);
   return PFMPE_OK;
 }
@@ -1040,8 +1052,10 @@ int pfmpe_track_init(pfmpe_handle* h, int tracker, const double pose0[16], doubl
   const float4 r0 = make_float4(f.p[0], f.p[1], f.p[2], f.p[3]), r1 = make_float4(f.p[4], f.p[5], f.p[6], f.p[7]),
                r2 = make_float4(f.p[8], f.p[9], f.p[10], f.p[11]);
   const int blocks = (N + 255) / 256;
-  pf_fill_kernel<<<blocks, 256, 0, h->stream>>>(h->pose0 + (size_t)tracker * 3 * N, N, r0, r1, r2);
-  pf_fill_kernel<<<blocks, 256, 0, h->stream>>>(h->pose1 + (size_t)tracker * 3 * N, N, r0, r1, r2);
+  const int S = (int)h->pstride;
+  pf_fill_kernel<<<blocks, 256, 0, h->stream>>>(h->pose0 + (size_t)tracker * 3 * S, N, S, r0, r1, r2);
+  pf_fill_kernel<<<blocks, 256, 0, h->stream>>>(h->pose1 + (size_t)tracker * 3 * S, N, S, r0, r1, r2);
+  h->sh_src = 0;
   PF_CUDA(h, cudaGetLastError());
   h->launches += 2;
   PF_CUDA(h, cudaStreamSynchronize(h->stream));   // h_state is reused by the next call
@@ -1536,12 +1550,19 @@ int pfmpe_shard_configure(pfmpe_handle* h, int64_t global_offset, int64_t n_glob
   cudaFree(h->idx); h->idx = nullptr;
   PF_CUDA(h, dev_alloc(&h->idx, (size_t)n_global));
   PF_CUDA(h, cudaMemset(h->idx, 0, (size_t)n_global * sizeof(int)));
-  // pose0 receives the rebalanced set: its allocation grows by the lead[] array the peers write next to the rows
+  // One allocation [pose0: 3 planes x 2N | pose1: 3 planes x 2N | lead: N] -- one CUDA IPC handle for the peers.  The
+  // second half of every plane is the receive area the other ranks' rebalance writes rows into.
   if (h->particles_set[0]) return fail(h, PFMPE_ERR_STATE, "pfmpe_shard_configure must precede set_particles / track_init");
-  cudaFree(h->pose0); h->pose0 = nullptr; h->lead = nullptr;
-  PF_CUDA(h, cudaMalloc((void**)&h->pose0, (size_t)N * (3 * sizeof(float4) + sizeof(int))));
-  PF_CUDA(h, cudaMemset(h->pose0, 0, (size_t)N * (3 * sizeof(float4) + sizeof(int))));
-  h->lead = reinterpret_cast<int*>(h->pose0 + 3 * (size_t)N);
+  cudaFree(h->pose0); if (!h->shard_alloc) cudaFree(h->pose1);
+  h->pose0 = h->pose1 = nullptr; h->lead = nullptr;
+  const size_t S = 2 * (size_t)N, bytes = 6 * S * sizeof(float4) + (size_t)N * sizeof(int);
+  PF_CUDA(h, cudaMalloc((void**)&h->pose0, bytes));
+  PF_CUDA(h, cudaMemset(h->pose0, 0, bytes));
+  h->shard_alloc = true;
+  h->pstride = S;
+  h->pose1 = h->pose0 + 3 * S;
+  h->lead = reinterpret_cast<int*>(h->pose0 + 6 * S);
+  h->sh_src = 0;
   if (!h->warp_agg_g) PF_CUDA(h, dev_alloc(&h->warp_agg_g, (size_t)PF_MAX_GRID * PF_MAX_WARPS));
   if (!h->shard_partial) PF_CUDA(h, dev_alloc(&h->shard_partial, PF_XMAIL_WORDS));
   h->sharded = true;
@@ -1594,7 +1615,9 @@ int pfmpe_shard_resample(pfmpe_handle* h, int64_t sum_fx, int iterations, const 
   sa.iters_total = iterations;
   for (int i = 0; i < 3; ++i) { sa.excl[i] = lower[i]; sa.total[i] = all[i]; }
   sa.partial = static_cast<long long*>(d_partial);
-  return launch_frames(h, 4, 0, 1, 0, 1, &sa);
+  rc = launch_frames(h, 4, 0, 1, 0, 1, &sa);
+  if (rc == PFMPE_OK && h->peers_dev) h->sh_src ^= 1;   // peer-memory rebalance: the propagated set becomes the source (see the kernel's mode-4 epilogue)
+  return rc;
 }
 
 int pfmpe_shard_export(pfmpe_handle* h, int64_t first_owned_slot, int64_t first_slot, int64_t count, void* d_rows)
@@ -1607,7 +1630,7 @@ int pfmpe_shard_export(pfmpe_handle* h, int64_t first_owned_slot, int64_t first_
   if (first_slot - first_owned_slot + count > (int64_t)h->n_global)
     return fail(h, PFMPE_ERR_INVALID, "slot range outside this shard's output");
   const int blocks = (int)((count + PF_BLOCK - 1) / PF_BLOCK);
-  pf_shard_export_kernel<<<blocks, PF_BLOCK, 0, h->stream>>>(h->pose1, h->idx, (int)N, first_owned_slot, first_slot, count,
+  pf_shard_export_kernel<<<blocks, PF_BLOCK, 0, h->stream>>>(h->sh_src == 0 ? h->pose1 : h->pose0, h->idx, (int)h->pstride, first_owned_slot, first_slot, count,
                                                             1, static_cast<float4*>(d_rows));
   PF_CUDA(h, cudaGetLastError());
   h->launches += 1;
@@ -1624,8 +1647,8 @@ int pfmpe_shard_import(pfmpe_handle* h, const void* d_rows, int64_t local_offset
   h->particles_set[0] = 1;
   if (count == 0) return PFMPE_OK;
   const int blocks = (int)((count + PF_BLOCK - 1) / PF_BLOCK);
-  pf_shard_import_kernel<<<blocks, PF_BLOCK, 0, h->stream>>>(static_cast<const float4*>(d_rows), (int)N, (int)local_offset,
-                                                            (int)count, h->pose0);
+  pf_shard_import_kernel<<<blocks, PF_BLOCK, 0, h->stream>>>(static_cast<const float4*>(d_rows), (int)h->pstride, (int)local_offset,
+                                                            (int)count, h->sh_src == 0 ? h->pose0 : h->pose1);
   PF_CUDA(h, cudaGetLastError());
   h->launches += 1;
   return PFMPE_OK;
@@ -1641,8 +1664,8 @@ int pfmpe_shard_keep(pfmpe_handle* h, int64_t first_owned_slot, int64_t first_sl
   if (first_slot - first_owned_slot + count > (int64_t)h->n_global) return fail(h, PFMPE_ERR_INVALID, "slot range outside this shard's output");
   if (count == 0) return PFMPE_OK;
   const int blocks = (int)((count + PF_BLOCK - 1) / PF_BLOCK);
-  pf_shard_keep_kernel<<<blocks, PF_BLOCK, 0, h->stream>>>(h->pose1, h->idx, (int)N, first_owned_slot, first_slot, (int)count,
-                                                          (int)local_offset, h->pose0);
+  pf_shard_keep_kernel<<<blocks, PF_BLOCK, 0, h->stream>>>(h->sh_src == 0 ? h->pose1 : h->pose0, h->idx, (int)h->pstride, first_owned_slot, first_slot, (int)count,
+                                                          (int)local_offset, h->sh_src == 0 ? h->pose0 : h->pose1);
   PF_CUDA(h, cudaGetLastError());
   h->launches += 1;
   return PFMPE_OK;
@@ -1717,7 +1740,9 @@ int pfmpe_shard_scatter(pfmpe_handle* h, int64_t first_owned_slot, int64_t count
   long long blocks = (count + PF_BLOCK - 1) / PF_BLOCK;
   const long long cap = (long long)h->num_sms * 32;
   if (blocks > cap) blocks = cap;
-  pf_shard_scatter_kernel<<<(int)blocks, PF_BLOCK, 0, h->stream>>>(h->pose1, h->idx, h->kend, N, first_owned_slot, count, h->peers_dev);
+  // called after pfmpe_shard_resample: sh_src already names the buffer that holds T (the new source)
+  pf_shard_scatter_kernel<<<(int)blocks, PF_BLOCK, 0, h->stream>>>(h->sh_src == 0 ? h->pose0 : h->pose1, h->idx, h->kend, N, (int)h->pstride,
+                                                                   first_owned_slot, count, h->peers_dev, h->sh_src, (int)(h->goff / N));
   PF_CUDA(h, cudaGetLastError());
   h->launches += 1;
   return PFMPE_OK;
@@ -2088,12 +2113,12 @@ int pfmpe_state_checksum(pfmpe_handle* h, int tracker, uint64_t out[3])
   const size_t N = (size_t)h->cfg.n_particles;
   if (!h->cksum) PF_CUDA(h, cudaMalloc((void**)&h->cksum, 3 * sizeof(unsigned long long)));
   PF_CUDA(h, cudaMemsetAsync(h->cksum, 0, 3 * sizeof(unsigned long long), h->stream));
-  const float4* T = (s.t_buf == 0 ? h->pose0 : h->pose1) + (size_t)tracker * 3 * N;
-  const float4* src = (s.src_buf == 0 ? h->pose0 : h->pose1) + (size_t)tracker * 3 * N;
+  const float4* T = (s.t_buf == 0 ? h->pose0 : h->pose1) + (size_t)tracker * 3 * h->pstride;
+  const float4* src = (s.src_buf == 0 ? h->pose0 : h->pose1) + (size_t)tracker * 3 * h->pstride;
   const int* gidx = (h->sharded && h->lead) ? h->lead : h->idx + (size_t)tracker * N;
   int blocks = (int)((N + PF_BLOCK - 1) / PF_BLOCK);
   if (blocks > h->num_sms * 16) blocks = h->num_sms * 16;
-  pf_checksum_kernel<<<blocks, PF_BLOCK, 0, h->stream>>>(T, h->w + (size_t)tracker * N, src, gidx, s.src_mode, (int)N,
+  pf_checksum_kernel<<<blocks, PF_BLOCK, 0, h->stream>>>(T, h->w + (size_t)tracker * N, src, gidx, s.src_mode, (int)N, (int)h->pstride,
                                                           (unsigned long long)(h->sharded ? h->goff : 0), h->cksum);
   PF_CUDA(h, cudaGetLastError());
   h->launches += 1;
