@@ -249,6 +249,19 @@ int pfmpe_p3p_histogram(pfmpe_handle* h, int tracker, const double* image_points
 int pfmpe_p3p_histogram_dev(pfmpe_handle* h, int tracker, const double* d_image_points, int32_t n_image_points,
                             uint32_t* hist, pfmpe_p3p_stats* stats);
 
+/* The same vote with NO allocation (no reference counterpart: added for callers
+ * that cannot call cudaMalloc -- code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The
+ * kernels' scratch (device copy of the detections, copy sorted by x, bearing vectors, world table of the LED
+ * permutations, counters, histogram) lives in a file-scope device array of 128 KiB that every GPU loading the library
+ * holds until exit; the call makes no cudaMalloc / cudaFree.  Limit: n_image_points <= PFMPE_P3P_STATIC_MAX_POINTS,
+ * beyond it PFMPE_ERR_INVALID (use pfmpe_p3p_histogram).  image_points and hist are HOST buffers as for
+ * pfmpe_p3p_histogram; results are identical to it.  All calls on one device share the array, which keeps the last
+ * call's contents (each call's prologue kernel rewrites its tables and zeroes histogram and counters): calls that
+ * overlap on the GPU -- two handles or streams at once -- race; serialise them. */
+#define PFMPE_P3P_STATIC_MAX_POINTS 256
+int pfmpe_p3p_histogram_static(pfmpe_handle* h, int tracker, const double* image_points, int32_t n_image_points,
+                               uint32_t* hist, pfmpe_p3p_stats* stats);
+
 /* The per-combination body of PoseEstimator::checkCorrespondences (pose_estimator.cpp:1340-1445), batched over
  * n_sets candidate correspondence sets (the entries of correspondencesFromHistogram's list, :1733-1751): for every
  * combination of three pairs of a set (Combinations::combinationsNoReplacement order = lexicographic) P3P on the

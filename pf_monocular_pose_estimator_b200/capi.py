@@ -25,7 +25,7 @@ EXPORTS = [
     "pfmpe_optimise_pose", "pfmpe_predict_pose", "pfmpe_exponential_map", "pfmpe_logarithm_map",
     "pfmpe_track_init", "pfmpe_track_set_state", "pfmpe_track_upload", "pfmpe_track_attach", "pfmpe_track_run", "pfmpe_track_replay", "pfmpe_track_results",
     "pfmpe_track_frame_host", "pfmpe_track_frame_host_batch", "pfmpe_track_sequence_host",
-    "pfmpe_predict_roi", "pfmpe_p3p_histogram", "pfmpe_p3p_histogram_dev", "pfmpe_p3p_solve", "pfmpe_p3p_check",
+    "pfmpe_predict_roi", "pfmpe_p3p_histogram", "pfmpe_p3p_histogram_dev", "pfmpe_p3p_histogram_static", "pfmpe_p3p_solve", "pfmpe_p3p_check",
     "pfmpe_shard_configure", "pfmpe_shard_begin_frame", "pfmpe_shard_score", "pfmpe_shard_resample",
     "pfmpe_shard_export", "pfmpe_shard_keep", "pfmpe_shard_import", "pfmpe_shard_winner",
     "pfmpe_shard_mail_create", "pfmpe_shard_mail_set_peers", "pfmpe_shard_collect", "pfmpe_shard_advance",
@@ -143,6 +143,7 @@ def lib():
         L.pfmpe_p3p_histogram.argtypes = [C.c_void_p, C.c_int, _dp, C.c_int32, C.POINTER(C.c_uint32), C.POINTER(P3pStats)]
         L.pfmpe_p3p_histogram_dev.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int32, C.POINTER(C.c_uint32),
                                               C.POINTER(P3pStats)]
+        L.pfmpe_p3p_histogram_static.argtypes = [C.c_void_p, C.c_int, _dp, C.c_int32, C.POINTER(C.c_uint32), C.POINTER(P3pStats)]
         L.pfmpe_p3p_solve.argtypes = [C.c_void_p, C.c_int32, _dp, _dp, _dp, C.POINTER(C.c_int32)]
         L.pfmpe_p3p_check.argtypes = [C.c_void_p, C.c_int, _dp, C.c_int32, C.POINTER(C.c_uint32), C.POINTER(C.c_int32), C.c_int32,
                                       C.c_int32, C.c_double, C.POINTER(P3pCheckResult)]
@@ -395,6 +396,18 @@ class Handle:
             self._chk(lib().pfmpe_p3p_histogram(self._h, tracker, _d(im), D, hp, C.byref(st)))
         else:
             self._chk(lib().pfmpe_p3p_histogram_dev(self._h, tracker, C.c_void_p(int(d_image_points)), D, hp, C.byref(st)))
+        return hist, dict(triples=int(st.triples), p3p_solved=int(st.p3p_solved),
+                          solutions_projected=int(st.solutions_projected), solutions_voted=int(st.solutions_voted),
+                          device_ms=float(st.device_ms))
+
+    def p3p_histogram_static(self, image_points, tracker=0):
+        """pfmpe_p3p_histogram_static: the same vote with its scratch in the library's file-scope device array (no
+        allocation in the call; at most PFMPE_P3P_STATIC_MAX_POINTS = 256 detections)."""
+        im = _c64(image_points).reshape(-1, 2)
+        D, L = im.shape[0], self.L
+        hist = np.zeros((D, L), dtype=np.uint32)
+        st = P3pStats()
+        self._chk(lib().pfmpe_p3p_histogram_static(self._h, tracker, _d(im), D, hist.ctypes.data_as(C.POINTER(C.c_uint32)), C.byref(st)))
         return hist, dict(triples=int(st.triples), p3p_solved=int(st.p3p_solved),
                           solutions_projected=int(st.solutions_projected), solutions_voted=int(st.solutions_voted),
                           device_ms=float(st.device_ms))

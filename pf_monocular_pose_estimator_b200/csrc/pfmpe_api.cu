@@ -1454,6 +1454,99 @@ int pfmpe_p3p_histogram_dev(pfmpe_handle* h, int tracker, const double* d_image_
   return p3p_histogram_impl(h, tracker, d_image_points, true, n_image_points, hist, stats);
 }
 
+// ---- the vote without any allocation: scratch in a file-scope device array --------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernels as pfmpe_p3p_histogram
+// (pf_p3p_prep_kernel + pf_p3p_hist_kernel); their scratch -- the device copy of the detections, the copy sorted by x,
+// the bearing vectors, the world-frame table of the LED permutations, the counters and the histogram -- lives in the
+// static array below instead of the handle's grow-on-demand cudaMalloc buffer.  Every GPU that loads the library holds
+// the array until the process exits.  All calls on a device share it and it keeps the last call's contents: the
+// prologue kernel rewrites every table and zeroes the histogram and the counters at the start of each call, so calls
+// that are ordered on the GPU are independent; calls that OVERLAP on the GPU (two handles / two streams at once) race.
+#define PF_STATIC_SCRATCH_BYTES (128 * 1024)
+static __device__ __align__(256) unsigned char pf_static_scratch[PF_STATIC_SCRATCH_BYTES];
+
+namespace {
+// In host code `pf_static_scratch` is a host-side stand-in, not a device address: the address is asked for once per
+// device, with that device current, and cached.
+std::mutex g_static_mu;
+unsigned char* g_static_ptr[64] = {nullptr};
+
+int static_scratch_ptr(pfmpe_handle* h, unsigned char** out)
+{
+  const int dev = h->cfg.device;
+  if (dev < 0 || dev >= 64) return fail(h, PFMPE_ERR_UNSUPPORTED, "device ordinal beyond the static scratch table (64)");
+  std::lock_guard<std::mutex> g(g_static_mu);
+  if (!g_static_ptr[dev]) {
+    void* q = nullptr;
+    PF_CUDA(h, cudaSetDevice(dev));
+    PF_CUDA(h, cudaGetSymbolAddress(&q, pf_static_scratch));
+    g_static_ptr[dev] = static_cast<unsigned char*>(q);
+  }
+  *out = g_static_ptr[dev];
+  return PFMPE_OK;
+}
+}  // namespace
+
+int pfmpe_p3p_histogram_static(pfmpe_handle* h, int tracker, const double* image_points, int32_t D, uint32_t* hist,
+                               pfmpe_p3p_stats* stats)
+{
+  if (!h || !image_points || !hist) return PFMPE_ERR_INVALID;
+  if (tracker < 0 || tracker >= h->cfg.n_trackers) return fail(h, PFMPE_ERR_INVALID, "tracker out of range");
+  int rc = check_ready(h);
+  if (rc) return rc;
+  const int L = h->cfg.n_leds;
+  if (L < 3) return fail(h, PFMPE_ERR_UNSUPPORTED, "P3P needs at least 3 LEDs");
+  if (D < 3) return fail(h, PFMPE_ERR_INVALID, "n_image_points must be >= 3");
+  if (D > PFMPE_P3P_STATIC_MAX_POINTS)
+    return fail(h, PFMPE_ERR_INVALID, "pfmpe_p3p_histogram_static: n_image_points exceeds PFMPE_P3P_STATIC_MAX_POINTS (256); "
+                                      "use pfmpe_p3p_histogram for larger frames");
+  // scratch layout (as pfmpe_p3p_histogram): img 2D | simg 2D | vec 3D | stats 4 | wtab 2*nperm*16 (all 8-byte) | hist D*L u32 | sidx D i32
+  const int nperm = L * (L - 1) * (L - 2);
+  const size_t wtab_doubles = (size_t)2 * nperm * (sizeof(pf_p3p_world) / sizeof(double));
+  const size_t need = ((size_t)D * 7 + 4 + wtab_doubles) * 8 + (size_t)D * L * 4 + (size_t)D * 4;
+  if (need > PF_STATIC_SCRATCH_BYTES) return fail(h, PFMPE_ERR_INVALID, "pfmpe_p3p_histogram_static: problem exceeds the static scratch (128 KiB)");
+  unsigned char* scratch = nullptr;
+  rc = static_scratch_ptr(h, &scratch);
+  if (rc) return rc;
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  pf_p3p_params p;
+  std::memset(&p, 0, sizeof p);
+  p.D = D; p.L = L;
+  for (int i = 0; i < 9; ++i) p.K[i] = h->K[i];
+  for (int i = 0; i < 3 * L; ++i) p.obj[i] = h->markers[(size_t)tracker * PF_MAX_LED * 3 + i];
+  p.tol = h->prm.back_projection_pixel_tolerance;
+  double* base = reinterpret_cast<double*>(scratch);
+  double* d_img = base;
+  p.img = d_img;
+  p.simg = base + 2 * (size_t)D;
+  p.vec = base + 4 * (size_t)D;
+  p.stats = reinterpret_cast<unsigned long long*>(base + 7 * (size_t)D);
+  p.wtab = reinterpret_cast<pf_p3p_world*>(base + 7 * (size_t)D + 4);
+  p.hist = reinterpret_cast<unsigned*>(base + 7 * (size_t)D + 4 + wtab_doubles);
+  p.sidx = reinterpret_cast<int*>(p.hist + (size_t)D * L);
+  const long long triples = (long long)D * (D - 1) * (D - 2) / 6;
+  const long long want_threads = (long long)h->num_sms * 3 * PF_P3P_BLOCK * 2;
+  long long nchunk = (want_threads + triples - 1) / triples;
+  p.nchunk = (int)(nchunk < 1 ? 1 : nchunk > nperm ? nperm : nchunk);
+  PF_CUDA(h, cudaMemcpyAsync(d_img, image_points, (size_t)D * 2 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  PF_CUDA(h, cudaEventRecord(h->ev0, h->stream));
+  PF_CUDA(h, pf_p3p_launch_hist(p, h->stream));   // the prologue zeroes hist / stats and rewrites every table
+  PF_CUDA(h, cudaEventRecord(h->ev1, h->stream));
+  h->launches += 2;
+  h->timing_valid = false;
+  unsigned long long st[4];
+  PF_CUDA(h, cudaMemcpyAsync(hist, p.hist, (size_t)D * L * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
+  PF_CUDA(h, cudaMemcpyAsync(st, p.stats, sizeof st, cudaMemcpyDeviceToHost, h->stream));
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  if (stats) {
+    stats->triples = st[0]; stats->p3p_solved = st[1]; stats->solutions_projected = st[2]; stats->solutions_voted = st[3];
+    stats->reserved = 0;
+    PF_CUDA(h, cudaEventElapsedTime(&stats->device_ms, h->ev0, h->ev1));
+  }
+  return PFMPE_OK;
+}
+
 int pfmpe_p3p_check(pfmpe_handle* h, int tracker, const double* image_points, int32_t D, const uint32_t* correspondences,
                     const int32_t* counts, int32_t M, int32_t stride, double certainty_threshold, pfmpe_p3p_check_result* results)
 {
