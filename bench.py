@@ -265,11 +265,25 @@ def gpu_measure(workload, trackers, K, W, dev, local_rank, barrier, flush_ok=Tru
     if sampler:
         sampler.__enter__()
     t_wall0 = time.perf_counter()
-    for f in range(W, F):
-        if flush is not None:
+    if flush is not None:
+        # per-step CUDA events on the launching stream (pfmpe_last_launch_ms); the untimed flush that precedes every
+        # step keeps the GPU busy while the host enqueues the step, so no host launch time falls between the events
+        for f in range(W, F):
             flush.zero_()
-        h.track_replay(f, 1)
-        step_ms.append(h.last_launch_ms())      # CUDA events recorded on the launching stream
+            h.track_replay(f, 1)
+            step_ms.append(h.last_launch_ms())
+    else:
+        # no flush (working set > L2): the K launches go back to back without a host wait in between, bracketed by one
+        # event pair on the launching stream -- a per-step wait would leave the GPU idle at every step's first event and
+        # book the host's launch time to the device
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for f in range(W, F):
+            h.track_replay(f, 1)
+        e1.record(stream)
+        e1.synchronize()
+        step_ms = [e0.elapsed_time(e1) / K] * K
+        out["timing"] = "K launches back to back between one CUDA event pair on the launching stream"
     barrier()
     out["wall_s"] = time.perf_counter() - t_wall0
     if sampler:
