@@ -380,13 +380,13 @@ def contract(workload, m, world, reduce_max, reduce_sum, reduce_min, peak, peak_
     return o
 
 
-def sharded_filter_measure(world, rank, dev, local_rank, barrier, allreduce, RO, peak, n_global=1 << 26, K=MIN_SUB_STEPS, W=3):
+def sharded_filter_measure(world, rank, dev, local_rank, barrier, allreduce, RO, peak, n_global=1 << 26, K=MIN_SUB_STEPS, W=3, virtual=1):
     """BASELINE configs[4]: one filter of 2^26 particles, particle shards over the ranks, driven by the C frame call
     pfmpe_shard_track_frame_host (predictPose -> sharded PF update -> Gauss-Newton; host blobs in, pose + covariance out)."""
     import torch
     from pf_monocular_pose_estimator_b200 import scenes as S, sharded as SH
     sc = S.Scene(0)
-    comm = SH.TorchDist() if world > 1 else SH.Loopback(1)
+    comm = SH.TorchDist(virtual=virtual) if world > 1 else SH.Loopback(1)
     sf = SH.ShardedFilter(n_global, comm, n_leds=L_LED, max_blobs=sc.blobs(0).shape[0] + 4, device=local_rank)
     sf.configure(sc.markers, sc.K, sc.params)
     sf.track_init(sc.pose(0), sc.time(0), sc.pose(1), sc.time(1))
@@ -413,7 +413,7 @@ def sharded_filter_measure(world, rank, dev, local_rank, barrier, allreduce, RO,
     (wall,) = allreduce([wall], RO.MAX if RO else None)
     (okf,) = allreduce([1.0 if ok else 0.0], RO.MIN if RO else None)
     pme = float(n_global) * L_LED * passes
-    n_loc = n_global // world
+    n_loc = n_global // world                                             # particles per GPU
     alg = alg_bytes_per_frame(n_loc, passes / K) * K                      # 136 B per particle and frame
     alg_reb = alg + 100.0 * n_loc * K                                     # + the rebalance: idx 4 + row read 48 + row write 48
     rebalance, loop = sf.rebalance, sf.loop
@@ -433,7 +433,9 @@ def sharded_filter_measure(world, rank, dev, local_rank, barrier, allreduce, RO,
             "state_checksums": ["%016x" % c for c in checks],
             "exchange": "64-byte partials by NVLink peer stores into every rank's mailbox (no NCCL call in the frame loop); rebalance = %s"
                         % ("one scatter kernel, local + NVLink peer stores (CUDA IPC)" if rebalance == "p2p" else "row export + all_to_all + import"),
-            "rebalance": rebalance, "host_loop": loop}
+            "rebalance": rebalance, "host_loop": loop,
+            "placement": "contiguous shards, one per GPU" if virtual == 1 or world == 1 else
+                         "block-cyclic: %d shards, GPU p hosts the shards p, p + %d, ..." % (world * virtual, world)}
 
 
 def p3p_vote_measure(dev, with_cpu, n_detections=205, K=5, W=2):
@@ -494,6 +496,7 @@ def main():
     ap.add_argument("--no-p3p", action="store_true", help="skip the initialisation-vote sub-line (p3p_vote)")
     ap.add_argument("--only", action="store_true", help="headline workload only (all sub-lines off)")
     ap.add_argument("--trackers", type=int, default=None, help="override the tracker count of the workload (experiments)")
+    ap.add_argument("--shard-virtual", type=int, default=0, help="shards per GPU of the sharded_filter sub-line (block-cyclic placement; default 1 = contiguous)")
     ap.add_argument("--cpu-budget", type=float, default=6.0, help="seconds of CPU work per cpu_baseline sample")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -603,7 +606,8 @@ def main():
         barrier()
     # ---- BASELINE configs[4] alongside: ONE filter of 2^26 particles sharded by particle over the ranks
     if not args.no_sharded:
-        line["sharded_filter"] = sharded_filter_measure(world, rank, dev, local_rank, barrier, allreduce, RO, peak)
+        v = args.shard_virtual or 1
+        line["sharded_filter"] = sharded_filter_measure(world, rank, dev, local_rank, barrier, allreduce, RO, peak, virtual=v)
     if on0 and not args.no_p3p:
         line["p3p_vote"] = p3p_vote_measure(local_rank, with_cpu=(world == 1 and not args.no_cpu))
 

@@ -1314,6 +1314,67 @@ __global__ void __launch_bounds__(PF_BLOCK) pf_shard_scatter_kernel(const float4
   }
 }
 
+// The same rebalance with the cross-rank rows PACKED: with run de-duplication the sparse form above stores a row only at
+// the first slot of a run, i.e. isolated 16-byte NVLink writes (measured on 8 B200: 1.5-1.7 ms per frame for the rank that
+// holds most of the weight, a third of the link rate).  Here a CTA takes PF_BLOCK consecutive global slots -- shards are
+// a multiple of PF_BLOCK, so the chunk has one destination -- numbers the runs that start in it (a chunk boundary also
+// starts one: at most one extra row per PF_BLOCK slots), reserves that many consecutive places in the destination's
+// receive area with one atomic on a per-destination cursor, collects the runs' source indices in shared memory and then
+// moves the rows with ALL threads: consecutive threads, consecutive remote addresses, three 16-byte planes.  Source rank
+// r owns the places [first slot of r in d, ...) of d's receive area: the streams of different ranks cannot collide, and a
+// stream is never longer than the number of slots it serves.  Which place a row gets depends on the order in which the
+// CTAs reach the atomic; lead[] records it, so the resampled set the next score pass gathers is the same whatever the
+// order.  cursor: [world] zeroed before the launch.
+__global__ void __launch_bounds__(PF_BLOCK) pf_shard_scatter_dense_kernel(const float4* T, const int* idx, int N, int S, long long kbase,
+                                                                          long long count, float4* const* bases, int tsel, int me,
+                                                                          unsigned* cursor)
+{
+  __shared__ int list[PF_BLOCK];
+  __shared__ int wsum[PF_BLOCK / 32];
+  __shared__ int s_base;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const long long k_first = kbase / PF_BLOCK * PF_BLOCK;
+  const long long nchunks = (kbase + count - k_first + PF_BLOCK - 1) / PF_BLOCK;
+  for (long long c = blockIdx.x; c < nchunks; c += gridDim.x) {
+    const long long kc = k_first + c * PF_BLOCK, k = kc + t;
+    const bool valid = k >= kbase && k < kbase + count;
+    const int d = (int)(kc / N);                                   // uniform: N is a multiple of PF_BLOCK
+    const long long d0 = (long long)d * N, i = k - kbase;
+    const int n = (int)(k - d0);
+    const int s = valid ? idx[i] : -1;
+    float4* base = bases[d];
+    int* lead = reinterpret_cast<int*>(base + 6 * (size_t)S);
+    if (d == me) {                                                 // stays on this rank: the source row is not moved
+      if (valid) lead[n] = s;
+      continue;
+    }
+    const int sp = (valid && i > 0) ? idx[i - 1] : -2;
+    const bool starts = valid && (t == 0 || sp != s);
+    const unsigned m = __ballot_sync(PF_FULL, starts);
+    const int incl_w = __popc(m & (0xFFFFFFFFu >> (31 - lane)));
+    if (lane == 0) wsum[warp] = __popc(m);
+    __syncthreads();
+    int woff = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < PF_BLOCK / 32; ++w) { const int v = wsum[w]; woff += w < warp ? v : 0; total += v; }
+    const int incl = woff + incl_w;                                // runs started at or before this slot (>= 1 for a valid slot)
+    if (t == 0) s_base = (int)atomicAdd(&cursor[d], (unsigned)total);
+    if (starts) list[incl - 1] = s;
+    __syncthreads();
+    const int pos0 = (int)((kbase > d0 ? kbase : d0) - d0) + s_base;   // this rank's stream in d's receive area + the reservation
+    if (valid) lead[n] = N + pos0 + incl - 1;
+    if (t < total) {
+      const int src = list[t];
+      float4* dst = base + (tsel ? 3 * (size_t)S : 0) + N + pos0 + t;
+      const float4 r0 = T[src], r1 = T[(size_t)S + src], r2 = T[2 * (size_t)S + src];
+      dst[0] = r0;
+      dst[(size_t)S] = r1;
+      dst[2 * (size_t)S] = r2;
+    }
+    __syncthreads();                                               // list / wsum / s_base are reused by the next chunk
+  }
+}
+
 // Sharded filter: wait until the message of exchange `seq` has arrived from every rank (or from
 // `only` alone), sent with peer stores by pf_shard_publish, then -- if host_out is given -- hand the
 // table to the host through pinned memory: [world][PF_XMAIL_WORDS] words followed by the sequence

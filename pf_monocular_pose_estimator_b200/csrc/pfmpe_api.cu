@@ -184,6 +184,7 @@ struct pfmpe_handle {
   int xworld = 0, xrank = 0;
   long long xseq = 0;
   float4** peers_dev = nullptr;         // [peer_world] next-frame particle planes of every rank (peer memory)
+  unsigned* scatter_cursor = nullptr;   // [peer_world] places reserved per destination by the packed rebalance
   int peer_world = 0;
   std::vector<void*> ipc_opened;
   std::unique_ptr<HostPool> pool;       // host workers of the batched host tail (created on first use)
@@ -229,7 +230,7 @@ void free_all(pfmpe_handle* h)
   for (void* q : h->ipc_opened) cudaIpcCloseMemHandle(q);
   cudaFree(h->xmail); cudaFree(h->xmail_peers_dev);
   if (h->h_xtable) cudaFreeHost(h->h_xtable);
-  cudaFree(h->peers_dev); cudaFree(h->mc_part); cudaFree(h->mc_mean); cudaFree(h->roi_keys); cudaFree(h->roi_out);
+  cudaFree(h->peers_dev); cudaFree(h->scatter_cursor); cudaFree(h->mc_part); cudaFree(h->mc_mean); cudaFree(h->roi_keys); cudaFree(h->roi_out);
   if (h->h_roi) cudaFreeHost(h->h_roi);
   cudaFree(h->p3p_buf); cudaFree(h->p3p_io); cudaFree(h->cksum);
   cudaFree(h->rng_tab); cudaFree(h->timeline); cudaFree(h->warp_agg_g); cudaFree(h->shard_partial); cudaFree(h->gfill);
@@ -1816,6 +1817,8 @@ int pfmpe_shard_set_peers(pfmpe_handle* h, int world, void* const* d_ptrs)
   cudaFree(h->peers_dev); h->peers_dev = nullptr;
   PF_CUDA(h, cudaMalloc((void**)&h->peers_dev, sizeof(float4*) * (size_t)world));
   PF_CUDA(h, cudaMemcpy(h->peers_dev, d_ptrs, sizeof(float4*) * (size_t)world, cudaMemcpyHostToDevice));
+  cudaFree(h->scatter_cursor); h->scatter_cursor = nullptr;
+  PF_CUDA(h, cudaMalloc((void**)&h->scatter_cursor, sizeof(unsigned) * (size_t)world));
   h->peer_world = world;
   return PFMPE_OK;
 }
@@ -1834,8 +1837,17 @@ int pfmpe_shard_scatter(pfmpe_handle* h, int64_t first_owned_slot, int64_t count
   const long long cap = (long long)h->num_sms * 32;
   if (blocks > cap) blocks = cap;
   // called after pfmpe_shard_resample: sh_src already names the buffer that holds T (the new source)
-  pf_shard_scatter_kernel<<<(int)blocks, PF_BLOCK, 0, h->stream>>>(h->sh_src == 0 ? h->pose0 : h->pose1, h->idx, h->kend, N, (int)h->pstride,
-                                                                   first_owned_slot, count, h->peers_dev, h->sh_src, (int)(h->goff / N));
+  static const bool force_sparse = [] { const char* e = std::getenv("PFMPE_SCATTER"); return e && std::string(e) == "sparse"; }();
+  const float4* Tbuf = h->sh_src == 0 ? h->pose0 : h->pose1;
+  const int me = (int)(h->goff / N);
+  if (N % PF_BLOCK == 0 && h->scatter_cursor && !force_sparse) {   // packed cross-rank rows (pf_shard_scatter_dense_kernel)
+    PF_CUDA(h, cudaMemsetAsync(h->scatter_cursor, 0, sizeof(unsigned) * (size_t)h->peer_world, h->stream));
+    pf_shard_scatter_dense_kernel<<<(int)blocks, PF_BLOCK, 0, h->stream>>>(Tbuf, h->idx, N, (int)h->pstride, first_owned_slot, count, h->peers_dev,
+                                                                          h->sh_src, me, h->scatter_cursor);
+  } else {
+    pf_shard_scatter_kernel<<<(int)blocks, PF_BLOCK, 0, h->stream>>>(Tbuf, h->idx, h->kend, N, (int)h->pstride, first_owned_slot, count,
+                                                                    h->peers_dev, h->sh_src, me);
+  }
   PF_CUDA(h, cudaGetLastError());
   h->launches += 1;
   return PFMPE_OK;

@@ -143,22 +143,36 @@ class Loopback:
 
 
 class TorchDist:
-    """One shard per process (rank = shard); NCCL on GPUs, gloo in the CPU tests."""
+    """One process per GPU; NCCL on GPUs, gloo in the CPU tests.
 
-    def __init__(self, group=None):
+    virtual = V > 1: block-cyclic placement.  The filter is cut into procs * V shards and process p hosts the shards
+    {p, p + procs, p + 2 procs, ...} (V handles on its GPU, one stream), so that every GPU holds V blocks spread over
+    the global particle order: when the weight concentrates in one stretch of the order -- the usual state of a
+    converged filter -- the resampling work and the cross-GPU traffic of the rebalance spread over the GPUs instead of
+    falling on one.  Needs the C frame loop (peer mailboxes + peer-memory rebalance); procs * V <= 32."""
+
+    def __init__(self, group=None, virtual=1):
         import torch.distributed as dist
         self.dist, self.group = dist, group
-        self.world = dist.get_world_size(group)
+        self.procs = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
-        self.local = [self.rank]
+        self.virtual = int(virtual)
+        self.world = self.procs * self.virtual
+        self.local = [self.rank + j * self.procs for j in range(self.virtual)]
+
+    def _need_single(self, what):
+        if self.virtual != 1:
+            raise RuntimeError("%s: block-cyclic placement (virtual > 1) runs through the C frame loop only" % what)
 
     def gather(self, partials):
         import torch
+        self._need_single("all_gather of the partials")
         out = torch.empty((self.world, partials.shape[1]), dtype=partials.dtype, device=partials.device)
         self.dist.all_gather_into_tensor(out, partials.reshape(-1, partials.shape[1]), group=self.group)
         return out.cpu().numpy()
 
     def exchange(self, send_rows, send, outs):
+        self._need_single("row exchange")
         r = self.rank
         recv = [send[q][r] for q in range(self.world)]
         self.dist.all_to_all_single(outs[0], send_rows[0], output_split_sizes=recv, input_split_sizes=list(send[r]),
@@ -180,27 +194,30 @@ class TorchDist:
         self.dist.all_reduce(t, op=self.dist.ReduceOp.MIN, group=self.group)
         return bool(int(t.item()))
 
-    def peer_pointers(self, shards, dev):
-        """CUDA IPC: every rank publishes its buffer, opens the others (NVLink peer access)."""
+    def _all_handles(self, mine, dev):
+        """mine: V 64-byte CUDA IPC handles of this process's shards -> (procs, V, 64) uint8 of everybody's."""
         import torch
-        mine = torch.tensor(list(shards[0].shard_ipc_export()), dtype=torch.uint8, device=dev)
-        allh = torch.empty((self.world, 64), dtype=torch.uint8, device=dev)
-        self.dist.all_gather_into_tensor(allh, mine.reshape(1, 64), group=self.group)
-        allh = allh.cpu().numpy()
-        return [shards[0].shard_local_ptr() if q == self.rank else shards[0].shard_ipc_open(allh[q].tobytes())
-                for q in range(self.world)]
+        t = torch.tensor([list(hd) for hd in mine], dtype=torch.uint8, device=dev).reshape(1, self.virtual, 64)
+        allh = torch.empty((self.procs, self.virtual, 64), dtype=torch.uint8, device=dev)
+        self.dist.all_gather_into_tensor(allh, t, group=self.group)
+        return allh.cpu().numpy()
+
+    def peer_pointers(self, shards, dev):
+        """CUDA IPC: every process publishes the buffers of its shards and opens the others' (NVLink peer access).
+        Returns the pointers in shard order (shard q lives on process q % procs as its local shard q // procs)."""
+        allh = self._all_handles([h.shard_ipc_export() for h in shards], dev)
+        return [shards[q // self.procs].shard_local_ptr() if q % self.procs == self.rank
+                else shards[0].shard_ipc_open(allh[q % self.procs, q // self.procs].tobytes()) for q in range(self.world)]
 
     def mail_pointers(self, shards, dev):
-        import torch
-        ptr, handle = shards[0].shard_mail_create(self.world, self.rank)
-        mine = torch.tensor(list(handle), dtype=torch.uint8, device=dev)
-        allh = torch.empty((self.world, 64), dtype=torch.uint8, device=dev)
-        self.dist.all_gather_into_tensor(allh, mine.reshape(1, 64), group=self.group)
-        allh = allh.cpu().numpy()
-        return [ptr if q == self.rank else shards[0].shard_ipc_open(allh[q].tobytes()) for q in range(self.world)]
+        made = [h.shard_mail_create(self.world, q) for h, q in zip(shards, self.local)]
+        allh = self._all_handles([hd for _, hd in made], dev)
+        return [made[q // self.procs][0] if q % self.procs == self.rank
+                else shards[0].shard_ipc_open(allh[q % self.procs, q // self.procs].tobytes()) for q in range(self.world)]
 
     def bcast(self, arr, owner):
         import torch
+        self._need_single("broadcast of the winner")
         dev = "cuda" if self.dist.get_backend(self.group) == "nccl" else "cpu"
         t = torch.from_numpy(np.ascontiguousarray(arr, dtype=np.float64)).to(dev)
         src = owner if self.group is None else self.dist.get_global_rank(self.group, owner)

@@ -19,7 +19,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, n_global, frames, q):
+def _worker(rank, world, port, n_global, frames, virtual, q):
     import torch
     import torch.distributed as dist
     from pf_monocular_pose_estimator_b200 import capi, scenes as S, sharded
@@ -33,7 +33,7 @@ def _worker(rank, world, port, n_global, frames, q):
         ref = capi.Handle(n_global, n_trackers=1, n_leds=5, max_blobs=D + 4, device=rank)
         ref.configure(sc.markers, sc.K, sc.params)
         ref.track_init(sc.pose(0), sc.time(0), sc.pose(1), sc.time(1))
-        sh = sharded.ShardedFilter(n_global, sharded.TorchDist(), n_leds=5, max_blobs=D + 4, device=rank, rebalance="p2p", loop="c")
+        sh = sharded.ShardedFilter(n_global, sharded.TorchDist(virtual=virtual), n_leds=5, max_blobs=D + 4, device=rank, rebalance="p2p", loop="c")
         sh.configure(sc.markers, sc.K, sc.params)
         sh.track_init(sc.pose(0), sc.time(0), sc.pose(1), sc.time(1))
         ok, why = True, ""
@@ -57,8 +57,9 @@ def _worker(rank, world, port, n_global, frames, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("n_global", [200_000, 1 << 22])
-def test_two_processes_two_gpus_match_the_unsharded_filter(n_global):
+@pytest.mark.parametrize("n_global,virtual", [(200_000, 1), (1 << 22, 1), (1 << 20, 4)])
+def test_two_processes_two_gpus_match_the_unsharded_filter(n_global, virtual):
+    """virtual = 4: block-cyclic placement, 8 shards, process p hosts the shards p, p + 2, p + 4, p + 6."""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs (run with gpurun --gpus 2)")
@@ -66,7 +67,7 @@ def test_two_processes_two_gpus_match_the_unsharded_filter(n_global):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, n_global, 6, q)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, n_global, 6, virtual, q)) for r in range(2)]
     for p in procs:
         p.start()
     for p in procs:

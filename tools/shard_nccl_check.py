@@ -30,14 +30,16 @@ def main():
     ap.add_argument("--particles", type=int, default=1 << 18)
     ap.add_argument("--frames", type=int, default=6)
     ap.add_argument("--no-compare", action="store_true", help="timing only (large filters: the getters copy everything to the host)")
+    ap.add_argument("--shards-per-gpu", dest="virtual", type=int, default=1, help="shards per GPU (block-cyclic placement), world * virtual <= 32")
     ap.add_argument("--stages", action="store_true", help="per-stage wall times (synchronises after every stage)")
     a = ap.parse_args()
     rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    N = a.particles // world * world
-    n_loc = N // world
+    V = a.virtual
+    N = a.particles // (world * V) * (world * V)
+    n_loc = N // (world * V)
     sc = scenes.Scene(0)
     D = sc.blobs(0).shape[0] + 4
     cmp_ = not a.no_compare
@@ -46,7 +48,7 @@ def main():
         ref.configure(sc.markers, sc.K, sc.params)
         ta = HostTracker(ref, sc, init_particles=False)
         ref.track_init(sc.pose(0), sc.time(0), sc.pose(1), sc.time(1))
-    sh = sharded.ShardedFilter(N, sharded.TorchDist() if world > 1 else sharded.Loopback(1), n_leds=5, max_blobs=D, device=local)
+    sh = sharded.ShardedFilter(N, sharded.TorchDist(virtual=V) if world > 1 else sharded.Loopback(V), n_leds=5, max_blobs=D, device=local)
     sh.configure(sc.markers, sc.K, sc.params)
     tb = HostTracker(sh, sc, init_particles=False)
     sh.track_init(sc.pose(0), sc.time(0), sc.pose(1), sc.time(1))
@@ -74,7 +76,9 @@ def main():
         for k in FIELDS:
             bad += int(ra[k] != rb[k])
         bad += int(not (ra["pose"] == rb["pose"]).all()) + int(not (ra["correspondences"] == rb["correspondences"]).all())
-        sl = slice(rank * n_loc, (rank + 1) * n_loc)
+        # this process hosts the shards rank, rank + world, ... (block-cyclic for V > 1): their slices of the unsharded filter
+        ids = sh.comm.local
+        sl = np.concatenate([np.arange(q * n_loc, (q + 1) * n_loc) for q in ids])
         bad += int(not (ref.weights(False)[sl] == sh.weights(False)).all())
         bad += int(not (ref.particles(0)[sl] == sh.particles(0)).all())
         if ra["resampled"]:
@@ -83,7 +87,7 @@ def main():
     if world > 1:
         dist.all_reduce(t)
     if rank == 0:
-        print(json.dumps(dict(check="shard_nccl", loop=sh.loop, rebalance=sh.rebalance, partials=sh.partial_exchange, p2p_error=sh.p2p_error, world=world, particles=N, frames=a.frames, mismatches=int(t.item()),
+        print(json.dumps(dict(check="shard_nccl", virtual=V, loop=sh.loop, rebalance=sh.rebalance, partials=sh.partial_exchange, p2p_error=sh.p2p_error, world=world, particles=N, frames=a.frames, mismatches=int(t.item()),
                               ms_per_frame_host_loop=round(1e3 * float(np.median(t_sh)), 3),
                               all_ms=[round(1e3 * v, 2) for v in t_sh])))
     if world > 1:
