@@ -210,6 +210,25 @@ int pfmpe_track_sequence_host(pfmpe_handle* h, int n_frames, const double* times
                               const int32_t* counts, const uint32_t* seeds, pfmpe_track_result* out,
                               double* frame_seconds);
 
+/* The same tracked frame for EVERY tracker of the handle with HOST buffers in and out, but with the FP64 tail on the
+ * device: predictPose (:234 -> :995-1010), the PF update (:475-689), optimiseAndUpdatePose (:690,
+ * :1805-2009, :2011-2035) and the jump check (:693-701) run in one launch of the track-mode kernel; per call the
+ * detections go host -> device through pinned staging and the result records come back.  For batches of tracked objects
+ * (the `for objectNumber` loop at :89 with thousands of objects), where the host-tail form spends its time in the
+ * Gauss-Newton of every object on the host cores.  Poses agree with the host-tail form to ~1e-9 (same algorithm, FP64,
+ * different operation order).  The device runs at most 64 Gauss-Newton iterations per object (PFMPE_GN_CAP in the
+ * environment; 0 = the reference's full 500): the ~1 % of objects still iterating then (the median is 8, a few never
+ * converge and run all 500) would hold the whole launch for their serial chain, so their records are packed into pinned
+ * memory first, the host cores redo exactly those optimisations (pf_optimise_pose, full :1805-2009 semantics) under the
+ * copy of the full record array, and one small kernel patches the device state -- the results are those of the uncapped
+ * form.  PFMPE_TRACE=1 prints the per-phase times of this call to stderr every 20 frames.  Layouts as pfmpe_track_frame_host_batch / pfmpe_track_sequence_host; the tracked objects'
+ * state (pfmpe_track_init) is shared with the host-tail calls and kept in step. */
+int pfmpe_track_frame_device_batch(pfmpe_handle* h, double time_to_predict, const double* image_points,
+                                   const int32_t* counts, const uint32_t* seeds, pfmpe_track_result* out);
+int pfmpe_track_sequence_device(pfmpe_handle* h, int n_frames, const double* times, const double* image_points,
+                                const int32_t* counts, const uint32_t* seeds, pfmpe_track_result* out,
+                                double* frame_seconds);
+
 /* results of frames [first, first+n) of one tracker */
 int pfmpe_track_results(pfmpe_handle* h, int tracker, int first_frame, int n_frames, pfmpe_track_result* out);
 

@@ -25,6 +25,7 @@ EXPORTS = [
     "pfmpe_optimise_pose", "pfmpe_predict_pose", "pfmpe_exponential_map", "pfmpe_logarithm_map",
     "pfmpe_track_init", "pfmpe_track_set_state", "pfmpe_track_upload", "pfmpe_track_attach", "pfmpe_track_run", "pfmpe_track_replay", "pfmpe_track_results",
     "pfmpe_track_frame_host", "pfmpe_track_frame_host_batch", "pfmpe_track_sequence_host",
+    "pfmpe_track_frame_device_batch", "pfmpe_track_sequence_device",
     "pfmpe_predict_roi", "pfmpe_p3p_histogram", "pfmpe_p3p_histogram_dev", "pfmpe_p3p_histogram_static", "pfmpe_p3p_solve", "pfmpe_p3p_check",
     "pfmpe_shard_configure", "pfmpe_shard_begin_frame", "pfmpe_shard_score", "pfmpe_shard_resample",
     "pfmpe_shard_export", "pfmpe_shard_keep", "pfmpe_shard_import", "pfmpe_shard_winner",
@@ -139,6 +140,8 @@ def lib():
                                                    C.POINTER(TrackResult)]
         L.pfmpe_track_sequence_host.argtypes = [C.c_void_p, C.c_int, _dp, _dp, C.POINTER(C.c_int32), C.POINTER(C.c_uint32),
                                                 C.POINTER(TrackResult), _dp]
+        L.pfmpe_track_sequence_device.argtypes = L.pfmpe_track_sequence_host.argtypes
+        L.pfmpe_track_frame_device_batch.argtypes = L.pfmpe_track_frame_host_batch.argtypes
         L.pfmpe_predict_roi.argtypes = [C.c_void_p, C.c_int, _dp, _dp, _dp, _dp]
         L.pfmpe_p3p_histogram.argtypes = [C.c_void_p, C.c_int, _dp, C.c_int32, C.POINTER(C.c_uint32), C.POINTER(P3pStats)]
         L.pfmpe_p3p_histogram_dev.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int32, C.POINTER(C.c_uint32),
@@ -533,8 +536,10 @@ class Handle:
         self._chk(lib().pfmpe_shard_winner(self._h, int(local_index), C.byref(o)))
         return unpack_frame_out(o)
 
-    def track_sequence_host(self, times, image_points, counts, seeds):
+    def track_sequence_host(self, times, image_points, counts, seeds, device_tail=False, out=None):
         """Per-frame host-buffer tracking of a whole sequence, looped in C (layouts of track_upload).
+        device_tail: pfmpe_track_sequence_device (predictPose / Gauss-Newton on the device, row f2) instead of the host tail.
+        out: a result array of an earlier call over as many frames, reused (a caller's own, already-touched buffer).
         Returns (results[tracker][frame], seconds per frame)."""
         ip = _c64(image_points)
         cn = np.ascontiguousarray(counts, dtype=np.int32)
@@ -542,11 +547,24 @@ class Handle:
         sd = np.ascontiguousarray(seeds, dtype=np.uint32)
         F = tm.shape[0]
         assert ip.shape == (self.T, F, self.max_blobs, 2) and cn.shape == (self.T, F) and sd.shape == (self.T, F)
-        arr = (TrackResult * (self.T * F))()
+        arr = out if out is not None else (TrackResult * (self.T * F))()
+        assert len(arr) == self.T * F
         secs = np.zeros(F)
-        self._chk(lib().pfmpe_track_sequence_host(self._h, F, _d(tm), _d(ip), cn.ctypes.data_as(C.POINTER(C.c_int32)),
-                                                 sd.ctypes.data_as(C.POINTER(C.c_uint32)), arr, _d(secs)))
+        fn = lib().pfmpe_track_sequence_device if device_tail else lib().pfmpe_track_sequence_host
+        self._chk(fn(self._h, F, _d(tm), _d(ip), cn.ctypes.data_as(C.POINTER(C.c_int32)),
+                     sd.ctypes.data_as(C.POINTER(C.c_uint32)), arr, _d(secs)))
         return arr, secs
+
+    def track_frame_device_batch(self, time_to_predict, image_points, counts, seeds):
+        """pfmpe_track_frame_device_batch: one tracked frame of every tracker, host buffers in / out, FP64 tail on the device."""
+        ip = _c64(image_points)
+        cn = np.ascontiguousarray(counts, dtype=np.int32)
+        sd = np.ascontiguousarray(seeds, dtype=np.uint32)
+        assert ip.shape == (self.T, self.max_blobs, 2) and cn.shape == (self.T,) and sd.shape == (self.T,)
+        arr = (TrackResult * self.T)()
+        self._chk(lib().pfmpe_track_frame_device_batch(self._h, float(time_to_predict), _d(ip), cn.ctypes.data_as(C.POINTER(C.c_int32)),
+                                                       sd.ctypes.data_as(C.POINTER(C.c_uint32)), arr))
+        return self._unpack_track(arr)
 
     def unpack_track(self, arr, tracker, n_frames):
         return self._unpack_track([arr[tracker * n_frames + f] for f in range(n_frames)])

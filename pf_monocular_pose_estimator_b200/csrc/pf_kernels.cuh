@@ -946,7 +946,7 @@ __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, pf_ctx& cx, pf_t
       pf_aff pose = pf_aff_from_f32(Tw);                 // predicted_pose_ = PoseParticle[q]  (:687)
       const pf_aff before = pose;
       const double* img = p.blobs + ((size_t)trk * p.total_frames + frame) * (size_t)p.D_max * 2;
-      const int gn = pf_gn_warp<L>(p.K9d, cx.objd, img, pairs, npairs, pose, ts, lane);   // cov -> ts.M
+      const int gn = pf_gn_warp<L>(p.K9d, cx.objd, img, pairs, npairs, pose, ts, lane, p.gn_cap);   // cov -> ts.M
       pf_stamp(p, 10);
       if (isi < 2) ++isi;                                // :2027-2030
       prev = cur;                                        // updatePose :2013-2014

@@ -250,9 +250,12 @@ __device__ __forceinline__ void pf_tri_ij(int l, int& i, int& j)
 // marker coordinates (shared memory); img: detections of the frame (D x 2 doubles, global);
 // pairs: (LED+1, blob+1) rows in registers.  pose in/out (replicated in every lane).  The
 // covariance (:2004) is left in ts.M (row-major).  Returns PubData.numIter (-1 when max_itr is hit).
+// cap > 0: give up after `cap` iterations and return -2 (the pose is then an intermediate iterate): the caller hands the
+// object to the host, which runs the whole optimisation again with the reference's full 500-iteration semantics -- an
+// iteration that creeps just above 1e-13 costs one warp 0.7 ms but a host core 0.15 ms.
 template <int L>
 __device__ __forceinline__ int pf_gn_warp(const double* K9, const double* obj, const double* img, const unsigned* pairs,
-                                          int npairs, pf_aff& pose, pf_tail_smem& ts, int lane)
+                                          int npairs, pf_aff& pose, pf_tail_smem& ts, int lane, int cap = 0)
 {
   const double conv = 1e-13;
   const int max_itr = 500;
@@ -284,6 +287,7 @@ __device__ __forceinline__ int pf_gn_warp(const double* K9, const double* obj, c
   double e_first = 0, e_last = 0;
   int reported = -1;
   for (int it = 0; it < max_itr; ++it) {
+    if (cap > 0 && it == cap) { reported = -2; break; }
     double Jr[14];
 #pragma unroll
     for (int i = 0; i < 14; ++i) Jr[i] = 0.0;

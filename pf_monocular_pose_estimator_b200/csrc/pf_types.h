@@ -125,6 +125,7 @@ struct pf_kparams {
   // (no host->device copy before the launch)
   int inline_in;
   int done_seq;                   // != 0: the result record lives in pinned host memory; published last, after a system fence
+  int gn_cap;                     // track mode: > 0 caps the device Gauss-Newton (gn_iters = -2: the host finishes the object)
   pf_frame_const fc_inline;
   double blobs_inline[2 * PF_INLINE_BLOBS];
   float dist[5];                  // plumb_bob (k1, k2, p1, p2, k3), used by the V = 2 kernel (PFMPE_FLAG_DISTORT)

@@ -4,6 +4,8 @@
 // needs the device fails with PFMPE_ERR_NO_DEVICE / PFMPE_ERR_CUDA if it is not usable.
 #include <cuda_runtime.h>
 
+#include <algorithm>
+#include <array>
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
@@ -71,6 +73,21 @@ class HostPool {
     done_.wait(g, [this]() { return pending_ == 0; });
     body_ = nullptr;
   }
+  // the same for a few items of very uneven cost (a Gauss-Newton of 70 or of 500 iterations): every thread takes the next
+  // item as it becomes free
+  void run_uneven(int n, const std::function<void(int)>& body)
+  {
+    {
+      std::lock_guard<std::mutex> g(m_);
+      next_.store(0);
+      body_ = &body; n_ = n; per_ = -1; pending_ = (int)th_.size(); ++gen_;
+    }
+    cv_.notify_all();
+    for (int i; (i = next_.fetch_add(1)) < n;) body(i);
+    std::unique_lock<std::mutex> g(m_);
+    done_.wait(g, [this]() { return pending_ == 0; });
+    body_ = nullptr;
+  }
 
  private:
   void loop(int id)
@@ -86,7 +103,8 @@ class HostPool {
         if (stop_) return;
         body = body_; n = n_; per = per_;
       }
-      for (int i = id * per; i < n && i < (id + 1) * per; ++i) (*body)(i);
+      if (per < 0) for (int i; (i = next_.fetch_add(1)) < n;) (*body)(i);
+      else for (int i = id * per; i < n && i < (id + 1) * per; ++i) (*body)(i);
       {
         std::lock_guard<std::mutex> g(m_);
         if (--pending_ == 0) done_.notify_one();
@@ -98,6 +116,7 @@ class HostPool {
   std::condition_variable cv_, done_;
   const std::function<void(int)>* body_ = nullptr;
   int n_ = 0, per_ = 0, pending_ = 0;
+  std::atomic<int> next_{0};
   unsigned long long gen_ = 0;
   bool stop_ = false;
 };
@@ -173,6 +192,13 @@ struct pfmpe_handle {
   bool last_was_track = false;
   TrackSeq seq;
   std::vector<HostTrack> host_trk;   // host mirror of the tracked objects (pfmpe_track_frame_host)
+  int gn_cap = 0;                    // launch_frames: Gauss-Newton cap of the next track-mode launch (live frames only)
+  TrackSeq live;                     // one-frame sequence of pfmpe_track_frame_device_batch (device buffers, created on first use)
+  unsigned char* h_live = nullptr;   // pinned staging of its inputs: blobs [T][D][2] | time | counts [T] | seeds [T]
+  pf_frame_result* h_live_res = nullptr;   // pinned: the T result records of the frame
+  int* h_late_hdr = nullptr;               // pinned, written by pf_track_late_kernel: [0] count, [4..] tracker list
+  pf_frame_result* h_late_rec = nullptr;   // pinned, written by pf_track_late_kernel: the records of those trackers
+  cudaEvent_t ev_late = nullptr;
   // sharded single filter (pfmpe_shard_*): this handle owns global particles [goff, goff + N) of n_global
   bool sharded = false;
   int goff = 0, n_global = 0;
@@ -236,6 +262,12 @@ void free_all(pfmpe_handle* h)
   cudaFree(h->rng_tab); cudaFree(h->timeline); cudaFree(h->warp_agg_g); cudaFree(h->shard_partial); cudaFree(h->gfill);
   if (h->seq.owned) { cudaFree(h->seq.blobs); cudaFree(h->seq.counts); cudaFree(h->seq.times); cudaFree(h->seq.seeds); }
   cudaFree(h->seq.result); cudaFree(h->seq.fc_log);
+  cudaFree(h->live.blobs); cudaFree(h->live.counts); cudaFree(h->live.times); cudaFree(h->live.seeds); cudaFree(h->live.result);
+  if (h->h_live) cudaFreeHost(h->h_live);
+  if (h->h_live_res) cudaFreeHost(h->h_live_res);
+  if (h->h_late_hdr) cudaFreeHost(h->h_late_hdr);
+  if (h->h_late_rec) cudaFreeHost(h->h_late_rec);
+  if (h->ev_late) cudaEventDestroy(h->ev_late);
   if (h->h_inbox) cudaFreeHost(h->h_inbox);
   if (h->h_result) cudaFreeHost(h->h_result);
   if (h->h_state) cudaFreeHost(h->h_state);
@@ -366,6 +398,7 @@ int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_f
   p.mode = mode;
   p.frame0 = frame0;
   p.n_frames = n_frames;
+  p.gn_cap = mode == 1 ? h->gn_cap : 0;
   if (sa) {
     p.pass_it = sa->pass_it; p.iters_total = sa->iters_total; p.q_local = sa->q_local; p.S_fx = sa->S_fx;
     for (int i = 0; i < 3; ++i) { p.rank_excl[i] = sa->excl[i]; p.rank_total[i] = sa->total[i]; }
@@ -515,6 +548,47 @@ __global__ void pf_fill_kernel(float4* base, int N, int S, float4 r0, float4 r1,
   base[n] = r0;
   base[(size_t)S + n] = r1;
   base[2 * (size_t)S + n] = r2;
+}
+
+// pfmpe_track_frame_device_batch: the host finished the Gauss-Newton of n objects (list[], records in pinned host memory,
+// read through the unified address space): their refined pose / covariance replace the capped iterate in the device state
+__global__ void pf_track_patch_kernel(pf_tracker_state* state, const pf_frame_result* rec, const int* list, int n)
+{
+  const int q = blockIdx.x, e = threadIdx.x;      // one block per object, 64 threads: 12 pose + 36 covariance entries
+  if (q >= n) return;
+  const int t = list[q];
+  if (e < 12) { const double v = rec[t].pose[e]; state[t].cur[e] = v; state[t].pred[e] = v; }
+  else if (e < 48) state[t].cov[e - 12] = rec[t].cov[e - 12];
+}
+
+// pfmpe_track_frame_device_batch: the records of the objects whose device Gauss-Newton was capped (gn_iters == -2), packed
+// and written straight into pinned host memory (hdr[0] = how many, hdr[4..] = which trackers, out[] = their records), so
+// that the host can start on them while the full record array is still crossing the bus.  One CTA; more than
+// PF_LATE_MAX objects: hdr[0] = -1, the host then picks them out of the full array.
+#define PF_LATE_MAX 2048
+__global__ void pf_track_late_kernel(const pf_frame_result* rec, int T, int* hdr, pf_frame_result* out)
+{
+  static_assert(sizeof(pf_frame_result) % 4 == 0, "records are copied as 32-bit words");
+  __shared__ int cnt;
+  __shared__ int lst[PF_LATE_MAX];
+  if (threadIdx.x == 0) cnt = 0;
+  __syncthreads();
+  for (int t = threadIdx.x; t < T; t += blockDim.x)
+    if (rec[t].status != 0 && rec[t].resampled && rec[t].gn_iters == -2) {
+      const int q = atomicAdd(&cnt, 1);
+      if (q < PF_LATE_MAX) lst[q] = t;
+    }
+  __syncthreads();
+  const int n = cnt;
+  if (n > PF_LATE_MAX) { if (threadIdx.x == 0) hdr[0] = -1; return; }
+  if (threadIdx.x == 0) hdr[0] = n;
+  for (int q = threadIdx.x; q < n; q += blockDim.x) hdr[4 + q] = lst[q];
+  const int W = sizeof(pf_frame_result) / 4;
+  for (int q = threadIdx.x >> 5; q < n; q += blockDim.x >> 5) {
+    const uint32_t* a = reinterpret_cast<const uint32_t*>(rec + lst[q]);
+    uint32_t* b = reinterpret_cast<uint32_t*>(out + q);
+    for (int i = threadIdx.x & 31; i < W; i += 32) b[i] = a[i];
+  }
 }
 
 // track mode: stage the constants of `frame` from the device-resident tracker state
@@ -1327,6 +1401,198 @@ int pfmpe_track_sequence_host(pfmpe_handle* h, int n_frames, const double* times
     const auto a = std::chrono::steady_clock::now();
     const int rc = track_frames_host(h, 0, T, times[f], image_points + (size_t)f * D2, (size_t)n_frames * D2, counts + f, seeds + f,
                                      (size_t)n_frames, out + f, (size_t)n_frames);
+    if (rc) return rc;
+    if (frame_seconds) frame_seconds[f] = std::chrono::duration<double>(std::chrono::steady_clock::now() - a).count();
+  }
+  return PFMPE_OK;
+}
+
+// ---- per-frame tracking with HOST buffers and the DEVICE tail (row f2) ---------------------------------------------
+// The same branch of estimateBodyPose as pfmpe_track_frame_host_batch, but predictPose, the PF update,
+// optimiseAndUpdatePose and the jump check all run in ONE launch of the track-mode kernel: the frame's detections go
+// host -> device (pinned staging), the result records come back device -> host.  For batches of tracked objects, where
+// the FP64 Gauss-Newton of thousands of objects would otherwise run on the host cores.
+static int track_frames_device(pfmpe_handle* h, double time_to_predict, const double* image_points, size_t stride,
+                               const int32_t* counts, const uint32_t* seeds, size_t cstride, pfmpe_track_result* out, size_t ostride)
+{
+  int rc = check_ready(h);
+  if (rc) return rc;
+  const int T = h->cfg.n_trackers, D = h->cfg.max_blobs;
+  for (int t = 0; t < T; ++t) {
+    if (!h->particles_set[t] || !h->host_trk[t].valid) return fail(h, PFMPE_ERR_STATE, "track_init must be called for every tracker");
+    if (counts[t * cstride] < 0 || counts[t * cstride] > D) return fail(h, PFMPE_ERR_INVALID, "blob count exceeds max_blobs");
+  }
+  PF_CUDA(h, cudaSetDevice(h->cfg.device));
+  const size_t nb = (size_t)T * D * 2 * sizeof(double), off_time = nb, off_cnt = off_time + 8, off_seed = off_cnt + (size_t)T * 4;
+  if (!h->live.blobs) {
+    PF_CUDA(h, dev_alloc(&h->live.blobs, (size_t)T * D * 2));
+    PF_CUDA(h, dev_alloc(&h->live.counts, (size_t)T));
+    PF_CUDA(h, dev_alloc(&h->live.times, (size_t)1));
+    PF_CUDA(h, dev_alloc(&h->live.seeds, (size_t)T));
+    PF_CUDA(h, dev_alloc(&h->live.result, (size_t)T));
+    PF_CUDA(h, cudaMemset(h->live.result, 0, (size_t)T * sizeof(pf_frame_result)));
+    PF_CUDA(h, cudaMallocHost((void**)&h->h_live, off_seed + (size_t)T * 4));
+    PF_CUDA(h, cudaMallocHost((void**)&h->h_live_res, (size_t)T * sizeof(pf_frame_result)));
+    PF_CUDA(h, cudaMallocHost((void**)&h->h_late_hdr, sizeof(int) * (4 + (size_t)T)));
+    PF_CUDA(h, cudaMallocHost((void**)&h->h_late_rec, sizeof(pf_frame_result) * (size_t)std::min(T, PF_LATE_MAX)));
+    PF_CUDA(h, cudaEventCreateWithFlags(&h->ev_late, cudaEventDisableTiming));
+    h->live.n_frames = 1; h->live.owned = true;
+  }
+  static const bool trace = std::getenv("PFMPE_TRACE") != nullptr;    // per-phase wall times of this call, printed every 20 frames
+  static std::vector<std::array<double, 10>> tr;
+  auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+  const double t0 = trace ? now() : 0.0;
+  double t1 = 0, t2 = 0, t3 = 0, t4 = 0;
+  double* sb = reinterpret_cast<double*>(h->h_live);
+  int32_t* sc = reinterpret_cast<int32_t*>(h->h_live + off_cnt);
+  uint32_t* ss = reinterpret_cast<uint32_t*>(h->h_live + off_seed);
+  *reinterpret_cast<double*>(h->h_live + off_time) = time_to_predict;
+  host_parallel_for(h, T, [&](int t) {
+    const int n = counts[t * cstride];
+    std::memcpy(sb + (size_t)t * D * 2, image_points + (size_t)t * stride, sizeof(double) * 2 * (size_t)n);
+    sc[t] = n; ss[t] = seeds[t * cstride];
+  });
+  static cudaEvent_t eA = nullptr, eB = nullptr;
+  if (trace && !eA) { cudaEventCreate(&eA); cudaEventCreate(&eB); }
+  if (trace) { t1 = now(); cudaEventRecord(eA, h->stream); }
+  PF_CUDA(h, cudaMemcpyAsync(h->live.blobs, sb, nb, cudaMemcpyHostToDevice, h->stream));
+  PF_CUDA(h, cudaMemcpyAsync(h->live.times, h->h_live + off_time, 8, cudaMemcpyHostToDevice, h->stream));
+  PF_CUDA(h, cudaMemcpyAsync(h->live.counts, sc, (size_t)T * 4, cudaMemcpyHostToDevice, h->stream));
+  PF_CUDA(h, cudaMemcpyAsync(h->live.seeds, ss, (size_t)T * 4, cudaMemcpyHostToDevice, h->stream));
+  std::swap(h->seq, h->live);                      // the track-mode launch reads its sequence from h->seq
+  {
+    pf_kparams p;
+    fill_kparams(h, p);
+    p.blob_count = h->seq.counts; p.times = h->seq.times; p.seeds = h->seq.seeds; p.total_frames = 1;
+    pf_track_prepare_kernel<<<(T + 127) / 128, 128, 0, h->stream>>>(p, 0);      // predictPose (:234 -> :995-1010) per tracker
+    rc = cudaGetLastError() == cudaSuccess ? PFMPE_OK : PFMPE_ERR_CUDA;
+    h->launches += 1;
+    // Gauss-Newton on the device for at most gn_cap iterations (PFMPE_GN_CAP, default 64: one object in ~300 goes beyond; 0 = the full 500): objects
+    // still iterating then are finished by the host below
+    static const int cap_env = [] { const char* e = std::getenv("PFMPE_GN_CAP"); return e ? std::atoi(e) : 64; }();
+    h->gn_cap = cap_env;
+    if (rc == PFMPE_OK) rc = launch_frames(h, 1, 0, T, 0, 1);
+    h->gn_cap = 0;
+  }
+  std::swap(h->seq, h->live);
+  if (rc) return rc;
+  // the capped objects first, packed, straight into pinned memory; then the full record array
+  pf_track_late_kernel<<<1, 1024, 0, h->stream>>>(h->live.result, T, h->h_late_hdr, h->h_late_rec);
+  PF_CUDA(h, cudaGetLastError());
+  h->launches += 1;
+  PF_CUDA(h, cudaEventRecord(h->ev_late, h->stream));
+  PF_CUDA(h, cudaMemcpyAsync(h->h_live_res, h->live.result, (size_t)T * sizeof(pf_frame_result), cudaMemcpyDeviceToHost, h->stream));
+  if (trace) { cudaEventRecord(eB, h->stream); t2 = now(); }
+  PF_CUDA(h, cudaEventSynchronize(h->ev_late));
+  if (trace) t3 = now();
+  // objects whose device Gauss-Newton was capped: the whole optimisation again on the host (:690 -> :1805-2009, full
+  // semantics), in parallel over the objects and under the copy of the full array; their records and device state
+  // (cur / pred / cov) are patched
+  auto redo = [&](pf_frame_result& s, int t) {
+    pf_pose Tw;
+    for (int i = 0; i < 12; ++i) Tw.p[i] = s.winner_pose[i];
+    pf_aff pose = pf_aff_from_f32(Tw);
+    const pf_aff before = pose;
+    double c[36];
+    s.gn_iters = pf_optimise_pose(h->K, &h->markers[(size_t)t * PF_MAX_LED * 3], image_points + (size_t)t * stride, s.pairs, s.npairs, pose, c);
+    s.flag_fail = 1.0f;
+    for (int r = 0; r < 3; ++r)
+      for (int k = 0; k < 3; ++k)
+        if (fabs(before.a[4 * r + k] - pose.a[4 * r + k]) >= 0.3) s.flag_fail = 1.5f;   // :693-701
+    for (int i = 0; i < 12; ++i) s.pose[i] = pose.a[i];
+    for (int i = 0; i < 36; ++i) s.cov[i] = c[i];
+  };
+  auto redo_all = [&](int n, const std::function<void(int)>& one) {
+    if (n >= 2 && h->pool && h->pool->size() > 0) h->pool->run_uneven(n, one);
+    else for (int q = 0; q < n; ++q) one(q);
+  };
+  int* list = h->h_late_hdr + 4;
+  int n_late = h->h_late_hdr[0];
+  if (n_late > 0) redo_all(n_late, [&](int q) { redo(h->h_late_rec[q], list[q]); });
+  PF_CUDA(h, cudaStreamSynchronize(h->stream));
+  float pre_ms = 0.f, post_ms = 0.f;
+  if (trace) { cudaEventElapsedTime(&pre_ms, eA, h->ev0); cudaEventElapsedTime(&post_ms, h->ev1, eB); }
+  if (n_late > 0) {
+    for (int q = 0; q < n_late; ++q) h->h_live_res[list[q]] = h->h_late_rec[q];
+  } else if (n_late < 0) {                          // more than PF_LATE_MAX of them: out of the full array
+    n_late = 0;
+    for (int t = 0; t < T; ++t)
+      if (h->h_live_res[t].status != 0 && h->h_live_res[t].resampled && h->h_live_res[t].gn_iters == -2) list[n_late++] = t;
+    redo_all(n_late, [&](int q) { redo(h->h_live_res[list[q]], list[q]); });
+  }
+  if (n_late > 0) {
+    pf_track_patch_kernel<<<(unsigned)n_late, 64, 0, h->stream>>>(h->state, h->h_live_res, list, n_late);
+    PF_CUDA(h, cudaGetLastError());
+    h->launches += 1;
+    PF_CUDA(h, cudaStreamSynchronize(h->stream));   // the pinned records and the list are rewritten by the next frame
+  }
+  if (trace) t4 = now();
+  host_parallel_for(h, T, [&](int t) {
+    const pf_frame_result& s = h->h_live_res[t];
+    pfmpe_track_result* o = out + (size_t)t * ostride;
+    std::memset(o, 0, sizeof *o);
+    o->status = s.status; o->flag_fail = s.flag_fail; o->iterations = s.iterations; o->gn_iterations = s.gn_iters;
+    o->most_likely_pose_idx = s.most_likely_pose_idx; o->max_count = s.max_count;
+    o->highest_prob = s.highest_prob; o->weight_sum = (double)s.sum_fx / 1073741824.0;
+    pf_aff P;
+    for (int i = 0; i < 12; ++i) P.a[i] = s.pose[i];
+    pf_aff_to_cm16(P, o->pose);
+    for (int i = 0; i < 6; ++i) for (int j = 0; j < 6; ++j) o->cov[i + 6 * j] = s.cov[6 * i + j];
+    pf_aff W;
+    for (int i = 0; i < 12; ++i) W.a[i] = (double)s.winner_pose[i];
+    pf_aff_to_cm16(W, o->winner_pose);
+    o->n_correspondences = s.npairs;
+    for (int i = 0; i < 2 * PFMPE_MAX_LED; ++i) o->correspondences[i] = s.pairs[i];
+    h->last_sum_fx[t] = s.sum_fx;
+    // host mirror of the tracked object (updatePose :2011-2021), so that the host-tail calls can take over
+    HostTrack& ht = h->host_trk[t];
+    if (s.status != 0) {
+      if (s.resampled) {
+        if (ht.isi < 2) ++ht.isi;
+        ht.prev = ht.cur; ht.cur = P;
+        if (time_to_predict - ht.t_cur > 0.001 || time_to_predict < ht.t_cur) { ht.t_prev = ht.t_cur; ht.t_cur = time_to_predict; }
+        for (int i = 0; i < 36; ++i) ht.cov[i] = s.cov[i];
+      } else ht.isi = 0;
+    }
+  });
+  h->last_was_track = false;
+  if (trace) {
+    const double t5 = now();
+    float kms = 0.f;
+    cudaEventElapsedTime(&kms, h->ev0, h->ev1);
+    tr.push_back({t1 - t0, t2 - t1, t3 - t2, t4 - t3, t5 - t4, (double)kms * 1e-3, (double)n_late, t5 - t0, (double)pre_ms * 1e-3, (double)post_ms * 1e-3});
+    if (tr.size() % 20 == 0) {
+      const char* nm[10] = {"stage", "enqueue", "wait (capped list)", "host GN + rest of D2H", "convert", "kernel(events)", "late objects", "total", "H2D+prepare(events)", "D2H(events)"};
+      std::fprintf(stderr, "[pfmpe trace, last 20 frames, median / max]");
+      for (int k = 0; k < 10; ++k) {
+        std::vector<double> v;
+        for (size_t i = tr.size() - 20; i < tr.size(); ++i) v.push_back(tr[i][(size_t)k]);
+        std::sort(v.begin(), v.end());
+        if (k == 6) std::fprintf(stderr, "  %s %.0f / %.0f", nm[k], v[10], v[19]);
+        else std::fprintf(stderr, "  %s %.3f / %.3f ms", nm[k], 1e3 * v[10], 1e3 * v[19]);
+      }
+      std::fprintf(stderr, "\n");
+    }
+  }
+  return PFMPE_OK;
+}
+
+int pfmpe_track_frame_device_batch(pfmpe_handle* h, double time_to_predict, const double* image_points, const int32_t* counts,
+                                   const uint32_t* seeds, pfmpe_track_result* out)
+{
+  if (!h || !out || !image_points || !counts || !seeds) return PFMPE_ERR_INVALID;
+  return track_frames_device(h, time_to_predict, image_points, (size_t)h->cfg.max_blobs * 2, counts, seeds, 1, out, 1);
+}
+
+int pfmpe_track_sequence_device(pfmpe_handle* h, int n_frames, const double* times, const double* image_points,
+                                const int32_t* counts, const uint32_t* seeds, pfmpe_track_result* out, double* frame_seconds)
+{
+  if (!h || n_frames < 1 || !times || !image_points || !counts || !seeds || !out) return PFMPE_ERR_INVALID;
+  const size_t D2 = (size_t)h->cfg.max_blobs * 2;
+  for (int f = 0; f < n_frames; ++f) {
+    const auto a = std::chrono::steady_clock::now();
+    const int rc = track_frames_device(h, times[f], image_points + (size_t)f * D2, (size_t)n_frames * D2, counts + f, seeds + f,
+                                       (size_t)n_frames, out + f, (size_t)n_frames);
     if (rc) return rc;
     if (frame_seconds) frame_seconds[f] = std::chrono::duration<double>(std::chrono::steady_clock::now() - a).count();
   }

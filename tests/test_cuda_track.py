@@ -155,3 +155,48 @@ def test_track_run_errors():
     h.track_run(0, 4)
     assert all(r["status"] == 1 for r in h.track_results(0, 4))
     h.close()
+
+
+def test_track_frame_device_batch_matches_host_tail_batch():
+    """Host buffers in / out with the FP64 tail on the device (pfmpe_track_frame_device_batch) against the host-tail
+    form (pfmpe_track_frame_host_batch) on the same batch: same PF decisions (integers exact), poses within 1e-8
+    (two FP64 Gauss-Newton implementations of the same algorithm); and the host-tail call can take over afterwards."""
+    T, N, F = 6, 2048, 8
+    trackers = np.arange(T)
+    frames = list(range(2, 2 + F))
+    blobs, counts = S.blob_tensor_fast(trackers, frames, n_outliers=10)
+    seeds = np.array([[S.pf_seed(f, int(t)) for f in frames] for t in trackers], dtype=np.uint32)
+    hs = []
+    for _ in range(2):
+        h = capi.Handle(N, n_trackers=T, n_leds=5, max_blobs=blobs.shape[2])
+        h.configure(S.MARKERS_5, S.K_README, S.DEFAULT_PARAMS)
+        for t in trackers:
+            ph = S.tracker_phase(int(t))
+            h.track_init(S.true_pose(0.0, ph), 0.0, S.true_pose(S.DT, ph), S.DT, tracker=int(t))
+        hs.append(h)
+    ha, hb = hs
+    for k, f in enumerate(frames):
+        last = k == F - 1
+        # the last frame goes through the host-tail call on BOTH handles: hb's host mirror must be in step by then
+        arr = (capi.TrackResult * T)()
+        ha._chk(capi.lib().pfmpe_track_frame_host_batch(ha._h, f * S.DT, capi._d(np.ascontiguousarray(blobs[:, k])),
+                np.ascontiguousarray(counts[:, k]).ctypes.data_as(capi.C.POINTER(capi.C.c_int32)),
+                np.ascontiguousarray(seeds[:, k]).ctypes.data_as(capi.C.POINTER(capi.C.c_uint32)), arr))
+        ra = ha._unpack_track(arr)
+        if last:
+            arr2 = (capi.TrackResult * T)()
+            hb._chk(capi.lib().pfmpe_track_frame_host_batch(hb._h, f * S.DT, capi._d(np.ascontiguousarray(blobs[:, k])),
+                    np.ascontiguousarray(counts[:, k]).ctypes.data_as(capi.C.POINTER(capi.C.c_int32)),
+                    np.ascontiguousarray(seeds[:, k]).ctypes.data_as(capi.C.POINTER(capi.C.c_uint32)), arr2))
+            rb = hb._unpack_track(arr2)
+        else:
+            rb = hb.track_frame_device_batch(f * S.DT, blobs[:, k], counts[:, k], seeds[:, k])
+        for t in range(T):
+            a, b = ra[t], rb[t]
+            assert a["status"] == b["status"] == 1 and a["iterations"] == b["iterations"], (f, t)
+            assert a["correspondences"].shape == b["correspondences"].shape and (a["correspondences"] == b["correspondences"]).all()
+            assert a["most_likely_pose_idx"] == b["most_likely_pose_idx"] and a["max_count"] == b["max_count"]
+            np.testing.assert_allclose(b["pose"], a["pose"], atol=1e-7, rtol=0)
+            assert np.abs(b["pose"][:3, 3] - S.true_pose(f * S.DT, S.tracker_phase(t))[:3, 3]).max() < 0.03
+    ha.close()
+    hb.close()
