@@ -1,5 +1,9 @@
 """-m gpu: device-resident tracking (whole sequences on the GPU, FP64 tail on the device) against
 (a) the per-frame C-ABI path with the host FP64 tail and (b) the oracle tracker."""
+import os
+import subprocess
+import sys
+
 import numpy as np
 import pytest
 
@@ -198,5 +202,20 @@ def test_track_frame_device_batch_matches_host_tail_batch():
             assert a["most_likely_pose_idx"] == b["most_likely_pose_idx"] and a["max_count"] == b["max_count"]
             np.testing.assert_allclose(b["pose"], a["pose"], atol=1e-7, rtol=0)
             assert np.abs(b["pose"][:3, 3] - S.true_pose(f * S.DT, S.tracker_phase(t))[:3, 3]).max() < 0.03
+            if os.environ.get("PFMPE_GN_CAP") == "2" and a["gn_iterations"] > 2:
+                # capped on the device and finished by the host: the very same host optimisation as the host-tail form
+                assert a["gn_iterations"] == b["gn_iterations"]
+                np.testing.assert_allclose(b["cov"], a["cov"], atol=0, rtol=1e-12)
     ha.close()
     hb.close()
+
+
+def test_track_frame_device_batch_capped_objects_finished_by_host():
+    """The same comparison in a fresh process with the device Gauss-Newton capped at 2 iterations (PFMPE_GN_CAP=2, read
+    once per process): every object then takes the capped route -- gather kernel -> host optimisation -> patch kernel --
+    and the following frames start from the patched device state."""
+    env = dict(os.environ, PFMPE_GN_CAP="2")
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu",
+                        __file__ + "::test_track_frame_device_batch_matches_host_tail_batch"],
+                       env=env, capture_output=True, text=True, timeout=600, cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
