@@ -206,6 +206,7 @@ __device__ __forceinline__ void pf_p3p_roots(const pf_p3p_cam& Cc, const pf_p3p_
 // Back-substitution of one root (p3p.cpp:181-233): S = [R | C] column-major 3x4, R = N^T R'^T T, C = P1 + N^T C'
 __device__ __forceinline__ void pf_p3p_backsub(const pf_p3p_cam& Cc, const pf_p3p_world& W, double r, double S[12])
 {
+  // evaluated as the reference writes it: the solution entries feed the exact-equality duplicate rule (:1659-1663)
   const double cot_alpha = (-Cc.phi1 * W.p1 / Cc.phi2 - r * W.p2 + W.d12 * Cc.b) / (-Cc.phi1 * r * W.p2 / Cc.phi2 + W.p1 - W.d12);
   const double cos_theta = r, sin_theta = sqrt(1 - r * r);
   const double sin_alpha = sqrt(1 / (cot_alpha * cot_alpha + 1));
@@ -416,11 +417,14 @@ __device__ __forceinline__ long long pf_c2(long long m) { return m * (m - 1) / 2
 // permutations (p.nchunk slices per triple, so that small problems still fill the GPU): pre-filters and camera part
 // once, then per permutation the quartic, four back-substitutions, back-projection and votes.
 // dynamic shared memory: sxy [D] double2 | hist [D*L] u32 | sid [D] int
-template <int MINB>
+// LT: the LED count as a compile-time constant (5: the unused LEDs of a permutation and their projections stay in
+// registers), or 0 for any count up to PF_P3P_MAX_L (local arrays)
+template <int MINB, int LT>
 __global__ void __launch_bounds__(PF_P3P_BLOCK, MINB) pf_p3p_hist_kernel(pf_p3p_params p)
 {
+  constexpr int NU = LT ? LT - 3 : PF_P3P_MAX_L - 3;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int D = p.D, L = p.L;
+  const int D = p.D, L = LT ? LT : p.L;
   double2* sxy = reinterpret_cast<double2*>(smem_raw);
   unsigned* sh = reinterpret_cast<unsigned*>(sxy + D);
   int* sid = reinterpret_cast<int*>(sh + D * L);
@@ -479,7 +483,7 @@ __global__ void __launch_bounds__(PF_P3P_BLOCK, MINB) pf_p3p_hist_kernel(pf_p3p_
   const int pr_begin = chunk * per, pr_end = min(nperm, pr_begin + per);
   const double tol = p.tol;
   const double reach = tol + 1e-6;   // column window; every candidate is then tested exactly
-  const int n_un = L - 3;
+  const int n_un = LT ? NU : L - 3;
 
   // The loops are written so that a warp stays converged: every thread runs `per` steps, dead threads skip the
   // bodies, and the warp re-joins after every solution.
@@ -519,33 +523,50 @@ __global__ void __launch_bounds__(PF_P3P_BLOCK, MINB) pf_p3p_hist_kernel(pf_p3p_
       __syncwarp();
       if (use) {
         ++n_proj;
-        // inverse of [R C; 0 1] by cofactors: Ai = adj(R) / det(R), ti = -Ai C
+        // inverse of [R C; 0 1] by cofactors: Ai = adj(R) / det(R) (one reciprocal), ti = -Ai C
         const double a00 = S[0], a10 = S[1], a20 = S[2], a01 = S[3], a11 = S[4], a21 = S[5], a02 = S[6], a12 = S[7], a22 = S[8];
         const double c00 = a11 * a22 - a12 * a21, c01 = a12 * a20 - a10 * a22, c02 = a10 * a21 - a11 * a20;
-        const double det = a00 * c00 + a01 * c01 + a02 * c02;
-        const double i00 = c00 / det, i01 = (a02 * a21 - a01 * a22) / det, i02 = (a01 * a12 - a02 * a11) / det;
-        const double i10 = c01 / det, i11 = (a00 * a22 - a02 * a20) / det, i12 = (a02 * a10 - a00 * a12) / det;
-        const double i20 = c02 / det, i21 = (a01 * a20 - a00 * a21) / det, i22 = (a00 * a11 - a01 * a10) / det;
+        const double idet = 1.0 / (a00 * c00 + a01 * c01 + a02 * c02);
+        const double i00 = c00 * idet, i01 = (a02 * a21 - a01 * a22) * idet, i02 = (a01 * a12 - a02 * a11) * idet;
+        const double i10 = c01 * idet, i11 = (a00 * a22 - a02 * a20) * idet, i12 = (a02 * a10 - a00 * a12) * idet;
+        const double i20 = c02 * idet, i21 = (a01 * a20 - a00 * a21) * idet, i22 = (a00 * a11 - a01 * a10) * idet;
         const double t0 = -(i00 * S[9] + i01 * S[10] + i02 * S[11]), t1 = -(i10 * S[9] + i11 * S[10] + i12 * S[11]),
                      t2 = -(i20 * S[9] + i21 * S[10] + i22 * S[11]);
         // project the unused LEDs (ascending LED number, :1637-1656) with the full K (project2d :1017-1034)
-        double pu[PF_P3P_MAX_L - 3], pv[PF_P3P_MAX_L - 3];
-        int pl[PF_P3P_MAX_L - 3];
-        int m = 0;
-        for (int ll = 0; ll < L; ++ll) {
-          if (ll == j0 || ll == j1 || ll == j2) continue;
+        double pu[NU], pv[NU];
+        int pl[NU];
+        auto project = [&](int ll, double& u, double& v) {
           const double X = p.obj[3 * ll], Y = p.obj[3 * ll + 1], Z = p.obj[3 * ll + 2];
           const double xc = i00 * X + i01 * Y + i02 * Z + t0, yc = i10 * X + i11 * Y + i12 * Z + t1,
                        zc = i20 * X + i21 * Y + i22 * Z + t2;
           const double q0 = p.K[0] * xc + p.K[1] * yc + p.K[2] * zc, q1 = p.K[3] * xc + p.K[4] * yc + p.K[5] * zc,
                        q2 = p.K[6] * xc + p.K[7] * yc + p.K[8] * zc;
-          pu[m] = q0 / q2; pv[m] = q1 / q2; pl[m] = ll;
-          ++m;
+          const double iq2 = 1.0 / q2;
+          u = q0 * iq2; v = q1 * iq2;
+        };
+        if (LT) {
+          unsigned mk = ((1u << LT) - 1u) ^ ((1u << j0) | (1u << j1) | (1u << j2));
+#pragma unroll
+          for (int a = 0; a < NU; ++a) {
+            pl[a] = __ffs(mk) - 1;
+            mk &= mk - 1u;
+            project(pl[a], pu[a], pv[a]);
+          }
+        } else {
+          int m = 0;
+          for (int ll = 0; ll < L; ++ll) {
+            if (ll == j0 || ll == j1 || ll == j2) continue;
+            project(ll, pu[m], pv[m]);
+            pl[m] = ll;
+            ++m;
+          }
         }
         // votes (:1680-1712): every unused detection close to the triple's centroid whose nearest projected LED is
         // closer than tol votes for (detection, that LED); if any did, the triple's own three pairs vote too
         unsigned votes = 0;
-        for (int a = 0; a < n_un; ++a) {
+#pragma unroll
+        for (int a = 0; a < NU; ++a) {
+          if (!LT && a >= n_un) break;
           const double u = pu[a], xlo = u - reach, xhi = u + reach;
           int lb = 0, ub = D;
           while (lb < ub) {   // first sorted detection with x >= xlo
@@ -560,7 +581,9 @@ __global__ void __launch_bounds__(PF_P3P_BLOCK, MINB) pf_p3p_hist_kernel(pf_p3p_
             if (!(pf_sqd2(mx, my, bx, by) < thresh)) continue;   // :1598
             double best = INFINITY;
             int bj = -1;
-            for (int c = 0; c < n_un; ++c) {   // calculateMinDistancesAndPairs (:2093-2137): first strict minimum
+#pragma unroll
+            for (int c = 0; c < NU; ++c) {   // calculateMinDistancesAndPairs (:2093-2137): first strict minimum
+              if (!LT && c >= n_un) break;
               const double d2 = pf_sqd2(bx, by, pu[c], pv[c]);
               if (d2 < best) { best = d2; bj = c; }
             }
@@ -615,7 +638,13 @@ cudaError_t pf_p3p_launch_hist(const pf_p3p_params& p, cudaStream_t stream)
   static int occ_env = -1;
   if (occ_env < 0) { const char* e = getenv("PFMPE_P3P_OCC"); occ_env = e ? atoi(e) : 0; }
   const int occ = occ_env ? occ_env : (p.D >= 100 ? 5 : 4);
-  void (*kern)(pf_p3p_params) = occ == 5 ? pf_p3p_hist_kernel<5> : occ == 4 ? pf_p3p_hist_kernel<4> : pf_p3p_hist_kernel<3>;
+  void (*kern)(pf_p3p_params);
+  if (p.L == 5)
+    kern = occ >= 8 ? pf_p3p_hist_kernel<8, 5> : occ == 6 ? pf_p3p_hist_kernel<6, 5> : occ == 5 ? pf_p3p_hist_kernel<5, 5>
+         : occ == 4 ? pf_p3p_hist_kernel<4, 5> : pf_p3p_hist_kernel<3, 5>;
+  else
+    kern = occ >= 8 ? pf_p3p_hist_kernel<8, 0> : occ == 6 ? pf_p3p_hist_kernel<6, 0> : occ == 5 ? pf_p3p_hist_kernel<5, 0>
+         : occ == 4 ? pf_p3p_hist_kernel<4, 0> : pf_p3p_hist_kernel<3, 0>;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
