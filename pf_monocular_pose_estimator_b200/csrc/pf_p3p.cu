@@ -79,7 +79,7 @@ __device__ __forceinline__ pf_cxd pf_cx_pow_real_int(double x, int n)
 }
 
 // P3P::solveQuartic (p3p.cpp:238-292): Ferrari's closed form, real parts of the four roots
-__device__ __noinline__ void pf_p3p_quartic(const double f[5], double roots[4])
+__device__ __forceinline__ void pf_p3p_quartic(const double f[5], double roots[4])
 {
   const double A = f[0], B = f[1], C = f[2], D = f[3], E = f[4];
   const double A2 = A * A, B2 = B * B, A3 = A2 * A, B3 = B2 * B, A4 = A3 * A, B4 = B3 * B;
@@ -416,18 +416,35 @@ __device__ __forceinline__ long long pf_c2(long long m) { return m * (m - 1) / 2
 // One thread owns one detection triple (i0 < i1 < i2, lexicographic rank = its number) and a slice of the LED
 // permutations (p.nchunk slices per triple, so that small problems still fill the GPU): pre-filters and camera part
 // once, then per permutation the quartic, four back-substitutions, back-projection and votes.
-// dynamic shared memory: sxy [D] double2 | hist [D*L] u32 | sid [D] int
+// dynamic shared memory: sxy [D] double2 | xb [2] double | hist [D*L] u32 | sid [D] int | first [PF_P3P_NB + 1] int
+// The detections near a projected LED are found through a bucket table over x (first[b] = the first sorted detection
+// whose bucket is >= b; bucket = a monotone function of x, so nothing left of first[bucket(x_lo)] can be >= x_lo)
+// instead of a binary search per projected LED: one shared-memory load in place of eight dependent ones.
+#define PF_P3P_NB 256
+__device__ __forceinline__ int pf_p3p_bucket(double x, double x0, double inv_w)
+{
+  const double t = (x - x0) * inv_w;
+  if (x != x) return PF_P3P_NB;                               // NaN sorts last
+  return t >= (double)PF_P3P_NB ? PF_P3P_NB : (t > 0.0 ? (int)t : 0);
+}
 // LT: the LED count as a compile-time constant (5: the unused LEDs of a permutation and their projections stay in
 // registers), or 0 for any count up to PF_P3P_MAX_L (local arrays)
-template <int MINB, int LT>
-__global__ void __launch_bounds__(PF_P3P_BLOCK, MINB) pf_p3p_hist_kernel(pf_p3p_params p)
+// MODE 0: everything in one kernel.  MODE 1 / 2: the same work as two launches -- 1 = up to the four roots of every
+// (triple, permutation), written to rbuf [step][thread] (32 B each); 2 = from those roots on (back-substitution,
+// back-projection, votes).  The single kernel is 80 KB of code and waits for instruction fetch more than for anything
+// else (`no_instruction` 5.7 stall cycles per issued instruction); the second half alone fits the 32 KB instruction
+// cache.  gid0 / nthr: the slab of threads this launch covers (rbuf holds one slab).
+template <int MINB, int LT, int MODE>
+__global__ void __launch_bounds__(PF_P3P_BLOCK, MINB) pf_p3p_hist_kernel(pf_p3p_params p, double2* rbuf, long long gid0, long long nthr)
 {
   constexpr int NU = LT ? LT - 3 : PF_P3P_MAX_L - 3;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int D = p.D, L = LT ? LT : p.L;
   double2* sxy = reinterpret_cast<double2*>(smem_raw);
-  unsigned* sh = reinterpret_cast<unsigned*>(sxy + D);
+  double* xb = reinterpret_cast<double*>(sxy + D);
+  unsigned* sh = reinterpret_cast<unsigned*>(xb + 2);
   int* sid = reinterpret_cast<int*>(sh + D * L);
+  int* first = sid + D;
   const int tid = threadIdx.x;
   for (int i = tid; i < D; i += PF_P3P_BLOCK) {
     sxy[i] = make_double2(p.simg[2 * i], p.simg[2 * i + 1]);
@@ -435,12 +452,31 @@ __global__ void __launch_bounds__(PF_P3P_BLOCK, MINB) pf_p3p_hist_kernel(pf_p3p_
   }
   for (int i = tid; i < D * L; i += PF_P3P_BLOCK) sh[i] = 0u;
   __syncthreads();
+  if (MODE != 1 && tid == 0) {         // bucket grid over [smallest x, largest finite x]
+    int e = D - 1;
+    while (e > 0 && !(fabs(sxy[e].x) < INFINITY)) --e;
+    const double span = sxy[e].x - sxy[0].x;
+    xb[0] = sxy[0].x;
+    xb[1] = (span > 0.0 && span < INFINITY) ? (double)PF_P3P_NB / span : 0.0;
+  }
+  __syncthreads();
+  const double bx0 = MODE != 1 ? xb[0] : 0.0, binv = MODE != 1 ? xb[1] : 0.0;
+  for (int b = tid; MODE != 1 && b <= PF_P3P_NB; b += PF_P3P_BLOCK) {
+    int lo = 0, hi = D;
+    while (lo < hi) {                  // first sorted detection whose bucket is >= b
+      const int mid = (lo + hi) >> 1;
+      if (pf_p3p_bucket(sxy[mid].x, bx0, binv) < b) lo = mid + 1; else hi = mid;
+    }
+    first[b] = lo;
+  }
+  __syncthreads();
 
   const long long n_triples_all = pf_c3(D);
-  const long long gid = (long long)blockIdx.x * PF_P3P_BLOCK + tid;
+  const long long lgid = (long long)blockIdx.x * PF_P3P_BLOCK + tid;     // thread of this launch (slab)
+  const long long gid = gid0 + lgid;
   const long long triple = gid / p.nchunk;
   const int chunk = (int)(gid % p.nchunk);
-  const bool in_range = triple < n_triples_all;
+  const bool in_range = triple < n_triples_all && lgid < nthr;
   // unrank: i0 = largest a with C(D,3) - C(D-a,3) <= triple; then the pair (i1, i2) inside the D-1-i0 that follow
   int i0 = 0, i1 = 1, i2 = 2;
   if (in_range) {
@@ -472,7 +508,7 @@ __global__ void __launch_bounds__(PF_P3P_BLOCK, MINB) pf_p3p_hist_kernel(pf_p3p_
     for (int q = 0; q < D; ++q) cd += pf_sqd2(mx, my, sxy[q].x, sxy[q].y) < thresh ? 1 : 0;
     pass = cd >= 5;
   }
-  unsigned n_triples = (pass && chunk == 0) ? 1u : 0u, n_solved = 0, n_proj = 0, n_vote = 0;
+  unsigned n_triples = (pass && chunk == 0 && MODE != 1) ? 1u : 0u, n_solved = 0, n_proj = 0, n_vote = 0;
 
   pf_p3p_cam Cc;
   pf_p3p_cam_frame(pf_d3m(p.vec[3 * i0], p.vec[3 * i0 + 1], p.vec[3 * i0 + 2]),
@@ -495,12 +531,24 @@ __global__ void __launch_bounds__(PF_P3P_BLOCK, MINB) pf_p3p_hist_kernel(pf_p3p_
     pf_p3p_perm(live ? pr : 0, L, j0, j1, j2);
     const pf_p3p_world W = p.wtab[2 * (live ? pr : 0) + Cc.swapped];
     live = live && W.colinear == 0.0;
-    n_solved += live ? 1u : 0u;
+    n_solved += (live && MODE != 1) ? 1u : 0u;
     double r0 = 0, r1 = 0, r2 = 0, r3 = 0;
-    if (live) {
+    if (MODE == 2) {
+      if (live) {
+        const double2 a = rbuf[2 * ((long long)step * nthr + lgid)], b = rbuf[2 * ((long long)step * nthr + lgid) + 1];
+        r0 = a.x; r1 = a.y; r2 = b.x; r3 = b.y;
+      }
+    } else if (live) {
       double roots[4];
       pf_p3p_roots(Cc, W, roots);
       r0 = roots[0]; r1 = roots[1]; r2 = roots[2]; r3 = roots[3];
+    }
+    if (MODE == 1) {
+      if (live) {
+        rbuf[2 * ((long long)step * nthr + lgid)] = make_double2(r0, r1);
+        rbuf[2 * ((long long)step * nthr + lgid) + 1] = make_double2(r2, r3);
+      }
+      continue;
     }
     __syncwarp();
     double Sprev[12];
@@ -568,13 +616,10 @@ __global__ void __launch_bounds__(PF_P3P_BLOCK, MINB) pf_p3p_hist_kernel(pf_p3p_
         for (int a = 0; a < NU; ++a) {
           if (!LT && a >= n_un) break;
           const double u = pu[a], xlo = u - reach, xhi = u + reach;
-          int lb = 0, ub = D;
-          while (lb < ub) {   // first sorted detection with x >= xlo
-            const int mid = (lb + ub) >> 1;
-            if (sxy[mid].x < xlo) lb = mid + 1; else ub = mid;
-          }
-          for (int q = lb; q < D && sxy[q].x <= xhi; ++q) {
+          for (int q = first[pf_p3p_bucket(xlo, bx0, binv)]; q < D; ++q) {   // sorted detections with xlo <= x <= xhi
             const double bx = sxy[q].x, by = sxy[q].y;
+            if (bx < xlo) continue;
+            if (!(bx <= xhi)) break;
             if (!(fabs(by - pv[a]) <= reach)) continue;          // farther than tol from this LED: cannot vote for it
             const int det_i = sid[q];
             if (det_i == i0 || det_i == i1 || det_i == i2) continue;
@@ -603,6 +648,7 @@ __global__ void __launch_bounds__(PF_P3P_BLOCK, MINB) pf_p3p_hist_kernel(pf_p3p_
       __syncwarp();
     }
   }
+  if (MODE == 1) return;
   __syncthreads();
   for (int i = tid; i < D * L; i += PF_P3P_BLOCK) {
     const unsigned v = sh[i];
@@ -626,33 +672,65 @@ __global__ void __launch_bounds__(PF_P3P_BLOCK, MINB) pf_p3p_hist_kernel(pf_p3p_
 
 size_t pf_p3p_smem_bytes(int D, int L)
 {
-  return (size_t)D * 16 + (size_t)D * L * 4 + (size_t)D * 4 + 16;
+  return (size_t)D * 16 + 16 + (size_t)D * L * 4 + (size_t)D * 4 + (size_t)(PF_P3P_NB + 1) * 4 + 16;
 }
 
-cudaError_t pf_p3p_launch_hist(const pf_p3p_params& p, cudaStream_t stream)
+template <int LT, int MODE>
+static void (*pf_p3p_pick(int occ))(pf_p3p_params, double2*, long long, long long)
+{
+  return occ >= 8 ? pf_p3p_hist_kernel<8, LT, MODE> : occ == 6 ? pf_p3p_hist_kernel<6, LT, MODE> : occ == 5 ? pf_p3p_hist_kernel<5, LT, MODE>
+       : occ == 4 ? pf_p3p_hist_kernel<4, LT, MODE> : pf_p3p_hist_kernel<3, LT, MODE>;
+}
+
+size_t pf_p3p_roots_bytes_per_thread(int L, int nchunk)
+{
+  const int nperm = L * (L - 1) * (L - 2);
+  return (size_t)((nperm + nchunk - 1) / nchunk) * 32;
+}
+
+// rbuf / rbuf_bytes: scratch for the roots (pf_p3p_roots_bytes_per_thread per thread of a slab), or nullptr / 0: one kernel
+cudaError_t pf_p3p_launch_hist(const pf_p3p_params& p, cudaStream_t stream, double2* rbuf, size_t rbuf_bytes)
 {
   const size_t smem = pf_p3p_smem_bytes(p.D, p.L);
-  // resident CTAs per SM = register budget 168 / 128 / 96: the kernel waits on FP64 dependency chains, so more
-  // warps beat fewer spills (measured, D = 205: 77.4 / 70.4 / 66.9 ms; D = 45: 0.90 / 0.74 / 0.81 ms).
-  // PFMPE_P3P_OCC = 3 | 4 | 5 overrides (tuning aid).
-  static int occ_env = -1;
+  // resident CTAs per SM = register budget 168 / 128 / 96 / 80 / 64: the kernel waits on FP64 dependency chains and on
+  // instruction fetch (80 KB of code), so more warps beat fewer spills (measured on one B200, D = 205: 44.8 / 39.4 / 38.7 /
+  // 36.5 / 36.1 ms for 3 / 4 / 5 / 6 / 8; D = 45: 0.51 / 0.45 / 0.48 / 0.52 / 0.41 ms).  PFMPE_P3P_OCC overrides (tuning aid).
+  // Tried and dropped: one out-of-line copy of the FP64 division / square root for the ~45 sites of the inner loop (code
+  // 5000 -> 4536 instructions, but 36.1 -> 38.2 ms: the calls cost more than the fetches they save).
+  static int occ_env = -1, occ_a_env = -1;
   if (occ_env < 0) { const char* e = getenv("PFMPE_P3P_OCC"); occ_env = e ? atoi(e) : 0; }
-  const int occ = occ_env ? occ_env : (p.D >= 100 ? 5 : 4);
-  void (*kern)(pf_p3p_params);
-  if (p.L == 5)
-    kern = occ >= 8 ? pf_p3p_hist_kernel<8, 5> : occ == 6 ? pf_p3p_hist_kernel<6, 5> : occ == 5 ? pf_p3p_hist_kernel<5, 5>
-         : occ == 4 ? pf_p3p_hist_kernel<4, 5> : pf_p3p_hist_kernel<3, 5>;
-  else
-    kern = occ >= 8 ? pf_p3p_hist_kernel<8, 0> : occ == 6 ? pf_p3p_hist_kernel<6, 0> : occ == 5 ? pf_p3p_hist_kernel<5, 0>
-         : occ == 4 ? pf_p3p_hist_kernel<4, 0> : pf_p3p_hist_kernel<3, 0>;
-  if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-  }
+  if (occ_a_env < 0) { const char* e = getenv("PFMPE_P3P_OCC_ROOTS"); occ_a_env = e ? atoi(e) : 0; }
+  const int occ = occ_env ? occ_env : 8;
+  const int occ_a = occ_a_env ? occ_a_env : occ;
+  const bool l5 = p.L == 5;
   const long long triples = (long long)p.D * (p.D - 1) * (p.D - 2) / 6;
   const long long threads = triples * p.nchunk;
   pf_p3p_prep_kernel<<<(p.D + 127) / 128 + 2, 128, 0, stream>>>(p);
-  kern<<<(unsigned)((threads + PF_P3P_BLOCK - 1) / PF_P3P_BLOCK), PF_P3P_BLOCK, smem, stream>>>(p);
+  const size_t per_thread = pf_p3p_roots_bytes_per_thread(p.L, p.nchunk);
+  long long slab = rbuf ? (long long)(rbuf_bytes / per_thread) : 0;
+  slab -= slab % PF_P3P_BLOCK;
+  if (slab < 8 * 148 * PF_P3P_BLOCK && slab < threads) slab = 0;      // less than a wave per launch: not worth it
+  auto prepare = [&](void (*k)(pf_p3p_params, double2*, long long, long long)) -> cudaError_t {
+    return smem > 48 * 1024 ? cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) : cudaSuccess;
+  };
+  if (slab == 0) {
+    auto kern = l5 ? pf_p3p_pick<5, 0>(occ) : pf_p3p_pick<0, 0>(occ);
+    cudaError_t e = prepare(kern);
+    if (e != cudaSuccess) return e;
+    kern<<<(unsigned)((threads + PF_P3P_BLOCK - 1) / PF_P3P_BLOCK), PF_P3P_BLOCK, smem, stream>>>(p, nullptr, 0, threads);
+    return cudaGetLastError();
+  }
+  auto ka = l5 ? pf_p3p_pick<5, 1>(occ_a) : pf_p3p_pick<0, 1>(occ_a);
+  auto kb = l5 ? pf_p3p_pick<5, 2>(occ) : pf_p3p_pick<0, 2>(occ);
+  cudaError_t e = prepare(ka);
+  if (e == cudaSuccess) e = prepare(kb);
+  if (e != cudaSuccess) return e;
+  for (long long g0 = 0; g0 < threads; g0 += slab) {
+    const long long n = threads - g0 < slab ? threads - g0 : slab;
+    const unsigned grid = (unsigned)((n + PF_P3P_BLOCK - 1) / PF_P3P_BLOCK);
+    ka<<<grid, PF_P3P_BLOCK, smem, stream>>>(p, rbuf, g0, n);
+    kb<<<grid, PF_P3P_BLOCK, smem, stream>>>(p, rbuf, g0, n);
+  }
   return cudaGetLastError();
 }
 

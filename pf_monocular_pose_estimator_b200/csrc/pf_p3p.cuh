@@ -56,7 +56,9 @@ struct pf_p3p_check_rec {
 // host-side launchers (pf_p3p.cu, compiled with -fmad=false: the reference is an x86-64 build without FMA
 // contraction, and the duplicate-solution test of :1659-1663 compares doubles for exact equality)
 size_t pf_p3p_smem_bytes(int D, int L);
-cudaError_t pf_p3p_launch_hist(const pf_p3p_params& p, cudaStream_t stream);   // prologue + vote, 2 kernels
+size_t pf_p3p_roots_bytes_per_thread(int L, int nchunk);
+// prologue + vote; with a roots buffer (rbuf, rbuf_bytes) the vote runs as roots kernel + back-projection kernel per slab
+cudaError_t pf_p3p_launch_hist(const pf_p3p_params& p, cudaStream_t stream, double2* rbuf = nullptr, size_t rbuf_bytes = 0);
 cudaError_t pf_p3p_launch_check(const pf_p3p_params& p, int M, int stride, const unsigned* corr, const int* counts,
                                 double certainty_threshold, pf_p3p_check_rec* out, cudaStream_t stream);
 cudaError_t pf_p3p_launch_solve(int n, const double* fv, const double* wp, double* sol, int* rc, cudaStream_t stream);

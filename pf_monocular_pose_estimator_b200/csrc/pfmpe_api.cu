@@ -168,6 +168,8 @@ struct pfmpe_handle {
   int sh_src = 0;                       // sharded: host mirror of the source-buffer selector (stage calls are issued in order)
   unsigned char* p3p_buf = nullptr;     // K9 scratch: detections, sorted copy, bearing vectors, counters, histogram
   size_t p3p_bytes = 0;
+  double2* p3p_roots = nullptr;         // K9: roots of the quartics of one slab of problems (two-kernel form of large votes)
+  size_t p3p_roots_bytes = 0;
   double* p3p_io = nullptr;             // batched solver scratch
   size_t p3p_io_bytes = 0;
   double *mc_part = nullptr, *mc_mean = nullptr;   // K7 (PFMPE_FLAG_MEAN_COV): per-block partials, mean poses
@@ -258,7 +260,7 @@ void free_all(pfmpe_handle* h)
   if (h->h_xtable) cudaFreeHost(h->h_xtable);
   cudaFree(h->peers_dev); cudaFree(h->scatter_cursor); cudaFree(h->mc_part); cudaFree(h->mc_mean); cudaFree(h->roi_keys); cudaFree(h->roi_out);
   if (h->h_roi) cudaFreeHost(h->h_roi);
-  cudaFree(h->p3p_buf); cudaFree(h->p3p_io); cudaFree(h->cksum);
+  cudaFree(h->p3p_buf); cudaFree(h->p3p_roots); cudaFree(h->p3p_io); cudaFree(h->cksum);
   cudaFree(h->rng_tab); cudaFree(h->timeline); cudaFree(h->warp_agg_g); cudaFree(h->shard_partial); cudaFree(h->gfill);
   if (h->seq.owned) { cudaFree(h->seq.blobs); cudaFree(h->seq.counts); cudaFree(h->seq.times); cudaFree(h->seq.seeds); }
   cudaFree(h->seq.result); cudaFree(h->seq.fc_log);
@@ -1691,8 +1693,25 @@ int p3p_histogram_impl(pfmpe_handle* h, int tracker, const double* image_points,
     PF_CUDA(h, cudaMemcpyAsync(d_img, image_points, (size_t)D * 2 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
     p.img = d_img;
   }
+  // Large votes run as two kernels per slab of threads (roots, then back-projection + votes; see pf_p3p_hist_kernel) through a
+  // roots buffer of 32 B per P3P problem, at most PFMPE_P3P_ROOTS_MB (default 3072; 0 = always the single kernel) of it, kept
+  // with the handle.  Below 2e6 problems the single kernel is as fast and needs no buffer.
+  static const long long roots_cap = [] { const char* e = std::getenv("PFMPE_P3P_ROOTS_MB"); return (e ? std::atoll(e) : 3072ll) << 20; }();
+  const size_t per_thread = pf_p3p_roots_bytes_per_thread(L, p.nchunk);
+  const long long n_threads = triples * p.nchunk;
+  size_t want_roots = 0;
+  if (roots_cap > 0 && n_threads * (long long)(per_thread / 32) >= 2000000ll) {
+    const unsigned long long all = (unsigned long long)n_threads * per_thread;
+    want_roots = (size_t)(all < (unsigned long long)roots_cap ? all : (unsigned long long)roots_cap);
+  }
+  if (want_roots > h->p3p_roots_bytes) {
+    PF_CUDA(h, cudaStreamSynchronize(h->stream));
+    cudaFree(h->p3p_roots); h->p3p_roots = nullptr; h->p3p_roots_bytes = 0;
+    PF_CUDA(h, cudaMalloc((void**)&h->p3p_roots, want_roots));
+    h->p3p_roots_bytes = want_roots;
+  }
   PF_CUDA(h, cudaEventRecord(h->ev0, h->stream));
-  PF_CUDA(h, pf_p3p_launch_hist(p, h->stream));
+  PF_CUDA(h, pf_p3p_launch_hist(p, h->stream, want_roots ? h->p3p_roots : nullptr, want_roots ? h->p3p_roots_bytes : 0));
   PF_CUDA(h, cudaEventRecord(h->ev1, h->stream));
   h->launches += 2;
   h->timing_valid = false;

@@ -57,7 +57,7 @@ def function_ranges(root):
     import os
     out = []
     pat = re.compile(r"^(?:template\s*<[^>]*>\s*)?(?:PF_HD|__device__|__global__|static|inline)[^;{]*?\b(pf_\w+)\s*\(")
-    for fn in ("pf_kernels.cuh", "pf_math.cuh", "pf_tail.cuh", "pf_tail_dev.cuh", "pf_meancov.cuh"):
+    for fn in ("pf_kernels.cuh", "pf_math.cuh", "pf_tail.cuh", "pf_tail_dev.cuh", "pf_meancov.cuh", "pf_p3p.cu"):
         p = os.path.join(root, "pf_monocular_pose_estimator_b200", "csrc", fn)
         if not os.path.exists(p):
             continue
