@@ -416,7 +416,7 @@ __device__ __forceinline__ long long pf_c2(long long m) { return m * (m - 1) / 2
 // One thread owns one detection triple (i0 < i1 < i2, lexicographic rank = its number) and a slice of the LED
 // permutations (p.nchunk slices per triple, so that small problems still fill the GPU): pre-filters and camera part
 // once, then per permutation the quartic, four back-substitutions, back-projection and votes.
-// dynamic shared memory: sxy [D] double2 | xb [2] double | hist [D*L] u32 | sid [D] int | first [PF_P3P_NB + 1] int
+// dynamic shared memory: sxy [D] double2 | xb [2] double | hist [D*L] u32 | sid [D] int | first [PF_P3P_NB + 1] int | sprev [12][threads] double
 // The detections near a projected LED are found through a bucket table over x (first[b] = the first sorted detection
 // whose bucket is >= b; bucket = a monotone function of x, so nothing left of first[bucket(x_lo)] can be >= x_lo)
 // instead of a binary search per projected LED: one shared-memory load in place of eight dependent ones.
@@ -446,6 +446,8 @@ __global__ void __launch_bounds__(PF_P3P_BLOCK, MINB) pf_p3p_hist_kernel(pf_p3p_
   int* sid = reinterpret_cast<int*>(sh + D * L);
   int* first = sid + D;
   const int tid = threadIdx.x;
+  // the previous solution of this thread's problem (duplicate rule, :1659-1663): [12][threads], behind the tables
+  double* sprev = reinterpret_cast<double*>(smem_raw + ((size_t)D * 16 + 16 + (size_t)D * L * 4 + (size_t)D * 4 + (size_t)(PF_P3P_NB + 1) * 4 + 15) / 16 * 16) + tid;
   for (int i = tid; i < D; i += PF_P3P_BLOCK) {
     sxy[i] = make_double2(p.simg[2 * i], p.simg[2 * i + 1]);
     sid[i] = p.sidx[i];
@@ -529,7 +531,9 @@ __global__ void __launch_bounds__(PF_P3P_BLOCK, MINB) pf_p3p_hist_kernel(pf_p3p_
     bool live = pass && pr < pr_end;
     int j0, j1, j2;
     pf_p3p_perm(live ? pr : 0, L, j0, j1, j2);
-    const pf_p3p_world W = p.wtab[2 * (live ? pr : 0) + Cc.swapped];
+    // the world part is read through the table (one 128-byte line, L1-resident) where it is used, not copied: 32 fewer
+    // live registers in a kernel that spills
+    const pf_p3p_world& W = p.wtab[2 * (live ? pr : 0) + Cc.swapped];
     live = live && W.colinear == 0.0;
     n_solved += (live && MODE != 1) ? 1u : 0u;
     double r0 = 0, r1 = 0, r2 = 0, r3 = 0;
@@ -551,21 +555,21 @@ __global__ void __launch_bounds__(PF_P3P_BLOCK, MINB) pf_p3p_hist_kernel(pf_p3p_
       continue;
     }
     __syncwarp();
-    double Sprev[12];
 #pragma unroll 1
     for (int k = 0; k < 4; ++k) {
       double S[12];
       bool use = false;
+      asm volatile("" ::: "memory");     // table entries are re-read per solution rather than kept across the loop
       if (live) {
         pf_p3p_backsub(Cc, W, k == 0 ? r0 : k == 1 ? r1 : k == 2 ? r2 : r3, S);
         bool skip = false;
         if (k > 0) {   // :1659-1663: a solution is dropped when ANY entry equals the previous solution's
 #pragma unroll
-          for (int e = 0; e < 12; ++e) skip |= (S[e] - Sprev[e] == 0.0);
+          for (int e = 0; e < 12; ++e) skip |= (S[e] - sprev[e * PF_P3P_BLOCK] == 0.0);
         }
         bool finite = true;   // isFinite(H) (:1670)
 #pragma unroll
-        for (int e = 0; e < 12; ++e) { finite &= ((S[e] - S[e]) == (S[e] - S[e])); Sprev[e] = S[e]; }
+        for (int e = 0; e < 12; ++e) { finite &= ((S[e] - S[e]) == (S[e] - S[e])); sprev[e * PF_P3P_BLOCK] = S[e]; }
         use = !skip && finite;
       }
       __syncwarp();
@@ -672,7 +676,7 @@ __global__ void __launch_bounds__(PF_P3P_BLOCK, MINB) pf_p3p_hist_kernel(pf_p3p_
 
 size_t pf_p3p_smem_bytes(int D, int L)
 {
-  return (size_t)D * 16 + 16 + (size_t)D * L * 4 + (size_t)D * 4 + (size_t)(PF_P3P_NB + 1) * 4 + 16;
+  return ((size_t)D * 16 + 16 + (size_t)D * L * 4 + (size_t)D * 4 + (size_t)(PF_P3P_NB + 1) * 4 + 15) / 16 * 16 + (size_t)12 * PF_P3P_BLOCK * 8;
 }
 
 template <int LT, int MODE>
@@ -708,8 +712,13 @@ cudaError_t pf_p3p_launch_hist(const pf_p3p_params& p, cudaStream_t stream, doub
   pf_p3p_prep_kernel<<<(p.D + 127) / 128 + 2, 128, 0, stream>>>(p);
   const size_t per_thread = pf_p3p_roots_bytes_per_thread(p.L, p.nchunk);
   long long slab = rbuf ? (long long)(rbuf_bytes / per_thread) : 0;
-  slab -= slab % PF_P3P_BLOCK;
-  if (slab < 8 * 148 * PF_P3P_BLOCK && slab < threads) slab = 0;      // less than a wave per launch: not worth it
+  if (slab >= threads) slab = threads;                                 // everything in one slab
+  else if (slab >= 8 * 148 * PF_P3P_BLOCK) {                           // equal slabs, whole CTAs
+    const long long cap = slab - slab % PF_P3P_BLOCK, n_slabs = (threads + cap - 1) / cap;
+    slab = (threads + n_slabs - 1) / n_slabs;
+    slab = (slab + PF_P3P_BLOCK - 1) / PF_P3P_BLOCK * PF_P3P_BLOCK;
+    if (slab > cap) slab = cap;
+  } else slab = 0;                                                     // less than a wave per launch: not worth it
   auto prepare = [&](void (*k)(pf_p3p_params, double2*, long long, long long)) -> cudaError_t {
     return smem > 48 * 1024 ? cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) : cudaSuccess;
   };
