@@ -496,8 +496,8 @@ def p3p_vote_measure(dev, with_cpu, n_detections=205, K=5, W=2):
            "e2e": {"value": solves / float(np.median(wall)), "unit": "P3P solves/s", "ms": 1e3 * float(np.median(wall)),
                    "h2d_bytes_per_step": int(img.nbytes), "d2h_bytes_per_step": int(hist.nbytes) + 32},
            "dtype": "f64", "votes": int(hist.sum()), "steps": K, "warmup": W,
-           "note": "pfmpe_p3p_histogram: FP64 Kneip P3P + back-projection + votes in one kernel (K9); bound by FP64 dependency chains and "
-                   "instruction fetch, not by memory (inputs 3 KB, output 4 KB): no HBM roofline applies"}
+           "note": "pfmpe_p3p_histogram: FP64 Kneip P3P (roots kernel) + back-projection + votes (vote kernel), K9; bound by FP64 dependency "
+                   "chains, not by memory (inputs 3 KB, output 4 KB, 2.7 GB of roots between the kernels): no HBM roofline applies"}
     if with_cpu:
         from oracle import orc
         sc2, img2, _ = vote_scene(40)
