@@ -219,3 +219,54 @@ def test_track_frame_device_batch_capped_objects_finished_by_host():
                         __file__ + "::test_track_frame_device_batch_matches_host_tail_batch"],
                        env=env, capture_output=True, text=True, timeout=600, cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+
+
+def _many_capped_inner():
+    """Body of the test below (runs in the child process, PFMPE_GN_CAP=1)."""
+    T, N, F = 2100, 128, 2
+    trackers = np.arange(T)
+    frames = list(range(2, 2 + F))
+    blobs, counts = S.blob_tensor_fast(trackers, frames, n_outliers=3)
+    seeds = np.array([[S.pf_seed(f, int(t)) for f in frames] for t in trackers], dtype=np.uint32)
+    hs = []
+    for _ in range(2):
+        h = capi.Handle(N, n_trackers=T, n_leds=5, max_blobs=blobs.shape[2])
+        h.configure(S.MARKERS_5, S.K_README, S.DEFAULT_PARAMS)
+        for t in trackers:
+            ph = S.tracker_phase(int(t))
+            h.track_init(S.true_pose(0.0, ph), 0.0, S.true_pose(S.DT, ph), S.DT, tracker=int(t))
+        hs.append(h)
+    ha, hb = hs
+    n_capped = 0
+    for k, f in enumerate(frames):
+        arr = (capi.TrackResult * T)()
+        ha._chk(capi.lib().pfmpe_track_frame_host_batch(ha._h, f * S.DT, capi._d(np.ascontiguousarray(blobs[:, k])),
+                np.ascontiguousarray(counts[:, k]).ctypes.data_as(capi.C.POINTER(capi.C.c_int32)),
+                np.ascontiguousarray(seeds[:, k]).ctypes.data_as(capi.C.POINTER(capi.C.c_uint32)), arr))
+        ra = ha._unpack_track(arr)
+        rb = hb.track_frame_device_batch(f * S.DT, blobs[:, k], counts[:, k], seeds[:, k])
+        for t in range(T):
+            a, b = ra[t], rb[t]
+            assert a["status"] == b["status"] and a["iterations"] == b["iterations"], (f, t)
+            assert (a["correspondences"] == b["correspondences"]).all() and a["most_likely_pose_idx"] == b["most_likely_pose_idx"]
+            if a["status"] == 1:
+                np.testing.assert_allclose(b["pose"], a["pose"], atol=1e-7, rtol=0)
+                if a["gn_iterations"] > 1 or a["gn_iterations"] < 0:
+                    assert a["gn_iterations"] == b["gn_iterations"]
+                    n_capped += 1
+    assert n_capped > 2048 * F * 0.9, n_capped      # more capped objects per frame than the packed list holds
+    ha.close()
+    hb.close()
+
+
+def test_track_frame_device_batch_more_capped_objects_than_the_packed_list_holds():
+    """2100 tracked objects, device Gauss-Newton capped at 1 iteration: every object is capped, the gather kernel's packed list
+    (2048 records) overflows and the host picks the capped objects out of the full record array instead."""
+    if os.environ.get("PFMPE_TEST_CHILD") == "many_capped":
+        _many_capped_inner()
+        return
+    env = dict(os.environ, PFMPE_GN_CAP="1", PFMPE_TEST_CHILD="many_capped")
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu", "-p", "no:cacheprovider",
+                        __file__ + "::test_track_frame_device_batch_more_capped_objects_than_the_packed_list_holds"],
+                       env=env, capture_output=True, text=True, timeout=900, cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
