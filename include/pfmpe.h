@@ -395,7 +395,9 @@ int pfmpe_shard_winner(pfmpe_handle* h, int local_index, pfmpe_frame_out* out);
  * iteration, resampling against the global strata, the peer-memory rebalance, a stream-ordered barrier, the winner record
  * from its owner.  `shards` are the handles of this process: one per process in a multi-GPU run (every rank makes the same
  * call with the same inputs and gets the same outputs), or all `world` logical shards of a single-GPU run (they must then
- * share one stream).  Needs pfmpe_shard_configure, pfmpe_shard_set_peers and pfmpe_shard_mail_set_peers on every shard. */
+ * share one stream).  Needs pfmpe_shard_configure, pfmpe_shard_set_peers and pfmpe_shard_mail_set_peers on every shard.
+ * Shards created with PFMPE_FLAG_MEAN_COV: out->mean_pose / mean_cov of the WHOLE filter (two more exchanges of 12 and 21
+ * partial sums through the mailboxes, added in rank order on every rank). */
 int pfmpe_shard_frame(pfmpe_handle* const* shards, int n_local, const pfmpe_frame_in* in, pfmpe_frame_out* out);
 /* The tracked frame around it, as pfmpe_track_frame_host does for an unsharded filter: predictPose (host, FP64), the
  * sharded PF update, optimiseAndUpdatePose + jump check (host, FP64); pfmpe_track_init on every shard first. */

@@ -47,20 +47,21 @@ __device__ __forceinline__ const float4* pf_mc_T(const pf_kparams& p, int trk)
   return (tb == 0 ? p.pose0 : p.pose1) + (size_t)trk * 3 * (size_t)p.pstride;
 }
 
-__device__ __forceinline__ double pf_mc_inv_sum(const pf_kparams& p, int trk)
+// S_all: the weight sum of the WHOLE filter when this handle holds one shard of it (0: this handle's own record)
+__device__ __forceinline__ double pf_mc_inv_sum(const pf_kparams& p, int trk, long long S_all)
 {
-  const long long s = p.result[trk].sum_fx;
+  const long long s = S_all != 0 ? S_all : p.result[trk].sum_fx;
   return s != 0 ? 1073741824.0 / (double)s : 1.0;    // probPart / probPartSum only if the sum is non-zero (:628)
 }
 
 // pass 1: partial sums of w t (3) and w R (9, row-major)
-__global__ void __launch_bounds__(PF_MC_THREADS) pf_meancov_pass1(const pf_kparams p, double* part)
+__global__ void __launch_bounds__(PF_MC_THREADS) pf_meancov_pass1(const pf_kparams p, double* part, long long S_all)
 {
   __shared__ double sm[8 * 12];
   const int trk = p.tracker_base + blockIdx.y, N = p.N;
   const float4* T = pf_mc_T(p, trk);
   const float* w = p.w + (size_t)trk * N;
-  const double inv = pf_mc_inv_sum(p, trk);
+  const double inv = pf_mc_inv_sum(p, trk, S_all);
   double acc[12];
 #pragma unroll
   for (int j = 0; j < 12; ++j) acc[j] = 0;
@@ -77,7 +78,7 @@ __global__ void __launch_bounds__(PF_MC_THREADS) pf_meancov_pass1(const pf_kpara
 // closest rotation (det +1) to the 3x3 matrix in rows 0..2 / columns 0..2 of m (row stride 4):
 // eigenvectors of M^T M by cyclic Jacobi, u_i = M v_i / sigma_i for the two largest, third columns
 // by cross products (det U = det V = +1), R = U V^T.
-__device__ inline void pf_mc_closest_rotation(const double* m, double* R /* row stride 4 */)
+__host__ __device__ inline void pf_mc_closest_rotation(const double* m, double* R /* row stride 4 */)
 {
   double S[3][3], V[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
   for (int i = 0; i < 3; ++i)
@@ -139,7 +140,7 @@ __global__ void pf_meancov_mean(const pf_kparams p, const double* part, int nblk
 }
 
 // pass 2: partial sums of w xi xi^T (21 unique terms, row-major upper triangle)
-__global__ void __launch_bounds__(PF_MC_THREADS) pf_meancov_pass2(const pf_kparams p, const double* mean, double* part)
+__global__ void __launch_bounds__(PF_MC_THREADS) pf_meancov_pass2(const pf_kparams p, const double* mean, double* part, long long S_all)
 {
   __shared__ double sm[8 * 21];
   __shared__ double mb[12];
@@ -148,7 +149,7 @@ __global__ void __launch_bounds__(PF_MC_THREADS) pf_meancov_pass2(const pf_kpara
   __syncthreads();
   const float4* T = pf_mc_T(p, trk);
   const float* w = p.w + (size_t)trk * N;
-  const double inv = pf_mc_inv_sum(p, trk);
+  const double inv = pf_mc_inv_sum(p, trk, S_all);
   double acc[21];
 #pragma unroll
   for (int j = 0; j < 21; ++j) acc[j] = 0;
@@ -188,6 +189,27 @@ __global__ void pf_meancov_cov(const pf_kparams p, const double* part, int nblk)
     int q = 0;
     for (int i = 0; i < 6; ++i)
       for (int j = i; j < 6; ++j) { p.result[trk].mean_cov[6 * i + j] = c[q]; p.result[trk].mean_cov[6 * j + i] = c[q]; ++q; }
+  }
+}
+
+// Sharded filter ("config 5: allreduce of 33 doubles"): this shard's K partial sums (12 after pass 1, 21 after
+// pass 2), combined in block order and sent to every rank's mailbox as the bit patterns of the doubles; the ranks' rows are
+// then added in rank order by the frame loop (pfmpe_shard_frame), identically on every rank.
+__global__ void pf_shard_mc_publish_kernel(const double* part, int nblk, int K, long long* const* peers, int world, int rank,
+                                           int slot, long long seq)
+{
+  __shared__ long long words[PF_XMAIL_WORDS];
+  if ((int)threadIdx.x < K) {
+    double s = 0;
+    for (int b = 0; b < nblk; ++b) s += part[(size_t)b * K + threadIdx.x];
+    words[threadIdx.x] = __double_as_longlong(s);
+  }
+  __syncthreads();
+  if ((int)threadIdx.x < world) {
+    long long* dst = peers[threadIdx.x] + ((size_t)slot * world + rank) * PF_XMAIL_WORDS;
+    for (int i = 0; i < K; ++i) dst[i] = words[i];
+    __threadfence_system();
+    *reinterpret_cast<volatile long long*>(dst + PF_XMAIL_WORDS - 1) = seq;
   }
 }
 

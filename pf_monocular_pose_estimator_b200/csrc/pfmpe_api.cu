@@ -358,9 +358,9 @@ int launch_meancov(pfmpe_handle* h, int t0, int nt)
   p.result = h->result;
   const dim3 grid((unsigned)h->mc_blocks, (unsigned)nt, 1);
   double* mean = h->mc_mean + (size_t)t0 * 12;
-  pf_meancov_pass1<<<grid, PF_MC_THREADS, 0, h->stream>>>(p, h->mc_part);
+  pf_meancov_pass1<<<grid, PF_MC_THREADS, 0, h->stream>>>(p, h->mc_part, 0ll);
   pf_meancov_mean<<<nt, 32, 0, h->stream>>>(p, h->mc_part, h->mc_blocks, mean);
-  pf_meancov_pass2<<<grid, PF_MC_THREADS, 0, h->stream>>>(p, mean, h->mc_part);
+  pf_meancov_pass2<<<grid, PF_MC_THREADS, 0, h->stream>>>(p, mean, h->mc_part, 0ll);
   pf_meancov_cov<<<nt, 32, 0, h->stream>>>(p, h->mc_part, h->mc_blocks);
   PF_CUDA(h, cudaGetLastError());
   h->launches += 4;
@@ -2281,6 +2281,37 @@ int pfmpe_shard_winner(pfmpe_handle* h, int local_index, pfmpe_frame_out* out)
 // accept, :666-688 resampling + winner): stage launches on every local shard, the 64-byte partials of ALL ranks arrive
 // in this process's mailbox by peer stores, and the decisions -- identical on every rank -- are taken here.
 namespace {
+// K7 on one shard: pass 1 (mean12 == nullptr: sums of w t and w R) or pass 2 (sums of w xi xi^T about the mean pose of the
+// whole filter) over this shard's particles, weights normalised by the weight sum S of the whole filter; the K partial sums
+// go to every rank's mailbox (one exchange: xseq advances)
+int shard_meancov_round(pfmpe_handle* h, const double* mean12, long long S)
+{
+  int rc = shard_ready(h);
+  if (rc) return rc;
+  if (!h->mc_part) return fail(h, PFMPE_ERR_STATE, "the handle was created without PFMPE_FLAG_MEAN_COV");
+  pf_kparams p;
+  fill_kparams(h, p);
+  p.tracker_base = 0;
+  p.result = h->result;
+  const dim3 grid((unsigned)h->mc_blocks, 1, 1);
+  const long long S_all = S != 0 ? S : (1ll << 30);    // zero sum: weights are left unnormalised (:628), 2^30 / 2^30 = 1
+  int K;
+  if (!mean12) {
+    pf_meancov_pass1<<<grid, PF_MC_THREADS, 0, h->stream>>>(p, h->mc_part, S_all);
+    K = 12;
+  } else {
+    PF_CUDA(h, cudaMemcpyAsync(h->mc_mean, mean12, 12 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    pf_meancov_pass2<<<grid, PF_MC_THREADS, 0, h->stream>>>(p, h->mc_mean, h->mc_part, S_all);
+    K = 21;
+  }
+  h->xseq += 1;
+  pf_shard_mc_publish_kernel<<<1, 64, 0, h->stream>>>(h->mc_part, h->mc_blocks, K, h->xmail_peers_dev, h->xworld, h->xrank,
+                                                      (int)(h->xseq % PF_XMAIL_RING), h->xseq);
+  PF_CUDA(h, cudaGetLastError());
+  h->launches += 2;
+  return PFMPE_OK;
+}
+
 inline float shard_unord(unsigned long long key_hi32)
 {
   unsigned o = (unsigned)key_hi32;
@@ -2431,6 +2462,33 @@ int pfmpe_shard_frame(pfmpe_handle* const* hs, int n_local, const pfmpe_frame_in
     for (int i = 0; i < 2 * PF_MAX_LED; ++i) out->correspondences[i] = i < 2 * nc ? pr[i] : 0u;
   }
   for (int i = 0; i < n_local; ++i) hs[i]->last_sum_fx[0] = S;
+  // ---- K7 (PFMPE_FLAG_MEAN_COV): weighted mean pose + covariance of the whole filter = two exchanges of 12 + 21 doubles
+  if (h0->cfg.flags & PFMPE_FLAG_MEAN_COV) {
+    double sum12[12], mean[12], sum21[21];
+    for (int pass = 0; pass < 2; ++pass) {
+      const int K = pass == 0 ? 12 : 21;
+      double* acc = pass == 0 ? sum12 : sum21;
+      for (int i = 0; i < n_local; ++i) if ((rc = shard_meancov_round(hs[i], pass == 0 ? nullptr : mean, S)) != PFMPE_OK) return rc;
+      if ((rc = pfmpe_shard_collect(h0, -1, table.data())) != PFMPE_OK) return rc;
+      for (int k = 0; k < K; ++k) acc[k] = 0.0;
+      for (int r = 0; r < W; ++r)                       // rank order: the same sum on every rank
+        for (int k = 0; k < K; ++k) {
+          double v;
+          std::memcpy(&v, &table[(size_t)r * PF_XMAIL_WORDS + k], sizeof v);
+          acc[k] += v;
+        }
+      if (pass == 0) {
+        pf_mc_closest_rotation(sum12, mean);
+        mean[3] = sum12[3]; mean[7] = sum12[7]; mean[11] = sum12[11];
+      }
+    }
+    pf_aff Tm;
+    for (int i = 0; i < 12; ++i) Tm.a[i] = mean[i];
+    pf_aff_to_cm16(Tm, out->mean_pose);
+    int q21 = 0;
+    for (int i = 0; i < 6; ++i)
+      for (int j = i; j < 6; ++j) { out->mean_cov[6 * i + j] = sum21[q21]; out->mean_cov[6 * j + i] = sum21[q21]; ++q21; }
+  }
   return PFMPE_OK;
 }
 

@@ -132,3 +132,27 @@ def test_sharded_tracking_loop_matches_unsharded():
     assert (ref.particles(1) == sh.particles(1)).all()
     ref.close()
     sh.close()
+
+
+@pytest.mark.parametrize("N,W", [(8192, 4), (200000, 2)])
+def test_sharded_weighted_mean_and_covariance(N, W):
+    """K7 under particle sharding (an exchange of 12 + 21 doubles): the weighted mean pose and covariance the
+    sharded C frame loop returns against the unsharded filter's (same particles and weights bit for bit; the sums are
+    taken in a different order, hence 1e-10) -- which tests/test_cuda_parity.py checks against the oracle."""
+    fi = frame_inputs(N, frame=9)
+    ref = make_handle(fi, N, flags=capi.FLAG_MEAN_COV)
+    sh = _make_sharded(fi, N, W, flags=capi.FLAG_MEAN_COV)
+    assert sh.loop == "c"
+    ref.set_particles(fi["E"])
+    sh.set_particles(fi["E"])
+    args = (fi["img"], fi["T_cur"], fi["T_pred"], fi["P"], fi["Cm"], fi["isi"], fi["dt"])
+    for f in range(3):
+        a = ref.update(*args, fi["seed"] + f)
+        b = sh.update(*args, fi["seed"] + f)
+        _same_frame(a, b, ref, sh)
+        assert np.abs(a["mean_pose"][:3, :3] @ a["mean_pose"][:3, :3].T - np.eye(3)).max() < 1e-12
+        np.testing.assert_allclose(b["mean_pose"], a["mean_pose"], rtol=0, atol=1e-10)
+        np.testing.assert_allclose(b["mean_cov"], a["mean_cov"], rtol=1e-8, atol=1e-16)
+        assert np.abs(a["mean_cov"]).max() > 0
+    ref.close()
+    sh.close()
