@@ -150,6 +150,31 @@ def test_pf_update_c_vs_numpy_twin(isi):
     assert a["rng_steps"] == 12 * (N - 2) + 2 * N
 
 
+@pytest.mark.parametrize("N,kw", [
+    (100, dict(frame=5)),                                   # BASELINE configs[0]: 100 particles, 15 detections, README parameters
+    (100, dict(frame=31, tracker=7)),                       # another trajectory phase (configs[3]'s per-tracker scenes)
+    (2500, dict(frame=9)),                                  # configs[1]'s scene at the size the twin's O(N^2) resampler finishes in seconds
+    (1200, dict(frame=12, n_outliers=200)),                 # configs[2]: 205 detections
+    (400, dict(frame=3, n_outliers=0)),                     # exactly the five true detections
+    (300, dict(frame=20, isi=1)),                           # the frame right after initialisation: full noise ranges, no resampling shortcut
+    (500, dict(frame=8, spread=(0.05, 0.05))),              # a wide particle cloud: many zero and negative scores
+])
+def test_pf_update_c_vs_numpy_twin_at_config_sizes(N, kw):
+    """The C oracle against the independent NumPy twin on every BASELINE scene at the largest size the twin's literal
+    resampling scan finishes in a few seconds (the oracle cannot be pinned to the reference, so its two
+    independent restatements are compared wherever that is feasible)."""
+    fi = frame_inputs(N, **kw)
+    a = _compare_with_twin(fi, N)
+    assert a["iterations"] >= 1
+
+
+def test_pf_update_c_vs_numpy_twin_four_leds():
+    from pf_monocular_pose_estimator_b200 import scenes as S
+    N = 300
+    fi = frame_inputs(N, frame=6, n_outliers=6, markers=S.MARKERS_4)
+    _compare_with_twin(fi, N)
+
+
 def test_pf_update_multi_iteration_c_vs_numpy_twin():
     # one LED occluded + outliers -> max score stays below L*min(5,D) -> all 80 iterations run (D7)
     N = 12
