@@ -933,7 +933,7 @@ __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, pf_ctx& cx, pf_t
   __syncwarp();
   pf_stamp(p, 7);
 
-  if (p.mode == 1) {
+  if (p.mode == 1 && !p.split_tail) {
     // ---- device tail (track mode): optimiseAndUpdatePose + next predictPose -------------
     pf_aff cur, prev;
 #pragma unroll
@@ -1007,7 +1007,7 @@ __device__ __noinline__ void pf_frame_tail(const pf_kparams& p, pf_ctx& cx, pf_t
     const uint32_t* s32 = reinterpret_cast<const uint32_t*>(&st);
     uint32_t* g32 = reinterpret_cast<uint32_t*>(p.state + trk);
     for (int i = lane; i < (int)(sizeof(pf_tracker_state) / 4); i += 32) g32[i] = s32[i];
-    if (p.mode == 1) {
+    if (p.mode == 1 && !p.split_tail) {
       const uint32_t* f32 = reinterpret_cast<const uint32_t*>(&cx.fc);
       uint32_t* h32 = reinterpret_cast<uint32_t*>(p.fconst + trk);
       for (int i = lane; i < (int)(sizeof(pf_frame_const) / 4); i += 32) h32[i] = f32[i];
@@ -1215,6 +1215,92 @@ __global__ void __launch_bounds__(V == 3 ? PF_BLOCK : PF_MAX_BLOCK, V == 3 ? 4 :
   if (p.coop == 1 && blockIdx.x == 0 && threadIdx.x == 0) {
     p.accum[3].maxkey = (unsigned long long)(bar.round % 3u);
     p.accum[3].minkey_inv = bar.done;
+  }
+}
+
+// Track mode, one frame per launch, a batch of filters (p.split_tail): the FP64 tail of pf_frame_tail as a kernel of its
+// own, ONE WARP PER FILTER instead of one warp of a 256-thread CTA whose other seven wait -- 4096 filters keep 4096 warps
+// busy instead of 592 CTA slots, and the FP64 code (a third of the fused kernel's 190 KB) stays out of the instruction
+// cache of the streaming stages.  Reads the frame's record (winner pose, correspondences, accept / resample flags) and
+// the tracker state the frame kernel mirrored to global memory; same arithmetic as the fused form (pf_gn_warp,
+// pf_predict_pose_dev), same results.
+#define PF_TAIL_WARPS 4
+template <int L>
+__global__ void __launch_bounds__(32 * PF_TAIL_WARPS) pf_track_tail_kernel(const __grid_constant__ pf_kparams p, int frame)
+{
+  __shared__ pf_tail_smem tsm[PF_TAIL_WARPS];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int trk = p.tracker_base + blockIdx.x * PF_TAIL_WARPS + warp;
+  if (trk >= p.tracker_base + p.tail_count) return;
+  pf_tail_smem& ts = tsm[warp];
+  pf_tracker_state* st = p.state + trk;
+  pf_frame_result* res = p.result + (size_t)trk * p.total_frames + frame;
+  if (res->status == 0) return;                          // track lost earlier: the frame kernel skipped this filter
+  const bool resampled = res->resampled != 0;
+  pf_pose Tw;
+#pragma unroll
+  for (int i = 0; i < 12; ++i) Tw.p[i] = res->winner_pose[i];
+  unsigned pairs[2 * L];
+#pragma unroll
+  for (int j = 0; j < 2 * L; ++j) pairs[j] = res->pairs[j];
+  const int npairs = res->npairs;
+  pf_aff cur, prev;
+#pragma unroll
+  for (int i = 0; i < 12; ++i) { cur.a[i] = st->cur[i]; prev.a[i] = st->prev[i]; }
+  double t_cur = st->t_cur, t_prev = st->t_prev;
+  const double t_pred = st->t_pred;
+  uint32_t isi = st->isi;
+  __syncwarp();
+  if (resampled) {
+    pf_aff pose = pf_aff_from_f32(Tw);                   // predicted_pose_ = PoseParticle[q]  (:687)
+    const pf_aff before = pose;
+    const double* img = p.blobs + ((size_t)trk * p.total_frames + frame) * (size_t)p.D_max * 2;
+    const int gn = pf_gn_warp<L>(p.K9d, p.obj_d + (size_t)trk * PF_MAX_LED * 3, img, pairs, npairs, pose, ts, lane, p.gn_cap);   // cov -> ts.M
+    if (isi < 2) ++isi;                                  // :2027-2030
+    prev = cur;                                          // updatePose :2013-2014
+    cur = pose;
+    if (t_pred - t_cur > 0.001 || t_pred < t_cur) { t_prev = t_cur; t_cur = t_pred; }   // :2016-2020
+    float flag = 1.0f;
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = 0; j < 3; ++j)
+        if (fabs(before.a[4 * i + j] - pose.a[4 * i + j]) >= 0.3) flag = 1.5f;           // :693-701
+    if (lane == 0) { res->flag_fail = flag; res->gn_iters = gn; }
+    for (int i = lane; i < 36; i += 32) {
+      const double c = ts.M[i];
+      st->cov[i] = c;
+      res->cov[i] = c;
+    }
+    if (lane == 0) {
+#pragma unroll
+      for (int i = 0; i < 12; ++i) st->pred[i] = pose.a[i];
+    }
+  } else {
+    isi = 0;                                             // :710
+    if (lane == 0) {
+      st->failed = 1;
+#pragma unroll
+      for (int i = 0; i < 12; ++i) st->pred[i] = (double)Tw.p[i];   // :716
+    }
+  }
+  if (lane == 0) {
+#pragma unroll
+    for (int i = 0; i < 12; ++i) { st->cur[i] = cur.a[i]; st->prev[i] = prev.a[i]; res->pose[i] = cur.a[i]; }
+    st->t_cur = t_cur; st->t_prev = t_prev; st->isi = isi;
+  }
+  if (resampled && frame + 1 < p.total_frames) {
+    const double t_next = p.times[frame + 1];
+    pf_aff P, predn;
+    pf_predict_pose_dev(prev, cur, t_prev, t_cur, t_next, P, predn);   // :234 -> :995-1010
+    const size_t fi = (size_t)trk * p.total_frames + frame + 1;
+    if (lane == 0) {
+      st->t_pred = t_next;
+#pragma unroll
+      for (int i = 0; i < 12; ++i) st->pred[i] = predn.a[i];
+      pf_make_frame_const(p.fconst[trk], cur, predn, P, pf_aff_identity(), isi, t_next - t_cur, p.seeds[fi],
+                          p.blob_count[fi], p.min_ang, p.max_ang, p.min_tr, p.max_tr);
+    }
   }
 }
 

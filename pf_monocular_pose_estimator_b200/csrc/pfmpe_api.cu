@@ -334,6 +334,20 @@ frames_kernel_t kernel_for_sh(int L)
   }
 }
 
+typedef void (*tail_kernel_t)(const pf_kparams, int);
+tail_kernel_t tail_kernel_for(int L)
+{
+  switch (L) {
+#ifndef PF_DEV_ONLY_L5
+    case 1: return pf_track_tail_kernel<1>; case 2: return pf_track_tail_kernel<2>; case 3: return pf_track_tail_kernel<3>;
+    case 4: return pf_track_tail_kernel<4>; case 6: return pf_track_tail_kernel<6>; case 7: return pf_track_tail_kernel<7>;
+    case 8: return pf_track_tail_kernel<8>;
+#endif
+    case 5: return pf_track_tail_kernel<5>;
+    default: return nullptr;
+  }
+}
+
 frames_kernel_t kernel_for(int L, int variant)
 {
   return variant == 1 ? kernel_for_sh<1>(L) : (variant == 2 ? kernel_for_sh<2>(L) : (variant == 3 ? kernel_for_sh<3>(L) : kernel_for_sh<0>(L)));
@@ -401,6 +415,13 @@ int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_f
   p.frame0 = frame0;
   p.n_frames = n_frames;
   p.gn_cap = mode == 1 ? h->gn_cap : 0;
+  // A tracked frame of a batch of filters, one frame per launch: the FP64 tail as a second kernel, one warp per filter
+  // (pf_track_tail_kernel; PFMPE_SPLIT_TAIL=0 keeps it inside the frame kernel).  Sequences of several frames per launch
+  // keep the fused form: there the tail's result feeds the next frame inside the same launch.
+  static const bool split_off = [] { const char* e = std::getenv("PFMPE_SPLIT_TAIL"); return e && std::atoi(e) == 0; }();
+  const bool split_tail = mode == 1 && n_frames == 1 && nt > 1 && !grid_mode && !split_off;
+  p.split_tail = split_tail ? 1 : 0;
+  p.tail_count = nt;
   if (sa) {
     p.pass_it = sa->pass_it; p.iters_total = sa->iters_total; p.q_local = sa->q_local; p.S_fx = sa->S_fx;
     for (int i = 0; i < 3; ++i) { p.rank_excl[i] = sa->excl[i]; p.rank_total[i] = sa->total[i]; }
@@ -518,6 +539,13 @@ int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_f
       else { k<<<grid, block, smem, h->stream>>>(p); PF_CUDA(h, cudaGetLastError()); }
       h->launches += 1;
     }
+  }
+  if (split_tail) {
+    p.tracker_base = t0;
+    tail_kernel_t tk = tail_kernel_for(h->cfg.n_leds);
+    tk<<<(unsigned)((nt + PF_TAIL_WARPS - 1) / PF_TAIL_WARPS), 32 * PF_TAIL_WARPS, 0, h->stream>>>(p, frame0);
+    PF_CUDA(h, cudaGetLastError());
+    h->launches += 1;
   }
   if (timed) PF_CUDA(h, cudaEventRecord(h->ev1, h->stream));
   h->timing_valid = timed;
