@@ -117,6 +117,46 @@ PF_HD pf_aff pf_exp_map(const double* tw)
   return T;
 }
 
+// exponentialMap for the Gauss-Newton update (:1876), where the twist is a correction step: the divisions of the reference
+// expressions (O / theta * sin, O^2 / theta^2 * (1 - cos), ...) are hoisted into one reciprocal, and below |omega| = 0.01 the
+// three coefficients come from their Taylor series in theta^2 (next omitted term < 1e-21 relative; also free of the
+// cancellation in (1 - cos theta) / theta^2).  Agrees with pf_exp_map to a few ulp; the dependent chain is several times shorter.
+PF_HD pf_aff pf_exp_map_step(const double* tw)
+{
+  const double wx = tw[3], wy = tw[4], wz = tw[5];
+  const double th2 = wx * wx + wy * wy + wz * wz;
+  double a, b, c;                                  // R = I + a O + b O^2 ; V = I + b O + c O^2
+  if (th2 < 1e-4) {
+    a = 1.0 + th2 * (-1.0 / 6.0 + th2 * (1.0 / 120.0 + th2 * (-1.0 / 5040.0 + th2 * (1.0 / 362880.0))));
+    b = 0.5 + th2 * (-1.0 / 24.0 + th2 * (1.0 / 720.0 + th2 * (-1.0 / 40320.0 + th2 * (1.0 / 3628800.0))));
+    c = 1.0 / 6.0 + th2 * (-1.0 / 120.0 + th2 * (1.0 / 5040.0 + th2 * (-1.0 / 362880.0 + th2 * (1.0 / 39916800.0))));
+  } else {
+    const double theta = sqrt(th2);
+    const double st = sin(theta), ct = cos(theta);
+    const double it = 1.0 / theta, it2 = it * it;
+    a = st * it; b = (1.0 - ct) * it2; c = (theta - st) * it2 * it;
+  }
+  const double O[9] = {0, -wz, wy, wz, 0, -wx, -wy, wx, 0};
+  double O2[9];
+  PF_UNROLL
+  for (int i = 0; i < 3; ++i)
+    PF_UNROLL
+    for (int j = 0; j < 3; ++j) O2[3 * i + j] = O[3 * i] * O[j] + O[3 * i + 1] * O[3 + j] + O[3 * i + 2] * O[6 + j];
+  pf_aff T;
+  PF_UNROLL
+  for (int i = 0; i < 3; ++i) {
+    double V[3];
+    PF_UNROLL
+    for (int j = 0; j < 3; ++j) {
+      const double id = i == j ? 1.0 : 0.0;
+      T.a[4 * i + j] = id + a * O[3 * i + j] + b * O2[3 * i + j];
+      V[j] = id + b * O[3 * i + j] + c * O2[3 * i + j];
+    }
+    T.a[4 * i + 3] = V[0] * tw[0] + V[1] * tw[1] + V[2] * tw[2];
+  }
+  return T;
+}
+
 // logarithmMap (:2228-2296), including Eigen's isApprox / isApproxToConstant tests
 PF_HD void pf_log_map(const pf_aff& T, double* xi)
 {
@@ -272,6 +312,77 @@ PF_HD void pf_inv6(const double* A, double* Ai)
   }
 }
 
+// ---- 6x6 SPD system in 3x3 blocks ------------------------------------------------------------
+// A = [P Q; Q^T R] (symmetric positive definite normal matrix of the Gauss-Newton step).
+// inv(P) and inv(S), S = R - Q^T inv(P) Q, by cofactors: two reciprocals on the critical path
+// instead of six pivots (the reference solves with Eigen's pivoted LDL^T, :1872; same solution up
+// to rounding).  Device: evaluated redundantly by every lane from the shared-memory copy of A; host: pf_optimise_pose.
+// pf_blk6_factor returns false when a block is singular (the host form then takes the pivoted LDL^T for that step).
+struct pf_blk6 { double Pi[6], W[9], Si[6]; };     // symmetric 3x3 stored as 00 01 02 11 12 22
+
+PF_HD bool pf_sym3_inv(const double* m, double* o)
+{
+  const double c00 = m[3] * m[5] - m[4] * m[4], c01 = m[2] * m[4] - m[1] * m[5], c02 = m[1] * m[4] - m[2] * m[3];
+  const double id = 1.0 / (m[0] * c00 + m[1] * c01 + m[2] * c02);
+  o[0] = c00 * id; o[1] = c01 * id; o[2] = c02 * id;
+  o[3] = (m[0] * m[5] - m[2] * m[2]) * id; o[4] = (m[1] * m[2] - m[0] * m[4]) * id;
+  o[5] = (m[0] * m[3] - m[1] * m[1]) * id;
+  return id - id == 0.0;                                 // false: singular block (1 / 0) or NaN
+}
+#define PF_S3(m, i, j) ((m)[(i) <= (j) ? ((i) == 0 ? (j) : ((i) == 1 ? 2 + (j) : 5)) : ((j) == 0 ? (i) : ((j) == 1 ? 2 + (i) : 5))])
+
+PF_HD bool pf_blk6_factor(const double* A, pf_blk6& f)
+{
+  const double P[6] = {A[0], A[1], A[2], A[7], A[8], A[14]};
+  const bool okP = pf_sym3_inv(P, f.Pi);
+PF_UNROLL
+  for (int i = 0; i < 3; ++i)
+PF_UNROLL
+    for (int j = 0; j < 3; ++j)   // W = inv(P) Q,  Q(k,j) = A[6k + 3 + j]
+      f.W[3 * i + j] = PF_S3(f.Pi, i, 0) * A[3 + j] + PF_S3(f.Pi, i, 1) * A[9 + j] + PF_S3(f.Pi, i, 2) * A[15 + j];
+  double S[6];
+  int t = 0;
+PF_UNROLL
+  for (int i = 0; i < 3; ++i)
+PF_UNROLL
+    for (int j = i; j < 3; ++j, ++t)   // S = R - Q^T W
+      S[t] = A[6 * (3 + i) + 3 + j] - (A[3 + i] * f.W[j] + A[9 + i] * f.W[3 + j] + A[15 + i] * f.W[6 + j]);
+  return pf_sym3_inv(S, f.Si) && okP;
+}
+
+PF_HD void pf_blk6_solve(const pf_blk6& f, const double* A, const double* b, double* x)
+{
+  double y1[3], r2[3];
+PF_UNROLL
+  for (int i = 0; i < 3; ++i) y1[i] = PF_S3(f.Pi, i, 0) * b[0] + PF_S3(f.Pi, i, 1) * b[1] + PF_S3(f.Pi, i, 2) * b[2];
+PF_UNROLL
+  for (int i = 0; i < 3; ++i) r2[i] = b[3 + i] - (A[3 + i] * y1[0] + A[9 + i] * y1[1] + A[15 + i] * y1[2]);
+PF_UNROLL
+  for (int i = 0; i < 3; ++i) x[3 + i] = PF_S3(f.Si, i, 0) * r2[0] + PF_S3(f.Si, i, 1) * r2[1] + PF_S3(f.Si, i, 2) * r2[2];
+PF_UNROLL
+  for (int i = 0; i < 3; ++i) x[i] = y1[i] - (f.W[3 * i] * x[3] + f.W[3 * i + 1] * x[4] + f.W[3 * i + 2] * x[5]);
+}
+
+// inv(A) = [inv(P) + W Si W^T, -W Si; -Si W^T, Si]  -> cov (row-major 6x6)
+PF_HD void pf_blk6_inverse(const pf_blk6& f, double* cov)
+{
+  double WS[9];
+PF_UNROLL
+  for (int i = 0; i < 3; ++i)
+PF_UNROLL
+    for (int j = 0; j < 3; ++j)
+      WS[3 * i + j] = f.W[3 * i] * PF_S3(f.Si, 0, j) + f.W[3 * i + 1] * PF_S3(f.Si, 1, j) + f.W[3 * i + 2] * PF_S3(f.Si, 2, j);
+PF_UNROLL
+  for (int i = 0; i < 3; ++i)
+PF_UNROLL
+    for (int j = 0; j < 3; ++j) {
+      cov[6 * i + j] = PF_S3(f.Pi, i, j) + (WS[3 * i] * f.W[3 * j] + WS[3 * i + 1] * f.W[3 * j + 1] + WS[3 * i + 2] * f.W[3 * j + 2]);
+      cov[6 * i + 3 + j] = -WS[3 * i + j];
+      cov[6 * (3 + j) + i] = -WS[3 * i + j];
+      cov[6 * (3 + i) + 3 + j] = PF_S3(f.Si, i, j);
+    }
+}
+
 // optimisePose (:1805-2009).  K9 row-major; obj: L x 3 doubles; img: D x 2 doubles;
 // pairs: npairs x (LED+1, blob+1).  pose in/out.  cov: 6x6 (symmetric; row-major == col-major
 // up to rounding).  Returns PubData.numIter (-1 when max_itr is hit).
@@ -286,6 +397,8 @@ PF_HD int pf_optimise_pose(const double* K9, const double* obj, const double* im
   double A[36], b[6], dT[6];
   PF_UNROLL
   for (int i = 0; i < 36; ++i) A[i] = 0.0;
+  pf_blk6 f;
+  bool blocks = false;
   int reported = -1;
   for (int it = 0; it < max_itr; ++it) {
     PF_UNROLL
@@ -304,29 +417,38 @@ PF_HD int pf_optimise_pose(const double* K9, const double* obj, const double* im
       const double p0 = K9[0] * x + K9[1] * y + K9[2] * z;
       const double p1 = K9[3] * x + K9[4] * y + K9[5] * z;
       const double p2 = K9[6] * x + K9[7] * y + K9[8] * z;
-      const double ex = img[2 * (det - 1)] - p0 / p2, ey = img[2 * (det - 1) + 1] - p1 / p2;
-      const double en = sqrt(ex * ex + ey * ey);
-      if (it == 0) e_first = en;                 // `=+` in the reference: last pair wins (:1859)
-      else if (it + 1 == max_itr) e_last = en;   // :1861
-      const double z2 = z * z;
-      const double J0[6] = {1 / z * fx, 0, -x / z2 * fx, -x * y / z2 * fx, (1 + (x * x / z2)) * fx, -y / z * fx};
-      const double J1[6] = {0, 1 / z * fy, -y / z2 * fy, -(1 + y * y / z2) * fy, x * y / z2 * fy, x / z * fy};
+      const double ip2 = 1.0 / p2, iz = 1.0 / z;
+      const double ex = img[2 * (det - 1)] - p0 * ip2, ey = img[2 * (det - 1) + 1] - p1 * ip2;
+      if (it == 0) e_first = sqrt(ex * ex + ey * ey);                 // `=+` in the reference: last pair wins (:1859)
+      else if (it + 1 == max_itr) e_last = sqrt(ex * ex + ey * ey);   // :1861
+      // computeJacobian (:2163-2192) with 1/z formed once (as the device form, pf_gn_warp)
+      const double xz = x * iz, yz = y * iz;
+      const double J0[6] = {fx * iz, 0, -fx * xz * iz, -fx * xz * yz, fx * (1.0 + xz * xz), -fx * yz};
+      const double J1[6] = {0, fy * iz, -fy * yz * iz, -fy * (1.0 + yz * yz), fy * xz * yz, fy * xz};
       PF_UNROLL
       for (int r = 0; r < 6; ++r) {
         PF_UNROLL
-        for (int c = 0; c < 6; ++c) A[6 * r + c] += J0[r] * J0[c] + J1[r] * J1[c];
+        for (int c = r; c < 6; ++c) A[6 * r + c] += J0[r] * J0[c] + J1[r] * J1[c];   // upper triangle, mirrored below
         b[r] += J0[r] * ex + J1[r] * ey;
       }
     }
-    pf_ldlt6_solve(A, b, dT);
-    pose = pf_aff_mul(pf_exp_map(dT), pose);   // :1876
+    PF_UNROLL
+    for (int r = 1; r < 6; ++r) {
+      PF_UNROLL
+      for (int c = 0; c < r; ++c) A[6 * r + c] = A[6 * c + r];
+    }
+    // A.ldlt().solve(b) (:1872): in 3x3 blocks like the device form (a third of the time of the pivoted LDL^T, the same
+    // solution up to rounding); a singular block (degenerate correspondences) takes the pivoted LDL^T, which skips zero pivots
+    blocks = pf_blk6_factor(A, f);
+    if (blocks) pf_blk6_solve(f, A, b, dT); else pf_ldlt6_solve(A, b, dT);
+    pose = pf_aff_mul(pf_exp_map_step(dT), pose);   // :1876
     double nm = -1;
     PF_UNROLL
     for (int i = 0; i < 6; ++i) { double v = fabs(dT[i]); if (v > nm) nm = v; }
     if (nm <= conv) { reported = it; break; }
     if (it + 1 == max_itr && e_first < e_last) pose = pose0;   // :1886-1892
   }
-  pf_inv6(A, cov);
+  if (blocks) pf_blk6_inverse(f, cov); else pf_inv6(A, cov);   // pose_covariance_ = A.inverse() (:2004)
   return reported;
 }
 

@@ -126,74 +126,8 @@ __device__ __forceinline__ void pf_predict_pose_dev(const pf_aff& prev, const pf
   pred = pf_aff_mul(cur, P);
 }
 
-// ---- 6x6 SPD system in 3x3 blocks ------------------------------------------------------------
-// A = [P Q; Q^T R] (symmetric positive definite normal matrix of the Gauss-Newton step).
-// inv(P) and inv(S), S = R - Q^T inv(P) Q, by cofactors: two reciprocals on the critical path
-// instead of six pivots (the reference solves with Eigen's pivoted LDL^T, :1872; same solution up
-// to rounding).  Evaluated redundantly by every lane from the shared-memory copy of A.
-struct pf_blk6 { double Pi[6], W[9], Si[6]; };     // symmetric 3x3 stored as 00 01 02 11 12 22
-
-__device__ __forceinline__ void pf_sym3_inv(const double* m, double* o)
-{
-  const double c00 = m[3] * m[5] - m[4] * m[4], c01 = m[2] * m[4] - m[1] * m[5], c02 = m[1] * m[4] - m[2] * m[3];
-  const double id = 1.0 / (m[0] * c00 + m[1] * c01 + m[2] * c02);
-  o[0] = c00 * id; o[1] = c01 * id; o[2] = c02 * id;
-  o[3] = (m[0] * m[5] - m[2] * m[2]) * id; o[4] = (m[1] * m[2] - m[0] * m[4]) * id;
-  o[5] = (m[0] * m[3] - m[1] * m[1]) * id;
-}
-#define PF_S3(m, i, j) ((m)[(i) <= (j) ? ((i) == 0 ? (j) : ((i) == 1 ? 2 + (j) : 5)) : ((j) == 0 ? (i) : ((j) == 1 ? 2 + (i) : 5))])
-
-__device__ __forceinline__ void pf_blk6_factor(const double* A, pf_blk6& f)
-{
-  const double P[6] = {A[0], A[1], A[2], A[7], A[8], A[14]};
-  pf_sym3_inv(P, f.Pi);
-#pragma unroll
-  for (int i = 0; i < 3; ++i)
-#pragma unroll
-    for (int j = 0; j < 3; ++j)   // W = inv(P) Q,  Q(k,j) = A[6k + 3 + j]
-      f.W[3 * i + j] = PF_S3(f.Pi, i, 0) * A[3 + j] + PF_S3(f.Pi, i, 1) * A[9 + j] + PF_S3(f.Pi, i, 2) * A[15 + j];
-  double S[6];
-  int t = 0;
-#pragma unroll
-  for (int i = 0; i < 3; ++i)
-#pragma unroll
-    for (int j = i; j < 3; ++j, ++t)   // S = R - Q^T W
-      S[t] = A[6 * (3 + i) + 3 + j] - (A[3 + i] * f.W[j] + A[9 + i] * f.W[3 + j] + A[15 + i] * f.W[6 + j]);
-  pf_sym3_inv(S, f.Si);
-}
-
-__device__ __forceinline__ void pf_blk6_solve(const pf_blk6& f, const double* A, const double* b, double* x)
-{
-  double y1[3], r2[3];
-#pragma unroll
-  for (int i = 0; i < 3; ++i) y1[i] = PF_S3(f.Pi, i, 0) * b[0] + PF_S3(f.Pi, i, 1) * b[1] + PF_S3(f.Pi, i, 2) * b[2];
-#pragma unroll
-  for (int i = 0; i < 3; ++i) r2[i] = b[3 + i] - (A[3 + i] * y1[0] + A[9 + i] * y1[1] + A[15 + i] * y1[2]);
-#pragma unroll
-  for (int i = 0; i < 3; ++i) x[3 + i] = PF_S3(f.Si, i, 0) * r2[0] + PF_S3(f.Si, i, 1) * r2[1] + PF_S3(f.Si, i, 2) * r2[2];
-#pragma unroll
-  for (int i = 0; i < 3; ++i) x[i] = y1[i] - (f.W[3 * i] * x[3] + f.W[3 * i + 1] * x[4] + f.W[3 * i + 2] * x[5]);
-}
-
-// inv(A) = [inv(P) + W Si W^T, -W Si; -Si W^T, Si]  -> cov (row-major 6x6)
-__device__ __forceinline__ void pf_blk6_inverse(const pf_blk6& f, double* cov)
-{
-  double WS[9];
-#pragma unroll
-  for (int i = 0; i < 3; ++i)
-#pragma unroll
-    for (int j = 0; j < 3; ++j)
-      WS[3 * i + j] = f.W[3 * i] * PF_S3(f.Si, 0, j) + f.W[3 * i + 1] * PF_S3(f.Si, 1, j) + f.W[3 * i + 2] * PF_S3(f.Si, 2, j);
-#pragma unroll
-  for (int i = 0; i < 3; ++i)
-#pragma unroll
-    for (int j = 0; j < 3; ++j) {
-      cov[6 * i + j] = PF_S3(f.Pi, i, j) + (WS[3 * i] * f.W[3 * j] + WS[3 * i + 1] * f.W[3 * j + 1] + WS[3 * i + 2] * f.W[3 * j + 2]);
-      cov[6 * i + 3 + j] = -WS[3 * i + j];
-      cov[6 * (3 + j) + i] = -WS[3 * i + j];
-      cov[6 * (3 + i) + 3 + j] = PF_S3(f.Si, i, j);
-    }
-}
+// (the 6x6 SPD solve in 3x3 blocks -- pf_blk6_factor / pf_blk6_solve / pf_blk6_inverse -- lives in pf_tail.cuh: the host form
+// of the Gauss-Newton uses it too)
 
 // Correspondences of one pose by the whole warp (calculateEstimationProbability :2385-2445 for the
 // winner): lane i scans blobs i, i+32, ...; per LED the (distance, blob index) minimum is combined
