@@ -252,7 +252,10 @@ int pfmpe_predict_roi(pfmpe_handle* h, int tracker, const double cam_move_inv[16
  * back_projection_pixel_tolerance are the handle's.  hist: n x n_leds, row-major = hist_corr(detection, LED);
  * the caller feeds it to correspondencesFromHistogram (:1134-1288) / checkCorrespondences (:1312-1501)
  * unchanged.  Counts are integers: identical to the reference except where a vote sits within rounding of
- * the tolerance or a conjugate root pair collapses within rounding. */
+ * the tolerance or a conjugate root pair collapses within rounding.
+ * Device memory: a few KB of tables per handle, plus -- for votes of 2e6 P3P problems and more (about 60 detections with
+ * 5 LEDs) -- a buffer of 32 B per problem for the roots between the vote's two kernels, allocated on first use, kept with
+ * the handle and capped at PFMPE_P3P_ROOTS_MB (environment, default 3072; larger votes run in slabs, 0 = never: one kernel). */
 typedef struct {
   uint64_t triples;             /* detection triples that pass the pre-filters (:1561-1581)            */
   uint64_t p3p_solved;          /* computePoses calls that returned 0                                  */
