@@ -90,24 +90,51 @@ def profiled_traffic(workload):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    """SM clock / throttle reasons sampled DURING the timed region: NVML in-process every 2 ms (a timed region of ~0.1 s
+    would see one or two nvidia-smi invocations), nvidia-smi as the fallback."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, gpu):
-        self.gpu, self.rows, self._stop = gpu, [], threading.Event()
+        self.gpu, self.rows, self._stop = gpu, [], threading.Event()   # rows: (sm MHz, max MHz, set of reasons)
+        self.source = "nvidia-smi"
+        self.nv = self.dev = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv, self.dev, self.source = pynvml, pynvml.nvmlDeviceGetHandleByIndex(gpu), "nvml"
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.dev, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.nv = None
         self.th = threading.Thread(target=self._run, daemon=True)
+
+    def _nvml_sample(self):
+        nv = self.nv
+        mhz = float(nv.nvmlDeviceGetClockInfo(self.dev, nv.NVML_CLOCK_SM))
+        get = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        bits = int(get(self.dev))
+        masks = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
+        self.rows.append((mhz, self.max_mhz, {n for n, m in masks.items() if bits & m}))
+
+    def _smi_sample(self):
+        out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
+                             capture_output=True, text=True, timeout=5).stdout.strip()
+        if out:
+            r = [c.strip() for c in out.split(",")]
+            self.rows.append((float(r[1]), float(r[2]), {nm for i, nm in enumerate(self.NAMES) if len(r) > 5 + i and r[5 + i].lower().startswith("active")}))
 
     def _run(self):
         while not self._stop.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([c.strip() for c in out.split(",")])
+                if self.nv is not None:
+                    self._nvml_sample()
+                else:
+                    self._smi_sample()
             except Exception:
-                pass
-            self._stop.wait(0.1)
+                if self.nv is not None:          # NVML query not supported here: fall back for the rest of the run
+                    self.nv, self.source = None, "nvidia-smi"
+            self._stop.wait(0.002 if self.nv is not None else 0.1)
 
     def __enter__(self):
         self.th.start()
@@ -120,15 +147,12 @@ class ClockSampler:
     def summary(self):
         if not self.rows:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
-        sm = sorted(float(r[1]) for r in self.rows)
+        sm = sorted(r[0] for r in self.rows)
         reasons = set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for r in self.rows:
-            for i, nm in enumerate(names):
-                if len(r) > 5 + i and r[5 + i].lower().startswith("active"):
-                    reasons.add(nm)
-        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][2]), "reasons": sorted(reasons),
-                "samples": len(self.rows)}
+            reasons |= r[2]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_min_mhz": sm[0], "sm_max_mhz": self.rows[0][1], "reasons": sorted(reasons),
+                "samples": len(self.rows), "source": self.source}
 
 
 def make_sequence(trackers, first_frame, n_frames, n_outliers):
