@@ -1497,7 +1497,7 @@ static int track_frames_device(pfmpe_handle* h, double time_to_predict, const do
     pf_track_prepare_kernel<<<(T + 127) / 128, 128, 0, h->stream>>>(p, 0);      // predictPose (:234 -> :995-1010) per tracker
     rc = cudaGetLastError() == cudaSuccess ? PFMPE_OK : PFMPE_ERR_CUDA;
     h->launches += 1;
-    // Gauss-Newton on the device for at most gn_cap iterations (PFMPE_GN_CAP, default 64: one object in ~300 goes beyond; 0 = the full 500): objects
+    // Gauss-Newton on the device for at most gn_cap iterations (PFMPE_GN_CAP, default 64: about one object in 110 goes beyond on the bench scene; 0 = the full 500): objects
     // still iterating then are finished by the host below
     static const int cap_env = [] { const char* e = std::getenv("PFMPE_GN_CAP"); return e ? std::atoi(e) : 64; }();
     h->gn_cap = cap_env;
