@@ -127,6 +127,7 @@ struct pf_kparams {
   int done_seq;                   // != 0: the result record lives in pinned host memory; published last, after a system fence
   int gn_cap;                     // track mode: > 0 caps the device Gauss-Newton (gn_iters = -2: the host finishes the object)
   int split_tail;                 // track mode, one frame per launch, batch shape: the FP64 tail runs as pf_track_tail_kernel (one warp per filter)
+  int prefetch;                   // score pass: prefetch the next step's source rows into L1
   int tail_count;                 // ... over the filters [tracker_base, tracker_base + tail_count)
   pf_frame_const fc_inline;
   double blobs_inline[2 * PF_INLINE_BLOBS];

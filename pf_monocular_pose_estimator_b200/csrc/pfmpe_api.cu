@@ -422,6 +422,8 @@ int launch_frames(pfmpe_handle* h, int mode, int t0, int nt, int frame0, int n_f
   const bool split_tail = mode == 1 && n_frames == 1 && nt > 1 && !grid_mode && !split_off;
   p.split_tail = split_tail ? 1 : 0;
   p.tail_count = nt;
+  static const bool prefetch_off = [] { const char* e = std::getenv("PFMPE_PREFETCH"); return e && std::atoi(e) == 0; }();   // A/B
+  p.prefetch = prefetch_off ? 0 : 1;
   if (sa) {
     p.pass_it = sa->pass_it; p.iters_total = sa->iters_total; p.q_local = sa->q_local; p.S_fx = sa->S_fx;
     for (int i = 0; i < 3; ++i) { p.rank_excl[i] = sa->excl[i]; p.rank_total[i] = sa->total[i]; }
