@@ -474,7 +474,11 @@ def sharded_filter_measure(world, rank, dev, local_rank, barrier, allreduce, RO,
     wall = time.perf_counter() - t0
     barrier()
     passes = sf.passes - p0
-    checks = sf.state_checksums()                       # device-side, position-keyed: comparable with the unsharded filter's
+    checks = sf.state_checksums()                       # device-side, position-keyed: this rank's share
+    if world > 1:                                       # the filter's checksum = the ranks' shares added mod 2^64 (int64 addition wraps):
+        t = torch.tensor([c - (1 << 64) if c >= (1 << 63) else c for c in checks], dtype=torch.int64, device="cuda:%d" % local_rank)
+        torch.distributed.all_reduce(t)                 # the same three words at every --gpus N, and for the unsharded filter
+        checks = [int(v) & 0xFFFFFFFFFFFFFFFF for v in t.cpu()]
     (ms,) = allreduce([max(e0.elapsed_time(e1), 0.0)], RO.MAX if RO else None)
     (wall,) = allreduce([wall], RO.MAX if RO else None)
     (okf,) = allreduce([1.0 if ok else 0.0], RO.MIN if RO else None)
@@ -497,6 +501,8 @@ def sharded_filter_measure(world, rank, dev, local_rank, barrier, allreduce, RO,
             "e2e": {"value": pme / wall, "unit": "PME/s", "h2d_bytes_per_step": 224 + 16 * nblob, "d2h_bytes_per_step": 808,
                     "note": "this sub-line IS the end-to-end figure: host detections in, pose + covariance out, every frame"},
             "state_checksums": ["%016x" % c for c in checks],
+            "state_checksums_note": "position-keyed checksums of weights / propagated set / resampled set of the WHOLE filter after the last frame "
+                                    "(ranks' shares added mod 2^64): identical at every --gpus N = the sharded filter is bit-identical across world sizes",
             "exchange": "64-byte partials by NVLink peer stores into every rank's mailbox (no NCCL call in the frame loop); rebalance = %s"
                         % ("one scatter kernel, local + NVLink peer stores (CUDA IPC)" if rebalance == "p2p" else "row export + all_to_all + import"),
             "rebalance": rebalance, "host_loop": loop,
